@@ -1,0 +1,323 @@
+/* TEST INFRASTRUCTURE -- NOT PRODUCT CODE.
+ *
+ * CPU restatement of the reference's GMM emission-scoring algorithms (3dimaging/rasr, src/Mm), in
+ * plain C, used only as the checker by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs.  The product (rasr_b200/) never imports, links or executes this file.
+ *
+ * Parity status: PINNED against the reference itself.  The reference ships no golden vector for any
+ * Mm scorer, so the pin is the unmodified reference classes compiled by
+ * oracle/ref_build/Makefile into oracle/_ref/ref_scorer and run in the build container:
+ * tests/test_oracle_vs_ref.py compares every function below with it, and tests/golden/ holds outputs
+ * of that binary (generator: tests/golden/make_golden.py).
+ *
+ * Compile WITHOUT -ffast-math: every operation is written in the order the reference binary executes
+ * it (its -ffast-math build was inspected by disassembly where the source leaves the order open).
+ *
+ * Each function cites the reference file:line it follows (paths relative to /root/reference/src/Mm).
+ */
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <xmmintrin.h>
+
+typedef struct {
+    uint32_t        D, M, nDens, nMeans, nCov;
+    const uint32_t* mixOffsets;   /* [M+1] */
+    const uint32_t* mixDensity;   /* [G]   density index per (mixture, k) */
+    const double*   mixLogWeight; /* [G]   */
+    const uint32_t* densMean;     /* [nDens] */
+    const uint32_t* densCov;      /* [nDens] */
+    const float*    means;        /* [nMeans x D] */
+    const float*    variances;    /* [nCov x D]   */
+} orc_model;
+
+/* ---------------------------------------------------------------------------------------------
+ * Table preparation
+ * ------------------------------------------------------------------------------------------- */
+
+/* Utilities.hh:86-91 inverseSquareRoot<T>: (T)1 / (T)sqrt(x).  Under the reference's flags
+ * (-O2 -ffast-math -msse3, config/proc-x86_64.make:13-29) g++ emits rsqrtss plus one Newton step:
+ *     r = rsqrtss(x); out = ((x*r)*r + -3.0f) * (r * -0.5f)
+ * (objdump of CovarianceFeatureScorerElement.o, calculateInverseSquareRootDiagonal).  exact != 0
+ * gives the IEEE value instead (what a non-fast-math build of the reference would store). */
+void orc_inverse_sqrt(const float* var, float* isr, size_t n, int exact) {
+    for (size_t i = 0; i < n; ++i) {
+        float x = var[i];
+        if (exact) {
+            isr[i] = 1.0f / sqrtf(x);
+        }
+        else {
+            float r = _mm_cvtss_f32(_mm_rsqrt_ss(_mm_set_ss(x)));
+            float t = x * r;
+            t       = t * r;
+            t       = t + -3.0f;
+            isr[i]  = t * (r * -0.5f);
+        }
+    }
+}
+
+/* Utilities.hh:52-58,72-76 gaussLogNormFactor: D*log(2*pi) + sum_d log|var_d| in f64, stored f32
+ * (CovarianceFeatureScorerElement.cc:36-39). */
+float orc_log_norm_factor(const float* var, uint32_t D) {
+    double s = 0.0;
+    for (uint32_t d = 0; d < D; ++d)
+        s += log(fabs((double)var[d]));
+    return (float)((double)D * log((double)2 * M_PI) + s);
+}
+
+/* CovarianceFeatureScorerElement.cc:20-51 (operator= then scale(factor)) for every covariance.
+ * GaussDiagonalMaximumFeatureScorer.cc:52,82-85: factor = sqrt(gaussian-scale) (1 by default). */
+void orc_covariance_tables(const orc_model* m, float factor, int exactRsqrt, float* isr /*[nCov x D]*/,
+                           float* logNorm /*[nCov]*/) {
+    orc_inverse_sqrt(m->variances, isr, (size_t)m->nCov * m->D, exactRsqrt);
+    for (uint32_t c = 0; c < m->nCov; ++c) {
+        logNorm[c] = orc_log_norm_factor(m->variances + (size_t)c * m->D, m->D);
+        /* scale(): isr *= factor ; logNorm *= factor*factor   (:45-51) */
+        for (uint32_t d = 0; d < m->D; ++d)
+            isr[(size_t)c * m->D + d] = isr[(size_t)c * m->D + d] * factor;
+        logNorm[c] *= factor * factor;
+    }
+}
+
+/* MixtureFeatureScorerElement.cc:21-33: w2 = f32(-2 * logw) then *= mixture-weight-scale. */
+void orc_minus2_log_weights(const orc_model* m, float mixtureWeightScale, float* w2 /*[G]*/) {
+    size_t G = m->mixOffsets[m->M];
+    for (size_t i = 0; i < G; ++i) {
+        float v = (float)(-2 * m->mixLogWeight[i]);
+        w2[i]   = v * mixtureWeightScale;
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Float scorers
+ * ------------------------------------------------------------------------------------------- */
+
+/* GaussDiagonalMaximumFeatureScorer.cc:144-218, the __SSE3__ branch: four lane sums over
+ * d < 4*floor(D/4), hadd -> (l0+l1, l2+l3), result = (l0+l1) + (l2+l3), then the scalar tail. */
+static float orc_distance(const float* x, const float* mean, const float* isr, uint32_t D) {
+    float    lane[4] = {0.f, 0.f, 0.f, 0.f};
+    uint32_t eff     = D & ~3u, d = 0;
+    for (; d < eff; d += 4) {
+        for (int l = 0; l < 4; ++l) {
+            float df = (mean[d + l] - x[d + l]) * isr[d + l];
+            lane[l] += df * df;
+        }
+    }
+    float b0     = lane[0] + lane[1];
+    float b1     = lane[2] + lane[3];
+    float result = 0.f;
+    result += b0 + b1;
+    for (; d < D; ++d) {
+        float df = (mean[d] - x[d]) * isr[d];
+        result += df * df;
+    }
+    return result;
+}
+
+/* GaussDiagonalMaximumFeatureScorer.cc:116-142 calculateScoreAndDensity for all mixtures of all
+ * frames.  bestScore is an f32 that is compared (promoted) against the f64 candidate and assigned
+ * (rounded) from it; the first strict improvement wins. */
+void orc_score_max(const orc_model* m, const float* isr, const float* logNorm, const float* w2, const float* x,
+                   size_t T, float* score /*[T x M]*/, uint32_t* best /*[T x M]*/) {
+#pragma omp parallel for schedule(static)
+    for (long t = 0; t < (long)T; ++t) {
+        const float* xt = x + (size_t)t * m->D;
+        for (uint32_t mix = 0; mix < m->M; ++mix) {
+            float  bestScore   = FLT_MAX;    /* Core::Type<Score>::max */
+            size_t bestDensity = (size_t)-1; /* Core::Type<size_t>::max */
+            for (uint32_t k = m->mixOffsets[mix]; k < m->mixOffsets[mix + 1]; ++k) {
+                uint32_t dns = m->mixDensity[k];
+                uint32_t cov = m->densCov[dns];
+                double   s   = (double)w2[k] + (double)logNorm[cov] +
+                           (double)orc_distance(xt, m->means + (size_t)m->densMean[dns] * m->D,
+                                                isr + (size_t)cov * m->D, m->D);
+                if ((double)bestScore > s) {
+                    bestScore   = (float)s;
+                    bestDensity = k - m->mixOffsets[mix];
+                }
+            }
+            score[(size_t)t * m->M + mix] = (float)(0.5 * bestScore);
+            if (best)
+                best[(size_t)t * m->M + mix] = (uint32_t)bestDensity;
+        }
+    }
+}
+
+/* GaussDiagonalMaximumFeatureScorer.cc:239-289 (GaussDiagonalSumFeatureScorer): all f32;
+ * s_k = 0.5*(w2 + L + dist); best = first min; score = best - log(sum_k exp(best - s_k)).
+ * `0.5 * score` is a double product rounded to f32 (:258); std::exp/std::log on f32 are expf/logf.
+ * posterior != NULL additionally returns exp(score - s_k) per density slot (:291-298), [T x G]. */
+void orc_score_sum(const orc_model* m, const float* isr, const float* logNorm, const float* w2, const float* x,
+                   size_t T, float* score, uint32_t* best, float* posterior) {
+    size_t G = m->mixOffsets[m->M];
+#pragma omp parallel for schedule(static)
+    for (long t = 0; t < (long)T; ++t) {
+        const float* xt = x + (size_t)t * m->D;
+        float*       sc = (float*)malloc(sizeof(float) * (G ? G : 1));
+        for (uint32_t mix = 0; mix < m->M; ++mix) {
+            uint32_t a = m->mixOffsets[mix], b = m->mixOffsets[mix + 1];
+            for (uint32_t k = a; k < b; ++k) {
+                uint32_t dns = m->mixDensity[k];
+                uint32_t cov = m->densCov[dns];
+                float    s   = w2[k] + logNorm[cov] +
+                          orc_distance(xt, m->means + (size_t)m->densMean[dns] * m->D, isr + (size_t)cov * m->D, m->D);
+                sc[k] = (float)(0.5 * s);
+            }
+            float  bestScore   = FLT_MAX;
+            size_t bestDensity = (size_t)-1;
+            for (uint32_t k = a; k < b; ++k) {
+                if (bestScore > sc[k]) {
+                    bestScore   = sc[k];
+                    bestDensity = k - a;
+                }
+            }
+            float sumExp = 0.f;
+            for (uint32_t k = a; k < b; ++k)
+                sumExp += expf(bestScore - sc[k]);
+            float r                       = bestScore - logf(sumExp);
+            score[(size_t)t * m->M + mix] = r;
+            if (best)
+                best[(size_t)t * m->M + mix] = (uint32_t)bestDensity;
+            if (posterior)
+                for (uint32_t k = a; k < b; ++k)
+                    posterior[(size_t)t * G + k] = expf(r - sc[k]);
+        }
+        free(sc);
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Quantized SIMD scorer
+ * ------------------------------------------------------------------------------------------- */
+
+/* Utilities.hh:179-191 quantize<f32,u8>: clip((int)round(x) + 128, 0, 255); round() is half away
+ * from zero.  (int) of an out-of-range float is the x86 cvttss2si "integer indefinite" 0x80000000,
+ * which the clip turns into 0 after the +128 (it stays negative). */
+static uint8_t orc_quantize(float x) {
+    int r = _mm_cvttss_si32(_mm_set_ss(roundf(x)));
+    int v = (int)((unsigned)r + 128u); /* wraps like the reference's int add */
+    if (v < 0)
+        v = 0;
+    if (v > 255)
+        v = 255;
+    return (uint8_t)v;
+}
+
+/* IntelOptimization.hh:55-57 optimalVectorSize with BlockSize = 16 (ENABLE_SSE2). */
+uint32_t orc_simd_padded_dimension(uint32_t D) {
+    return ((D + 15u) / 16u) * 16u;
+}
+
+/* IntelOptimization.cc:50-67 multiplyAndQuantize: r[d] = Q(x[d] * y[d]), zero padded to Dpad. */
+static void orc_multiply_and_quantize(const float* x, const float* y, uint32_t D, uint32_t Dpad, uint8_t* r) {
+    uint32_t d = 0;
+    for (; d < D; ++d)
+        r[d] = orc_quantize(x[d] * y[d]);
+    for (; d < Dpad; ++d)
+        r[d] = 0;
+}
+
+/* SimdFeatureScorer.cc:64-133 init/getScaling/quantizationScalingFactor/buildMixtureTable and
+ * IntelOptimization.cc:39-48 createDensityElement.
+ * Outputs: isrS [nCov x D] (isr * scaling), logNormS [nCov] (L * scaling^2), scalingSquared,
+ * qmean [G x Dpad], qconst [G], qcov [G] -- one entry per (mixture, density slot), untied. */
+void orc_simd_prepare(const orc_model* m, int exactRsqrt, float* isrS, float* logNormS, float* scalingSquared,
+                      uint8_t* qmean, int32_t* qconst, uint32_t* qcov) {
+    const uint32_t D = m->D, Dpad = orc_simd_padded_dimension(D);
+    /* init(): covarianceTable_[i] = covariance (unscaled)                       (:64-67) */
+    orc_covariance_tables(m, 1.0f, exactRsqrt, isrS, logNormS);
+    /* getScaling(): min/max over all densities of mean*isr                      (:106-126) */
+    float minMean = FLT_MAX, maxMean = -FLT_MAX; /* Core::Type<f32>::max / ::min */
+    for (uint32_t i = 0; i < m->nDens; ++i) {
+        const float* mean = m->means + (size_t)m->densMean[i] * D;
+        const float* isr  = isrS + (size_t)m->densCov[i] * D;
+        for (uint32_t d = 0; d < D; ++d) {
+            float dividedMean = mean[d] * isr[d];
+            minMean           = dividedMean < minMean ? dividedMean : minMean;
+            maxMean           = maxMean < dividedMean ? dividedMean : maxMean;
+        }
+    }
+    /* quantizationScalingFactor(): (f32)255 / (1.25 * intervalSize), double division  (:128-133) */
+    float a            = fabsf(minMean), b = fabsf(maxMean);
+    float intervalSize = 2 * (a < b ? b : a);
+    float scaling      = (float)((double)(float)255 / (1.25 * (double)intervalSize));
+    *scalingSquared    = scaling * scaling; /* (:72) */
+    /* covarianceTable_[i].scale(scaling)                                        (:75-76) */
+    for (uint32_t c = 0; c < m->nCov; ++c) {
+        for (uint32_t d = 0; d < D; ++d)
+            isrS[(size_t)c * D + d] = isrS[(size_t)c * D + d] * scaling;
+        logNormS[c] *= scaling * scaling;
+    }
+    /* buildMixtureTable()                                                       (:81-104) */
+    for (uint32_t mix = 0; mix < m->M; ++mix) {
+        for (uint32_t k = m->mixOffsets[mix]; k < m->mixOffsets[mix + 1]; ++k) {
+            uint32_t dns = m->mixDensity[k];
+            uint32_t cov = m->densCov[dns];
+            qcov[k]      = cov;
+            /* Weight(f64) scaledMinus2LogWeight = scalingSquared_ * -2 * logWeight: (f32 * int) * f64 */
+            double scaledMinus2LogWeight = (double)(*scalingSquared * -2) * m->mixLogWeight[k];
+            /* passed as Score (f32) into createDensityElement, added to f32 L, truncated to s32 */
+            float w = (float)scaledMinus2LogWeight;
+            orc_multiply_and_quantize(m->means + (size_t)m->densMean[dns] * D, isrS + (size_t)cov * D, D, Dpad,
+                                      qmean + (size_t)k * Dpad);
+            qconst[k] = _mm_cvttss_si32(_mm_set_ss(w + logNormS[cov]));
+        }
+    }
+}
+
+/* SimdFeatureScorer.cc:22-35 Context ctor: the frame is quantized once per covariance.
+ * qx [T x nCov x Dpad]. */
+void orc_simd_quantize_features(const float* x, size_t T, uint32_t D, uint32_t nCov, const float* isrS,
+                                uint8_t* qx) {
+    const uint32_t Dpad = orc_simd_padded_dimension(D);
+#pragma omp parallel for schedule(static)
+    for (long t = 0; t < (long)T; ++t)
+        for (uint32_t c = 0; c < nCov; ++c)
+            orc_multiply_and_quantize(x + (size_t)t * D, isrS + (size_t)c * D, D, Dpad,
+                                      qx + ((size_t)t * nCov + c) * Dpad);
+}
+
+/* SSE2CodeGenerator.cc:324-374 / scalar restatement IntelOptimization.cc:71-113:
+ * sum over all Dpad bytes of (mean - feature)^2 in s32. */
+static int32_t orc_u8_distance(const uint8_t* a, const uint8_t* b, uint32_t Dpad) {
+    int32_t s = 0;
+    for (uint32_t d = 0; d < Dpad; ++d) {
+        int32_t df = (int32_t)a[d] - (int32_t)b[d];
+        s += df * df;
+    }
+    return s;
+}
+
+/* SimdFeatureScorer.cc:158-176 quantizedScore: q = min_k (const_k + dist_k), first strict minimum. */
+void orc_simd_score(uint32_t M, const uint32_t* mixOffsets, uint32_t Dpad, uint32_t nCov, const uint8_t* qmean,
+                    const int32_t* qconst, const uint32_t* qcov, const uint8_t* qx, size_t T,
+                    int32_t* q /*[T x M]*/, uint32_t* best /*[T x M]*/) {
+#pragma omp parallel for schedule(static)
+    for (long t = 0; t < (long)T; ++t) {
+        for (uint32_t mix = 0; mix < M; ++mix) {
+            int32_t minScore    = INT32_MAX;
+            size_t  bestDensity = (size_t)-1;
+            for (uint32_t k = mixOffsets[mix]; k < mixOffsets[mix + 1]; ++k) {
+                /* int + int; wraps like the reference build when const is the 0x80000000 indefinite */
+                int32_t s = (int32_t)((uint32_t)qconst[k] +
+                                      (uint32_t)orc_u8_distance(qmean + (size_t)k * Dpad,
+                                                                qx + ((size_t)t * nCov + qcov[k]) * Dpad, Dpad));
+                if (s < minScore) {
+                    minScore    = s;
+                    bestDensity = k - mixOffsets[mix];
+                }
+            }
+            q[(size_t)t * M + mix] = minScore;
+            if (best)
+                best[(size_t)t * M + mix] = (uint32_t)bestDensity;
+        }
+    }
+}
+
+/* SimdFeatureScorer.cc:135-145: score = f32( 0.5 * q / scalingSquared_ ), double arithmetic. */
+void orc_simd_final_score(const int32_t* q, size_t n, float scalingSquared, float* score) {
+    for (size_t i = 0; i < n; ++i)
+        score[i] = (float)(0.5 * q[i] / (double)scalingSquared);
+}

@@ -1,0 +1,195 @@
+"""TEST INFRASTRUCTURE -- NOT PRODUCT CODE.
+
+ctypes front end of oracle/gmm_oracle.c (the CPU restatement of the reference's scorers) and a runner for
+oracle/_ref/ref_scorer (the unmodified reference classes compiled by oracle/ref_build/Makefile).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgmm_oracle.so")
+REF_BIN = os.path.join(HERE, "_ref", "ref_scorer")
+REFERENCE_ROOT = "/root/reference"
+
+
+def build(force: bool = False) -> str:
+    """gcc the C restatement (no -ffast-math: operation order is explicit in the source)."""
+    src = os.path.join(HERE, "gmm_oracle.c")
+    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < os.path.getmtime(src):
+        subprocess.check_call(["gcc", "-O2", "-msse3", "-fopenmp", "-fPIC", "-shared", "-funsigned-char",
+                               "-o", LIB_PATH, src, "-lm"])
+    return LIB_PATH
+
+
+def build_ref(force: bool = False) -> str | None:
+    """Compile the reference scorer classes from /root/reference (build container only)."""
+    if not os.path.isdir(REFERENCE_ROOT):
+        return REF_BIN if os.path.exists(REF_BIN) else None
+    if force or not os.path.exists(REF_BIN):
+        subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(HERE, "ref_build")])
+    return REF_BIN
+
+
+class _Model(C.Structure):
+    _fields_ = [("D", C.c_uint32), ("M", C.c_uint32), ("nDens", C.c_uint32), ("nMeans", C.c_uint32),
+                ("nCov", C.c_uint32), ("mixOffsets", C.c_void_p), ("mixDensity", C.c_void_p),
+                ("mixLogWeight", C.c_void_p), ("densMean", C.c_void_p), ("densCov", C.c_void_p),
+                ("means", C.c_void_p), ("variances", C.c_void_p)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        _lib.orc_simd_padded_dimension.restype = C.c_uint32
+    return _lib
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+def _cmodel(ms):
+    return _Model(ms.D, ms.M, ms.n_densities, ms.n_means, ms.n_cov, ms.mix_offsets.ctypes.data,
+                  ms.mix_density.ctypes.data, ms.mix_logw.ctypes.data, ms.dens_mean.ctypes.data,
+                  ms.dens_cov.ctypes.data, ms.means.ctypes.data, ms.variances.ctypes.data)
+
+
+def float_tables(ms, *, mixture_weight_scale=1.0, gaussian_scale=1.0, exact_rsqrt=False):
+    """(isr [C,D], logNorm [C], w2 [G]) as GaussDiagonalMaximumFeatureScorer::init builds them."""
+    cm = _cmodel(ms)
+    isr = np.empty((ms.n_cov, ms.D), np.float32)
+    logn = np.empty(ms.n_cov, np.float32)
+    w2 = np.empty(ms.G, np.float32)
+    factor = np.float32(np.sqrt(np.float64(gaussian_scale)))  # ctor: gaussianScale_(std::sqrt(param)) f64->f32
+    lib().orc_covariance_tables(C.byref(cm), C.c_float(float(factor)), int(exact_rsqrt), _p(isr), _p(logn))
+    lib().orc_minus2_log_weights(C.byref(cm), C.c_float(mixture_weight_scale), _p(w2))
+    return isr, logn, w2
+
+
+def score_max(ms, x, tables=None):
+    x = np.ascontiguousarray(x, np.float32)
+    isr, logn, w2 = tables if tables is not None else float_tables(ms)
+    T = x.shape[0]
+    score = np.empty((T, ms.M), np.float32)
+    best = np.empty((T, ms.M), np.uint32)
+    cm = _cmodel(ms)
+    lib().orc_score_max(C.byref(cm), _p(isr), _p(logn), _p(w2), _p(x), C.c_size_t(T), _p(score), _p(best))
+    return score, best
+
+
+def score_sum(ms, x, tables=None, posterior=False):
+    x = np.ascontiguousarray(x, np.float32)
+    isr, logn, w2 = tables if tables is not None else float_tables(ms)
+    T = x.shape[0]
+    score = np.empty((T, ms.M), np.float32)
+    best = np.empty((T, ms.M), np.uint32)
+    post = np.empty((T, ms.G), np.float32) if posterior else None
+    cm = _cmodel(ms)
+    lib().orc_score_sum(C.byref(cm), _p(isr), _p(logn), _p(w2), _p(x), C.c_size_t(T), _p(score), _p(best), _p(post))
+    return (score, best, post) if posterior else (score, best)
+
+
+def simd_prepare(ms, exact_rsqrt=False):
+    """Quantized tables of SimdGaussDiagonalMaximumFeatureScorer::init."""
+    cm = _cmodel(ms)
+    Dpad = int(lib().orc_simd_padded_dimension(ms.D))
+    isrs = np.empty((ms.n_cov, ms.D), np.float32)
+    logns = np.empty(ms.n_cov, np.float32)
+    s2 = C.c_float(0)
+    qmean = np.empty((ms.G, Dpad), np.uint8)
+    qconst = np.empty(ms.G, np.int32)
+    qcov = np.empty(ms.G, np.uint32)
+    lib().orc_simd_prepare(C.byref(cm), int(exact_rsqrt), _p(isrs), _p(logns), C.byref(s2), _p(qmean), _p(qconst),
+                           _p(qcov))
+    return dict(isrs=isrs, logns=logns, scaling_squared=np.float32(s2.value), qmean=qmean, qconst=qconst,
+                qcov=qcov, Dpad=Dpad)
+
+
+def simd_quantize_features(x, isrs):
+    x = np.ascontiguousarray(x, np.float32)
+    T, D = x.shape
+    nCov = isrs.shape[0]
+    Dpad = int(lib().orc_simd_padded_dimension(D))
+    qx = np.empty((T, nCov, Dpad), np.uint8)
+    lib().orc_simd_quantize_features(_p(x), C.c_size_t(T), D, nCov, _p(isrs), _p(qx))
+    return qx
+
+
+def simd_score(mix_offsets, tab, qx):
+    T = qx.shape[0]
+    M = mix_offsets.shape[0] - 1
+    q = np.empty((T, M), np.int32)
+    best = np.empty((T, M), np.uint32)
+    lib().orc_simd_score(M, _p(mix_offsets), tab["Dpad"], qx.shape[1], _p(tab["qmean"]), _p(tab["qconst"]),
+                         _p(tab["qcov"]), _p(qx), C.c_size_t(T), _p(q), _p(best))
+    return q, best
+
+
+def simd_final_score(q, scaling_squared):
+    q = np.ascontiguousarray(q, np.int32)
+    out = np.empty(q.shape, np.float32)
+    lib().orc_simd_final_score(_p(q), C.c_size_t(q.size), C.c_float(float(scaling_squared)), _p(out))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# Runner for the compiled reference (oracle/_ref/ref_scorer)
+# ---------------------------------------------------------------------------------------------------
+def ref_available() -> bool:
+    return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
+
+
+def run_ref(ms, x, scorer="max", *, threads=0, repeat=1, dump=True, workdir=None):
+    """Run the unmodified reference scorer `scorer` (max|sum|simd|batchint|batchfloat) on (ms, x).
+
+    Returns a dict of numpy arrays (score, best, and for simd q/qmean/qconst/qcov/isrs/qx/meta) plus
+    "timing" when threads > 0."""
+    if not ref_available():
+        raise RuntimeError("oracle/_ref/ref_scorer is not built (needs /root/reference: oracle.build_ref())")
+    x = np.ascontiguousarray(x, np.float32)
+    T, M = x.shape[0], ms.M
+    with tempfile.TemporaryDirectory(dir=workdir) as tmp:
+        mp, fp, op = os.path.join(tmp, "model.gms"), os.path.join(tmp, "feat.f32"), os.path.join(tmp, "out")
+        ms.save(mp)
+        x.tofile(fp)
+        cmd = [REF_BIN, f"model={mp}", f"features={fp}", f"scorer={scorer}", f"out={op}",
+               f"dump={1 if dump else 0}", f"threads={threads}", f"repeat={repeat}"]
+        r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"ref_scorer failed ({r.returncode}):\n{r.stdout[-2000:]}")
+        out = {"log": r.stdout}
+        if dump:
+            out["score"] = np.fromfile(op + ".score.f32", np.float32).reshape(T, M)
+            if os.path.exists(op + ".best.u32"):
+                out["best"] = np.fromfile(op + ".best.u32", np.uint32).reshape(T, M)
+            if scorer == "simd":
+                meta = {}
+                with open(op + ".meta.txt") as f:
+                    for line in f:
+                        k, v = line.split()
+                        meta[k] = float(v) if k == "scalingSquared" else int(v)
+                Dpad, G, Cn = meta["Dpad"], meta["G"], meta["C"]
+                out["meta"] = meta
+                out["scaling_squared"] = np.float32(meta["scalingSquared"])
+                out["q"] = np.fromfile(op + ".q.i32", np.int32).reshape(T, M)
+                out["qmean"] = np.fromfile(op + ".qmean.u8", np.uint8).reshape(G, Dpad)
+                out["qconst"] = np.fromfile(op + ".qconst.i32", np.int32)
+                out["qcov"] = np.fromfile(op + ".qcov.u32", np.uint32)
+                out["isrs"] = np.fromfile(op + ".isrs.f32", np.float32).reshape(Cn, ms.D)
+                out["qx"] = np.fromfile(op + ".qx.u8", np.uint8).reshape(T, Cn, Dpad)
+        if threads > 0:
+            with open(op + ".timing.json") as f:
+                out["timing"] = json.load(f)
+        return out
