@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""bench.py -- scored frames/s of the GMM emission-scoring hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one batch of synthetic frames: S utterance segments of 1000 frames of
+45-dim features scored against the 4501 x 16-density mixture set (float maximum-approximation scorer, the
+reference's `diagonal-maximum`), i.e. a slice of BASELINE.json configs[3] (corpus-scale, segment-sharded) on
+the configs[0]/[1] model.  With N > 1 (torchrun, one rank per GPU) every rank scores its own segments
+(segment i -> rank i mod N, no collective on the data path): weak scaling.
+
+`value`   : whole-job frames/s, features and scores resident in HBM, CUDA-event timed, max over ranks.
+`e2e`     : the same through the C-ABI host call (gmm_score_host): pinned host features in, host scores out,
+            both copies inside the timed region.
+`roofline`: dominant kernel, algorithmic flops 2*(2D+1)*G per frame / CUDA-event time,
+            against MEASURED_PEAKS.json.
+`cpu_baseline`: the reference's own scorer classes (oracle/_ref/ref_scorer, built from the unmodified reference
+            sources) timed on this box's host cores on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "scored frames/sec (45-dim, 4501x16 dens.)"
+UNIT = "frames/s"
+SEG_FRAMES = 1000
+L2_BYTES = 126 << 20
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=float(d["hbm_gbs"]), tensor=float(d["bf16_tflops"]),
+                    tensor_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), source="measured")
+    return dict(hbm=6650.0, tensor=1590.0, tensor_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for (ts, r) in self.rows if t0 - 0.05 <= ts <= t1 + 0.15 and len(r) >= 7] or \
+               [r for (_, r) in self.rows if len(r) >= 7]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = [float(r[0]) for r in rows if r[0].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": float(rows[0][1]),
+                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows), "reasons": reasons}
+
+
+def workload(segments: int):
+    from rasr_b200 import synth
+    ms = synth.make_model(4501, 16, 45, seed=1001, covariance="pooled")
+    return ms, segments * SEG_FRAMES
+
+
+def segment_features(ms, seg_ids):
+    """Features of whole segments, regenerated from seed 3000 + segment id."""
+    from rasr_b200 import synth
+    return np.concatenate([synth.make_features(ms, SEG_FRAMES, seed=3000 + int(s)) for s in seg_ids])
+
+
+# -------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the reference's own CPU scorer on the host cores
+# -------------------------------------------------------------------------------------------------
+def cpu_reference_run(ms, frames: int, scorer: str, repeat: int):
+    """Times oracle/_ref/ref_scorer (kind "reference") or, if it was not built, the oracle port ("port")."""
+    from oracle import oracle as O
+    from rasr_b200 import synth
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    x = synth.make_features(ms, frames, seed=3000)
+    if O.ref_available():
+        r = O.run_ref(ms, x, scorer, threads=cores, repeat=repeat, dump=False)
+        fps = float(r["timing"]["frames_per_s"])
+        kind = "reference"
+    else:
+        O.build()
+        os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+        f = {"max": O.score_max, "sum": O.score_sum}[scorer]
+        best = 1e30
+        for _ in range(repeat):
+            t0 = time.perf_counter()
+            f(ms, x)
+            best = min(best, time.perf_counter() - t0)
+        fps, kind = frames / best, "port"
+    return dict(value=fps, unit=UNIT, cores=cores, kind=kind,
+                sample=f"{frames} frames of the same model/features, all {ms.M} mixtures per frame, "
+                       f"one scorer instance per thread on {cores} threads, best of {repeat}")
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    ms, _ = workload(1)
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    frames = max(256, 48 * cores)  # about 1-2 s of CPU work per step
+    for _ in range(args.warmup):
+        cpu_reference_run(ms, frames, "max", 1)
+    vals = []
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        vals.append(cpu_reference_run(ms, frames, "max", 1))
+    wall = time.perf_counter() - t0
+    fps = statistics.median(v["value"] for v in vals)
+    cb = dict(vals[0], value=fps)
+    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * frames / fps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "cfg4-slice: 4501x16x45 float diagonal-maximum, reference CPU scorer",
+                       "frames_per_step": frames, "wall_s": wall},
+            "cpu_baseline": cb, "gpu_launches": 0,
+            "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+# -------------------------------------------------------------------------------------------------
+# our arm
+# -------------------------------------------------------------------------------------------------
+def time_device(torch, fn, steps, warmup, dist=None):
+    """W warm-up steps, then exactly K steps bracketed by barrier + synchronize; CUDA events on the current
+    stream (the engine is bound to it); returns (seconds max over ranks, wall t0, wall t1)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.time()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    w1 = time.time()
+    if dist is not None:
+        dist.barrier()
+    sec = e0.elapsed_time(e1) * 1e-3
+    if dist is not None:
+        t = torch.tensor([sec], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sec = float(t.item())
+    return sec, w0, w1
+
+
+def float_roofline(ms, frames, sec_per_step, peaks, kernel_name, share=1.0):
+    flops = 2.0 * (2 * ms.D + 1) * ms.G * frames  # algorithmic, SURVEY.md 8(d)
+    ach = flops / (sec_per_step * share) / 1e12
+    return {"bound": "tensor", "achieved": ach, "peak": peaks["tensor"], "unit": "TFLOP/s",
+            "frac": ach / peaks["tensor"], "traffic": None, "kernel": kernel_name,
+            "peak_source": f"{peaks['source']} bf16 dense burst (MEASURED_PEAKS.json)",
+            "algorithmic_flops_per_launch": flops,
+            "gaussian_evals_per_s": ms.G * frames / sec_per_step}
+
+
+def quant_roofline(ms, frames, sec_per_step, peaks, outputs=2):
+    dpad = ((ms.D + 15) // 16) * 16
+    nbytes = ms.G * (dpad + 4) + frames * dpad + frames * ms.M * 4 * outputs
+    ach = nbytes / sec_per_step / 1e9
+    return {"bound": "hbm", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s", "frac": ach / peaks["hbm"],
+            "traffic": None, "kernel": "quant_score_kernel", "algorithmic_bytes_per_launch": nbytes,
+            "peak_source": f"{peaks['source']} copy bandwidth (MEASURED_PEAKS.json)"}
+
+
+def run_ours(args):
+    import torch
+    from rasr_b200 import capi, synth, tables
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+    peaks = measured_peaks()
+    segs = args.segments
+    ms, frames = workload(segs)
+    tab = tables.float_tables(ms)
+    eng = capi.Engine(local)
+    stream = torch.cuda.current_stream()
+    eng.set_stream(stream.cuda_stream)
+    eng.upload_float(tab["offsets"], tab["mean"], tab["isr"], tab["cov_idx"], tab["w2"], tab["log_norm"],
+                     mode=capi.MODE_MAX, kernel=capi.KERNEL_AUTO)
+    kname = {capi.KERNEL_DIRECT: "direct_kernel (CUDA cores, reference order)",
+             capi.KERNEL_TENSOR: "tc_score_kernel (tcgen05 split-fp16 + fused min)"}[eng.float_kernel]
+
+    # this rank's segments: i -> rank i mod N; two alternating batches so consecutive steps read fresh inputs
+    seg_ids = [rank + world * i for i in range(2 * segs)]
+    x_host = torch.from_numpy(segment_features(ms, seg_ids)).pin_memory()
+    xa, xb = x_host[:frames].cuda(), x_host[frames:].cuda()
+    scores = torch.empty((frames, ms.M), dtype=torch.float32, device="cuda")
+    state = {"i": 0}
+
+    def step():
+        eng.score_device(frames, xa if state["i"] % 2 == 0 else xb, scores)
+        state["i"] += 1
+
+    step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    l0 = eng.launch_count
+    sec, w0, w1 = time_device(torch, step, args.steps, args.warmup, dist)
+    launches = (eng.launch_count - l0) - 0
+    launches_timed = launches * args.steps // (args.steps + args.warmup)
+    clocks = sampler.stop(w0, w1) if rank == 0 else None
+    sec_per_step = sec / args.steps
+    value = world * frames / sec_per_step
+
+    # end to end through the host API: pinned features in, host scores out, every step
+    e2e_frames = min(frames, 8 * SEG_FRAMES)
+    out_host = torch.empty((e2e_frames, ms.M), dtype=torch.float32).pin_memory()
+    xh = x_host[:e2e_frames].numpy()
+    oh = out_host.numpy()
+
+    def e2e_step():
+        eng.score_host(xh, want_best=False, out=oh)
+
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_sec = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e2e_sec], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_sec = float(t.item())
+    e2e_value = world * e2e_frames * e2e_steps / e2e_sec
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sec_per_step * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 (fp16x3 split operands, f32 accumulate)" if
+            eng.float_kernel == capi.KERNEL_TENSOR else "f32", "data": "synthetic",
+            "config": {"workload": "cfg4-slice: 4501 mixtures x 16 densities x 45 dims, float diagonal-maximum, "
+                                   f"{segs} segments x {SEG_FRAMES} frames per GPU per step",
+                       "frames_per_step_per_gpu": frames, "segment_sharding": "segment i -> rank i mod N, no collective",
+                       "l2": f"scores written per step {frames * ms.M * 4 / 2**20:.0f} MiB > 126 MiB L2; "
+                             "inputs alternate between two batches",
+                       "kernel": kname},
+            "gpu_launches": launches_timed,
+            "gaussian_evals_per_s": value * ms.G,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": e2e_frames * ms.D * 4,
+                    "d2h_bytes_per_step": e2e_frames * ms.M * 4, "frames_per_step_per_gpu": e2e_frames,
+                    "api": "gmm_score_host (C-ABI, pinned host buffers)"},
+            "clocks": clocks}
+    if rank == 0:
+        line["roofline"] = float_roofline(ms, frames, sec_per_step, peaks, kname)
+        if world == 1 and not args.no_cpu:
+            cores = len(os.sched_getaffinity(0))
+            line["cpu_baseline"] = cpu_reference_run(ms, max(512, 96 * cores), "max", 2)
+        if world == 1 and not args.no_extra:
+            line["extra"] = extra_cases(torch, eng, peaks, args)
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    eng.close()
+    return 0
+
+
+def extra_cases(torch, eng, peaks, args):
+    """The other single-GPU configurations of BASELINE.json, kernel-only, for DESIGN.md's tables (not the headline)."""
+    from rasr_b200 import capi, synth, tables
+    out = {}
+    steps, warmup = max(3, min(args.steps, 10)), 3
+    # cfg2: same model through the quantized scorer (bit-exact integer path)
+    ms, x = synth.make_config("cfg2", T=8 * SEG_FRAMES)
+    qt = tables.quant_tables(ms)
+    eng.upload_quant(qt["offsets"], qt["qmean"], qt["cov_idx"], qt["qconst"], qt["isr_scaled"], qt["scaling_squared"])
+    T = x.shape[0]
+    dx = torch.from_numpy(x).cuda()
+    dq = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
+    db = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
+    sec, _, _ = time_device(torch, lambda: eng.quant_score_device(T, dx, dq, db), steps, warmup)
+    out["cfg2_quantized"] = {"frames_per_s": T * steps / sec, "ms_per_step": 1e3 * sec / steps, "frames": T,
+                             "roofline": quant_roofline(ms, T, sec / steps, peaks)}
+    del dq, db
+    # cfg3: 12001 x 64, 10k-frame batches, max and sum
+    ms, x = synth.make_config("cfg3", T=10000)
+    tab = tables.float_tables(ms)
+    T = x.shape[0]
+    dx = torch.from_numpy(x).cuda()
+    ds = torch.empty((T, ms.M), dtype=torch.float32, device="cuda")
+    for mode, name in ((capi.MODE_MAX, "cfg3_max"), (capi.MODE_SUM, "cfg3_sum")):
+        eng.upload_float(tab["offsets"], tab["mean"], tab["isr"], tab["cov_idx"], tab["w2"], tab["log_norm"],
+                         mode=mode, kernel=capi.KERNEL_AUTO)
+        st = steps if eng.float_kernel == capi.KERNEL_TENSOR else 2
+        sec, _, _ = time_device(torch, lambda: eng.score_device(T, dx, ds), st, 1 if st == 2 else warmup)
+        out[name] = {"frames_per_s": T * st / sec, "ms_per_step": 1e3 * sec / st, "frames": T,
+                     "kernel": eng.float_kernel, "roofline": float_roofline(ms, T, sec / st, peaks, str(eng.float_kernel))}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--segments", type=int, default=32, help="1000-frame segments per GPU per step")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the cfg2 / cfg3 side measurements")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,112 @@
+/* gmm_b200.h -- C-ABI of the B200-native GMM emission-scoring engine.
+ *
+ * This is the drop-in boundary: the only thing the RASR-side scorer class
+ * (rasr/GpuFeatureScorer.cc, an Mm::AssigningFeatureScorer registered in Mm::FeatureScorerFactory)
+ * binds to.  Plain C types, no RASR and no torch types; the library owns all device memory, the caller
+ * owns all host buffers.  Every entry point returns GMM_OK (0) or a negative error code; the message
+ * is available from gmm_last_error().  There is no CPU fallback: without a CUDA device gmm_create fails.
+ *
+ * Which reference interface each entry point replaces (paths relative to /root/reference/src/Mm):
+ *
+ *   gmm_upload_float    GaussDiagonalMaximumFeatureScorer::init             GaussDiagonalMaximumFeatureScorer.cc:64-86
+ *                       (tables from MixtureFeatureScorerElement.cc:21-33, CovarianceFeatureScorerElement.cc:20-51)
+ *   gmm_score_*  (max)  GaussDiagonalMaximumFeatureScorer::calculateScoreAndDensity + distance   .cc:116-218
+ *   gmm_score_*  (sum)  GaussDiagonalSumFeatureScorer::calculateScoreAndDensity                  .cc:239-289
+ *   gmm_posteriors      GaussDiagonalSumFeatureScorer::calculateDensityPosteriorProbabilities    .cc:291-298
+ *   gmm_upload_quant    SimdGaussDiagonalMaximumFeatureScorer::init/buildMixtureTable  SimdFeatureScorer.cc:64-104
+ *   gmm_quant_* (qx)    SimdGaussDiagonalMaximumFeatureScorer::Context ctor            SimdFeatureScorer.cc:22-35
+ *                       FeatureScorerIntelOptimization::multiplyAndQuantize            IntelOptimization.cc:50-67
+ *   gmm_quant_* (q)     quantizedScore + FeatureScorerIntelOptimization::distance      SimdFeatureScorer.cc:158-176,
+ *                       SSE2L2NormCodeGenerator (JIT SSE2)                             SSE2CodeGenerator.cc:324-374
+ *   gmm_quant_* (score) calculateScoreAndDensity: f32(0.5 * q / scalingSquared)        SimdFeatureScorer.cc:135-145
+ *   batching            BatchFeatureScorerBase ring buffer (caller side)               BatchFeatureScorer.cc:40-105
+ *
+ * Layout conventions: all matrices row-major; "slot" g in [0,G) enumerates (mixture, density) pairs in
+ * mixture order, offsets[m]..offsets[m+1] are the slots of mixture m (tying already flattened, as
+ * BatchFeatureScorerBase::initialize does, BatchFeatureScorer.cc:62-75).  Scores are -log p(x|m),
+ * lower is better (FeatureScorer.hh:39-40).
+ */
+#ifndef GMM_B200_H
+#define GMM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gmm_handle gmm_handle;
+
+enum {
+    GMM_OK            = 0,
+    GMM_ERR_ARG       = -1, /* invalid argument / model not uploaded */
+    GMM_ERR_CUDA      = -2, /* CUDA runtime error (message in gmm_last_error) */
+    GMM_ERR_NO_DEVICE = -3, /* no usable sm_100 device */
+    GMM_ERR_UNSUPPORTED = -4
+};
+
+/* scoring mode of the float engine */
+enum {
+    GMM_MODE_MAX = 0, /* maximum approximation: 0.5 * min_k(...)      (diagonal-maximum) */
+    GMM_MODE_SUM = 1  /* full sum: -log sum_k exp(-s_k)               (GaussDiagonalSumFeatureScorer) */
+};
+
+/* kernel selection for the float engine */
+enum {
+    GMM_KERNEL_AUTO   = 0, /* tensor-core kernel when the model fits it, else direct */
+    GMM_KERNEL_DIRECT = 1, /* CUDA-core kernel, ((mu - x) * isr)^2 evaluated as the reference does */
+    GMM_KERNEL_TENSOR = 2  /* tcgen05 split-fp16 contraction with fused min / log-sum-exp epilogue */
+};
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+int         gmm_create(gmm_handle** out, int device);
+void        gmm_destroy(gmm_handle* h);
+const char* gmm_last_error(const gmm_handle* h); /* h may be NULL: error of the last failed gmm_create */
+/* Run all work of this handle on an existing CUDA stream (a cudaStream_t passed as void*). NULL = own stream. */
+int gmm_set_stream(gmm_handle* h, void* cuda_stream);
+
+/* ---- float engine --------------------------------------------------------------------------- */
+/* mean [G x D], isr [C x D] (inverse standard deviation, already scaled), cov_idx [G] in [0,C),
+ * w2 [G] = minus2LogWeight of the slot (+inf for a zero-weight density), log_norm [C] = logNormFactor:
+ * the four tables GaussDiagonalMaximumFeatureScorer::init builds, flattened per slot. */
+int gmm_upload_float(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t C, const uint32_t* offsets,
+                     const float* mean, const float* isr, const uint32_t* cov_idx, const float* w2,
+                     const float* log_norm, int mode, int kernel);
+
+/* Score T frames held in HOST memory: x [T x D] -> scores [T x ld] (ld >= M), best [T x ld] or NULL.
+ * Copies H2D, launches, copies D2H on the handle's stream and waits.  best = index of the winning
+ * density within its mixture (first minimum), 0xFFFFFFFF for a mixture without a finite density. */
+int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld);
+/* Same with DEVICE pointers; asynchronous on the handle's stream (call gmm_sync to wait). */
+int gmm_score_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
+/* Density posteriors of the sum scorer for T frames: post [T x G] (device pointers), exp(score - s_k). */
+int gmm_posteriors_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_post);
+
+/* ---- quantized engine (bit-exact SIMD-diagonal-maximum) -------------------------------------- */
+/* qmean [G x Dpad] u8, cov_idx [G], qconst [G] s32, isr_scaled [C x D] f32: the tables exactly as the
+ * reference's init() produced them on the host (so build-dependent rsqrt effects are inherited). */
+int gmm_upload_quant(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t Dpad, uint32_t C,
+                     const uint32_t* offsets, const uint8_t* qmean, const uint32_t* cov_idx, const int32_t* qconst,
+                     const float* isr_scaled, float scaling_squared);
+/* x [T x D] f32 -> q [T x ld] s32 (may be NULL), best [T x ld] (may be NULL), score [T x ld] f32 (may
+ * be NULL; f32(0.5 * q / scalingSquared) evaluated in IEEE double), qx [T x C x Dpad] u8 (may be NULL). */
+int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, uint32_t* best, float* score,
+                         uint8_t* qx, size_t ld);
+int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,
+                           float* d_score, uint8_t* d_qx, size_t ld);
+
+/* ---- plumbing -------------------------------------------------------------------------------- */
+/* Page-locked host buffers for the feature / score blocks (cudaMallocHost); NULL on failure. */
+void* gmm_host_alloc(size_t bytes);
+void  gmm_host_free(void* p);
+int      gmm_sync(gmm_handle* h);                       /* wait for the handle's stream */
+uint64_t gmm_launch_count(const gmm_handle* h);         /* kernels launched by this handle so far */
+/* 1 = direct, 2 = tensor: the float kernel the last gmm_upload_float selected. */
+int         gmm_float_kernel(const gmm_handle* h);
+const char* gmm_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GMM_B200_H */

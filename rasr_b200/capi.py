@@ -1,0 +1,195 @@
+"""ctypes binding of the C-ABI in include/gmm_b200.h (libgmm_b200.so, hand-written CUDA for sm_100a).
+
+This is the binding a maintainer would write for any host language; it is what the tests, bench.py and the
+Python mirror of the reference's scorer interface (rasr_b200/feature_scorer.py) call.  There is NO fallback:
+if the shared library is missing, or no sm_100 device is present, loading / ``Engine()`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgmm_b200.so")
+
+MODE_MAX, MODE_SUM = 0, 1
+KERNEL_AUTO, KERNEL_DIRECT, KERNEL_TENSOR = 0, 1, 2
+
+# every symbol include/gmm_b200.h declares: (name, restype, argtypes)
+_vp, _u32, _sz, _i = C.c_void_p, C.c_uint32, C.c_size_t, C.c_int
+SYMBOLS = [
+    ("gmm_create", _i, [C.POINTER(_vp), _i]),
+    ("gmm_destroy", None, [_vp]),
+    ("gmm_last_error", C.c_char_p, [_vp]),
+    ("gmm_set_stream", _i, [_vp, _vp]),
+    ("gmm_upload_float", _i, [_vp, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i]),
+    ("gmm_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _sz]),
+    ("gmm_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _sz]),
+    ("gmm_posteriors_device", _i, [_vp, _u32, _vp, _vp]),
+    ("gmm_upload_quant", _i, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, C.c_float]),
+    ("gmm_quant_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
+    ("gmm_quant_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
+    ("gmm_host_alloc", _vp, [_sz]),
+    ("gmm_host_free", None, [_vp]),
+    ("gmm_sync", _i, [_vp]),
+    ("gmm_launch_count", C.c_uint64, [_vp]),
+    ("gmm_float_kernel", _i, [_vp]),
+    ("gmm_version", C.c_char_p, []),
+]
+
+_lib = None
+
+
+class GmmError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen libgmm_b200.so and bind every declared symbol; raises if the library was not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise GmmError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(make -C rasr_b200/csrc).  There is no CPU fallback.")
+        lib = C.CDLL(LIB_PATH)
+        for name, res, args in SYMBOLS:
+            fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if isinstance(a, int):
+        return a
+    return a.data_ptr()  # torch tensor
+
+
+def _np(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a
+
+
+class Engine:
+    """One gmm_handle: one GPU, one CUDA stream, at most one float and one quantized model."""
+
+    def __init__(self, device: int = 0):
+        self._lib = load()
+        h = _vp()
+        rc = self._lib.gmm_create(C.byref(h), int(device))
+        if rc != 0:
+            raise GmmError(f"gmm_create failed ({rc}): {self._lib.gmm_last_error(None).decode()}")
+        self._h = h
+        self.M = self.G = self.D = 0
+        self.qM = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.gmm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise GmmError(f"{what} failed ({rc}): {self._lib.gmm_last_error(self._h).decode()}")
+
+    # -- plumbing ---------------------------------------------------------------------------------
+    def set_stream(self, cuda_stream_ptr: int | None):
+        self._check(self._lib.gmm_set_stream(self._h, cuda_stream_ptr), "gmm_set_stream")
+
+    def sync(self):
+        self._check(self._lib.gmm_sync(self._h), "gmm_sync")
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.gmm_launch_count(self._h))
+
+    @property
+    def float_kernel(self) -> int:
+        return int(self._lib.gmm_float_kernel(self._h))
+
+    # -- float engine -----------------------------------------------------------------------------
+    def upload_float(self, offsets, mean, isr, cov_idx, w2, log_norm, mode=MODE_MAX, kernel=KERNEL_AUTO):
+        offsets = _np(offsets, np.uint32)
+        mean = _np(mean, np.float32)
+        isr = _np(isr, np.float32)
+        cov_idx = _np(cov_idx, np.uint32)
+        w2 = _np(w2, np.float32)
+        log_norm = _np(log_norm, np.float32)
+        M, G = offsets.shape[0] - 1, int(offsets[-1])
+        Cn, D = isr.shape
+        if mean.shape != (G, D) or cov_idx.shape != (G,) or w2.shape != (G,) or log_norm.shape != (Cn,):
+            raise ValueError("upload_float: table shapes are inconsistent")
+        self._check(self._lib.gmm_upload_float(self._h, M, G, D, Cn, _ptr(offsets), _ptr(mean), _ptr(isr),
+                                               _ptr(cov_idx), _ptr(w2), _ptr(log_norm), mode, kernel),
+                    "gmm_upload_float")
+        self.M, self.G, self.D = M, G, D
+
+    def score_host(self, x, want_best=True, ld=None, out=None):
+        """x [T, D] f32 host array -> (scores [T, M] f32, best [T, M] u32 | None), host arrays."""
+        x = _np(x, np.float32)
+        if x.ndim != 2 or x.shape[1] != self.D:
+            raise ValueError(f"features must be [T, {self.D}]")
+        T = x.shape[0]
+        ld = self.M if ld is None else int(ld)
+        scores = out if out is not None else np.empty((T, ld), np.float32)
+        best = np.empty((T, ld), np.uint32) if want_best else None
+        self._check(self._lib.gmm_score_host(self._h, T, _ptr(x), _ptr(scores), _ptr(best), ld), "gmm_score_host")
+        return scores, best
+
+    def score_device(self, T, d_x, d_scores, d_best=None, ld=None):
+        """Device pointers (ints or torch tensors); asynchronous on the handle's stream."""
+        ld = self.M if ld is None else int(ld)
+        self._check(self._lib.gmm_score_device(self._h, int(T), _ptr(d_x), _ptr(d_scores), _ptr(d_best), ld),
+                    "gmm_score_device")
+
+    def posteriors_device(self, T, d_x, d_post):
+        self._check(self._lib.gmm_posteriors_device(self._h, int(T), _ptr(d_x), _ptr(d_post)),
+                    "gmm_posteriors_device")
+
+    # -- quantized engine -------------------------------------------------------------------------
+    def upload_quant(self, offsets, qmean, cov_idx, qconst, isr_scaled, scaling_squared):
+        offsets = _np(offsets, np.uint32)
+        qmean = _np(qmean, np.uint8)
+        cov_idx = _np(cov_idx, np.uint32)
+        qconst = _np(qconst, np.int32)
+        isr_scaled = _np(isr_scaled, np.float32)
+        M, G = offsets.shape[0] - 1, int(offsets[-1])
+        Cn, D = isr_scaled.shape
+        Dpad = qmean.shape[1]
+        if qmean.shape[0] != G or cov_idx.shape != (G,) or qconst.shape != (G,):
+            raise ValueError("upload_quant: table shapes are inconsistent")
+        self._check(self._lib.gmm_upload_quant(self._h, M, G, D, Dpad, Cn, _ptr(offsets), _ptr(qmean), _ptr(cov_idx),
+                                               _ptr(qconst), _ptr(isr_scaled), C.c_float(float(scaling_squared))),
+                    "gmm_upload_quant")
+        self.qM, self.qD, self.qC, self.qDpad = M, D, Cn, Dpad
+
+    def quant_score_host(self, x, want_q=True, want_best=True, want_score=True, want_qx=False):
+        x = _np(x, np.float32)
+        if x.ndim != 2 or x.shape[1] != self.qD:
+            raise ValueError(f"features must be [T, {self.qD}]")
+        T, M = x.shape[0], self.qM
+        q = np.empty((T, M), np.int32) if want_q else None
+        best = np.empty((T, M), np.uint32) if want_best else None
+        score = np.empty((T, M), np.float32) if want_score else None
+        qx = np.empty((T, self.qC, self.qDpad), np.uint8) if want_qx else None
+        self._check(self._lib.gmm_quant_score_host(self._h, T, _ptr(x), _ptr(q), _ptr(best), _ptr(score), _ptr(qx), M),
+                    "gmm_quant_score_host")
+        return dict(q=q, best=best, score=score, qx=qx)
+
+    def quant_score_device(self, T, d_x, d_q=None, d_best=None, d_score=None, d_qx=None, ld=None):
+        ld = self.qM if ld is None else int(ld)
+        self._check(self._lib.gmm_quant_score_device(self._h, int(T), _ptr(d_x), _ptr(d_q), _ptr(d_best),
+                                                     _ptr(d_score), _ptr(d_qx), ld), "gmm_quant_score_device")

@@ -1,0 +1,452 @@
+// C-ABI of libgmm_b200.so (include/gmm_b200.h): handle lifetime, model upload / packing, and the host- and
+// device-pointer scoring entry points.  No CPU fallback anywhere: every scoring call ends in a CUDA kernel.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "gmm_internal.cuh"
+
+static std::string g_createError;
+
+int gmm_handle::devAlloc(void** p, size_t bytes, bool quant) {
+    *p = nullptr;
+    if (bytes == 0)
+        bytes = 16;
+    GMM_CUDA_TRY(this, cudaMalloc(p, bytes));
+    (quant ? ownedQuant : owned).push_back(*p);
+    return GMM_OK;
+}
+
+int gmm_handle::upload(void** p, const void* src, size_t bytes, bool quant) {
+    int rc = devAlloc(p, bytes, quant);
+    if (rc)
+        return rc;
+    if (bytes)
+        GMM_CUDA_TRY(this, cudaMemcpyAsync(*p, src, bytes, cudaMemcpyHostToDevice, stream));
+    return GMM_OK;
+}
+
+int gmm_handle::reserve(int slot, size_t bytes, void** out) {
+    if (bytes > scratchBytes[slot]) {
+        GMM_CUDA_TRY(this, cudaStreamSynchronize(stream));
+        if (scratch[slot])
+            GMM_CUDA_TRY(this, cudaFree(scratch[slot]));
+        scratch[slot]      = nullptr;
+        scratchBytes[slot] = 0;
+        size_t want        = bytes + bytes / 4 + 256;
+        GMM_CUDA_TRY(this, cudaMalloc(&scratch[slot], want));
+        scratchBytes[slot] = want;
+    }
+    *out = scratch[slot];
+    return GMM_OK;
+}
+
+static void releaseFloatModel(gmm_handle* h) {
+    cudaStreamSynchronize(h->stream);
+    for (void* p : h->owned)
+        cudaFree(p);
+    h->owned.clear();
+    h->floatValid = false;
+    h->direct     = DirectModel();
+    h->tensor     = TensorModel();
+}
+
+static void releaseQuantModel(gmm_handle* h) {
+    cudaStreamSynchronize(h->stream);
+    for (void* p : h->ownedQuant)
+        cudaFree(p);
+    h->ownedQuant.clear();
+    h->quant = QuantModel();
+}
+
+extern "C" {
+
+const char* gmm_version(void) {
+    return "gmm_b200 0.1 (sm_100a)";
+}
+
+int gmm_create(gmm_handle** out, int device) {
+    if (!out) {
+        g_createError = "gmm_create: out is NULL";
+        return GMM_ERR_ARG;
+    }
+    *out  = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_createError = std::string("gmm_create: no CUDA device (") + cudaGetErrorString(e) + ")";
+        return GMM_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= n) {
+        g_createError = "gmm_create: device index out of range";
+        return GMM_ERR_ARG;
+    }
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) {
+        g_createError = std::string("gmm_create: ") + cudaGetErrorString(e);
+        return GMM_ERR_CUDA;
+    }
+    if (prop.major != 10) {
+        g_createError = "gmm_create: device is not sm_100 (the library is built for sm_100a only)";
+        return GMM_ERR_NO_DEVICE;
+    }
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+        g_createError = std::string("gmm_create: ") + cudaGetErrorString(e);
+        return GMM_ERR_CUDA;
+    }
+    gmm_handle* h = new gmm_handle;
+    h->device     = device;
+    h->smCount    = prop.multiProcessorCount;
+    e             = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        g_createError = std::string("gmm_create: ") + cudaGetErrorString(e);
+        delete h;
+        return GMM_ERR_CUDA;
+    }
+    h->ownStream = true;
+    *out         = h;
+    return GMM_OK;
+}
+
+void gmm_destroy(gmm_handle* h) {
+    if (!h)
+        return;
+    cudaSetDevice(h->device);
+    releaseFloatModel(h);
+    releaseQuantModel(h);
+    for (int i = 0; i < 8; ++i)
+        if (h->scratch[i])
+            cudaFree(h->scratch[i]);
+    if (h->ownStream && h->stream)
+        cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+const char* gmm_last_error(const gmm_handle* h) {
+    return h ? h->error.c_str() : g_createError.c_str();
+}
+
+int gmm_set_stream(gmm_handle* h, void* cuda_stream) {
+    if (!h)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    if (h->ownStream && h->stream)
+        cudaStreamDestroy(h->stream);
+    if (cuda_stream) {
+        h->stream    = (cudaStream_t)cuda_stream;
+        h->ownStream = false;
+    }
+    else {
+        GMM_CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        h->ownStream = true;
+    }
+    return GMM_OK;
+}
+
+int gmm_sync(gmm_handle* h) {
+    if (!h)
+        return GMM_ERR_ARG;
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GMM_OK;
+}
+
+uint64_t gmm_launch_count(const gmm_handle* h) {
+    return h ? h->launches : 0;
+}
+
+int gmm_float_kernel(const gmm_handle* h) {
+    return (h && h->floatValid) ? h->kernel : 0;
+}
+
+void* gmm_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 16) != cudaSuccess)
+        return nullptr;
+    return p;
+}
+
+void gmm_host_free(void* p) {
+    if (p)
+        cudaFreeHost(p);
+}
+
+static int checkOffsets(gmm_handle* h, uint32_t M, uint32_t G, const uint32_t* offsets) {
+    if (!offsets || offsets[0] != 0 || offsets[M] != G) {
+        h->setError("offsets must be a prefix sum with offsets[0] == 0 and offsets[M] == G");
+        return GMM_ERR_ARG;
+    }
+    for (uint32_t m = 0; m < M; ++m)
+        if (offsets[m + 1] < offsets[m]) {
+            h->setError("offsets must be non-decreasing");
+            return GMM_ERR_ARG;
+        }
+    return GMM_OK;
+}
+
+int gmm_upload_float(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t C, const uint32_t* offsets,
+                     const float* mean, const float* isr, const uint32_t* cov_idx, const float* w2,
+                     const float* log_norm, int mode, int kernel) {
+    if (!h)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    if (D == 0 || C == 0 || (G && (!mean || !cov_idx || !w2)) || !isr || !log_norm ||
+        (mode != GMM_MODE_MAX && mode != GMM_MODE_SUM) || kernel < GMM_KERNEL_AUTO || kernel > GMM_KERNEL_TENSOR) {
+        h->setError("gmm_upload_float: invalid argument");
+        return GMM_ERR_ARG;
+    }
+    int rc = checkOffsets(h, M, G, offsets);
+    if (rc)
+        return rc;
+    for (uint32_t g = 0; g < G; ++g)
+        if (cov_idx[g] >= C) {
+            h->setError("gmm_upload_float: covariance index out of range");
+            return GMM_ERR_ARG;
+        }
+    releaseFloatModel(h);  // a handle holds one float model; re-upload replaces it
+    h->M    = M;
+    h->G    = G;
+    h->D    = D;
+    h->C    = C;
+    h->mode = mode;
+
+    // direct layout: rows padded to a multiple of 4 floats (16/32/48/64/96/128 kernel variants)
+    uint32_t DP = D <= 16 ? 16 : D <= 32 ? 32 : D <= 48 ? 48 : D <= 64 ? 64 : D <= 96 ? 96 : 128;
+    if (D > 128) {
+        h->setError("feature dimension above 128 is not supported");
+        return GMM_ERR_UNSUPPORTED;
+    }
+    DirectModel& dm = h->direct;
+    dm.DP           = DP;
+    {
+        std::vector<float> pm((size_t)G * DP, 0.f), pi((size_t)C * DP, 0.f);
+        for (size_t g = 0; g < G; ++g)
+            memcpy(&pm[g * DP], mean + g * D, D * sizeof(float));
+        for (size_t c = 0; c < C; ++c)
+            memcpy(&pi[c * DP], isr + c * D, D * sizeof(float));
+        if ((rc = h->upload((void**)&dm.mean, pm.data(), pm.size() * sizeof(float))))
+            return rc;
+        if ((rc = h->upload((void**)&dm.isr, pi.data(), pi.size() * sizeof(float))))
+            return rc;
+        GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));  // staging vectors go out of scope
+    }
+    if ((rc = h->upload((void**)&dm.covIdx, cov_idx, (size_t)G * 4)))
+        return rc;
+    if ((rc = h->upload((void**)&dm.w2, w2, (size_t)G * 4)))
+        return rc;
+    if ((rc = h->upload((void**)&dm.logNorm, log_norm, (size_t)C * 4)))
+        return rc;
+    if ((rc = h->upload((void**)&dm.offsets, offsets, (size_t)(M + 1) * 4)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+
+    h->kernel = GMM_KERNEL_DIRECT;
+    if (kernel != GMM_KERNEL_DIRECT) {
+        rc = gmm_tc_pack(h, offsets, mean, isr, cov_idx, w2, log_norm);
+        if (rc == GMM_OK && h->tensor.valid)
+            h->kernel = GMM_KERNEL_TENSOR;
+        else if (kernel == GMM_KERNEL_TENSOR) {
+            if (rc == GMM_OK) {
+                h->setError("gmm_upload_float: model does not fit the tensor kernel");
+                rc = GMM_ERR_UNSUPPORTED;
+            }
+            return rc;
+        }
+        else if (rc != GMM_OK && rc != GMM_ERR_UNSUPPORTED)
+            return rc;
+    }
+    h->floatValid = true;
+    return GMM_OK;
+}
+
+int gmm_score_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid) {
+        h->setError("gmm_score: no float model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (ld < h->M || (T && (!d_x || !d_scores))) {
+        h->setError("gmm_score: invalid argument (ld < M or NULL buffer)");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    if (h->kernel == GMM_KERNEL_TENSOR)
+        return gmm_tc_score(h, T, d_x, d_scores, d_best, ld);
+    return gmm_direct_score(h, T, d_x, d_scores, d_best, ld);
+}
+
+static int copyOut(gmm_handle* h, void* host, const void* dev, uint32_t T, uint32_t M, size_t ld, size_t devLd) {
+    if (ld == devLd)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(host, dev, (size_t)T * ld * 4, cudaMemcpyDeviceToHost, h->stream));
+    else
+        GMM_CUDA_TRY(h, cudaMemcpy2DAsync(host, ld * 4, dev, devLd * 4, (size_t)M * 4, T, cudaMemcpyDeviceToHost,
+                                          h->stream));
+    return GMM_OK;
+}
+
+int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid) {
+        h->setError("gmm_score: no float model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (T == 0)
+        return GMM_OK;
+    if (ld < h->M || !x || !scores) {
+        h->setError("gmm_score_host: invalid argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    void *dx = nullptr, *ds = nullptr, *db = nullptr;
+    int   rc;
+    const size_t devLd = h->M;
+    if ((rc = h->reserve(SCR_X, (size_t)T * h->D * 4, &dx)))
+        return rc;
+    if ((rc = h->reserve(SCR_SCORE, (size_t)T * devLd * 4, &ds)))
+        return rc;
+    if (best && (rc = h->reserve(SCR_BEST, (size_t)T * devLd * 4, &db)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x, (size_t)T * h->D * 4, cudaMemcpyHostToDevice, h->stream));
+    if ((rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, (uint32_t*)db, devLd)))
+        return rc;
+    if ((rc = copyOut(h, scores, ds, T, h->M, ld, devLd)))
+        return rc;
+    if (best && (rc = copyOut(h, best, db, T, h->M, ld, devLd)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GMM_OK;
+}
+
+int gmm_posteriors_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_post) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid || (T && (!d_x || !d_post))) {
+        h->setError("gmm_posteriors: no float model uploaded or NULL buffer");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return gmm_direct_posteriors(h, T, d_x, d_post);
+}
+
+int gmm_upload_quant(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t Dpad, uint32_t C,
+                     const uint32_t* offsets, const uint8_t* qmean, const uint32_t* cov_idx, const int32_t* qconst,
+                     const float* isr_scaled, float scaling_squared) {
+    if (!h)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    if (D == 0 || C == 0 || Dpad < D || Dpad % 16 != 0 || Dpad > 128 || (G && (!qmean || !cov_idx || !qconst)) ||
+        !isr_scaled) {
+        h->setError("gmm_upload_quant: invalid argument (Dpad must be a multiple of 16, at most 128)");
+        return GMM_ERR_ARG;
+    }
+    int rc = checkOffsets(h, M, G, offsets);
+    if (rc)
+        return rc;
+    for (uint32_t g = 0; g < G; ++g)
+        if (cov_idx[g] >= C) {
+            h->setError("gmm_upload_quant: covariance index out of range");
+            return GMM_ERR_ARG;
+        }
+    releaseQuantModel(h);
+    QuantModel& qm = h->quant;
+    qm.M = M, qm.G = G, qm.D = D, qm.Dpad = Dpad, qm.C = C;
+    qm.scalingSquared = scaling_squared;
+    // qconst2 = qconst + |qmean|^2 with wrapping adds (the kernel adds |qx|^2 - 2 a.b)
+    std::vector<int32_t> c2(G);
+    for (size_t g = 0; g < G; ++g) {
+        uint32_t s = 0;
+        for (uint32_t d = 0; d < Dpad; ++d) {
+            uint32_t v = qmean[g * Dpad + d];
+            s += v * v;
+        }
+        c2[g] = (int32_t)((uint32_t)qconst[g] + s);
+    }
+    if ((rc = h->upload((void**)&qm.qmean, qmean, (size_t)G * Dpad, true)))
+        return rc;
+    if ((rc = h->upload((void**)&qm.covIdx, cov_idx, (size_t)G * 4, true)))
+        return rc;
+    if ((rc = h->upload((void**)&qm.qconst2, c2.data(), (size_t)G * 4, true)))
+        return rc;
+    if ((rc = h->upload((void**)&qm.isrS, isr_scaled, (size_t)C * D * 4, true)))
+        return rc;
+    if ((rc = h->upload((void**)&qm.offsets, offsets, (size_t)(M + 1) * 4, true)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    qm.valid = true;
+    return GMM_OK;
+}
+
+int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,
+                           float* d_score, uint8_t* d_qx, size_t ld) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->quant.valid) {
+        h->setError("gmm_quant_score: no quantized model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (ld < h->quant.M || (T && !d_x)) {
+        h->setError("gmm_quant_score: invalid argument (ld < M or NULL features)");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return gmm_quant_launch(h, T, d_x, d_q, d_best, d_score, d_qx, ld);
+}
+
+int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, uint32_t* best, float* score,
+                         uint8_t* qx, size_t ld) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->quant.valid) {
+        h->setError("gmm_quant_score: no quantized model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (T == 0)
+        return GMM_OK;
+    const QuantModel& qm = h->quant;
+    if (ld < qm.M || !x) {
+        h->setError("gmm_quant_score_host: invalid argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    // bound device scratch: frames in chunks
+    const size_t perFrame = (size_t)qm.M * 12 + (qx ? (size_t)qm.C * qm.Dpad : 0) + (size_t)qm.D * 4;
+    uint32_t     chunk    = (uint32_t)std::max<size_t>(1, std::min<size_t>(T, ((size_t)1 << 30) / perFrame));
+    for (uint32_t t0 = 0; t0 < T; t0 += chunk) {
+        const uint32_t n = std::min(chunk, T - t0);
+        void *dx = nullptr, *dq = nullptr, *db = nullptr, *ds = nullptr, *dqx = nullptr;
+        int   rc;
+        if ((rc = h->reserve(SCR_X, (size_t)n * qm.D * 4, &dx)))
+            return rc;
+        if (q && (rc = h->reserve(SCR_Q, (size_t)n * qm.M * 4, &dq)))
+            return rc;
+        if (best && (rc = h->reserve(SCR_BEST, (size_t)n * qm.M * 4, &db)))
+            return rc;
+        if (score && (rc = h->reserve(SCR_SCORE, (size_t)n * qm.M * 4, &ds)))
+            return rc;
+        if (qx && (rc = h->reserve(SCR_MISC, (size_t)n * qm.C * qm.Dpad, &dqx)))
+            return rc;
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x + (size_t)t0 * qm.D, (size_t)n * qm.D * 4, cudaMemcpyHostToDevice,
+                                        h->stream));
+        if ((rc = gmm_quant_launch(h, n, (const float*)dx, (int32_t*)dq, (uint32_t*)db, (float*)ds, (uint8_t*)dqx,
+                                   qm.M)))
+            return rc;
+        if (q && (rc = copyOut(h, q + (size_t)t0 * ld, dq, n, qm.M, ld, qm.M)))
+            return rc;
+        if (best && (rc = copyOut(h, best + (size_t)t0 * ld, db, n, qm.M, ld, qm.M)))
+            return rc;
+        if (score && (rc = copyOut(h, score + (size_t)t0 * ld, ds, n, qm.M, ld, qm.M)))
+            return rc;
+        if (qx)
+            GMM_CUDA_TRY(h, cudaMemcpyAsync(qx + (size_t)t0 * qm.C * qm.Dpad, dqx, (size_t)n * qm.C * qm.Dpad,
+                                            cudaMemcpyDeviceToHost, h->stream));
+        GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    }
+    return GMM_OK;
+}
+
+}  // extern "C"

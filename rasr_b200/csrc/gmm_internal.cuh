@@ -1,0 +1,95 @@
+// Internal declarations shared by the translation units of libgmm_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/gmm_b200.h"
+
+#define GMM_CUDA_TRY(h, expr)                                                                          \
+    do {                                                                                               \
+        cudaError_t e__ = (expr);                                                                      \
+        if (e__ != cudaSuccess) {                                                                      \
+            (h)->setError(std::string(#expr) + ": " + cudaGetErrorString(e__));                        \
+            return GMM_ERR_CUDA;                                                                       \
+        }                                                                                              \
+    } while (0)
+
+// ---- float model as the direct kernel reads it (slot-major, padded to DP floats per row) ---------
+struct DirectModel {
+    uint32_t  DP      = 0;        // D rounded up to a multiple of 4
+    float*    mean    = nullptr;  // [G x DP], zero padded
+    float*    isr     = nullptr;  // [C x DP], zero padded
+    uint32_t* covIdx  = nullptr;  // [G]
+    float*    w2      = nullptr;  // [G] minus2LogWeight
+    float*    logNorm = nullptr;  // [C] logNormalizationFactor
+    uint32_t* offsets = nullptr;  // [M+1]
+};
+
+// ---- float model as the tensor kernel reads it (see gmm_tc.cu for the tile image) -----------------
+struct TensorModel {
+    bool      valid     = false;
+    bool      pooled    = false;   // C == 1: whitened form, K = D; else K = 2D ([x^2, x] . [iv, -2 mu iv])
+    uint32_t  kSteps    = 0;       // 16-wide k-steps per precision part
+    uint32_t  nAtoms    = 0;       // swizzle atoms per operand row (both parts)
+    uint32_t  nTiles    = 0;       // 256-column tiles of the packed B operand
+    uint32_t  tileBytes = 0;       // bytes per B tile image
+    uint8_t*  bTiles    = nullptr; // [nTiles x tileBytes]
+    float*    center    = nullptr; // [D] translation applied to features and means (pooled form)
+    float*    isr       = nullptr; // [D] (pooled) inverse std-dev used by the frame preparation
+    uint32_t  maxMixPerHalf = 0;
+};
+
+struct QuantModel {
+    bool      valid   = false;
+    uint32_t  M = 0, G = 0, D = 0, Dpad = 0, C = 0;
+    float     scalingSquared = 0.f;
+    uint8_t*  qmean   = nullptr;  // [G x Dpad]
+    uint32_t* covIdx  = nullptr;  // [G]
+    int32_t*  qconst2 = nullptr;  // [G] qconst + sum_d qmean^2 (wrapping)
+    float*    isrS    = nullptr;  // [C x D]
+    uint32_t* offsets = nullptr;  // [M+1]
+};
+
+struct gmm_handle {
+    int          device     = 0;
+    int          smCount    = 0;
+    cudaStream_t stream     = nullptr;
+    bool         ownStream  = false;
+    uint64_t     launches   = 0;
+    std::string  error;
+
+    // float engine
+    bool        floatValid = false;
+    uint32_t    M = 0, G = 0, D = 0, C = 0;
+    int         mode = GMM_MODE_MAX, kernel = GMM_KERNEL_DIRECT;
+    DirectModel direct;
+    TensorModel tensor;
+    QuantModel  quant;
+
+    // scratch (grown on demand)
+    void*  scratch[8]      = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratchBytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::vector<void*> owned;       // device allocations of the float model
+    std::vector<void*> ownedQuant;  // device allocations of the quantized model
+
+    void setError(const std::string& s) { error = s; }
+    int  reserve(int slot, size_t bytes, void** out);
+    int  devAlloc(void** p, size_t bytes, bool quant = false);
+    int  upload(void** p, const void* src, size_t bytes, bool quant = false);
+};
+
+enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7 };
+
+// gmm_direct.cu
+int gmm_direct_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
+int gmm_direct_posteriors(gmm_handle* h, uint32_t T, const float* d_x, float* d_post);
+// gmm_quant.cu
+int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
+                     uint8_t* d_qx, size_t ld);
+// gmm_tc.cu
+int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
+                const float* w2, const float* logNorm);
+int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);

@@ -1,0 +1,339 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI (rasr_b200.capi), against the oracle and the
+golden vectors of the compiled reference.
+
+Bars: quantized scorer bit-exact (q, argmin, f32 score, quantized frames); float direct kernel bit-exact for the
+maximum approximation when fed the reference's tables, float tensor kernel and sum scorer within 1e-4 relative
+on the -log scores (BASELINE.json north_star), arg-min equal wherever the runner-up is not within tolerance.
+"""
+import numpy as np
+import pytest
+
+from conftest import (golden_names, load_golden, oracle_float_tables, oracle_quant_tables, ref_quant_tables)
+from rasr_b200 import capi, feature_scorer, synth, tables
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-4  # north_star: "within 1e-4 relative on -log scores for the float scorer"
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = capi.Engine(0)
+    yield e
+    e.close()
+
+
+def upload_float(eng, t, mode=capi.MODE_MAX, kernel=capi.KERNEL_DIRECT):
+    eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=mode, kernel=kernel)
+
+
+def upload_quant(eng, t):
+    eng.upload_quant(t["offsets"], t["qmean"], t["cov_idx"], t["qconst"], t["isr_scaled"], t["scaling_squared"])
+
+
+def assert_float_close(s, ref, rtol=RTOL):
+    fin = np.isfinite(ref) & (np.abs(ref) < 1e37)
+    assert np.array_equal(fin, np.isfinite(s) & (np.abs(s) < 1e37))
+    err = np.abs(s[fin] - ref[fin]) / np.maximum(np.abs(ref[fin]), 1.0)
+    assert err.size == 0 or err.max() <= rtol, f"max rel err {err.max():.3e}"
+    if (~fin).any():  # mixtures without a finite density: 0.5 * FLT_MAX in the reference
+        assert np.array_equal(bits(s[~fin]), bits(ref[~fin]))
+
+
+def assert_best_consistent(ms, x, best, ref_best, oracle, tab):
+    """arg-min must equal the reference's except where the two candidates' scores tie within tolerance."""
+    diff = np.argwhere(best != ref_best)
+    if diff.size == 0:
+        return
+    isr, logn, w2 = tab
+    mean, cov = tables.flatten(ms)
+    for t, m in diff[:200]:
+        a = int(ms.mix_offsets[m])
+        def sc(k):
+            g = a + int(k)
+            d = (((mean[g].astype(np.float64) - x[t]) * isr[cov[g]]) ** 2).sum()
+            return w2[g] + logn[cov[g]] + d
+        s1, s2 = sc(best[t, m]), sc(ref_best[t, m])
+        assert abs(s1 - s2) <= 2 * RTOL * max(abs(s2), 1.0), (t, m, best[t, m], ref_best[t, m], s1, s2)
+
+
+# ---------------------------------------------------------------------------------------------------
+# golden vectors of the compiled reference
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", golden_names())
+def test_golden_quantized_bit_exact(eng, name):
+    ms, z = load_golden(name)
+    upload_quant(eng, ref_quant_tables(ms, z))
+    r = eng.quant_score_host(z["x"], want_qx=True)
+    assert np.array_equal(r["qx"], z["simd_qx"])
+    assert np.array_equal(r["q"], z["simd_q"])
+    assert np.array_equal(r["best"], z["simd_best"])
+    assert np.array_equal(bits(r["score"]), bits(z["simd_score"]))
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_golden_float_direct(eng, oracle, name):
+    ms, z = load_golden(name)
+    upload_float(eng, oracle_float_tables(ms))  # the reference build's tables (rsqrt-based isr)
+    s, b = eng.score_host(z["x"])
+    assert np.array_equal(bits(s), bits(z["max_score"]))  # reference operation order: bit-identical
+    assert np.array_equal(b, z["max_best"])
+    upload_float(eng, tables.float_tables(ms))  # the product's own IEEE tables
+    s, b = eng.score_host(z["x"])
+    assert_float_close(s, z["max_score"])
+    upload_float(eng, oracle_float_tables(ms), mode=capi.MODE_SUM)
+    s, b = eng.score_host(z["x"])
+    assert_float_close(s, z["sum_score"])
+    assert np.array_equal(b, z["sum_best"])
+
+
+@pytest.mark.parametrize("name", golden_names())
+@pytest.mark.parametrize("mode", [capi.MODE_MAX, capi.MODE_SUM])
+def test_golden_float_auto_kernel(eng, oracle, name, mode):
+    ms, z = load_golden(name)
+    upload_float(eng, tables.float_tables(ms), mode=mode, kernel=capi.KERNEL_AUTO)
+    s, b = eng.score_host(z["x"])
+    assert_float_close(s, z["max_score"] if mode == capi.MODE_MAX else z["sum_score"])
+    t = oracle.float_tables(ms, exact_rsqrt=True)
+    assert_best_consistent(ms, z["x"], b, z["max_best"] if mode == capi.MODE_MAX else z["sum_best"], oracle, t)
+
+
+# ---------------------------------------------------------------------------------------------------
+# seeded random models against the oracle
+# ---------------------------------------------------------------------------------------------------
+MODELS = [
+    dict(M=257, K=16, D=45),
+    dict(M=64, K=64, D=45, seed=2),
+    dict(M=100, K=7, D=33, covariance="density", ragged=True, shared=True, zero_weight_frac=0.2, seed=3),
+    dict(M=50, K=20, D=64, covariance="mixture", seed=4),
+    dict(M=31, K=3, D=100, seed=5),
+    dict(M=40, K=150, D=12, ragged=True, seed=6),
+]
+
+
+@pytest.mark.parametrize("kw", MODELS)
+@pytest.mark.parametrize("T", [1, 33, 300])
+def test_quantized_bit_exact_vs_oracle(eng, oracle, kw, T):
+    ms = synth.make_model(**kw)
+    x = synth.make_features(ms, T)
+    x[0] *= 50.0  # saturate some components
+    t, raw = oracle_quant_tables(ms)
+    upload_quant(eng, t)
+    r = eng.quant_score_host(x, want_qx=True)
+    qx = oracle.simd_quantize_features(x, raw["isrs"])
+    q, b = oracle.simd_score(ms.mix_offsets, raw, qx)
+    assert np.array_equal(r["qx"], qx)
+    assert np.array_equal(r["q"], q)
+    assert np.array_equal(r["best"], b)
+    assert np.array_equal(bits(r["score"]), bits(oracle.simd_final_score(q, raw["scaling_squared"])))
+    # the product's own (IEEE) table builder gives the tables of a non-fast-math reference build
+    t2, raw2 = oracle_quant_tables(ms, exact_rsqrt=True)
+    mine = tables.quant_tables(ms)
+    upload_quant(eng, mine)
+    r2 = eng.quant_score_host(x)
+    qx2 = oracle.simd_quantize_features(x, raw2["isrs"])
+    q2, b2 = oracle.simd_score(ms.mix_offsets, raw2, qx2)
+    assert np.array_equal(r2["q"], q2) and np.array_equal(r2["best"], b2)
+
+
+@pytest.mark.parametrize("kw", MODELS)
+@pytest.mark.parametrize("T", [1, 33, 300])
+def test_float_direct_bit_exact_vs_oracle(eng, oracle, kw, T):
+    ms = synth.make_model(**kw)
+    x = synth.make_features(ms, T)
+    tab = oracle_float_tables(ms, mixture_weight_scale=0.9, gaussian_scale=1.2)
+    upload_float(eng, tab)
+    s, b = eng.score_host(x)
+    so, bo = oracle.score_max(ms, x, tables=(tab["isr"], tab["log_norm"], tab["w2"]))
+    assert np.array_equal(bits(s), bits(so))
+    assert np.array_equal(b, bo)
+    upload_float(eng, tab, mode=capi.MODE_SUM)
+    s, b = eng.score_host(x)
+    so, bo = oracle.score_sum(ms, x, tables=(tab["isr"], tab["log_norm"], tab["w2"]))
+    assert_float_close(s, so)
+    assert np.array_equal(b, bo)
+
+
+@pytest.mark.parametrize("kw", MODELS)
+@pytest.mark.parametrize("mode", [capi.MODE_MAX, capi.MODE_SUM])
+def test_float_auto_kernel_vs_oracle(eng, oracle, kw, mode):
+    ms = synth.make_model(**kw)
+    x = synth.make_features(ms, 300)
+    tab = tables.float_tables(ms)
+    upload_float(eng, tab, mode=mode, kernel=capi.KERNEL_AUTO)
+    s, b = eng.score_host(x)
+    f = oracle.score_max if mode == capi.MODE_MAX else oracle.score_sum
+    so, bo = f(ms, x, tables=(tab["isr"], tab["log_norm"], tab["w2"]))
+    assert_float_close(s, so)
+    assert_best_consistent(ms, x, b, bo, oracle, (tab["isr"], tab["log_norm"], tab["w2"]))
+
+
+def test_posteriors(eng, oracle):
+    import torch
+    ms = synth.make_model(M=40, K=9, D=45, ragged=True, seed=8)
+    x = synth.make_features(ms, 70)
+    tab = oracle_float_tables(ms)
+    upload_float(eng, tab, mode=capi.MODE_SUM)
+    dx = torch.from_numpy(x).cuda()
+    post = torch.empty((70, ms.G), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    eng.posteriors_device(70, dx, post)
+    eng.sync()
+    _, _, po = oracle.score_sum(ms, x, tables=(tab["isr"], tab["log_norm"], tab["w2"]), posterior=True)
+    np.testing.assert_allclose(post.cpu().numpy(), po, rtol=1e-3, atol=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------
+# edge cases
+# ---------------------------------------------------------------------------------------------------
+def test_empty_batch_and_empty_mixture(eng, oracle):
+    ms = synth.make_model(M=6, K=4, D=10, seed=9)
+    # mixture 2 gets no densities at all
+    offs = ms.mix_offsets.copy()
+    offs[3:] -= (offs[3] - offs[2])
+    keep = np.r_[0:ms.mix_offsets[2], ms.mix_offsets[3]:ms.G]
+    from rasr_b200.gms import MixtureSetData
+    ms2 = MixtureSetData(ms.D, offs, ms.mix_density[keep], ms.mix_logw[keep], ms.dens_mean, ms.dens_cov, ms.means,
+                         ms.variances)
+    x = synth.make_features(ms, 5)
+    tab = oracle_float_tables(ms2)
+    upload_float(eng, tab, kernel=capi.KERNEL_AUTO)
+    s, b = eng.score_host(x)
+    so, bo = oracle.score_max(ms2, x)
+    assert np.array_equal(bits(s[:, 2]), bits(so[:, 2])) and (b[:, 2] == 0xFFFFFFFF).all()
+    assert_float_close(s, so)
+    s0, b0 = eng.score_host(np.zeros((0, ms.D), np.float32))
+    assert s0.shape == (0, ms.M)
+    t, raw = oracle_quant_tables(ms2)
+    upload_quant(eng, t)
+    r = eng.quant_score_host(x)
+    q, bq = oracle.simd_score(ms2.mix_offsets, raw, oracle.simd_quantize_features(x, raw["isrs"]))
+    assert np.array_equal(r["q"], q) and np.array_equal(r["best"], bq)
+
+
+def test_argument_errors(eng):
+    ms = synth.make_model(M=4, K=2, D=6)
+    tab = tables.float_tables(ms)
+    upload_float(eng, tab)
+    with pytest.raises(ValueError):
+        eng.score_host(np.zeros((3, 5), np.float32))
+    with pytest.raises(capi.GmmError):
+        eng.score_host(np.zeros((3, 6), np.float32), ld=2)
+    bad = dict(tab)
+    bad["cov_idx"] = tab["cov_idx"] + 5
+    with pytest.raises(capi.GmmError):
+        upload_float(eng, bad)
+    e2 = capi.Engine(0)
+    with pytest.raises(capi.GmmError):
+        e2.D = 6
+        e2.M = 4
+        e2.score_host(np.zeros((3, 6), np.float32))
+    e2.close()
+
+
+def test_padded_leading_dimension(eng, oracle):
+    ms = synth.make_model(M=37, K=8, D=20, seed=10)
+    x = synth.make_features(ms, 19)
+    upload_float(eng, oracle_float_tables(ms), kernel=capi.KERNEL_AUTO)
+    s, b = eng.score_host(x, ld=64)
+    so, bo = oracle.score_max(ms, x)
+    assert_float_close(s[:, :37], so)
+
+
+# ---------------------------------------------------------------------------------------------------
+# full-size configurations of BASELINE.json
+# ---------------------------------------------------------------------------------------------------
+def viterbi_path(scores, states):
+    """Best path of a left-to-right HMM (loop / forward transitions, no skip; the Search::Aligner recursion of
+    /root/reference/src/Search/Aligner.cc:206-239 with zero transition scores) through emission `states`."""
+    T, S = scores.shape[0], len(states)
+    em = scores[:, states].astype(np.float64)
+    cost = np.full((T, S), np.inf)
+    back = np.zeros((T, S), np.int32)
+    cost[0, 0] = em[0, 0]
+    for t in range(1, T):
+        stay = cost[t - 1]
+        move = np.r_[np.inf, cost[t - 1, :-1]]
+        back[t] = (move < stay).astype(np.int32)
+        cost[t] = np.minimum(stay, move) + em[t]
+    path = [S - 1]
+    for t in range(T - 1, 0, -1):
+        path.append(path[-1] - back[t, path[-1]])
+    return np.array(path[::-1])
+
+
+def test_cfg1_full_size_float_and_alignment(eng, oracle):
+    ms, x = synth.make_config("cfg1")  # 4501 x 16 x 45, T = 1000
+    tab = oracle_float_tables(ms)
+    so, bo = oracle.score_max(ms, x)
+    upload_float(eng, tab, kernel=capi.KERNEL_DIRECT)
+    s, b = eng.score_host(x)
+    assert np.array_equal(bits(s), bits(so)) and np.array_equal(b, bo)
+    upload_float(eng, tables.float_tables(ms), kernel=capi.KERNEL_AUTO)
+    s2, b2 = eng.score_host(x)
+    assert_float_close(s2, so)
+    rng = np.random.default_rng(5)
+    for seg in range(4):  # identical best-path alignments on the test segments
+        states = rng.integers(0, ms.M, size=60)
+        fr = slice(seg * 250, (seg + 1) * 250)
+        assert np.array_equal(viterbi_path(s2[fr], states), viterbi_path(so[fr], states))
+
+
+def test_cfg2_full_size_quantized(eng, oracle):
+    ms, x = synth.make_config("cfg2")
+    t, raw = oracle_quant_tables(ms)
+    upload_quant(eng, t)
+    r = eng.quant_score_host(x)
+    q, b = oracle.simd_score(ms.mix_offsets, raw, oracle.simd_quantize_features(x, raw["isrs"]))
+    assert np.array_equal(r["q"], q) and np.array_equal(r["best"], b)
+    assert np.array_equal(bits(r["score"]), bits(oracle.simd_final_score(q, raw["scaling_squared"])))
+
+
+@pytest.mark.parametrize("mode", [capi.MODE_MAX, capi.MODE_SUM])
+def test_cfg3_large_model_properties(eng, oracle, mode):
+    """12001 x 64: oracle on a frame sample; batch-split invariance and frame-permutation equivariance at T=10k."""
+    ms, x = synth.make_config("cfg3", T=10000)
+    tab = tables.float_tables(ms)
+    upload_float(eng, tab, mode=mode, kernel=capi.KERNEL_AUTO)
+    s, _ = eng.score_host(x, want_best=False)
+    idx = np.random.default_rng(1).choice(10000, 48, replace=False)
+    f = oracle.score_max if mode == capi.MODE_MAX else oracle.score_sum
+    so, _ = f(ms, x[idx], tables=(tab["isr"], tab["log_norm"], tab["w2"]))
+    assert_float_close(s[idx], so)
+    perm = np.random.default_rng(2).permutation(10000)[:3000]
+    sp, _ = eng.score_host(x[perm], want_best=False)
+    assert np.array_equal(bits(sp), bits(s[perm]))  # a frame's scores do not depend on its batch neighbours
+    s1, _ = eng.score_host(x[:777], want_best=False)
+    assert np.array_equal(bits(s1), bits(s[:777]))
+
+
+def test_feature_scorer_interface_on_gpu(oracle):
+    ms = synth.make_model(M=120, K=8, D=45, seed=12)
+    x = synth.make_features(ms, 50)
+    so, bo = oracle.score_max(ms, x)
+    fs = feature_scorer.GpuFeatureScorer(ms, "diagonal-maximum", buffer_size=8, float_tables=oracle_float_tables(ms),
+                                         kernel=capi.KERNEL_DIRECT)
+    got = []
+    for f in x:
+        if not fs.bufferFilled():
+            fs.addFeature(f)
+        else:
+            got.append(fs.getScorer(f))
+            got[-1].score(0)
+    while not fs.bufferEmpty():
+        got.append(fs.flush())
+    assert len(got) == 50
+    for t in (0, 7, 8, 49):
+        assert got[t].score(5) == so[t, 5] and got[t].bestDensity(5) == bo[t, 5]
+    t, raw = oracle_quant_tables(ms)
+    fq = feature_scorer.GpuFeatureScorer(ms, "SIMD-diagonal-maximum", quant_tables=t)
+    for f in x:
+        fq.addFeature(f)
+    q, bq = oracle.simd_score(ms.mix_offsets, raw, oracle.simd_quantize_features(x, raw["isrs"]))
+    sc = oracle.simd_final_score(q, raw["scaling_squared"])
+    for t_ in range(50):
+        c = fq.flush()
+        assert c.score(3) == sc[t_, 3] and c.bestDensity(3) == bq[t_, 3]
