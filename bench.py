@@ -224,7 +224,8 @@ def run_ours(args):
     ms, frames = workload(segs)
     tab = tables.float_tables(ms)
     eng = capi.Engine(local)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()  # a real (non-default) stream: the engine launches on it, the events time it
+    torch.cuda.set_stream(stream)
     eng.set_stream(stream.cuda_stream)
     eng.upload_float(tab["offsets"], tab["mean"], tab["isr"], tab["cov_idx"], tab["w2"], tab["log_norm"],
                      mode=capi.MODE_MAX, kernel=capi.KERNEL_AUTO)

@@ -38,8 +38,12 @@ struct TensorModel {
     uint32_t  tileBytes = 0;       // bytes per B tile image
     uint8_t*  bTiles    = nullptr; // [nTiles x tileBytes]
     float*    center    = nullptr; // [D] translation applied to features and means (pooled form)
-    float*    isr       = nullptr; // [D] (pooled) inverse std-dev used by the frame preparation
+    float*    scale     = nullptr; // [D] per-dimension factor of the frame preparation (pooled: isr)
     uint32_t  maxMixPerHalf = 0;
+    uint32_t  swz       = 128;     // swizzle atom width in bytes (128 or 64)
+    uint32_t  aTileBytes = 0;
+    uint32_t  buffersB  = 0;       // B tile buffers that fit in shared memory (1 or 2)
+    uint32_t  stagesA   = 0;       // A tile ring depth with the arg-min staging enabled
 };
 
 struct QuantModel {

@@ -1,10 +1,760 @@
-// placeholder until the tcgen05 kernel lands (next commit): the model never "fits", AUTO selects direct
+// Tensor-core float scorer for sm_100a: the diagonal-Gaussian distance as one dense contraction on tcgen05
+// with accumulators in TMEM and a fused per-mixture min / log-sum-exp epilogue, so density-level scores
+// never reach HBM.  Replaces the inner loops of the reference's float scorers
+// (/root/reference/src/Mm/GaussDiagonalMaximumFeatureScorer.cc:116-218 max, :239-289 sum).
+//
+// Math (pooled covariance, C == 1; "whitened" form):
+//     a_t = (x_t - ctr) * isr            b_g = (mu_g - ctr) * isr
+//     w2_g + L + dist(x_t, g) = |a_t|^2 + ( c_g - 2 a_t.b_g ),   c_g = |b_g|^2 + L + w2_g
+//   general covariance (C > 1):  A row = [ (x s)^2 , x s ],  B row = [ iv/s^2 , -2 mu iv / s ],
+//     c_g = sum mu^2 iv + L_c + w2_g,  row term 0  (s = per-dimension scale that keeps fp16 in range).
+// Split precision: every operand value v is stored as fp16 hi = rn(v), lo = rn(v - hi) (22 significant bits);
+// the contraction runs hi.hi + lo.hi + hi.lo with f32 accumulation in TMEM (kind::f16, 2x the TF32 rate).
+// The per-Gaussian constant stays OUT of the MMA (it can be +inf for zero-weight densities): it is added in
+// the epilogue from shared memory.
+//
+// Layout.  Both operands live in HBM as ready-made shared-memory tile images (K-major, 128B- or 64B-swizzled
+// canonical UMMA layout), so one cp.async.bulk (TMA unit, SASS UBLKCP) per tile stages them:
+//   B tile  = 256 packed columns (Gaussians):  [atoms][256 rows][SWZ bytes] | c[256] f32 | slot[256] u16 | meta
+//   A tile  = 128 frames:                       [atoms][128 rows][SWZ bytes]
+// Packed columns: the live densities of a mixture are consecutive, padded to a multiple of 8 columns (pads:
+// zero row, c = +inf); a mixture never straddles a 128-column half tile.  meta = {segEnd mask, segLive mask,
+// first mixture of half 0, of half 1}: bit s of segEnd says "8-column segment s closes a mixture".
+//
+// Kernel: persistent, one CTA per SM, 12 warps: warp 0 bulk-copy producer, warp 1 MMA issuer (one elected
+// thread, M=128 N=256 K=16 per instruction), warp 2 TMEM allocator, warps 4-11 epilogue (TMEM lane quarter =
+// warp % 4, column half = (warp-4)/4).  Work item = (B tile, range of frame tiles); B stays in shared memory for
+// the whole item while A tiles stream through a ring; two 256-column accumulators in TMEM double-buffer MMA
+// against the epilogue.
+#include <cuda_fp16.h>
+#include <float.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
 #include "gmm_internal.cuh"
-int gmm_tc_pack(gmm_handle* h, const uint32_t*, const float*, const float*, const uint32_t*, const float*, const float*) {
-    h->tensor.valid = false;
+
+namespace {
+
+constexpr int kTileN       = 256;  // packed columns per B tile (UMMA N)
+constexpr int kTileM       = 128;  // frames per A tile (UMMA M, TMEM lanes)
+constexpr int kThreads     = 384;
+constexpr int kEpiWarp0    = 4;
+constexpr int kMaxStagesA  = 4;
+constexpr int kMetaBytes   = kTileN * 4 + kTileN * 2 + 16;  // c, slot, meta
+constexpr uint32_t kSmemLimit = 232448;                     // 227 KB
+
+struct TileMeta {
+    uint32_t segEnd, segLive, mixBase0, mixBase1;
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "WAIT_%=:\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+            "@p bra DONE_%=;\n\t"
+            "bra WAIT_%=;\n\t"
+            "DONE_%=:\n\t}" ::"r"(bar),
+            "r"(parity)
+            : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t dTmem, uint64_t aDesc, uint64_t bDesc, uint32_t idesc,
+                                           uint32_t accumulate) {
+    asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(dTmem),
+            "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
+            : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+    asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr)
+            : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// UMMA shared-memory descriptor, K-major, swizzled canonical layout (8-row groups of SWZ-byte rows).
+template<int SWZ>
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    constexpr uint64_t layout = SWZ == 128 ? 2ull : 4ull;  // SWIZZLE_128B : SWIZZLE_64B
+    constexpr uint64_t sbo    = (8 * SWZ) >> 4;            // stride between 8-row groups
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | (sbo << 32) | (1ull << 46) | (layout << 61);
+}
+
+struct KParams {
+    const uint8_t* bTiles;
+    const uint8_t* aTiles;
+    const float*   rowTerm;
+    float*         scores;
+    uint32_t*      best;
+    size_t         ld;
+    uint32_t       T;
+    uint32_t       nTiles, frameTiles, split;  // items = nTiles * split
+    uint32_t       kSteps;                     // k-steps (16 elements) per precision part
+    uint32_t       atoms;                      // swizzle atoms per operand row
+    uint32_t       aTileBytes, bTileBytes;     // bTileBytes includes c / slot / meta
+    uint32_t       stagesA, buffersB;
+    uint32_t       stagePitch;                 // floats per staging row (maxMixPerHalf + 1)
+};
+
+// MODE 0 = max, 1 = sum.  BEST: also write the index of the winning density.
+template<int SWZ, int MODE, bool BEST>
+__global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) {
+    extern __shared__ uint8_t smemRaw[];
+    // swizzled operand tiles need 1024-byte alignment of the shared-memory address itself
+    uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // carve shared memory: [B buffers][A stages][staging][barriers]
+    const uint32_t bBytes    = (p.bTileBytes + 1023u) & ~1023u;
+    uint8_t*       sB        = smem;
+    uint8_t*       sA        = sB + (size_t)p.buffersB * bBytes;
+    float*         sStage    = reinterpret_cast<float*>(sA + (size_t)p.stagesA * p.aTileBytes);
+    const uint32_t stageWarp = 32 * p.stagePitch;  // floats per warp
+    uint32_t*      sStageB   = reinterpret_cast<uint32_t*>(sStage + 8 * stageWarp);
+    uint64_t*      bars      = reinterpret_cast<uint64_t*>(sStageB + (BEST ? 8 * stageWarp : 0));
+    // barrier indices
+    uint64_t* fullA     = bars;                    // [kMaxStagesA]
+    uint64_t* emptyA    = bars + kMaxStagesA;      // [kMaxStagesA]
+    uint64_t* fullB     = bars + 2 * kMaxStagesA;  // [2]
+    uint64_t* emptyB    = fullB + 2;               // [2]
+    uint64_t* tmemFull  = emptyB + 2;              // [2]
+    uint64_t* tmemEmpty = tmemFull + 2;            // [2]
+    uint32_t* tmemSlot  = reinterpret_cast<uint32_t*>(tmemEmpty + 2);
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kMaxStagesA; ++i) {
+            mbar_init(smem_u32(&fullA[i]), 1);
+            mbar_init(smem_u32(&emptyA[i]), 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(smem_u32(&fullB[i]), 1);
+            mbar_init(smem_u32(&emptyB[i]), 1 + 8);  // MMA commit + 8 epilogue warps
+            mbar_init(smem_u32(&tmemFull[i]), 1);
+            mbar_init(smem_u32(&tmemEmpty[i]), 8);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmemSlot)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmemBase = *tmemSlot;
+
+    const uint32_t items        = p.nTiles * p.split;
+    const uint32_t tilesPerItem = (p.frameTiles + p.split - 1) / p.split;
+
+    if (warp == 0) {
+        // ===== producer: one lane issues the bulk copies =====
+        if (lane == 0) {
+            uint32_t stage = 0, phaseA = 0, itemCount = 0;
+            for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
+                const uint32_t nt = item / p.split, chunk = item % p.split;
+                const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+                if (f0 >= f1)
+                    continue;
+                const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+                mbar_wait(smem_u32(&emptyB[b]), (useB & 1) ^ 1);
+                mbar_expect_tx(smem_u32(&fullB[b]), p.bTileBytes);
+                bulk_g2s(smem_u32(sB + (size_t)b * bBytes), p.bTiles + (size_t)nt * p.bTileBytes, p.bTileBytes,
+                         smem_u32(&fullB[b]));
+                for (uint32_t f = f0; f < f1; ++f) {
+                    mbar_wait(smem_u32(&emptyA[stage]), phaseA ^ 1);
+                    mbar_expect_tx(smem_u32(&fullA[stage]), p.aTileBytes);
+                    bulk_g2s(smem_u32(sA + (size_t)stage * p.aTileBytes), p.aTiles + (size_t)f * p.aTileBytes,
+                             p.aTileBytes, smem_u32(&fullA[stage]));
+                    if (++stage == p.stagesA) {
+                        stage = 0;
+                        phaseA ^= 1;
+                    }
+                }
+            }
+        }
+    }
+    else if (warp == 1) {
+        // ===== MMA issuer: one lane issues tcgen05.mma for the whole CTA =====
+        if (lane == 0) {
+            // instruction descriptor: D=f32, A=B=f16, K-major both, N=256, M=128
+            constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+            constexpr uint32_t kPerAtom = SWZ / 32;  // 16-element k-steps per swizzle atom
+            uint32_t stage = 0, phaseA = 0, itemCount = 0, tileCount = 0;
+            for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
+                const uint32_t chunk = item % p.split;
+                const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+                if (f0 >= f1)
+                    continue;
+                const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+                mbar_wait(smem_u32(&fullB[b]), useB & 1);
+                const uint32_t bAddr = smem_u32(sB + (size_t)b * bBytes);
+                for (uint32_t f = f0; f < f1; ++f, ++tileCount) {
+                    const uint32_t acc = tileCount & 1, useAcc = tileCount >> 1;
+                    mbar_wait(smem_u32(&tmemEmpty[acc]), (useAcc & 1) ^ 1);
+                    mbar_wait(smem_u32(&fullA[stage]), phaseA);
+                    tc_fence_after();
+                    const uint32_t aAddr = smem_u32(sA + (size_t)stage * p.aTileBytes);
+                    const uint32_t dTmem = tmemBase + acc * kTileN;
+                    uint32_t       first = 1;
+                    // hi.hi, lo.hi, hi.lo
+#pragma unroll 1
+                    for (uint32_t pair = 0; pair < 3; ++pair) {
+                        const uint32_t pa = (pair == 1) ? p.kSteps : 0, pb = (pair == 2) ? p.kSteps : 0;
+                        for (uint32_t ks = 0; ks < p.kSteps; ++ks) {
+                            const uint32_t ka = pa + ks, kb = pb + ks;
+                            const uint32_t ao = (ka / kPerAtom) * (kTileM * SWZ) + (ka % kPerAtom) * 32;
+                            const uint32_t bo = (kb / kPerAtom) * (kTileN * SWZ) + (kb % kPerAtom) * 32;
+                            tc_mma_f16(dTmem, umma_desc<SWZ>(aAddr + ao), umma_desc<SWZ>(bAddr + bo), idesc,
+                                       first ? 0u : 1u);
+                            first = 0;
+                        }
+                    }
+                    tc_commit(smem_u32(&emptyA[stage]));   // A stage free when these MMAs retire
+                    tc_commit(smem_u32(&tmemFull[acc]));   // accumulator ready for the epilogue
+                    if (f + 1 == f1)
+                        tc_commit(smem_u32(&emptyB[b]));   // B buffer no longer read by the tensor core
+                    if (++stage == p.stagesA) {
+                        stage = 0;
+                        phaseA ^= 1;
+                    }
+                }
+            }
+        }
+    }
+    else if (warp >= kEpiWarp0) {
+        // ===== epilogue: TMEM -> registers -> (+c, min / log-sum-exp per mixture) -> staged -> global =====
+        const int      e = warp - kEpiWarp0, q = warp & 3, half = e >> 2;
+        float*         stg  = sStage + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
+        uint32_t*      stgB = sStageB + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
+        uint32_t       itemCount = 0, tileCount = 0;
+        constexpr float kHalfLog2e = 0.72134752044448170368f;  // 0.5 * log2(e)
+        constexpr float kLn2       = 0.69314718055994530942f;
+        for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
+            const uint32_t nt = item / p.split, chunk = item % p.split;
+            const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+            if (f0 >= f1)
+                continue;
+            (void)nt;
+            const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+            mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            const uint8_t*  tile  = sB + (size_t)b * bBytes + (size_t)p.atoms * kTileN * SWZ;
+            const float4*   cvec  = reinterpret_cast<const float4*>(tile) + half * 32;  // 128 floats per half
+            const uint16_t* slots = reinterpret_cast<const uint16_t*>(tile + kTileN * 4);
+            const TileMeta  meta  = *reinterpret_cast<const TileMeta*>(tile + kTileN * 4 + kTileN * 2);
+            const uint32_t  segEnd  = (meta.segEnd >> (16 * half)) & 0xFFFFu;
+            const uint32_t  segLive = (meta.segLive >> (16 * half)) & 0xFFFFu;
+            const uint32_t  mixBase = half ? meta.mixBase1 : meta.mixBase0;
+            const uint32_t  nMix    = __popc(segEnd);
+            for (uint32_t f = f0; f < f1; ++f, ++tileCount) {
+                const uint32_t acc = tileCount & 1, useAcc = tileCount >> 1;
+                const uint32_t row = f * kTileM + q * 32 + lane;
+                const float    rt  = p.rowTerm[row];
+                mbar_wait(smem_u32(&tmemFull[acc]), useAcc & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + half * 128;
+                float    run = INFINITY, sum = 0.f;
+                uint32_t idx = 0xFFFFFFFFu, cnt = 0;
+#pragma unroll 1
+                for (int ch = 0; ch < 4; ++ch) {
+                    uint32_t v[32];
+                    tmem_ld32(taddr + ch * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int s = 0; s < 4; ++s) {
+                        const int    seg = ch * 4 + s;
+                        const float4 c0 = cvec[seg * 2], c1 = cvec[seg * 2 + 1];
+                        float        u[8];
+                        u[0] = __uint_as_float(v[s * 8 + 0]) + c0.x;
+                        u[1] = __uint_as_float(v[s * 8 + 1]) + c0.y;
+                        u[2] = __uint_as_float(v[s * 8 + 2]) + c0.z;
+                        u[3] = __uint_as_float(v[s * 8 + 3]) + c0.w;
+                        u[4] = __uint_as_float(v[s * 8 + 4]) + c1.x;
+                        u[5] = __uint_as_float(v[s * 8 + 5]) + c1.y;
+                        u[6] = __uint_as_float(v[s * 8 + 6]) + c1.z;
+                        u[7] = __uint_as_float(v[s * 8 + 7]) + c1.w;
+                        if (MODE == 0 && !BEST) {
+                            float m8 = fminf(fminf(fminf(u[0], u[1]), fminf(u[2], u[3])),
+                                             fminf(fminf(u[4], u[5]), fminf(u[6], u[7])));
+                            run      = fminf(run, m8);
+                        }
+                        else if (MODE == 0) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (u[j] < run) {
+                                    run = u[j];
+                                    idx = (uint32_t)(half * 128 + seg * 8 + j);
+                                }
+                        }
+                        else if ((segLive >> seg) & 1u) {  // uniform: skip all-pad segments (inf - inf)
+                            float m8 = u[0];
+                            int   j8 = 0;
+#pragma unroll
+                            for (int j = 1; j < 8; ++j)
+                                if (u[j] < m8) {
+                                    m8 = u[j];
+                                    j8 = j;
+                                }
+                            if (m8 < run) {
+                                sum *= ex2((m8 - run) * kHalfLog2e);  // run == inf -> factor 0 (sum is 0 anyway)
+                                run = m8;
+                                idx = (uint32_t)(half * 128 + seg * 8 + j8);
+                            }
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                sum += ex2((run - u[j]) * kHalfLog2e);
+                        }
+                        if ((segEnd >> seg) & 1u) {  // uniform across the warp
+                            float sc;
+                            if (MODE == 0)
+                                sc = 0.5f * (fminf(run, FLT_MAX) + rt);
+                            else
+                                sc = 0.5f * (fminf(run, FLT_MAX) + rt) - kLn2 * __log2f(sum);
+                            stg[cnt] = sc;
+                            if (BEST)
+                                stgB[cnt] = (idx == 0xFFFFFFFFu) ? idx : (uint32_t)slots[idx];
+                            ++cnt;
+                            run = INFINITY;
+                            sum = 0.f;
+                            idx = 0xFFFFFFFFu;
+                        }
+                    }
+                }
+                // accumulator drained: hand it back to the MMA warp before the global stores
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0)
+                    mbar_arrive(smem_u32(&tmemEmpty[acc]));
+                // coalesced store of the staged [32 rows x nMix] block
+                const uint32_t total = 32 * nMix;
+                const float*   wst   = sStage + (size_t)e * stageWarp;
+                const uint32_t* wsb  = sStageB + (size_t)e * stageWarp;
+                const uint32_t rbase = f * kTileM + q * 32;
+                for (uint32_t i = lane; i < total; i += 32) {
+                    const uint32_t r = i / nMix, j = i - r * nMix;
+                    if (rbase + r < p.T) {
+                        const size_t o = (size_t)(rbase + r) * p.ld + mixBase + j;
+                        p.scores[o]    = wst[r * p.stagePitch + j];
+                        if (BEST)
+                            p.best[o] = wsb[r * p.stagePitch + j];
+                    }
+                }
+                __syncwarp();
+            }
+            // this warp no longer reads c / slot / meta of the B buffer
+            if (lane == 0)
+                mbar_arrive(smem_u32(&emptyB[b]));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmemBase));
+    }
+}
+
+// ---- swizzled tile image addressing (host + device) ---------------------------------------------------
+// byte offset of 16-byte chunk `c16` of row `row` inside one atom block [rows][SWZ bytes]
+__host__ __device__ inline uint32_t swz_offset(uint32_t row, uint32_t c16, uint32_t swz) {
+    const uint32_t lin  = row * swz + c16 * 16;
+    const uint32_t mask = (swz / 16) - 1;  // 7 for 128B, 3 for 64B
+    return lin ^ (((lin >> 7) & mask) << 4);
+}
+
+__device__ __forceinline__ void split_fp16(float v, __half& hi, __half& lo) {
+    v  = fminf(fmaxf(v, -60000.f), 60000.f);
+    hi = __float2half_rn(v);
+    lo = __float2half_rn(v - __half2float(hi));
+}
+
+// Frame preparation: x [T x D] -> A tile images (fp16 hi | lo parts, swizzled) + row terms.
+//   pooled : a = (x - ctr) * isr,                 K = D,   row term = |a|^2
+//   general: a = [ ((x - ctr) s)^2 , (x - ctr) s ], K = 2D, row term = 0
+// One thread per (frame, 8-element chunk of one precision part pair); the row term by a second small pass.
+template<bool POOLED>
+__global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t D, uint32_t frameTiles,
+                               const float* __restrict__ ctr, const float* __restrict__ scale, uint32_t kSteps,
+                               uint32_t atoms, uint32_t swz, uint8_t* __restrict__ aTiles,
+                               float* __restrict__ rowTerm) {
+    const uint32_t chunks = kSteps * 2;  // 8-element chunks per precision part
+    const uint32_t total  = frameTiles * kTileM * chunks;
+    const uint32_t epa    = swz / 2;     // fp16 elements per atom row
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const uint32_t t = i / chunks, ch = i % chunks;
+        __align__(16) __half hi[8], lo[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t k = ch * 8 + j;
+            float          v = 0.f;
+            if (t < T) {
+                if (POOLED) {
+                    if (k < D)
+                        v = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
+                }
+                else if (k < D) {
+                    const float y = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
+                    v             = y * y;
+                }
+                else if (k < 2 * D) {
+                    v = (x[(size_t)t * D + (k - D)] - ctr[k - D]) * scale[k - D];
+                }
+            }
+            split_fp16(v, hi[j], lo[j]);
+        }
+        const uint32_t tile = t / kTileM, row = t % kTileM;
+        uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * swz;
+        const uint32_t kHi = ch * 8, kLo = kSteps * 16 + ch * 8;
+        *reinterpret_cast<uint4*>(base + (size_t)(kHi / epa) * kTileM * swz + swz_offset(row, (kHi % epa) / 8, swz)) =
+                *reinterpret_cast<const uint4*>(hi);
+        *reinterpret_cast<uint4*>(base + (size_t)(kLo / epa) * kTileM * swz + swz_offset(row, (kLo % epa) / 8, swz)) =
+                *reinterpret_cast<const uint4*>(lo);
+    }
+    // row terms and the zero padding of partially used atoms
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < frameTiles * kTileM; t += gridDim.x * blockDim.x) {
+        float r = 0.f;
+        if (POOLED && t < T) {
+            for (uint32_t k = 0; k < D; ++k) {
+                const float a = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
+                r             = fmaf(a, a, r);
+            }
+        }
+        rowTerm[t] = r;
+        const uint32_t used = kSteps * 2 * 2, all = atoms * (swz / 16);  // 16-byte chunks per row
+        const uint32_t tile = t / kTileM, row = t % kTileM;
+        uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * swz;
+        for (uint32_t c = used; c < all; ++c)
+            *reinterpret_cast<uint4*>(base + (size_t)(c / (swz / 16)) * kTileM * swz +
+                                      swz_offset(row, c % (swz / 16), swz)) = make_uint4(0, 0, 0, 0);
+    }
+}
+
+// host-side fp16 split (round to nearest even), mirrors split_fp16
+void host_split(float v, uint16_t& hi, uint16_t& lo) {
+    v         = std::min(std::max(v, -60000.f), 60000.f);
+    __half h  = __float2half_rn(v);
+    float  hf = __half2float(h);
+    __half l  = __float2half_rn(v - hf);
+    memcpy(&hi, &h, 2);
+    memcpy(&lo, &l, 2);
+}
+
+template<int SWZ, int MODE, bool BEST>
+cudaError_t launch_tc(const KParams& p, int grid, size_t smemBytes, cudaStream_t stream) {
+    cudaError_t e = cudaFuncSetAttribute(tc_score_kernel<SWZ, MODE, BEST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smemBytes);
+    if (e != cudaSuccess)
+        return e;
+    tc_score_kernel<SWZ, MODE, BEST><<<grid, kThreads, smemBytes, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+// ---- host side: packing --------------------------------------------------------------------------------
+static uint32_t smemNeed(uint32_t bTileBytes, uint32_t aTileBytes, uint32_t buffersB, uint32_t stagesA,
+                         uint32_t pitch, bool best) {
+    const uint32_t bBytes = (bTileBytes + 1023u) & ~1023u;
+    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 8 * 32 * pitch * 4 * (best ? 2 : 1) + 512;
+}
+
+int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
+                const float* w2, const float* logNorm) {
+    TensorModel& tm = h->tensor;
+    tm              = TensorModel();
+    const uint32_t M = h->M, G = h->G, D = h->D, C = h->C;
+    if (G == 0 || M == 0)
+        return GMM_OK;
+    const char* env = getenv("GMM_TC_SWIZZLE");
+    tm.swz          = (env && atoi(env) == 64) ? 64 : 128;
+    tm.pooled       = (C == 1);
+    const uint32_t kel = tm.pooled ? D : 2 * D;
+    tm.kSteps          = (kel + 15) / 16;
+    tm.nAtoms          = (tm.kSteps * 64 + tm.swz - 1) / tm.swz;
+    tm.aTileBytes      = tm.nAtoms * kTileM * tm.swz;
+    tm.tileBytes       = tm.nAtoms * kTileN * tm.swz + kMetaBytes;
+
+    // ---- column assignment ----
+    struct Col {
+        uint32_t g;     // slot, or 0xFFFFFFFF for a pad
+        uint16_t slot;  // density index within the mixture
+    };
+    std::vector<Col>      cols;
+    std::vector<TileMeta> metas;
+    std::vector<uint32_t> mixPerHalf;
+    auto halfOf = [&]() { return (uint32_t)(cols.size() / 128); };
+    auto ensureHalf = [&](uint32_t hf) {
+        while (metas.size() * 2 <= hf) {
+            TileMeta z = {0, 0, 0, 0};
+            metas.push_back(z);
+        }
+        while (mixPerHalf.size() <= hf)
+            mixPerHalf.push_back(0);
+    };
+    for (uint32_t m = 0; m < M; ++m) {
+        std::vector<uint32_t> live;
+        for (uint32_t g = offsets[m]; g < offsets[m + 1]; ++g)
+            if (isfinite(w2[g]) && isfinite(logNorm[covIdx[g]]))
+                live.push_back(g);
+        uint32_t padded = std::max<uint32_t>(8, (uint32_t)((live.size() + 7) / 8 * 8));
+        if (padded > 128 || offsets[m + 1] - offsets[m] > 0xFFFF)
+            return GMM_OK;  // does not fit the tensor kernel: tm.valid stays false
+        const uint32_t inHalf = (uint32_t)(cols.size() % 128);
+        if (inHalf + padded > 128) {
+            const Col pad = {0xFFFFFFFFu, 0xFFFF};
+            cols.insert(cols.end(), 128 - inHalf, pad);
+        }
+        const uint32_t hf = halfOf();
+        ensureHalf(hf);
+        TileMeta& mt = metas[hf / 2];
+        if (mixPerHalf[hf] == 0)
+            (hf & 1 ? mt.mixBase1 : mt.mixBase0) = m;
+        mixPerHalf[hf]++;
+        const uint32_t seg0 = (uint32_t)((cols.size() % 256) / 8);
+        for (uint32_t i = 0; i < padded; ++i) {
+            Col c = {0xFFFFFFFFu, 0xFFFF};
+            if (i < live.size()) {
+                c.g    = live[i];
+                c.slot = (uint16_t)(live[i] - offsets[m]);
+            }
+            cols.push_back(c);
+        }
+        const uint32_t nseg = padded / 8;
+        for (uint32_t s = 0; s < nseg; ++s)
+            if (s * 8 < live.size())
+                mt.segLive |= 1u << (seg0 + s);
+        mt.segEnd |= 1u << (seg0 + nseg - 1);
+    }
+    {
+        const Col pad = {0xFFFFFFFFu, 0xFFFF};
+        while (cols.size() % kTileN)
+            cols.push_back(pad);
+    }
+    tm.nTiles = (uint32_t)(cols.size() / kTileN);
+    ensureHalf(tm.nTiles * 2 - 1);
+    tm.maxMixPerHalf = 1;
+    for (uint32_t v : mixPerHalf)
+        tm.maxMixPerHalf = std::max(tm.maxMixPerHalf, v);
+
+    // ---- shared-memory configuration (sized for the arg-min variant) ----
+    const uint32_t pitch = tm.maxMixPerHalf + 1;
+    tm.buffersB = 0;
+    for (uint32_t nb = 2; nb >= 1 && !tm.buffersB; --nb)
+        for (uint32_t sa = kMaxStagesA; sa >= 2; --sa)
+            if (smemNeed(tm.tileBytes, tm.aTileBytes, nb, sa, pitch, true) <= kSmemLimit) {
+                tm.buffersB = nb;
+                tm.stagesA  = sa;
+                break;
+            }
+    if (!tm.buffersB)
+        return GMM_OK;  // operand tiles too large for shared memory (very high dimension): direct kernel
+
+    // ---- centre / scale ----
+    std::vector<double> ctr(D, 0.0);
+    size_t              nLive = 0;
+    for (const Col& c : cols)
+        if (c.g != 0xFFFFFFFFu) {
+            for (uint32_t d = 0; d < D; ++d)
+                ctr[d] += mean[(size_t)c.g * D + d];
+            ++nLive;
+        }
+    std::vector<float> ctrF(D), scaleF(D);
+    for (uint32_t d = 0; d < D; ++d)
+        ctrF[d] = nLive ? (float)(ctr[d] / (double)nLive) : 0.f;
+    if (tm.pooled) {
+        for (uint32_t d = 0; d < D; ++d)
+            scaleF[d] = isr[d];
+    }
+    else {
+        for (uint32_t d = 0; d < D; ++d) {
+            double s = 0.0;
+            for (uint32_t c = 0; c < C; ++c)
+                s += (double)isr[(size_t)c * D + d] * isr[(size_t)c * D + d];
+            scaleF[d] = (float)sqrt(s / C);
+        }
+    }
+
+    // ---- tile images ----
+    std::vector<uint8_t> img((size_t)tm.nTiles * tm.tileBytes, 0);
+    const uint32_t       epa = tm.swz / 2;
+    std::vector<float>   row(tm.kSteps * 16);
+    for (uint32_t t = 0; t < tm.nTiles; ++t) {
+        uint8_t*  base  = img.data() + (size_t)t * tm.tileBytes;
+        float*    cOut  = reinterpret_cast<float*>(base + (size_t)tm.nAtoms * kTileN * tm.swz);
+        uint16_t* slOut = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(cOut) + kTileN * 4);
+        TileMeta* mOut  = reinterpret_cast<TileMeta*>(reinterpret_cast<uint8_t*>(slOut) + kTileN * 2);
+        *mOut           = metas[t];
+        for (uint32_t r = 0; r < (uint32_t)kTileN; ++r) {
+            const Col& col = cols[(size_t)t * kTileN + r];
+            slOut[r]       = col.slot;
+            if (col.g == 0xFFFFFFFFu) {
+                cOut[r] = INFINITY;
+                continue;
+            }
+            const float* mu = mean + (size_t)col.g * D;
+            const float* is = isr + (size_t)covIdx[col.g] * D;
+            std::fill(row.begin(), row.end(), 0.f);
+            double cc = (double)logNorm[covIdx[col.g]] + (double)w2[col.g];
+            for (uint32_t d = 0; d < D; ++d) {
+                const double mc = (double)mu[d] - (double)ctrF[d];
+                if (tm.pooled) {
+                    const double b = mc * (double)is[d];
+                    row[d]         = (float)(-2.0 * b);
+                    cc += b * b;
+                }
+                else {
+                    const double iv = (double)is[d] * (double)is[d], s = scaleF[d];
+                    row[d]          = (float)(iv / (s * s));
+                    row[D + d]      = (float)(-2.0 * mc * iv / s);
+                    cc += mc * mc * iv;
+                }
+            }
+            cOut[r] = (float)cc;
+            for (uint32_t k = 0; k < tm.kSteps * 16; ++k) {
+                uint16_t hi, lo;
+                host_split(row[k], hi, lo);
+                const uint32_t kl = tm.kSteps * 16 + k;
+                uint8_t* pHi = base + (size_t)(k / epa) * kTileN * tm.swz + swz_offset(r, (k % epa) / 8, tm.swz) + (k % 8) * 2;
+                uint8_t* pLo = base + (size_t)(kl / epa) * kTileN * tm.swz + swz_offset(r, (kl % epa) / 8, tm.swz) + (kl % 8) * 2;
+                memcpy(pHi, &hi, 2);
+                memcpy(pLo, &lo, 2);
+            }
+        }
+    }
+    int rc;
+    if ((rc = h->upload((void**)&tm.bTiles, img.data(), img.size())))
+        return rc;
+    if ((rc = h->upload((void**)&tm.center, ctrF.data(), D * 4)))
+        return rc;
+    if ((rc = h->upload((void**)&tm.scale, scaleF.data(), D * 4)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    tm.valid = true;
     return GMM_OK;
 }
-int gmm_tc_score(gmm_handle* h, uint32_t, const float*, float*, uint32_t*, size_t) {
-    h->setError("tensor kernel not built");
-    return GMM_ERR_UNSUPPORTED;
+
+int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld) {
+    const TensorModel& tm = h->tensor;
+    if (T == 0)
+        return GMM_OK;
+    const uint32_t FT = (T + kTileM - 1) / kTileM;
+    void *         aT = nullptr, *rT = nullptr;
+    int            rc;
+    if ((rc = h->reserve(SCR_A, (size_t)FT * tm.aTileBytes, &aT)))
+        return rc;
+    if ((rc = h->reserve(SCR_ROW, (size_t)FT * kTileM * 4, &rT)))
+        return rc;
+    {
+        const uint32_t total  = FT * kTileM * tm.kSteps * 2;
+        int            blocks = (int)std::min<uint32_t>((total + 255) / 256, (uint32_t)h->smCount * 8);
+        if (tm.pooled)
+            tc_prep_kernel<true><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps,
+                                                                tm.nAtoms, tm.swz, (uint8_t*)aT, (float*)rT);
+        else
+            tc_prep_kernel<false><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps,
+                                                                 tm.nAtoms, tm.swz, (uint8_t*)aT, (float*)rT);
+        h->launches++;
+        GMM_CUDA_TRY(h, cudaGetLastError());
+    }
+    KParams p;
+    p.bTiles     = tm.bTiles;
+    p.aTiles     = (const uint8_t*)aT;
+    p.rowTerm    = (const float*)rT;
+    p.scores     = d_scores;
+    p.best       = d_best;
+    p.ld         = ld;
+    p.T          = T;
+    p.nTiles     = tm.nTiles;
+    p.frameTiles = FT;
+    p.kSteps     = tm.kSteps;
+    p.atoms      = tm.nAtoms;
+    p.aTileBytes = tm.aTileBytes;
+    p.bTileBytes = tm.tileBytes;
+    p.buffersB   = tm.buffersB;
+    p.stagePitch = tm.maxMixPerHalf + 1;
+    const bool best = d_best != nullptr;
+    // A ring depth: whatever shared memory allows for this variant
+    p.stagesA = tm.stagesA;
+    while (p.stagesA < (uint32_t)kMaxStagesA &&
+           smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA + 1, p.stagePitch, best) <= kSmemLimit)
+        p.stagesA++;
+    const size_t smemBytes = smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best);
+    // split the frame range so that the items fill the SMs evenly: cost in A-tile MMA times
+    const double bCost = tm.buffersB == 2 ? 0.5 : 2.0;
+    uint32_t     bestS = 1;
+    double       bestCost = 1e300;
+    for (uint32_t S = 1; S <= std::min<uint32_t>(FT, 64); ++S) {
+        const uint32_t per = (FT + S - 1) / S;
+        if ((uint64_t)per * (S - 1) >= FT)
+            continue;  // an empty chunk
+        const uint64_t items  = (uint64_t)tm.nTiles * S;
+        const uint64_t rounds = (items + h->smCount - 1) / h->smCount;
+        const double   cost   = (double)rounds * (per + bCost);
+        if (cost < bestCost - 1e-9) {
+            bestCost = cost;
+            bestS    = S;
+        }
+    }
+    p.split        = bestS;
+    const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
+    cudaError_t e;
+    const int   mode = h->mode == GMM_MODE_SUM ? 1 : 0;
+#define GMM_TC_LAUNCH(SWZ)                                                                                   \
+    (mode == 0 ? (best ? launch_tc<SWZ, 0, true>(p, grid, smemBytes, h->stream)                               \
+                       : launch_tc<SWZ, 0, false>(p, grid, smemBytes, h->stream))                             \
+               : (best ? launch_tc<SWZ, 1, true>(p, grid, smemBytes, h->stream)                               \
+                       : launch_tc<SWZ, 1, false>(p, grid, smemBytes, h->stream)))
+    if (tm.swz == 128)
+        e = GMM_TC_LAUNCH(128);
+    else
+        e = GMM_TC_LAUNCH(64);
+#undef GMM_TC_LAUNCH
+    h->launches++;
+    GMM_CUDA_TRY(h, e);
+    return GMM_OK;
 }
