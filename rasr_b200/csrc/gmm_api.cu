@@ -245,7 +245,7 @@ int gmm_upload_float(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t
 
     h->kernel = GMM_KERNEL_DIRECT;
     if (kernel != GMM_KERNEL_DIRECT) {
-        rc = gmm_tc_pack(h, offsets, mean, isr, cov_idx, w2, log_norm);
+        rc = gmm_tc_pack(h, offsets, mean, isr, cov_idx, w2, log_norm, kernel == GMM_KERNEL_TENSOR);
         if (rc == GMM_OK && h->tensor.valid)
             h->kernel = GMM_KERNEL_TENSOR;
         else if (kernel == GMM_KERNEL_TENSOR) {

@@ -95,5 +95,5 @@ int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, 
                      uint8_t* d_qx, size_t ld);
 // gmm_tc.cu
 int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
-                const float* w2, const float* logNorm);
+                const float* w2, const float* logNorm, bool force);
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);

@@ -128,7 +128,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
 struct KParams {
     const uint8_t* bTiles;
     const uint8_t* aTiles;
-    const float*   rowTerm;
+    const float2*  rowInfo;  // per frame row: {row term |a|^2, power-of-two row scale}
     float*         scores;
     uint32_t*      best;
     size_t         ld;
@@ -140,6 +140,83 @@ struct KParams {
     uint32_t       stagesA, buffersB;
     uint32_t       stagePitch;                 // floats per staging row (maxMixPerHalf + 1)
 };
+
+struct EpiState {
+    float    run, sum;
+    uint32_t idx, cnt;
+};
+
+// One 32-column chunk (four 8-column segments) of a row's accumulator: u = acc * rowScale + c, then the
+// running per-mixture min (+ arg-min) or online log-sum-exp; a closing segment stages the mixture's score.
+template<int MODE, bool BEST>
+__device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, const float4* __restrict__ cvec,
+                                          const uint16_t* __restrict__ slots, uint32_t segEnd, uint32_t segLive,
+                                          float rt, float rs, float* stg, uint32_t* stgB, EpiState& st) {
+    constexpr float kHalfLog2e = 0.72134752044448170368f;  // 0.5 * log2(e)
+    constexpr float kLn2       = 0.69314718055994530942f;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int    seg = ch * 4 + s;
+        const float4 c0 = cvec[seg * 2], c1 = cvec[seg * 2 + 1];
+        float        u[8];
+        u[0] = fmaf(__uint_as_float(v[s * 8 + 0]), rs, c0.x);
+        u[1] = fmaf(__uint_as_float(v[s * 8 + 1]), rs, c0.y);
+        u[2] = fmaf(__uint_as_float(v[s * 8 + 2]), rs, c0.z);
+        u[3] = fmaf(__uint_as_float(v[s * 8 + 3]), rs, c0.w);
+        u[4] = fmaf(__uint_as_float(v[s * 8 + 4]), rs, c1.x);
+        u[5] = fmaf(__uint_as_float(v[s * 8 + 5]), rs, c1.y);
+        u[6] = fmaf(__uint_as_float(v[s * 8 + 6]), rs, c1.z);
+        u[7] = fmaf(__uint_as_float(v[s * 8 + 7]), rs, c1.w);
+        if (MODE == 0 && !BEST) {
+            float m8 = fminf(fminf(fminf(u[0], u[1]), fminf(u[2], u[3])), fminf(fminf(u[4], u[5]), fminf(u[6], u[7])));
+            st.run   = fminf(st.run, m8);
+        }
+        else if (MODE == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (u[j] < st.run) {
+                    st.run = u[j];
+                    st.idx = (uint32_t)(half * 128 + seg * 8 + j);
+                }
+        }
+        else if ((segLive >> seg) & 1u) {  // uniform: skip all-pad segments (inf - inf)
+            float m8 = u[0];
+            int   j8 = 0;
+#pragma unroll
+            for (int j = 1; j < 8; ++j)
+                if (u[j] < m8) {
+                    m8 = u[j];
+                    j8 = j;
+                }
+            // exp(-0.5 * 40) < 2^-28: a segment that far above the running best of every frame of the warp
+            // cannot change an f32 sum that is >= 1
+            if (__any_sync(0xffffffffu, !(m8 - st.run >= 40.f))) {
+                if (m8 < st.run) {
+                    st.sum *= ex2((m8 - st.run) * kHalfLog2e);  // run == inf -> factor 0 (sum is 0 anyway)
+                    st.run = m8;
+                    st.idx = (uint32_t)(half * 128 + seg * 8 + j8);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    st.sum += ex2((st.run - u[j]) * kHalfLog2e);
+            }
+        }
+        if ((segEnd >> seg) & 1u) {  // uniform across the warp
+            float sc;
+            if (MODE == 0)
+                sc = 0.5f * (fminf(st.run, FLT_MAX) + rt);
+            else
+                sc = 0.5f * (fminf(st.run, FLT_MAX) + rt) - kLn2 * __log2f(st.sum);
+            stg[st.cnt] = sc;
+            if (BEST)
+                stgB[st.cnt] = (st.idx == 0xFFFFFFFFu) ? st.idx : (uint32_t)slots[st.idx];
+            ++st.cnt;
+            st.run = INFINITY;
+            st.sum = 0.f;
+            st.idx = 0xFFFFFFFFu;
+        }
+    }
+}
 
 // MODE 0 = max, 1 = sum.  BEST: also write the index of the winning density.
 template<int SWZ, int MODE, bool BEST>
@@ -272,8 +349,6 @@ __global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) 
         float*         stg  = sStage + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
         uint32_t*      stgB = sStageB + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
         uint32_t       itemCount = 0, tileCount = 0;
-        constexpr float kHalfLog2e = 0.72134752044448170368f;  // 0.5 * log2(e)
-        constexpr float kLn2       = 0.69314718055994530942f;
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
             const uint32_t nt = item / p.split, chunk = item % p.split;
             const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
@@ -293,89 +368,42 @@ __global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) 
             for (uint32_t f = f0; f < f1; ++f, ++tileCount) {
                 const uint32_t acc = tileCount & 1, useAcc = tileCount >> 1;
                 const uint32_t row = f * kTileM + q * 32 + lane;
-                const float    rt  = p.rowTerm[row];
+                const float2   ri  = p.rowInfo[row];
+                const float    rt = ri.x, rs = ri.y;
                 mbar_wait(smem_u32(&tmemFull[acc]), useAcc & 1);
                 tc_fence_after();
                 const uint32_t taddr = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + half * 128;
-                float    run = INFINITY, sum = 0.f;
-                uint32_t idx = 0xFFFFFFFFu, cnt = 0;
-#pragma unroll 1
-                for (int ch = 0; ch < 4; ++ch) {
-                    uint32_t v[32];
-                    tmem_ld32(taddr + ch * 32, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int s = 0; s < 4; ++s) {
-                        const int    seg = ch * 4 + s;
-                        const float4 c0 = cvec[seg * 2], c1 = cvec[seg * 2 + 1];
-                        float        u[8];
-                        u[0] = __uint_as_float(v[s * 8 + 0]) + c0.x;
-                        u[1] = __uint_as_float(v[s * 8 + 1]) + c0.y;
-                        u[2] = __uint_as_float(v[s * 8 + 2]) + c0.z;
-                        u[3] = __uint_as_float(v[s * 8 + 3]) + c0.w;
-                        u[4] = __uint_as_float(v[s * 8 + 4]) + c1.x;
-                        u[5] = __uint_as_float(v[s * 8 + 5]) + c1.y;
-                        u[6] = __uint_as_float(v[s * 8 + 6]) + c1.z;
-                        u[7] = __uint_as_float(v[s * 8 + 7]) + c1.w;
-                        if (MODE == 0 && !BEST) {
-                            float m8 = fminf(fminf(fminf(u[0], u[1]), fminf(u[2], u[3])),
-                                             fminf(fminf(u[4], u[5]), fminf(u[6], u[7])));
-                            run      = fminf(run, m8);
-                        }
-                        else if (MODE == 0) {
-#pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                if (u[j] < run) {
-                                    run = u[j];
-                                    idx = (uint32_t)(half * 128 + seg * 8 + j);
-                                }
-                        }
-                        else if ((segLive >> seg) & 1u) {  // uniform: skip all-pad segments (inf - inf)
-                            float m8 = u[0];
-                            int   j8 = 0;
-#pragma unroll
-                            for (int j = 1; j < 8; ++j)
-                                if (u[j] < m8) {
-                                    m8 = u[j];
-                                    j8 = j;
-                                }
-                            if (m8 < run) {
-                                sum *= ex2((m8 - run) * kHalfLog2e);  // run == inf -> factor 0 (sum is 0 anyway)
-                                run = m8;
-                                idx = (uint32_t)(half * 128 + seg * 8 + j8);
-                            }
-#pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                sum += ex2((run - u[j]) * kHalfLog2e);
-                        }
-                        if ((segEnd >> seg) & 1u) {  // uniform across the warp
-                            float sc;
-                            if (MODE == 0)
-                                sc = 0.5f * (fminf(run, FLT_MAX) + rt);
-                            else
-                                sc = 0.5f * (fminf(run, FLT_MAX) + rt) - kLn2 * __log2f(sum);
-                            stg[cnt] = sc;
-                            if (BEST)
-                                stgB[cnt] = (idx == 0xFFFFFFFFu) ? idx : (uint32_t)slots[idx];
-                            ++cnt;
-                            run = INFINITY;
-                            sum = 0.f;
-                            idx = 0xFFFFFFFFu;
-                        }
-                    }
-                }
-                // accumulator drained: hand it back to the MMA warp before the global stores
+                EpiState st;
+                st.run = INFINITY, st.sum = 0.f, st.idx = 0xFFFFFFFFu, st.cnt = 0;
+                // TMEM -> registers in four 32-column chunks, the next load in flight while one is reduced
+                uint32_t va[32], vb[32];
+                tmem_ld32(taddr, va);
+                tmem_ld_wait();
+                tmem_ld32(taddr + 32, vb);
+                epi_chunk<MODE, BEST>(va, 0, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                tmem_ld_wait();
+                tmem_ld32(taddr + 64, va);
+                epi_chunk<MODE, BEST>(vb, 1, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                tmem_ld_wait();
+                tmem_ld32(taddr + 96, vb);
+                epi_chunk<MODE, BEST>(va, 2, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                tmem_ld_wait();
+                // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0)
                     mbar_arrive(smem_u32(&tmemEmpty[acc]));
+                epi_chunk<MODE, BEST>(vb, 3, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                __syncwarp();
                 // coalesced store of the staged [32 rows x nMix] block
                 const uint32_t total = 32 * nMix;
                 const float*   wst   = sStage + (size_t)e * stageWarp;
                 const uint32_t* wsb  = sStageB + (size_t)e * stageWarp;
                 const uint32_t rbase = f * kTileM + q * 32;
+                const bool     pow2  = (nMix & (nMix - 1)) == 0;
+                const uint32_t sh    = 31 - __clz(nMix | 1);
                 for (uint32_t i = lane; i < total; i += 32) {
-                    const uint32_t r = i / nMix, j = i - r * nMix;
+                    const uint32_t r = pow2 ? (i >> sh) : (i / nMix), j = i - r * nMix;
                     if (rbase + r < p.T) {
                         const size_t o = (size_t)(rbase + r) * p.ld + mixBase + j;
                         p.scores[o]    = wst[r * p.stagePitch + j];
@@ -413,62 +441,76 @@ __device__ __forceinline__ void split_fp16(float v, __half& hi, __half& lo) {
     lo = __float2half_rn(v - __half2float(hi));
 }
 
-// Frame preparation: x [T x D] -> A tile images (fp16 hi | lo parts, swizzled) + row terms.
-//   pooled : a = (x - ctr) * isr,                 K = D,   row term = |a|^2
-//   general: a = [ ((x - ctr) s)^2 , (x - ctr) s ], K = 2D, row term = 0
-// One thread per (frame, 8-element chunk of one precision part pair); the row term by a second small pass.
+// Frame preparation: x [T x D] -> A tile images (fp16 hi | lo parts, swizzled) + per-row {term, scale}.
+//   pooled : a = (x - ctr) * isr,                   K = D,   row term = |a|^2
+//   general: a = [ ((x - ctr) s)^2 , (x - ctr) s ],  K = 2D,  row term = 0
+// A row whose largest |a| would leave the fp16 range is stored divided by a power of two (row scale); the
+// epilogue multiplies the accumulator back (one FFMA with the constant add), so outlier frames stay exact.
+// One warp per frame: lane l owns the 8-element chunk l of each precision part (kSteps <= 16 -> <= 32 chunks).
 template<bool POOLED>
 __global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t D, uint32_t frameTiles,
                                const float* __restrict__ ctr, const float* __restrict__ scale, uint32_t kSteps,
                                uint32_t atoms, uint32_t swz, uint8_t* __restrict__ aTiles,
-                               float* __restrict__ rowTerm) {
+                               float2* __restrict__ rowInfo) {
     const uint32_t chunks = kSteps * 2;  // 8-element chunks per precision part
-    const uint32_t total  = frameTiles * kTileM * chunks;
     const uint32_t epa    = swz / 2;     // fp16 elements per atom row
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const uint32_t t = i / chunks, ch = i % chunks;
-        __align__(16) __half hi[8], lo[8];
+    const uint32_t lane   = threadIdx.x & 31;
+    const uint32_t warpsPerGrid = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < frameTiles * kTileM; t += warpsPerGrid) {
+        float v[8];
+        float vmax = 0.f, ssq = 0.f;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const uint32_t k = ch * 8 + j;
-            float          v = 0.f;
-            if (t < T) {
+            const uint32_t k = lane * 8 + j;
+            v[j]             = 0.f;
+            if (t < T && lane < chunks) {
                 if (POOLED) {
-                    if (k < D)
-                        v = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
+                    if (k < D) {
+                        v[j] = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
+                        ssq  = fmaf(v[j], v[j], ssq);
+                    }
                 }
                 else if (k < D) {
                     const float y = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
-                    v             = y * y;
+                    v[j]          = y * y;
                 }
                 else if (k < 2 * D) {
-                    v = (x[(size_t)t * D + (k - D)] - ctr[k - D]) * scale[k - D];
+                    v[j] = (x[(size_t)t * D + (k - D)] - ctr[k - D]) * scale[k - D];
                 }
             }
-            split_fp16(v, hi[j], lo[j]);
+            vmax = fmaxf(vmax, fabsf(v[j]));
         }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+            ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+        }
+        // power-of-two row scale: largest |a| / rs <= 16384 (non-finite frames are passed through clamped)
+        float rs = 1.f;
+        if (vmax > 16384.f && vmax < 3.0e38f) {
+            int e;
+            frexpf(vmax, &e);  // vmax = m * 2^e, m in [0.5, 1)
+            rs = ldexpf(1.f, e - 14);
+        }
+        const float inv = 1.f / rs;
+        if (lane == 0)
+            rowInfo[t] = make_float2(ssq, rs);
         const uint32_t tile = t / kTileM, row = t % kTileM;
         uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * swz;
-        const uint32_t kHi = ch * 8, kLo = kSteps * 16 + ch * 8;
-        *reinterpret_cast<uint4*>(base + (size_t)(kHi / epa) * kTileM * swz + swz_offset(row, (kHi % epa) / 8, swz)) =
-                *reinterpret_cast<const uint4*>(hi);
-        *reinterpret_cast<uint4*>(base + (size_t)(kLo / epa) * kTileM * swz + swz_offset(row, (kLo % epa) / 8, swz)) =
-                *reinterpret_cast<const uint4*>(lo);
-    }
-    // row terms and the zero padding of partially used atoms
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < frameTiles * kTileM; t += gridDim.x * blockDim.x) {
-        float r = 0.f;
-        if (POOLED && t < T) {
-            for (uint32_t k = 0; k < D; ++k) {
-                const float a = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
-                r             = fmaf(a, a, r);
-            }
+        if (lane < chunks) {
+            __align__(16) __half hi[8], lo[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                split_fp16(v[j] * inv, hi[j], lo[j]);
+            const uint32_t kHi = lane * 8, kLo = kSteps * 16 + lane * 8;
+            *reinterpret_cast<uint4*>(base + (size_t)(kHi / epa) * kTileM * swz +
+                                      swz_offset(row, (kHi % epa) / 8, swz)) = *reinterpret_cast<const uint4*>(hi);
+            *reinterpret_cast<uint4*>(base + (size_t)(kLo / epa) * kTileM * swz +
+                                      swz_offset(row, (kLo % epa) / 8, swz)) = *reinterpret_cast<const uint4*>(lo);
         }
-        rowTerm[t] = r;
-        const uint32_t used = kSteps * 2 * 2, all = atoms * (swz / 16);  // 16-byte chunks per row
-        const uint32_t tile = t / kTileM, row = t % kTileM;
-        uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * swz;
-        for (uint32_t c = used; c < all; ++c)
+        // zero the unused tail of the last atom
+        const uint32_t used = chunks * 2, all = atoms * (swz / 16);  // 16-byte chunks per row
+        for (uint32_t c = used + lane; c < all; c += 32)
             *reinterpret_cast<uint4*>(base + (size_t)(c / (swz / 16)) * kTileM * swz +
                                       swz_offset(row, c % (swz / 16), swz)) = make_uint4(0, 0, 0, 0);
     }
@@ -504,7 +546,7 @@ static uint32_t smemNeed(uint32_t bTileBytes, uint32_t aTileBytes, uint32_t buff
 }
 
 int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
-                const float* w2, const float* logNorm) {
+                const float* w2, const float* logNorm, bool force) {
     TensorModel& tm = h->tensor;
     tm              = TensorModel();
     const uint32_t M = h->M, G = h->G, D = h->D, C = h->C;
@@ -623,6 +665,7 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     std::vector<uint8_t> img((size_t)tm.nTiles * tm.tileBytes, 0);
     const uint32_t       epa = tm.swz / 2;
     std::vector<float>   row(tm.kSteps * 16);
+    double               kappa = 0.0;  // largest squared Mahalanobis norm of a centred mean
     for (uint32_t t = 0; t < tm.nTiles; ++t) {
         uint8_t*  base  = img.data() + (size_t)t * tm.tileBytes;
         float*    cOut  = reinterpret_cast<float*>(base + (size_t)tm.nAtoms * kTileN * tm.swz);
@@ -639,22 +682,23 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
             const float* mu = mean + (size_t)col.g * D;
             const float* is = isr + (size_t)covIdx[col.g] * D;
             std::fill(row.begin(), row.end(), 0.f);
-            double cc = (double)logNorm[covIdx[col.g]] + (double)w2[col.g];
+            double cc = (double)logNorm[covIdx[col.g]] + (double)w2[col.g], kap = 0.0;
             for (uint32_t d = 0; d < D; ++d) {
                 const double mc = (double)mu[d] - (double)ctrF[d];
                 if (tm.pooled) {
                     const double b = mc * (double)is[d];
                     row[d]         = (float)(-2.0 * b);
-                    cc += b * b;
+                    kap += b * b;
                 }
                 else {
                     const double iv = (double)is[d] * (double)is[d], s = scaleF[d];
                     row[d]          = (float)(iv / (s * s));
                     row[D + d]      = (float)(-2.0 * mc * iv / s);
-                    cc += mc * mc * iv;
+                    kap += mc * mc * iv;
                 }
             }
-            cOut[r] = (float)cc;
+            cOut[r] = (float)(cc + kap);
+            kappa   = std::max(kappa, kap);
             for (uint32_t k = 0; k < tm.kSteps * 16; ++k) {
                 uint16_t hi, lo;
                 host_split(row[k], hi, lo);
@@ -666,6 +710,11 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
             }
         }
     }
+    // The expanded form |a|^2 + |b|^2 - 2 a.b cancels in f32: its absolute error grows like 2^-22 * |b|^2 while a
+    // frame next to such a mean has a score of order D/2.  Models whose centred, whitened means are further out
+    // than 8 sigma (rms per dimension) keep the 1e-4 relative bar only in the direct kernel.
+    if (!force && kappa > 64.0 * D)
+        return GMM_OK;
     int rc;
     if ((rc = h->upload((void**)&tm.bTiles, img.data(), img.size())))
         return rc;
@@ -687,24 +736,23 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
     int            rc;
     if ((rc = h->reserve(SCR_A, (size_t)FT * tm.aTileBytes, &aT)))
         return rc;
-    if ((rc = h->reserve(SCR_ROW, (size_t)FT * kTileM * 4, &rT)))
+    if ((rc = h->reserve(SCR_ROW, (size_t)FT * kTileM * 8, &rT)))
         return rc;
     {
-        const uint32_t total  = FT * kTileM * tm.kSteps * 2;
-        int            blocks = (int)std::min<uint32_t>((total + 255) / 256, (uint32_t)h->smCount * 8);
+        int blocks = (int)std::min<uint32_t>((FT * kTileM + 7) / 8, (uint32_t)h->smCount * 8);
         if (tm.pooled)
             tc_prep_kernel<true><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps,
-                                                                tm.nAtoms, tm.swz, (uint8_t*)aT, (float*)rT);
+                                                                tm.nAtoms, tm.swz, (uint8_t*)aT, (float2*)rT);
         else
             tc_prep_kernel<false><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps,
-                                                                 tm.nAtoms, tm.swz, (uint8_t*)aT, (float*)rT);
+                                                                 tm.nAtoms, tm.swz, (uint8_t*)aT, (float2*)rT);
         h->launches++;
         GMM_CUDA_TRY(h, cudaGetLastError());
     }
     KParams p;
     p.bTiles     = tm.bTiles;
     p.aTiles     = (const uint8_t*)aT;
-    p.rowTerm    = (const float*)rT;
+    p.rowInfo    = (const float2*)rT;
     p.scores     = d_scores;
     p.best       = d_best;
     p.ld         = ld;
