@@ -10,16 +10,17 @@
 //     c_g = sum mu^2 iv + L_c + w2_g,  row term 0  (s = per-dimension scale that keeps fp16 in range).
 // Split precision: every operand value v is stored as fp16 hi = rn(v), lo = rn(v - hi) (22 significant bits);
 // the contraction runs hi.hi + lo.hi + hi.lo with f32 accumulation in TMEM (kind::f16, 2x the TF32 rate).
-// The per-Gaussian constant stays OUT of the MMA (it can be +inf for zero-weight densities): it is added in
-// the epilogue from shared memory.
+// The per-Gaussian constant c_g rides in three spare K columns as fp16 pieces c0+c1+c2 (33 bits) against ones
+// on the frame side, so the accumulator already holds c_g - 2 a.b and the max-approx epilogue is a bare min
+// tree.  Zero-weight densities (c = +inf in the reference) are dropped at packing time: they never win a min.
 //
 // Layout.  Both operands live in HBM as ready-made shared-memory tile images (K-major, 128B- or 64B-swizzled
 // canonical UMMA layout), so one cp.async.bulk (TMA unit, SASS UBLKCP) per tile stages them:
-//   B tile  = 256 packed columns (Gaussians):  [atoms][256 rows][SWZ bytes] | c[256] f32 | slot[256] u16 | meta
+//   B tile  = 256 packed columns (Gaussians):  [atoms][256 rows][SWZ bytes] | slot[256] u16 | TileMeta
 //   A tile  = 128 frames:                       [atoms][128 rows][SWZ bytes]
-// Packed columns: the live densities of a mixture are consecutive, padded to a multiple of 8 columns (pads:
-// zero row, c = +inf); a mixture never straddles a 128-column half tile.  meta = {segEnd mask, segLive mask,
-// first mixture of half 0, of half 1}: bit s of segEnd says "8-column segment s closes a mixture".
+// Packed columns: the live densities of a mixture are consecutive, padded to a multiple of 8 columns (a pad
+// repeats the mixture's first live column); a mixture never straddles a 128-column half tile.  TileMeta: bit s
+// of segEnd says "8-column segment s closes a mixture", plus live-column counts and the first mixture per half.
 //
 // Kernel: persistent, one CTA per SM, 12 warps: warp 0 bulk-copy producer, warp 1 MMA issuer (one elected
 // thread, M=128 N=256 K=16 per instruction), warp 2 TMEM allocator, warps 4-11 epilogue (TMEM lane quarter =
@@ -43,11 +44,14 @@ constexpr int kTileM       = 128;  // frames per A tile (UMMA M, TMEM lanes)
 constexpr int kThreads     = 384;
 constexpr int kEpiWarp0    = 4;
 constexpr int kMaxStagesA  = 4;
-constexpr int kMetaBytes   = kTileN * 4 + kTileN * 2 + 16;  // c, slot, meta
+constexpr int kMetaBytes   = kTileN * 2 + 32;  // slot[256] u16, TileMeta
 constexpr uint32_t kSmemLimit = 232448;                     // 227 KB
 
 struct TileMeta {
-    uint32_t segEnd, segLive, mixBase0, mixBase1;
+    uint32_t segEnd;       // bit s: 8-column segment s closes a mixture
+    uint32_t segEmpty;     // bit s (on a closing segment): the mixture has no live density at all
+    uint32_t mixBase0, mixBase1;  // first mixture of column half 0 / 1
+    uint32_t live[4];      // 4 bits per segment: live columns - 1 (pads repeat the first live column)
 };
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
@@ -146,27 +150,22 @@ struct EpiState {
     uint32_t idx, cnt;
 };
 
-// One 32-column chunk (four 8-column segments) of a row's accumulator: u = acc * rowScale + c, then the
-// running per-mixture min (+ arg-min) or online log-sum-exp; a closing segment stages the mixture's score.
+// One 32-column chunk (four 8-column segments) of a row's accumulator.  The accumulator already holds
+// u / rowScale with u = c - 2 a.b (the constant rides in spare K columns of the contraction), so the maximum
+// approximation is a bare min tree over TMEM values; a closing segment stages the mixture's score.
 template<int MODE, bool BEST>
-__device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, const float4* __restrict__ cvec,
-                                          const uint16_t* __restrict__ slots, uint32_t segEnd, uint32_t segLive,
-                                          float rt, float rs, float* stg, uint32_t* stgB, EpiState& st) {
-    constexpr float kHalfLog2e = 0.72134752044448170368f;  // 0.5 * log2(e)
-    constexpr float kLn2       = 0.69314718055994530942f;
+__device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, const uint16_t* __restrict__ slots,
+                                          uint32_t segEnd, uint32_t segEmpty, uint64_t liveBits, float rt, float rs,
+                                          float* stg, uint32_t* stgB, EpiState& st) {
+    constexpr float kLn2 = 0.69314718055994530942f;
+    const float     hl2e = 0.72134752044448170368f * rs;  // 0.5 * log2(e) * rowScale
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
-        const int    seg = ch * 4 + s;
-        const float4 c0 = cvec[seg * 2], c1 = cvec[seg * 2 + 1];
-        float        u[8];
-        u[0] = fmaf(__uint_as_float(v[s * 8 + 0]), rs, c0.x);
-        u[1] = fmaf(__uint_as_float(v[s * 8 + 1]), rs, c0.y);
-        u[2] = fmaf(__uint_as_float(v[s * 8 + 2]), rs, c0.z);
-        u[3] = fmaf(__uint_as_float(v[s * 8 + 3]), rs, c0.w);
-        u[4] = fmaf(__uint_as_float(v[s * 8 + 4]), rs, c1.x);
-        u[5] = fmaf(__uint_as_float(v[s * 8 + 5]), rs, c1.y);
-        u[6] = fmaf(__uint_as_float(v[s * 8 + 6]), rs, c1.z);
-        u[7] = fmaf(__uint_as_float(v[s * 8 + 7]), rs, c1.w);
+        const int seg = ch * 4 + s;
+        float     u[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            u[j] = __uint_as_float(v[s * 8 + j]);
         if (MODE == 0 && !BEST) {
             float m8 = fminf(fminf(fminf(u[0], u[1]), fminf(u[2], u[3])), fminf(fminf(u[4], u[5]), fminf(u[6], u[7])));
             st.run   = fminf(st.run, m8);
@@ -174,14 +173,15 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, c
         else if (MODE == 0) {
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-                if (u[j] < st.run) {
+                if (u[j] < st.run) {  // pads repeat the first live column: never strictly smaller
                     st.run = u[j];
                     st.idx = (uint32_t)(half * 128 + seg * 8 + j);
                 }
         }
-        else if ((segLive >> seg) & 1u) {  // uniform: skip all-pad segments (inf - inf)
-            float m8 = u[0];
-            int   j8 = 0;
+        else {
+            const int live = (int)((liveBits >> (seg * 4)) & 15ull) + 1;  // uniform
+            float     m8 = u[0];
+            int       j8 = 0;
 #pragma unroll
             for (int j = 1; j < 8; ++j)
                 if (u[j] < m8) {
@@ -190,26 +190,27 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, c
                 }
             // exp(-0.5 * 40) < 2^-28: a segment that far above the running best of every frame of the warp
             // cannot change an f32 sum that is >= 1
-            if (__any_sync(0xffffffffu, !(m8 - st.run >= 40.f))) {
+            if (__any_sync(0xffffffffu, !((m8 - st.run) * rs >= 40.f))) {
                 if (m8 < st.run) {
-                    st.sum *= ex2((m8 - st.run) * kHalfLog2e);  // run == inf -> factor 0 (sum is 0 anyway)
+                    st.sum *= ex2((m8 - st.run) * hl2e);  // run == inf -> factor 0 (sum is 0 anyway)
                     st.run = m8;
                     st.idx = (uint32_t)(half * 128 + seg * 8 + j8);
                 }
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
-                    st.sum += ex2((st.run - u[j]) * kHalfLog2e);
+                    if (j < live)
+                        st.sum += ex2((st.run - u[j]) * hl2e);
             }
         }
         if ((segEnd >> seg) & 1u) {  // uniform across the warp
-            float sc;
-            if (MODE == 0)
-                sc = 0.5f * (fminf(st.run, FLT_MAX) + rt);
-            else
-                sc = 0.5f * (fminf(st.run, FLT_MAX) + rt) - kLn2 * __log2f(st.sum);
+            const bool  empty = (segEmpty >> seg) & 1u;
+            const float best  = empty ? FLT_MAX : fminf(st.run * rs, FLT_MAX);
+            float       sc    = 0.5f * (best + rt);
+            if (MODE == 1)
+                sc = empty ? INFINITY : sc - kLn2 * __log2f(st.sum);
             stg[st.cnt] = sc;
             if (BEST)
-                stgB[st.cnt] = (st.idx == 0xFFFFFFFFu) ? st.idx : (uint32_t)slots[st.idx];
+                stgB[st.cnt] = (empty || st.idx == 0xFFFFFFFFu) ? 0xFFFFFFFFu : (uint32_t)slots[st.idx];
             ++st.cnt;
             st.run = INFINITY;
             st.sum = 0.f;
@@ -358,12 +359,13 @@ __global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) 
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
             const uint8_t*  tile  = sB + (size_t)b * bBytes + (size_t)p.atoms * kTileN * SWZ;
-            const float4*   cvec  = reinterpret_cast<const float4*>(tile) + half * 32;  // 128 floats per half
-            const uint16_t* slots = reinterpret_cast<const uint16_t*>(tile + kTileN * 4);
-            const TileMeta  meta  = *reinterpret_cast<const TileMeta*>(tile + kTileN * 4 + kTileN * 2);
+            const uint16_t* slots = reinterpret_cast<const uint16_t*>(tile);
+            const TileMeta  meta  = *reinterpret_cast<const TileMeta*>(tile + kTileN * 2);
             const uint32_t  segEnd  = (meta.segEnd >> (16 * half)) & 0xFFFFu;
-            const uint32_t  segLive = (meta.segLive >> (16 * half)) & 0xFFFFu;
             const uint32_t  mixBase = half ? meta.mixBase1 : meta.mixBase0;
+            const uint32_t  segEmpty = (meta.segEmpty >> (16 * half)) & 0xFFFFu;
+            const uint64_t  liveBits = half ? ((uint64_t)meta.live[3] << 32 | meta.live[2])
+                                            : ((uint64_t)meta.live[1] << 32 | meta.live[0]);
             const uint32_t  nMix    = __popc(segEnd);
             for (uint32_t f = f0; f < f1; ++f, ++tileCount) {
                 const uint32_t acc = tileCount & 1, useAcc = tileCount >> 1;
@@ -380,20 +382,20 @@ __global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) 
                 tmem_ld32(taddr, va);
                 tmem_ld_wait();
                 tmem_ld32(taddr + 32, vb);
-                epi_chunk<MODE, BEST>(va, 0, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                epi_chunk<MODE, BEST>(va, 0, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
                 tmem_ld_wait();
                 tmem_ld32(taddr + 64, va);
-                epi_chunk<MODE, BEST>(vb, 1, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                epi_chunk<MODE, BEST>(vb, 1, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
                 tmem_ld_wait();
                 tmem_ld32(taddr + 96, vb);
-                epi_chunk<MODE, BEST>(va, 2, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                epi_chunk<MODE, BEST>(va, 2, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
                 tmem_ld_wait();
                 // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0)
                     mbar_arrive(smem_u32(&tmemEmpty[acc]));
-                epi_chunk<MODE, BEST>(vb, 3, half, cvec, slots, segEnd, segLive, rt, rs, stg, stgB, st);
+                epi_chunk<MODE, BEST>(vb, 3, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
                 __syncwarp();
                 // coalesced store of the staged [32 rows x nMix] block
                 const uint32_t total = 32 * nMix;
@@ -445,7 +447,8 @@ __device__ __forceinline__ void split_fp16(float v, __half& hi, __half& lo) {
 //   pooled : a = (x - ctr) * isr,                   K = D,   row term = |a|^2
 //   general: a = [ ((x - ctr) s)^2 , (x - ctr) s ],  K = 2D,  row term = 0
 // A row whose largest |a| would leave the fp16 range is stored divided by a power of two (row scale); the
-// epilogue multiplies the accumulator back (one FFMA with the constant add), so outlier frames stay exact.
+// epilogue multiplies the per-mixture minimum back, so outlier frames stay exact.  Three spare K columns hold
+// 1/rowScale: they multiply the fp16 pieces of the per-Gaussian constant stored in the B operand.
 // One warp per frame: lane l owns the 8-element chunk l of each precision part (kSteps <= 16 -> <= 32 chunks).
 template<bool POOLED>
 __global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t D, uint32_t frameTiles,
@@ -455,6 +458,7 @@ __global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t
     const uint32_t chunks = kSteps * 2;  // 8-element chunks per precision part
     const uint32_t epa    = swz / 2;     // fp16 elements per atom row
     const uint32_t lane   = threadIdx.x & 31;
+    const uint32_t kel    = POOLED ? D : 2 * D;
     const uint32_t warpsPerGrid = gridDim.x * (blockDim.x >> 5);
     for (uint32_t t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < frameTiles * kTileM; t += warpsPerGrid) {
         float v[8];
@@ -478,6 +482,8 @@ __global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t
                     v[j] = (x[(size_t)t * D + (k - D)] - ctr[k - D]) * scale[k - D];
                 }
             }
+            if (k >= kel && k < kel + 3)
+                v[j] = 1.f;  // multiplies the three fp16 pieces of the per-Gaussian constant (stored as 1/rowScale)
             vmax = fmaxf(vmax, fabsf(v[j]));
         }
 #pragma unroll
@@ -556,15 +562,15 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     tm.swz          = (env && atoi(env) == 64) ? 64 : 128;
     tm.pooled       = (C == 1);
     const uint32_t kel = tm.pooled ? D : 2 * D;
-    tm.kSteps          = (kel + 15) / 16;
+    tm.kSteps          = (kel + 3 + 15) / 16;  // 3 spare K columns carry the per-Gaussian constant
     tm.nAtoms          = (tm.kSteps * 64 + tm.swz - 1) / tm.swz;
     tm.aTileBytes      = tm.nAtoms * kTileM * tm.swz;
     tm.tileBytes       = tm.nAtoms * kTileN * tm.swz + kMetaBytes;
 
     // ---- column assignment ----
     struct Col {
-        uint32_t g;     // slot, or 0xFFFFFFFF for a pad
-        uint16_t slot;  // density index within the mixture
+        uint32_t g;     // slot whose operand row fills the column, or 0xFFFFFFFF for a zero filler column
+        uint16_t slot;  // density index within the mixture (0xFFFF: pad / filler)
     };
     std::vector<Col>      cols;
     std::vector<TileMeta> metas;
@@ -572,7 +578,7 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     auto halfOf = [&]() { return (uint32_t)(cols.size() / 128); };
     auto ensureHalf = [&](uint32_t hf) {
         while (metas.size() * 2 <= hf) {
-            TileMeta z = {0, 0, 0, 0};
+            TileMeta z = {0, 0, 0, 0, {0, 0, 0, 0}};
             metas.push_back(z);
         }
         while (mixPerHalf.size() <= hf)
@@ -604,12 +610,19 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
                 c.g    = live[i];
                 c.slot = (uint16_t)(live[i] - offsets[m]);
             }
+            else if (!live.empty()) {
+                c.g = live[0];  // pad: repeats the first live column, so it never changes a min / strict arg-min
+            }
             cols.push_back(c);
         }
         const uint32_t nseg = padded / 8;
-        for (uint32_t s = 0; s < nseg; ++s)
-            if (s * 8 < live.size())
-                mt.segLive |= 1u << (seg0 + s);
+        for (uint32_t s = 0; s < nseg; ++s) {
+            const uint32_t gs = seg0 + s;
+            const uint32_t lv = live.size() > s * 8 ? std::min<uint32_t>(8, (uint32_t)live.size() - s * 8) : 1;
+            mt.live[gs >> 3] |= (lv - 1) << ((gs & 7) * 4);
+        }
+        if (live.empty())
+            mt.segEmpty |= 1u << (seg0 + nseg - 1);
         mt.segEnd |= 1u << (seg0 + nseg - 1);
     }
     {
@@ -666,19 +679,17 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     const uint32_t       epa = tm.swz / 2;
     std::vector<float>   row(tm.kSteps * 16);
     double               kappa = 0.0;  // largest squared Mahalanobis norm of a centred mean
+    bool                 cRange = true;
     for (uint32_t t = 0; t < tm.nTiles; ++t) {
         uint8_t*  base  = img.data() + (size_t)t * tm.tileBytes;
-        float*    cOut  = reinterpret_cast<float*>(base + (size_t)tm.nAtoms * kTileN * tm.swz);
-        uint16_t* slOut = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(cOut) + kTileN * 4);
+        uint16_t* slOut = reinterpret_cast<uint16_t*>(base + (size_t)tm.nAtoms * kTileN * tm.swz);
         TileMeta* mOut  = reinterpret_cast<TileMeta*>(reinterpret_cast<uint8_t*>(slOut) + kTileN * 2);
         *mOut           = metas[t];
         for (uint32_t r = 0; r < (uint32_t)kTileN; ++r) {
             const Col& col = cols[(size_t)t * kTileN + r];
             slOut[r]       = col.slot;
-            if (col.g == 0xFFFFFFFFu) {
-                cOut[r] = INFINITY;
-                continue;
-            }
+            if (col.g == 0xFFFFFFFFu)
+                continue;  // filler / empty mixture: zero operand row
             const float* mu = mean + (size_t)col.g * D;
             const float* is = isr + (size_t)covIdx[col.g] * D;
             std::fill(row.begin(), row.end(), 0.f);
@@ -697,8 +708,25 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
                     kap += mc * mc * iv;
                 }
             }
-            cOut[r] = (float)(cc + kap);
-            kappa   = std::max(kappa, kap);
+            kappa = std::max(kappa, kap);
+            // constant c = |b|^2 + L + w2 as three fp16 pieces in the spare K columns (the A side holds 1/rowScale)
+            const float cf = (float)(cc + kap);
+            if (!(fabsf(cf) < 60000.f))
+                cRange = false;
+            {
+                uint16_t h0, h1, h2, dummy;
+                host_split(cf, h0, h1);
+                __half hh0, hh1;
+                memcpy(&hh0, &h0, 2);
+                memcpy(&hh1, &h1, 2);
+                const float rest = (cf - __half2float(hh0)) - __half2float(hh1);
+                host_split(rest, h2, dummy);
+                __half hh2;
+                memcpy(&hh2, &h2, 2);
+                row[kel]     = __half2float(hh0);
+                row[kel + 1] = __half2float(hh1);
+                row[kel + 2] = __half2float(hh2);
+            }
             for (uint32_t k = 0; k < tm.kSteps * 16; ++k) {
                 uint16_t hi, lo;
                 host_split(row[k], hi, lo);
@@ -715,6 +743,13 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     // than 8 sigma (rms per dimension) keep the 1e-4 relative bar only in the direct kernel.
     if (!force && kappa > 64.0 * D)
         return GMM_OK;
+    if (!cRange) {
+        if (force) {
+            h->setError("tensor kernel: a per-Gaussian constant exceeds the fp16 range");
+            return GMM_ERR_UNSUPPORTED;
+        }
+        return GMM_OK;
+    }
     int rc;
     if ((rc = h->upload((void**)&tm.bTiles, img.data(), img.size())))
         return rc;
