@@ -39,7 +39,8 @@ struct TensorModel {
     uint8_t*  bTiles    = nullptr; // [nTiles x tileBytes]
     float*    center    = nullptr; // [D] translation applied to features and means (pooled form)
     float*    scale     = nullptr; // [D] per-dimension factor of the frame preparation (pooled: isr)
-    uint32_t  maxMixPerHalf = 0;
+    uint32_t  partW     = 128;     // packed columns reduced by one epilogue warp (128: 8 warps, 64: 16 warps)
+    uint32_t  maxMixPerPart = 0;
     uint32_t  swz       = 128;     // swizzle atom width in bytes (128 or 64)
     uint32_t  aTileBytes = 0;
     uint32_t  buffersB  = 0;       // B tile buffers that fit in shared memory (1 or 2)

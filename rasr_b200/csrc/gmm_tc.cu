@@ -30,6 +30,7 @@
 #include <cuda_fp16.h>
 #include <float.h>
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -41,18 +42,20 @@ namespace {
 
 constexpr int kTileN       = 256;  // packed columns per B tile (UMMA N)
 constexpr int kTileM       = 128;  // frames per A tile (UMMA M, TMEM lanes)
-constexpr int kThreads     = 384;
-constexpr int kEpiWarp0    = 4;
+constexpr int kEpiWarp0    = 2;    // warp 0: bulk-copy producer + TMEM allocator, warp 1: MMA issuer
 constexpr int kMaxStagesA  = 4;
-constexpr int kMetaBytes   = kTileN * 2 + 32;  // slot[256] u16, TileMeta
+constexpr int kRing        = 4;    // tile-indexed barrier rings (>= kMaxStagesA, >= 2 accumulators + 2)
+constexpr int kMaxKSteps   = 16;   // 16-element k-steps per precision part (K <= 256)
+constexpr int kMetaBytes   = kTileN * 2 + 48;  // slot[256] u16, TileMeta
 constexpr uint32_t kSmemLimit = 232448;                     // 227 KB
 
 struct TileMeta {
     uint32_t segEnd;       // bit s: 8-column segment s closes a mixture
     uint32_t segEmpty;     // bit s (on a closing segment): the mixture has no live density at all
-    uint32_t mixBase0, mixBase1;  // first mixture of column half 0 / 1
+    uint32_t mixBase[4];   // first mixture of column part p (part = 128 or 64 columns, one epilogue warp each)
     uint32_t live[4];      // 4 bits per segment: live columns - 1 (pads repeat the first live column)
 };
+static_assert(sizeof(TileMeta) == 40, "TileMeta layout");
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -100,6 +103,11 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t dTmem, uint64_t aDesc, uint6
             "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
             : "memory");
 }
+__device__ __forceinline__ bool elect_one() {  // true in exactly one lane of the (converged) warp
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
     asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -142,7 +150,8 @@ struct KParams {
     uint32_t       atoms;                      // swizzle atoms per operand row
     uint32_t       aTileBytes, bTileBytes;     // bTileBytes includes c / slot / meta
     uint32_t       stagesA, buffersB;
-    uint32_t       stagePitch;                 // floats per staging row (maxMixPerHalf + 1)
+    uint32_t       stagePitch;                 // floats per staging row (maxMixPerPart + 1)
+    unsigned long long* dbg;                   // GMM_TC_DEBUG: per-CTA cycle counters of the MMA thread
 };
 
 struct EpiState {
@@ -154,7 +163,7 @@ struct EpiState {
 // u / rowScale with u = c - 2 a.b (the constant rides in spare K columns of the contraction), so the maximum
 // approximation is a bare min tree over TMEM values; a closing segment stages the mixture's score.
 template<int MODE, bool BEST>
-__device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, const uint16_t* __restrict__ slots,
+__device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase, const uint16_t* __restrict__ slots,
                                           uint32_t segEnd, uint32_t segEmpty, uint64_t liveBits, float rt, float rs,
                                           float* stg, uint32_t* stgB, EpiState& st) {
     constexpr float kLn2 = 0.69314718055994530942f;
@@ -167,15 +176,25 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, c
         for (int j = 0; j < 8; ++j)
             u[j] = __uint_as_float(v[s * 8 + j]);
         if (MODE == 0 && !BEST) {
-            float m8 = fminf(fminf(fminf(u[0], u[1]), fminf(u[2], u[3])), fminf(fminf(u[4], u[5]), fminf(u[6], u[7])));
-            st.run   = fminf(st.run, m8);
+            // branch-free: three-input min tree including the running minimum; a closing segment stores
+            // 0.5 * (min * rowScale + rowTerm) = fma(min, 0.5 rowScale, 0.5 rowTerm) (rowScale is a power of two)
+            const float m = fminf(fminf(fminf(fminf(u[0], u[1]), u[2]), fminf(fminf(u[3], u[4]), u[5])),
+                                  fminf(fminf(u[6], u[7]), st.run));
+            const bool  close = (segEnd >> seg) & 1u;
+            float       sc    = fminf(fmaf(m, 0.5f * rs, 0.5f * rt), 0.5f * (FLT_MAX + rt));
+            sc                = ((segEmpty >> seg) & 1u) ? 0.5f * (FLT_MAX + rt) : sc;
+            if (close)
+                stg[st.cnt] = sc;
+            st.cnt += close ? 1u : 0u;
+            st.run = close ? INFINITY : m;
+            continue;
         }
         else if (MODE == 0) {
 #pragma unroll
             for (int j = 0; j < 8; ++j)
                 if (u[j] < st.run) {  // pads repeat the first live column: never strictly smaller
                     st.run = u[j];
-                    st.idx = (uint32_t)(half * 128 + seg * 8 + j);
+                    st.idx = (uint32_t)(colBase + seg * 8 + j);
                 }
         }
         else {
@@ -194,7 +213,7 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, c
                 if (m8 < st.run) {
                     st.sum *= ex2((m8 - st.run) * hl2e);  // run == inf -> factor 0 (sum is 0 anyway)
                     st.run = m8;
-                    st.idx = (uint32_t)(half * 128 + seg * 8 + j8);
+                    st.idx = (uint32_t)(colBase + seg * 8 + j8);
                 }
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
@@ -220,44 +239,50 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int half, c
 }
 
 // MODE 0 = max, 1 = sum.  BEST: also write the index of the winning density.
-template<int SWZ, int MODE, bool BEST>
-__global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) {
+// NE = epilogue warps (8 or 16): warp e handles TMEM lane quarter (warp & 3) and column part e / 4 of
+// 1024 / NE columns (128 or 64).  16 warps give every scheduler four epilogue warps to hide the latencies of
+// the min tree, and drain an accumulator in half the time; they need mixtures of at most 64 packed columns.
+template<int SWZ, int MODE, bool BEST, int NE>
+__device__ __forceinline__ void tc_score_body(const KParams& p) {
     extern __shared__ uint8_t smemRaw[];
     // swizzled operand tiles need 1024-byte alignment of the shared-memory address itself
     uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int PW   = 1024 / NE;  // columns per epilogue warp
+    constexpr int SEGS = PW / 8;     // 8-column segments per epilogue warp
 
-    // carve shared memory: [B buffers][A stages][staging][barriers]
+    // carve shared memory: [B buffers][A stages][staging][barriers][MMA descriptor offsets]
     const uint32_t bBytes    = (p.bTileBytes + 1023u) & ~1023u;
     uint8_t*       sB        = smem;
     uint8_t*       sA        = sB + (size_t)p.buffersB * bBytes;
     float*         sStage    = reinterpret_cast<float*>(sA + (size_t)p.stagesA * p.aTileBytes);
     const uint32_t stageWarp = 32 * p.stagePitch;  // floats per warp
-    uint32_t*      sStageB   = reinterpret_cast<uint32_t*>(sStage + 8 * stageWarp);
-    uint64_t*      bars      = reinterpret_cast<uint64_t*>(sStageB + (BEST ? 8 * stageWarp : 0));
-    // barrier indices
-    uint64_t* fullA     = bars;                    // [kMaxStagesA]
-    uint64_t* emptyA    = bars + kMaxStagesA;      // [kMaxStagesA]
-    uint64_t* fullB     = bars + 2 * kMaxStagesA;  // [2]
-    uint64_t* emptyB    = fullB + 2;               // [2]
-    uint64_t* tmemFull  = emptyB + 2;              // [2]
-    uint64_t* tmemEmpty = tmemFull + 2;            // [2]
-    uint32_t* tmemSlot  = reinterpret_cast<uint32_t*>(tmemEmpty + 2);
+    uint32_t*      sStageB   = reinterpret_cast<uint32_t*>(sStage + NE * stageWarp);
+    uint64_t*      bars      = reinterpret_cast<uint64_t*>(
+            (reinterpret_cast<uintptr_t>(sStageB + (BEST ? NE * stageWarp : 0)) + 15) & ~(uintptr_t)15);
+    // Barriers.  Tiles are numbered t = 0, 1, ... per CTA across its items; rings of kRing follow t % kRing.
+    //   ready[t % 4]: tile t may be issued = its A operand has landed (producer arrive + bytes) AND the
+    //                 accumulator t & 1 was drained by every epilogue warp (after tile t - 2)
+    //   done[t % 4] : the MMAs of tile t have retired (one tcgen05.commit): the epilogue may read the
+    //                 accumulator, the producer may overwrite the A stage
+    uint64_t* ready    = bars;                // [kRing]
+    uint64_t* done     = bars + kRing;        // [kRing]
+    uint64_t* fullB    = bars + 2 * kRing;    // [2]
+    uint64_t* emptyB   = fullB + 2;           // [2]
+    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(emptyB + 2);
 
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < kMaxStagesA; ++i) {
-            mbar_init(smem_u32(&fullA[i]), 1);
-            mbar_init(smem_u32(&emptyA[i]), 1);
+    if (threadIdx.x == 32) {
+        for (int i = 0; i < kRing; ++i) {
+            mbar_init(smem_u32(&ready[i]), 1 + NE);
+            mbar_init(smem_u32(&done[i]), 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(smem_u32(&fullB[i]), 1);
-            mbar_init(smem_u32(&emptyB[i]), 1 + 8);  // MMA commit + 8 epilogue warps
-            mbar_init(smem_u32(&tmemFull[i]), 1);
-            mbar_init(smem_u32(&tmemEmpty[i]), 8);
+            mbar_init(smem_u32(&emptyB[i]), 1 + NE);  // MMA commit + the epilogue warps
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) {
+    if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmemSlot)));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
@@ -272,7 +297,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) 
     if (warp == 0) {
         // ===== producer: one lane issues the bulk copies =====
         if (lane == 0) {
-            uint32_t stage = 0, phaseA = 0, itemCount = 0;
+            uint32_t itemCount = 0, t = 0;
             for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
                 const uint32_t nt = item / p.split, chunk = item % p.split;
                 const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
@@ -283,139 +308,189 @@ __global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) 
                 mbar_expect_tx(smem_u32(&fullB[b]), p.bTileBytes);
                 bulk_g2s(smem_u32(sB + (size_t)b * bBytes), p.bTiles + (size_t)nt * p.bTileBytes, p.bTileBytes,
                          smem_u32(&fullB[b]));
-                for (uint32_t f = f0; f < f1; ++f) {
-                    mbar_wait(smem_u32(&emptyA[stage]), phaseA ^ 1);
-                    mbar_expect_tx(smem_u32(&fullA[stage]), p.aTileBytes);
-                    bulk_g2s(smem_u32(sA + (size_t)stage * p.aTileBytes), p.aTiles + (size_t)f * p.aTileBytes,
-                             p.aTileBytes, smem_u32(&fullA[stage]));
-                    if (++stage == p.stagesA) {
-                        stage = 0;
-                        phaseA ^= 1;
+                for (uint32_t f = f0; f < f1; ++f, ++t) {
+                    if (t >= p.stagesA) {  // the stage's previous tenant has been consumed by the tensor core
+                        const uint32_t u = t - p.stagesA;
+                        mbar_wait(smem_u32(&done[u % kRing]), (u / kRing) & 1);
                     }
+                    const uint32_t rb = smem_u32(&ready[t % kRing]);
+                    mbar_expect_tx(rb, p.aTileBytes);
+                    bulk_g2s(smem_u32(sA + (size_t)(t % p.stagesA) * p.aTileBytes), p.aTiles + (size_t)f * p.aTileBytes,
+                             p.aTileBytes, rb);
                 }
             }
         }
     }
     else if (warp == 1) {
-        // ===== MMA issuer: one lane issues tcgen05.mma for the whole CTA =====
-        if (lane == 0) {
-            // instruction descriptor: D=f32, A=B=f16, K-major both, N=256, M=128
-            constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
-            constexpr uint32_t kPerAtom = SWZ / 32;  // 16-element k-steps per swizzle atom
-            uint32_t stage = 0, phaseA = 0, itemCount = 0, tileCount = 0;
-            for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
-                const uint32_t chunk = item % p.split;
-                const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
-                if (f0 >= f1)
-                    continue;
-                const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
-                mbar_wait(smem_u32(&fullB[b]), useB & 1);
-                const uint32_t bAddr = smem_u32(sB + (size_t)b * bBytes);
-                for (uint32_t f = f0; f < f1; ++f, ++tileCount) {
-                    const uint32_t acc = tileCount & 1, useAcc = tileCount >> 1;
-                    mbar_wait(smem_u32(&tmemEmpty[acc]), (useAcc & 1) ^ 1);
-                    mbar_wait(smem_u32(&fullA[stage]), phaseA);
-                    tc_fence_after();
-                    const uint32_t aAddr = smem_u32(sA + (size_t)stage * p.aTileBytes);
-                    const uint32_t dTmem = tmemBase + acc * kTileN;
-                    uint32_t       first = 1;
-                    // hi.hi, lo.hi, hi.lo
-#pragma unroll 1
-                    for (uint32_t pair = 0; pair < 3; ++pair) {
-                        const uint32_t pa = (pair == 1) ? p.kSteps : 0, pb = (pair == 2) ? p.kSteps : 0;
-                        for (uint32_t ks = 0; ks < p.kSteps; ++ks) {
-                            const uint32_t ka = pa + ks, kb = pb + ks;
-                            const uint32_t ao = (ka / kPerAtom) * (kTileM * SWZ) + (ka % kPerAtom) * 32;
-                            const uint32_t bo = (kb / kPerAtom) * (kTileN * SWZ) + (kb % kPerAtom) * 32;
-                            tc_mma_f16(dTmem, umma_desc<SWZ>(aAddr + ao), umma_desc<SWZ>(bAddr + bo), idesc,
-                                       first ? 0u : 1u);
-                            first = 0;
-                        }
-                    }
-                    tc_commit(smem_u32(&emptyA[stage]));   // A stage free when these MMAs retire
-                    tc_commit(smem_u32(&tmemFull[acc]));   // accumulator ready for the epilogue
-                    if (f + 1 == f1)
-                        tc_commit(smem_u32(&emptyB[b]));   // B buffer no longer read by the tensor core
-                    if (++stage == p.stagesA) {
-                        stage = 0;
-                        phaseA ^= 1;
-                    }
-                }
-            }
-        }
-    }
-    else if (warp >= kEpiWarp0) {
-        // ===== epilogue: TMEM -> registers -> (+c, min / log-sum-exp per mixture) -> staged -> global =====
-        const int      e = warp - kEpiWarp0, q = warp & 3, half = e >> 2;
-        float*         stg  = sStage + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
-        uint32_t*      stgB = sStageB + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
-        uint32_t       itemCount = 0, tileCount = 0;
+        // ===== MMA issuer: the warp stays converged (every operand below is warp-uniform, so descriptors live in
+        // uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit for the whole CTA =====
+        // instruction descriptor: D=f32, A=B=f16, K-major both, N=256, M=128
+        constexpr uint32_t idesc    = (1u << 4) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+        constexpr uint32_t kPerAtom = SWZ / 32;  // 16-element k-steps per swizzle atom
+        // high word of the shared-memory descriptor: SBO = 8 rows * SWZ bytes (>> 4), version 1, swizzle mode
+        constexpr uint32_t descHi   = (uint32_t)((8 * SWZ) >> 4) | (1u << 14) | ((SWZ == 128 ? 2u : 4u) << 29);
+        const bool         leader   = elect_one();
+        const uint32_t     kS       = p.kSteps;
+        uint32_t  itemCount = 0, t = 0;
+        long long tStart = clock64(), wR = 0, wI = 0, t0 = 0;
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
-            const uint32_t nt = item / p.split, chunk = item % p.split;
+            const uint32_t chunk = item % p.split;
             const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
             if (f0 >= f1)
                 continue;
-            (void)nt;
+            const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+            mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            const uint32_t bLo = (smem_u32(sB + (size_t)b * bBytes) & 0x3FFFF) >> 4;
+            for (uint32_t f = f0; f < f1; ++f, ++t) {
+                if (p.dbg) t0 = clock64();
+                mbar_wait(smem_u32(&ready[t % kRing]), (t / kRing) & 1);
+                tc_fence_after();
+                if (p.dbg) { const long long t1 = clock64(); wR += t1 - t0; t0 = t1; }
+                const uint32_t aLo   = (smem_u32(sA + (size_t)(t % p.stagesA) * p.aTileBytes) & 0x3FFFF) >> 4;
+                const uint32_t dTmem = tmemBase + (t & 1) * kTileN;
+                if (leader) {
+                    // per k-step: hi.hi, lo.hi, hi.lo (hi part = k-step ks, lo part = k-step kS + ks of the image)
+                    for (uint32_t ks = 0; ks < kS; ++ks) {
+                        const uint32_t kl = kS + ks;
+                        const uint32_t ah = aLo + (ks / kPerAtom) * (kTileM * SWZ / 16) + (ks % kPerAtom) * 2;
+                        const uint32_t al = aLo + (kl / kPerAtom) * (kTileM * SWZ / 16) + (kl % kPerAtom) * 2;
+                        const uint32_t bh = bLo + (ks / kPerAtom) * (kTileN * SWZ / 16) + (ks % kPerAtom) * 2;
+                        const uint32_t bl = bLo + (kl / kPerAtom) * (kTileN * SWZ / 16) + (kl % kPerAtom) * 2;
+                        tc_mma_f16(dTmem, ((uint64_t)descHi << 32) | ah, ((uint64_t)descHi << 32) | bh, idesc, ks ? 1u : 0u);
+                        tc_mma_f16(dTmem, ((uint64_t)descHi << 32) | al, ((uint64_t)descHi << 32) | bh, idesc, 1u);
+                        tc_mma_f16(dTmem, ((uint64_t)descHi << 32) | ah, ((uint64_t)descHi << 32) | bl, idesc, 1u);
+                    }
+                    tc_commit(smem_u32(&done[t % kRing]));  // accumulator ready, A stage free
+                    if (f + 1 == f1)
+                        tc_commit(smem_u32(&emptyB[b]));    // B buffer no longer read by the tensor core
+                }
+                __syncwarp();
+                if (p.dbg) wI += clock64() - t0;
+            }
+        }
+        if (p.dbg && leader) {
+            unsigned long long* d = p.dbg + blockIdx.x * 8;
+            d[0] = clock64() - tStart, d[1] = wR, d[2] = wI, d[3] = 0, d[4] = t, d[5] = itemCount;
+        }
+    }
+    else {
+        // ===== epilogue: TMEM -> registers -> (min / log-sum-exp per mixture) -> staged -> global =====
+        const int      e = warp - kEpiWarp0, q = warp & 3, part = e >> 2;
+        float*         stg  = sStage + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
+        uint32_t*      stgB = sStageB + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
+        uint32_t       itemCount = 0, t = 0;
+        if (lane == 0) {  // both accumulators start out drained
+            mbar_arrive(smem_u32(&ready[0]));
+            mbar_arrive(smem_u32(&ready[1]));
+        }
+        for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
+            const uint32_t chunk = item % p.split;
+            const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+            if (f0 >= f1)
+                continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
             const uint8_t*  tile  = sB + (size_t)b * bBytes + (size_t)p.atoms * kTileN * SWZ;
             const uint16_t* slots = reinterpret_cast<const uint16_t*>(tile);
-            const TileMeta  meta  = *reinterpret_cast<const TileMeta*>(tile + kTileN * 2);
-            const uint32_t  segEnd  = (meta.segEnd >> (16 * half)) & 0xFFFFu;
-            const uint32_t  mixBase = half ? meta.mixBase1 : meta.mixBase0;
-            const uint32_t  segEmpty = (meta.segEmpty >> (16 * half)) & 0xFFFFu;
-            const uint64_t  liveBits = half ? ((uint64_t)meta.live[3] << 32 | meta.live[2])
-                                            : ((uint64_t)meta.live[1] << 32 | meta.live[0]);
-            const uint32_t  nMix    = __popc(segEnd);
-            for (uint32_t f = f0; f < f1; ++f, ++tileCount) {
-                const uint32_t acc = tileCount & 1, useAcc = tileCount >> 1;
+            const uint32_t* meta  = reinterpret_cast<const uint32_t*>(tile + kTileN * 2);  // TileMeta words
+            constexpr uint32_t segMask = (1u << SEGS) - 1u;
+            const uint32_t  segEnd   = (meta[0] >> (SEGS * part)) & segMask;
+            const uint32_t  segEmpty = (meta[1] >> (SEGS * part)) & segMask;
+            const uint32_t  mixBase  = meta[2 + part];
+            const uint64_t  liveBits = (SEGS == 16) ? ((uint64_t)meta[6 + 2 * part + 1] << 32 | meta[6 + 2 * part])
+                                                    : (uint64_t)meta[6 + part];
+            const uint32_t  nMix     = __popc(segEnd);
+            // staged block [32 rows x nMix] -> global: lane starts at element `lane`, every pass advances 32 elements
+            const uint32_t  adv_r = 32 / max(nMix, 1u), adv_j = 32 - adv_r * nMix;
+            const uint32_t  lr0 = lane / max(nMix, 1u), lj0 = lane - lr0 * nMix;
+            const size_t    gStep = (size_t)adv_r * p.ld + adv_j, gStepW = gStep + p.ld - nMix;
+            const uint32_t  sStep = adv_r * p.stagePitch + adv_j, sStepW = sStep + p.stagePitch - nMix;
+            for (uint32_t f = f0; f < f1; ++f, ++t) {
+                const uint32_t acc = t & 1;
                 const uint32_t row = f * kTileM + q * 32 + lane;
                 const float2   ri  = p.rowInfo[row];
                 const float    rt = ri.x, rs = ri.y;
-                mbar_wait(smem_u32(&tmemFull[acc]), useAcc & 1);
+                mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
                 tc_fence_after();
-                const uint32_t taddr = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + half * 128;
+                const uint32_t taddr    = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + part * PW;
+                const uint32_t drained  = smem_u32(&ready[(t + 2) % kRing]);  // tile t + 2 reuses this accumulator
                 EpiState st;
                 st.run = INFINITY, st.sum = 0.f, st.idx = 0xFFFFFFFFu, st.cnt = 0;
-                // TMEM -> registers in four 32-column chunks, the next load in flight while one is reduced
                 uint32_t va[32], vb[32];
-                tmem_ld32(taddr, va);
-                tmem_ld_wait();
-                tmem_ld32(taddr + 32, vb);
-                epi_chunk<MODE, BEST>(va, 0, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
-                tmem_ld_wait();
-                tmem_ld32(taddr + 64, va);
-                epi_chunk<MODE, BEST>(vb, 1, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
-                tmem_ld_wait();
-                tmem_ld32(taddr + 96, vb);
-                epi_chunk<MODE, BEST>(va, 2, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
-                tmem_ld_wait();
-                // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
-                tc_fence_before();
+                if (NE == 16) {
+                    // 64 columns: both loads in flight, then the accumulator goes straight back to the MMA warp
+                    tmem_ld32(taddr, va);
+                    tmem_ld32(taddr + 32, vb);
+                    tmem_ld_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(drained);
+                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                }
+                else {
+                    // 128 columns in four 32-column chunks, the next load in flight while one is reduced
+                    tmem_ld32(taddr, va);
+                    tmem_ld_wait();
+                    tmem_ld32(taddr + 32, vb);
+                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    tmem_ld_wait();
+                    tmem_ld32(taddr + 64, va);
+                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    tmem_ld_wait();
+                    tmem_ld32(taddr + 96, vb);
+                    epi_chunk<MODE, BEST>(va, 2, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    tmem_ld_wait();
+                    // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(drained);
+                    epi_chunk<MODE, BEST>(vb, 3, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                }
                 __syncwarp();
-                if (lane == 0)
-                    mbar_arrive(smem_u32(&tmemEmpty[acc]));
-                epi_chunk<MODE, BEST>(vb, 3, half, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
-                __syncwarp();
-                // coalesced store of the staged [32 rows x nMix] block
-                const uint32_t total = 32 * nMix;
-                const float*   wst   = sStage + (size_t)e * stageWarp;
-                const uint32_t* wsb  = sStageB + (size_t)e * stageWarp;
-                const uint32_t rbase = f * kTileM + q * 32;
-                const bool     pow2  = (nMix & (nMix - 1)) == 0;
-                const uint32_t sh    = 31 - __clz(nMix | 1);
-                for (uint32_t i = lane; i < total; i += 32) {
-                    const uint32_t r = pow2 ? (i >> sh) : (i / nMix), j = i - r * nMix;
-                    if (rbase + r < p.T) {
-                        const size_t o = (size_t)(rbase + r) * p.ld + mixBase + j;
-                        p.scores[o]    = wst[r * p.stagePitch + j];
+                // coalesced store of the staged [32 rows x nMix] block: nMix passes of 32 consecutive elements;
+                // pointers advance by per-item constants (a pass that wraps past a row end takes the `w` step)
+                const uint32_t  rbase = f * kTileM + q * 32;
+                const uint32_t  rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
+                const float*    ss    = sStage + (size_t)e * stageWarp + lr0 * p.stagePitch + lj0;
+                const uint32_t* sb    = sStageB + (size_t)e * stageWarp + lr0 * p.stagePitch + lj0;
+                const size_t    g0    = (size_t)(rbase + lr0) * p.ld + mixBase + lj0;
+                float*          gs    = p.scores + g0;
+                uint32_t*       gb    = BEST ? p.best + g0 : nullptr;
+                if (adv_j == 0) {  // nMix divides 32: a lane keeps its column
+#pragma unroll 4
+                    for (uint32_t i = 0, r = lr0; i < nMix; ++i, r += adv_r) {
+                        if (r < rows) {
+                            *gs = *ss;
+                            if (BEST)
+                                *gb = *sb;
+                        }
+                        gs += gStep, ss += sStep;
                         if (BEST)
-                            p.best[o] = wsb[r * p.stagePitch + j];
+                            gb += gStep, sb += sStep;
+                    }
+                }
+                else {
+                    uint32_t r = lr0, j = lj0;
+                    for (uint32_t i = 0; i < nMix; ++i) {
+                        if (r < rows) {
+                            *gs = *ss;
+                            if (BEST)
+                                *gb = *sb;
+                        }
+                        const bool w = j + adv_j >= nMix;
+                        j            = w ? j + adv_j - nMix : j + adv_j;
+                        r += adv_r + (w ? 1u : 0u);
+                        gs += w ? gStepW : gStep, ss += w ? sStepW : sStep;
+                        if (BEST)
+                            gb += w ? gStepW : gStep, sb += w ? sStepW : sStep;
                     }
                 }
                 __syncwarp();
             }
-            // this warp no longer reads c / slot / meta of the B buffer
+            // this warp no longer reads slot / meta of the B buffer
             if (lane == 0)
                 mbar_arrive(smem_u32(&emptyB[b]));
         }
@@ -423,10 +498,20 @@ __global__ void __launch_bounds__(kThreads, 1) tc_score_kernel(const KParams p) 
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 2) {
+    if (warp == 0) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmemBase));
     }
+}
+
+// 8 epilogue warps: 320 threads, up to 204 registers; 16 epilogue warps: 576 threads (20 warp slots at allocation granularity 4), 96 registers
+template<int SWZ, int MODE, bool BEST>
+__global__ void __launch_bounds__(32 * (kEpiWarp0 + 8), 1) tc_score_kernel8(const KParams p) {
+    tc_score_body<SWZ, MODE, BEST, 8>(p);
+}
+template<int SWZ, int MODE, bool BEST>
+__global__ void __launch_bounds__(32 * (kEpiWarp0 + 16), 1) tc_score_kernel16(const KParams p) {
+    tc_score_body<SWZ, MODE, BEST, 16>(p);
 }
 
 // ---- swizzled tile image addressing (host + device) ---------------------------------------------------
@@ -532,13 +617,13 @@ void host_split(float v, uint16_t& hi, uint16_t& lo) {
     memcpy(&lo, &l, 2);
 }
 
-template<int SWZ, int MODE, bool BEST>
+template<int SWZ, int MODE, bool BEST, int NE>
 cudaError_t launch_tc(const KParams& p, int grid, size_t smemBytes, cudaStream_t stream) {
-    cudaError_t e = cudaFuncSetAttribute(tc_score_kernel<SWZ, MODE, BEST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smemBytes);
+    void (*kernel)(const KParams) = NE == 16 ? tc_score_kernel16<SWZ, MODE, BEST> : tc_score_kernel8<SWZ, MODE, BEST>;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     if (e != cudaSuccess)
         return e;
-    tc_score_kernel<SWZ, MODE, BEST><<<grid, kThreads, smemBytes, stream>>>(p);
+    kernel<<<grid, 32 * (kEpiWarp0 + NE), smemBytes, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -546,9 +631,9 @@ cudaError_t launch_tc(const KParams& p, int grid, size_t smemBytes, cudaStream_t
 
 // ---- host side: packing --------------------------------------------------------------------------------
 static uint32_t smemNeed(uint32_t bTileBytes, uint32_t aTileBytes, uint32_t buffersB, uint32_t stagesA,
-                         uint32_t pitch, bool best) {
+                         uint32_t pitch, bool best, uint32_t epiWarps) {
     const uint32_t bBytes = (bTileBytes + 1023u) & ~1023u;
-    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 8 * 32 * pitch * 4 * (best ? 2 : 1) + 512;
+    return 1024 + buffersB * bBytes + stagesA * aTileBytes + epiWarps * 32 * pitch * 4 * (best ? 2 : 1) + 512;
 }
 
 int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
@@ -563,6 +648,8 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     tm.pooled       = (C == 1);
     const uint32_t kel = tm.pooled ? D : 2 * D;
     tm.kSteps          = (kel + 3 + 15) / 16;  // 3 spare K columns carry the per-Gaussian constant
+    if (tm.kSteps > (uint32_t)kMaxKSteps)
+        return GMM_OK;  // dimension beyond the tensor kernel: tm.valid stays false
     tm.nAtoms          = (tm.kSteps * 64 + tm.swz - 1) / tm.swz;
     tm.aTileBytes      = tm.nAtoms * kTileM * tm.swz;
     tm.tileBytes       = tm.nAtoms * kTileN * tm.swz + kMetaBytes;
@@ -574,35 +661,50 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     };
     std::vector<Col>      cols;
     std::vector<TileMeta> metas;
-    std::vector<uint32_t> mixPerHalf;
-    auto halfOf = [&]() { return (uint32_t)(cols.size() / 128); };
-    auto ensureHalf = [&](uint32_t hf) {
-        while (metas.size() * 2 <= hf) {
-            TileMeta z = {0, 0, 0, 0, {0, 0, 0, 0}};
+    std::vector<uint32_t> mixPerPart;
+    auto isLive = [&](uint32_t g) { return isfinite(w2[g]) && isfinite(logNorm[covIdx[g]]); };
+    // column part = the columns one epilogue warp reduces: 64 (16 epilogue warps) when every mixture fits, else 128
+    uint32_t maxLive = 0;
+    for (uint32_t m = 0; m < M; ++m) {
+        uint32_t n = 0;
+        for (uint32_t g = offsets[m]; g < offsets[m + 1]; ++g)
+            n += isLive(g);
+        maxLive = std::max(maxLive, n);
+    }
+    const char* envW = getenv("GMM_TC_EPI_WARPS");
+    // 16 warps pay off where the epilogue is latency-bound (log-sum-exp); for the min tree their extra issue
+    // slots starve the MMA-issuing warp that shares a scheduler with a quarter of them (profiles/ubench_mma.cu)
+    const bool wide  = envW ? atoi(envW) == 16 : h->mode == GMM_MODE_SUM;
+    tm.partW         = (maxLive <= 64 && wide) ? 64 : 128;
+    const uint32_t partW = tm.partW, partsPerTile = kTileN / partW;
+    auto partOf = [&]() { return (uint32_t)(cols.size() / partW); };
+    auto ensurePart = [&](uint32_t pt) {
+        while (metas.size() * partsPerTile <= pt) {
+            TileMeta z = {0, 0, {0, 0, 0, 0}, {0, 0, 0, 0}};
             metas.push_back(z);
         }
-        while (mixPerHalf.size() <= hf)
-            mixPerHalf.push_back(0);
+        while (mixPerPart.size() <= pt)
+            mixPerPart.push_back(0);
     };
     for (uint32_t m = 0; m < M; ++m) {
         std::vector<uint32_t> live;
         for (uint32_t g = offsets[m]; g < offsets[m + 1]; ++g)
-            if (isfinite(w2[g]) && isfinite(logNorm[covIdx[g]]))
+            if (isLive(g))
                 live.push_back(g);
         uint32_t padded = std::max<uint32_t>(8, (uint32_t)((live.size() + 7) / 8 * 8));
         if (padded > 128 || offsets[m + 1] - offsets[m] > 0xFFFF)
             return GMM_OK;  // does not fit the tensor kernel: tm.valid stays false
-        const uint32_t inHalf = (uint32_t)(cols.size() % 128);
-        if (inHalf + padded > 128) {
+        const uint32_t inPart = (uint32_t)(cols.size() % partW);
+        if (inPart + padded > partW) {
             const Col pad = {0xFFFFFFFFu, 0xFFFF};
-            cols.insert(cols.end(), 128 - inHalf, pad);
+            cols.insert(cols.end(), partW - inPart, pad);
         }
-        const uint32_t hf = halfOf();
-        ensureHalf(hf);
-        TileMeta& mt = metas[hf / 2];
-        if (mixPerHalf[hf] == 0)
-            (hf & 1 ? mt.mixBase1 : mt.mixBase0) = m;
-        mixPerHalf[hf]++;
+        const uint32_t pt = partOf();
+        ensurePart(pt);
+        TileMeta& mt = metas[pt / partsPerTile];
+        if (mixPerPart[pt] == 0)
+            mt.mixBase[pt % partsPerTile] = m;
+        mixPerPart[pt]++;
         const uint32_t seg0 = (uint32_t)((cols.size() % 256) / 8);
         for (uint32_t i = 0; i < padded; ++i) {
             Col c = {0xFFFFFFFFu, 0xFFFF};
@@ -631,17 +733,17 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
             cols.push_back(pad);
     }
     tm.nTiles = (uint32_t)(cols.size() / kTileN);
-    ensureHalf(tm.nTiles * 2 - 1);
-    tm.maxMixPerHalf = 1;
-    for (uint32_t v : mixPerHalf)
-        tm.maxMixPerHalf = std::max(tm.maxMixPerHalf, v);
+    ensurePart(tm.nTiles * partsPerTile - 1);
+    tm.maxMixPerPart = 1;
+    for (uint32_t v : mixPerPart)
+        tm.maxMixPerPart = std::max(tm.maxMixPerPart, v);
 
     // ---- shared-memory configuration (sized for the arg-min variant) ----
-    const uint32_t pitch = tm.maxMixPerHalf + 1;
+    const uint32_t pitch = tm.maxMixPerPart + 1, epiWarps = 4 * partsPerTile;
     tm.buffersB = 0;
     for (uint32_t nb = 2; nb >= 1 && !tm.buffersB; --nb)
         for (uint32_t sa = kMaxStagesA; sa >= 2; --sa)
-            if (smemNeed(tm.tileBytes, tm.aTileBytes, nb, sa, pitch, true) <= kSmemLimit) {
+            if (smemNeed(tm.tileBytes, tm.aTileBytes, nb, sa, pitch, true, epiWarps) <= kSmemLimit) {
                 tm.buffersB = nb;
                 tm.stagesA  = sa;
                 break;
@@ -799,14 +901,23 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
     p.aTileBytes = tm.aTileBytes;
     p.bTileBytes = tm.tileBytes;
     p.buffersB   = tm.buffersB;
-    p.stagePitch = tm.maxMixPerHalf + 1;
+    p.stagePitch = tm.maxMixPerPart + 1;
+    p.dbg        = nullptr;
+    const bool debug = getenv("GMM_TC_DEBUG") != nullptr;
+    if (debug) {
+        void* d = nullptr;
+        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 64, &d)))
+            return rc;
+        p.dbg = (unsigned long long*)d;
+    }
+    const uint32_t epiWarps = 4 * (kTileN / tm.partW);
     const bool best = d_best != nullptr;
     // A ring depth: whatever shared memory allows for this variant
     p.stagesA = tm.stagesA;
     while (p.stagesA < (uint32_t)kMaxStagesA &&
-           smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA + 1, p.stagePitch, best) <= kSmemLimit)
+           smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA + 1, p.stagePitch, best, epiWarps) <= kSmemLimit)
         p.stagesA++;
-    const size_t smemBytes = smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best);
+    const size_t smemBytes = smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best, epiWarps);
     // split the frame range so that the items fill the SMs evenly: cost in A-tile MMA times
     const double bCost = tm.buffersB == 2 ? 0.5 : 2.0;
     uint32_t     bestS = 1;
@@ -827,17 +938,31 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
     const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
     cudaError_t e;
     const int   mode = h->mode == GMM_MODE_SUM ? 1 : 0;
-#define GMM_TC_LAUNCH(SWZ)                                                                                   \
-    (mode == 0 ? (best ? launch_tc<SWZ, 0, true>(p, grid, smemBytes, h->stream)                               \
-                       : launch_tc<SWZ, 0, false>(p, grid, smemBytes, h->stream))                             \
-               : (best ? launch_tc<SWZ, 1, true>(p, grid, smemBytes, h->stream)                               \
-                       : launch_tc<SWZ, 1, false>(p, grid, smemBytes, h->stream)))
+#define GMM_TC_LAUNCH(SWZ, NE)                                                                               \
+    (mode == 0 ? (best ? launch_tc<SWZ, 0, true, NE>(p, grid, smemBytes, h->stream)                           \
+                       : launch_tc<SWZ, 0, false, NE>(p, grid, smemBytes, h->stream))                         \
+               : (best ? launch_tc<SWZ, 1, true, NE>(p, grid, smemBytes, h->stream)                           \
+                       : launch_tc<SWZ, 1, false, NE>(p, grid, smemBytes, h->stream)))
     if (tm.swz == 128)
-        e = GMM_TC_LAUNCH(128);
+        e = epiWarps == 16 ? GMM_TC_LAUNCH(128, 16) : GMM_TC_LAUNCH(128, 8);
     else
-        e = GMM_TC_LAUNCH(64);
+        e = epiWarps == 16 ? GMM_TC_LAUNCH(64, 16) : GMM_TC_LAUNCH(64, 8);
 #undef GMM_TC_LAUNCH
     h->launches++;
     GMM_CUDA_TRY(h, e);
+    if (debug) {  // development aid: where the MMA-issuing thread spends its cycles
+        std::vector<unsigned long long> d((size_t)h->smCount * 8);
+        GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+        GMM_CUDA_TRY(h, cudaMemcpy(d.data(), p.dbg, d.size() * 8, cudaMemcpyDeviceToHost));
+        double tot = 0, wR = 0, wI = 0, wC = 0, tiles = 0;
+        for (int c = 0; c < grid; ++c)
+            tot += d[c * 8], wR += d[c * 8 + 1], wI += d[c * 8 + 2], wC += d[c * 8 + 3], tiles += d[c * 8 + 4];
+        tiles = std::max(1.0, tiles);
+        fprintf(stderr,
+                "[gmm_tc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u | MMA thread, cycles per tile: "
+                "total %.0f = wait-ready %.0f + issue+commit %.0f + other (%.0f)\n",
+                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, tot / tiles, wR / tiles, wI / tiles,
+                wC / tiles);
+    }
     return GMM_OK;
 }
