@@ -81,6 +81,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             "r"(parity)
             : "memory");
 }
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {  // one probe, no spinning
+    uint32_t ok;
+    asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                  "l"(src), "r"(bytes), "r"(bar)
@@ -123,6 +132,22 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
 __device__ __forceinline__ void tmem_ld_wait() {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
 __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -156,7 +181,8 @@ struct KParams {
 
 struct EpiState {
     float    run, sum;
-    uint32_t idx, cnt;
+    uint32_t idx;
+    uint32_t sp;  // shared-memory address of this row's next staged score (the index plane lies offB behind)
 };
 
 // One 32-column chunk (four 8-column segments) of a row's accumulator.  The accumulator already holds
@@ -165,7 +191,7 @@ struct EpiState {
 template<int MODE, bool BEST>
 __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase, const uint16_t* __restrict__ slots,
                                           uint32_t segEnd, uint32_t segEmpty, uint64_t liveBits, float rt, float rs,
-                                          float* stg, uint32_t* stgB, EpiState& st) {
+                                          uint32_t offB, EpiState& st) {
     constexpr float kLn2 = 0.69314718055994530942f;
     const float     hl2e = 0.72134752044448170368f * rs;  // 0.5 * log2(e) * rowScale
 #pragma unroll
@@ -184,8 +210,8 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
             float       sc    = fminf(fmaf(m, 0.5f * rs, 0.5f * rt), 0.5f * (FLT_MAX + rt));
             sc                = ((segEmpty >> seg) & 1u) ? 0.5f * (FLT_MAX + rt) : sc;
             if (close)
-                stg[st.cnt] = sc;
-            st.cnt += close ? 1u : 0u;
+                sts_f32(st.sp, sc);
+            st.sp += close ? 4u : 0u;
             st.run = close ? INFINITY : m;
             continue;
         }
@@ -227,10 +253,10 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
             float       sc    = 0.5f * (best + rt);
             if (MODE == 1)
                 sc = empty ? INFINITY : sc - kLn2 * __log2f(st.sum);
-            stg[st.cnt] = sc;
+            sts_f32(st.sp, sc);
             if (BEST)
-                stgB[st.cnt] = (empty || st.idx == 0xFFFFFFFFu) ? 0xFFFFFFFFu : (uint32_t)slots[st.idx];
-            ++st.cnt;
+                sts_u32(st.sp + offB, (empty || st.idx == 0xFFFFFFFFu) ? 0xFFFFFFFFu : (uint32_t)slots[st.idx]);
+            st.sp += 4;
             st.run = INFINITY;
             st.sum = 0.f;
             st.idx = 0xFFFFFFFFu;
@@ -297,7 +323,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     if (warp == 0) {
         // ===== producer: one lane issues the bulk copies =====
         if (lane == 0) {
-            uint32_t itemCount = 0, t = 0;
+            uint32_t itemCount = 0, t = 0, stage = 0;
             for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
                 const uint32_t nt = item / p.split, chunk = item % p.split;
                 const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
@@ -315,8 +341,10 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     }
                     const uint32_t rb = smem_u32(&ready[t % kRing]);
                     mbar_expect_tx(rb, p.aTileBytes);
-                    bulk_g2s(smem_u32(sA + (size_t)(t % p.stagesA) * p.aTileBytes), p.aTiles + (size_t)f * p.aTileBytes,
+                    bulk_g2s(smem_u32(sA + (size_t)stage * p.aTileBytes), p.aTiles + (size_t)f * p.aTileBytes,
                              p.aTileBytes, rb);
+                    if (++stage == p.stagesA)
+                        stage = 0;
                 }
             }
         }
@@ -331,7 +359,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
         constexpr uint32_t descHi   = (uint32_t)((8 * SWZ) >> 4) | (1u << 14) | ((SWZ == 128 ? 2u : 4u) << 29);
         const bool         leader   = elect_one();
         const uint32_t     kS       = p.kSteps;
-        uint32_t  itemCount = 0, t = 0;
+        uint32_t  itemCount = 0, t = 0, stage = 0;
+        bool      have = false;  // ready[t % kRing] was already seen complete (probed while tile t - 1 was being issued)
         long long tStart = clock64(), wR = 0, wI = 0, t0 = 0;
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
             const uint32_t chunk = item % p.split;
@@ -343,10 +372,11 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             const uint32_t bLo = (smem_u32(sB + (size_t)b * bBytes) & 0x3FFFF) >> 4;
             for (uint32_t f = f0; f < f1; ++f, ++t) {
                 if (p.dbg) t0 = clock64();
-                mbar_wait(smem_u32(&ready[t % kRing]), (t / kRing) & 1);
+                if (!have)
+                    mbar_wait(smem_u32(&ready[t % kRing]), (t / kRing) & 1);
                 tc_fence_after();
                 if (p.dbg) { const long long t1 = clock64(); wR += t1 - t0; t0 = t1; }
-                const uint32_t aLo   = (smem_u32(sA + (size_t)(t % p.stagesA) * p.aTileBytes) & 0x3FFFF) >> 4;
+                const uint32_t aLo   = (smem_u32(sA + (size_t)stage * p.aTileBytes) & 0x3FFFF) >> 4;
                 const uint32_t dTmem = tmemBase + (t & 1) * kTileN;
                 if (leader) {
                     // per k-step: hi.hi, lo.hi, hi.lo (hi part = k-step ks, lo part = k-step kS + ks of the image)
@@ -364,7 +394,11 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     if (f + 1 == f1)
                         tc_commit(smem_u32(&emptyB[b]));    // B buffer no longer read by the tensor core
                 }
+                // probe the next tile's barrier while this tile's MMAs are still queued in the tensor core
+                have = mbar_test(smem_u32(&ready[(t + 1) % kRing]), ((t + 1) / kRing) & 1);
                 __syncwarp();
+                if (++stage == p.stagesA)
+                    stage = 0;
                 if (p.dbg) wI += clock64() - t0;
             }
         }
@@ -376,8 +410,10 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     else {
         // ===== epilogue: TMEM -> registers -> (min / log-sum-exp per mixture) -> staged -> global =====
         const int      e = warp - kEpiWarp0, q = warp & 3, part = e >> 2;
-        float*         stg  = sStage + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
-        uint32_t*      stgB = sStageB + (size_t)e * stageWarp + (size_t)lane * p.stagePitch;
+        const uint32_t stWarp = smem_u32(sStage) + (uint32_t)e * stageWarp * 4;  // this warp's staging block
+        const uint32_t stRow  = stWarp + (uint32_t)lane * p.stagePitch * 4;      // this lane's (frame's) row in it
+        const uint32_t offB   = NE * stageWarp * 4;                              // index plane behind the scores
+        const ptrdiff_t bestDelta = BEST ? reinterpret_cast<const char*>(p.best) - reinterpret_cast<const char*>(p.scores) : 0;
         uint32_t       itemCount = 0, t = 0;
         if (lane == 0) {  // both accumulators start out drained
             mbar_arrive(smem_u32(&ready[0]));
@@ -403,19 +439,23 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             // staged block [32 rows x nMix] -> global: lane starts at element `lane`, every pass advances 32 elements
             const uint32_t  adv_r = 32 / max(nMix, 1u), adv_j = 32 - adv_r * nMix;
             const uint32_t  lr0 = lane / max(nMix, 1u), lj0 = lane - lr0 * nMix;
-            const size_t    gStep = (size_t)adv_r * p.ld + adv_j, gStepW = gStep + p.ld - nMix;
-            const uint32_t  sStep = adv_r * p.stagePitch + adv_j, sStepW = sStep + p.stagePitch - nMix;
+            const size_t    gStep = ((size_t)adv_r * p.ld + adv_j) * 4, gStepW = gStep + (p.ld - nMix) * 4;  // bytes
+            const uint32_t  sStep = (adv_r * p.stagePitch + adv_j) * 4, sStepW = sStep + (p.stagePitch - nMix) * 4;
+            const uint32_t  ssLane = stWarp + (lr0 * p.stagePitch + lj0) * 4;
+            char*           gTile  = reinterpret_cast<char*>(p.scores + (size_t)(f0 * kTileM + q * 32 + lr0) * p.ld + mixBase + lj0);
+            const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
+            const float2*   rip = p.rowInfo + (size_t)f0 * kTileM + q * 32 + lane;
             for (uint32_t f = f0; f < f1; ++f, ++t) {
                 const uint32_t acc = t & 1;
-                const uint32_t row = f * kTileM + q * 32 + lane;
-                const float2   ri  = p.rowInfo[row];
+                const float2   ri  = *rip;
                 const float    rt = ri.x, rs = ri.y;
+                rip += kTileM;
                 mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
                 tc_fence_after();
                 const uint32_t taddr    = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + part * PW;
                 const uint32_t drained  = smem_u32(&ready[(t + 2) % kRing]);  // tile t + 2 reuses this accumulator
                 EpiState st;
-                st.run = INFINITY, st.sum = 0.f, st.idx = 0xFFFFFFFFu, st.cnt = 0;
+                st.run = INFINITY, st.sum = 0.f, st.idx = 0xFFFFFFFFu, st.sp = stRow;
                 uint32_t va[32], vb[32];
                 if (NE == 16) {
                     // 64 columns: both loads in flight, then the accumulator goes straight back to the MMA warp
@@ -426,66 +466,60 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     __syncwarp();
                     if (lane == 0)
                         mbar_arrive(drained);
-                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
-                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
                 }
                 else {
                     // 128 columns in four 32-column chunks, the next load in flight while one is reduced
                     tmem_ld32(taddr, va);
                     tmem_ld_wait();
                     tmem_ld32(taddr + 32, vb);
-                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
                     tmem_ld_wait();
                     tmem_ld32(taddr + 64, va);
-                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
                     tmem_ld_wait();
                     tmem_ld32(taddr + 96, vb);
-                    epi_chunk<MODE, BEST>(va, 2, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    epi_chunk<MODE, BEST>(va, 2, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
                     tmem_ld_wait();
                     // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0)
                         mbar_arrive(drained);
-                    epi_chunk<MODE, BEST>(vb, 3, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, stg, stgB, st);
+                    epi_chunk<MODE, BEST>(vb, 3, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
                 }
                 __syncwarp();
                 // coalesced store of the staged [32 rows x nMix] block: nMix passes of 32 consecutive elements;
                 // pointers advance by per-item constants (a pass that wraps past a row end takes the `w` step)
-                const uint32_t  rbase = f * kTileM + q * 32;
-                const uint32_t  rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
-                const float*    ss    = sStage + (size_t)e * stageWarp + lr0 * p.stagePitch + lj0;
-                const uint32_t* sb    = sStageB + (size_t)e * stageWarp + lr0 * p.stagePitch + lj0;
-                const size_t    g0    = (size_t)(rbase + lr0) * p.ld + mixBase + lj0;
-                float*          gs    = p.scores + g0;
-                uint32_t*       gb    = BEST ? p.best + g0 : nullptr;
+                const uint32_t rbase = f * kTileM + q * 32;
+                const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
+                char*          gs    = gTile;
+                uint32_t       ss    = ssLane;
+                gTile += gTileStep;
                 if (adv_j == 0) {  // nMix divides 32: a lane keeps its column
 #pragma unroll 4
                     for (uint32_t i = 0, r = lr0; i < nMix; ++i, r += adv_r) {
                         if (r < rows) {
-                            *gs = *ss;
+                            *reinterpret_cast<float*>(gs) = lds_f32(ss);
                             if (BEST)
-                                *gb = *sb;
+                                *reinterpret_cast<uint32_t*>(gs + bestDelta) = lds_u32(ss + offB);
                         }
                         gs += gStep, ss += sStep;
-                        if (BEST)
-                            gb += gStep, sb += sStep;
                     }
                 }
                 else {
                     uint32_t r = lr0, j = lj0;
                     for (uint32_t i = 0; i < nMix; ++i) {
                         if (r < rows) {
-                            *gs = *ss;
+                            *reinterpret_cast<float*>(gs) = lds_f32(ss);
                             if (BEST)
-                                *gb = *sb;
+                                *reinterpret_cast<uint32_t*>(gs + bestDelta) = lds_u32(ss + offB);
                         }
                         const bool w = j + adv_j >= nMix;
                         j            = w ? j + adv_j - nMix : j + adv_j;
                         r += adv_r + (w ? 1u : 0u);
                         gs += w ? gStepW : gStep, ss += w ? sStepW : sStep;
-                        if (BEST)
-                            gb += w ? gStepW : gStep, sb += w ? sStepW : sStep;
                     }
                 }
                 __syncwarp();
