@@ -35,6 +35,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <type_traits>
 
 #include "gmm_internal.cuh"
 
@@ -54,8 +55,10 @@ struct TileMeta {
     uint32_t segEmpty;     // bit s (on a closing segment): the mixture has no live density at all
     uint32_t mixBase[4];   // first mixture of column part p (part = 128 or 64 columns, one epilogue warp each)
     uint32_t live[4];      // 4 bits per segment: live columns - 1 (pads repeat the first live column)
+    uint32_t uni;          // byte p: segments per mixture if every mixture of part p has that many and none is
+                           // empty (the part is full), else 0
 };
-static_assert(sizeof(TileMeta) == 40, "TileMeta layout");
+static_assert(sizeof(TileMeta) == 44, "TileMeta layout");
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -188,7 +191,9 @@ struct EpiState {
 // One 32-column chunk (four 8-column segments) of a row's accumulator.  The accumulator already holds
 // u / rowScale with u = c - 2 a.b (the constant rides in spare K columns of the contraction), so the maximum
 // approximation is a bare min tree over TMEM values; a closing segment stages the mixture's score.
-template<int MODE, bool BEST>
+// SP > 0: every mixture of this column part spans exactly SP segments and none is empty (a property of the packed
+// tile, TileMeta::uni), so the closing positions are compile-time constants; SP = 0: driven by the segEnd bits.
+template<int MODE, bool BEST, int SP>
 __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase, const uint16_t* __restrict__ slots,
                                           uint32_t segEnd, uint32_t segEmpty, uint64_t liveBits, float rt, float rs,
                                           uint32_t offB, EpiState& st) {
@@ -202,10 +207,20 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
         for (int j = 0; j < 8; ++j)
             u[j] = __uint_as_float(v[s * 8 + j]);
         if (MODE == 0 && !BEST) {
-            // branch-free: three-input min tree including the running minimum; a closing segment stores
-            // 0.5 * (min * rowScale + rowTerm) = fma(min, 0.5 rowScale, 0.5 rowTerm) (rowScale is a power of two)
-            const float m = fminf(fminf(fminf(fminf(u[0], u[1]), u[2]), fminf(fminf(u[3], u[4]), u[5])),
-                                  fminf(fminf(u[6], u[7]), st.run));
+            // three-input min tree; a closing segment stores 0.5 * (min * rowScale + rowTerm)
+            // = fma(min, 0.5 rowScale, 0.5 rowTerm) (rowScale is a power of two, so both roundings agree)
+            const float m6 = fminf(fminf(fminf(u[0], u[1]), u[2]), fminf(fminf(u[3], u[4]), u[5]));
+            if (SP > 0) {
+                const bool  first = (seg % SP) == 0, last = (seg % SP) == SP - 1;  // compile-time after unrolling
+                const float m = first ? fminf(m6, fminf(u[6], u[7])) : fminf(m6, fminf(fminf(u[6], u[7]), st.run));
+                if (last) {
+                    sts_f32(st.sp, fminf(fmaf(m, 0.5f * rs, 0.5f * rt), 0.5f * (FLT_MAX + rt)));
+                    st.sp += 4;
+                }
+                st.run = m;
+                continue;
+            }
+            const float m = fminf(m6, fminf(fminf(u[6], u[7]), st.run));
             const bool  close = (segEnd >> seg) & 1u;
             float       sc    = fminf(fmaf(m, 0.5f * rs, 0.5f * rt), 0.5f * (FLT_MAX + rt));
             sc                = ((segEmpty >> seg) & 1u) ? 0.5f * (FLT_MAX + rt) : sc;
@@ -247,8 +262,8 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
                         st.sum += ex2((st.run - u[j]) * hl2e);
             }
         }
-        if ((segEnd >> seg) & 1u) {  // uniform across the warp
-            const bool  empty = (segEmpty >> seg) & 1u;
+        if (SP > 0 ? (seg % SP) == SP - 1 : (bool)((segEnd >> seg) & 1u)) {  // uniform across the warp
+            const bool  empty = SP > 0 ? false : (bool)((segEmpty >> seg) & 1u);
             const float best  = empty ? FLT_MAX : fminf(st.run * rs, FLT_MAX);
             float       sc    = 0.5f * (best + rt);
             if (MODE == 1)
@@ -445,84 +460,96 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             char*           gTile  = reinterpret_cast<char*>(p.scores + (size_t)(f0 * kTileM + q * 32 + lr0) * p.ld + mixBase + lj0);
             const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
             const float2*   rip = p.rowInfo + (size_t)f0 * kTileM + q * 32 + lane;
-            for (uint32_t f = f0; f < f1; ++f, ++t) {
-                const uint32_t acc = t & 1;
-                const float2   ri  = *rip;
-                const float    rt = ri.x, rs = ri.y;
-                rip += kTileM;
-                mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
-                tc_fence_after();
-                const uint32_t taddr    = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + part * PW;
-                const uint32_t drained  = smem_u32(&ready[(t + 2) % kRing]);  // tile t + 2 reuses this accumulator
-                EpiState st;
-                st.run = INFINITY, st.sum = 0.f, st.idx = 0xFFFFFFFFu, st.sp = stRow;
-                uint32_t va[32], vb[32];
-                if (NE == 16) {
-                    // 64 columns: both loads in flight, then the accumulator goes straight back to the MMA warp
-                    tmem_ld32(taddr, va);
-                    tmem_ld32(taddr + 32, vb);
-                    tmem_ld_wait();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive(drained);
-                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                }
-                else {
-                    // 128 columns in four 32-column chunks, the next load in flight while one is reduced
-                    tmem_ld32(taddr, va);
-                    tmem_ld_wait();
-                    tmem_ld32(taddr + 32, vb);
-                    epi_chunk<MODE, BEST>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                    tmem_ld_wait();
-                    tmem_ld32(taddr + 64, va);
-                    epi_chunk<MODE, BEST>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                    tmem_ld_wait();
-                    tmem_ld32(taddr + 96, vb);
-                    epi_chunk<MODE, BEST>(va, 2, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                    tmem_ld_wait();
-                    // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive(drained);
-                    epi_chunk<MODE, BEST>(vb, 3, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                }
-                __syncwarp();
-                // coalesced store of the staged [32 rows x nMix] block: nMix passes of 32 consecutive elements;
-                // pointers advance by per-item constants (a pass that wraps past a row end takes the `w` step)
-                const uint32_t rbase = f * kTileM + q * 32;
-                const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
-                char*          gs    = gTile;
-                uint32_t       ss    = ssLane;
-                gTile += gTileStep;
-                if (adv_j == 0) {  // nMix divides 32: a lane keeps its column
-#pragma unroll 4
-                    for (uint32_t i = 0, r = lr0; i < nMix; ++i, r += adv_r) {
-                        if (r < rows) {
-                            *reinterpret_cast<float*>(gs) = lds_f32(ss);
-                            if (BEST)
-                                *reinterpret_cast<uint32_t*>(gs + bestDelta) = lds_u32(ss + offB);
-                        }
-                        gs += gStep, ss += sStep;
+            // the tile loop, specialised on the tile's mixture shape when it is uniform (see epi_chunk)
+            auto tiles = [&](auto spTag) {
+                constexpr int SP = decltype(spTag)::value;
+                for (uint32_t f = f0; f < f1; ++f, ++t) {
+                    const uint32_t acc = t & 1;
+                    const float2   ri  = *rip;
+                    const float    rt = ri.x, rs = ri.y;
+                    rip += kTileM;
+                    mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
+                    tc_fence_after();
+                    const uint32_t taddr    = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + part * PW;
+                    const uint32_t drained  = smem_u32(&ready[(t + 2) % kRing]);  // tile t + 2 reuses this accumulator
+                    EpiState st;
+                    st.run = INFINITY, st.sum = 0.f, st.idx = 0xFFFFFFFFu, st.sp = stRow;
+                    uint32_t va[32], vb[32];
+                    if (NE == 16) {
+                        // 64 columns: both loads in flight, then the accumulator goes straight back to the MMA warp
+                        tmem_ld32(taddr, va);
+                        tmem_ld32(taddr + 32, vb);
+                        tmem_ld_wait();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(drained);
+                        epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
                     }
-                }
-                else {
-                    uint32_t r = lr0, j = lj0;
-                    for (uint32_t i = 0; i < nMix; ++i) {
-                        if (r < rows) {
-                            *reinterpret_cast<float*>(gs) = lds_f32(ss);
-                            if (BEST)
-                                *reinterpret_cast<uint32_t*>(gs + bestDelta) = lds_u32(ss + offB);
-                        }
-                        const bool w = j + adv_j >= nMix;
-                        j            = w ? j + adv_j - nMix : j + adv_j;
-                        r += adv_r + (w ? 1u : 0u);
-                        gs += w ? gStepW : gStep, ss += w ? sStepW : sStep;
+                    else {
+                        // 128 columns in four 32-column chunks, the next load in flight while one is reduced
+                        tmem_ld32(taddr, va);
+                        tmem_ld_wait();
+                        tmem_ld32(taddr + 32, vb);
+                        epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        tmem_ld_wait();
+                        tmem_ld32(taddr + 64, va);
+                        epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        tmem_ld_wait();
+                        tmem_ld32(taddr + 96, vb);
+                        epi_chunk<MODE, BEST, SP>(va, 2, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        tmem_ld_wait();
+                        // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(drained);
+                        epi_chunk<MODE, BEST, SP>(vb, 3, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
                     }
+                    __syncwarp();
+                    // coalesced store of the staged [32 rows x nMix] block: nMix passes of 32 consecutive elements;
+                    // pointers advance by per-item constants (a pass that wraps past a row end takes the `w` step)
+                    const uint32_t rbase = f * kTileM + q * 32;
+                    const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
+                    char*          gs    = gTile;
+                    uint32_t       ss    = ssLane;
+                    gTile += gTileStep;
+                    if (adv_j == 0) {  // nMix divides 32: a lane keeps its column
+    #pragma unroll 4
+                        for (uint32_t i = 0, r = lr0; i < nMix; ++i, r += adv_r) {
+                            if (r < rows) {
+                                *reinterpret_cast<float*>(gs) = lds_f32(ss);
+                                if (BEST)
+                                    *reinterpret_cast<uint32_t*>(gs + bestDelta) = lds_u32(ss + offB);
+                            }
+                            gs += gStep, ss += sStep;
+                        }
+                    }
+                    else {
+                        uint32_t r = lr0, j = lj0;
+                        for (uint32_t i = 0; i < nMix; ++i) {
+                            if (r < rows) {
+                                *reinterpret_cast<float*>(gs) = lds_f32(ss);
+                                if (BEST)
+                                    *reinterpret_cast<uint32_t*>(gs + bestDelta) = lds_u32(ss + offB);
+                            }
+                            const bool w = j + adv_j >= nMix;
+                            j            = w ? j + adv_j - nMix : j + adv_j;
+                            r += adv_r + (w ? 1u : 0u);
+                            gs += w ? gStepW : gStep, ss += w ? sStepW : sStep;
+                        }
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
+            };
+            const uint32_t uni = (MODE == 0) ? ((meta[10] >> (8 * part)) & 0xFFu) : 0u;  // TileMeta::uni
+            switch (uni) {
+                case 1: tiles(std::integral_constant<int, 1>{}); break;
+                case 2: tiles(std::integral_constant<int, 2>{}); break;
+                case 4: tiles(std::integral_constant<int, 4>{}); break;
+                case 8: tiles(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
+                default: tiles(std::integral_constant<int, 0>{}); break;
             }
             // this warp no longer reads slot / meta of the B buffer
             if (lane == 0)
@@ -714,7 +741,7 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     auto partOf = [&]() { return (uint32_t)(cols.size() / partW); };
     auto ensurePart = [&](uint32_t pt) {
         while (metas.size() * partsPerTile <= pt) {
-            TileMeta z = {0, 0, {0, 0, 0, 0}, {0, 0, 0, 0}};
+            TileMeta z = {0, 0, {0, 0, 0, 0}, {0, 0, 0, 0}, 0};
             metas.push_back(z);
         }
         while (mixPerPart.size() <= pt)
@@ -768,6 +795,21 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     }
     tm.nTiles = (uint32_t)(cols.size() / kTileN);
     ensurePart(tm.nTiles * partsPerTile - 1);
+    // uniform parts: all segments of the part taken by mixtures of the same power-of-two segment count, none empty
+    for (TileMeta& mt : metas) {
+        const uint32_t segsPerPart = partW / 8;
+        for (uint32_t pp = 0; pp < partsPerTile; ++pp) {
+            const uint32_t mask = segsPerPart == 32 ? 0xFFFFFFFFu : ((1u << segsPerPart) - 1u);
+            const uint32_t ends = (mt.segEnd >> (pp * segsPerPart)) & mask, empt = (mt.segEmpty >> (pp * segsPerPart)) & mask;
+            for (uint32_t S = 1; S <= 8 && S <= segsPerPart; S *= 2) {
+                uint32_t pat = 0;
+                for (uint32_t b = S - 1; b < segsPerPart; b += S)
+                    pat |= 1u << b;
+                if (ends == pat && empt == 0)
+                    mt.uni |= S << (8 * pp);
+            }
+        }
+    }
     tm.maxMixPerPart = 1;
     for (uint32_t v : mixPerPart)
         tm.maxMixPerPart = std::max(tm.maxMixPerPart, v);
