@@ -61,7 +61,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -186,22 +186,46 @@ def time_device(torch, fn, steps, warmup, dist=None):
     return sec, w0, w1
 
 
-def float_roofline(ms, frames, sec_per_step, peaks, kernel_name, share=1.0):
+def ncu_traffic(summary_name):
+    """dram read + write bytes per launch of the dominant kernel, from the committed ncu summary (profiles/)."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", summary_name)
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        for line in open(path):
+            if line.startswith("traffic ="):
+                tok = line.split(")")[-1].split()
+                return float(tok[0]) * mult[tok[1]] + float(tok[3]) * mult[tok[4]]
+    except (OSError, KeyError, ValueError, IndexError):
+        pass
+    return None
+
+
+def float_roofline(ms, frames, kernel_sec, peaks, kernel_name, step_sec=None, traffic=None, sustained=False):
+    """kernel_sec: average duration of ONE launch of the scoring kernel (CUDA events around the launch).
+    sustained: the kernel ran back to back for >= 100 ms (power-capped clocks) -> the sustained cuBLAS figure is
+    the denominator; a kernel timed in a short burst is compared with the burst figure."""
     flops = 2.0 * (2 * ms.D + 1) * ms.G * frames  # algorithmic, SURVEY.md 8(d)
-    ach = flops / (sec_per_step * share) / 1e12
-    return {"bound": "tensor", "achieved": ach, "peak": peaks["tensor"], "unit": "TFLOP/s",
-            "frac": ach / peaks["tensor"], "traffic": None, "kernel": kernel_name,
-            "peak_source": f"{peaks['source']} bf16 dense burst (MEASURED_PEAKS.json)",
+    ach = flops / kernel_sec / 1e12
+    peak = peaks["tensor_sustained"] if sustained else peaks["tensor"]
+    return {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+            "frac": ach / peak, "traffic": traffic, "kernel": kernel_name,
+            "kernel_ms_per_launch": kernel_sec * 1e3,
+            "kernel_share_of_step": (kernel_sec / step_sec) if step_sec else None,
+            "frac_of_burst_peak": ach / peaks["tensor"],
+            "executed_over_algorithmic": 3.0 * (16 * (((ms.D if ms.variances.shape[0] == 1 else 2 * ms.D) + 3 + 15) // 16))
+                                         / (2 * ms.D + 1),
+            "peak_source": f"{peaks['source']} bf16 dense {'sustained' if sustained else 'burst'} (MEASURED_PEAKS.json)",
             "algorithmic_flops_per_launch": flops,
-            "gaussian_evals_per_s": ms.G * frames / sec_per_step}
+            "gaussian_evals_per_s_kernel": ms.G * frames / kernel_sec}
 
 
-def quant_roofline(ms, frames, sec_per_step, peaks, outputs=2):
+def quant_roofline(ms, frames, kernel_sec, peaks, outputs=2, traffic=None):
     dpad = ((ms.D + 15) // 16) * 16
     nbytes = ms.G * (dpad + 4) + frames * dpad + frames * ms.M * 4 * outputs  # SURVEY.md 8(d)
-    ach = nbytes / sec_per_step / 1e9
+    ach = nbytes / kernel_sec / 1e9
     return {"bound": "hbm", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s", "frac": ach / peaks["hbm"],
-            "traffic": None, "kernel": "quant_score_kernel", "algorithmic_bytes_per_launch": nbytes,
+            "traffic": traffic, "kernel": "quant_score_kernel", "kernel_ms_per_launch": kernel_sec * 1e3,
+            "algorithmic_bytes_per_launch": nbytes,
             "peak_source": f"{peaks['source']} copy bandwidth (MEASURED_PEAKS.json)"}
 
 
@@ -257,6 +281,15 @@ def run_ours(args):
     sec_per_step = sec / args.steps
     value = world * frames / sec_per_step
 
+    # roofline pass: the same steps again with CUDA events bracketing each launch of the scoring kernel
+    eng.kernel_timing(True)
+    eng.kernel_time()
+    for _ in range(args.steps):
+        step()
+    kernel_ms, kernel_n = eng.kernel_time()
+    eng.kernel_timing(False)
+    kernel_sec = kernel_ms / 1e3 / max(1, args.steps)  # one launch per step on the tensor path
+
     # end to end through the host API: pinned features in, host scores out, every step
     e2e_frames = min(frames, 8 * SEG_FRAMES)
     out_host = torch.empty((e2e_frames, ms.M), dtype=torch.float32).pin_memory()
@@ -299,7 +332,9 @@ def run_ours(args):
                     "api": "gmm_score_host (C-ABI, pinned host buffers)"},
             "clocks": clocks}
     if rank == 0:
-        line["roofline"] = float_roofline(ms, frames, sec_per_step, peaks, kname)
+        line["roofline"] = float_roofline(ms, frames, kernel_sec, peaks, kname, sec_per_step,
+                                          ncu_traffic("prof_tc_cfg1_bench_r01.txt") if frames == 512000 else None,
+                                          sustained=sec >= 0.1)
         if world == 1 and not args.no_cpu:
             cores = len(os.sched_getaffinity(0))
             line["cpu_baseline"] = cpu_reference_run(ms, max(512, 96 * cores), "max", 2)
@@ -311,6 +346,17 @@ def run_ours(args):
         dist.destroy_process_group()
     eng.close()
     return 0
+
+
+def timed_kernel(eng, fn, steps):
+    """Device time of the scoring kernel per call, averaged over `steps` calls (events inside the library)."""
+    eng.kernel_timing(True)
+    eng.kernel_time()
+    for _ in range(steps):
+        fn()
+    ms_total, n = eng.kernel_time()
+    eng.kernel_timing(False)
+    return ms_total / 1e3 / max(1, steps)  # per call (a call may chunk the frames over several launches)
 
 
 def extra_cases(torch, eng, peaks, args):
@@ -327,8 +373,10 @@ def extra_cases(torch, eng, peaks, args):
     dq = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
     db = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
     sec, _, _ = time_device(torch, lambda: eng.quant_score_device(T, dx, dq, db), steps, warmup)
+    ksec = timed_kernel(eng, lambda: eng.quant_score_device(T, dx, dq, db), steps)
     out["cfg2_quantized"] = {"frames_per_s": T * steps / sec, "ms_per_step": 1e3 * sec / steps, "frames": T,
-                             "roofline": quant_roofline(ms, T, sec / steps, peaks)}
+                             "roofline": quant_roofline(ms, T, ksec, peaks,
+                                                        traffic=ncu_traffic("prof_quant_cfg2_r01.txt"))}
     del dq, db
     # cfg3: 12001 x 64, 10k-frame batches, max and sum
     ms, x = synth.make_config("cfg3", T=10000)
@@ -341,8 +389,11 @@ def extra_cases(torch, eng, peaks, args):
                          mode=mode, kernel=capi.KERNEL_AUTO)
         st = steps if eng.float_kernel == capi.KERNEL_TENSOR else 2
         sec, _, _ = time_device(torch, lambda: eng.score_device(T, dx, ds), st, 1 if st == 2 else warmup)
+        ksec = timed_kernel(eng, lambda: eng.score_device(T, dx, ds), st)
+        prof = {"cfg3_max": "prof_tc_cfg3_max_10000_r01.txt", "cfg3_sum": "prof_tc_cfg3_sum_10000_r01.txt"}[name]
         out[name] = {"frames_per_s": T * st / sec, "ms_per_step": 1e3 * sec / st, "frames": T,
-                     "kernel": eng.float_kernel, "roofline": float_roofline(ms, T, sec / st, peaks, str(eng.float_kernel))}
+                     "kernel": eng.float_kernel,
+                     "roofline": float_roofline(ms, T, ksec, peaks, str(eng.float_kernel), sec / st, ncu_traffic(prof))}
     return out
 
 
@@ -352,7 +403,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--segments", type=int, default=32, help="1000-frame segments per GPU per step")
+    ap.add_argument("--segments", type=int, default=512, help="1000-frame segments per GPU per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the cfg2 / cfg3 side measurements")
     args = ap.parse_args()

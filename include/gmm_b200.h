@@ -102,6 +102,12 @@ void* gmm_host_alloc(size_t bytes);
 void  gmm_host_free(void* p);
 int      gmm_sync(gmm_handle* h);                       /* wait for the handle's stream */
 uint64_t gmm_launch_count(const gmm_handle* h);         /* kernels launched by this handle so far */
+/* Measurement aid (bench.py's roofline): with timing on, every launch of a SCORING kernel (tensor, direct or
+ * quantized scorer; not the frame preparation / quantization passes) is bracketed by CUDA events on the handle's
+ * stream.  gmm_kernel_time waits for the stream, returns the summed device time and the number of bracketed
+ * launches since the last call, and resets both. */
+int gmm_kernel_timing(gmm_handle* h, int on);
+int gmm_kernel_time(gmm_handle* h, double* total_ms, uint64_t* launches);
 /* 1 = direct, 2 = tensor: the float kernel the last gmm_upload_float selected. */
 int         gmm_float_kernel(const gmm_handle* h);
 const char* gmm_version(void);

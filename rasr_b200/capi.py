@@ -35,6 +35,8 @@ SYMBOLS = [
     ("gmm_host_free", None, [_vp]),
     ("gmm_sync", _i, [_vp]),
     ("gmm_launch_count", C.c_uint64, [_vp]),
+    ("gmm_kernel_timing", _i, [_vp, _i]),
+    ("gmm_kernel_time", _i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     ("gmm_float_kernel", _i, [_vp]),
     ("gmm_version", C.c_char_p, []),
 ]
@@ -115,6 +117,15 @@ class Engine:
     @property
     def launch_count(self) -> int:
         return int(self._lib.gmm_launch_count(self._h))
+
+    def kernel_timing(self, on: bool):
+        self._check(self._lib.gmm_kernel_timing(self._h, 1 if on else 0), "gmm_kernel_timing")
+
+    def kernel_time(self):
+        """(summed device ms, launches) of the scoring kernels bracketed since the last call."""
+        ms, n = C.c_double(0.0), C.c_uint64(0)
+        self._check(self._lib.gmm_kernel_time(self._h, C.byref(ms), C.byref(n)), "gmm_kernel_time")
+        return ms.value, int(n.value)
 
     @property
     def float_kernel(self) -> int:

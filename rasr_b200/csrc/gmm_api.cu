@@ -117,6 +117,10 @@ void gmm_destroy(gmm_handle* h) {
     cudaSetDevice(h->device);
     releaseFloatModel(h);
     releaseQuantModel(h);
+    for (size_t i = 0; i < h->timed.size(); ++i) {
+        cudaEventDestroy(h->timed[i].first);
+        cudaEventDestroy(h->timed[i].second);
+    }
     for (int i = 0; i < 8; ++i)
         if (h->scratch[i])
             cudaFree(h->scratch[i]);
@@ -151,6 +155,34 @@ int gmm_sync(gmm_handle* h) {
     if (!h)
         return GMM_ERR_ARG;
     GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GMM_OK;
+}
+
+int gmm_kernel_timing(gmm_handle* h, int on) {
+    if (!h)
+        return GMM_ERR_ARG;
+    h->timing = on != 0;
+    return GMM_OK;
+}
+
+int gmm_kernel_time(gmm_handle* h, double* total_ms, uint64_t* launches) {
+    if (!h)
+        return GMM_ERR_ARG;
+    GMM_CUDA_TRY(h, cudaSetDevice(h->device));
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    double sum = 0.0;
+    for (size_t i = 0; i < h->timed.size(); ++i) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, h->timed[i].first, h->timed[i].second) == cudaSuccess)
+            sum += ms;
+        cudaEventDestroy(h->timed[i].first);
+        cudaEventDestroy(h->timed[i].second);
+    }
+    if (total_ms)
+        *total_ms = sum;
+    if (launches)
+        *launches = h->timed.size();
+    h->timed.clear();
     return GMM_OK;
 }
 

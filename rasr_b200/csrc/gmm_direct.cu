@@ -210,6 +210,7 @@ int launch(gmm_handle* h, int mode, uint32_t T, const float* d_x, float* d_score
     dim3      grid(gx, gy), block(256);
 #define GMM_ARGS d_x, (int)T, (int)h->D, (int)h->M, dm.mean, dm.isr, dm.covIdx, dm.w2, dm.logNorm, \
     dm.offsets, mixPerBlock, d_scores, d_best, ld, d_post, (size_t)h->G
+    h->timeBegin();
     if (mode == 0)
         direct_kernel<DP, FR, 0><<<grid, block, 0, h->stream>>>(GMM_ARGS);
     else if (mode == 1)
@@ -217,6 +218,7 @@ int launch(gmm_handle* h, int mode, uint32_t T, const float* d_x, float* d_score
     else
         direct_kernel<DP, FR, 2><<<grid, block, 0, h->stream>>>(GMM_ARGS);
 #undef GMM_ARGS
+    h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
     return GMM_OK;

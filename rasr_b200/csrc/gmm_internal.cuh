@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/gmm_b200.h"
@@ -64,6 +65,21 @@ struct gmm_handle {
     cudaStream_t stream     = nullptr;
     bool         ownStream  = false;
     uint64_t     launches   = 0;
+    bool         timing     = false;                            // gmm_kernel_timing
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed;     // brackets of scoring-kernel launches
+    void timeBegin() {
+        if (!timing)
+            return;
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        cudaEventRecord(a, stream);
+        timed.push_back(std::make_pair(a, b));
+    }
+    void timeEnd() {
+        if (timing && !timed.empty())
+            cudaEventRecord(timed.back().second, stream);
+    }
     std::string  error;
 
     // float engine

@@ -165,6 +165,7 @@ int launchScore(gmm_handle* h, uint32_t T, const uint8_t* d_qx, int32_t* d_q, ui
         mixPerBlock = 1;
     const int gx = (qm.M + mixPerBlock - 1) / mixPerBlock;
     dim3      grid(gx, gy), block(256);
+    h->timeBegin();
     if (qm.C == 1)
         quant_score_kernel<DW, FR, true><<<grid, block, 0, h->stream>>>(
                 d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
@@ -173,6 +174,7 @@ int launchScore(gmm_handle* h, uint32_t T, const uint8_t* d_qx, int32_t* d_q, ui
         quant_score_kernel<DW, FR, false><<<grid, block, 0, h->stream>>>(
                 d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
                 (double)qm.scalingSquared, d_q, d_best, d_score, ld);
+    h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
     return GMM_OK;

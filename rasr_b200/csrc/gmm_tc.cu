@@ -87,7 +87,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {  // one probe, no spinning
     uint32_t ok;
     asm volatile(
-            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            "{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(ok)
             : "r"(bar), "r"(parity)
             : "memory");
@@ -595,25 +595,30 @@ __device__ __forceinline__ void split_fp16(float v, __half& hi, __half& lo) {
 // A row whose largest |a| would leave the fp16 range is stored divided by a power of two (row scale); the
 // epilogue multiplies the per-mixture minimum back, so outlier frames stay exact.  Three spare K columns hold
 // 1/rowScale: they multiply the fp16 pieces of the per-Gaussian constant stored in the B operand.
-// One warp per frame: lane l owns the 8-element chunk l of each precision part (kSteps <= 16 -> <= 32 chunks).
-template<bool POOLED>
-__global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t D, uint32_t frameTiles,
-                               const float* __restrict__ ctr, const float* __restrict__ scale, uint32_t kSteps,
-                               uint32_t atoms, uint32_t swz, uint8_t* __restrict__ aTiles,
-                               float2* __restrict__ rowInfo) {
+// LPF lanes share a frame (LPF = power of two >= the 8-element chunks per precision part, so 32 / LPF frames per
+// warp): lane c of a frame's group owns chunk c of the hi and of the lo part; group reductions give the row term.
+template<bool POOLED, int LPF>
+__global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t D,
+                                                      uint32_t frameTiles, const float* __restrict__ ctr,
+                                                      const float* __restrict__ scale, uint32_t kSteps, uint32_t atoms,
+                                                      uint32_t swz, uint8_t* __restrict__ aTiles,
+                                                      float2* __restrict__ rowInfo) {
     const uint32_t chunks = kSteps * 2;  // 8-element chunks per precision part
     const uint32_t epa    = swz / 2;     // fp16 elements per atom row
-    const uint32_t lane   = threadIdx.x & 31;
+    const uint32_t lane   = threadIdx.x & 31, c = lane % LPF;
     const uint32_t kel    = POOLED ? D : 2 * D;
-    const uint32_t warpsPerGrid = gridDim.x * (blockDim.x >> 5);
-    for (uint32_t t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < frameTiles * kTileM; t += warpsPerGrid) {
+    constexpr uint32_t fpw = 32 / LPF;   // frames per warp
+    const uint32_t framesPerGrid = gridDim.x * (blockDim.x >> 5) * fpw;
+    const uint32_t rows = frameTiles * kTileM;
+    for (uint32_t t = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * fpw + lane / LPF; t < rows;
+         t += framesPerGrid) {
         float v[8];
         float vmax = 0.f, ssq = 0.f;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const uint32_t k = lane * 8 + j;
+            const uint32_t k = c * 8 + j;
             v[j]             = 0.f;
-            if (t < T && lane < chunks) {
+            if (t < T && c < chunks) {
                 if (POOLED) {
                     if (k < D) {
                         v[j] = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
@@ -633,7 +638,7 @@ __global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t
             vmax = fmaxf(vmax, fabsf(v[j]));
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
+        for (int o = LPF / 2; o > 0; o >>= 1) {
             vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
             ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
         }
@@ -645,16 +650,16 @@ __global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t
             rs = ldexpf(1.f, e - 14);
         }
         const float inv = 1.f / rs;
-        if (lane == 0)
+        if (c == 0)
             rowInfo[t] = make_float2(ssq, rs);
         const uint32_t tile = t / kTileM, row = t % kTileM;
         uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * swz;
-        if (lane < chunks) {
+        if (c < chunks) {
             __align__(16) __half hi[8], lo[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j)
                 split_fp16(v[j] * inv, hi[j], lo[j]);
-            const uint32_t kHi = lane * 8, kLo = kSteps * 16 + lane * 8;
+            const uint32_t kHi = c * 8, kLo = kSteps * 16 + c * 8;
             *reinterpret_cast<uint4*>(base + (size_t)(kHi / epa) * kTileM * swz +
                                       swz_offset(row, (kHi % epa) / 8, swz)) = *reinterpret_cast<const uint4*>(hi);
             *reinterpret_cast<uint4*>(base + (size_t)(kLo / epa) * kTileM * swz +
@@ -662,9 +667,9 @@ __global__ void tc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t
         }
         // zero the unused tail of the last atom
         const uint32_t used = chunks * 2, all = atoms * (swz / 16);  // 16-byte chunks per row
-        for (uint32_t c = used + lane; c < all; c += 32)
-            *reinterpret_cast<uint4*>(base + (size_t)(c / (swz / 16)) * kTileM * swz +
-                                      swz_offset(row, c % (swz / 16), swz)) = make_uint4(0, 0, 0, 0);
+        for (uint32_t cc = used + c; cc < all; cc += LPF)
+            *reinterpret_cast<uint4*>(base + (size_t)(cc / (swz / 16)) * kTileM * swz +
+                                      swz_offset(row, cc % (swz / 16), swz)) = make_uint4(0, 0, 0, 0);
     }
 }
 
@@ -952,13 +957,30 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
     if ((rc = h->reserve(SCR_ROW, (size_t)FT * kTileM * 8, &rT)))
         return rc;
     {
-        int blocks = (int)std::min<uint32_t>((FT * kTileM + 7) / 8, (uint32_t)h->smCount * 8);
-        if (tm.pooled)
-            tc_prep_kernel<true><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps,
-                                                                tm.nAtoms, tm.swz, (uint8_t*)aT, (float2*)rT);
-        else
-            tc_prep_kernel<false><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps,
-                                                                 tm.nAtoms, tm.swz, (uint8_t*)aT, (float2*)rT);
+        const uint32_t chunks = tm.kSteps * 2;
+        const uint32_t lpf    = chunks <= 8 ? 8 : chunks <= 16 ? 16 : 32;
+        const uint32_t fpb    = 8 * (32 / lpf);  // frames per 256-thread block
+        int blocks = (int)std::min<uint32_t>((FT * kTileM + fpb - 1) / fpb, (uint32_t)h->smCount * 16);
+#define GMM_PREP(P, L)                                                                                          \
+    tc_prep_kernel<P, L><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps, tm.nAtoms, \
+                                                        tm.swz, (uint8_t*)aT, (float2*)rT)
+        if (tm.pooled) {
+            if (lpf == 8)
+                GMM_PREP(true, 8);
+            else if (lpf == 16)
+                GMM_PREP(true, 16);
+            else
+                GMM_PREP(true, 32);
+        }
+        else {
+            if (lpf == 8)
+                GMM_PREP(false, 8);
+            else if (lpf == 16)
+                GMM_PREP(false, 16);
+            else
+                GMM_PREP(false, 32);
+        }
+#undef GMM_PREP
         h->launches++;
         GMM_CUDA_TRY(h, cudaGetLastError());
     }
@@ -994,7 +1016,10 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
            smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA + 1, p.stagePitch, best, epiWarps) <= kSmemLimit)
         p.stagesA++;
     const size_t smemBytes = smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best, epiWarps);
-    // split the frame range so that the items fill the SMs evenly: cost in A-tile MMA times
+    // split the frame range so that the items fill the SMs evenly: cost in A-tile MMA times.  Items are handed out
+    // round-robin, so the CTAs running together hold ADJACENT B tiles over the same frames and their 16..64-byte row
+    // pieces merge into full lines in L2.  (Giving every CTA one contiguous range of the linearised tile space
+    // balances perfectly but scatters those pieces in time: measured 0.49 -> 0.82 ms on the 4501x16 model.)
     const double bCost = tm.buffersB == 2 ? 0.5 : 2.0;
     uint32_t     bestS = 1;
     double       bestCost = 1e300;
@@ -1019,11 +1044,13 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
                        : launch_tc<SWZ, 0, false, NE>(p, grid, smemBytes, h->stream))                         \
                : (best ? launch_tc<SWZ, 1, true, NE>(p, grid, smemBytes, h->stream)                           \
                        : launch_tc<SWZ, 1, false, NE>(p, grid, smemBytes, h->stream)))
+    h->timeBegin();
     if (tm.swz == 128)
         e = epiWarps == 16 ? GMM_TC_LAUNCH(128, 16) : GMM_TC_LAUNCH(128, 8);
     else
         e = epiWarps == 16 ? GMM_TC_LAUNCH(64, 16) : GMM_TC_LAUNCH(64, 8);
 #undef GMM_TC_LAUNCH
+    h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, e);
     if (debug) {  // development aid: where the MMA-issuing thread spends its cycles
