@@ -89,6 +89,19 @@ class ClockSampler:
                 "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows), "reasons": reasons}
 
 
+def bind_to_gpu_numa_node(index: int):
+    """One process per GPU: pin this process to the CPUs next to its GPU (NVML's ideal affinity) so that page-locked
+    buffers and the copy threads sit on the GPU's NUMA node; without it the 8-rank host-delivered rate is limited by
+    cross-socket traffic.  Best effort: silently skipped when NVML is unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(index))
+        return True
+    except Exception:
+        return False
+
+
 def workload(segments: int):
     from rasr_b200 import synth
     ms = synth.make_model(4501, 16, 45, seed=1001, covariance="pooled")
@@ -247,6 +260,8 @@ def run_ours(args):
     segs = args.segments
     ms, frames = workload(segs)
     tab = tables.float_tables(ms)
+    all_cpus = os.sched_getaffinity(0)
+    bind_to_gpu_numa_node(local)  # before any pinned allocation: host buffers land on the GPU's own NUMA node
     eng = capi.Engine(local)
     stream = torch.cuda.Stream()  # a real (non-default) stream: the engine launches on it, the events time it
     torch.cuda.set_stream(stream)
@@ -336,6 +351,7 @@ def run_ours(args):
                                           ncu_traffic("prof_tc_cfg1_bench_r01.txt") if frames == 512000 else None,
                                           sustained=sec >= 0.1)
         if world == 1 and not args.no_cpu:
+            os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core again
             cores = len(os.sched_getaffinity(0))
             line["cpu_baseline"] = cpu_reference_run(ms, max(512, 96 * cores), "max", 2)
         if world == 1 and not args.no_extra:

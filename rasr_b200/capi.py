@@ -38,6 +38,7 @@ SYMBOLS = [
     ("gmm_kernel_timing", _i, [_vp, _i]),
     ("gmm_kernel_time", _i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     ("gmm_float_kernel", _i, [_vp]),
+    ("gmm_quant_kernel", _i, [_vp]),
     ("gmm_version", C.c_char_p, []),
 ]
 
@@ -130,6 +131,10 @@ class Engine:
     @property
     def float_kernel(self) -> int:
         return int(self._lib.gmm_float_kernel(self._h))
+
+    @property
+    def quant_kernel(self) -> int:
+        return int(self._lib.gmm_quant_kernel(self._h))
 
     # -- float engine -----------------------------------------------------------------------------
     def upload_float(self, offsets, mean, isr, cov_idx, w2, log_norm, mode=MODE_MAX, kernel=KERNEL_AUTO):

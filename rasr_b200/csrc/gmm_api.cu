@@ -57,7 +57,8 @@ static void releaseQuantModel(gmm_handle* h) {
     for (void* p : h->ownedQuant)
         cudaFree(p);
     h->ownedQuant.clear();
-    h->quant = QuantModel();
+    h->quant   = QuantModel();
+    h->qtensor = QTensorModel();
 }
 
 extern "C" {
@@ -156,6 +157,12 @@ int gmm_sync(gmm_handle* h) {
         return GMM_ERR_ARG;
     GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     return GMM_OK;
+}
+
+int gmm_quant_kernel(const gmm_handle* h) {
+    if (!h || !h->quant.valid)
+        return 0;
+    return h->qtensor.valid ? 2 : 1;
 }
 
 int gmm_kernel_timing(gmm_handle* h, int on) {
@@ -410,7 +417,8 @@ int gmm_upload_quant(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t
         return rc;
     GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     qm.valid = true;
-    return GMM_OK;
+    // integer tensor path where the model allows it (pooled covariance, no wrap-around); else dp4a
+    return gmm_qtc_pack(h, offsets, qmean, c2.data());
 }
 
 int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,

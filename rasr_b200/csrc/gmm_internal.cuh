@@ -59,6 +59,20 @@ struct QuantModel {
     uint32_t* offsets = nullptr;  // [M+1]
 };
 
+// quantized scorer on the integer tensor path (gmm_qtc.cu); valid only for models that meet its requirements
+struct QTensorModel {
+    bool      valid      = false;
+    uint32_t  kSteps     = 0;       // 32-byte k-steps (K = Dpad rounded up to 32)
+    uint32_t  nAtoms     = 0;       // 64-byte swizzle atoms per operand row
+    uint32_t  nTiles     = 0;       // 256-column tiles of the packed B operand
+    uint32_t  tileBytes  = 0;       // bytes per B tile image (operand rows, Kc table, TileMeta)
+    uint32_t  aTileBytes = 0;
+    uint8_t*  bTiles     = nullptr;
+    uint32_t  maxMixPerPart = 0;
+    uint32_t  buffersB   = 0, stagesA = 0;
+    uint32_t  qBase      = 0;       // min c2 - 2 Dmax (wrapping)
+};
+
 struct gmm_handle {
     int          device     = 0;
     int          smCount    = 0;
@@ -89,6 +103,7 @@ struct gmm_handle {
     DirectModel direct;
     TensorModel tensor;
     QuantModel  quant;
+    QTensorModel qtensor;
 
     // scratch (grown on demand)
     void*  scratch[8]      = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -111,6 +126,9 @@ int gmm_direct_posteriors(gmm_handle* h, uint32_t T, const float* d_x, float* d_
 int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
                      uint8_t* d_qx, size_t ld);
 // gmm_tc.cu
+int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, const int32_t* c2);
+int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
+                  uint8_t* d_qx, size_t ld);
 int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
                 const float* w2, const float* logNorm, bool force);
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);

@@ -1,0 +1,603 @@
+// Quantized (u8) scorer on the integer tensor path of sm_100a (tcgen05.mma kind::i8, u8 x u8 -> s32, exact):
+// bit-identical to the reference's SIMD-diagonal-maximum scorer
+// (/root/reference/src/Mm/SimdFeatureScorer.cc:135-176, IntelOptimization.cc:50-113) for pooled-covariance models;
+// everything else stays on the dp4a kernel of gmm_quant.cu, which is the same arithmetic on CUDA cores.
+//
+//   q[t][m] = min_k( qconst_k + sum_d (qmean_k[d] - qx_t[d])^2 )              (first strict minimum)
+//           = min_k( c2_k - 2 dot(qmean_k, qx_t) ) + |qx_t|^2,                  c2_k = qconst_k + |qmean_k|^2
+// The contraction dot() is one dense u8 GEMM: frames x Gaussians, K = Dpad rounded up to 32 bytes, accumulated
+// in s32 in TMEM.  Every partial is an exact integer (dot <= K * 255^2 < 2^23), so nothing is approximated.
+//
+// Arg-min without compare/select chains: with cmin = min_k c2_k over the model and Dmax = K * 255^2,
+//   u_k = (c2_k - cmin) + 2 Dmax - 2 dot_k  >= 0            and   key_k = (u_k << 8) | slot_k
+// orders columns by score first and by density index second, so an unsigned min over keys IS the reference's
+// first-strict-minimum rule.  key_k = Kc_k - (dot_k << 9) with the per-column constant Kc_k = ((c2_k - cmin + 2 Dmax)
+// << 8) | slot_k shipped next to the operand tile: one integer op per accumulator element plus a 3-input min tree.
+// Requirements checked at packing time (else the model is left to the dp4a kernel): one covariance, mixtures of
+// at most 128 densities, (max c2 - min c2) + 2 Dmax < 2^24 - 1 (no wrap-around anywhere: zero-weight densities,
+// whose reference constant is the x86 "integer indefinite" 0x80000000, fail this test and take the exact
+// wrapping path of gmm_quant.cu).
+//
+// Layout and pipeline are those of the float tensor kernel (gmm_tc.cu): pre-swizzled tile images in HBM staged
+// by cp.async.bulk, B tile resident per work item, A tiles streaming through a ring, two accumulators in TMEM,
+// tile-indexed ready/done barrier rings, one MMA-issuing lane, eight epilogue warps.
+//   B tile = 256 packed columns: [atoms][256 rows][64 B] u8 | Kc[256] u32 | TileMeta
+//   A tile = 128 frames:         [atoms][128 rows][64 B] u8          + per-frame |qx|^2 (u32)
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <type_traits>
+
+#include "gmm_internal.cuh"
+#include "gmm_umma.cuh"
+
+namespace {
+
+constexpr int      kQSwz       = 64;                   // swizzle atom: 64-byte rows hold two 32-byte k-steps
+constexpr int      kQEpiWarps  = 8;
+constexpr int      kQMetaBytes = kTileN * 4 + 48;      // Kc[256] u32, TileMeta
+constexpr uint32_t kNoKey      = 0xFFFFFFFFu;          // pad / filler column: never the minimum
+
+struct QKParams {
+    const uint8_t*  bTiles;
+    const uint8_t*  aTiles;
+    const uint32_t* rowXX;  // per frame row: |qx|^2
+    int32_t*        q;
+    uint32_t*       best;
+    float*          score;
+    size_t          ld;
+    double          scalingSquared;
+    uint32_t        T;
+    uint32_t        nTiles, frameTiles, split;
+    uint32_t        kSteps;      // 32-byte k-steps
+    uint32_t        atoms;       // 64-byte swizzle atoms per operand row
+    uint32_t        aTileBytes, bTileBytes;
+    uint32_t        stagesA, buffersB;
+    uint32_t        stagePitch;  // words per staging row (maxMixPerPart + 1)
+    uint32_t        qBase;       // cmin - 2 Dmax (wrapping u32): q = (key >> 8) + qBase + |qx|^2
+};
+
+__device__ __forceinline__ uint8_t quantize_u8(float v) {
+    // round(): half away from zero; (int) of an out-of-range value is cvttss2si's 0x80000000
+    // (/root/reference/src/Mm/Utilities.hh:179-191)
+    float r = roundf(v);
+    int   i = (fabsf(r) < 2147483648.f) ? __float2int_rz(r) : (int)0x80000000;
+    int   s = (int)((unsigned)i + 128u);
+    s       = s < 0 ? 0 : (s > 255 ? 255 : s);
+    return (uint8_t)s;
+}
+
+// Frame preparation: x [T x D] -> A tile images (quantized bytes, swizzled) + |qx|^2 per frame; optionally the plain
+// quantized frames [T x Dpad] for the caller.  Eight lanes share a frame, lane c owns bytes [16c, 16c + 16).
+__global__ void __launch_bounds__(256) qtc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t D,
+                                                       uint32_t Dpad, uint32_t frameTiles,
+                                                       const float* __restrict__ isrS, uint32_t atoms,
+                                                       uint8_t* __restrict__ aTiles, uint32_t* __restrict__ rowXX,
+                                                       uint8_t* __restrict__ qxOut) {
+    const uint32_t lane = threadIdx.x & 31, c = lane & 7;
+    const uint32_t rows = frameTiles * kTileM, chunksAll = atoms * (kQSwz / 16);
+    const uint32_t framesPerGrid = gridDim.x * (blockDim.x >> 5) * 4;
+    for (uint32_t t = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4 + (lane >> 3); t < rows;
+         t += framesPerGrid) {
+        uint32_t w[4] = {0, 0, 0, 0};
+        if (t < T && c * 16 < Dpad) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const uint32_t d = c * 16 + j;
+                uint32_t       v = 0;
+                if (d < D)
+                    v = quantize_u8(__fmul_rn(x[(size_t)t * D + d], isrS[d]));
+                w[j >> 2] |= v << (8 * (j & 3));
+            }
+        }
+        uint32_t xx = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            xx = __dp4a(w[i], w[i], xx);
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1)
+            xx += __shfl_xor_sync(0xffffffffu, xx, o);
+        if (c == 0)
+            rowXX[t] = xx;
+        const uint32_t tile = t / kTileM, row = t % kTileM;
+        uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * kQSwz;
+        if (c < chunksAll)  // bytes past Dpad inside the last atom are written as zeros (w == 0)
+            *reinterpret_cast<uint4*>(base + (size_t)(c / 4) * kTileM * kQSwz + swz_offset(row, c % 4, kQSwz)) =
+                    make_uint4(w[0], w[1], w[2], w[3]);
+        if (qxOut && t < T && c * 16 < Dpad)
+            *reinterpret_cast<uint4*>(qxOut + (size_t)t * Dpad + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+__device__ __forceinline__ void tc_mma_i8(uint32_t dTmem, uint64_t aDesc, uint64_t bDesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(dTmem),
+            "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
+            : "memory");
+}
+
+struct QEpiState {
+    uint32_t run;  // running minimum key of the open mixture
+    uint32_t sp;   // shared-memory address of this row's next staged q (the arg-min plane lies offB behind)
+};
+
+// One 32-column chunk (four 8-column segments) of a row's s32 accumulator.  SP as in the float kernel: > 0 when
+// every mixture of the column part spans exactly SP segments (closing positions become compile-time constants).
+template<int SP>
+__device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t xxBase,
+                                           uint32_t offB, QEpiState& st) {
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int seg = ch * 4 + s;
+        uint32_t  kc[8];
+        {
+            uint4 a, b;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w)
+                         : "r"(kcAddr + seg * 32));
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                         : "r"(kcAddr + seg * 32 + 16));
+            kc[0] = a.x, kc[1] = a.y, kc[2] = a.z, kc[3] = a.w, kc[4] = b.x, kc[5] = b.y, kc[6] = b.z, kc[7] = b.w;
+        }
+        uint32_t key[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            key[j] = kc[j] - (v[s * 8 + j] << 9);  // pads: Kc = 0xFFFFFFFF and dot = 0
+        const uint32_t m6 = __vimin3_u32(__vimin3_u32(key[0], key[1], key[2]), __vimin3_u32(key[3], key[4], key[5]),
+                                         min(key[6], key[7]));
+        bool     close;
+        uint32_t m;
+        if (SP > 0) {
+            m     = (seg % SP) == 0 ? m6 : min(m6, st.run);
+            close = (seg % SP) == SP - 1;
+        }
+        else {
+            m     = min(m6, st.run);
+            close = (segEnd >> seg) & 1u;
+        }
+        if (close) {  // uniform across the warp
+            const bool none = m == kNoKey;  // mixture without densities: the reference leaves INT_MAX / no density
+            sts_u32(st.sp, none ? 0x7FFFFFFFu : (m >> 8) + xxBase);
+            sts_u32(st.sp + offB, none ? 0xFFFFFFFFu : (m & 255u));
+            st.sp += 4;
+            m = kNoKey;
+        }
+        st.run = m;
+    }
+}
+
+// Persistent kernel: warp 0 bulk-copy producer (+ TMEM allocation), warp 1 MMA issuer, warps 2-9 epilogue (TMEM lane
+// quarter = warp & 3, column half = (warp - 2) / 4).  Barrier protocol as in gmm_tc.cu.
+__global__ void __launch_bounds__(32 * (kEpiWarp0 + kQEpiWarps), 1) qtc_score_kernel(const QKParams p) {
+    extern __shared__ uint8_t smemRaw[];
+    uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int NE = kQEpiWarps, PW = 1024 / NE, SEGS = PW / 8, SWZ = kQSwz;
+
+    // carve shared memory: [B buffers][A stages][staging: q plane, arg-min plane][barriers]
+    const uint32_t bBytes    = (p.bTileBytes + 1023u) & ~1023u;
+    uint8_t*       sB        = smem;
+    uint8_t*       sA        = sB + (size_t)p.buffersB * bBytes;
+    uint32_t*      sStage    = reinterpret_cast<uint32_t*>(sA + (size_t)p.stagesA * p.aTileBytes);
+    const uint32_t stageWarp = 32 * p.stagePitch;  // words per warp and plane
+    uint64_t*      bars      = reinterpret_cast<uint64_t*>(
+            (reinterpret_cast<uintptr_t>(sStage + 2 * NE * stageWarp) + 15) & ~(uintptr_t)15);
+    uint64_t* ready    = bars;              // [kRing] tile t may be issued (A landed, accumulator drained)
+    uint64_t* done     = bars + kRing;      // [kRing] the MMAs of tile t have retired
+    uint64_t* fullB    = bars + 2 * kRing;  // [2]
+    uint64_t* emptyB   = fullB + 2;         // [2]
+    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(emptyB + 2);
+
+    if (threadIdx.x == 32) {
+        for (int i = 0; i < kRing; ++i) {
+            mbar_init(smem_u32(&ready[i]), 1 + NE);
+            mbar_init(smem_u32(&done[i]), 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(smem_u32(&fullB[i]), 1);
+            mbar_init(smem_u32(&emptyB[i]), 1 + NE);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmemSlot)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmemBase = *tmemSlot;
+
+    const uint32_t items        = p.nTiles * p.split;
+    const uint32_t tilesPerItem = (p.frameTiles + p.split - 1) / p.split;
+
+    if (warp == 0) {
+        // ===== producer =====
+        if (lane == 0) {
+            uint32_t itemCount = 0, t = 0, stage = 0;
+            for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
+                const uint32_t nt = item / p.split, chunk = item % p.split;
+                const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+                if (f0 >= f1)
+                    continue;
+                const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+                mbar_wait(smem_u32(&emptyB[b]), (useB & 1) ^ 1);
+                mbar_expect_tx(smem_u32(&fullB[b]), p.bTileBytes);
+                bulk_g2s(smem_u32(sB + (size_t)b * bBytes), p.bTiles + (size_t)nt * p.bTileBytes, p.bTileBytes,
+                         smem_u32(&fullB[b]));
+                for (uint32_t f = f0; f < f1; ++f, ++t) {
+                    if (t >= p.stagesA) {
+                        const uint32_t u = t - p.stagesA;
+                        mbar_wait(smem_u32(&done[u % kRing]), (u / kRing) & 1);
+                    }
+                    const uint32_t rb = smem_u32(&ready[t % kRing]);
+                    mbar_expect_tx(rb, p.aTileBytes);
+                    bulk_g2s(smem_u32(sA + (size_t)stage * p.aTileBytes), p.aTiles + (size_t)f * p.aTileBytes,
+                             p.aTileBytes, rb);
+                    if (++stage == p.stagesA)
+                        stage = 0;
+                }
+            }
+        }
+    }
+    else if (warp == 1) {
+        // ===== MMA issuer (warp converged, one elected lane issues) =====
+        // instruction descriptor: D = s32, A = B = u8, K-major both, N = 256, M = 128
+        constexpr uint32_t idesc    = (2u << 4) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+        constexpr uint32_t kPerAtom = SWZ / 32;
+        constexpr uint32_t descHi   = (uint32_t)((8 * SWZ) >> 4) | (1u << 14) | (4u << 29);  // SBO, version, SWIZZLE_64B
+        const bool         leader   = elect_one();
+        const uint32_t     kS       = p.kSteps;
+        uint32_t           itemCount = 0, t = 0, stage = 0;
+        bool               have = false;
+        for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
+            const uint32_t chunk = item % p.split;
+            const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+            if (f0 >= f1)
+                continue;
+            const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+            mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            const uint32_t bLo = (smem_u32(sB + (size_t)b * bBytes) & 0x3FFFF) >> 4;
+            for (uint32_t f = f0; f < f1; ++f, ++t) {
+                if (!have)
+                    mbar_wait(smem_u32(&ready[t % kRing]), (t / kRing) & 1);
+                tc_fence_after();
+                const uint32_t aLo   = (smem_u32(sA + (size_t)stage * p.aTileBytes) & 0x3FFFF) >> 4;
+                const uint32_t dTmem = tmemBase + (t & 1) * kTileN;
+                if (leader) {
+                    for (uint32_t ks = 0; ks < kS; ++ks) {
+                        const uint32_t ao = aLo + (ks / kPerAtom) * (kTileM * SWZ / 16) + (ks % kPerAtom) * 2;
+                        const uint32_t bo = bLo + (ks / kPerAtom) * (kTileN * SWZ / 16) + (ks % kPerAtom) * 2;
+                        tc_mma_i8(dTmem, ((uint64_t)descHi << 32) | ao, ((uint64_t)descHi << 32) | bo, idesc, ks ? 1u : 0u);
+                    }
+                    tc_commit(smem_u32(&done[t % kRing]));
+                    if (f + 1 == f1)
+                        tc_commit(smem_u32(&emptyB[b]));
+                }
+                have = mbar_test(smem_u32(&ready[(t + 1) % kRing]), ((t + 1) / kRing) & 1);
+                __syncwarp();
+                if (++stage == p.stagesA)
+                    stage = 0;
+            }
+        }
+    }
+    else {
+        // ===== epilogue: TMEM -> registers -> packed-key min per mixture -> staged -> global =====
+        const int      e = warp - kEpiWarp0, qd = warp & 3, part = e >> 2;
+        const uint32_t stWarp = smem_u32(sStage) + (uint32_t)e * stageWarp * 4;
+        const uint32_t stRow  = stWarp + (uint32_t)lane * p.stagePitch * 4;
+        const uint32_t offB   = NE * stageWarp * 4;
+        uint32_t       itemCount = 0, t = 0;
+        if (lane == 0) {
+            mbar_arrive(smem_u32(&ready[0]));
+            mbar_arrive(smem_u32(&ready[1]));
+        }
+        for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
+            const uint32_t chunk = item % p.split;
+            const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+            if (f0 >= f1)
+                continue;
+            const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+            mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            const uint8_t*  tile = sB + (size_t)b * bBytes + (size_t)p.atoms * kTileN * SWZ;
+            const uint32_t  kcAddr = smem_u32(tile) + (uint32_t)part * PW * 4;  // Kc of this warp's columns
+            const uint32_t* meta = reinterpret_cast<const uint32_t*>(tile + kTileN * 4);  // TileMeta words
+            constexpr uint32_t segMask = (1u << SEGS) - 1u;
+            const uint32_t  segEnd  = (meta[0] >> (SEGS * part)) & segMask;
+            const uint32_t  mixBase = meta[2 + part];
+            const uint32_t  nMix    = __popc(segEnd);
+            const uint32_t  adv_r = 32 / max(nMix, 1u), adv_j = 32 - adv_r * nMix;
+            const uint32_t  lr0 = lane / max(nMix, 1u), lj0 = lane - lr0 * nMix;
+            const size_t    gStep = (size_t)adv_r * p.ld + adv_j, gStepW = gStep + p.ld - nMix;  // elements
+            const uint32_t  sStep = (adv_r * p.stagePitch + adv_j) * 4, sStepW = sStep + (p.stagePitch - nMix) * 4;
+            const uint32_t  ssLane = stWarp + (lr0 * p.stagePitch + lj0) * 4;
+            size_t          gTile = (size_t)(f0 * kTileM + qd * 32 + lr0) * p.ld + mixBase + lj0;
+            const size_t    gTileStep = (size_t)kTileM * p.ld;
+            const uint32_t* xxp = p.rowXX + (size_t)f0 * kTileM + qd * 32 + lane;
+            auto tiles = [&](auto spTag) {
+                constexpr int SP = decltype(spTag)::value;
+                for (uint32_t f = f0; f < f1; ++f, ++t) {
+                    const uint32_t acc    = t & 1;
+                    const uint32_t xxBase = *xxp + p.qBase;
+                    xxp += kTileM;
+                    mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
+                    tc_fence_after();
+                    const uint32_t taddr   = tmemBase + ((uint32_t)(qd * 32) << 16) + acc * kTileN + part * PW;
+                    const uint32_t drained = smem_u32(&ready[(t + 2) % kRing]);
+                    QEpiState st;
+                    st.run = kNoKey, st.sp = stRow;
+                    uint32_t va[32], vb[32];
+                    tmem_ld32(taddr, va);
+                    tmem_ld_wait();
+                    tmem_ld32(taddr + 32, vb);
+                    qepi_chunk<SP>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                    tmem_ld_wait();
+                    tmem_ld32(taddr + 64, va);
+                    qepi_chunk<SP>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
+                    tmem_ld_wait();
+                    tmem_ld32(taddr + 96, vb);
+                    qepi_chunk<SP>(va, 2, kcAddr, segEnd, xxBase, offB, st);
+                    tmem_ld_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(drained);
+                    qepi_chunk<SP>(vb, 3, kcAddr, segEnd, xxBase, offB, st);
+                    __syncwarp();
+                    // coalesced store of the staged [32 rows x nMix] blocks: nMix passes of 32 consecutive elements
+                    const uint32_t rbase = f * kTileM + qd * 32;
+                    const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
+                    size_t         g     = gTile;
+                    uint32_t       ss    = ssLane;
+                    gTile += gTileStep;
+                    uint32_t r = lr0, j = lj0;
+                    for (uint32_t i = 0; i < nMix; ++i) {
+                        if (r < rows) {
+                            const uint32_t qv = lds_u32(ss);
+                            if (p.q)
+                                p.q[g] = (int32_t)qv;
+                            if (p.best)
+                                p.best[g] = lds_u32(ss + offB);
+                            if (p.score)  // f32( 0.5 * q / scalingSquared ) in double, SimdFeatureScorer.cc:135-145
+                                p.score[g] = (float)(0.5 * (double)(int32_t)qv / p.scalingSquared);
+                        }
+                        const bool w = j + adv_j >= nMix;
+                        j            = w ? j + adv_j - nMix : j + adv_j;
+                        r += adv_r + (w ? 1u : 0u);
+                        g += w ? gStepW : gStep, ss += w ? sStepW : sStep;
+                    }
+                    __syncwarp();
+                }
+            };
+            const uint32_t uni = (meta[10] >> (8 * part)) & 0xFFu;  // TileMeta::uni
+            switch (uni) {
+                case 1: tiles(std::integral_constant<int, 1>{}); break;
+                case 2: tiles(std::integral_constant<int, 2>{}); break;
+                case 4: tiles(std::integral_constant<int, 4>{}); break;
+                case 8: tiles(std::integral_constant<int, 8>{}); break;
+                default: tiles(std::integral_constant<int, 0>{}); break;
+            }
+            if (lane == 0)
+                mbar_arrive(smem_u32(&emptyB[b]));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmemBase));
+    }
+}
+
+}  // namespace
+
+// ---- host side ----------------------------------------------------------------------------------------
+static uint32_t qSmemNeed(uint32_t bTileBytes, uint32_t aTileBytes, uint32_t buffersB, uint32_t stagesA,
+                          uint32_t pitch) {
+    const uint32_t bBytes = (bTileBytes + 1023u) & ~1023u;
+    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 2 * kQEpiWarps * 32 * pitch * 4 + 512;
+}
+
+// Packs the quantized model for the tensor kernel; leaves h->qtensor.valid false when the model does not meet the
+// requirements in the header comment (the dp4a kernel then serves it).  c2[g] = qconst[g] + |qmean_g|^2 (wrapping).
+int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, const int32_t* c2) {
+    QTensorModel&     tm = h->qtensor;
+    const QuantModel& qm = h->quant;
+    tm                   = QTensorModel();
+    const uint32_t M = qm.M, G = qm.G, Dpad = qm.Dpad;
+    const char*    env = getenv("GMM_QUANT_KERNEL");
+    if (G == 0 || M == 0 || qm.C != 1 || (env && !strcmp(env, "dp4a")))
+        return GMM_OK;
+    tm.kSteps     = (Dpad + 31) / 32;
+    tm.nAtoms     = (tm.kSteps * 32 + kQSwz - 1) / kQSwz;
+    tm.aTileBytes = tm.nAtoms * kTileM * kQSwz;
+    tm.tileBytes  = tm.nAtoms * kTileN * kQSwz + kQMetaBytes;
+    // value ranges: everything must stay far from 32-bit wrap-around and the key must fit 24 + 8 bits
+    const int64_t dmax = (int64_t)tm.kSteps * 32 * 255 * 255;
+    int64_t       cmin = INT64_MAX, cmax = INT64_MIN;
+    for (uint32_t g = 0; g < G; ++g) {
+        cmin = std::min<int64_t>(cmin, c2[g]);
+        cmax = std::max<int64_t>(cmax, c2[g]);
+    }
+    if (cmin < -(1ll << 30) || cmax > (1ll << 30) || (cmax - cmin) + 2 * dmax >= (1ll << 24) - 1)
+        return GMM_OK;
+
+    // ---- column assignment: densities of a mixture consecutive, padded to 8, never straddling a 128-column half
+    struct Col {
+        uint32_t g;  // density, or 0xFFFFFFFF for a pad / filler column
+        uint32_t slot;
+    };
+    const uint32_t        partW = 128, partsPerTile = kTileN / partW;
+    std::vector<Col>      cols;
+    std::vector<TileMeta> metas;
+    std::vector<uint32_t> mixPerPart;
+    auto ensurePart = [&](uint32_t pt) {
+        while (metas.size() * partsPerTile <= pt) {
+            TileMeta z = {0, 0, {0, 0, 0, 0}, {0, 0, 0, 0}, 0};
+            metas.push_back(z);
+        }
+        while (mixPerPart.size() <= pt)
+            mixPerPart.push_back(0);
+    };
+    const Col pad = {0xFFFFFFFFu, 0};
+    for (uint32_t m = 0; m < M; ++m) {
+        const uint32_t n      = offsets[m + 1] - offsets[m];
+        const uint32_t padded = std::max<uint32_t>(8, (n + 7) / 8 * 8);
+        if (padded > partW)
+            return GMM_OK;  // slot would not fit 8 bits of the key / the column part
+        const uint32_t inPart = (uint32_t)(cols.size() % partW);
+        if (inPart + padded > partW)
+            cols.insert(cols.end(), partW - inPart, pad);
+        const uint32_t pt = (uint32_t)(cols.size() / partW);
+        ensurePart(pt);
+        TileMeta& mt = metas[pt / partsPerTile];
+        if (mixPerPart[pt] == 0)
+            mt.mixBase[pt % partsPerTile] = m;
+        mixPerPart[pt]++;
+        const uint32_t seg0 = (uint32_t)((cols.size() % kTileN) / 8);
+        for (uint32_t i = 0; i < padded; ++i) {
+            Col c = pad;
+            if (i < n) {
+                c.g    = offsets[m] + i;
+                c.slot = i;
+            }
+            cols.push_back(c);
+        }
+        mt.segEnd |= 1u << (seg0 + padded / 8 - 1);
+    }
+    while (cols.size() % kTileN)
+        cols.push_back(pad);
+    tm.nTiles = (uint32_t)(cols.size() / kTileN);
+    ensurePart(tm.nTiles * partsPerTile - 1);
+    for (TileMeta& mt : metas) {
+        const uint32_t segsPerPart = partW / 8;
+        for (uint32_t pp = 0; pp < partsPerTile; ++pp) {
+            const uint32_t mask = (1u << segsPerPart) - 1u;
+            const uint32_t ends = (mt.segEnd >> (pp * segsPerPart)) & mask;
+            for (uint32_t S = 1; S <= 8; S *= 2) {
+                uint32_t pat = 0;
+                for (uint32_t b = S - 1; b < segsPerPart; b += S)
+                    pat |= 1u << b;
+                if (ends == pat)
+                    mt.uni |= S << (8 * pp);
+            }
+        }
+    }
+    tm.maxMixPerPart = 1;
+    for (uint32_t v : mixPerPart)
+        tm.maxMixPerPart = std::max(tm.maxMixPerPart, v);
+
+    // ---- shared-memory configuration ----
+    const uint32_t pitch = tm.maxMixPerPart + 1;
+    for (uint32_t nb = 2; nb >= 1 && !tm.buffersB; --nb)
+        for (uint32_t sa = kMaxStagesA; sa >= 2; --sa)
+            if (qSmemNeed(tm.tileBytes, tm.aTileBytes, nb, sa, pitch) <= kSmemLimit) {
+                tm.buffersB = nb;
+                tm.stagesA  = sa;
+                break;
+            }
+    if (!tm.buffersB)
+        return GMM_OK;
+
+    // ---- tile images ----
+    std::vector<uint8_t> img((size_t)tm.nTiles * tm.tileBytes, 0);
+    for (uint32_t t = 0; t < tm.nTiles; ++t) {
+        uint8_t*  base = img.data() + (size_t)t * tm.tileBytes;
+        uint32_t* kc   = reinterpret_cast<uint32_t*>(base + (size_t)tm.nAtoms * kTileN * kQSwz);
+        TileMeta* mOut = reinterpret_cast<TileMeta*>(reinterpret_cast<uint8_t*>(kc) + kTileN * 4);
+        *mOut          = metas[t];
+        for (uint32_t r = 0; r < (uint32_t)kTileN; ++r) {
+            const Col& col = cols[(size_t)t * kTileN + r];
+            if (col.g == 0xFFFFFFFFu) {
+                kc[r] = kNoKey;  // zero operand row: dot = 0, key stays 0xFFFFFFFF
+                continue;
+            }
+            kc[r] = (uint32_t)((((int64_t)c2[col.g] - cmin + 2 * dmax) << 8) | col.slot);
+            const uint8_t* mu = qmean + (size_t)col.g * Dpad;
+            for (uint32_t d = 0; d < Dpad; ++d)
+                base[(size_t)(d / kQSwz) * kTileN * kQSwz + swz_offset(r, (d % kQSwz) / 16, kQSwz) + (d % 16)] = mu[d];
+        }
+    }
+    tm.qBase = (uint32_t)(cmin - 2 * dmax);
+    int rc;
+    if ((rc = h->upload((void**)&tm.bTiles, img.data(), img.size(), true)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    tm.valid = true;
+    return GMM_OK;
+}
+
+int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
+                  uint8_t* d_qx, size_t ld) {
+    const QTensorModel& tm = h->qtensor;
+    const QuantModel&   qm = h->quant;
+    if (T == 0)
+        return GMM_OK;
+    const uint32_t FT = (T + kTileM - 1) / kTileM;
+    void *         aT = nullptr, *rT = nullptr;
+    int            rc;
+    if ((rc = h->reserve(SCR_A, (size_t)FT * tm.aTileBytes, &aT)))
+        return rc;
+    if ((rc = h->reserve(SCR_ROW, (size_t)FT * kTileM * 4, &rT)))
+        return rc;
+    {
+        const int blocks = (int)std::min<uint32_t>((FT * kTileM + 31) / 32, (uint32_t)h->smCount * 16);
+        qtc_prep_kernel<<<blocks, 256, 0, h->stream>>>(d_x, T, qm.D, qm.Dpad, FT, qm.isrS, tm.nAtoms, (uint8_t*)aT,
+                                                       (uint32_t*)rT, d_qx);
+        h->launches++;
+        GMM_CUDA_TRY(h, cudaGetLastError());
+    }
+    QKParams p;
+    p.bTiles         = tm.bTiles;
+    p.aTiles         = (const uint8_t*)aT;
+    p.rowXX          = (const uint32_t*)rT;
+    p.q              = d_q;
+    p.best           = d_best;
+    p.score          = d_score;
+    p.ld             = ld;
+    p.scalingSquared = (double)qm.scalingSquared;
+    p.T              = T;
+    p.nTiles         = tm.nTiles;
+    p.frameTiles     = FT;
+    p.kSteps         = tm.kSteps;
+    p.atoms          = tm.nAtoms;
+    p.aTileBytes     = tm.aTileBytes;
+    p.bTileBytes     = tm.tileBytes;
+    p.stagesA        = tm.stagesA;
+    p.buffersB       = tm.buffersB;
+    p.stagePitch     = tm.maxMixPerPart + 1;
+    p.qBase          = tm.qBase;
+    const size_t smemBytes = qSmemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, tm.stagesA, p.stagePitch);
+    // frame range split so that the items fill the SMs evenly (round-robin items keep adjacent B tiles together in
+    // time, see gmm_tc.cu)
+    const double bCost = tm.buffersB == 2 ? 0.5 : 2.0;
+    uint32_t     bestS = 1;
+    double       bestCost = 1e300;
+    for (uint32_t S = 1; S <= std::min<uint32_t>(FT, 64); ++S) {
+        const uint32_t per = (FT + S - 1) / S;
+        if ((uint64_t)per * (S - 1) >= FT)
+            continue;
+        const uint64_t items  = (uint64_t)tm.nTiles * S;
+        const uint64_t rounds = (items + h->smCount - 1) / h->smCount;
+        const double   cost   = (double)rounds * (per + bCost);
+        if (cost < bestCost - 1e-9) {
+            bestCost = cost;
+            bestS    = S;
+        }
+    }
+    p.split        = bestS;
+    const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
+    cudaError_t e  = cudaFuncSetAttribute(qtc_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    GMM_CUDA_TRY(h, e);
+    h->timeBegin();
+    qtc_score_kernel<<<grid, 32 * (kEpiWarp0 + kQEpiWarps), smemBytes, h->stream>>>(p);
+    h->timeEnd();
+    h->launches++;
+    GMM_CUDA_TRY(h, cudaGetLastError());
+    return GMM_OK;
+}

@@ -187,6 +187,8 @@ int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, 
     const QuantModel& qm = h->quant;
     if (T == 0)
         return GMM_OK;
+    if (h->qtensor.valid)  // integer tensor path (gmm_qtc.cu); this file's dp4a kernel serves every other model
+        return gmm_qtc_score(h, T, d_x, d_q, d_best, d_score, d_qx, ld);
     // frames are processed in chunks so that the per-covariance quantized copies stay bounded
     const size_t perFrame = (size_t)qm.C * qm.Dpad;
     uint32_t     chunk    = T;

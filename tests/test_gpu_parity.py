@@ -114,6 +114,27 @@ MODELS = [
 ]
 
 
+@pytest.mark.parametrize("kernel", ["auto", "dp4a"])
+@pytest.mark.parametrize("T", [1, 130, 700])
+def test_quantized_kernels_agree_with_oracle(eng, oracle, kernel, T, monkeypatch):
+    """Pooled-covariance model: the integer tensor path (auto) and the forced dp4a kernel are both bit-exact."""
+    if kernel == "dp4a":
+        monkeypatch.setenv("GMM_QUANT_KERNEL", "dp4a")
+    ms = synth.make_model(M=300, K=16, D=45, ragged=True, seed=11)
+    x = synth.make_features(ms, T)
+    x[-1] *= -40.0
+    t, raw = oracle_quant_tables(ms)
+    upload_quant(eng, t)
+    assert eng.quant_kernel == (1 if kernel == "dp4a" else 2)
+    r = eng.quant_score_host(x, want_qx=True)
+    qx = oracle.simd_quantize_features(x, raw["isrs"])
+    q, b = oracle.simd_score(ms.mix_offsets, raw, qx)
+    assert np.array_equal(r["qx"], qx)
+    assert np.array_equal(r["q"], q)
+    assert np.array_equal(r["best"], b)
+    assert np.array_equal(bits(r["score"]), bits(oracle.simd_final_score(q, raw["scaling_squared"])))
+
+
 @pytest.mark.parametrize("kw", MODELS)
 @pytest.mark.parametrize("T", [1, 33, 300])
 def test_quantized_bit_exact_vs_oracle(eng, oracle, kw, T):
