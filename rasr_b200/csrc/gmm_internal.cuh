@@ -68,6 +68,7 @@ struct QTensorModel {
     uint32_t  tileBytes  = 0;       // bytes per B tile image (operand rows, Kc table, TileMeta)
     uint32_t  aTileBytes = 0;
     uint8_t*  bTiles     = nullptr;
+    uint32_t  partW      = 128;     // packed columns reduced by one epilogue warp (64: 16 warps)
     uint32_t  maxMixPerPart = 0;
     uint32_t  buffersB   = 0, stagesA = 0;
     uint32_t  qBase      = 0;       // min c2 - 2 Dmax (wrapping)

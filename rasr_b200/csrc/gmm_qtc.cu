@@ -35,7 +35,6 @@
 namespace {
 
 constexpr int      kQSwz       = 64;                   // swizzle atom: 64-byte rows hold two 32-byte k-steps
-constexpr int      kQEpiWarps  = 8;
 constexpr int      kQMetaBytes = kTileN * 4 + 48;      // Kc[256] u32, TileMeta
 constexpr uint32_t kNoKey      = 0xFFFFFFFFu;          // pad / filler column: never the minimum
 
@@ -129,24 +128,20 @@ struct QEpiState {
 template<int SP>
 __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t xxBase,
                                            uint32_t offB, QEpiState& st) {
+    // the chunk's 32 per-column constants first (eight 128-bit loads in flight together), then the arithmetic
+    uint32_t kc[32];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(kc[4 * i]), "=r"(kc[4 * i + 1]), "=r"(kc[4 * i + 2]), "=r"(kc[4 * i + 3])
+                     : "r"(kcAddr + ch * 128 + i * 16));
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
         const int seg = ch * 4 + s;
-        uint32_t  kc[8];
-        {
-            uint4 a, b;
-            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w)
-                         : "r"(kcAddr + seg * 32));
-            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-                         : "r"(kcAddr + seg * 32 + 16));
-            kc[0] = a.x, kc[1] = a.y, kc[2] = a.z, kc[3] = a.w, kc[4] = b.x, kc[5] = b.y, kc[6] = b.z, kc[7] = b.w;
-        }
-        uint32_t key[8];
+        uint32_t  key[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-            key[j] = kc[j] - (v[s * 8 + j] << 9);  // pads: Kc = 0xFFFFFFFF and dot = 0
+            key[j] = kc[s * 8 + j] - (v[s * 8 + j] << 9);  // pads: Kc = 0xFFFFFFFF and dot = 0
         const uint32_t m6 = __vimin3_u32(__vimin3_u32(key[0], key[1], key[2]), __vimin3_u32(key[3], key[4], key[5]),
                                          min(key[6], key[7]));
         bool     close;
@@ -170,13 +165,15 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
     }
 }
 
-// Persistent kernel: warp 0 bulk-copy producer (+ TMEM allocation), warp 1 MMA issuer, warps 2-9 epilogue (TMEM lane
-// quarter = warp & 3, column half = (warp - 2) / 4).  Barrier protocol as in gmm_tc.cu.
-__global__ void __launch_bounds__(32 * (kEpiWarp0 + kQEpiWarps), 1) qtc_score_kernel(const QKParams p) {
+// Persistent kernel: warp 0 bulk-copy producer (+ TMEM allocation), warp 1 MMA issuer, NE = 8 or 16 epilogue warps
+// (TMEM lane quarter = warp & 3, column part of 1024 / NE columns = (warp - 2) / 4; 16 warps when no mixture has more
+// than 64 densities: the epilogue, not the two MMAs per tile, bounds this kernel).  Barrier protocol as in gmm_tc.cu.
+template<int NE>
+__global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(const QKParams p) {
     extern __shared__ uint8_t smemRaw[];
     uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    constexpr int NE = kQEpiWarps, PW = 1024 / NE, SEGS = PW / 8, SWZ = kQSwz;
+    constexpr int PW = 1024 / NE, SEGS = PW / 8, SWZ = kQSwz;
 
     // carve shared memory: [B buffers][A stages][staging: q plane, arg-min plane][barriers]
     const uint32_t bBytes    = (p.bTileBytes + 1023u) & ~1023u;
@@ -291,6 +288,10 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + kQEpiWarps), 1) qtc_score_ke
         const uint32_t stWarp = smem_u32(sStage) + (uint32_t)e * stageWarp * 4;
         const uint32_t stRow  = stWarp + (uint32_t)lane * p.stagePitch * 4;
         const uint32_t offB   = NE * stageWarp * 4;
+        // the three outputs share one indexing: address everything relative to a base array that is present
+        char* const     gBase = reinterpret_cast<char*>(p.q ? (void*)p.q : p.best ? (void*)p.best : (void*)p.score);
+        const ptrdiff_t bestDelta  = p.best ? reinterpret_cast<char*>(p.best) - gBase : 0;
+        const ptrdiff_t scoreDelta = p.score ? reinterpret_cast<char*>(p.score) - gBase : 0;
         uint32_t       itemCount = 0, t = 0;
         if (lane == 0) {
             mbar_arrive(smem_u32(&ready[0]));
@@ -312,63 +313,94 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + kQEpiWarps), 1) qtc_score_ke
             const uint32_t  nMix    = __popc(segEnd);
             const uint32_t  adv_r = 32 / max(nMix, 1u), adv_j = 32 - adv_r * nMix;
             const uint32_t  lr0 = lane / max(nMix, 1u), lj0 = lane - lr0 * nMix;
-            const size_t    gStep = (size_t)adv_r * p.ld + adv_j, gStepW = gStep + p.ld - nMix;  // elements
+            const size_t    gStep = ((size_t)adv_r * p.ld + adv_j) * 4, gStepW = gStep + (p.ld - nMix) * 4;  // bytes
             const uint32_t  sStep = (adv_r * p.stagePitch + adv_j) * 4, sStepW = sStep + (p.stagePitch - nMix) * 4;
             const uint32_t  ssLane = stWarp + (lr0 * p.stagePitch + lj0) * 4;
-            size_t          gTile = (size_t)(f0 * kTileM + qd * 32 + lr0) * p.ld + mixBase + lj0;
-            const size_t    gTileStep = (size_t)kTileM * p.ld;
+            size_t          gTile = ((size_t)(f0 * kTileM + qd * 32 + lr0) * p.ld + mixBase + lj0) * 4;
+            const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
             const uint32_t* xxp = p.rowXX + (size_t)f0 * kTileM + qd * 32 + lane;
             auto tiles = [&](auto spTag) {
                 constexpr int SP = decltype(spTag)::value;
+                uint32_t xxNext = *xxp;  // |qx|^2 of the next tile's row, fetched one tile ahead
                 for (uint32_t f = f0; f < f1; ++f, ++t) {
                     const uint32_t acc    = t & 1;
-                    const uint32_t xxBase = *xxp + p.qBase;
+                    const uint32_t xxBase = xxNext + p.qBase;
                     xxp += kTileM;
+                    if (f + 1 < f1)
+                        xxNext = *xxp;
                     mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
                     tc_fence_after();
                     const uint32_t taddr   = tmemBase + ((uint32_t)(qd * 32) << 16) + acc * kTileN + part * PW;
                     const uint32_t drained = smem_u32(&ready[(t + 2) % kRing]);
                     QEpiState st;
                     st.run = kNoKey, st.sp = stRow;
-                    uint32_t va[32], vb[32];
-                    tmem_ld32(taddr, va);
-                    tmem_ld_wait();
-                    tmem_ld32(taddr + 32, vb);
-                    qepi_chunk<SP>(va, 0, kcAddr, segEnd, xxBase, offB, st);
-                    tmem_ld_wait();
-                    tmem_ld32(taddr + 64, va);
-                    qepi_chunk<SP>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
-                    tmem_ld_wait();
-                    tmem_ld32(taddr + 96, vb);
-                    qepi_chunk<SP>(va, 2, kcAddr, segEnd, xxBase, offB, st);
-                    tmem_ld_wait();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive(drained);
-                    qepi_chunk<SP>(vb, 3, kcAddr, segEnd, xxBase, offB, st);
+                    uint32_t va[32];
+                    if (NE == 16) {
+                        // 96 registers per thread: one 32-column chunk (+ its 32 constants) live at a time
+                        tmem_ld32(taddr, va);
+                        tmem_ld_wait();
+                        qepi_chunk<SP>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                        tmem_ld32(taddr + 32, va);
+                        tmem_ld_wait();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(drained);
+                        qepi_chunk<SP>(va, 1, kcAddr, segEnd, xxBase, offB, st);
+                    }
+                    else {
+                        uint32_t vb[32];
+                        tmem_ld32(taddr, va);
+                        tmem_ld_wait();
+                        tmem_ld32(taddr + 32, vb);
+                        qepi_chunk<SP>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                        tmem_ld_wait();
+                        tmem_ld32(taddr + 64, va);
+                        qepi_chunk<SP>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
+                        tmem_ld_wait();
+                        tmem_ld32(taddr + 96, vb);
+                        qepi_chunk<SP>(va, 2, kcAddr, segEnd, xxBase, offB, st);
+                        tmem_ld_wait();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(drained);
+                        qepi_chunk<SP>(vb, 3, kcAddr, segEnd, xxBase, offB, st);
+                    }
                     __syncwarp();
                     // coalesced store of the staged [32 rows x nMix] blocks: nMix passes of 32 consecutive elements
                     const uint32_t rbase = f * kTileM + qd * 32;
                     const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
-                    size_t         g     = gTile;
+                    char*          g     = gBase + gTile;  // byte address of this lane's first element in q[]
                     uint32_t       ss    = ssLane;
                     gTile += gTileStep;
-                    uint32_t r = lr0, j = lj0;
-                    for (uint32_t i = 0; i < nMix; ++i) {
+                    auto put = [&](uint32_t r) {
                         if (r < rows) {
                             const uint32_t qv = lds_u32(ss);
                             if (p.q)
-                                p.q[g] = (int32_t)qv;
+                                *reinterpret_cast<uint32_t*>(g) = qv;
                             if (p.best)
-                                p.best[g] = lds_u32(ss + offB);
+                                *reinterpret_cast<uint32_t*>(g + bestDelta) = lds_u32(ss + offB);
                             if (p.score)  // f32( 0.5 * q / scalingSquared ) in double, SimdFeatureScorer.cc:135-145
-                                p.score[g] = (float)(0.5 * (double)(int32_t)qv / p.scalingSquared);
+                                *reinterpret_cast<float*>(g + scoreDelta) = (float)(0.5 * (double)(int32_t)qv / p.scalingSquared);
                         }
-                        const bool w = j + adv_j >= nMix;
-                        j            = w ? j + adv_j - nMix : j + adv_j;
-                        r += adv_r + (w ? 1u : 0u);
-                        g += w ? gStepW : gStep, ss += w ? sStepW : sStep;
+                    };
+                    if (adv_j == 0) {  // nMix divides 32: a lane keeps its column
+#pragma unroll 4
+                        for (uint32_t i = 0, r = lr0; i < nMix; ++i, r += adv_r) {
+                            put(r);
+                            g += gStep, ss += sStep;
+                        }
+                    }
+                    else {
+                        uint32_t r = lr0, j = lj0;
+                        for (uint32_t i = 0; i < nMix; ++i) {
+                            put(r);
+                            const bool w = j + adv_j >= nMix;
+                            j            = w ? j + adv_j - nMix : j + adv_j;
+                            r += adv_r + (w ? 1u : 0u);
+                            g += w ? gStepW : gStep, ss += w ? sStepW : sStep;
+                        }
                     }
                     __syncwarp();
                 }
@@ -378,7 +410,7 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + kQEpiWarps), 1) qtc_score_ke
                 case 1: tiles(std::integral_constant<int, 1>{}); break;
                 case 2: tiles(std::integral_constant<int, 2>{}); break;
                 case 4: tiles(std::integral_constant<int, 4>{}); break;
-                case 8: tiles(std::integral_constant<int, 8>{}); break;
+                case 8: tiles(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
                 default: tiles(std::integral_constant<int, 0>{}); break;
             }
             if (lane == 0)
@@ -398,9 +430,9 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + kQEpiWarps), 1) qtc_score_ke
 
 // ---- host side ----------------------------------------------------------------------------------------
 static uint32_t qSmemNeed(uint32_t bTileBytes, uint32_t aTileBytes, uint32_t buffersB, uint32_t stagesA,
-                          uint32_t pitch) {
+                          uint32_t pitch, uint32_t epiWarps) {
     const uint32_t bBytes = (bTileBytes + 1023u) & ~1023u;
-    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 2 * kQEpiWarps * 32 * pitch * 4 + 512;
+    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 2 * epiWarps * 32 * pitch * 4 + 512;
 }
 
 // Packs the quantized model for the tensor kernel; leaves h->qtensor.valid false when the model does not meet the
@@ -432,7 +464,14 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
         uint32_t g;  // density, or 0xFFFFFFFF for a pad / filler column
         uint32_t slot;
     };
-    const uint32_t        partW = 128, partsPerTile = kTileN / partW;
+    uint32_t maxN = 0;
+    for (uint32_t m = 0; m < M; ++m)
+        maxN = std::max(maxN, offsets[m + 1] - offsets[m]);
+    const char* envW = getenv("GMM_QTC_EPI_WARPS");
+    // 8 epilogue warps (128-column parts) by default: the 16-warp variant is faster on small batches (48 vs 41 M
+    // frames/s at 8000 frames, 4501x16) but its 16-byte output pieces collapse on large ones (20 vs 38 M at 64000)
+    tm.partW         = (maxN <= 64 && envW && atoi(envW) == 16) ? 64 : 128;
+    const uint32_t        partW = tm.partW, partsPerTile = kTileN / partW;
     std::vector<Col>      cols;
     std::vector<TileMeta> metas;
     std::vector<uint32_t> mixPerPart;
@@ -479,7 +518,7 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
         for (uint32_t pp = 0; pp < partsPerTile; ++pp) {
             const uint32_t mask = (1u << segsPerPart) - 1u;
             const uint32_t ends = (mt.segEnd >> (pp * segsPerPart)) & mask;
-            for (uint32_t S = 1; S <= 8; S *= 2) {
+            for (uint32_t S = 1; S <= 8 && S <= segsPerPart; S *= 2) {
                 uint32_t pat = 0;
                 for (uint32_t b = S - 1; b < segsPerPart; b += S)
                     pat |= 1u << b;
@@ -493,10 +532,10 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
         tm.maxMixPerPart = std::max(tm.maxMixPerPart, v);
 
     // ---- shared-memory configuration ----
-    const uint32_t pitch = tm.maxMixPerPart + 1;
+    const uint32_t pitch = tm.maxMixPerPart + 1, epiWarps = 4 * partsPerTile;
     for (uint32_t nb = 2; nb >= 1 && !tm.buffersB; --nb)
         for (uint32_t sa = kMaxStagesA; sa >= 2; --sa)
-            if (qSmemNeed(tm.tileBytes, tm.aTileBytes, nb, sa, pitch) <= kSmemLimit) {
+            if (qSmemNeed(tm.tileBytes, tm.aTileBytes, nb, sa, pitch, epiWarps) <= kSmemLimit) {
                 tm.buffersB = nb;
                 tm.stagesA  = sa;
                 break;
@@ -572,7 +611,8 @@ int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uin
     p.buffersB       = tm.buffersB;
     p.stagePitch     = tm.maxMixPerPart + 1;
     p.qBase          = tm.qBase;
-    const size_t smemBytes = qSmemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, tm.stagesA, p.stagePitch);
+    const uint32_t epiWarps = 4 * (kTileN / tm.partW);
+    const size_t   smemBytes = qSmemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, tm.stagesA, p.stagePitch, epiWarps);
     // frame range split so that the items fill the SMs evenly (round-robin items keep adjacent B tiles together in
     // time, see gmm_tc.cu)
     const double bCost = tm.buffersB == 2 ? 0.5 : 2.0;
@@ -592,10 +632,11 @@ int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uin
     }
     p.split        = bestS;
     const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
-    cudaError_t e  = cudaFuncSetAttribute(qtc_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    void (*kernel)(const QKParams) = epiWarps == 16 ? qtc_score_kernel<16> : qtc_score_kernel<8>;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     GMM_CUDA_TRY(h, e);
     h->timeBegin();
-    qtc_score_kernel<<<grid, 32 * (kEpiWarp0 + kQEpiWarps), smemBytes, h->stream>>>(p);
+    kernel<<<grid, 32 * (kEpiWarp0 + epiWarps), smemBytes, h->stream>>>(p);
     h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());

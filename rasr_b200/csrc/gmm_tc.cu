@@ -340,11 +340,13 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             // the tile loop, specialised on the tile's mixture shape when it is uniform (see epi_chunk)
             auto tiles = [&](auto spTag) {
                 constexpr int SP = decltype(spTag)::value;
+                float2 riNext = *rip;  // row term / scale of the next tile's row, fetched one tile ahead
                 for (uint32_t f = f0; f < f1; ++f, ++t) {
                     const uint32_t acc = t & 1;
-                    const float2   ri  = *rip;
-                    const float    rt = ri.x, rs = ri.y;
+                    const float    rt = riNext.x, rs = riNext.y;
                     rip += kTileM;
+                    if (f + 1 < f1)
+                        riNext = *rip;
                     mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
                     tc_fence_after();
                     const uint32_t taddr    = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + part * PW;
