@@ -19,14 +19,16 @@
 //   B tile  = 256 packed columns (Gaussians):  [atoms][256 rows][SWZ bytes] | slot[256] u16 | TileMeta
 //   A tile  = 128 frames:                       [atoms][128 rows][SWZ bytes]
 // Packed columns: the live densities of a mixture are consecutive, padded to a multiple of 8 columns (a pad
-// repeats the mixture's first live column); a mixture never straddles a 128-column half tile.  TileMeta: bit s
-// of segEnd says "8-column segment s closes a mixture", plus live-column counts and the first mixture per half.
+// repeats the mixture's first live column); a mixture never straddles a column part (the 128 or 64 columns one
+// epilogue warp reduces).  TileMeta: bit s of segEnd says "8-column segment s closes a mixture", plus live-column
+// counts, the first mixture per part and the uniform-shape flags the epilogue specialises on.
 //
-// Kernel: persistent, one CTA per SM, 12 warps: warp 0 bulk-copy producer, warp 1 MMA issuer (one elected
-// thread, M=128 N=256 K=16 per instruction), warp 2 TMEM allocator, warps 4-11 epilogue (TMEM lane quarter =
-// warp % 4, column half = (warp-4)/4).  Work item = (B tile, range of frame tiles); B stays in shared memory for
-// the whole item while A tiles stream through a ring; two 256-column accumulators in TMEM double-buffer MMA
-// against the epilogue.
+// Kernel: persistent, one CTA per SM.  Warp 0: bulk-copy producer (one lane) and TMEM allocation; warp 1: MMA
+// issuer (warp converged, one elected lane, M=128 N=256 K=16 per instruction, descriptors in uniform registers);
+// then 8 or 16 epilogue warps (TMEM lane quarter = warp % 4, column part = (warp - 2) / 4).  Work item = (B tile,
+// range of frame tiles); B stays in shared memory for the whole item while A tiles stream through a ring; two
+// 256-column accumulators in TMEM double-buffer MMA against the epilogue.  Synchronisation: tile-indexed mbarrier
+// rings ready[] / done[] (see tc_score_body).  DESIGN.md 4.1 lists the measurements behind these choices.
 #include <cuda_fp16.h>
 #include <float.h>
 #include <math.h>
