@@ -96,6 +96,31 @@ int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, 
 int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,
                            float* d_score, uint8_t* d_qx, size_t ld);
 
+/* ---- device-resident consumer: Viterbi alignment over the score block ------------------
+ * Replaces, for unpruned Viterbi alignment, Search::Aligner::SearchSpace::{addStartupHypothesis, expand,
+ * activateOrUpdateStateHypothesisViterbi, getAlignmentFsaViterbi} (src/Search/Aligner.cc:132-158,190-239,398-437):
+ * only the best path leaves the GPU (4 bytes per frame instead of 4*M).
+ * nSeg independent segments; segment i owns rows [frameOffsets[i], frameOffsets[i+1]) of the score block and the
+ * automaton states [stateOffsets[i], stateOffsets[i+1]).  Automata are given like Fsa states: arcs of (global)
+ * state s are arcOffsets[s] .. arcOffsets[s+1], each with a SEGMENT-LOCAL target state, an emission index (column
+ * of the score block; RASR: acousticModel->emissionIndex(arc.input)) and a transition weight; every arc consumes one
+ * frame.  initialState[i] is segment-local; finalWeight[s] = +inf marks a non-final state.  All automaton and
+ * output arrays are HOST memory.  Outputs: pathEmission[t] (emission index of frame t on the best path, 0xFFFFFFFF
+ * for a segment that cannot reach a final state), pathState[t] (state entered at frame t; may be NULL),
+ * pathScore[i] (best final score, FLT_MAX if none).  The call returns after the outputs are valid. */
+int gmm_align_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
+                     const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                     const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore);
+/* Segments (since gmm_create) whose alignment met an exact f32 tie and was therefore replayed in the reference's
+ * hypothesis order by the ordered pass (see gmm_align.cu); all other segments have a unique best path. */
+uint64_t gmm_align_ordered_count(const gmm_handle* h);
+/* Features (host, [frameOffsets[nSeg] x D]) -> float scorer of this handle -> alignment, scores stay in HBM. */
+int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                         const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                         const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                         const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore);
+
 /* ---- plumbing -------------------------------------------------------------------------------- */
 /* Page-locked host buffers for the feature / score blocks (cudaMallocHost); NULL on failure. */
 void* gmm_host_alloc(size_t bytes);

@@ -10,6 +10,9 @@
  * tests/test_oracle_vs_ref.py compares every function below with it, and tests/golden/ holds outputs
  * of that binary (generator: tests/golden/make_golden.py).
  *
+ * Exception: orc_viterbi_align (the alignment consumer, end of file) is PARITY UNPINNED -- the
+ * reference's Search::Aligner cannot be compiled here; see the note above that function.
+ *
  * Compile WITHOUT -ffast-math: every operation is written in the order the reference binary executes
  * it (its -ffast-math build was inspected by disassembly where the source leaves the order open).
  *
@@ -320,4 +323,99 @@ void orc_simd_score(uint32_t M, const uint32_t* mixOffsets, uint32_t Dpad, uint3
 void orc_simd_final_score(const int32_t* q, size_t n, float scalingSquared, float* score) {
     for (size_t i = 0; i < n; ++i)
         score[i] = (float)(0.5 * q[i] / (double)scalingSquared);
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Viterbi alignment over a score block (the consumer of the scores)
+ *
+ * PARITY UNPINNED for this function: Search::Aligner needs the reference's Fsa, Am, Core and Speech
+ * libraries (their own build system, libxml2, generated code), which cannot be compiled here, and the
+ * reference holds no golden alignment.  The restatement follows the source line by line instead.
+ * Paths relative to /root/reference/src/Search.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    uint32_t state;
+    float    score;
+    uint32_t trace;    /* index of the predecessor hypothesis */
+    uint32_t emission; /* Aligner.cc:205 stores the arc label; the emission index stands in for it here */
+} orc_state_hyp;
+
+/* One segment.  Automaton as in include/gmm_b200.h: arcs of state s are arcOffsets[s]..arcOffsets[s+1] in Fsa
+ * order, finalWeight[s] = +inf marks a non-final state.  Returns the best final score (FLT_MAX and a path of
+ * 0xFFFFFFFF when no final state is reached, Aligner.cc:417-420). */
+float orc_viterbi_align(uint32_t T, const float* scores, size_t ld, uint32_t S, const uint32_t* arcOffsets,
+                        const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
+                        uint32_t initial, const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState) {
+    size_t         cap = 1024, n = 0;
+    orc_state_hyp* hyp = (orc_state_hyp*)malloc(cap * sizeof(orc_state_hyp));
+    size_t*        hypForState = (size_t*)calloc(S ? S : 1, sizeof(size_t));
+    /* Aligner.cc:176-181 addStartupHypothesis: score 0 at the initial state */
+    hyp[n++]             = (orc_state_hyp){initial, 0.0f, 0xFFFFFFFFu, 0xFFFFFFFFu};
+    hypForState[initial] = 0;
+    size_t firstCur      = 0;
+    for (uint32_t t = 0; t < T; ++t) {
+        /* Aligner.cc:190-239 expand */
+        const float* row       = scores + (size_t)t * ld;
+        size_t       firstPrev = firstCur;
+        firstCur               = n;
+        for (size_t shi = firstPrev; shi < firstCur; ++shi) {
+            const uint32_t st    = hyp[shi].state;
+            const float    score = hyp[shi].score;
+            for (uint32_t a = arcOffsets[st]; a < arcOffsets[st + 1]; ++a) {
+                const float emissionScore   = row[arcEmission[a]];
+                const float transitionScore = arcWeight[a];
+                volatile float partial      = score + transitionScore; /* Aligner.cc:207, left to right in f32 */
+                const float    sco          = partial + emissionScore;
+                /* Aligner.cc:132-158 activateOrUpdateStateHypothesisViterbi */
+                const uint32_t target = arcTarget[a];
+                size_t         k      = hypForState[target];
+                if (k >= n || k < firstCur || hyp[k].state != target) {
+                    hypForState[target] = n;
+                    if (n == cap) {
+                        cap *= 2;
+                        hyp = (orc_state_hyp*)realloc(hyp, cap * sizeof(orc_state_hyp));
+                    }
+                    hyp[n++] = (orc_state_hyp){target, sco, (uint32_t)shi, arcEmission[a]};
+                }
+                else if (hyp[k].score >= sco) {
+                    hyp[k].score    = sco;
+                    hyp[k].trace    = (uint32_t)shi;
+                    hyp[k].emission = arcEmission[a];
+                }
+            }
+        }
+    }
+    /* Aligner.cc:398-411 getAlignmentFsaViterbi: best final hypothesis of the last frame, strict < */
+    size_t bestHyp   = (size_t)-1;
+    float  bestScore = FLT_MAX;
+    for (size_t shi = firstCur; shi < n; ++shi) {
+        const float fw = finalWeight[hyp[shi].state];
+        if (isinf(fw) && fw > 0)
+            continue; /* not final */
+        const float sc = fw + hyp[shi].score;
+        if (sc < bestScore) {
+            bestScore = sc;
+            bestHyp   = shi;
+        }
+    }
+    if (bestScore == FLT_MAX) {
+        for (uint32_t t = 0; t < T; ++t) {
+            pathEmission[t] = 0xFFFFFFFFu;
+            if (pathState)
+                pathState[t] = 0xFFFFFFFFu;
+        }
+    }
+    else {
+        /* Aligner.cc:425-434 trace back */
+        size_t shi = bestHyp;
+        for (uint32_t t = T; t > 0; --t) {
+            pathEmission[t - 1] = hyp[shi].emission;
+            if (pathState)
+                pathState[t - 1] = hyp[shi].state;
+            shi = hyp[shi].trace;
+        }
+    }
+    free(hyp);
+    free(hypForState);
+    return bestScore;
 }

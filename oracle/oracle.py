@@ -147,6 +147,39 @@ def simd_final_score(q, scaling_squared):
 # ---------------------------------------------------------------------------------------------------
 # Runner for the compiled reference (oracle/_ref/ref_scorer)
 # ---------------------------------------------------------------------------------------------------
+def viterbi_align(frame_offsets, scores, automata):
+    """orc_viterbi_align per segment.  `automata` has the fields of rasr_b200.align.AlignmentAutomata.
+    -> (path_emission [frames] u32, path_state [frames] u32, path_score [segments] f32)."""
+    L = lib()
+    L.orc_viterbi_align.restype = C.c_float
+    fo = np.ascontiguousarray(frame_offsets, np.uint32)
+    scores = np.ascontiguousarray(scores, np.float32)
+    a = automata
+    n_seg = fo.shape[0] - 1
+    em = np.empty(int(fo[-1]), np.uint32)
+    st = np.empty(int(fo[-1]), np.uint32)
+    sc = np.empty(n_seg, np.float32)
+    ld = scores.shape[1] if scores.ndim == 2 else 1
+    for i in range(n_seg):
+        f0, f1 = int(fo[i]), int(fo[i + 1])
+        s0, s1 = int(a.state_offsets[i]), int(a.state_offsets[i + 1])
+        a0 = int(a.arc_offsets[s0])
+        ao = np.ascontiguousarray(a.arc_offsets[s0:s1 + 1] - np.uint32(a0))
+        tg = np.ascontiguousarray(a.arc_target[a0:])
+        ae = np.ascontiguousarray(a.arc_emission[a0:])
+        aw = np.ascontiguousarray(a.arc_weight[a0:])
+        fw = np.ascontiguousarray(a.final_weight[s0:s1])
+        rows = scores[f0:f1]
+        e_i = np.empty(f1 - f0, np.uint32)
+        s_i = np.empty(f1 - f0, np.uint32)
+        sc[i] = L.orc_viterbi_align(C.c_uint32(f1 - f0), _p(rows) if f1 > f0 else C.c_void_p(0), C.c_size_t(ld),
+                                    C.c_uint32(s1 - s0), _p(ao), _p(tg), _p(ae), _p(aw),
+                                    C.c_uint32(int(a.initial_state[i])), _p(fw), _p(e_i), _p(s_i))
+        em[f0:f1] = e_i
+        st[f0:f1] = s_i
+    return em, st, sc
+
+
 def ref_available() -> bool:
     return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
 

@@ -31,6 +31,9 @@ SYMBOLS = [
     ("gmm_upload_quant", _i, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, C.c_float]),
     ("gmm_quant_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_quant_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
+    ("gmm_align_device", _i, [_vp, _u32, _vp, _vp, _sz] + [_vp] * 10),
+    ("gmm_align_ordered_count", C.c_uint64, [_vp]),
+    ("gmm_score_align_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
     ("gmm_host_alloc", _vp, [_sz]),
     ("gmm_host_free", None, [_vp]),
     ("gmm_sync", _i, [_vp]),
@@ -174,6 +177,51 @@ class Engine:
     def posteriors_device(self, T, d_x, d_post):
         self._check(self._lib.gmm_posteriors_device(self._h, int(T), _ptr(d_x), _ptr(d_post)),
                     "gmm_posteriors_device")
+
+    # -- alignment consumer (scores never leave the device) ---------------------------------------
+    def _align_args(self, frame_offsets, automata):
+        fo = _np(frame_offsets, np.uint32)
+        a = automata
+        n_seg = fo.shape[0] - 1
+        if a.state_offsets.shape[0] != n_seg + 1 or a.initial_state.shape[0] != n_seg:
+            raise ValueError("align: automata and frame offsets describe different numbers of segments")
+        n_frames = int(fo[-1]) if n_seg >= 0 and fo.shape[0] else 0
+        return fo, n_seg, n_frames
+
+    def align_device(self, frame_offsets, d_scores, automata, ld=None, want_states=True):
+        """Best Viterbi path of every segment through its automaton over the DEVICE score block.
+        -> (path_emission [frames] u32, path_state [frames] u32 | None, path_score [segments] f32), host arrays."""
+        fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
+        a = automata
+        ld = self.M if ld is None else int(ld)
+        em = np.empty(n_frames, np.uint32)
+        st = np.empty(n_frames, np.uint32) if want_states else None
+        sc = np.empty(max(n_seg, 0), np.float32)
+        self._check(self._lib.gmm_align_device(self._h, n_seg, _ptr(fo), _ptr(d_scores), ld, _ptr(a.state_offsets),
+                                               _ptr(a.arc_offsets), _ptr(a.arc_target), _ptr(a.arc_emission),
+                                               _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight),
+                                               _ptr(em), _ptr(st), _ptr(sc)), "gmm_align_device")
+        return em, st, sc
+
+    def score_align_host(self, frame_offsets, x, automata, want_states=True):
+        """Host features [frames, D] -> float scorer -> alignment; only the paths come back."""
+        fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
+        a = automata
+        x = _np(x, np.float32)
+        if x.ndim != 2 or x.shape != (n_frames, self.D):
+            raise ValueError(f"features must be [{n_frames}, {self.D}]")
+        em = np.empty(n_frames, np.uint32)
+        st = np.empty(n_frames, np.uint32) if want_states else None
+        sc = np.empty(max(n_seg, 0), np.float32)
+        self._check(self._lib.gmm_score_align_host(self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets),
+                                                   _ptr(a.arc_offsets), _ptr(a.arc_target), _ptr(a.arc_emission),
+                                                   _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight),
+                                                   _ptr(em), _ptr(st), _ptr(sc)), "gmm_score_align_host")
+        return em, st, sc
+
+    @property
+    def align_ordered_count(self) -> int:
+        return int(self._lib.gmm_align_ordered_count(self._h))
 
     # -- quantized engine -------------------------------------------------------------------------
     def upload_quant(self, offsets, qmean, cov_idx, qconst, isr_scaled, scaling_squared):

@@ -361,6 +361,85 @@ int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uin
     return GMM_OK;
 }
 
+int gmm_align_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
+                     const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                     const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (nSeg == 0)
+        return GMM_OK;
+    if (!frameOffsets || !stateOffsets || !arcOffsets || !initialState || !finalWeight || !pathEmission || !pathScore ||
+        (frameOffsets[nSeg] && !d_scores) || (arcOffsets[stateOffsets[nSeg]] && (!arcTarget || !arcEmission || !arcWeight))) {
+        h->setError("gmm_align: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return gmm_align_launch(h, nSeg, frameOffsets, d_scores, ld, stateOffsets, arcOffsets, arcTarget, arcEmission,
+                            arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore);
+}
+
+uint64_t gmm_align_ordered_count(const gmm_handle* h) {
+    return h ? h->alignOrdered : 0;
+}
+
+int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                         const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                         const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                         const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid) {
+        h->setError("gmm_score_align: no float model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (nSeg == 0)
+        return GMM_OK;
+    if (!frameOffsets || !stateOffsets || !arcOffsets || !initialState || !finalWeight || !pathEmission || !pathScore ||
+        (frameOffsets[nSeg] && !x)) {
+        h->setError("gmm_score_align: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    // groups of whole segments whose score block stays bounded (it never leaves the device)
+    const size_t devLd = h->M, maxFrames = std::max<size_t>(1, ((size_t)2 << 30) / (devLd * 4));
+    uint32_t     s0 = 0;
+    while (s0 < nSeg) {
+        uint32_t s1 = s0 + 1;
+        while (s1 < nSeg && (size_t)(frameOffsets[s1 + 1] - frameOffsets[s0]) <= maxFrames)
+            ++s1;
+        const uint32_t f0 = frameOffsets[s0], T = frameOffsets[s1] - f0, n = s1 - s0;
+        std::vector<uint32_t> fo(n + 1), so(n + 1);
+        for (uint32_t i = 0; i <= n; ++i) {
+            fo[i] = frameOffsets[s0 + i] - f0;
+            so[i] = stateOffsets[s0 + i] - stateOffsets[s0];
+        }
+        std::vector<uint32_t> ao(so[n] + 1);
+        const uint32_t        st0 = stateOffsets[s0], a0 = arcOffsets[st0];
+        for (uint32_t s = 0; s <= so[n]; ++s)
+            ao[s] = arcOffsets[st0 + s] - a0;
+        void *dx = nullptr, *ds = nullptr;
+        int   rc;
+        if ((rc = h->reserve(SCR_X, (size_t)std::max(1u, T) * h->D * 4, &dx)))
+            return rc;
+        if ((rc = h->reserve(SCR_SCORE, (size_t)std::max(1u, T) * devLd * 4, &ds)))
+            return rc;
+        if (T) {
+            GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x + (size_t)f0 * h->D, (size_t)T * h->D * 4, cudaMemcpyHostToDevice,
+                                            h->stream));
+            if ((rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, nullptr, devLd)))
+                return rc;
+        }
+        if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, devLd, so.data(), ao.data(),
+                                   arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
+                                   arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0,
+                                   pathEmission + f0, pathState ? pathState + f0 : nullptr, pathScore + s0)))
+            return rc;
+        s0 = s1;
+    }
+    return GMM_OK;
+}
+
 int gmm_posteriors_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_post) {
     if (!h)
         return GMM_ERR_ARG;

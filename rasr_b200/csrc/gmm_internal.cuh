@@ -80,6 +80,7 @@ struct gmm_handle {
     cudaStream_t stream     = nullptr;
     bool         ownStream  = false;
     uint64_t     launches   = 0;
+    uint64_t     alignOrdered = 0;  // segments aligned by the ordered (tie-resolving) pass so far
     bool         timing     = false;                            // gmm_kernel_timing
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed;     // brackets of scoring-kernel launches
     void timeBegin() {
@@ -127,6 +128,10 @@ int gmm_direct_posteriors(gmm_handle* h, uint32_t T, const float* d_x, float* d_
 int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
                      uint8_t* d_qx, size_t ld);
 // gmm_tc.cu
+int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
+                     const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                     const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore);
 int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, const int32_t* c2);
 int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
                   uint8_t* d_qx, size_t ld);

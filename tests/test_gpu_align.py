@@ -1,0 +1,146 @@
+"""GPU parity of the device-resident alignment consumer (gmm_align_device / gmm_score_align_host, SURVEY.md 8(f)
+rank 1) against the oracle's restatement of Search::Aligner's Viterbi search space: bit-exact paths and scores,
+including exact f32 ties, which must be resolved in the reference's hypothesis order."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import oracle_float_tables
+from rasr_b200 import capi, synth, tables
+from rasr_b200.align import AlignmentAutomata, linear_hmm
+
+pytestmark = pytest.mark.gpu
+FLT_MAX = np.finfo(np.float32).max
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = capi.Engine(0)
+    yield e
+    e.close()
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def random_graph(rng, S, M, integer_weights):
+    """General automaton: random out-degree, random targets, arcs in random order, several final states."""
+    states = []
+    for s in range(S):
+        arcs = []
+        for _ in range(int(rng.integers(0, 5))):
+            w = float(rng.integers(0, 3)) if integer_weights else float(rng.uniform(0, 5))
+            arcs.append((int(rng.integers(0, S)), int(rng.integers(0, M)), w))
+        states.append(arcs)
+    final = {int(s): (float(rng.integers(0, 2)) if integer_weights else float(rng.uniform(0, 3)))
+             for s in rng.choice(S, size=max(1, S // 4), replace=False)}
+    return states, int(rng.integers(0, S)), final
+
+
+def check(eng, oracle, fo, scores, au):
+    d = torch.from_numpy(scores).cuda()
+    n0 = eng.align_ordered_count
+    em, st, sc = eng.align_device(fo, d, au, ld=scores.shape[1])
+    emo, sto, sco = oracle.viterbi_align(fo, scores, au)
+    assert np.array_equal(bits(sc), bits(sco))
+    assert np.array_equal(em, emo) and np.array_equal(st, sto)
+    em2, st2, sc2 = eng.align_device(fo, d, au, ld=scores.shape[1], want_states=False)
+    assert st2 is None and np.array_equal(em2, emo)
+    return eng.align_ordered_count - n0
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_linear_automata_ragged_segments(eng, oracle, seed):
+    rng = np.random.default_rng(seed)
+    M, segs, fo = 300, [], [0]
+    for i in range(int(rng.integers(40, 400))):
+        n = int(rng.integers(1, 120))
+        T = 0 if i % 37 == 5 else int(rng.integers(max(1, n // 3), 3 * n + 5))   # some unreachable, some empty
+        segs.append(linear_hmm(rng.integers(0, M, n), loop=rng.uniform(0, 4), forward=rng.uniform(0, 2),
+                               skip=rng.uniform(2, 8) if i % 3 else None))
+        fo.append(fo[-1] + T)
+    scores = rng.uniform(0, 80, size=(fo[-1], M)).astype(np.float32)
+    ordered = check(eng, oracle, np.array(fo, np.uint32), scores, AlignmentAutomata.from_arc_lists(segs))
+    assert ordered <= 2   # continuous random scores: (almost) no exact ties
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_general_graphs_with_ties_take_the_ordered_pass(eng, oracle, seed):
+    """Integer scores and weights: ties everywhere, states not numbered in activation order."""
+    rng = np.random.default_rng(100 + seed)
+    M, segs, fo = 17, [], [0]
+    for _ in range(60):
+        segs.append(random_graph(rng, int(rng.integers(1, 70)), M, integer_weights=True))
+        fo.append(fo[-1] + int(rng.integers(0, 40)))
+    scores = rng.integers(0, 3, size=(fo[-1], M)).astype(np.float32)
+    ordered = check(eng, oracle, np.array(fo, np.uint32), scores, AlignmentAutomata.from_arc_lists(segs))
+    assert ordered >= 20
+
+
+def test_general_graphs_continuous_scores(eng, oracle):
+    rng = np.random.default_rng(7)
+    M, segs, fo = 64, [], [0]
+    for _ in range(200):
+        segs.append(random_graph(rng, int(rng.integers(1, 400)), M, integer_weights=False))
+        fo.append(fo[-1] + int(rng.integers(0, 60)))
+    scores = rng.uniform(0, 30, size=(fo[-1], M)).astype(np.float32)
+    scores[rng.random(scores.shape) < 0.02] = np.inf      # unusable emissions
+    check(eng, oracle, np.array(fo, np.uint32), scores, AlignmentAutomata.from_arc_lists(segs))
+
+
+def test_tie_rules_of_the_reference(eng, oracle):
+    states = [[(1, 3, 0.0), (2, 4, 0.0)], [(3, 5, 0.0)], [(3, 6, 0.0)], []]
+    a = AlignmentAutomata.from_arc_lists([(states, 0, {3: 0.0}), ([[(2, 1, 0.0), (1, 0, 0.0)], [], []], 0,
+                                                                  {1: 0.0, 2: 0.0})])
+    scores = np.ones((3, 8), np.float32)
+    em, st, sc = eng.align_device([0, 2, 3], torch.from_numpy(scores).cuda(), a, ld=8)
+    assert list(em) == [4, 6, 1] and list(st) == [2, 3, 2] and list(sc) == [2.0, 1.0]
+    assert check(eng, oracle, np.array([0, 2, 3], np.uint32), scores, a) == 4   # 2 segments x 2 calls
+
+
+def test_large_automaton_and_long_segment(eng, oracle):
+    rng = np.random.default_rng(3)
+    M = 4501
+    segs = [linear_hmm(rng.integers(0, M, 3000), loop=1.0, forward=0.5, skip=4.0),
+            linear_hmm(rng.integers(0, M, 7), loop=0.1, forward=0.5, skip=None)]
+    fo = np.array([0, 4000, 4600], np.uint32)
+    scores = rng.uniform(0, 100, size=(4600, M)).astype(np.float32)
+    check(eng, oracle, fo, scores, AlignmentAutomata.from_arc_lists(segs))
+
+
+def test_argument_errors(eng):
+    a = AlignmentAutomata.from_arc_lists([linear_hmm([1, 2])])
+    d = torch.zeros((2, 4), device="cuda")
+    bad = AlignmentAutomata.from_arc_lists([linear_hmm([1, 9])])
+    with pytest.raises(capi.GmmError, match="emission index"):
+        eng.align_device([0, 2], d, bad, ld=4)
+    a.arc_target[0] = 77
+    with pytest.raises(capi.GmmError, match="arc target"):
+        eng.align_device([0, 2], d, a, ld=4)
+    with pytest.raises(ValueError):
+        eng.align_device([0, 1, 2], d, a, ld=4)
+    em, st, sc = eng.align_device(np.zeros(1, np.uint32), d, AlignmentAutomata.from_arc_lists([]), ld=4)
+    assert em.size == 0 and sc.size == 0
+
+
+def test_score_and_align_from_host_features(eng, oracle):
+    """Features in, paths out: the path must be the oracle's Viterbi path over the scores this engine computes
+    (bit-exact), and over the oracle's own scores (north_star: identical best-path alignments)."""
+    ms, x = synth.make_config("cfg1")   # 4501 x 16 x 45, 1000 frames
+    rng = np.random.default_rng(11)
+    fo = np.array([0, 250, 480, 480, 1000], np.uint32)
+    segs = [linear_hmm(rng.integers(0, ms.M, n), loop=3.0, forward=0.0, skip=30.0) for n in (60, 75, 1, 140)]
+    au = AlignmentAutomata.from_arc_lists(segs)
+    for kernel in (capi.KERNEL_DIRECT, capi.KERNEL_AUTO):
+        t = oracle_float_tables(ms) if kernel == capi.KERNEL_DIRECT else tables.float_tables(ms)
+        eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=capi.MODE_MAX,
+                         kernel=kernel)
+        em, st, sc = eng.score_align_host(fo, x, au)
+        s, _ = eng.score_host(x, want_best=False)
+        emo, sto, sco = oracle.viterbi_align(fo, s, au)
+        assert np.array_equal(em, emo) and np.array_equal(st, sto) and np.array_equal(bits(sc), bits(sco))
+        so, _ = oracle.score_max(ms, x)
+        emr, str_, scr = oracle.viterbi_align(fo, so, au)
+        assert np.array_equal(em, emr) and np.array_equal(st, str_)
+        np.testing.assert_allclose(sc, scr, rtol=1e-4)
