@@ -12,16 +12,26 @@
 // empty alignment (all emissions 0xFFFFFFFF, score FLT_MAX).
 // Order of candidates: the reference visits the previous frame's hypotheses in their order of activation and the
 // arcs of each in Fsa order, so exact f32 ties (between candidates of one state, between final states) are
-// resolved by that order.  The parallel pass below is order-free: it finds each state's minimum with one thread per
-// state over the state's incoming arcs and records whether any minimum was reached by two candidates.  A segment
-// with no such tie has a unique best path whatever the order.  A segment WITH a tie is redone by one thread of the
-// same CTA that replays the reference's hypothesis lists literally (ordered_pass), so the result is the
-// reference's in both cases; the number of segments that took the ordered pass is reported (gmm_align_ordered_count).
+// resolved by that order -- and with f32 path scores in the thousands such ties are common, not exotic.  Without
+// pruning the order is a property of the automaton alone: the list of frame t is the ordered set of arc targets of
+// the list of frame t-1.  align_ranked_kernel carries it as a dense rank per state: a target's arrival key is
+// rank(source) * A + arc position in the source, the rank of a new hypothesis is the number of smaller FIRST arrival
+// keys (a bitmap of keys + prefix pop-count per frame), and once the ranking repeats (the list is a fixed point of
+// the map above) it is frozen.  Among equal candidates of a state the largest arrival key wins (`>=` lets the later
+// arrival replace), among equal final hypotheses the smallest rank (strict `<` keeps the first).
+// Automata too large for that kernel's shared-memory tables take align_generic_kernel: an order-free parallel pass
+// that detects whether any minimum was shared, and, only then, a literal single-thread replay of the reference's
+// hypothesis lists (ordered_pass); gmm_align_ordered_count reports how many segments were replayed.
 //
-// One CTA per segment (segments are independent): state scores of the previous / current frame in shared memory,
-// one thread per state and frame, back-pointers [T x S] in HBM, traceback by one thread.
+// One CTA per segment (segments are independent).  align_ranked_kernel keeps the automaton, the state scores and
+// the ranks in shared memory, gathers the emission scores of the next frames with asynchronous 4-byte copies
+// (K frames in flight) so that the frame loop never waits for HBM, writes one back-pointer per (frame, state), and
+// tracks for every state its ancestor at the last 32-frame boundary, so that the traceback is ceil(T/32) dependent
+// steps by one thread followed by independent 32-frame walks by one thread each.
 #include <float.h>
 #include <math.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include <algorithm>
 #include <vector>
@@ -30,14 +40,16 @@
 
 namespace {
 
-constexpr uint32_t kNoArc = 0xFFFFFFFFu;
+constexpr uint32_t kNoArc       = 0xFFFFFFFFu;
+constexpr uint32_t kBlockFrames = 32;  // traceback block
 
 struct AlignSeg {
     uint32_t frame0, frames;  // rows [frame0, frame0 + frames) of the score block
     uint32_t state0, states;  // states [state0, state0 + states) of the concatenated automata
     uint32_t initial;         // segment-local initial state
-    uint32_t pad;
+    uint32_t keyShift;        // arrival key = rank << keyShift | arc position in its source state
     uint64_t back0;           // offset of this segment's back-pointer block [frames x states]
+    uint64_t map0;            // offset of this segment's boundary-ancestor block [ceil(frames / 32) x states]
 };
 
 struct AlignParams {
@@ -47,6 +59,7 @@ struct AlignParams {
     size_t          ld;
     const uint32_t* inOff;  // [nStates + 1] incoming arcs of every (global) state
     const uint32_t* inSrc;  // segment-local source state
+    const uint32_t* inSK;   // source state << 16 | position of the arc in its source's arc list (ranked kernel)
     const uint32_t* inEm;
     const float*    inW;
     const uint32_t* outOff;     // [nStates + 1] the caller's arc lists (Fsa order) ...
@@ -54,6 +67,7 @@ struct AlignParams {
     const uint32_t* outToIn;    // ... and the arc's position in the in* arrays
     const float*    finalW;     // [nStates], +inf: not final
     uint32_t*       back;       // back-pointers: index into the in* arrays, or kNoArc
+    uint32_t*       map;        // ranked kernel: ancestor state at the last 32-frame boundary, per block and state
     uint32_t*       lists;      // ordered pass: 6 arrays of maxStates words per CTA
     uint32_t        maxStates;
     uint32_t*       orderedCount;
@@ -128,7 +142,7 @@ __device__ uint32_t ordered_pass(const AlignParams& p, const AlignSeg& sg, float
     return bestState;
 }
 
-__global__ void __launch_bounds__(256) align_kernel(const AlignParams p) {
+__global__ void __launch_bounds__(256) align_generic_kernel(const AlignParams p) {
     extern __shared__ float sm[];
     for (uint32_t si = blockIdx.x; si < p.nSeg; si += gridDim.x) {
         const AlignSeg sg  = p.seg[si];
@@ -208,6 +222,210 @@ __global__ void __launch_bounds__(256) align_kernel(const AlignParams p) {
     }
 }
 
+__device__ __forceinline__ void cp_async4(float* smemDst, const float* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smemDst)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template<int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// Shared-memory words align_ranked_kernel needs for an automaton of S states, nIn arcs and W key-bitmap words.
+__host__ __device__ inline size_t ranked_smem_words(uint32_t S, uint32_t nIn, uint32_t W, int K) {
+    return (size_t)6 * S + (S + 1) + (size_t)3 * nIn + (size_t)K * nIn + (size_t)3 * W;
+}
+
+template<int K>
+__global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) {
+    extern __shared__ uint32_t smw[];
+    const uint32_t tid = threadIdx.x, nThreads = blockDim.x;
+    for (uint32_t si = blockIdx.x; si < p.nSeg; si += gridDim.x) {
+        const AlignSeg sg      = p.seg[si];
+        const uint32_t S       = sg.states, T = sg.frames;
+        const uint32_t arcBase = p.inOff[sg.state0];
+        const uint32_t nIn     = p.inOff[sg.state0 + S] - arcBase;
+        const uint32_t W       = (uint32_t)((((uint64_t)S << sg.keyShift) + 31) >> 5);
+        float*         cur     = (float*)smw;
+        float*         nxt     = cur + S;
+        uint32_t*      rankO   = smw + 2 * (size_t)S;
+        uint32_t*      rankN   = rankO + S;
+        uint32_t*      ancO    = rankN + S;
+        uint32_t*      ancN    = ancO + S;
+        uint32_t*      offs    = ancN + S;          // [S + 1] incoming arcs of state s: offs[s] .. offs[s + 1]
+        uint32_t*      tabSK   = offs + S + 1;      // [nIn]
+        float*         tabW    = (float*)(tabSK + nIn);
+        uint32_t*      tabEm   = (uint32_t*)(tabW + nIn);
+        float*         ring    = (float*)(tabEm + nIn);  // [K][nIn] emission scores of the frames in flight
+        uint32_t*      bm0     = (uint32_t*)(ring + (size_t)K * nIn);
+        uint32_t*      bm1     = bm0 + W;
+        uint32_t*      pref    = bm1 + W;
+        for (uint32_t s = tid; s <= S; s += nThreads)
+            offs[s] = p.inOff[sg.state0 + s] - arcBase;
+        for (uint32_t a = tid; a < nIn; a += nThreads) {
+            tabSK[a] = p.inSK[arcBase + a];
+            tabW[a]  = p.inW[arcBase + a];
+            tabEm[a] = p.inEm[arcBase + a];
+        }
+        for (uint32_t s = tid; s < S; s += nThreads) {
+            cur[s]   = (s == sg.initial) ? 0.f : INFINITY;
+            rankO[s] = (s == sg.initial) ? 0u : kNoArc;
+            ancO[s]  = kNoArc;
+        }
+        for (uint32_t w = tid; w < 2 * W; w += nThreads)
+            bm0[w] = 0;
+        __syncthreads();
+        auto prefetch = [&](uint32_t f) {
+            if (f < T) {
+                const float* row = p.scores + (size_t)(sg.frame0 + f) * p.ld;
+                float*       dst = ring + (size_t)(f % K) * nIn;
+                for (uint32_t a = tid; a < nIn; a += nThreads)
+                    cp_async4(dst + a, row + tabEm[a]);
+            }
+            cp_async_commit();
+        };
+        for (uint32_t f = 0; f + 1 < (uint32_t)K; ++f)
+            prefetch(f);
+        int stable = 0;
+        for (uint32_t t = 0; t < T; ++t) {
+            cp_async_wait<K - 2>();
+            __syncthreads();  // frame t's scores landed; frame t-1's state scores, ranks and ancestors are complete
+            prefetch(t + K - 1);
+            const float*   E        = ring + (size_t)(t % K) * nIn;
+            uint32_t*      bm       = (t & 1) ? bm1 : bm0;
+            uint32_t*      bk       = p.back + sg.back0 + (size_t)t * S;
+            const bool     boundary = (t % kBlockFrames) == 0;
+            const bool     emitMap  = ((t + 1) % kBlockFrames) == 0 || t + 1 == T;
+            uint32_t*      mapRow   = p.map + sg.map0 + (size_t)(t / kBlockFrames) * S;
+            const uint32_t keyMask  = (1u << sg.keyShift) - 1;
+            for (uint32_t s = tid; s < S; s += nThreads) {
+                float    best = INFINITY;
+                uint32_t bestArc = kNoArc, bestKey = 0, firstKey = kNoArc, bestSrc = 0;
+                for (uint32_t a = offs[s]; a < offs[s + 1]; ++a) {
+                    const uint32_t sk = tabSK[a], src = sk >> 16;
+                    const uint32_t r  = rankO[src];
+                    if (r == kNoArc)
+                        continue;  // no hypothesis in the previous frame
+                    const uint32_t key = (r << sg.keyShift) | (sk & 0xFFFFu & keyMask);
+                    firstKey           = min(firstKey, key);
+                    const float c      = __fadd_rn(__fadd_rn(cur[src], tabW[a]), E[a]);
+                    if (bestArc == kNoArc || c < best || (c == best && key > bestKey)) {
+                        best    = c;
+                        bestArc = a;
+                        bestKey = key;
+                        bestSrc = src;
+                    }
+                }
+                nxt[s] = best;
+                bk[s]  = bestArc;
+                const uint32_t anc = bestArc == kNoArc ? kNoArc : (boundary ? bestSrc : ancO[bestSrc]);
+                ancN[s]            = anc;
+                if (emitMap)
+                    mapRow[s] = anc;
+                if (!stable) {
+                    rankN[s] = firstKey;
+                    if (firstKey != kNoArc)
+                        atomicOr(&bm[firstKey >> 5], 1u << (firstKey & 31));
+                }
+            }
+            if (!stable) {
+                __syncthreads();
+                if (tid < 32) {  // exclusive prefix pop-count of the key bitmap
+                    uint32_t carry = 0;
+                    for (uint32_t w0 = 0; w0 < W; w0 += 32) {
+                        const uint32_t w = w0 + tid;
+                        const uint32_t v = w < W ? __popc(bm[w]) : 0;
+                        uint32_t       x = v;
+                        for (int d = 1; d < 32; d <<= 1) {
+                            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, d);
+                            if ((int)tid >= d)
+                                x += y;
+                        }
+                        if (w < W)
+                            pref[w] = carry + x - v;
+                        carry += __shfl_sync(0xFFFFFFFFu, x, 31);
+                    }
+                }
+                __syncthreads();
+                int same = 1;
+                for (uint32_t s = tid; s < S; s += nThreads) {
+                    const uint32_t k = rankN[s];
+                    uint32_t       r = kNoArc;
+                    if (k != kNoArc)
+                        r = pref[k >> 5] + __popc(bm[k >> 5] & ((1u << (k & 31)) - 1));
+                    rankN[s] = r;
+                    same &= (r == rankO[s]);
+                }
+                stable = __syncthreads_and(same);  // the hypothesis list repeats: it is a fixed point from here on
+                for (uint32_t w = tid; w < W; w += nThreads)
+                    bm[w] = 0;
+                uint32_t* sw = rankO;
+                rankO        = rankN;
+                rankN        = sw;
+            }
+            float* sf = cur;
+            cur       = nxt;
+            nxt       = sf;
+            uint32_t* sa = ancO;
+            ancO         = ancN;
+            ancN         = sa;
+        }
+        cp_async_wait<0>();
+        __syncthreads();
+        // best final hypothesis: smallest score, the earliest activated among equals (Aligner.cc:398-411)
+        const uint32_t nBlocks = (T + kBlockFrames - 1) / kBlockFrames;
+        uint32_t*      dState  = p.pathState + sg.frame0;
+        __shared__ uint32_t bestShared;
+        if (tid == 0) {
+            float    best = FLT_MAX;
+            uint32_t bestState = kNoArc, bestRank = kNoArc;
+            for (uint32_t s = 0; s < S; ++s) {
+                const float fw = p.finalW[sg.state0 + s];
+                if (rankO[s] == kNoArc || fw == INFINITY)
+                    continue;
+                const float sc = __fadd_rn(fw, cur[s]);
+                if (sc < best || (sc == best && sc < FLT_MAX && rankO[s] < bestRank)) {
+                    best      = sc;
+                    bestState = s;
+                    bestRank  = rankO[s];
+                }
+            }
+            p.pathScore[si] = best;
+            bestShared      = bestState;
+            // state after the last frame of every 32-frame block, walking the boundary-ancestor maps backwards
+            uint32_t s = bestState;
+            for (uint32_t b = nBlocks; b-- > 0 && s != kNoArc;) {
+                const uint32_t tLast = min(T, (b + 1) * kBlockFrames) - 1;
+                dState[tLast]        = s;
+                s                    = p.map[sg.map0 + (size_t)b * S + s];
+            }
+        }
+        __syncthreads();
+        if (bestShared == kNoArc) {
+            for (uint32_t t = tid; t < T; t += nThreads) {
+                p.pathEmission[sg.frame0 + t] = kNoArc;
+                dState[t]                     = kNoArc;
+            }
+        }
+        else {
+            for (uint32_t b = tid; b < nBlocks; b += nThreads) {
+                const uint32_t tFirst = b * kBlockFrames, tLast = min(T, tFirst + kBlockFrames) - 1;
+                uint32_t       s      = dState[tLast];
+                for (uint32_t t = tLast + 1; t-- > tFirst;) {
+                    const uint32_t a              = p.back[sg.back0 + (size_t)t * S + s];
+                    dState[t]                     = s;
+                    p.pathEmission[sg.frame0 + t] = tabEm[a];
+                    s                             = tabSK[a] >> 16;
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace
 
 // Host arrays in, host arrays out; `d_scores` is the DEVICE score block.  See include/gmm_b200.h.
@@ -220,22 +438,25 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     const uint32_t nStates = stateOffsets[nSeg], nFrames = frameOffsets[nSeg];
     const uint32_t nArcs   = arcOffsets[nStates];
     // incoming-arc lists (CSR by target), arcs of a state ordered by (source state, arc index)
-    std::vector<uint32_t> inOff(nStates + 1, 0), inSrc(nArcs), inEm(nArcs), outToIn(nArcs);
+    std::vector<uint32_t> inOff(nStates + 1, 0), inSrc(nArcs), inSK(nArcs), inEm(nArcs), outToIn(nArcs);
     std::vector<float>    inW(nArcs);
     std::vector<AlignSeg> segs(nSeg);
-    uint64_t              backTotal = 0;
-    uint32_t              maxStates = 0;
+    uint64_t              backTotal = 0, mapTotal = 0;
+    uint32_t              maxStates = 0, maxDegree = 0;
+    size_t                maxWords[3] = {0, 0, 0};  // shared memory of the ranked kernel with 8 / 4 / 2 frames in flight
     for (uint32_t i = 0; i < nSeg; ++i) {
         const uint32_t s0 = stateOffsets[i], s1 = stateOffsets[i + 1];
         if (s1 < s0 || frameOffsets[i + 1] < frameOffsets[i] || initialState[i] >= std::max(1u, s1 - s0)) {
             h->setError("gmm_align: offsets not ascending or initial state out of range");
             return GMM_ERR_ARG;
         }
+        uint32_t degree = 0;
         for (uint32_t s = s0; s < s1; ++s) {
             if (arcOffsets[s + 1] < arcOffsets[s]) {
                 h->setError("gmm_align: arc offsets not ascending");
                 return GMM_ERR_ARG;
             }
+            degree = std::max(degree, arcOffsets[s + 1] - arcOffsets[s]);
             for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a) {
                 if (arcTarget[a] >= s1 - s0) {
                     h->setError("gmm_align: arc target outside its segment's automaton");
@@ -248,15 +469,29 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                 inOff[s0 + arcTarget[a] + 1]++;
             }
         }
-        segs[i].frame0  = frameOffsets[i];
-        segs[i].frames  = frameOffsets[i + 1] - frameOffsets[i];
-        segs[i].state0  = s0;
-        segs[i].states  = s1 - s0;
-        segs[i].initial = initialState[i];
-        segs[i].pad     = 0;
-        segs[i].back0   = backTotal;
-        backTotal += (uint64_t)segs[i].frames * segs[i].states;
-        maxStates = std::max(maxStates, s1 - s0);
+        uint32_t shift = 0;
+        while ((1u << shift) < degree)
+            ++shift;
+        AlignSeg& sg = segs[i];
+        sg.frame0    = frameOffsets[i];
+        sg.frames    = frameOffsets[i + 1] - frameOffsets[i];
+        sg.state0    = s0;
+        sg.states    = s1 - s0;
+        sg.initial   = initialState[i];
+        sg.keyShift  = shift;
+        sg.back0     = backTotal;
+        sg.map0      = mapTotal;
+        backTotal += (uint64_t)sg.frames * sg.states;
+        mapTotal += (uint64_t)((sg.frames + kBlockFrames - 1) / kBlockFrames) * sg.states;
+        maxStates = std::max(maxStates, sg.states);
+        maxDegree = std::max(maxDegree, degree);
+        const uint64_t keyBits = (uint64_t)sg.states << shift;
+        const uint32_t segArcs = arcOffsets[s1] - arcOffsets[s0];
+        for (int k = 0; k < 3; ++k)
+            maxWords[k] = std::max(maxWords[k], keyBits >= ((uint64_t)1 << 31)
+                                                        ? (size_t)1 << 40
+                                                        : ranked_smem_words(sg.states, segArcs, (uint32_t)((keyBits + 31) >> 5),
+                                                                            8 >> k));
     }
     for (uint32_t s = 0; s < nStates; ++s)
         inOff[s + 1] += inOff[s];
@@ -267,16 +502,30 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                 for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a) {
                     const uint32_t k = fill[stateOffsets[i] + arcTarget[a]]++;
                     inSrc[k]         = s - stateOffsets[i];
+                    inSK[k]          = (inSrc[k] << 16) | ((a - arcOffsets[s]) & 0xFFFFu);
                     inEm[k]          = arcEmission[a];
                     inW[k]           = arcWeight[a];
                     outToIn[a]       = k;
                 }
     }
-    const size_t smemBytes = (size_t)2 * maxStates * sizeof(float);
+    // kernel choice: the ranked kernel when every automaton's tables fit in shared memory
+    const char* force   = getenv("GMM_ALIGN_KERNEL");
+    int         inFlight = 0;  // 0: generic kernel
+    if (!(force && !strcmp(force, "generic")) && maxStates < 65536 && maxDegree < 65536) {
+        if (maxWords[0] * 4 <= 110 * 1024)
+            inFlight = 8;
+        else if (maxWords[1] * 4 <= 200 * 1024)
+            inFlight = 4;
+        else if (maxWords[2] * 4 <= 200 * 1024)
+            inFlight = 2;
+    }
+    const size_t smemBytes = inFlight ? maxWords[inFlight == 8 ? 0 : inFlight == 4 ? 1 : 2] * 4 + 16
+                                      : (size_t)2 * maxStates * sizeof(float);
     if (smemBytes > 200 * 1024) {
         h->setError("gmm_align: automaton with more than 25600 states");
         return GMM_ERR_UNSUPPORTED;
     }
+    const int grid = (int)std::min<uint32_t>(nSeg, (uint32_t)h->smCount * 8);
     // device buffers: one allocation, carved
     auto   al   = [](size_t v) { return (v + 255) & ~(size_t)255; };
     size_t off  = 0;
@@ -286,27 +535,32 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
         return o;
     };
     const size_t oSeg = take(nSeg * sizeof(AlignSeg)), oOff = take((nStates + 1) * 4), oSrc = take((size_t)nArcs * 4),
-                 oEm = take((size_t)nArcs * 4), oW = take((size_t)nArcs * 4), oFin = take((size_t)nStates * 4),
-                 oPe = take((size_t)nFrames * 4), oPs = take((size_t)nFrames * 4), oSc = take((size_t)nSeg * 4),
-                 oOut = take((nStates + 1) * 4), oTgt = take((size_t)nArcs * 4), oO2i = take((size_t)nArcs * 4),
-                 oCnt = take(4), oBack = take(backTotal * 4);
-    const int    grid   = (int)std::min<uint32_t>(nSeg, (uint32_t)h->smCount * 8);
-    const size_t oLists = take((size_t)grid * 6 * maxStates * 4);
+                 oSK = take((size_t)nArcs * 4), oEm = take((size_t)nArcs * 4), oW = take((size_t)nArcs * 4),
+                 oFin = take((size_t)nStates * 4), oPe = take((size_t)nFrames * 4), oPs = take((size_t)nFrames * 4),
+                 oSc = take((size_t)nSeg * 4), oOut = take((nStates + 1) * 4), oTgt = take((size_t)nArcs * 4),
+                 oO2i = take((size_t)nArcs * 4), oCnt = take(4), oBack = take(backTotal * 4),
+                 oMap = take(inFlight ? mapTotal * 4 : 0), oLists = take(inFlight ? 0 : (size_t)grid * 6 * maxStates * 4);
     void* base = nullptr;
     int   rc   = h->reserve(SCR_MISC, off, &base);
     if (rc)
         return rc;
-    char* d = (char*)base;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oSeg, segs.data(), nSeg * sizeof(AlignSeg), cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oOff, inOff.data(), (nStates + 1) * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oSrc, inSrc.data(), (size_t)nArcs * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oEm, inEm.data(), (size_t)nArcs * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oW, inW.data(), (size_t)nArcs * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oOut, arcOffsets, (nStates + 1) * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oTgt, arcTarget, (size_t)nArcs * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oO2i, outToIn.data(), (size_t)nArcs * 4, cudaMemcpyHostToDevice, h->stream));
+    char* d  = (char*)base;
+    auto  up = [&](size_t o, const void* src, size_t bytes) {
+        return bytes ? cudaMemcpyAsync(d + o, src, bytes, cudaMemcpyHostToDevice, h->stream) : cudaSuccess;
+    };
+    GMM_CUDA_TRY(h, up(oSeg, segs.data(), nSeg * sizeof(AlignSeg)));
+    GMM_CUDA_TRY(h, up(oOff, inOff.data(), (nStates + 1) * 4));
+    GMM_CUDA_TRY(h, up(oSrc, inSrc.data(), (size_t)nArcs * 4));
+    GMM_CUDA_TRY(h, up(oSK, inSK.data(), (size_t)nArcs * 4));
+    GMM_CUDA_TRY(h, up(oEm, inEm.data(), (size_t)nArcs * 4));
+    GMM_CUDA_TRY(h, up(oW, inW.data(), (size_t)nArcs * 4));
+    GMM_CUDA_TRY(h, up(oFin, finalWeight, (size_t)nStates * 4));
+    if (!inFlight) {
+        GMM_CUDA_TRY(h, up(oOut, arcOffsets, (nStates + 1) * 4));
+        GMM_CUDA_TRY(h, up(oTgt, arcTarget, (size_t)nArcs * 4));
+        GMM_CUDA_TRY(h, up(oO2i, outToIn.data(), (size_t)nArcs * 4));
+    }
     GMM_CUDA_TRY(h, cudaMemsetAsync(d + oCnt, 0, 4, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oFin, finalWeight, (size_t)nStates * 4, cudaMemcpyHostToDevice, h->stream));
     AlignParams p;
     p.seg          = (const AlignSeg*)(d + oSeg);
     p.nSeg         = nSeg;
@@ -314,22 +568,30 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     p.ld           = ld;
     p.inOff        = (const uint32_t*)(d + oOff);
     p.inSrc        = (const uint32_t*)(d + oSrc);
+    p.inSK         = (const uint32_t*)(d + oSK);
     p.inEm         = (const uint32_t*)(d + oEm);
     p.inW          = (const float*)(d + oW);
     p.outOff       = (const uint32_t*)(d + oOut);
     p.outTarget    = (const uint32_t*)(d + oTgt);
     p.outToIn      = (const uint32_t*)(d + oO2i);
     p.finalW       = (const float*)(d + oFin);
+    p.back         = (uint32_t*)(d + oBack);
+    p.map          = (uint32_t*)(d + oMap);
     p.lists        = (uint32_t*)(d + oLists);
     p.maxStates    = maxStates;
     p.orderedCount = (uint32_t*)(d + oCnt);
-    p.back         = (uint32_t*)(d + oBack);
     p.pathEmission = (uint32_t*)(d + oPe);
-    p.pathState    = pathState ? (uint32_t*)(d + oPs) : nullptr;
+    p.pathState    = (uint32_t*)(d + oPs);
     p.pathScore    = (float*)(d + oSc);
+    void (*kernel)(AlignParams) = inFlight == 8   ? align_ranked_kernel<8>
+                                  : inFlight == 4 ? align_ranked_kernel<4>
+                                  : inFlight == 2 ? align_ranked_kernel<2>
+                                                  : align_generic_kernel;
     if (smemBytes > 48 * 1024)
-        GMM_CUDA_TRY(h, cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-    align_kernel<<<grid, 256, smemBytes, h->stream>>>(p);
+        GMM_CUDA_TRY(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+    h->timeBegin();
+    kernel<<<grid, 256, smemBytes, h->stream>>>(p);
+    h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
     GMM_CUDA_TRY(h, cudaMemcpyAsync(pathEmission, d + oPe, (size_t)nFrames * 4, cudaMemcpyDeviceToHost, h->stream));

@@ -20,6 +20,16 @@ def eng():
     e.close()
 
 
+@pytest.fixture(params=["ranked", "generic"])
+def kernel(request, monkeypatch):
+    """Both device kernels: the rank-carrying one (default) and the order-free one with ordered replay on ties."""
+    if request.param == "generic":
+        monkeypatch.setenv("GMM_ALIGN_KERNEL", "generic")
+    else:
+        monkeypatch.delenv("GMM_ALIGN_KERNEL", raising=False)
+    return request.param
+
+
 def bits(a):
     return np.ascontiguousarray(a).view(np.uint32)
 
@@ -51,7 +61,7 @@ def check(eng, oracle, fo, scores, au):
 
 
 @pytest.mark.parametrize("seed", range(4))
-def test_linear_automata_ragged_segments(eng, oracle, seed):
+def test_linear_automata_ragged_segments(eng, oracle, kernel, seed):
     rng = np.random.default_rng(seed)
     M, segs, fo = 300, [], [0]
     for i in range(int(rng.integers(40, 400))):
@@ -62,11 +72,12 @@ def test_linear_automata_ragged_segments(eng, oracle, seed):
         fo.append(fo[-1] + T)
     scores = rng.uniform(0, 80, size=(fo[-1], M)).astype(np.float32)
     ordered = check(eng, oracle, np.array(fo, np.uint32), scores, AlignmentAutomata.from_arc_lists(segs))
-    assert ordered <= 2   # continuous random scores: (almost) no exact ties
+    # f32 path scores in the thousands tie often: the generic kernel replays many segments, the ranked one none
+    assert ordered == 0 or kernel == "generic"
 
 
 @pytest.mark.parametrize("seed", range(4))
-def test_general_graphs_with_ties_take_the_ordered_pass(eng, oracle, seed):
+def test_general_graphs_with_ties(eng, oracle, kernel, seed):
     """Integer scores and weights: ties everywhere, states not numbered in activation order."""
     rng = np.random.default_rng(100 + seed)
     M, segs, fo = 17, [], [0]
@@ -75,10 +86,10 @@ def test_general_graphs_with_ties_take_the_ordered_pass(eng, oracle, seed):
         fo.append(fo[-1] + int(rng.integers(0, 40)))
     scores = rng.integers(0, 3, size=(fo[-1], M)).astype(np.float32)
     ordered = check(eng, oracle, np.array(fo, np.uint32), scores, AlignmentAutomata.from_arc_lists(segs))
-    assert ordered >= 20
+    assert (ordered >= 20) if kernel == "generic" else (ordered == 0)
 
 
-def test_general_graphs_continuous_scores(eng, oracle):
+def test_general_graphs_continuous_scores(eng, oracle, kernel):
     rng = np.random.default_rng(7)
     M, segs, fo = 64, [], [0]
     for _ in range(200):
@@ -89,23 +100,38 @@ def test_general_graphs_continuous_scores(eng, oracle):
     check(eng, oracle, np.array(fo, np.uint32), scores, AlignmentAutomata.from_arc_lists(segs))
 
 
-def test_tie_rules_of_the_reference(eng, oracle):
+def test_tie_rules_of_the_reference(eng, oracle, kernel):
     states = [[(1, 3, 0.0), (2, 4, 0.0)], [(3, 5, 0.0)], [(3, 6, 0.0)], []]
     a = AlignmentAutomata.from_arc_lists([(states, 0, {3: 0.0}), ([[(2, 1, 0.0), (1, 0, 0.0)], [], []], 0,
                                                                   {1: 0.0, 2: 0.0})])
     scores = np.ones((3, 8), np.float32)
     em, st, sc = eng.align_device([0, 2, 3], torch.from_numpy(scores).cuda(), a, ld=8)
     assert list(em) == [4, 6, 1] and list(st) == [2, 3, 2] and list(sc) == [2.0, 1.0]
-    assert check(eng, oracle, np.array([0, 2, 3], np.uint32), scores, a) == 4   # 2 segments x 2 calls
+    assert check(eng, oracle, np.array([0, 2, 3], np.uint32), scores, a) == (4 if kernel == "generic" else 0)
 
 
-def test_large_automaton_and_long_segment(eng, oracle):
+def test_large_automaton_and_long_segment(eng, oracle, kernel):
     rng = np.random.default_rng(3)
     M = 4501
     segs = [linear_hmm(rng.integers(0, M, 3000), loop=1.0, forward=0.5, skip=4.0),
             linear_hmm(rng.integers(0, M, 7), loop=0.1, forward=0.5, skip=None)]
     fo = np.array([0, 4000, 4600], np.uint32)
     scores = rng.uniform(0, 100, size=(4600, M)).astype(np.float32)
+    check(eng, oracle, fo, scores, AlignmentAutomata.from_arc_lists(segs))
+
+
+def test_wide_fan_out_and_oscillating_lists(eng, oracle, kernel):
+    """An entry state with hundreds of arcs (wide arrival keys) and a bipartite automaton whose hypothesis list
+    never becomes a fixed point (the ranking is recomputed every frame)."""
+    rng = np.random.default_rng(21)
+    M = 50
+    fan = [[(int(t), int(rng.integers(0, M)), float(rng.integers(0, 2))) for t in rng.permutation(300) + 1]]
+    fan += [[(int(rng.integers(1, 301)), int(rng.integers(0, M)), 0.0), (s, int(rng.integers(0, M)), 1.0)]
+            for s in range(1, 301)]
+    bip = [[(1, 3, 0.0), (3, 4, 0.0)], [(0, 5, 0.0), (2, 6, 1.0)], [(1, 7, 0.0), (3, 8, 0.0)], [(2, 9, 0.0), (0, 1, 0.0)]]
+    segs = [(fan, 0, {7: 0.0, 9: 0.0, 200: 1.0}), (bip, 0, {0: 0.0, 1: 0.0, 2: 0.0, 3: 0.0})]
+    fo = np.array([0, 40, 75], np.uint32)
+    scores = rng.integers(0, 4, size=(75, M)).astype(np.float32)
     check(eng, oracle, fo, scores, AlignmentAutomata.from_arc_lists(segs))
 
 
