@@ -332,7 +332,7 @@ def run_ours(args):
 
     # features in, best paths out: scores stay in HBM and feed the Viterbi consumer
     from rasr_b200.align import AlignmentAutomata, linear_hmm
-    al_segs = min(segs, 64)
+    al_segs = segs
     al_frames = al_segs * SEG_FRAMES
     rng = np.random.default_rng(77 + rank)
     automata = AlignmentAutomata.from_arc_lists(

@@ -60,6 +60,9 @@ struct AlignParams {
     const uint32_t* inOff;  // [nStates + 1] incoming arcs of every (global) state
     const uint32_t* inSrc;  // segment-local source state
     const uint32_t* inSK;   // source state << 16 | position of the arc in its source's arc list (ranked kernel)
+    const uint32_t* inEmSlot;  // ranked kernel: position of the arc's emission in its segment's emission list
+    const uint32_t* emOff;     // [nSeg + 1] the distinct emission indices each segment's automaton uses ...
+    const uint32_t* emList;    // ... (a frame's scores are gathered once per distinct emission, not per arc)
     const uint32_t* inEm;
     const float*    inW;
     const uint32_t* outOff;     // [nStates + 1] the caller's arc lists (Fsa order) ...
@@ -235,12 +238,12 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 // Shared-memory words align_ranked_kernel needs for an automaton of S states, nIn arcs and W key-bitmap words.
-__host__ __device__ inline size_t ranked_smem_words(uint32_t S, uint32_t nIn, uint32_t W, int K) {
-    return (size_t)6 * S + (S + 1) + (size_t)3 * nIn + (size_t)K * nIn + (size_t)3 * W;
+__host__ __device__ inline size_t ranked_smem_words(uint32_t S, uint32_t nIn, uint32_t nEm, uint32_t W, int K) {
+    return (size_t)6 * S + (S + 1) + (size_t)3 * nIn + (size_t)(K + 1) * nEm + (size_t)3 * W;
 }
 
 template<int K>
-__global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) {
+__global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p) {
     extern __shared__ uint32_t smw[];
     const uint32_t tid = threadIdx.x, nThreads = blockDim.x;
     for (uint32_t si = blockIdx.x; si < p.nSeg; si += gridDim.x) {
@@ -258,9 +261,11 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
         uint32_t*      offs    = ancN + S;          // [S + 1] incoming arcs of state s: offs[s] .. offs[s + 1]
         uint32_t*      tabSK   = offs + S + 1;      // [nIn]
         float*         tabW    = (float*)(tabSK + nIn);
-        uint32_t*      tabEm   = (uint32_t*)(tabW + nIn);
-        float*         ring    = (float*)(tabEm + nIn);  // [K][nIn] emission scores of the frames in flight
-        uint32_t*      bm0     = (uint32_t*)(ring + (size_t)K * nIn);
+        uint32_t*      tabEm   = (uint32_t*)(tabW + nIn);  // position in emIds / in a ring row
+        const uint32_t em0     = p.emOff[si], nEm = p.emOff[si + 1] - em0;
+        uint32_t*      emIds   = tabEm + nIn;               // [nEm] distinct emission indices of this automaton
+        float*         ring    = (float*)(emIds + nEm);     // [K][nEm] their scores for the frames in flight
+        uint32_t*      bm0     = (uint32_t*)(ring + (size_t)K * nEm);
         uint32_t*      bm1     = bm0 + W;
         uint32_t*      pref    = bm1 + W;
         for (uint32_t s = tid; s <= S; s += nThreads)
@@ -268,8 +273,10 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
         for (uint32_t a = tid; a < nIn; a += nThreads) {
             tabSK[a] = p.inSK[arcBase + a];
             tabW[a]  = p.inW[arcBase + a];
-            tabEm[a] = p.inEm[arcBase + a];
+            tabEm[a] = p.inEmSlot[arcBase + a];
         }
+        for (uint32_t e = tid; e < nEm; e += nThreads)
+            emIds[e] = p.emList[em0 + e];
         for (uint32_t s = tid; s < S; s += nThreads) {
             cur[s]   = (s == sg.initial) ? 0.f : INFINITY;
             rankO[s] = (s == sg.initial) ? 0u : kNoArc;
@@ -281,9 +288,9 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
         auto prefetch = [&](uint32_t f) {
             if (f < T) {
                 const float* row = p.scores + (size_t)(sg.frame0 + f) * p.ld;
-                float*       dst = ring + (size_t)(f % K) * nIn;
-                for (uint32_t a = tid; a < nIn; a += nThreads)
-                    cp_async4(dst + a, row + tabEm[a]);
+                float*       dst = ring + (size_t)(f % K) * nEm;
+                for (uint32_t e = tid; e < nEm; e += nThreads)
+                    cp_async4(dst + e, row + emIds[e]);
             }
             cp_async_commit();
         };
@@ -294,7 +301,7 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
             cp_async_wait<K - 2>();
             __syncthreads();  // frame t's scores landed; frame t-1's state scores, ranks and ancestors are complete
             prefetch(t + K - 1);
-            const float*   E        = ring + (size_t)(t % K) * nIn;
+            const float*   E        = ring + (size_t)(t % K) * nEm;
             uint32_t*      bm       = (t & 1) ? bm1 : bm0;
             uint32_t*      bk       = p.back + sg.back0 + (size_t)t * S;
             const bool     boundary = (t % kBlockFrames) == 0;
@@ -304,15 +311,16 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
             for (uint32_t s = tid; s < S; s += nThreads) {
                 float    best = INFINITY;
                 uint32_t bestArc = kNoArc, bestKey = 0, firstKey = kNoArc, bestSrc = 0;
-                for (uint32_t a = offs[s]; a < offs[s + 1]; ++a) {
+                const uint32_t a1 = offs[s + 1];
+#pragma unroll 4
+                for (uint32_t a = offs[s]; a < a1; ++a) {  // no early exit: the loads of several arcs overlap
                     const uint32_t sk = tabSK[a], src = sk >> 16;
-                    const uint32_t r  = rankO[src];
-                    if (r == kNoArc)
-                        continue;  // no hypothesis in the previous frame
-                    const uint32_t key = (r << sg.keyShift) | (sk & 0xFFFFu & keyMask);
-                    firstKey           = min(firstKey, key);
-                    const float c      = __fadd_rn(__fadd_rn(cur[src], tabW[a]), E[a]);
-                    if (bestArc == kNoArc || c < best || (c == best && key > bestKey)) {
+                    const uint32_t r   = rankO[src];  // kNoArc: no hypothesis in the previous frame
+                    const float    c   = __fadd_rn(__fadd_rn(cur[src], tabW[a]), E[tabEm[a]]);
+                    const uint32_t key = (r << sg.keyShift) | (sk & keyMask);
+                    const bool     hyp = r != kNoArc;
+                    firstKey           = hyp ? min(firstKey, key) : firstKey;
+                    if (hyp && (bestArc == kNoArc || c < best || (c == best && key > bestKey))) {
                         best    = c;
                         bestArc = a;
                         bestKey = key;
@@ -379,10 +387,12 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
         const uint32_t nBlocks = (T + kBlockFrames - 1) / kBlockFrames;
         uint32_t*      dState  = p.pathState + sg.frame0;
         __shared__ uint32_t bestShared;
-        if (tid == 0) {
+        __shared__ float    redScore[32];
+        __shared__ uint32_t redRank[32], redState[32];
+        {
             float    best = FLT_MAX;
             uint32_t bestState = kNoArc, bestRank = kNoArc;
-            for (uint32_t s = 0; s < S; ++s) {
+            for (uint32_t s = tid; s < S; s += nThreads) {
                 const float fw = p.finalW[sg.state0 + s];
                 if (rankO[s] == kNoArc || fw == INFINITY)
                     continue;
@@ -393,6 +403,32 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
                     bestRank  = rankO[s];
                 }
             }
+            auto merge = [&](float sc, uint32_t rk, uint32_t st) {
+                if (sc < best || (sc == best && rk < bestRank)) {
+                    best      = sc;
+                    bestRank  = rk;
+                    bestState = st;
+                }
+            };
+            for (int d = 16; d > 0; d >>= 1)
+                merge(__shfl_xor_sync(0xFFFFFFFFu, best, d), __shfl_xor_sync(0xFFFFFFFFu, bestRank, d),
+                      __shfl_xor_sync(0xFFFFFFFFu, bestState, d));
+            if ((tid & 31) == 0) {
+                redScore[tid >> 5] = best;
+                redRank[tid >> 5]  = bestRank;
+                redState[tid >> 5] = bestState;
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            float    best = FLT_MAX;
+            uint32_t bestState = kNoArc, bestRank = kNoArc;
+            for (uint32_t w = 0; w < (nThreads + 31) / 32; ++w)
+                if (redScore[w] < best || (redScore[w] == best && redRank[w] < bestRank)) {
+                    best      = redScore[w];
+                    bestRank  = redRank[w];
+                    bestState = redState[w];
+                }
             p.pathScore[si] = best;
             bestShared      = bestState;
             // state after the last frame of every 32-frame block, walking the boundary-ancestor maps backwards
@@ -417,7 +453,7 @@ __global__ void __launch_bounds__(256) align_ranked_kernel(const AlignParams p) 
                 for (uint32_t t = tLast + 1; t-- > tFirst;) {
                     const uint32_t a              = p.back[sg.back0 + (size_t)t * S + s];
                     dState[t]                     = s;
-                    p.pathEmission[sg.frame0 + t] = tabEm[a];
+                    p.pathEmission[sg.frame0 + t] = emIds[tabEm[a]];
                     s                             = tabSK[a] >> 16;
                 }
             }
@@ -439,6 +475,8 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     const uint32_t nArcs   = arcOffsets[nStates];
     // incoming-arc lists (CSR by target), arcs of a state ordered by (source state, arc index)
     std::vector<uint32_t> inOff(nStates + 1, 0), inSrc(nArcs), inSK(nArcs), inEm(nArcs), outToIn(nArcs);
+    std::vector<uint32_t> arcSlot(nArcs), inEmSlot(nArcs), emOff(nSeg + 1, 0), emList, slotOf(ld, 0), seenIn(ld, 0);
+    emList.reserve(nArcs);
     std::vector<float>    inW(nArcs);
     std::vector<AlignSeg> segs(nSeg);
     uint64_t              backTotal = 0, mapTotal = 0;
@@ -467,8 +505,16 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                     return GMM_ERR_ARG;
                 }
                 inOff[s0 + arcTarget[a] + 1]++;
+                const uint32_t e = arcEmission[a];
+                if (seenIn[e] != i + 1) {  // first use of this emission in segment i
+                    seenIn[e] = i + 1;
+                    slotOf[e] = (uint32_t)emList.size() - emOff[i];
+                    emList.push_back(e);
+                }
+                arcSlot[a] = slotOf[e];
             }
         }
+        emOff[i + 1]   = (uint32_t)emList.size();
         uint32_t shift = 0;
         while ((1u << shift) < degree)
             ++shift;
@@ -490,8 +536,8 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
         for (int k = 0; k < 3; ++k)
             maxWords[k] = std::max(maxWords[k], keyBits >= ((uint64_t)1 << 31)
                                                         ? (size_t)1 << 40
-                                                        : ranked_smem_words(sg.states, segArcs, (uint32_t)((keyBits + 31) >> 5),
-                                                                            8 >> k));
+                                                        : ranked_smem_words(sg.states, segArcs, emOff[i + 1] - emOff[i],
+                                                                            (uint32_t)((keyBits + 31) >> 5), 8 >> k));
     }
     for (uint32_t s = 0; s < nStates; ++s)
         inOff[s + 1] += inOff[s];
@@ -504,6 +550,7 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                     inSrc[k]         = s - stateOffsets[i];
                     inSK[k]          = (inSrc[k] << 16) | ((a - arcOffsets[s]) & 0xFFFFu);
                     inEm[k]          = arcEmission[a];
+                    inEmSlot[k]      = arcSlot[a];
                     inW[k]           = arcWeight[a];
                     outToIn[a]       = k;
                 }
@@ -539,6 +586,7 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                  oFin = take((size_t)nStates * 4), oPe = take((size_t)nFrames * 4), oPs = take((size_t)nFrames * 4),
                  oSc = take((size_t)nSeg * 4), oOut = take((nStates + 1) * 4), oTgt = take((size_t)nArcs * 4),
                  oO2i = take((size_t)nArcs * 4), oCnt = take(4), oBack = take(backTotal * 4),
+                 oSlot = take((size_t)nArcs * 4), oEmOff = take((nSeg + 1) * 4), oEmList = take(emList.size() * 4),
                  oMap = take(inFlight ? mapTotal * 4 : 0), oLists = take(inFlight ? 0 : (size_t)grid * 6 * maxStates * 4);
     void* base = nullptr;
     int   rc   = h->reserve(SCR_MISC, off, &base);
@@ -555,7 +603,12 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     GMM_CUDA_TRY(h, up(oEm, inEm.data(), (size_t)nArcs * 4));
     GMM_CUDA_TRY(h, up(oW, inW.data(), (size_t)nArcs * 4));
     GMM_CUDA_TRY(h, up(oFin, finalWeight, (size_t)nStates * 4));
-    if (!inFlight) {
+    if (inFlight) {
+        GMM_CUDA_TRY(h, up(oSlot, inEmSlot.data(), (size_t)nArcs * 4));
+        GMM_CUDA_TRY(h, up(oEmOff, emOff.data(), (nSeg + 1) * 4));
+        GMM_CUDA_TRY(h, up(oEmList, emList.data(), emList.size() * 4));
+    }
+    else {
         GMM_CUDA_TRY(h, up(oOut, arcOffsets, (nStates + 1) * 4));
         GMM_CUDA_TRY(h, up(oTgt, arcTarget, (size_t)nArcs * 4));
         GMM_CUDA_TRY(h, up(oO2i, outToIn.data(), (size_t)nArcs * 4));
@@ -570,6 +623,9 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     p.inSrc        = (const uint32_t*)(d + oSrc);
     p.inSK         = (const uint32_t*)(d + oSK);
     p.inEm         = (const uint32_t*)(d + oEm);
+    p.inEmSlot     = (const uint32_t*)(d + oSlot);
+    p.emOff        = (const uint32_t*)(d + oEmOff);
+    p.emList       = (const uint32_t*)(d + oEmList);
     p.inW          = (const float*)(d + oW);
     p.outOff       = (const uint32_t*)(d + oOut);
     p.outTarget    = (const uint32_t*)(d + oTgt);
@@ -590,7 +646,9 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     if (smemBytes > 48 * 1024)
         GMM_CUDA_TRY(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
     h->timeBegin();
-    kernel<<<grid, 256, smemBytes, h->stream>>>(p);
+    // ranked kernel: one thread per state where that is possible (the frame loop is a latency chain per thread)
+    const int threads = inFlight ? (int)std::min<uint32_t>(1024, std::max<uint32_t>(128, (maxStates + 31) / 32 * 32)) : 256;
+    kernel<<<grid, threads, smemBytes, h->stream>>>(p);
     h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());

@@ -402,7 +402,7 @@ int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffs
     }
     cudaSetDevice(h->device);
     // groups of whole segments whose score block stays bounded (it never leaves the device)
-    const size_t devLd = h->M, maxFrames = std::max<size_t>(1, ((size_t)2 << 30) / (devLd * 4));
+    const size_t devLd = h->M, maxFrames = std::max<size_t>(1, ((size_t)10 << 30) / (devLd * 4));
     uint32_t     s0 = 0;
     while (s0 < nSeg) {
         uint32_t s1 = s0 + 1;
