@@ -121,6 +121,27 @@ int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffs
                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                          const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore);
 
+/* ---- training E-step on the device ----------------------------------------------------
+ * Replaces Speech::KeyedEstimator::processAlignedFeature (src/Speech/KeyedEstimator.cc:108-121) and
+ * Mm::AbstractMixtureSetEstimator::accumulate (src/Mm/AbstractMixtureSetEstimator.cc:117-147): for every frame t
+ * aligned to mixture[t] (0xFFFFFFFF: skip), the best density of that mixture under the uploaded float model's
+ * scorer (reference operation order: the density index is the reference's bit for bit) and the accumulation of the
+ * frame into that density's estimators (MixtureEstimator.cc:86-97, GaussDensityEstimator.cc:22-32,
+ * VectorAccumulator.hh:60-67): mean sum += [w*]x, covariance sum += [w*]x*x, weights += w, all f64.
+ * viterbi = 0 selects the posterior-weighted branch (sum scorer only): every density k with w * p_k > weightThreshold
+ * (reference default: f32 epsilon) accumulates with weight w * p_k.
+ * The estimators live on the device until gmm_accumulator_read; they belong to the float model (uploading a new
+ * float model drops them).  meanIdx[g] names the mean of (mixture, density) slot g as the covariance table of
+ * gmm_upload_float names its covariance; sums are [nMeans x D] / [C x D], mixWeight is [G]. */
+int gmm_accumulator_create(gmm_handle* h, uint32_t nMeans, const uint32_t* meanIdx, int viterbi, double weightThreshold);
+int gmm_accumulator_reset(gmm_handle* h);
+int gmm_accumulate_device(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
+                          uint32_t* d_best);
+int gmm_accumulate_host(gmm_handle* h, uint32_t T, const float* x, const uint32_t* mixture, const double* weight,
+                        uint32_t* best);
+int gmm_accumulator_read(gmm_handle* h, double* meanSum, double* meanWeight, double* covSum, double* covWeight,
+                         double* mixWeight);
+
 /* ---- plumbing -------------------------------------------------------------------------------- */
 /* Page-locked host buffers for the feature / score blocks (cudaMallocHost); NULL on failure. */
 void* gmm_host_alloc(size_t bytes);

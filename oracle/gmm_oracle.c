@@ -419,3 +419,97 @@ float orc_viterbi_align(uint32_t T, const float* scores, size_t ld, uint32_t S, 
     free(hypForState);
     return bestScore;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Training E-step: best density of the aligned mixture + accumulation.
+ *
+ * PARITY UNPINNED for the accumulation itself (the estimator classes need Core's binary/XML streams and
+ * Configuration, not compiled here); the best density and the posteriors are the pinned scorer functions above
+ * restricted to one mixture.  Follows, in frame order and in f64 like the reference:
+ *   Speech/KeyedEstimator.cc:108-121 processAlignedFeature
+ *   AbstractMixtureSetEstimator.cc:117-147 accumulate (viterbi / posterior-weighted with weightThreshold)
+ *   MixtureEstimator.cc:86-97, GaussDensityEstimator.cc:22-32, VectorAccumulator.hh:60-67,
+ *   Utilities.hh:110-146 (sum + y, sum + y*y, sum + w*y, sum + w*y*y evaluated left to right)
+ * sumScorer = 0: GaussDiagonalMaximumFeatureScorer's best density; 1: GaussDiagonalSumFeatureScorer's.
+ * viterbi = 0 needs sumScorer = 1 (only the sum scorer has density posteriors).
+ * mixture[t] = 0xFFFFFFFF skips frame t; weight may be NULL (the unweighted overloads).
+ * Accumulators: meanSum [nMeans x D], meanW [nMeans], covSum [nCov x D], covW [nCov], mixW [G]; best [T] or NULL.
+ * ------------------------------------------------------------------------------------------- */
+static void orc_accumulate_density(const orc_model* m, uint32_t slot, const float* xt, double w, int weighted,
+                                   double* meanSum, double* meanW, double* covSum, double* covW, double* mixW) {
+    uint32_t dns = m->mixDensity[slot], mean = m->densMean[dns], cov = m->densCov[dns];
+    for (uint32_t d = 0; d < m->D; ++d) {
+        double y = (double)xt[d];
+        if (weighted) {
+            meanSum[(size_t)mean * m->D + d] = meanSum[(size_t)mean * m->D + d] + w * y;
+            covSum[(size_t)cov * m->D + d]   = covSum[(size_t)cov * m->D + d] + w * y * y;
+        }
+        else {
+            meanSum[(size_t)mean * m->D + d] = meanSum[(size_t)mean * m->D + d] + y;
+            covSum[(size_t)cov * m->D + d]   = covSum[(size_t)cov * m->D + d] + y * y;
+        }
+    }
+    /* unweighted: ++weight_ (VectorAccumulator.hh:61), ++weights_[i] (MixtureEstimator.cc:88) */
+    meanW[mean] += weighted ? w : 1.0;
+    covW[cov] += weighted ? w : 1.0;
+    mixW[slot] += weighted ? w : 1.0;
+}
+
+void orc_accumulate(const orc_model* m, const float* isr, const float* logNorm, const float* w2, const float* x,
+                    size_t T, const uint32_t* mixture, const double* weight, int sumScorer, int viterbi,
+                    double weightThreshold, double* meanSum, double* meanW, double* covSum, double* covW,
+                    double* mixW, uint32_t* best) {
+    float* sc = (float*)malloc(sizeof(float) * (m->mixOffsets[m->M] ? m->mixOffsets[m->M] : 1));
+    for (size_t t = 0; t < T; ++t) {
+        uint32_t mix = mixture[t];
+        if (best)
+            best[t] = 0xFFFFFFFFu;
+        if (mix == 0xFFFFFFFFu)
+            continue;
+        const float* xt = x + t * m->D;
+        uint32_t     a = m->mixOffsets[mix], b = m->mixOffsets[mix + 1];
+        float        bestScore   = FLT_MAX;
+        size_t       bestDensity = (size_t)-1;
+        for (uint32_t k = a; k < b; ++k) {
+            uint32_t dns = m->mixDensity[k], cov = m->densCov[dns];
+            float    dist =
+                    orc_distance(xt, m->means + (size_t)m->densMean[dns] * m->D, isr + (size_t)cov * m->D, m->D);
+            if (sumScorer) {
+                float s = w2[k] + logNorm[cov] + dist;
+                sc[k]   = (float)(0.5 * s);
+                if (bestScore > sc[k]) {
+                    bestScore   = sc[k];
+                    bestDensity = k - a;
+                }
+            }
+            else {
+                double s = (double)w2[k] + (double)logNorm[cov] + (double)dist;
+                if ((double)bestScore > s) {
+                    bestScore   = (float)s;
+                    bestDensity = k - a;
+                }
+            }
+        }
+        if (best)
+            best[t] = (uint32_t)bestDensity;
+        double w = weight ? weight[t] : 1.0;
+        if (viterbi) {
+            if (bestDensity != (size_t)-1)
+                orc_accumulate_density(m, a + (uint32_t)bestDensity, xt, w, weight != NULL, meanSum, meanW, covSum,
+                                       covW, mixW);
+        }
+        else if (sumScorer) {
+            float sumExp = 0.f;
+            for (uint32_t k = a; k < b; ++k)
+                sumExp += expf(bestScore - sc[k]);
+            float score = bestScore - logf(sumExp);
+            for (uint32_t k = a; k < b; ++k) {
+                double dnsWeight   = (double)expf(score - sc[k]); /* std::vector<Mm::Weight> of f32 exp results */
+                double finalWeight = w * dnsWeight;
+                if (finalWeight > weightThreshold)
+                    orc_accumulate_density(m, k, xt, finalWeight, 1, meanSum, meanW, covSum, covW, mixW);
+            }
+        }
+    }
+    free(sc);
+}

@@ -180,6 +180,25 @@ def viterbi_align(frame_offsets, scores, automata):
     return em, st, sc
 
 
+def accumulate(ms, x, mixture, weight=None, *, sum_scorer=False, viterbi=True, weight_threshold=0.0, tables=None):
+    """orc_accumulate: the reference's E-step in frame order.
+    -> dict(mean_sum [nMeans, D], mean_weight, cov_sum [nCov, D], cov_weight, mix_weight [G], best [T])."""
+    isr, logn, w2 = tables if tables is not None else float_tables(ms)
+    x = np.ascontiguousarray(x, np.float32)
+    mixture = np.ascontiguousarray(mixture, np.uint32)
+    weight = None if weight is None else np.ascontiguousarray(weight, np.float64)
+    T, D = x.shape
+    n_means, n_cov, G = ms.n_means, ms.n_cov, ms.G
+    out = dict(mean_sum=np.zeros((n_means, D)), mean_weight=np.zeros(n_means), cov_sum=np.zeros((n_cov, D)),
+               cov_weight=np.zeros(n_cov), mix_weight=np.zeros(G), best=np.empty(T, np.uint32))
+    cm = _cmodel(ms)
+    lib().orc_accumulate(C.byref(cm), _p(isr), _p(logn), _p(w2), _p(x), C.c_size_t(T), _p(mixture), _p(weight),
+                         C.c_int(int(sum_scorer)), C.c_int(int(viterbi)), C.c_double(weight_threshold),
+                         _p(out["mean_sum"]), _p(out["mean_weight"]), _p(out["cov_sum"]), _p(out["cov_weight"]),
+                         _p(out["mix_weight"]), _p(out["best"]))
+    return out
+
+
 def ref_available() -> bool:
     return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
 

@@ -34,6 +34,11 @@ SYMBOLS = [
     ("gmm_align_device", _i, [_vp, _u32, _vp, _vp, _sz] + [_vp] * 10),
     ("gmm_align_ordered_count", C.c_uint64, [_vp]),
     ("gmm_score_align_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
+    ("gmm_accumulator_create", _i, [_vp, _u32, _vp, _i, C.c_double]),
+    ("gmm_accumulator_reset", _i, [_vp]),
+    ("gmm_accumulate_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
+    ("gmm_accumulate_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
+    ("gmm_accumulator_read", _i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     ("gmm_host_alloc", _vp, [_sz]),
     ("gmm_host_free", None, [_vp]),
     ("gmm_sync", _i, [_vp]),
@@ -222,6 +227,44 @@ class Engine:
     @property
     def align_ordered_count(self) -> int:
         return int(self._lib.gmm_align_ordered_count(self._h))
+
+    # -- training E-step -------------------------------------------------------------------------
+    def create_accumulators(self, mean_idx, n_means=None, viterbi=True, weight_threshold=float(np.finfo(np.float32).eps)):
+        """Estimators for the uploaded float model; mean_idx [G] names the mean of every (mixture, density) slot."""
+        mean_idx = _np(mean_idx, np.uint32)
+        if mean_idx.shape != (self.G,):
+            raise ValueError(f"mean_idx must be [{self.G}]")
+        n_means = int(mean_idx.max()) + 1 if n_means is None else int(n_means)
+        self._check(self._lib.gmm_accumulator_create(self._h, n_means, _ptr(mean_idx), int(bool(viterbi)),
+                                                     C.c_double(float(weight_threshold))), "gmm_accumulator_create")
+        self.n_means = n_means
+
+    def reset_accumulators(self):
+        self._check(self._lib.gmm_accumulator_reset(self._h), "gmm_accumulator_reset")
+
+    def accumulate_host(self, x, mixture, weight=None, want_best=True):
+        """Frames x [T, D] aligned to `mixture` [T] (0xFFFFFFFF skips) -> chosen density per frame | None."""
+        x = _np(x, np.float32)
+        mixture = _np(mixture, np.uint32)
+        weight = None if weight is None else _np(weight, np.float64)
+        if x.ndim != 2 or x.shape[1] != self.D or mixture.shape != (x.shape[0],):
+            raise ValueError(f"features must be [T, {self.D}] and mixture [T]")
+        best = np.empty(x.shape[0], np.uint32) if want_best else None
+        self._check(self._lib.gmm_accumulate_host(self._h, x.shape[0], _ptr(x), _ptr(mixture), _ptr(weight), _ptr(best)),
+                    "gmm_accumulate_host")
+        return best
+
+    def accumulate_device(self, T, d_x, d_mixture, d_weight=None, d_best=None):
+        self._check(self._lib.gmm_accumulate_device(self._h, int(T), _ptr(d_x), _ptr(d_mixture), _ptr(d_weight),
+                                                    _ptr(d_best)), "gmm_accumulate_device")
+
+    def read_accumulators(self, n_cov):
+        out = dict(mean_sum=np.empty((self.n_means, self.D)), mean_weight=np.empty(self.n_means),
+                   cov_sum=np.empty((n_cov, self.D)), cov_weight=np.empty(n_cov), mix_weight=np.empty(self.G))
+        self._check(self._lib.gmm_accumulator_read(self._h, _ptr(out["mean_sum"]), _ptr(out["mean_weight"]),
+                                                   _ptr(out["cov_sum"]), _ptr(out["cov_weight"]),
+                                                   _ptr(out["mix_weight"])), "gmm_accumulator_read")
+        return out
 
     # -- quantized engine -------------------------------------------------------------------------
     def upload_quant(self, offsets, qmean, cov_idx, qconst, isr_scaled, scaling_squared):

@@ -50,6 +50,7 @@ static void releaseFloatModel(gmm_handle* h) {
     h->floatValid = false;
     h->direct     = DirectModel();
     h->tensor     = TensorModel();
+    h->accum      = AccumModel();  // its arrays were in `owned`
 }
 
 static void releaseQuantModel(gmm_handle* h) {
@@ -437,6 +438,149 @@ int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffs
             return rc;
         s0 = s1;
     }
+    return GMM_OK;
+}
+
+// ---- training E-step -------------------------------------------------------------------------------------------
+int gmm_accumulator_create(gmm_handle* h, uint32_t nMeans, const uint32_t* meanIdx, int viterbi, double weightThreshold) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid) {
+        h->setError("gmm_accumulator_create: no float model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (!meanIdx || nMeans == 0) {
+        h->setError("gmm_accumulator_create: NULL mean index table");
+        return GMM_ERR_ARG;
+    }
+    if (!viterbi && h->mode != GMM_MODE_SUM) {
+        // CachedAssigningFeatureScorer::calculateDensityPosteriorProbabilities is only implemented by the sum scorer
+        h->setError("gmm_accumulator_create: posterior-weighted accumulation needs the sum scorer (GMM_MODE_SUM)");
+        return GMM_ERR_UNSUPPORTED;
+    }
+    for (uint32_t g = 0; g < h->G; ++g)
+        if (meanIdx[g] >= nMeans) {
+            h->setError("gmm_accumulator_create: mean index out of range");
+            return GMM_ERR_ARG;
+        }
+    cudaSetDevice(h->device);
+    AccumModel& am = h->accum;
+    if (am.valid) {
+        h->setError("gmm_accumulator_create: this float model already has accumulators (upload the model again to replace)");
+        return GMM_ERR_ARG;
+    }
+    int rc;
+    if ((rc = h->upload((void**)&am.meanIdx, meanIdx, (size_t)h->G * 4)))
+        return rc;
+    const size_t D = h->D, n = (size_t)nMeans * D + nMeans + (size_t)h->C * D + h->C + h->G;
+    if ((rc = h->devAlloc((void**)&am.block, n * sizeof(double))))
+        return rc;
+    am.blockBytes = n * sizeof(double);
+    am.meanSum    = am.block;
+    am.meanW      = am.meanSum + (size_t)nMeans * D;
+    am.covSum     = am.meanW + nMeans;
+    am.covW       = am.covSum + (size_t)h->C * D;
+    am.mixW       = am.covW + h->C;
+    am.nMeans     = nMeans;
+    am.viterbi    = viterbi ? 1 : 0;
+    am.weightThreshold = weightThreshold;
+    GMM_CUDA_TRY(h, cudaMemsetAsync(am.block, 0, am.blockBytes, h->stream));
+    am.valid = true;
+    return GMM_OK;
+}
+
+int gmm_accumulator_reset(gmm_handle* h) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->accum.valid) {
+        h->setError("gmm_accumulator_reset: no accumulators");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    GMM_CUDA_TRY(h, cudaMemsetAsync(h->accum.block, 0, h->accum.blockBytes, h->stream));
+    return GMM_OK;
+}
+
+int gmm_accumulator_read(gmm_handle* h, double* meanSum, double* meanWeight, double* covSum, double* covWeight,
+                         double* mixWeight) {
+    if (!h)
+        return GMM_ERR_ARG;
+    const AccumModel& am = h->accum;
+    if (!am.valid) {
+        h->setError("gmm_accumulator_read: no accumulators");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    const size_t D = h->D;
+    auto down = [&](double* dst, const double* src, size_t n) {
+        return dst && n ? cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream) : cudaSuccess;
+    };
+    GMM_CUDA_TRY(h, down(meanSum, am.meanSum, (size_t)am.nMeans * D));
+    GMM_CUDA_TRY(h, down(meanWeight, am.meanW, am.nMeans));
+    GMM_CUDA_TRY(h, down(covSum, am.covSum, (size_t)h->C * D));
+    GMM_CUDA_TRY(h, down(covWeight, am.covW, h->C));
+    GMM_CUDA_TRY(h, down(mixWeight, am.mixW, h->G));
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GMM_OK;
+}
+
+int gmm_accumulate_device(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
+                          uint32_t* d_best) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid || !h->accum.valid) {
+        h->setError("gmm_accumulate: no float model or no accumulators (gmm_accumulator_create)");
+        return GMM_ERR_ARG;
+    }
+    if (T == 0)
+        return GMM_OK;
+    if (!d_x || !d_mixture) {
+        h->setError("gmm_accumulate: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return gmm_accum_launch(h, T, d_x, d_mixture, d_weight, d_best);
+}
+
+int gmm_accumulate_host(gmm_handle* h, uint32_t T, const float* x, const uint32_t* mixture, const double* weight,
+                        uint32_t* best) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid || !h->accum.valid) {
+        h->setError("gmm_accumulate: no float model or no accumulators (gmm_accumulator_create)");
+        return GMM_ERR_ARG;
+    }
+    if (T == 0)
+        return GMM_OK;
+    if (!x || !mixture) {
+        h->setError("gmm_accumulate: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    for (uint32_t t = 0; t < T; ++t)
+        if (mixture[t] != 0xFFFFFFFFu && mixture[t] >= h->M) {
+            h->setError("gmm_accumulate: mixture index out of range");
+            return GMM_ERR_ARG;
+        }
+    void *dx = nullptr, *dm = nullptr;
+    int   rc;
+    if ((rc = h->reserve(SCR_X, (size_t)T * h->D * 4, &dx)))
+        return rc;
+    // mixture indices, weights and chosen densities share one scratch reservation
+    const size_t oW = ((size_t)T * 4 + 255) & ~(size_t)255, oB = oW + (((size_t)T * 8 + 255) & ~(size_t)255);
+    if ((rc = h->reserve(SCR_BEST, oB + (size_t)T * 4, &dm)))
+        return rc;
+    char* base = (char*)dm;
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x, (size_t)T * h->D * 4, cudaMemcpyHostToDevice, h->stream));
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(base, mixture, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+    if (weight)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(base + oW, weight, (size_t)T * 8, cudaMemcpyHostToDevice, h->stream));
+    if ((rc = gmm_accum_launch(h, T, (const float*)dx, (const uint32_t*)base, weight ? (const double*)(base + oW) : nullptr,
+                               best ? (uint32_t*)(base + oB) : nullptr)))
+        return rc;
+    if (best)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(best, base + oB, (size_t)T * 4, cudaMemcpyDeviceToHost, h->stream));
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     return GMM_OK;
 }
 

@@ -59,6 +59,18 @@ struct QuantModel {
     uint32_t* offsets = nullptr;  // [M+1]
 };
 
+// estimators of the training E-step (gmm_accum.cu): f64 sums per mean / covariance / (mixture, density)
+struct AccumModel {
+    bool      valid   = false;
+    int       viterbi = 1;
+    double    weightThreshold = 0.0;
+    uint32_t  nMeans  = 0;
+    uint32_t* meanIdx = nullptr;  // [G] mean of every (mixture, density) slot
+    double*   block   = nullptr;  // one allocation: the five arrays below
+    size_t    blockBytes = 0;
+    double *  meanSum = nullptr, *meanW = nullptr, *covSum = nullptr, *covW = nullptr, *mixW = nullptr;
+};
+
 // quantized scorer on the integer tensor path (gmm_qtc.cu); valid only for models that meet its requirements
 struct QTensorModel {
     bool      valid      = false;
@@ -106,6 +118,7 @@ struct gmm_handle {
     TensorModel tensor;
     QuantModel  quant;
     QTensorModel qtensor;
+    AccumModel   accum;
 
     // scratch (grown on demand)
     void*  scratch[8]      = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -132,6 +145,8 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore);
+int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
+                     uint32_t* d_best);
 int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, const int32_t* c2);
 int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
                   uint8_t* d_qx, size_t ld);

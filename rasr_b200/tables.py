@@ -36,6 +36,11 @@ def flatten(ms: MixtureSetData):
     return mean, cov_idx
 
 
+def mean_index(ms: MixtureSetData) -> np.ndarray:
+    """Mean of every (mixture, density) slot, for the E-step's estimators (gmm_accumulator_create)."""
+    return np.ascontiguousarray(ms.dens_mean[ms.mix_density], dtype=np.uint32)
+
+
 def _log_norm(variances: np.ndarray) -> np.ndarray:
     D = variances.shape[1]
     # sequential f64 sum over d, as the reference's std::accumulate
