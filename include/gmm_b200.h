@@ -121,6 +121,15 @@ int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffs
                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                          const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore);
 
+/* The training pass: as gmm_score_align_host, then every aligned frame is accumulated into the estimators of
+ * gmm_accumulator_create (below) with its path emission as mixture -- AlignmentNode -> KeyedEstimator in the
+ * reference, here without the path leaving the device: pathEmission, pathState and pathScore may be NULL. */
+int gmm_score_align_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                    const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                                    const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                                    const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState,
+                                    float* pathScore);
+
 /* ---- training E-step on the device ----------------------------------------------------
  * Replaces Speech::KeyedEstimator::processAlignedFeature (src/Speech/KeyedEstimator.cc:108-121) and
  * Mm::AbstractMixtureSetEstimator::accumulate (src/Mm/AbstractMixtureSetEstimator.cc:117-147): for every frame t

@@ -34,6 +34,7 @@ SYMBOLS = [
     ("gmm_align_device", _i, [_vp, _u32, _vp, _vp, _sz] + [_vp] * 10),
     ("gmm_align_ordered_count", C.c_uint64, [_vp]),
     ("gmm_score_align_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
+    ("gmm_score_align_accumulate_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
     ("gmm_accumulator_create", _i, [_vp, _u32, _vp, _i, C.c_double]),
     ("gmm_accumulator_reset", _i, [_vp]),
     ("gmm_accumulate_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
@@ -208,17 +209,22 @@ class Engine:
                                                _ptr(em), _ptr(st), _ptr(sc)), "gmm_align_device")
         return em, st, sc
 
-    def score_align_host(self, frame_offsets, x, automata, want_states=True):
-        """Host features [frames, D] -> float scorer -> alignment; only the paths come back."""
+    def score_align_host(self, frame_offsets, x, automata, want_states=True, accumulate=False, want_paths=True):
+        """Host features [frames, D] -> float scorer -> alignment; only the paths come back.
+        accumulate=True: the aligned frames also go into the estimators (create_accumulators), on the device;
+        want_paths=False then returns nothing at all."""
         fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
         a = automata
         x = _np(x, np.float32)
         if x.ndim != 2 or x.shape != (n_frames, self.D):
             raise ValueError(f"features must be [{n_frames}, {self.D}]")
-        em = np.empty(n_frames, np.uint32)
-        st = np.empty(n_frames, np.uint32) if want_states else None
-        sc = np.empty(max(n_seg, 0), np.float32)
-        self._check(self._lib.gmm_score_align_host(self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets),
+        if not want_paths and not accumulate:
+            raise ValueError("want_paths=False only makes sense with accumulate=True")
+        em = np.empty(n_frames, np.uint32) if want_paths else None
+        st = np.empty(n_frames, np.uint32) if want_states and want_paths else None
+        sc = np.empty(max(n_seg, 0), np.float32) if want_paths else None
+        fn = self._lib.gmm_score_align_accumulate_host if accumulate else self._lib.gmm_score_align_host
+        self._check(fn(self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets),
                                                    _ptr(a.arc_offsets), _ptr(a.arc_target), _ptr(a.arc_emission),
                                                    _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight),
                                                    _ptr(em), _ptr(st), _ptr(sc)), "gmm_score_align_host")

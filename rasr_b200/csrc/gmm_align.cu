@@ -468,7 +468,10 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
 int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
                      const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
-                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore) {
+                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
+                     const uint32_t** d_pathEmission) {
+    if (d_pathEmission)
+        *d_pathEmission = nullptr;
     if (nSeg == 0)
         return GMM_OK;
     const uint32_t nStates = stateOffsets[nSeg], nFrames = frameOffsets[nSeg];
@@ -652,10 +655,14 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(pathEmission, d + oPe, (size_t)nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (d_pathEmission)
+        *d_pathEmission = p.pathEmission;  // stays valid until the next alignment call on this handle
+    if (pathEmission)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(pathEmission, d + oPe, (size_t)nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
     if (pathState)
         GMM_CUDA_TRY(h, cudaMemcpyAsync(pathState, d + oPs, (size_t)nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(pathScore, d + oSc, (size_t)nSeg * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (pathScore)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(pathScore, d + oSc, (size_t)nSeg * 4, cudaMemcpyDeviceToHost, h->stream));
     uint32_t ordered = 0;
     GMM_CUDA_TRY(h, cudaMemcpyAsync(&ordered, d + oCnt, 4, cudaMemcpyDeviceToHost, h->stream));
     GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));

@@ -384,7 +384,9 @@ uint64_t gmm_align_ordered_count(const gmm_handle* h) {
     return h ? h->alignOrdered : 0;
 }
 
-int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+}  // extern "C"
+
+static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
                          const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                          const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore) {
@@ -396,8 +398,12 @@ int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffs
     }
     if (nSeg == 0)
         return GMM_OK;
-    if (!frameOffsets || !stateOffsets || !arcOffsets || !initialState || !finalWeight || !pathEmission || !pathScore ||
-        (frameOffsets[nSeg] && !x)) {
+    if (accumulate && !h->accum.valid) {
+        h->setError("gmm_score_align_accumulate: no accumulators (gmm_accumulator_create)");
+        return GMM_ERR_ARG;
+    }
+    if (!frameOffsets || !stateOffsets || !arcOffsets || !initialState || !finalWeight ||
+        (!accumulate && (!pathEmission || !pathScore)) || (frameOffsets[nSeg] && !x)) {
         h->setError("gmm_score_align: NULL argument");
         return GMM_ERR_ARG;
     }
@@ -420,6 +426,7 @@ int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffs
         for (uint32_t s = 0; s <= so[n]; ++s)
             ao[s] = arcOffsets[st0 + s] - a0;
         void *dx = nullptr, *ds = nullptr;
+        const uint32_t* dPath = nullptr;
         int   rc;
         if ((rc = h->reserve(SCR_X, (size_t)std::max(1u, T) * h->D * 4, &dx)))
             return rc;
@@ -434,11 +441,34 @@ int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffs
         if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, devLd, so.data(), ao.data(),
                                    arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
                                    arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0,
-                                   pathEmission + f0, pathState ? pathState + f0 : nullptr, pathScore + s0)))
+                                   pathEmission ? pathEmission + f0 : nullptr, pathState ? pathState + f0 : nullptr,
+                                   pathScore ? pathScore + s0 : nullptr, &dPath)))
+            return rc;
+        // the aligned frames go straight into the estimators: the path is the per-frame mixture (kNoArc: skip)
+        if (accumulate && T && (rc = gmm_accum_launch(h, T, (const float*)dx, dPath, nullptr, nullptr)))
             return rc;
         s0 = s1;
     }
     return GMM_OK;
+}
+
+extern "C" {
+
+int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                         const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                         const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                         const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore) {
+    return scoreAlign(h, false, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
+                      initialState, finalWeight, pathEmission, pathState, pathScore);
+}
+
+int gmm_score_align_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                    const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                                    const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                                    const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState,
+                                    float* pathScore) {
+    return scoreAlign(h, true, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
+                      initialState, finalWeight, pathEmission, pathState, pathScore);
 }
 
 // ---- training E-step -------------------------------------------------------------------------------------------

@@ -144,7 +144,8 @@ int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, 
 int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
                      const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
-                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore);
+                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
+                     const uint32_t** d_pathEmission = nullptr);
 int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
                      uint32_t* d_best);
 int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, const int32_t* c2);

@@ -126,3 +126,11 @@ def test_align_then_accumulate_on_device(eng, oracle):
     want = oracle.accumulate(ms, x, em, tables=tab)
     assert got["mix_weight"].sum() == 640
     assert_accumulators(got, want, exact_weights=True)
+    # the same as one call, with and without the paths coming back
+    eng.reset_accumulators()
+    em2, st2, sc2 = eng.score_align_host(fo, x, au, accumulate=True)
+    assert np.array_equal(em2, em) and np.array_equal(st2, st) and np.array_equal(sc2, sc)
+    assert_accumulators(eng.read_accumulators(ms.n_cov), want, exact_weights=True)
+    eng.reset_accumulators()
+    assert eng.score_align_host(fo, x, au, accumulate=True, want_paths=False) == (None, None, None)
+    assert_accumulators(eng.read_accumulators(ms.n_cov), want, exact_weights=True)
