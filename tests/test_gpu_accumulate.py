@@ -134,3 +134,32 @@ def test_align_then_accumulate_on_device(eng, oracle):
     eng.reset_accumulators()
     assert eng.score_align_host(fo, x, au, accumulate=True, want_paths=False) == (None, None, None)
     assert_accumulators(eng.read_accumulators(ms.n_cov), want, exact_weights=True)
+
+
+def test_training_iteration_through_mixset_file(eng, oracle, tmp_path):
+    """GPU E-step -> MIXSET accumulator file -> M-step -> text model -> upload: the model the reference's own
+    tools would produce from the oracle's accumulators, to f32 rounding."""
+    from rasr_b200 import model_io
+    ms = synth.make_model(M=40, K=6, D=24, seed=21, covariance="pooled")
+    T = 20000
+    x = synth.make_features(ms, T, seed=8)
+    mixture = np.random.default_rng(8).integers(0, ms.M, T).astype(np.uint32)
+    tab = upload(eng, ms, capi.MODE_MAX)
+    eng.create_accumulators(tables.mean_index(ms), ms.n_means)
+    eng.accumulate_host(x, mixture, want_best=False)
+    est = model_io.MixtureSetEstimatorData.from_accumulators(ms, eng.read_accumulators(ms.n_cov))
+    model_io.write_mixset(est, tmp_path / "acc.mix")
+    new = model_io.read_mixset(tmp_path / "acc.mix").estimate()
+    ref = model_io.MixtureSetEstimatorData.from_accumulators(ms, oracle.accumulate(ms, x, mixture, tables=tab)).estimate()
+    assert np.array_equal(new.mix_offsets, ref.mix_offsets) and np.array_equal(new.mix_density, ref.mix_density)
+    assert np.array_equal(new.mix_logw, ref.mix_logw)                 # counts are exact
+    np.testing.assert_allclose(new.means, ref.means, rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(new.variances, ref.variances, rtol=1e-6)
+    model_io.write_mixture_set_text_exact(new, tmp_path / "new.pms.gz")
+    loaded = model_io.read_mixture_set_text(tmp_path / "new.pms.gz")
+    t = oracle_float_tables(loaded)
+    eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=capi.MODE_MAX,
+                     kernel=capi.KERNEL_DIRECT)
+    s, b = eng.score_host(x[:64])
+    so, bo = oracle.score_max(loaded, x[:64])
+    assert np.array_equal(s.view(np.uint32), so.view(np.uint32)) and np.array_equal(b, bo)
