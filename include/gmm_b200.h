@@ -151,6 +151,19 @@ int gmm_accumulate_host(gmm_handle* h, uint32_t T, const float* x, const uint32_
 int gmm_accumulator_read(gmm_handle* h, double* meanSum, double* meanWeight, double* covSum, double* covWeight,
                          double* mixWeight);
 
+/* ---- front end fused into the frame upload ---------------------------------------------
+ * Replaces the reference's lda.flow network (src/Tools/FeatureExtraction/share/lda.flow): sliding window
+ * (signal-vector-f32-sequence-concatenation: `length` frames, `right` of them after the current one, one output
+ * per input frame, a missing neighbour = the closest frame of the segment; src/Signal/VectorSequenceConcatenation.hh:
+ * 85-100, src/Signal/Delay.hh:32-46) followed by signal-matrix-multiplication-f32 (src/Signal/MatrixMult.hh:70;
+ * out[n] = sum_i matrix[n][i] * in[i] in f32, left to right: src/Math/Matrix.hh:482-489, Math/Vector.hh:95-101;
+ * bit-identical to the reference build).  matrix is [D x baseDim*length], row major, host memory.
+ * Once set, every *_host entry point takes BASE features [T x baseDim] and transforms them on the device (windows
+ * stay inside a segment; entry points without segments treat the call as one segment).  matrix = NULL clears. */
+int gmm_set_lda(gmm_handle* h, uint32_t baseDim, uint32_t length, uint32_t right, uint32_t D, const float* matrix);
+/* d_base [frames x baseDim] -> d_x [frames x D], both device; frameOffsets: host, nSeg + 1 entries. */
+int gmm_lda_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_base, float* d_x);
+
 /* ---- plumbing -------------------------------------------------------------------------------- */
 /* Page-locked host buffers for the feature / score blocks (cudaMallocHost); NULL on failure. */
 void* gmm_host_alloc(size_t bytes);

@@ -513,3 +513,45 @@ void orc_accumulate(const orc_model* m, const float* isr, const float* logNorm, 
     }
     free(sc);
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Front end: sliding window + matrix multiplication (lda.flow)
+ *
+ * The matrix product is PINNED: tests/test_oracle_vs_ref.py compares it with the reference's own
+ * Math::Matrix<f32> * Math::Vector<f32> (oracle/_ref/ref_matmul, built by oracle/ref_build/Makefile);
+ * tests/golden/lda_matmul.npz holds outputs of that binary.  The window (Flow DelayNode) is restated
+ * from the source: parity unpinned for the margin handling.
+ *   Signal/VectorSequenceConcatenation.hh:85-100  window of frames t-left .. t+right, oldest first
+ *   Signal/Delay.hh:32-46, Delay.cc:30-31,171-174  margin-condition present-not-empty (lda.flow), margin-policy
+ *                                                  copy: a missing frame is the closest existing one
+ *   Math/Matrix.hh:482-489, Math/Vector.hh:95-101  result[n] = sum_i a[n][i] * v[i], f32, left to right (the
+ *                                                  reference build keeps the scalar loop: mulss / addss)
+ * base [T x baseDim]; segments [frameOffsets[s], frameOffsets[s+1]); matrix [D x baseDim*length]; out [T x D].
+ * ------------------------------------------------------------------------------------------- */
+void orc_matrix_vector(const float* matrix, uint32_t rows, uint32_t cols, const float* v, float* out) {
+    for (uint32_t n = 0; n < rows; ++n) {
+        float result = 0.f;
+        for (uint32_t i = 0; i < cols; ++i)
+            result += matrix[(size_t)n * cols + i] * v[i];
+        out[n] = result;
+    }
+}
+
+void orc_lda(const float* base, uint32_t nSeg, const uint32_t* frameOffsets, uint32_t baseDim, uint32_t length,
+             uint32_t right, const float* matrix, uint32_t D, float* out) {
+    const uint32_t Din = baseDim * length;
+    float*         win = (float*)malloc(sizeof(float) * (Din ? Din : 1));
+    const long     left = (long)length - 1 - (long)right;
+    for (uint32_t s = 0; s < nSeg; ++s) {
+        const long b = frameOffsets[s], e = frameOffsets[s + 1];
+        for (long t = b; t < e; ++t) {
+            for (long r = -left; r <= (long)right; ++r) {
+                long f = t + r;
+                f      = f < b ? b : f >= e ? e - 1 : f;
+                memcpy(win + (size_t)(r + left) * baseDim, base + (size_t)f * baseDim, sizeof(float) * baseDim);
+            }
+            orc_matrix_vector(matrix, D, Din, win, out + (size_t)t * D);
+        }
+    }
+    free(win);
+}

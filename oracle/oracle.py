@@ -199,6 +199,46 @@ def accumulate(ms, x, mixture, weight=None, *, sum_scorer=False, viterbi=True, w
     return out
 
 
+def lda(base, frame_offsets, length, right, matrix):
+    """orc_lda: window (length frames, `right` after the current one, clamped to the segment) + matrix product."""
+    base = np.ascontiguousarray(base, np.float32)
+    matrix = np.ascontiguousarray(matrix, np.float32)
+    fo = np.ascontiguousarray(frame_offsets, np.uint32)
+    T, base_dim = base.shape
+    D = matrix.shape[0]
+    assert matrix.shape[1] == base_dim * length
+    out = np.empty((T, D), np.float32)
+    lib().orc_lda(_p(base), C.c_uint32(fo.shape[0] - 1), _p(fo), C.c_uint32(base_dim), C.c_uint32(length),
+                  C.c_uint32(right), _p(matrix), C.c_uint32(D), _p(out))
+    return out
+
+
+def matrix_vector(matrix, vectors):
+    matrix = np.ascontiguousarray(matrix, np.float32)
+    vectors = np.ascontiguousarray(vectors, np.float32)
+    out = np.empty((vectors.shape[0], matrix.shape[0]), np.float32)
+    for i in range(vectors.shape[0]):
+        lib().orc_matrix_vector(_p(matrix), C.c_uint32(matrix.shape[0]), C.c_uint32(matrix.shape[1]),
+                                _p(vectors[i]), _p(out[i]))
+    return out
+
+
+REF_MATMUL = os.path.join(HERE, "_ref", "ref_matmul")
+
+
+def run_ref_matmul(matrix, vectors):
+    """The reference's Math::Matrix<f32> * Math::Vector<f32> (oracle/_ref/ref_matmul)."""
+    matrix = np.ascontiguousarray(matrix, np.float32)
+    vectors = np.ascontiguousarray(vectors, np.float32)
+    with tempfile.TemporaryDirectory() as d:
+        with open(os.path.join(d, "in"), "wb") as f:
+            f.write(np.array([matrix.shape[0], matrix.shape[1], vectors.shape[0]], np.uint32).tobytes())
+            f.write(matrix.tobytes())
+            f.write(vectors.tobytes())
+        subprocess.check_call([REF_MATMUL, os.path.join(d, "in"), os.path.join(d, "out")])
+        return np.fromfile(os.path.join(d, "out"), np.float32).reshape(vectors.shape[0], matrix.shape[0])
+
+
 def ref_available() -> bool:
     return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
 

@@ -40,6 +40,8 @@ SYMBOLS = [
     ("gmm_accumulate_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
     ("gmm_accumulate_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
     ("gmm_accumulator_read", _i, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    ("gmm_set_lda", _i, [_vp, _u32, _u32, _u32, _u32, _vp]),
+    ("gmm_lda_device", _i, [_vp, _u32, _vp, _vp, _vp]),
     ("gmm_host_alloc", _vp, [_sz]),
     ("gmm_host_free", None, [_vp]),
     ("gmm_sync", _i, [_vp]),
@@ -165,8 +167,8 @@ class Engine:
     def score_host(self, x, want_best=True, ld=None, out=None):
         """x [T, D] f32 host array -> (scores [T, M] f32, best [T, M] u32 | None), host arrays."""
         x = _np(x, np.float32)
-        if x.ndim != 2 or x.shape[1] != self.D:
-            raise ValueError(f"features must be [T, {self.D}]")
+        if x.ndim != 2 or x.shape[1] != self._in_dim(self.D):
+            raise ValueError(f"features must be [T, {self._in_dim(self.D)}]")
         T = x.shape[0]
         ld = self.M if ld is None else int(ld)
         scores = out if out is not None else np.empty((T, ld), np.float32)
@@ -216,8 +218,8 @@ class Engine:
         fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
         a = automata
         x = _np(x, np.float32)
-        if x.ndim != 2 or x.shape != (n_frames, self.D):
-            raise ValueError(f"features must be [{n_frames}, {self.D}]")
+        if x.ndim != 2 or x.shape != (n_frames, self._in_dim(self.D)):
+            raise ValueError(f"features must be [{n_frames}, {self._in_dim(self.D)}]")
         if not want_paths and not accumulate:
             raise ValueError("want_paths=False only makes sense with accumulate=True")
         em = np.empty(n_frames, np.uint32) if want_paths else None
@@ -233,6 +235,29 @@ class Engine:
     @property
     def align_ordered_count(self) -> int:
         return int(self._lib.gmm_align_ordered_count(self._h))
+
+    # -- front end on the device (lda.flow) -------------------------------------------------------
+    def set_lda(self, matrix, base_dim, length, right):
+        """matrix [D, base_dim*length]; afterwards every *_host call takes base features [T, base_dim]."""
+        matrix = _np(matrix, np.float32)
+        if matrix.ndim != 2 or matrix.shape[1] != base_dim * length:
+            raise ValueError(f"matrix must be [D, {base_dim * length}]")
+        self._check(self._lib.gmm_set_lda(self._h, int(base_dim), int(length), int(right), matrix.shape[0],
+                                          _ptr(matrix)), "gmm_set_lda")
+        self._lda = (int(base_dim), matrix.shape[0])
+
+    def clear_lda(self):
+        self._check(self._lib.gmm_set_lda(self._h, 0, 0, 0, 0, None), "gmm_set_lda")
+        self._lda = None
+
+    def lda_device(self, frame_offsets, d_base, d_x):
+        fo = _np(frame_offsets, np.uint32)
+        self._check(self._lib.gmm_lda_device(self._h, fo.shape[0] - 1, _ptr(fo), _ptr(d_base), _ptr(d_x)),
+                    "gmm_lda_device")
+
+    def _in_dim(self, model_dim):
+        lda = getattr(self, "_lda", None)
+        return lda[0] if lda else model_dim
 
     # -- training E-step -------------------------------------------------------------------------
     def create_accumulators(self, mean_idx, n_means=None, viterbi=True, weight_threshold=float(np.finfo(np.float32).eps)):
@@ -253,8 +278,8 @@ class Engine:
         x = _np(x, np.float32)
         mixture = _np(mixture, np.uint32)
         weight = None if weight is None else _np(weight, np.float64)
-        if x.ndim != 2 or x.shape[1] != self.D or mixture.shape != (x.shape[0],):
-            raise ValueError(f"features must be [T, {self.D}] and mixture [T]")
+        if x.ndim != 2 or x.shape[1] != self._in_dim(self.D) or mixture.shape != (x.shape[0],):
+            raise ValueError(f"features must be [T, {self._in_dim(self.D)}] and mixture [T]")
         best = np.empty(x.shape[0], np.uint32) if want_best else None
         self._check(self._lib.gmm_accumulate_host(self._h, x.shape[0], _ptr(x), _ptr(mixture), _ptr(weight), _ptr(best)),
                     "gmm_accumulate_host")
@@ -291,8 +316,8 @@ class Engine:
 
     def quant_score_host(self, x, want_q=True, want_best=True, want_score=True, want_qx=False):
         x = _np(x, np.float32)
-        if x.ndim != 2 or x.shape[1] != self.qD:
-            raise ValueError(f"features must be [T, {self.qD}]")
+        if x.ndim != 2 or x.shape[1] != self._in_dim(self.qD):
+            raise ValueError(f"features must be [T, {self._in_dim(self.qD)}]")
         T, M = x.shape[0], self.qM
         q = np.empty((T, M), np.int32) if want_q else None
         best = np.empty((T, M), np.uint32) if want_best else None

@@ -62,6 +62,31 @@ static void releaseQuantModel(gmm_handle* h) {
     h->qtensor = QTensorModel();
 }
 
+// Host frames -> device x [T x D] in SCR_X.  Plain copy, or, with a front end set (gmm_set_lda), the narrow base
+// features [T x baseDim] go up and the device builds the windows and applies the matrix (gmm_lda.cu).
+// frameOffsets: nSeg + 1 entries starting at 0 (windows do not cross segment boundaries).
+static int uploadFrames(gmm_handle* h, uint32_t D, uint32_t nSeg, const uint32_t* frameOffsets, const float* x, void** dx) {
+    const uint32_t T = frameOffsets[nSeg];
+    int            rc;
+    if ((rc = h->reserve(SCR_X, (size_t)std::max(1u, T) * D * 4, dx)))
+        return rc;
+    if (T == 0)
+        return GMM_OK;
+    if (!h->lda.valid) {
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(*dx, x, (size_t)T * D * 4, cudaMemcpyHostToDevice, h->stream));
+        return GMM_OK;
+    }
+    if (h->lda.D != D) {
+        h->setError("front end (gmm_set_lda) produces a different dimension than the model takes");
+        return GMM_ERR_ARG;
+    }
+    void* db = nullptr;
+    if ((rc = h->reserve(SCR_BASE, (size_t)T * h->lda.baseDim * 4, &db)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(db, x, (size_t)T * h->lda.baseDim * 4, cudaMemcpyHostToDevice, h->stream));
+    return gmm_lda_launch(h, nSeg, frameOffsets, (const float*)db, (float*)*dx);
+}
+
 extern "C" {
 
 const char* gmm_version(void) {
@@ -123,9 +148,11 @@ void gmm_destroy(gmm_handle* h) {
         cudaEventDestroy(h->timed[i].first);
         cudaEventDestroy(h->timed[i].second);
     }
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < SCR_COUNT; ++i)
         if (h->scratch[i])
             cudaFree(h->scratch[i]);
+    if (h->lda.matrix)
+        cudaFree(h->lda.matrix);
     if (h->ownStream && h->stream)
         cudaStreamDestroy(h->stream);
     delete h;
@@ -345,13 +372,13 @@ int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uin
     void *dx = nullptr, *ds = nullptr, *db = nullptr;
     int   rc;
     const size_t devLd = h->M;
-    if ((rc = h->reserve(SCR_X, (size_t)T * h->D * 4, &dx)))
+    const uint32_t one[2] = {0, T};
+    if ((rc = uploadFrames(h, h->D, 1, one, x, &dx)))
         return rc;
     if ((rc = h->reserve(SCR_SCORE, (size_t)T * devLd * 4, &ds)))
         return rc;
     if (best && (rc = h->reserve(SCR_BEST, (size_t)T * devLd * 4, &db)))
         return rc;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x, (size_t)T * h->D * 4, cudaMemcpyHostToDevice, h->stream));
     if ((rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, (uint32_t*)db, devLd)))
         return rc;
     if ((rc = copyOut(h, scores, ds, T, h->M, ld, devLd)))
@@ -428,13 +455,12 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
         void *dx = nullptr, *ds = nullptr;
         const uint32_t* dPath = nullptr;
         int   rc;
-        if ((rc = h->reserve(SCR_X, (size_t)std::max(1u, T) * h->D * 4, &dx)))
+        const uint32_t inDim = h->lda.valid ? h->lda.baseDim : h->D;
+        if ((rc = uploadFrames(h, h->D, n, fo.data(), x + (size_t)f0 * inDim, &dx)))
             return rc;
         if ((rc = h->reserve(SCR_SCORE, (size_t)std::max(1u, T) * devLd * 4, &ds)))
             return rc;
         if (T) {
-            GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x + (size_t)f0 * h->D, (size_t)T * h->D * 4, cudaMemcpyHostToDevice,
-                                            h->stream));
             if ((rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, nullptr, devLd)))
                 return rc;
         }
@@ -469,6 +495,50 @@ int gmm_score_align_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t
                                     float* pathScore) {
     return scoreAlign(h, true, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
                       initialState, finalWeight, pathEmission, pathState, pathScore);
+}
+
+// ---- front end on the device -------------------------------------------------------------------------------------
+int gmm_set_lda(gmm_handle* h, uint32_t baseDim, uint32_t length, uint32_t right, uint32_t D, const float* matrix) {
+    if (!h)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    if (h->lda.matrix)
+        cudaFree(h->lda.matrix);
+    h->lda = LdaModel();
+    if (!matrix || baseDim == 0)
+        return GMM_OK;  // cleared: host entry points take model-dimension features again
+    if (length == 0 || right >= length || D == 0) {
+        h->setError("gmm_set_lda: need length >= 1, right < length, D >= 1");
+        return GMM_ERR_ARG;
+    }
+    const size_t bytes = (size_t)D * baseDim * length * 4;
+    GMM_CUDA_TRY(h, cudaMalloc((void**)&h->lda.matrix, bytes));
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(h->lda.matrix, matrix, bytes, cudaMemcpyHostToDevice, h->stream));
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    h->lda.baseDim = baseDim;
+    h->lda.length  = length;
+    h->lda.right   = right;
+    h->lda.D       = D;
+    h->lda.valid   = true;
+    return GMM_OK;
+}
+
+int gmm_lda_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_base, float* d_x) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->lda.valid) {
+        h->setError("gmm_lda_device: no front end set (gmm_set_lda)");
+        return GMM_ERR_ARG;
+    }
+    if (nSeg == 0)
+        return GMM_OK;
+    if (!frameOffsets || (frameOffsets[nSeg] > frameOffsets[0] && (!d_base || !d_x))) {
+        h->setError("gmm_lda_device: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return gmm_lda_launch(h, nSeg, frameOffsets, d_base, d_x);
 }
 
 // ---- training E-step -------------------------------------------------------------------------------------------
@@ -594,14 +664,14 @@ int gmm_accumulate_host(gmm_handle* h, uint32_t T, const float* x, const uint32_
         }
     void *dx = nullptr, *dm = nullptr;
     int   rc;
-    if ((rc = h->reserve(SCR_X, (size_t)T * h->D * 4, &dx)))
+    const uint32_t one[2] = {0, T};
+    if ((rc = uploadFrames(h, h->D, 1, one, x, &dx)))
         return rc;
     // mixture indices, weights and chosen densities share one scratch reservation
     const size_t oW = ((size_t)T * 4 + 255) & ~(size_t)255, oB = oW + (((size_t)T * 8 + 255) & ~(size_t)255);
     if ((rc = h->reserve(SCR_BEST, oB + (size_t)T * 4, &dm)))
         return rc;
     char* base = (char*)dm;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x, (size_t)T * h->D * 4, cudaMemcpyHostToDevice, h->stream));
     GMM_CUDA_TRY(h, cudaMemcpyAsync(base, mixture, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
     if (weight)
         GMM_CUDA_TRY(h, cudaMemcpyAsync(base + oW, weight, (size_t)T * 8, cudaMemcpyHostToDevice, h->stream));
@@ -706,6 +776,14 @@ int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, 
         return GMM_ERR_ARG;
     }
     cudaSetDevice(h->device);
+    // with a front end the whole block of base features is transformed first (windows span chunk boundaries)
+    void* dxAll = nullptr;
+    if (h->lda.valid) {
+        const uint32_t one[2] = {0, T};
+        int            rc     = uploadFrames(h, qm.D, 1, one, x, &dxAll);
+        if (rc)
+            return rc;
+    }
     // bound device scratch: frames in chunks
     const size_t perFrame = (size_t)qm.M * 12 + (qx ? (size_t)qm.C * qm.Dpad : 0) + (size_t)qm.D * 4;
     uint32_t     chunk    = (uint32_t)std::max<size_t>(1, std::min<size_t>(T, ((size_t)1 << 30) / perFrame));
@@ -713,7 +791,9 @@ int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, 
         const uint32_t n = std::min(chunk, T - t0);
         void *dx = nullptr, *dq = nullptr, *db = nullptr, *ds = nullptr, *dqx = nullptr;
         int   rc;
-        if ((rc = h->reserve(SCR_X, (size_t)n * qm.D * 4, &dx)))
+        if (dxAll)
+            dx = (float*)dxAll + (size_t)t0 * qm.D;
+        else if ((rc = h->reserve(SCR_X, (size_t)n * qm.D * 4, &dx)))
             return rc;
         if (q && (rc = h->reserve(SCR_Q, (size_t)n * qm.M * 4, &dq)))
             return rc;
@@ -723,8 +803,9 @@ int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, 
             return rc;
         if (qx && (rc = h->reserve(SCR_MISC, (size_t)n * qm.C * qm.Dpad, &dqx)))
             return rc;
-        GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x + (size_t)t0 * qm.D, (size_t)n * qm.D * 4, cudaMemcpyHostToDevice,
-                                        h->stream));
+        if (!dxAll)
+            GMM_CUDA_TRY(h, cudaMemcpyAsync(dx, x + (size_t)t0 * qm.D, (size_t)n * qm.D * 4, cudaMemcpyHostToDevice,
+                                            h->stream));
         if ((rc = gmm_quant_launch(h, n, (const float*)dx, (int32_t*)dq, (uint32_t*)db, (float*)ds, (uint8_t*)dqx,
                                    qm.M)))
             return rc;

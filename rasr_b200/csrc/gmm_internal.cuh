@@ -71,6 +71,13 @@ struct AccumModel {
     double *  meanSum = nullptr, *meanW = nullptr, *covSum = nullptr, *covW = nullptr, *mixW = nullptr;
 };
 
+// front end applied on the device when frames arrive from the host (gmm_lda.cu)
+struct LdaModel {
+    bool     valid   = false;
+    uint32_t baseDim = 0, length = 0, right = 0, D = 0;
+    float*   matrix  = nullptr;  // [D x baseDim * length], row major
+};
+
 // quantized scorer on the integer tensor path (gmm_qtc.cu); valid only for models that meet its requirements
 struct QTensorModel {
     bool      valid      = false;
@@ -119,10 +126,11 @@ struct gmm_handle {
     QuantModel  quant;
     QTensorModel qtensor;
     AccumModel   accum;
+    LdaModel     lda;
 
     // scratch (grown on demand)
-    void*  scratch[8]      = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t scratchBytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    void*  scratch[10]      = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratchBytes[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     std::vector<void*> owned;       // device allocations of the float model
     std::vector<void*> ownedQuant;  // device allocations of the quantized model
 
@@ -132,7 +140,7 @@ struct gmm_handle {
     int  upload(void** p, const void* src, size_t bytes, bool quant = false);
 };
 
-enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7 };
+enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7, SCR_BASE = 8, SCR_TILES = 9, SCR_COUNT = 10 };
 
 // gmm_direct.cu
 int gmm_direct_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
@@ -146,6 +154,7 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
                      const uint32_t** d_pathEmission = nullptr);
+int gmm_lda_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_base, float* d_x);
 int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
                      uint32_t* d_best);
 int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, const int32_t* c2);
