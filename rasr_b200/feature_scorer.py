@@ -106,6 +106,7 @@ class GpuFeatureScorer:
                                       mode=mode, kernel=kernel)
         self._fifo = collections.deque()  # ContextScorer objects in time order, oldest first
         self._pending = []  # ContextScorers without a score block yet (time order)
+        self._segment = []  # segment mode (buffer-size 0): every frame since reset(), addressable by time
         self.n_batches = 0
 
     # -- FeatureScorer interface -------------------------------------------------------------------
@@ -136,6 +137,18 @@ class GpuFeatureScorer:
     def reset(self) -> None:
         self._fifo.clear()
         self._pending = []
+        self._segment = []
+
+    def hasTimeIndexedCache(self) -> bool:
+        """FeatureScorer.hh:157-159; true in segment mode, where every frame of the segment is kept."""
+        return self._buffer_size == 0
+
+    def getTimeIndexedScorer(self, time: int) -> "ContextScorer":
+        """FeatureScorer.hh:160-163, used by Speech/SegmentwiseAlignmentGenerator.cc:90-156."""
+        if not self.hasTimeIndexedCache():
+            raise RuntimeError("time-indexed scores not available")
+        assert 0 <= time < len(self._segment)
+        return self._segment[time]
 
     def _push(self, f):
         f = np.asarray(f, dtype=np.float32)
@@ -144,6 +157,8 @@ class GpuFeatureScorer:
         cs = ContextScorer(self, f)
         self._fifo.append(cs)
         self._pending.append(cs)
+        if self._buffer_size == 0:
+            self._segment.append(cs)
 
     def addFeature(self, f) -> None:
         assert not self.bufferFilled(), "addFeature requires !bufferFilled()"

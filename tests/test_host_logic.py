@@ -146,6 +146,13 @@ def test_segment_mode_scores_in_one_batch(stub):
     assert fs.bufferSize() == 0xFFFFFFFF and len(scorers) == 37
     assert scorers[36].score(2) == 3602 and scorers[0].score(0) == 0
     assert fs.engine.batches == [37]
+    # time-indexed access in segment mode (FeatureScorer.hh:157-163, SegmentwiseAlignmentGenerator.cc:90-156)
+    assert fs.hasTimeIndexedCache() and fs.getTimeIndexedScorer(36) is scorers[36]
+    assert fs.getTimeIndexedScorer(4).score(1) == scorers[4].score(1)
+    buffered = feature_scorer.createFeatureScorer({"feature-scorer-type": "diagonal-maximum", "buffer-size": 8}, ms)
+    assert not buffered.hasTimeIndexedCache()
+    with pytest.raises(RuntimeError, match="time-indexed scores not available"):
+        buffered.getTimeIndexedScorer(0)
     # contexts outlive the next segment (the aligner keeps them)
     fs.reset()
     s = fs.getScorer(_frames(1, 5)[0] + 7)
