@@ -6,7 +6,7 @@
 //                  closest frame of the segment); oldest frame first
 //                  (src/Signal/VectorSequenceConcatenation.hh:85-100, src/Signal/Delay.hh:32-46, Delay.cc:30-31,171-174)
 //   multiplication signal-matrix-multiplication-f32: out = matrix * in
-//                  (src/Signal/MatrixMult.hh:70,236-250; src/Math/Matrix.hh:482-489; src/Math/Vector.hh:95-101:
+//                  (src/Signal/MatrixMult.hh:70,243; src/Math/Matrix.hh:482-489; src/Math/Vector.hh:95-101:
 //                  result += a[i] * b[i] in f32, left to right -- the reference build emits scalar mulss / addss for
 //                  this loop, no vectorisation, no FMA, so the device repeats exactly that and is bit-identical)
 //
