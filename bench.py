@@ -244,7 +244,7 @@ def quant_roofline(ms, frames, kernel_sec, peaks, outputs=2, traffic=None):
 
 def run_ours(args):
     import torch
-    from rasr_b200 import capi, synth, tables
+    from rasr_b200 import capi, sharded, synth, tables
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -363,6 +363,8 @@ def run_ours(args):
     t0 = time.perf_counter()
     for _ in range(al_steps):
         eng.score_align_host(al_fo, xal, automata, accumulate=True, want_paths=False)
+        if dist is not None:  # the pass ends with the combine step: one all-reduce of the f64 estimators
+            sharded.all_reduce_accumulators(eng, dist)
     eng.sync()
     tr_sec = time.perf_counter() - t0
     if dist is not None:
@@ -396,7 +398,8 @@ def run_ours(args):
                                   "d2h_bytes_per_step": 0, "frames_per_step_per_gpu": al_frames,
                                   "api": "gmm_score_align_accumulate_host (C-ABI): host features -> scores -> Viterbi "
                                          "path -> best density of the aligned mixture -> f64 estimator sums, all in "
-                                         "HBM; the estimators are read once per pass (gmm_accumulator_read)"},
+                                         "HBM; the estimators are read once per pass (gmm_accumulator_read); at N > 1 "
+                                         "every step ends with the all-reduce that combines the ranks' estimators"},
             "clocks": clocks}
     if rank == 0:
         line["roofline"] = float_roofline(ms, frames, kernel_sec, peaks, kname, sec_per_step,

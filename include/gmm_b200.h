@@ -148,6 +148,13 @@ int gmm_accumulate_device(gmm_handle* h, uint32_t T, const float* d_x, const uin
                           uint32_t* d_best);
 int gmm_accumulate_host(gmm_handle* h, uint32_t T, const float* x, const uint32_t* mixture, const double* weight,
                         uint32_t* best);
+/* The estimators as one block of gmm_accumulator_size() doubles, in the order meanSum [nMeans x D], meanWeight
+ * [nMeans], covSum [C x D], covWeight [C], mixWeight [G]: copied to / from DEVICE memory on the handle's stream, so
+ * that ranks can sum their estimators with one all-reduce (the combine step of
+ * AbstractMixtureSetEstimator::accumulate(const AbstractMixtureSetEstimator&), .cc:149-169) without a host trip. */
+size_t gmm_accumulator_size(const gmm_handle* h);
+int gmm_accumulator_export_device(gmm_handle* h, double* d_dst);
+int gmm_accumulator_import_device(gmm_handle* h, const double* d_src);
 int gmm_accumulator_read(gmm_handle* h, double* meanSum, double* meanWeight, double* covSum, double* covWeight,
                          double* mixWeight);
 

@@ -39,6 +39,9 @@ SYMBOLS = [
     ("gmm_accumulator_reset", _i, [_vp]),
     ("gmm_accumulate_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
     ("gmm_accumulate_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
+    ("gmm_accumulator_size", _sz, [_vp]),
+    ("gmm_accumulator_export_device", _i, [_vp, _vp]),
+    ("gmm_accumulator_import_device", _i, [_vp, _vp]),
     ("gmm_accumulator_read", _i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     ("gmm_set_lda", _i, [_vp, _u32, _u32, _u32, _u32, _vp]),
     ("gmm_lda_device", _i, [_vp, _u32, _vp, _vp, _vp]),
@@ -288,6 +291,17 @@ class Engine:
     def accumulate_device(self, T, d_x, d_mixture, d_weight=None, d_best=None):
         self._check(self._lib.gmm_accumulate_device(self._h, int(T), _ptr(d_x), _ptr(d_mixture), _ptr(d_weight),
                                                     _ptr(d_best)), "gmm_accumulate_device")
+
+    @property
+    def accumulator_size(self) -> int:
+        return int(self._lib.gmm_accumulator_size(self._h))
+
+    def export_accumulators(self, d_dst):
+        """All estimators as one block of `accumulator_size` doubles into device memory (async on the stream)."""
+        self._check(self._lib.gmm_accumulator_export_device(self._h, _ptr(d_dst)), "gmm_accumulator_export_device")
+
+    def import_accumulators(self, d_src):
+        self._check(self._lib.gmm_accumulator_import_device(self._h, _ptr(d_src)), "gmm_accumulator_import_device")
 
     def read_accumulators(self, n_cov):
         out = dict(mean_sum=np.empty((self.n_means, self.D)), mean_weight=np.empty(self.n_means),

@@ -624,6 +624,34 @@ int gmm_accumulator_read(gmm_handle* h, double* meanSum, double* meanWeight, dou
     return GMM_OK;
 }
 
+size_t gmm_accumulator_size(const gmm_handle* h) {
+    return h && h->accum.valid ? h->accum.blockBytes / sizeof(double) : 0;
+}
+
+int gmm_accumulator_export_device(gmm_handle* h, double* d_dst) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->accum.valid || !d_dst) {
+        h->setError("gmm_accumulator_export_device: no accumulators or NULL destination");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(d_dst, h->accum.block, h->accum.blockBytes, cudaMemcpyDeviceToDevice, h->stream));
+    return GMM_OK;
+}
+
+int gmm_accumulator_import_device(gmm_handle* h, const double* d_src) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->accum.valid || !d_src) {
+        h->setError("gmm_accumulator_import_device: no accumulators or NULL source");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(h->accum.block, d_src, h->accum.blockBytes, cudaMemcpyDeviceToDevice, h->stream));
+    return GMM_OK;
+}
+
 int gmm_accumulate_device(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
                           uint32_t* d_best) {
     if (!h)

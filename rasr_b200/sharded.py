@@ -9,6 +9,12 @@
   ``[N][T][Mp]``.  ``gathered_index(m)`` maps an emission index to (rank, column); ``to_frame_major`` restores
   ``[T][M]`` when a consumer wants it.
 
+* Training pass (alignment + E-step): segment sharded like scoring; the one real exchange is the sum of the
+  ranks' estimators at the end of a pass -- the reference combines the accumulator files of its parallel jobs
+  (AbstractMixtureSetEstimator::accumulate(const AbstractMixtureSetEstimator&),
+  /root/reference/src/Mm/AbstractMixtureSetEstimator.cc:149-169); here it is one ``all_reduce`` over the packed
+  f64 block on the device (``all_reduce_accumulators``).
+
 torch.distributed is plumbing only; the scores come from the C-ABI engine (rasr_b200.capi).
 """
 from __future__ import annotations
@@ -109,3 +115,43 @@ class MixtureShardedScorer:
         if not self._bound:
             self.engine.sync()  # the engine's own stream is not the one the collective runs on
         return all_gather_scores(self._local, self.dist, self.world)
+
+
+# ---- training pass: combine the ranks' estimators ----------------------------------------------------------
+ACC_FIELDS = ("mean_sum", "mean_weight", "cov_sum", "cov_weight", "mix_weight")
+
+
+def pack_accumulators(acc: dict) -> np.ndarray:
+    """dict of Engine.read_accumulators / oracle.accumulate -> the block layout of gmm_accumulator_export_device."""
+    return np.concatenate([np.asarray(acc[k], np.float64).ravel() for k in ACC_FIELDS])
+
+
+def unpack_accumulators(block, n_means: int, n_cov: int, D: int, G: int) -> dict:
+    block = np.asarray(block, np.float64)
+    sizes = (n_means * D, n_means, n_cov * D, n_cov, G)
+    assert block.shape == (sum(sizes),)
+    parts = np.split(block, np.cumsum(sizes)[:-1])
+    return dict(mean_sum=parts[0].reshape(n_means, D), mean_weight=parts[1], cov_sum=parts[2].reshape(n_cov, D),
+                cov_weight=parts[3], mix_weight=parts[4])
+
+
+def all_reduce_block(block, dist):
+    """Sum the packed estimator block over all ranks, in place (NCCL over NVLink on GPUs, gloo in the CPU tests)."""
+    dist.all_reduce(block, op=dist.ReduceOp.SUM)
+    return block
+
+
+def all_reduce_accumulators(engine, dist, stream=None):
+    """Every rank ends up with the sum of all ranks' estimators, without leaving the device."""
+    import torch
+    n = engine.accumulator_size
+    block = torch.empty(n, dtype=torch.float64, device="cuda")
+    engine.export_accumulators(block)
+    if stream is None:
+        engine.sync()  # the engine's own stream is not the one the collective runs on
+    all_reduce_block(block, dist)
+    engine.import_accumulators(block)
+    if stream is None:
+        torch.cuda.current_stream().synchronize()
+        engine.sync()
+    return block

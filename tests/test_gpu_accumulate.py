@@ -163,3 +163,27 @@ def test_training_iteration_through_mixset_file(eng, oracle, tmp_path):
     s, b = eng.score_host(x[:64])
     so, bo = oracle.score_max(loaded, x[:64])
     assert np.array_equal(s.view(np.uint32), so.view(np.uint32)) and np.array_equal(b, bo)
+
+
+def test_export_import_block_layout(eng, oracle):
+    """The packed device block (what ranks all-reduce) is the concatenation read_accumulators returns."""
+    from rasr_b200 import sharded
+    ms = synth.make_model(M=20, K=3, D=10, seed=2, covariance="mixture")
+    x = synth.make_features(ms, 500, seed=1)
+    mixture = np.random.default_rng(1).integers(0, ms.M, 500).astype(np.uint32)
+    upload(eng, ms, capi.MODE_MAX)
+    eng.create_accumulators(tables.mean_index(ms), ms.n_means)
+    eng.accumulate_host(x, mixture, want_best=False)
+    acc = eng.read_accumulators(ms.n_cov)
+    n = eng.accumulator_size
+    assert n == ms.n_means * ms.D + ms.n_means + ms.n_cov * ms.D + ms.n_cov + ms.G
+    block = torch.empty(n, dtype=torch.float64, device="cuda")
+    eng.export_accumulators(block)
+    eng.sync()
+    assert np.array_equal(block.cpu().numpy(), sharded.pack_accumulators(acc))
+    eng.import_accumulators(block * 2)
+    eng.sync()
+    twice = eng.read_accumulators(ms.n_cov)
+    assert all(np.array_equal(twice[k], 2 * acc[k]) for k in acc)
+    back = sharded.unpack_accumulators(block.cpu().numpy(), ms.n_means, ms.n_cov, ms.D, ms.G)
+    assert all(np.array_equal(back[k], acc[k]) for k in acc)

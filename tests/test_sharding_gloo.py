@@ -78,3 +78,59 @@ def test_mixture_sharded_all_gather_world2():
         assert p.exitcode == 0
     res = dict(q.get(timeout=5) for _ in range(2))
     assert res == {0: True, 1: True}
+
+
+def _train_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import oracle as O
+        from rasr_b200.align import AlignmentAutomata, linear_hmm
+        ms = synth.make_model(M=31, K=4, D=8, seed=6, covariance="mixture")
+        rng = np.random.default_rng(0)           # every rank builds the same corpus, then takes its segments
+        n_seg = 7
+        fo = np.cumsum([0] + [int(n) for n in rng.integers(20, 60, n_seg)]).astype(np.uint32)
+        x = synth.make_features(ms, int(fo[-1]), seed=9)
+        segs = [linear_hmm(rng.integers(0, ms.M, 6)) for _ in range(n_seg)]
+        tab = O.float_tables(ms)
+        scores, _ = O.score_max(ms, x, tables=tab)
+
+        def e_step(seg_ids):
+            acc = None
+            for i in seg_ids:                    # align the segment, accumulate its frames on its path
+                au = AlignmentAutomata.from_arc_lists([segs[i]])
+                rows = slice(int(fo[i]), int(fo[i + 1]))
+                em, _, _ = O.viterbi_align([0, rows.stop - rows.start], scores[rows], au)
+                a = O.accumulate(ms, x[rows], em, tables=tab)
+                acc = a if acc is None else {k: acc[k] + a[k] for k in acc if k != "best"}
+            return acc
+
+        mine = e_step(sharded.segments_of_rank(n_seg, rank, world))
+        block = torch.from_numpy(sharded.pack_accumulators(mine))
+        sharded.all_reduce_block(block, dist)
+        got = sharded.unpack_accumulators(block.numpy(), ms.n_means, ms.n_cov, ms.D, ms.G)
+        want = e_step(range(n_seg))
+        ok = np.array_equal(got["mix_weight"], want["mix_weight"]) and got["mix_weight"].sum() == fo[-1]
+        for k in sharded.ACC_FIELDS:
+            ok = ok and np.allclose(got[k], want[k], rtol=1e-12, atol=1e-12)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_training_pass_segment_sharded_all_reduce_world2():
+    """Segments i mod N per rank, alignment + E-step locally, one all-reduce of the packed estimators."""
+    from oracle import oracle as O
+    O.build()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_train_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    res = dict(q.get(timeout=5) for _ in range(2))
+    assert res == {0: True, 1: True}
