@@ -96,6 +96,18 @@ int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, 
 int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,
                            float* d_score, uint8_t* d_qx, size_t ld);
 
+/* ---- subset scoring ---------------------------------------------------------------------------------------------
+ * The reference's context scorers evaluate a mixture when a consumer first asks for it (CachedContextScorer::score,
+ * src/Mm/FeatureScorer.hh:170-230): an aligner pays for the few hundred emissions of the segment's automaton, not
+ * for all M.  Same here: rows [frameOffsets[s], frameOffsets[s+1]) of d_scores receive, in column j, the score of
+ * mixture mixtures[listOffsets[s] + j] -- bit-identical to column mixtures[..] of gmm_score_device on the tensor
+ * kernel.  ld >= gmm_score_subset_ld(h, longest list); columns between a list's end and that bound are scratch.
+ * frameOffsets / listOffsets / mixtures are HOST arrays.  GMM_ERR_UNSUPPORTED unless the tensor kernel is active
+ * and all mixtures have the same number of densities (score everything then). */
+int gmm_score_subset_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const uint32_t* listOffsets,
+                            const uint32_t* mixtures, const float* d_x, float* d_scores, size_t ld);
+uint32_t gmm_score_subset_ld(const gmm_handle* h, uint32_t maxListLength);
+
 /* ---- device-resident consumer: Viterbi alignment over the score block ------------------
  * Replaces, for unpruned Viterbi alignment, Search::Aligner::SearchSpace::{addStartupHypothesis, expand,
  * activateOrUpdateStateHypothesisViterbi, getAlignmentFsaViterbi} (src/Search/Aligner.cc:132-158,190-239,398-437):

@@ -31,6 +31,8 @@ SYMBOLS = [
     ("gmm_upload_quant", _i, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, C.c_float]),
     ("gmm_quant_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_quant_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
+    ("gmm_score_subset_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
+    ("gmm_score_subset_ld", _u32, [_vp, _u32]),
     ("gmm_align_device", _i, [_vp, _u32, _vp, _vp, _sz] + [_vp] * 10),
     ("gmm_align_ordered_count", C.c_uint64, [_vp]),
     ("gmm_score_align_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
@@ -188,6 +190,17 @@ class Engine:
     def posteriors_device(self, T, d_x, d_post):
         self._check(self._lib.gmm_posteriors_device(self._h, int(T), _ptr(d_x), _ptr(d_post)),
                     "gmm_posteriors_device")
+
+    def subset_ld(self, max_list_length: int) -> int:
+        return int(self._lib.gmm_score_subset_ld(self._h, int(max_list_length)))
+
+    def score_subset_device(self, frame_offsets, list_offsets, mixtures, d_x, d_scores, ld):
+        """Per segment, only the listed mixtures: column j of the segment's rows = mixture list[j]."""
+        fo, lo, mx = _np(frame_offsets, np.uint32), _np(list_offsets, np.uint32), _np(mixtures, np.uint32)
+        if lo.shape != fo.shape or int(lo[-1]) != mx.shape[0]:
+            raise ValueError("list offsets must have one entry per segment boundary and end at len(mixtures)")
+        self._check(self._lib.gmm_score_subset_device(self._h, fo.shape[0] - 1, _ptr(fo), _ptr(lo), _ptr(mx), _ptr(d_x),
+                                                      _ptr(d_scores), int(ld)), "gmm_score_subset_device")
 
     # -- alignment consumer (scores never leave the device) ---------------------------------------
     def _align_args(self, frame_offsets, automata):

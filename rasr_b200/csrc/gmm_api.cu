@@ -346,6 +346,33 @@ int gmm_score_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_score
     return gmm_direct_score(h, T, d_x, d_scores, d_best, ld);
 }
 
+int gmm_score_subset_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const uint32_t* listOffsets,
+                            const uint32_t* mixtures, const float* d_x, float* d_scores, size_t ld) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid) {
+        h->setError("gmm_score_subset: no float model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (nSeg == 0)
+        return GMM_OK;
+    if (!frameOffsets || !listOffsets || (listOffsets[nSeg] && !mixtures) || (frameOffsets[nSeg] && (!d_x || !d_scores))) {
+        h->setError("gmm_score_subset: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    if (!gmm_tc_subset_capable(h)) {
+        h->setError("gmm_score_subset: needs the tensor kernel and a model whose mixtures all have the same number "
+                    "of (live) densities; score all mixtures instead");
+        return GMM_ERR_UNSUPPORTED;
+    }
+    return gmm_tc_score_subset(h, nSeg, frameOffsets, listOffsets, mixtures, d_x, d_scores, ld);
+}
+
+uint32_t gmm_score_subset_ld(const gmm_handle* h, uint32_t maxListLength) {
+    return (h && h->floatValid && h->tensor.valid) ? gmm_tc_subset_ld(h, maxListLength) : 0;
+}
+
 static int copyOut(gmm_handle* h, void* host, const void* dev, uint32_t T, uint32_t M, size_t ld, size_t devLd) {
     if (ld == devLd)
         GMM_CUDA_TRY(h, cudaMemcpyAsync(host, dev, (size_t)T * ld * 4, cudaMemcpyDeviceToHost, h->stream));

@@ -46,6 +46,11 @@ struct TensorModel {
     uint32_t  aTileBytes = 0;
     uint32_t  buffersB  = 0;       // B tile buffers that fit in shared memory (1 or 2)
     uint32_t  stagesA   = 0;       // A tile ring depth with the arg-min staging enabled
+    // regular model: every mixture takes the same number of packed columns (mixCols, a divisor of partW) and none
+    // is empty, so mixture m sits at rows (m % mixPerTile) * mixCols of tile m / mixPerTile and a tile over ANY
+    // set of mixtures can be assembled from whole swizzle atoms of the canonical image (subset scoring)
+    bool      regular   = false;
+    uint32_t  mixCols   = 0, mixPerTile = 0;
 };
 
 struct QuantModel {
@@ -129,8 +134,8 @@ struct gmm_handle {
     LdaModel     lda;
 
     // scratch (grown on demand)
-    void*  scratch[10]      = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t scratchBytes[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    void*  scratch[12]      = {};
+    size_t scratchBytes[12] = {};
     std::vector<void*> owned;       // device allocations of the float model
     std::vector<void*> ownedQuant;  // device allocations of the quantized model
 
@@ -140,7 +145,7 @@ struct gmm_handle {
     int  upload(void** p, const void* src, size_t bytes, bool quant = false);
 };
 
-enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7, SCR_BASE = 8, SCR_TILES = 9, SCR_COUNT = 10 };
+enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7, SCR_BASE = 8, SCR_TILES = 9, SCR_VTILES = 10, SCR_TAB = 11, SCR_COUNT = 12 };
 
 // gmm_direct.cu
 int gmm_direct_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
@@ -163,3 +168,9 @@ int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uin
 int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
                 const float* w2, const float* logNorm, bool force);
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
+// scores of a per-segment subset of mixtures: column j of segment s's rows = mixture emList[emOff[s] + j]
+// (host arrays); GMM_ERR_UNSUPPORTED when the model is not regular (the caller scores everything instead)
+bool gmm_tc_subset_capable(const gmm_handle* h);
+uint32_t gmm_tc_subset_ld(const gmm_handle* h, uint32_t maxListLength);
+int gmm_tc_score_subset(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const uint32_t* emOff,
+                        const uint32_t* emList, const float* d_x, float* d_scores, size_t ld);

@@ -58,6 +58,8 @@ struct KParams {
     uint32_t       aTileBytes, bTileBytes;     // bTileBytes includes c / slot / meta
     uint32_t       stagesA, buffersB;
     uint32_t       stagePitch;                 // floats per staging row (maxMixPerPart + 1)
+    const uint32_t* itemTab;                   // subset scoring: 8 words per item {B tile, f0, f1, rowBase, rowEnd}
+    uint32_t       nItems;
     unsigned long long* dbg;                   // GMM_TC_DEBUG: per-CTA cycle counters of the MMA thread
 };
 
@@ -162,6 +164,31 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
 // NE = epilogue warps (8 or 16): warp e handles TMEM lane quarter (warp & 3) and column part e / 4 of
 // 1024 / NE columns (128 or 64).  16 warps give every scheduler four epilogue warps to hide the latencies of
 // the min tree, and drain an accumulator in half the time; they need mixtures of at most 64 packed columns.
+// Work item -> B tile, frame tiles [f0, f1), and where the rows of frame tile f0 land in the score block.
+// Full scoring: items enumerate (B tile, chunk of the frame range), rows are the frames themselves.  Subset scoring
+// (gmm_tc_score_subset): an item table pairs a segment's own B tile with the segment's frame tiles, whose rows are
+// the segment's frames [rowBase, rowEnd) although its A tiles sit in a tile-aligned (padded) row space.
+struct ItemRange {
+    uint32_t nt, f0, f1, rowBase, rowEnd;
+};
+__device__ __forceinline__ ItemRange item_range(const KParams& p, uint32_t item, uint32_t tilesPerItem) {
+    ItemRange r;
+    if (p.itemTab) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(p.itemTab) + 2 * (size_t)item);
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(p.itemTab) + 2 * (size_t)item + 1);
+        r.nt = a.x, r.f0 = a.y, r.f1 = a.z, r.rowBase = a.w, r.rowEnd = b.x;
+    }
+    else {
+        const uint32_t chunk = item % p.split;
+        r.nt      = item / p.split;
+        r.f0      = chunk * tilesPerItem;
+        r.f1      = min(p.frameTiles, r.f0 + tilesPerItem);
+        r.rowBase = r.f0 * kTileM;
+        r.rowEnd  = p.T;
+    }
+    return r;
+}
+
 template<int SWZ, int MODE, bool BEST, int NE>
 __device__ __forceinline__ void tc_score_body(const KParams& p) {
     extern __shared__ uint8_t smemRaw[];
@@ -211,7 +238,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     tc_fence_after();
     const uint32_t tmemBase = *tmemSlot;
 
-    const uint32_t items        = p.nTiles * p.split;
+    const uint32_t items        = p.itemTab ? p.nItems : p.nTiles * p.split;
     const uint32_t tilesPerItem = (p.frameTiles + p.split - 1) / p.split;
 
     if (warp == 0) {
@@ -219,8 +246,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
         if (lane == 0) {
             uint32_t itemCount = 0, t = 0, stage = 0;
             for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
-                const uint32_t nt = item / p.split, chunk = item % p.split;
-                const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+                const ItemRange ir = item_range(p, item, tilesPerItem);
+                const uint32_t  nt = ir.nt, f0 = ir.f0, f1 = ir.f1;
                 if (f0 >= f1)
                     continue;
                 const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
@@ -257,8 +284,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
         bool      have = false;  // ready[t % kRing] was already seen complete (probed while tile t - 1 was being issued)
         long long tStart = clock64(), wR = 0, wI = 0, t0 = 0;
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
-            const uint32_t chunk = item % p.split;
-            const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+            const ItemRange ir = item_range(p, item, tilesPerItem);
+            const uint32_t  f0 = ir.f0, f1 = ir.f1;
             if (f0 >= f1)
                 continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
@@ -314,8 +341,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             mbar_arrive(smem_u32(&ready[1]));
         }
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
-            const uint32_t chunk = item % p.split;
-            const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
+            const ItemRange ir = item_range(p, item, tilesPerItem);
+            const uint32_t  f0 = ir.f0, f1 = ir.f1;
             if (f0 >= f1)
                 continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
@@ -336,7 +363,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             const size_t    gStep = ((size_t)adv_r * p.ld + adv_j) * 4, gStepW = gStep + (p.ld - nMix) * 4;  // bytes
             const uint32_t  sStep = (adv_r * p.stagePitch + adv_j) * 4, sStepW = sStep + (p.stagePitch - nMix) * 4;
             const uint32_t  ssLane = stWarp + (lr0 * p.stagePitch + lj0) * 4;
-            char*           gTile  = reinterpret_cast<char*>(p.scores + (size_t)(f0 * kTileM + q * 32 + lr0) * p.ld + mixBase + lj0);
+            char*           gTile  = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + q * 32 + lr0) * p.ld + mixBase + lj0);
             const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
             const float2*   rip = p.rowInfo + (size_t)f0 * kTileM + q * 32 + lane;
             // the tile loop, specialised on the tile's mixture shape when it is uniform (see epi_chunk)
@@ -391,8 +418,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     __syncwarp();
                     // coalesced store of the staged [32 rows x nMix] block: nMix passes of 32 consecutive elements;
                     // pointers advance by per-item constants (a pass that wraps past a row end takes the `w` step)
-                    const uint32_t rbase = f * kTileM + q * 32;
-                    const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
+                    const uint32_t rbase = ir.rowBase + (f - f0) * kTileM + q * 32;
+                    const uint32_t rows  = min(32u, ir.rowEnd > rbase ? ir.rowEnd - rbase : 0u);
                     char*          gs    = gTile;
                     uint32_t       ss    = ssLane;
                     gTile += gTileStep;
@@ -475,7 +502,8 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ 
                                                       uint32_t frameTiles, const float* __restrict__ ctr,
                                                       const float* __restrict__ scale, uint32_t kSteps, uint32_t atoms,
                                                       uint32_t swz, uint8_t* __restrict__ aTiles,
-                                                      float2* __restrict__ rowInfo) {
+                                                      float2* __restrict__ rowInfo,
+                                                      const uint32_t* __restrict__ rowMap) {
     const uint32_t chunks = kSteps * 2;  // 8-element chunks per precision part
     const uint32_t epa    = swz / 2;     // fp16 elements per atom row
     const uint32_t lane   = threadIdx.x & 31, c = lane % LPF;
@@ -487,23 +515,27 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ 
          t += framesPerGrid) {
         float v[8];
         float vmax = 0.f, ssq = 0.f;
+        // row t of the tile space holds frame `src` (subset scoring: tiles are aligned to segments, rowMap names the
+        // frame of every row, 0xFFFFFFFF for padding)
+        const uint32_t src = rowMap ? rowMap[t] : (t < T ? t : 0xFFFFFFFFu);
+        const float*   xr  = x + (size_t)(src == 0xFFFFFFFFu ? 0 : src) * D;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const uint32_t k = c * 8 + j;
             v[j]             = 0.f;
-            if (t < T && c < chunks) {
+            if (src != 0xFFFFFFFFu && c < chunks) {
                 if (POOLED) {
                     if (k < D) {
-                        v[j] = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
+                        v[j] = (xr[k] - ctr[k]) * scale[k];
                         ssq  = fmaf(v[j], v[j], ssq);
                     }
                 }
                 else if (k < D) {
-                    const float y = (x[(size_t)t * D + k] - ctr[k]) * scale[k];
+                    const float y = (xr[k] - ctr[k]) * scale[k];
                     v[j]          = y * y;
                 }
                 else if (k < 2 * D) {
-                    v[j] = (x[(size_t)t * D + (k - D)] - ctr[k - D]) * scale[k - D];
+                    v[j] = (xr[k - D] - ctr[k - D]) * scale[k - D];
                 }
             }
             if (k >= kel && k < kel + 3)
@@ -691,6 +723,18 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     tm.maxMixPerPart = 1;
     for (uint32_t v : mixPerPart)
         tm.maxMixPerPart = std::max(tm.maxMixPerPart, v);
+    {   // regular model (see TensorModel): same live count everywhere, padded width dividing the column part
+        const uint32_t n0 = offsets[1] - offsets[0], P = std::max<uint32_t>(8, (n0 + 7) / 8 * 8);
+        bool           reg = n0 > 0 && partW % P == 0 && M >= kTileN / P;
+        for (uint32_t m = 0; m < M && reg; ++m) {
+            reg = offsets[m + 1] - offsets[m] == n0;
+            for (uint32_t g = offsets[m]; g < offsets[m + 1] && reg; ++g)
+                reg = isLive(g);
+        }
+        tm.regular    = reg;
+        tm.mixCols    = P;
+        tm.mixPerTile = kTileN / P;
+    }
 
     // ---- shared-memory configuration (sized for the arg-min variant) ----
     const uint32_t pitch = tm.maxMixPerPart + 1, epiWarps = 4 * partsPerTile;
@@ -818,11 +862,30 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     return GMM_OK;
 }
 
-int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld) {
+namespace {
+
+// One run of the preparation + scoring kernels.  Full scoring: FT = ceil(T / 128) frame tiles over all B tiles of the
+// model.  Subset scoring: tile-aligned row space described by rowMap, items from itemTab, B tiles gathered per call.
+struct TcJob {
+    uint32_t        T, FT;
+    const float*    d_x;
+    const uint32_t* rowMap;   // device, [FT * 128] or null
+    const uint8_t*  bTiles;
+    uint32_t        nTiles;
+    const uint32_t* itemTab;  // device, 8 words per item, or null
+    uint32_t        nItems;
+    float*          scores;
+    uint32_t*       best;
+    size_t          ld;
+};
+
+int tc_run(gmm_handle* h, const TcJob& job) {
     const TensorModel& tm = h->tensor;
-    if (T == 0)
-        return GMM_OK;
-    const uint32_t FT = (T + kTileM - 1) / kTileM;
+    const uint32_t     FT = job.FT, T = job.T;
+    const float*       d_x = job.d_x;
+    float*             d_scores = job.scores;
+    uint32_t*          d_best   = job.best;
+    const size_t       ld       = job.ld;
     void *         aT = nullptr, *rT = nullptr;
     int            rc;
     if ((rc = h->reserve(SCR_A, (size_t)FT * tm.aTileBytes, &aT)))
@@ -836,7 +899,7 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
         int blocks = (int)std::min<uint32_t>((FT * kTileM + fpb - 1) / fpb, (uint32_t)h->smCount * 16);
 #define GMM_PREP(P, L)                                                                                          \
     tc_prep_kernel<P, L><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps, tm.nAtoms, \
-                                                        tm.swz, (uint8_t*)aT, (float2*)rT)
+                                                        tm.swz, (uint8_t*)aT, (float2*)rT, job.rowMap)
         if (tm.pooled) {
             if (lpf == 8)
                 GMM_PREP(true, 8);
@@ -858,14 +921,16 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
         GMM_CUDA_TRY(h, cudaGetLastError());
     }
     KParams p;
-    p.bTiles     = tm.bTiles;
+    p.bTiles     = job.bTiles;
+    p.itemTab    = job.itemTab;
+    p.nItems     = job.nItems;
     p.aTiles     = (const uint8_t*)aT;
     p.rowInfo    = (const float2*)rT;
     p.scores     = d_scores;
     p.best       = d_best;
     p.ld         = ld;
     p.T          = T;
-    p.nTiles     = tm.nTiles;
+    p.nTiles     = job.nTiles;
     p.frameTiles = FT;
     p.kSteps     = tm.kSteps;
     p.atoms      = tm.nAtoms;
@@ -900,7 +965,7 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
         const uint32_t per = (FT + S - 1) / S;
         if ((uint64_t)per * (S - 1) >= FT)
             continue;  // an empty chunk
-        const uint64_t items  = (uint64_t)tm.nTiles * S;
+        const uint64_t items  = (uint64_t)job.nTiles * S;
         const uint64_t rounds = (items + h->smCount - 1) / h->smCount;
         const double   cost   = (double)rounds * (per + bCost);
         if (cost < bestCost - 1e-9) {
@@ -909,7 +974,8 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
         }
     }
     p.split        = bestS;
-    const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
+    const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount,
+                                             job.itemTab ? (uint64_t)job.nItems : (uint64_t)job.nTiles * bestS);
     cudaError_t e;
     const int   mode = h->mode == GMM_MODE_SUM ? 1 : 0;
 #define GMM_TC_LAUNCH(SWZ, NE)                                                                               \
@@ -941,4 +1007,152 @@ int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, u
                 wC / tiles);
     }
     return GMM_OK;
+}
+
+}  // namespace
+
+int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld) {
+    if (T == 0)
+        return GMM_OK;
+    TcJob job;
+    job.T       = T;
+    job.FT      = (T + kTileM - 1) / kTileM;
+    job.d_x     = d_x;
+    job.rowMap  = nullptr;
+    job.bTiles  = h->tensor.bTiles;
+    job.nTiles  = h->tensor.nTiles;
+    job.itemTab = nullptr;
+    job.nItems  = 0;
+    job.scores  = d_scores;
+    job.best    = d_best;
+    job.ld      = ld;
+    return tc_run(h, job);
+}
+
+// ---- subset scoring --------------------------------------------------------------------------------------------
+// The reference's context scorers evaluate a mixture only when a consumer asks for it (CachedContextScorer,
+// /root/reference/src/Mm/FeatureScorer.hh:170-230): an aligner touches the few hundred emissions of the segment's
+// automaton, not all M.  Here every segment gets its own B tiles, assembled from the canonical image one mixture
+// (mixCols rows = whole swizzle atoms) at a time, and an item table pairs them with the segment's frame tiles; the
+// scoring kernel itself is the one of the full path, so a (frame, mixture) score is bit-identical in both.
+namespace {
+
+__global__ void __launch_bounds__(256) gather_tiles_kernel(const uint8_t* __restrict__ bTiles, uint32_t tileBytes,
+                                                           uint32_t atoms, uint32_t swz, uint32_t mixCols,
+                                                           uint32_t mixPerTile, uint32_t mixPerPart, uint32_t parts,
+                                                           const uint32_t* __restrict__ vtMix,    // [nVt x mixPerTile]
+                                                           const uint32_t* __restrict__ vtBase,   // [nVt] first column
+                                                           uint32_t nVt, uint8_t* __restrict__ out) {
+    const uint32_t c16PerRow = swz / 16, operandU4 = atoms * kTileN * c16PerRow;
+    for (uint32_t vt = blockIdx.x; vt < nVt; vt += gridDim.x) {
+        uint8_t* dst = out + (size_t)vt * tileBytes;
+        for (uint32_t i = threadIdx.x; i < operandU4; i += blockDim.x) {
+            const uint32_t a = i / (kTileN * c16PerRow), rem = i % (kTileN * c16PerRow);
+            const uint32_t row = rem / c16PerRow, c = rem % c16PerRow;
+            const uint32_t m    = vtMix[vt * mixPerTile + row / mixCols];
+            const uint32_t srow = (m % mixPerTile) * mixCols + row % mixCols;
+            // rows move by multiples of 8 (mixCols is one), so the 16-byte chunk keeps its swizzled place in the row
+            const uint4* src = reinterpret_cast<const uint4*>(bTiles + (size_t)(m / mixPerTile) * tileBytes +
+                                                              (size_t)a * kTileN * swz + (size_t)srow * swz) + c;
+            reinterpret_cast<uint4*>(dst + (size_t)a * kTileN * swz + (size_t)row * swz)[c] = __ldg(src);
+        }
+        // slot table and TileMeta of a full canonical tile; the mixture base of every column part is this tile's
+        const uint32_t  metaOff = atoms * kTileN * swz;
+        const uint32_t* msrc    = reinterpret_cast<const uint32_t*>(bTiles + metaOff);
+        uint32_t*       mdst    = reinterpret_cast<uint32_t*>(dst + metaOff);
+        for (uint32_t i = threadIdx.x; i < kMetaBytes / 4; i += blockDim.x) {
+            uint32_t       v = msrc[i];
+            const uint32_t w = i - kTileN * 2 / 4;  // word index inside TileMeta (slots come first)
+            if (i >= kTileN * 2 / 4 && w >= 2 && w < 2 + parts)
+                v = vtBase[vt] + (w - 2) * mixPerPart;
+            mdst[i] = v;
+        }
+    }
+}
+
+}  // namespace
+
+bool gmm_tc_subset_capable(const gmm_handle* h) {
+    return h->floatValid && h->tensor.valid && h->tensor.regular && h->kernel == GMM_KERNEL_TENSOR;
+}
+
+// leading dimension a compact score block needs for segments whose longest emission list has maxListLength entries
+uint32_t gmm_tc_subset_ld(const gmm_handle* h, uint32_t maxListLength) {
+    const uint32_t mpt = std::max(1u, h->tensor.mixPerTile);
+    return std::max(1u, (maxListLength + mpt - 1) / mpt) * mpt;
+}
+
+int gmm_tc_score_subset(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const uint32_t* emOff,
+                        const uint32_t* emList, const float* d_x, float* d_scores, size_t ld) {
+    const TensorModel& tm = h->tensor;
+    if (!gmm_tc_subset_capable(h))
+        return GMM_ERR_UNSUPPORTED;
+    const uint32_t mpt = tm.mixPerTile, parts = kTileN / tm.partW, mixPerPart = tm.partW / tm.mixCols;
+    // tile-aligned row space, virtual tiles and items, segment by segment
+    std::vector<uint32_t> rowMap, vtMix, vtBase, items;
+    uint32_t              FT = 0;
+    for (uint32_t s = 0; s < nSeg; ++s) {
+        const uint32_t f0 = frameOffsets[s], f1 = frameOffsets[s + 1], n = emOff[s + 1] - emOff[s];
+        if (f1 <= f0 || n == 0)
+            continue;
+        if ((size_t)gmm_tc_subset_ld(h, n) > ld) {
+            h->setError("subset scoring: score block narrower than the segment's emission list");
+            return GMM_ERR_ARG;
+        }
+        const uint32_t ft0 = FT, nFt = (f1 - f0 + kTileM - 1) / kTileM;
+        FT += nFt;
+        rowMap.resize((size_t)FT * kTileM, 0xFFFFFFFFu);
+        for (uint32_t t = f0; t < f1; ++t)
+            rowMap[(size_t)ft0 * kTileM + (t - f0)] = t;
+        for (uint32_t v = 0; v * mpt < n; ++v) {
+            const uint32_t vt = (uint32_t)vtBase.size();
+            vtBase.push_back(v * mpt);
+            for (uint32_t j = 0; j < mpt; ++j) {
+                const uint32_t k = v * mpt + j;
+                const uint32_t m = emList[emOff[s] + (k < n ? k : 0)];  // spare places repeat the first mixture
+                if (m >= h->M) {
+                    h->setError("subset scoring: mixture index out of range");
+                    return GMM_ERR_ARG;
+                }
+                vtMix.push_back(m);
+            }
+            const uint32_t it[8] = {vt, ft0, ft0 + nFt, f0, f1, 0, 0, 0};
+            items.insert(items.end(), it, it + 8);
+        }
+    }
+    if (items.empty())
+        return GMM_OK;
+    const uint32_t nVt = (uint32_t)vtBase.size();
+    auto           al  = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t   oMap = 0, oMix = al(rowMap.size() * 4), oBase = oMix + al(vtMix.size() * 4),
+                 oItem = oBase + al(vtBase.size() * 4), total = oItem + al(items.size() * 4);
+    void *tab = nullptr, *vtiles = nullptr;
+    int   rc;
+    if ((rc = h->reserve(SCR_TAB, total, &tab)))
+        return rc;
+    if ((rc = h->reserve(SCR_VTILES, (size_t)nVt * tm.tileBytes, &vtiles)))
+        return rc;
+    char* d = (char*)tab;
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oMap, rowMap.data(), rowMap.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oMix, vtMix.data(), vtMix.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oBase, vtBase.data(), vtBase.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oItem, items.data(), items.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    gather_tiles_kernel<<<(int)std::min<uint32_t>(nVt, (uint32_t)h->smCount * 8), 256, 0, h->stream>>>(
+            tm.bTiles, tm.tileBytes, tm.nAtoms, tm.swz, tm.mixCols, mpt, mixPerPart, parts, (const uint32_t*)(d + oMix),
+            (const uint32_t*)(d + oBase), nVt, (uint8_t*)vtiles);
+    h->launches++;
+    GMM_CUDA_TRY(h, cudaGetLastError());
+    TcJob job;
+    job.T       = FT * kTileM;
+    job.FT      = FT;
+    job.d_x     = d_x;
+    job.rowMap  = (const uint32_t*)(d + oMap);
+    job.bTiles  = (const uint8_t*)vtiles;
+    job.nTiles  = nVt;
+    job.itemTab = (const uint32_t*)(d + oItem);
+    job.nItems  = nVt;
+    job.scores  = d_scores;
+    job.best    = nullptr;
+    job.ld      = ld;
+    return tc_run(h, job);
 }

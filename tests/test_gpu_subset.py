@@ -1,0 +1,70 @@
+"""GPU: subset scoring (gmm_score_subset_device) gives, for the listed mixtures of every segment, the very bits the
+full tensor-kernel pass gives, and stays within the float bar of the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from rasr_b200 import capi, synth, tables
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def eng():
+    e = capi.Engine(0)
+    yield e
+    e.close()
+
+
+def upload(eng, ms, mode=capi.MODE_MAX):
+    t = tables.float_tables(ms)
+    eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=mode,
+                     kernel=capi.KERNEL_TENSOR)
+
+
+@pytest.mark.parametrize("M,K,D,cov,mode", [(4501, 16, 45, "pooled", capi.MODE_MAX), (300, 8, 20, "density", capi.MODE_MAX),
+                                            (97, 32, 33, "pooled", capi.MODE_MAX), (200, 16, 24, "pooled", capi.MODE_SUM),
+                                            (64, 3, 9, "mixture", capi.MODE_MAX)])
+def test_subset_equals_full_scoring(eng, oracle, M, K, D, cov, mode):
+    ms = synth.make_model(M=M, K=K, D=D, seed=M + K, covariance=cov)
+    rng = np.random.default_rng(M)
+    lens = [1, 127, 128, 129, 0, 700, 33] + [int(n) for n in rng.integers(1, 400, 12)]
+    fo = np.cumsum([0] + lens).astype(np.uint32)
+    x = synth.make_features(ms, int(fo[-1]), seed=3)
+    upload(eng, ms, mode)
+    dx = torch.from_numpy(x).cuda()
+    full = torch.empty((x.shape[0], M), device="cuda")
+    eng.score_device(x.shape[0], dx, full)
+    lists = [rng.choice(M, size=int(n), replace=False) for n in rng.integers(1, min(M, 350), len(lens))]
+    lists[3] = np.arange(M)[::-1].copy()            # a whole model, backwards
+    lists[5] = np.array([M - 1])                    # a single mixture
+    lo = np.cumsum([0] + [len(v) for v in lists]).astype(np.uint32)
+    ld = eng.subset_ld(max(len(v) for v in lists))
+    sub = torch.full((x.shape[0], ld), -1.0, device="cuda")
+    eng.score_subset_device(fo, lo, np.concatenate(lists), dx, sub, ld)
+    eng.sync()
+    full, sub = full.cpu().numpy(), sub.cpu().numpy()
+    for s, v in enumerate(lists):
+        rows = slice(int(fo[s]), int(fo[s + 1]))
+        assert np.array_equal(sub[rows, :len(v)].view(np.uint32), full[rows][:, v].view(np.uint32)), s
+    if mode == capi.MODE_MAX:
+        ref, _ = oracle.score_max(ms, x[:int(fo[2])])
+        rows = slice(int(fo[1]), int(fo[2]))
+        r = ref[rows][:, lists[1]]
+        g = sub[rows, :len(lists[1])]
+        assert np.max(np.abs(g - r) / np.maximum(np.abs(r), 1)) <= 1e-4
+
+
+def test_subset_needs_a_regular_model(eng):
+    ms = synth.make_model(M=40, K=6, D=10, ragged=True, seed=2)
+    upload(eng, ms)
+    dx = torch.zeros((4, 10), device="cuda")
+    out = torch.zeros((4, 64), device="cuda")
+    with pytest.raises(capi.GmmError, match="same number"):
+        eng.score_subset_device([0, 4], [0, 2], [1, 2], dx, out, 64)
+    ms = synth.make_model(M=40, K=8, D=10, seed=2)
+    upload(eng, ms)
+    with pytest.raises(capi.GmmError, match="narrower"):
+        eng.score_subset_device([0, 4], [0, 40], np.arange(40), dx, out, 8)
+    with pytest.raises(capi.GmmError, match="out of range"):
+        eng.score_subset_device([0, 4], [0, 1], [40], dx, out, 64)
