@@ -64,6 +64,8 @@ struct AlignParams {
     const uint32_t* emOff;     // [nSeg + 1] the distinct emission indices each segment's automaton uses ...
     const uint32_t* emList;    // ... (a frame's scores are gathered once per distinct emission, not per arc)
     const uint32_t* inEm;
+    const uint32_t* inCol;      // column of the score block an arc reads: inEm, or inEmSlot for a compact block
+    uint32_t        compact;    // score block holds, per segment, one column per entry of its emission list
     const float*    inW;
     const uint32_t* outOff;     // [nStates + 1] the caller's arc lists (Fsa order) ...
     const uint32_t* outTarget;  // ... segment-local target ...
@@ -106,7 +108,7 @@ __device__ uint32_t ordered_pass(const AlignParams& p, const AlignSeg& sg, float
             for (uint32_t a = p.outOff[sg.state0 + s]; a < p.outOff[sg.state0 + s + 1]; ++a) {
                 const uint32_t k   = p.outToIn[a];
                 const uint32_t tgt = p.outTarget[a];
-                const float    c   = __fadd_rn(__fadd_rn(sc, p.inW[k]), row[p.inEm[k]]);
+                const float    c   = __fadd_rn(__fadd_rn(sc, p.inW[k]), row[p.inCol[k]]);
                 if (stamp[tgt] != t + 1) {
                     stamp[tgt]  = t + 1;
                     pos[tgt]    = nCur;
@@ -168,7 +170,7 @@ __global__ void __launch_bounds__(256) align_generic_kernel(const AlignParams p)
                     const float from = cur[p.inSrc[a]];
                     if (from == INFINITY)
                         continue;  // no hypothesis, or one that cannot win any more
-                    const float c = __fadd_rn(__fadd_rn(from, p.inW[a]), row[p.inEm[a]]);
+                    const float c = __fadd_rn(__fadd_rn(from, p.inW[a]), row[p.inCol[a]]);
                     if (bestArc == kNoArc || c < best) {
                         best    = c;
                         bestArc = a;
@@ -290,7 +292,7 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
                 const float* row = p.scores + (size_t)(sg.frame0 + f) * p.ld;
                 float*       dst = ring + (size_t)(f % K) * nEm;
                 for (uint32_t e = tid; e < nEm; e += nThreads)
-                    cp_async4(dst + e, row + emIds[e]);
+                    cp_async4(dst + e, row + (p.compact ? e : emIds[e]));
             }
             cp_async_commit();
         };
@@ -464,12 +466,38 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
 
 }  // namespace
 
+bool gmm_align_emission_lists(uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                              const uint32_t* arcEmission, uint32_t nEmissions, std::vector<uint32_t>& emOff,
+                              std::vector<uint32_t>& emList, uint32_t* arcSlot) {
+    std::vector<uint32_t> slotOf(nEmissions, 0), seenIn(nEmissions, 0);
+    emOff.assign(nSeg + 1, 0);
+    emList.clear();
+    for (uint32_t i = 0; i < nSeg; ++i) {
+        if (stateOffsets[i + 1] < stateOffsets[i] || arcOffsets[stateOffsets[i + 1]] < arcOffsets[stateOffsets[i]])
+            return false;
+        for (uint32_t a = arcOffsets[stateOffsets[i]]; a < arcOffsets[stateOffsets[i + 1]]; ++a) {
+            const uint32_t e = arcEmission[a];
+            if (e >= nEmissions)
+                return false;
+            if (seenIn[e] != i + 1) {  // first use of this emission in segment i
+                seenIn[e] = i + 1;
+                slotOf[e] = (uint32_t)emList.size() - emOff[i];
+                emList.push_back(e);
+            }
+            if (arcSlot)
+                arcSlot[a] = slotOf[e];
+        }
+        emOff[i + 1] = (uint32_t)emList.size();
+    }
+    return true;
+}
+
 // Host arrays in, host arrays out; `d_scores` is the DEVICE score block.  See include/gmm_b200.h.
 int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
                      const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
-                     const uint32_t** d_pathEmission) {
+                     const uint32_t** d_pathEmission, bool compact, uint32_t nEmissions) {
     if (d_pathEmission)
         *d_pathEmission = nullptr;
     if (nSeg == 0)
@@ -478,8 +506,12 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     const uint32_t nArcs   = arcOffsets[nStates];
     // incoming-arc lists (CSR by target), arcs of a state ordered by (source state, arc index)
     std::vector<uint32_t> inOff(nStates + 1, 0), inSrc(nArcs), inSK(nArcs), inEm(nArcs), outToIn(nArcs);
-    std::vector<uint32_t> arcSlot(nArcs), inEmSlot(nArcs), emOff(nSeg + 1, 0), emList, slotOf(ld, 0), seenIn(ld, 0);
-    emList.reserve(nArcs);
+    std::vector<uint32_t> arcSlot(nArcs), inEmSlot(nArcs), emOff, emList;
+    const uint32_t        emLimit = compact ? nEmissions : (uint32_t)std::min<size_t>(ld, 0xFFFFFFFFu);
+    if (!gmm_align_emission_lists(nSeg, stateOffsets, arcOffsets, arcEmission, emLimit, emOff, emList, arcSlot.data())) {
+        h->setError("gmm_align: arc offsets not ascending or emission index outside the score block");
+        return GMM_ERR_ARG;
+    }
     std::vector<float>    inW(nArcs);
     std::vector<AlignSeg> segs(nSeg);
     uint64_t              backTotal = 0, mapTotal = 0;
@@ -503,21 +535,13 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                     h->setError("gmm_align: arc target outside its segment's automaton");
                     return GMM_ERR_ARG;
                 }
-                if (arcEmission[a] >= ld) {
-                    h->setError("gmm_align: emission index >= ld");
-                    return GMM_ERR_ARG;
-                }
                 inOff[s0 + arcTarget[a] + 1]++;
-                const uint32_t e = arcEmission[a];
-                if (seenIn[e] != i + 1) {  // first use of this emission in segment i
-                    seenIn[e] = i + 1;
-                    slotOf[e] = (uint32_t)emList.size() - emOff[i];
-                    emList.push_back(e);
-                }
-                arcSlot[a] = slotOf[e];
             }
         }
-        emOff[i + 1]   = (uint32_t)emList.size();
+        if (compact && emOff[i + 1] - emOff[i] > ld) {
+            h->setError("gmm_align: compact score block narrower than a segment's emission list");
+            return GMM_ERR_ARG;
+        }
         uint32_t shift = 0;
         while ((1u << shift) < degree)
             ++shift;
@@ -606,8 +630,9 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     GMM_CUDA_TRY(h, up(oEm, inEm.data(), (size_t)nArcs * 4));
     GMM_CUDA_TRY(h, up(oW, inW.data(), (size_t)nArcs * 4));
     GMM_CUDA_TRY(h, up(oFin, finalWeight, (size_t)nStates * 4));
-    if (inFlight) {
+    if (inFlight || compact)
         GMM_CUDA_TRY(h, up(oSlot, inEmSlot.data(), (size_t)nArcs * 4));
+    if (inFlight) {
         GMM_CUDA_TRY(h, up(oEmOff, emOff.data(), (nSeg + 1) * 4));
         GMM_CUDA_TRY(h, up(oEmList, emList.data(), emList.size() * 4));
     }
@@ -627,6 +652,8 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     p.inSK         = (const uint32_t*)(d + oSK);
     p.inEm         = (const uint32_t*)(d + oEm);
     p.inEmSlot     = (const uint32_t*)(d + oSlot);
+    p.inCol        = compact ? p.inEmSlot : p.inEm;
+    p.compact      = compact ? 1u : 0u;
     p.emOff        = (const uint32_t*)(d + oEmOff);
     p.emList       = (const uint32_t*)(d + oEmList);
     p.inW          = (const float*)(d + oW);

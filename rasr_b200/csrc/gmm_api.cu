@@ -485,17 +485,41 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
         const uint32_t inDim = h->lda.valid ? h->lda.baseDim : h->D;
         if ((rc = uploadFrames(h, h->D, n, fo.data(), x + (size_t)f0 * inDim, &dx)))
             return rc;
-        if ((rc = h->reserve(SCR_SCORE, (size_t)std::max(1u, T) * devLd * 4, &ds)))
+        // Lazy evaluation as the reference's cached context scorers do it (FeatureScorer.hh:170-230): only the
+        // emissions a segment's automaton can ask for are scored, into a compact block whose column j is entry j of
+        // the segment's emission list; the bits are those of the full pass.  Taken when it saves tensor work.
+        std::vector<uint32_t> emOff, emList;
+        bool                  compact = false;
+        size_t                ldUse   = devLd;
+        const char*           env     = getenv("GMM_ALIGN_SUBSET");
+        if (T && gmm_tc_subset_capable(h) && !(env && env[0] == '0') && arcEmission &&
+            gmm_align_emission_lists(n, so.data(), ao.data(), arcEmission + a0, h->M, emOff, emList)) {
+            uint32_t maxList = 0;
+            double   subsetWork = 0, fullWork = (double)((T + 127) / 128) * ((h->M + h->tensor.mixPerTile - 1) / h->tensor.mixPerTile);
+            for (uint32_t i = 0; i < n; ++i) {
+                const uint32_t len = emOff[i + 1] - emOff[i];
+                maxList            = std::max(maxList, len);
+                subsetWork += (double)((fo[i + 1] - fo[i] + 127) / 128) * ((len + h->tensor.mixPerTile - 1) / h->tensor.mixPerTile);
+            }
+            compact = (env && env[0] == '1') || subsetWork < 0.6 * fullWork;
+            if (compact)
+                ldUse = gmm_tc_subset_ld(h, std::max(1u, maxList));
+        }
+        if ((rc = h->reserve(SCR_SCORE, (size_t)std::max(1u, T) * ldUse * 4, &ds)))
             return rc;
         if (T) {
-            if ((rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, nullptr, devLd)))
+            if (compact)
+                rc = gmm_tc_score_subset(h, n, fo.data(), emOff.data(), emList.data(), (const float*)dx, (float*)ds, ldUse);
+            else
+                rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, nullptr, devLd);
+            if (rc)
                 return rc;
         }
-        if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, devLd, so.data(), ao.data(),
+        if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, ldUse, so.data(), ao.data(),
                                    arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
                                    arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0,
                                    pathEmission ? pathEmission + f0 : nullptr, pathState ? pathState + f0 : nullptr,
-                                   pathScore ? pathScore + s0 : nullptr, &dPath)))
+                                   pathScore ? pathScore + s0 : nullptr, &dPath, compact, h->M)))
             return rc;
         // the aligned frames go straight into the estimators: the path is the per-frame mixture (kNoArc: skip)
         if (accumulate && T && (rc = gmm_accum_launch(h, T, (const float*)dx, dPath, nullptr, nullptr)))

@@ -158,7 +158,12 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
-                     const uint32_t** d_pathEmission = nullptr);
+                     const uint32_t** d_pathEmission = nullptr, bool compact = false, uint32_t nEmissions = 0);
+// the distinct emissions of every segment's automaton in order of first use (the column order of a compact score
+// block: gmm_tc_score_subset writes it, gmm_align_launch(compact) reads it)
+bool gmm_align_emission_lists(uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                              const uint32_t* arcEmission, uint32_t nEmissions, std::vector<uint32_t>& emOff,
+                              std::vector<uint32_t>& emList, uint32_t* arcSlot = nullptr);
 int gmm_lda_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_base, float* d_x);
 int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
                      uint32_t* d_best);

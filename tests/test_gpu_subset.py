@@ -68,3 +68,37 @@ def test_subset_needs_a_regular_model(eng):
         eng.score_subset_device([0, 4], [0, 40], np.arange(40), dx, out, 8)
     with pytest.raises(capi.GmmError, match="out of range"):
         eng.score_subset_device([0, 4], [0, 1], [40], dx, out, 64)
+
+
+@pytest.mark.parametrize("align_kernel", ["ranked", "generic"])
+def test_alignment_over_compact_score_blocks(eng, oracle, monkeypatch, align_kernel):
+    """gmm_score_align_host scores only the emissions each automaton can ask for (compact block, one column per
+    entry of the segment's emission list): paths, states and path scores must be the bits of the full-block run, and
+    the oracle's Viterbi path over the engine's own scores."""
+    from rasr_b200.align import AlignmentAutomata, linear_hmm
+    if align_kernel == "generic":
+        monkeypatch.setenv("GMM_ALIGN_KERNEL", "generic")
+    ms = synth.make_model(M=1200, K=16, D=45, seed=5)
+    rng = np.random.default_rng(3)
+    lens = [300, 0, 129, 1, 700, 64]
+    fo = np.cumsum([0] + lens).astype(np.uint32)
+    x = synth.make_features(ms, int(fo[-1]), seed=9)
+    segs = [linear_hmm(rng.integers(0, ms.M, n), loop=3.0, forward=0.0, skip=30.0) for n in (40, 5, 33, 1, 290, 17)]
+    au = AlignmentAutomata.from_arc_lists(segs)
+    upload(eng, ms)
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("GMM_ALIGN_SUBSET", flag)
+        n0 = eng.launch_count
+        out[flag] = eng.score_align_host(fo, x, au)
+        out[flag + "n"] = eng.launch_count - n0
+    for a, b in zip(out["0"], out["1"]):
+        assert np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+    assert out["1n"] == out["0n"] + 1            # the tile gather is the one extra launch of the compact path
+    monkeypatch.delenv("GMM_ALIGN_SUBSET")
+    auto = eng.score_align_host(fo, x, au)       # the work estimate picks the compact path here by itself
+    assert np.array_equal(auto[0], out["1"][0])
+    s, _ = eng.score_host(x, want_best=False)
+    emo, sto, sco = oracle.viterbi_align(fo, s, au)
+    assert np.array_equal(out["1"][0], emo) and np.array_equal(out["1"][1], sto)
+    assert np.array_equal(out["1"][2].view(np.uint32), sco.view(np.uint32))
