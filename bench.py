@@ -332,7 +332,7 @@ def run_ours(args):
 
     # features in, best paths out: scores stay in HBM and feed the Viterbi consumer
     from rasr_b200.align import AlignmentAutomata, linear_hmm
-    al_segs = segs
+    al_segs = 2 * segs        # both input batches in one call: groups of segments alternate between two lanes
     al_frames = al_segs * SEG_FRAMES
     rng = np.random.default_rng(77 + rank)
     automata = AlignmentAutomata.from_arc_lists(
@@ -390,8 +390,10 @@ def run_ours(args):
                     "api": "gmm_score_host (C-ABI, pinned host buffers)"},
             "e2e_alignment": {"value": al_value, "unit": UNIT, "h2d_bytes_per_step": al_frames * ms.D * 4,
                               "d2h_bytes_per_step": al_frames * 4 + al_segs * 4, "frames_per_step_per_gpu": al_frames,
-                              "api": "gmm_score_align_host (C-ABI): host features -> scores kept in HBM -> Viterbi "
-                                     "best path per segment (300-state loop/forward/skip automata) -> host paths",
+                              "api": "gmm_score_align_host (C-ABI): host features -> scores of the emissions each "
+                                     "segment's automaton uses (compact block, kept in HBM) -> Viterbi best path per "
+                                     "segment (300-state loop/forward/skip automata) -> host paths; groups of 296 "
+                                     "segments alternate between two streams, tables built by a host thread pool",
                               "note": "not the headline e2e: the consumer of the scores runs on the device, so "
                                       "only 4 bytes per frame return"},
             "e2e_training_pass": {"value": tr_value, "unit": UNIT, "h2d_bytes_per_step": al_frames * ms.D * 4,

@@ -1,5 +1,5 @@
 """Timing of the alignment consumer on resident scores: kernel (CUDA events inside the library) and whole call.
-usage: python profiles/time_align.py [segments] [frames_per_segment] [emissions_per_automaton]"""
+usage: python profiles/time_align.py [segments] [frames_per_segment] [emissions_per_automaton] [columns of the score block]"""
 import os
 import sys
 import time
@@ -14,7 +14,7 @@ from rasr_b200.align import AlignmentAutomata, linear_hmm  # noqa: E402
 segs = int(sys.argv[1]) if len(sys.argv) > 1 else 512
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 1000
 n = int(sys.argv[3]) if len(sys.argv) > 3 else 300
-M = 4501
+M = int(sys.argv[4]) if len(sys.argv) > 4 else 4501
 eng = capi.Engine(0)
 rng = np.random.default_rng(0)
 au = AlignmentAutomata.from_arc_lists([linear_hmm(rng.integers(0, M, n), 3.0, 0.0, 30.0) for _ in range(segs)])

@@ -27,8 +27,10 @@ x = torch.from_numpy(synth.make_features(ms, min(segs * T, 64000), seed=2)).repe
 x = x[:segs * T].contiguous().pin_memory().numpy()
 eng.create_accumulators(tables.mean_index(ms), ms.n_means)
 ref = None
-for flag in ("0", "1"):
+cases = [("0", "100000"), ("1", "100000"), ("1", "296"), ("1", "148"), ("1", "74")]
+for flag, group in cases:
     os.environ["GMM_ALIGN_SUBSET"] = flag
+    os.environ["GMM_ALIGN_GROUP"] = group
     for acc in (False, True):
         for _ in range(2):
             out = eng.score_align_host(fo, x, au, want_states=False, accumulate=acc, want_paths=not acc)
@@ -42,7 +44,7 @@ for flag in ("0", "1"):
         wall = (time.perf_counter() - t0) / reps
         kms, k = eng.kernel_time()
         eng.kernel_timing(False)
-        print(f"subset={flag} accumulate={acc}: {segs} x {T} frames, {n} emissions: call {wall * 1e3:.2f} ms = "
+        print(f"subset={flag} group={group} accumulate={acc}: {segs} x {T} frames, {n} emissions: call {wall * 1e3:.2f} ms = "
               f"{segs * T / wall / 1e6:.1f} M frames/s; timed kernels {kms / reps:.2f} ms per call ({k // reps} launches)")
         if not acc:
             if ref is None:

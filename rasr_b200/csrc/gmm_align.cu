@@ -34,6 +34,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <vector>
 
 #include "gmm_internal.cuh"
@@ -42,6 +43,7 @@ namespace {
 
 constexpr uint32_t kNoArc       = 0xFFFFFFFFu;
 constexpr uint32_t kBlockFrames = 32;  // traceback block
+constexpr int      kFastArcs    = 4;   // ranked kernel: incoming arcs per state kept in registers once the list is frozen
 
 struct AlignSeg {
     uint32_t frame0, frames;  // rows [frame0, frame0 + frames) of the score block
@@ -298,6 +300,17 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
         };
         for (uint32_t f = 0; f + 1 < (uint32_t)K; ++f)
             prefetch(f);
+        // fast frames (below): one state per thread and no state with more than kFastArcs incoming arcs
+        const uint32_t rArc0 = tid < S ? offs[tid] : 0, rDeg = tid < S ? offs[tid + 1] - offs[tid] : 0;
+        const int      fast  = __syncthreads_and(rDeg <= (uint32_t)kFastArcs) && S <= nThreads;
+        uint32_t       rSrc[kFastArcs], rEm[kFastArcs], rKey[kFastArcs];
+        float          rW[kFastArcs];
+#pragma unroll
+        for (int j = 0; j < kFastArcs; ++j) {
+            rSrc[j] = rEm[j] = 0;
+            rKey[j] = kNoArc;
+            rW[j]   = 0.f;
+        }
         int stable = 0;
         for (uint32_t t = 0; t < T; ++t) {
             cp_async_wait<K - 2>();
@@ -310,6 +323,33 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
             const bool     emitMap  = ((t + 1) % kBlockFrames) == 0 || t + 1 == T;
             uint32_t*      mapRow   = p.map + sg.map0 + (size_t)(t / kBlockFrames) * S;
             const uint32_t keyMask  = (1u << sg.keyShift) - 1;
+            if (stable && fast) {
+                // frozen hypothesis list, one state per thread, its (at most 4) incoming arcs in registers: a frame is
+                // two rounds of independent shared-memory loads, the comparisons, three stores and one barrier
+                if (tid < S) {
+                    float    best = INFINITY;
+                    uint32_t bestJ = kNoArc, bestKey = 0, bestSrc = 0;
+#pragma unroll
+                    for (int j = 0; j < kFastArcs; ++j) {
+                        if (rKey[j] != kNoArc) {  // the arc exists and its source carries a hypothesis
+                            const float c = __fadd_rn(__fadd_rn(cur[rSrc[j]], rW[j]), E[rEm[j]]);
+                            if (bestJ == kNoArc || c < best || (c == best && rKey[j] > bestKey)) {
+                                best    = c;
+                                bestJ   = (uint32_t)j;
+                                bestKey = rKey[j];
+                                bestSrc = rSrc[j];
+                            }
+                        }
+                    }
+                    nxt[tid] = best;
+                    bk[tid]  = bestJ == kNoArc ? kNoArc : rArc0 + bestJ;
+                    const uint32_t anc = bestJ == kNoArc ? kNoArc : (boundary ? bestSrc : ancO[bestSrc]);
+                    ancN[tid]          = anc;
+                    if (emitMap)
+                        mapRow[tid] = anc;
+                }
+            }
+            else
             for (uint32_t s = tid; s < S; s += nThreads) {
                 float    best = INFINITY;
                 uint32_t bestArc = kNoArc, bestKey = 0, firstKey = kNoArc, bestSrc = 0;
@@ -375,6 +415,19 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
                 uint32_t* sw = rankO;
                 rankO        = rankN;
                 rankN        = sw;
+                if (stable && fast && tid < S) {  // the frozen ranks give every arc its final arrival key
+#pragma unroll
+                    for (int j = 0; j < kFastArcs; ++j) {
+                        rKey[j] = kNoArc;
+                        if ((uint32_t)j < rDeg) {
+                            const uint32_t sk = tabSK[rArc0 + j], r = rankO[sk >> 16];
+                            rSrc[j]           = sk >> 16;
+                            rW[j]             = tabW[rArc0 + j];
+                            rEm[j]            = tabEm[rArc0 + j];
+                            rKey[j]           = r == kNoArc ? kNoArc : ((r << sg.keyShift) | (sk & keyMask));
+                        }
+                    }
+                }
             }
             float* sf = cur;
             cur       = nxt;
@@ -466,29 +519,59 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
 
 }  // namespace
 
-bool gmm_align_emission_lists(uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
-                              const uint32_t* arcEmission, uint32_t nEmissions, std::vector<uint32_t>& emOff,
-                              std::vector<uint32_t>& emList, uint32_t* arcSlot) {
-    std::vector<uint32_t> slotOf(nEmissions, 0), seenIn(nEmissions, 0);
-    emOff.assign(nSeg + 1, 0);
-    emList.clear();
-    for (uint32_t i = 0; i < nSeg; ++i) {
+bool gmm_align_emission_lists(gmm_handle* h, uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                              const uint32_t* arcEmission, uint32_t nEmissions, AlignLists& out) {
+    for (uint32_t i = 0; i < nSeg; ++i)
         if (stateOffsets[i + 1] < stateOffsets[i] || arcOffsets[stateOffsets[i + 1]] < arcOffsets[stateOffsets[i]])
             return false;
-        for (uint32_t a = arcOffsets[stateOffsets[i]]; a < arcOffsets[stateOffsets[i + 1]]; ++a) {
-            const uint32_t e = arcEmission[a];
-            if (e >= nEmissions)
-                return false;
-            if (seenIn[e] != i + 1) {  // first use of this emission in segment i
-                seenIn[e] = i + 1;
-                slotOf[e] = (uint32_t)emList.size() - emOff[i];
-                emList.push_back(e);
-            }
-            if (arcSlot)
-                arcSlot[a] = slotOf[e];
+    const uint32_t nArcs = arcOffsets[stateOffsets[nSeg]] - arcOffsets[stateOffsets[0]], arc0 = arcOffsets[stateOffsets[0]];
+    out.arcSlot.resize(nArcs);
+    out.emOff.assign(nSeg + 1, 0);
+    std::vector<uint32_t>& sparse = out.scratch;  // segment i's list at its first arc; emOff[i + 1] = its length
+    sparse.resize(nArcs);
+    std::atomic<bool> bad(false);
+    HostPool&         pool = h->hostPool();
+    pool.run(nSeg, std::max(1u, nSeg / (4 * (uint32_t)pool.size())), [&](uint32_t i0, uint32_t i1, int worker) {
+        gmm_handle::EmissionStamps& w = h->workerStamps[worker];
+        if (w.stamp.size() != nEmissions) {
+            w.slotOf.assign(nEmissions, 0);
+            w.stamp.assign(nEmissions, 0);
+            w.counter = 0;
         }
-        emOff[i + 1] = (uint32_t)emList.size();
-    }
+        uint32_t *slotOf = w.slotOf.data(), *stamp = w.stamp.data(), &counter = w.counter;
+        for (uint32_t i = i0; i < i1; ++i) {
+            if (++counter == 0) {  // stamps wrapped: start over
+                std::fill(stamp, stamp + nEmissions, 0u);
+                counter = 1;
+            }
+            const uint32_t a0 = arcOffsets[stateOffsets[i]], a1 = arcOffsets[stateOffsets[i + 1]];
+            uint32_t*      list = sparse.data() + (a0 - arc0);
+            uint32_t       n    = 0;
+            for (uint32_t a = a0; a < a1; ++a) {
+                const uint32_t e = arcEmission[a];
+                if (e >= nEmissions) {
+                    bad = true;
+                    break;
+                }
+                if (stamp[e] != counter) {  // first use of this emission in segment i
+                    stamp[e]  = counter;
+                    slotOf[e] = n;
+                    list[n++] = e;
+                }
+                out.arcSlot[a - arc0] = slotOf[e];
+            }
+            out.emOff[i + 1] = n;
+        }
+    });
+    if (bad)
+        return false;
+    for (uint32_t i = 0; i < nSeg; ++i)
+        out.emOff[i + 1] += out.emOff[i];
+    out.emList.resize(out.emOff[nSeg]);
+    for (uint32_t i = 0; i < nSeg; ++i)
+        if (out.emOff[i + 1] > out.emOff[i])
+            memcpy(out.emList.data() + out.emOff[i], sparse.data() + (arcOffsets[stateOffsets[i]] - arc0),
+                   (size_t)(out.emOff[i + 1] - out.emOff[i]) * 4);
     return true;
 }
 
@@ -497,95 +580,154 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
-                     const uint32_t** d_pathEmission, bool compact, uint32_t nEmissions) {
+                     const uint32_t** d_pathEmission, bool compact, uint32_t nEmissions, AlignDeferred* defer,
+                     const AlignLists* lists) {
+    if (defer)
+        defer->pending = false;
     if (d_pathEmission)
         *d_pathEmission = nullptr;
     if (nSeg == 0)
         return GMM_OK;
     const uint32_t nStates = stateOffsets[nSeg], nFrames = frameOffsets[nSeg];
     const uint32_t nArcs   = arcOffsets[nStates];
-    // incoming-arc lists (CSR by target), arcs of a state ordered by (source state, arc index)
-    std::vector<uint32_t> inOff(nStates + 1, 0), inSrc(nArcs), inSK(nArcs), inEm(nArcs), outToIn(nArcs);
-    std::vector<uint32_t> arcSlot(nArcs), inEmSlot(nArcs), emOff, emList;
-    const uint32_t        emLimit = compact ? nEmissions : (uint32_t)std::min<size_t>(ld, 0xFFFFFFFFu);
-    if (!gmm_align_emission_lists(nSeg, stateOffsets, arcOffsets, arcEmission, emLimit, emOff, emList, arcSlot.data())) {
-        h->setError("gmm_align: arc offsets not ascending or emission index outside the score block");
-        return GMM_ERR_ARG;
+    // the distinct emissions of every automaton (one gather / one compact column each) and each arc's place in them
+    AlignLists        own;
+    const AlignLists* L = lists;
+    const uint32_t    emLimit = compact ? nEmissions : (uint32_t)std::min<size_t>(ld, 0xFFFFFFFFu);
+    if (!L) {
+        if (!gmm_align_emission_lists(h, nSeg, stateOffsets, arcOffsets, arcEmission, emLimit, own)) {
+            h->setError("gmm_align: arc offsets not ascending or emission index outside the score block");
+            return GMM_ERR_ARG;
+        }
+        L = &own;
     }
-    std::vector<float>    inW(nArcs);
-    std::vector<AlignSeg> segs(nSeg);
-    uint64_t              backTotal = 0, mapTotal = 0;
-    uint32_t              maxStates = 0, maxDegree = 0;
-    size_t                maxWords[3] = {0, 0, 0};  // shared memory of the ranked kernel with 8 / 4 / 2 frames in flight
+    const std::vector<uint32_t>&emOff = L->emOff, &emList = L->emList, &arcSlot = L->arcSlot;
+    // Every table the kernels read is built in ONE pinned host block laid out like its device copy (tables of both
+    // kernels first, those only the generic kernel reads last), so a launch costs one asynchronous copy.
+    auto   al   = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    size_t off  = 0;
+    auto   take = [&](size_t bytes) {
+        size_t o = off;
+        off += al(bytes);
+        return o;
+    };
+    const size_t oSeg = take(nSeg * sizeof(AlignSeg)), oOff = take((nStates + 1) * 4), oSK = take((size_t)nArcs * 4),
+                 oEm = take((size_t)nArcs * 4), oW = take((size_t)nArcs * 4), oFin = take((size_t)nStates * 4),
+                 oSlot = take((size_t)nArcs * 4), oEmOff = take((nSeg + 1) * 4), oEmList = take(emList.size() * 4),
+                 oCnt = take(4), rankedBytes = off, oSrc = take((size_t)nArcs * 4), oOut = take((nStates + 1) * 4),
+                 oTgt = take((size_t)nArcs * 4), oO2i = take((size_t)nArcs * 4), tableBytes = off;
+    void* pin = nullptr;
+    int   rc  = h->reservePinned(PIN_ALIGN, tableBytes, &pin);
+    if (rc)
+        return rc;
+    char*     hp       = (char*)pin;
+    AlignSeg* segs     = (AlignSeg*)(hp + oSeg);
+    uint32_t *inOff = (uint32_t*)(hp + oOff), *inSK = (uint32_t*)(hp + oSK), *inEm = (uint32_t*)(hp + oEm),
+             *inEmSlot = (uint32_t*)(hp + oSlot), *inSrc = (uint32_t*)(hp + oSrc), *outToIn = (uint32_t*)(hp + oO2i);
+    float*    inW      = (float*)(hp + oW);
+    *(uint32_t*)(hp + oCnt) = 0;
+    // segments are independent (targets are segment-local: the incoming arcs of a segment's states are its own arcs,
+    // so its part of the incoming-arc CSR starts where its arcs start); the per-arc work runs on the host pool
+    uint64_t backTotal = 0, mapTotal = 0;
+    uint32_t maxStates = 0;
     for (uint32_t i = 0; i < nSeg; ++i) {
         const uint32_t s0 = stateOffsets[i], s1 = stateOffsets[i + 1];
         if (s1 < s0 || frameOffsets[i + 1] < frameOffsets[i] || initialState[i] >= std::max(1u, s1 - s0)) {
             h->setError("gmm_align: offsets not ascending or initial state out of range");
             return GMM_ERR_ARG;
         }
-        uint32_t degree = 0;
-        for (uint32_t s = s0; s < s1; ++s) {
-            if (arcOffsets[s + 1] < arcOffsets[s]) {
-                h->setError("gmm_align: arc offsets not ascending");
-                return GMM_ERR_ARG;
-            }
-            degree = std::max(degree, arcOffsets[s + 1] - arcOffsets[s]);
-            for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a) {
-                if (arcTarget[a] >= s1 - s0) {
-                    h->setError("gmm_align: arc target outside its segment's automaton");
-                    return GMM_ERR_ARG;
-                }
-                inOff[s0 + arcTarget[a] + 1]++;
-            }
-        }
         if (compact && emOff[i + 1] - emOff[i] > ld) {
             h->setError("gmm_align: compact score block narrower than a segment's emission list");
             return GMM_ERR_ARG;
         }
-        uint32_t shift = 0;
-        while ((1u << shift) < degree)
-            ++shift;
         AlignSeg& sg = segs[i];
         sg.frame0    = frameOffsets[i];
         sg.frames    = frameOffsets[i + 1] - frameOffsets[i];
         sg.state0    = s0;
         sg.states    = s1 - s0;
         sg.initial   = initialState[i];
-        sg.keyShift  = shift;
+        sg.keyShift  = 0;
         sg.back0     = backTotal;
         sg.map0      = mapTotal;
         backTotal += (uint64_t)sg.frames * sg.states;
         mapTotal += (uint64_t)((sg.frames + kBlockFrames - 1) / kBlockFrames) * sg.states;
         maxStates = std::max(maxStates, sg.states);
-        maxDegree = std::max(maxDegree, degree);
-        const uint64_t keyBits = (uint64_t)sg.states << shift;
-        const uint32_t segArcs = arcOffsets[s1] - arcOffsets[s0];
-        for (int k = 0; k < 3; ++k)
-            maxWords[k] = std::max(maxWords[k], keyBits >= ((uint64_t)1 << 31)
-                                                        ? (size_t)1 << 40
-                                                        : ranked_smem_words(sg.states, segArcs, emOff[i + 1] - emOff[i],
-                                                                            (uint32_t)((keyBits + 31) >> 5), 8 >> k));
     }
-    for (uint32_t s = 0; s < nStates; ++s)
-        inOff[s + 1] += inOff[s];
-    {
-        std::vector<uint32_t> fill(inOff.begin(), inOff.end() - 1);
-        for (uint32_t i = 0; i < nSeg; ++i)
-            for (uint32_t s = stateOffsets[i]; s < stateOffsets[i + 1]; ++s)  // ascending source, then arc index
+    const bool forceGeneric = [] {
+        const char* f = getenv("GMM_ALIGN_KERNEL");
+        return f && !strcmp(f, "generic");
+    }();
+    HostPool&             pool = h->hostPool();
+    std::vector<uint32_t> segDegree(nSeg, 0);
+    std::atomic<int>      bad(0);
+    inOff[0] = 0;
+    pool.run(nSeg, std::max(1u, nSeg / (4 * (uint32_t)pool.size())), [&](uint32_t i0, uint32_t i1, int worker) {
+        std::vector<uint32_t>& fill = h->workerWords[worker];  // next free place of every state's list
+        if (fill.size() < (size_t)maxStates + 1)
+            fill.resize((size_t)maxStates + 1);
+        for (uint32_t i = i0; i < i1; ++i) {
+            const uint32_t st0 = stateOffsets[i], S = stateOffsets[i + 1] - st0, arcBase = arcOffsets[st0];
+            uint32_t       degree = 0;
+            std::fill(fill.begin(), fill.begin() + S + 1, 0u);
+            for (uint32_t s = st0; s < st0 + S; ++s) {
+                if (arcOffsets[s + 1] < arcOffsets[s]) {
+                    bad = 1;
+                    return;
+                }
+                degree = std::max(degree, arcOffsets[s + 1] - arcOffsets[s]);
                 for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a) {
-                    const uint32_t k = fill[stateOffsets[i] + arcTarget[a]]++;
-                    inSrc[k]         = s - stateOffsets[i];
-                    inSK[k]          = (inSrc[k] << 16) | ((a - arcOffsets[s]) & 0xFFFFu);
+                    if (arcTarget[a] >= S) {
+                        bad = 2;
+                        return;
+                    }
+                    fill[arcTarget[a] + 1]++;
+                }
+            }
+            uint32_t run = arcBase;  // counts -> first place of every state's list
+            for (uint32_t s = 0; s < S; ++s) {
+                const uint32_t c   = fill[s + 1];
+                fill[s]            = run;
+                run += c;
+                inOff[st0 + s + 1] = run;
+            }
+            for (uint32_t s = st0; s < st0 + S; ++s)  // ascending source, then arc index
+                for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a) {
+                    const uint32_t k = fill[arcTarget[a]]++;
+                    inSK[k]          = ((s - st0) << 16) | ((a - arcOffsets[s]) & 0xFFFFu);
                     inEm[k]          = arcEmission[a];
                     inEmSlot[k]      = arcSlot[a];
                     inW[k]           = arcWeight[a];
-                    outToIn[a]       = k;
+                    if (forceGeneric) {
+                        inSrc[k]   = s - st0;
+                        outToIn[a] = k;
+                    }
                 }
+            segDegree[i] = degree;
+        }
+    });
+    if (bad) {
+        h->setError(bad == 1 ? "gmm_align: arc offsets not ascending" : "gmm_align: arc target outside its segment's automaton");
+        return GMM_ERR_ARG;
+    }
+    uint32_t maxDegree = 0;
+    size_t   maxWords[3] = {0, 0, 0};  // shared memory of the ranked kernel with 8 / 4 / 2 frames in flight
+    for (uint32_t i = 0; i < nSeg; ++i) {
+        uint32_t shift = 0;
+        while ((1u << shift) < segDegree[i])
+            ++shift;
+        segs[i].keyShift = shift;
+        maxDegree        = std::max(maxDegree, segDegree[i]);
+        const uint64_t keyBits = (uint64_t)segs[i].states << shift;
+        const uint32_t segArcs = arcOffsets[stateOffsets[i + 1]] - arcOffsets[stateOffsets[i]];
+        for (int k = 0; k < 3; ++k)
+            maxWords[k] = std::max(maxWords[k], keyBits >= ((uint64_t)1 << 31)
+                                                        ? (size_t)1 << 40
+                                                        : ranked_smem_words(segs[i].states, segArcs, emOff[i + 1] - emOff[i],
+                                                                            (uint32_t)((keyBits + 31) >> 5), 8 >> k));
     }
     // kernel choice: the ranked kernel when every automaton's tables fit in shared memory
-    const char* force   = getenv("GMM_ALIGN_KERNEL");
-    int         inFlight = 0;  // 0: generic kernel
-    if (!(force && !strcmp(force, "generic")) && maxStates < 65536 && maxDegree < 65536) {
+    int inFlight = 0;  // 0: generic kernel
+    if (!forceGeneric && maxStates < 65536 && maxDegree < 65536) {
         if (maxWords[0] * 4 <= 110 * 1024)
             inFlight = 8;
         else if (maxWords[1] * 4 <= 200 * 1024)
@@ -599,49 +741,37 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
         h->setError("gmm_align: automaton with more than 25600 states");
         return GMM_ERR_UNSUPPORTED;
     }
+    if (!inFlight && !forceGeneric)  // the generic kernel's own tables (rare: automata beyond the ranked kernel)
+        for (uint32_t k = 0; k < nArcs; ++k)
+            inSrc[k] = inSK[k] >> 16;
+    if (!inFlight && !forceGeneric) {
+        std::vector<uint32_t> fill(inOff, inOff + nStates);
+        for (uint32_t i = 0; i < nSeg; ++i)
+            for (uint32_t s = stateOffsets[i]; s < stateOffsets[i + 1]; ++s)
+                for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a)
+                    outToIn[a] = fill[stateOffsets[i] + arcTarget[a]]++;
+    }
+    memcpy(hp + oFin, finalWeight, (size_t)nStates * 4);
+    memcpy(hp + oEmOff, emOff.data(), (size_t)(nSeg + 1) * 4);
+    if (!emList.empty())
+        memcpy(hp + oEmList, emList.data(), emList.size() * 4);
+    if (!inFlight) {
+        memcpy(hp + oOut, arcOffsets, (size_t)(nStates + 1) * 4);
+        if (nArcs)
+            memcpy(hp + oTgt, arcTarget, (size_t)nArcs * 4);
+    }
     const int grid = (int)std::min<uint32_t>(nSeg, (uint32_t)h->smCount * 8);
-    // device buffers: one allocation, carved
-    auto   al   = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    size_t off  = 0;
-    auto   take = [&](size_t bytes) {
-        size_t o = off;
-        off += al(bytes);
-        return o;
-    };
-    const size_t oSeg = take(nSeg * sizeof(AlignSeg)), oOff = take((nStates + 1) * 4), oSrc = take((size_t)nArcs * 4),
-                 oSK = take((size_t)nArcs * 4), oEm = take((size_t)nArcs * 4), oW = take((size_t)nArcs * 4),
-                 oFin = take((size_t)nStates * 4), oPe = take((size_t)nFrames * 4), oPs = take((size_t)nFrames * 4),
-                 oSc = take((size_t)nSeg * 4), oOut = take((nStates + 1) * 4), oTgt = take((size_t)nArcs * 4),
-                 oO2i = take((size_t)nArcs * 4), oCnt = take(4), oBack = take(backTotal * 4),
-                 oSlot = take((size_t)nArcs * 4), oEmOff = take((nSeg + 1) * 4), oEmList = take(emList.size() * 4),
-                 oMap = take(inFlight ? mapTotal * 4 : 0), oLists = take(inFlight ? 0 : (size_t)grid * 6 * maxStates * 4);
+    // device block: the tables, then outputs, back-pointers and per-kernel work space
+    const size_t oPe = take((size_t)nFrames * 4), oPs = take((size_t)nFrames * 4), oSc = take((size_t)nSeg * 4),
+                 oBack = take(backTotal * 4), oMap = take(inFlight ? mapTotal * 4 : 0),
+                 oLists = take(inFlight ? 0 : (size_t)grid * 6 * maxStates * 4);
     void* base = nullptr;
-    int   rc   = h->reserve(SCR_MISC, off, &base);
-    if (rc)
+    if ((rc = h->reserve(SCR_MISC, off, &base)))
         return rc;
-    char* d  = (char*)base;
-    auto  up = [&](size_t o, const void* src, size_t bytes) {
-        return bytes ? cudaMemcpyAsync(d + o, src, bytes, cudaMemcpyHostToDevice, h->stream) : cudaSuccess;
-    };
-    GMM_CUDA_TRY(h, up(oSeg, segs.data(), nSeg * sizeof(AlignSeg)));
-    GMM_CUDA_TRY(h, up(oOff, inOff.data(), (nStates + 1) * 4));
-    GMM_CUDA_TRY(h, up(oSrc, inSrc.data(), (size_t)nArcs * 4));
-    GMM_CUDA_TRY(h, up(oSK, inSK.data(), (size_t)nArcs * 4));
-    GMM_CUDA_TRY(h, up(oEm, inEm.data(), (size_t)nArcs * 4));
-    GMM_CUDA_TRY(h, up(oW, inW.data(), (size_t)nArcs * 4));
-    GMM_CUDA_TRY(h, up(oFin, finalWeight, (size_t)nStates * 4));
-    if (inFlight || compact)
-        GMM_CUDA_TRY(h, up(oSlot, inEmSlot.data(), (size_t)nArcs * 4));
-    if (inFlight) {
-        GMM_CUDA_TRY(h, up(oEmOff, emOff.data(), (nSeg + 1) * 4));
-        GMM_CUDA_TRY(h, up(oEmList, emList.data(), emList.size() * 4));
-    }
-    else {
-        GMM_CUDA_TRY(h, up(oOut, arcOffsets, (nStates + 1) * 4));
-        GMM_CUDA_TRY(h, up(oTgt, arcTarget, (size_t)nArcs * 4));
-        GMM_CUDA_TRY(h, up(oO2i, outToIn.data(), (size_t)nArcs * 4));
-    }
-    GMM_CUDA_TRY(h, cudaMemsetAsync(d + oCnt, 0, 4, h->stream));
+    char* d = (char*)base;
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(d, hp, inFlight ? rankedBytes : tableBytes, cudaMemcpyHostToDevice, h->stream));
+    if ((rc = h->pinnedCopied(PIN_ALIGN)))
+        return rc;
     AlignParams p;
     p.seg          = (const AlignSeg*)(d + oSeg);
     p.nSeg         = nSeg;
@@ -684,14 +814,33 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     GMM_CUDA_TRY(h, cudaGetLastError());
     if (d_pathEmission)
         *d_pathEmission = p.pathEmission;  // stays valid until the next alignment call on this handle
-    if (pathEmission)
-        GMM_CUDA_TRY(h, cudaMemcpyAsync(pathEmission, d + oPe, (size_t)nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
-    if (pathState)
-        GMM_CUDA_TRY(h, cudaMemcpyAsync(pathState, d + oPs, (size_t)nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
-    if (pathScore)
-        GMM_CUDA_TRY(h, cudaMemcpyAsync(pathScore, d + oSc, (size_t)nSeg * 4, cudaMemcpyDeviceToHost, h->stream));
+    AlignDeferred now;
+    AlignDeferred& fin = defer ? *defer : now;
+    fin.pending        = true;
+    fin.dPathEmission  = (const uint8_t*)(d + oPe);
+    fin.dPathState     = (const uint8_t*)(d + oPs);
+    fin.dPathScore     = (const uint8_t*)(d + oSc);
+    fin.dOrdered       = (const uint8_t*)(d + oCnt);
+    fin.nFrames        = nFrames;
+    fin.nSeg           = nSeg;
+    fin.pathEmission   = pathEmission;
+    fin.pathState      = pathState;
+    fin.pathScore      = pathScore;
+    return defer ? GMM_OK : gmm_align_finish(h, fin);
+}
+
+int gmm_align_finish(gmm_handle* h, AlignDeferred& f) {
+    if (!f.pending)
+        return GMM_OK;
+    f.pending = false;
+    if (f.pathEmission)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(f.pathEmission, f.dPathEmission, (size_t)f.nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (f.pathState)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(f.pathState, f.dPathState, (size_t)f.nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (f.pathScore)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(f.pathScore, f.dPathScore, (size_t)f.nSeg * 4, cudaMemcpyDeviceToHost, h->stream));
     uint32_t ordered = 0;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(&ordered, d + oCnt, 4, cudaMemcpyDeviceToHost, h->stream));
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(&ordered, f.dOrdered, 4, cudaMemcpyDeviceToHost, h->stream));
     GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     h->alignOrdered += ordered;
     return GMM_OK;

@@ -1,9 +1,12 @@
 // C-ABI of libgmm_b200.so (include/gmm_b200.h): handle lifetime, model upload / packing, and the host- and
 // device-pointer scoring entry points.  No CPU fallback anywhere: every scoring call ends in a CUDA kernel.
 #include <math.h>
+#include <sched.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 
 #include "gmm_internal.cuh"
 
@@ -39,6 +42,67 @@ int gmm_handle::reserve(int slot, size_t bytes, void** out) {
         scratchBytes[slot] = want;
     }
     *out = scratch[slot];
+    return GMM_OK;
+}
+
+HostPool& gmm_handle::hostPool() {
+    if (!pool) {
+        int         n   = 4;
+        const char* env = getenv("GMM_HOST_THREADS");
+        cpu_set_t   set;
+        if (env)
+            n = std::max(1, atoi(env));
+        else if (sched_getaffinity(0, sizeof(set), &set) == 0)
+            n = std::max(1, std::min(4, CPU_COUNT(&set) / 2));
+        pool = new HostPool(n - 1);
+        workerWords.resize(n);
+        workerStamps.resize(n);
+    }
+    return *pool;
+}
+
+int gmm_handle::pinnedCopied(int slot) {
+    if (!pinEvent[slot])
+        GMM_CUDA_TRY(this, cudaEventCreateWithFlags(&pinEvent[slot], cudaEventDisableTiming));
+    GMM_CUDA_TRY(this, cudaEventRecord(pinEvent[slot], stream));
+    return GMM_OK;
+}
+
+int gmm_handle::reservePinned(int slot, size_t bytes, void** out) {
+    if (pinEvent[slot])
+        GMM_CUDA_TRY(this, cudaEventSynchronize(pinEvent[slot]));  // the previous copy out of this block is done
+    if (bytes > pinnedBytes[slot]) {
+        GMM_CUDA_TRY(this, cudaStreamSynchronize(stream));
+        if (pinned[slot])
+            GMM_CUDA_TRY(this, cudaFreeHost(pinned[slot]));
+        pinned[slot]      = nullptr;
+        pinnedBytes[slot] = 0;
+        const size_t want = bytes + bytes / 4 + 4096;
+        GMM_CUDA_TRY(this, cudaHostAlloc(&pinned[slot], want, cudaHostAllocDefault));
+        pinnedBytes[slot] = want;
+    }
+    *out = pinned[slot];
+    return GMM_OK;
+}
+
+int gmm_handle::useLane(int which) {
+    if (which == lane)
+        return GMM_OK;
+    if (!laneStream) {
+        GMM_CUDA_TRY(this, cudaStreamCreateWithFlags(&laneStream, cudaStreamNonBlocking));
+        GMM_CUDA_TRY(this, cudaEventCreateWithFlags(&laneEvent, cudaEventDisableTiming));
+    }
+    std::swap(stream, laneStream);
+    for (int i = 0; i < SCR_COUNT; ++i) {
+        std::swap(scratch[i], laneScratch[i]);
+        std::swap(scratchBytes[i], laneScratchBytes[i]);
+    }
+    for (int i = 0; i < 2; ++i) {
+        std::swap(pinned[i], lanePinned[i]);
+        std::swap(pinnedBytes[i], lanePinnedBytes[i]);
+        std::swap(pinEvent[i], lanePinEvent[i]);
+    }
+    lane = which;
     return GMM_OK;
 }
 
@@ -148,9 +212,28 @@ void gmm_destroy(gmm_handle* h) {
         cudaEventDestroy(h->timed[i].first);
         cudaEventDestroy(h->timed[i].second);
     }
-    for (int i = 0; i < SCR_COUNT; ++i)
+    h->useLane(0);
+    for (int i = 0; i < SCR_COUNT; ++i) {
         if (h->scratch[i])
             cudaFree(h->scratch[i]);
+        if (h->laneScratch[i])
+            cudaFree(h->laneScratch[i]);
+    }
+    for (int i = 0; i < 2; ++i) {
+        if (h->pinned[i])
+            cudaFreeHost(h->pinned[i]);
+        if (h->lanePinned[i])
+            cudaFreeHost(h->lanePinned[i]);
+        if (h->pinEvent[i])
+            cudaEventDestroy(h->pinEvent[i]);
+        if (h->lanePinEvent[i])
+            cudaEventDestroy(h->lanePinEvent[i]);
+    }
+    delete h->pool;
+    if (h->laneStream)
+        cudaStreamDestroy(h->laneStream);
+    if (h->laneEvent)
+        cudaEventDestroy(h->laneEvent);
     if (h->lda.matrix)
         cudaFree(h->lda.matrix);
     if (h->ownStream && h->stream)
@@ -440,6 +523,87 @@ uint64_t gmm_align_ordered_count(const gmm_handle* h) {
 
 }  // extern "C"
 
+// One group of whole segments: upload, score (compact block when that saves tensor work), align, accumulate --
+// everything enqueued on the active lane, nothing waited for; `fin` completes it (gmm_align_finish).
+static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t s1, const uint32_t* frameOffsets,
+                           const float* x, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                           const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
+                           const uint32_t* initialState, const float* finalWeight, uint32_t* pathEmission,
+                           uint32_t* pathState, float* pathScore, AlignDeferred* fin) {
+    const size_t   devLd = h->M;
+    const uint32_t f0 = frameOffsets[s0], T = frameOffsets[s1] - f0, n = s1 - s0;
+    static const bool trace = getenv("GMM_TRACE") != nullptr;
+    auto              clk   = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double            tr[6] = {clk(), 0, 0, 0, 0, 0};
+    std::vector<uint32_t> fo(n + 1), so(n + 1);
+    for (uint32_t i = 0; i <= n; ++i) {
+        fo[i] = frameOffsets[s0 + i] - f0;
+        so[i] = stateOffsets[s0 + i] - stateOffsets[s0];
+    }
+    std::vector<uint32_t> ao(so[n] + 1);
+    const uint32_t        st0 = stateOffsets[s0], a0 = arcOffsets[st0];
+    for (uint32_t s = 0; s <= so[n]; ++s)
+        ao[s] = arcOffsets[st0 + s] - a0;
+    void *dx = nullptr, *ds = nullptr;
+    const uint32_t* dPath = nullptr;
+    int   rc;
+    const uint32_t inDim = h->lda.valid ? h->lda.baseDim : h->D;
+    if ((rc = uploadFrames(h, h->D, n, fo.data(), x + (size_t)f0 * inDim, &dx)))
+        return rc;
+    tr[1] = clk();
+    // Lazy evaluation as the reference's cached context scorers do it (FeatureScorer.hh:170-230): only the
+    // emissions a segment's automaton can ask for are scored, into a compact block whose column j is entry j of
+    // the segment's emission list; the bits are those of the full pass.  Taken when it saves tensor work.
+    AlignLists             lists;
+    std::vector<uint32_t>& emOff = lists.emOff;
+    std::vector<uint32_t>& emList = lists.emList;
+    bool                  compact = false, haveLists = false;
+    size_t                ldUse   = devLd;
+    const char*           env     = getenv("GMM_ALIGN_SUBSET");
+    if (T && gmm_tc_subset_capable(h) && !(env && env[0] == '0') && arcEmission &&
+        gmm_align_emission_lists(h, n, so.data(), ao.data(), arcEmission + a0, h->M, lists)) {
+        haveLists = true;
+        const uint32_t mpt = h->tensor.mixPerTile;
+        uint32_t       maxList = 0;
+        double         subsetWork = 0, fullWork = (double)((T + 127) / 128) * ((h->M + mpt - 1) / mpt);
+        for (uint32_t i = 0; i < n; ++i) {
+            const uint32_t len = emOff[i + 1] - emOff[i];
+            maxList            = std::max(maxList, len);
+            subsetWork += (double)((fo[i + 1] - fo[i] + 127) / 128) * ((len + mpt - 1) / mpt);
+        }
+        compact = (env && env[0] == '1') || subsetWork < 0.6 * fullWork;
+        if (compact)
+            ldUse = gmm_tc_subset_ld(h, std::max(1u, maxList));
+    }
+    if ((rc = h->reserve(SCR_SCORE, (size_t)std::max(1u, T) * ldUse * 4, &ds)))
+        return rc;
+    tr[2] = clk();
+    if (T) {
+        if (compact)
+            rc = gmm_tc_score_subset(h, n, fo.data(), emOff.data(), emList.data(), (const float*)dx, (float*)ds, ldUse);
+        else
+            rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, nullptr, devLd);
+        if (rc)
+            return rc;
+    }
+    tr[3] = clk();
+    if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, ldUse, so.data(), ao.data(),
+                               arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
+                               arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0,
+                               pathEmission ? pathEmission + f0 : nullptr, pathState ? pathState + f0 : nullptr,
+                               pathScore ? pathScore + s0 : nullptr, &dPath, compact, h->M, fin,
+                               haveLists ? &lists : nullptr)))
+        return rc;
+    // the aligned frames go straight into the estimators: the path is the per-frame mixture (kNoArc: skip)
+    tr[4] = clk();
+    if (accumulate && T && (rc = gmm_accum_launch(h, T, (const float*)dx, dPath, nullptr, nullptr)))
+        return rc;
+    if (trace)
+        fprintf(stderr, "[gmm] group of %u segments, host ms: offsets+upload %.3f, lists %.3f, score enqueue %.3f, align enqueue %.3f, accumulate %.3f\n",
+                n, tr[1] - tr[0], tr[2] - tr[1], tr[3] - tr[2], tr[4] - tr[3], clk() - tr[4]);
+    return GMM_OK;
+}
+
 static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
                          const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
@@ -462,71 +626,56 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
         return GMM_ERR_ARG;
     }
     cudaSetDevice(h->device);
-    // groups of whole segments whose score block stays bounded (it never leaves the device)
-    const size_t devLd = h->M, maxFrames = std::max<size_t>(1, ((size_t)10 << 30) / (devLd * 4));
-    uint32_t     s0 = 0;
-    while (s0 < nSeg) {
+    // Groups of whole segments, alternating between the two lanes of the handle: while group g is scored and aligned
+    // on one stream, group g+1's tables are built on the host and its features cross PCIe on the other.  A group is
+    // large enough to fill the alignment kernel (one CTA per segment, two per SM), and bounded so that its score
+    // block (which never leaves the device) stays within 10 GB.
+    const size_t   maxFrames = std::max<size_t>(1, ((size_t)10 << 30) / ((size_t)h->M * 4));
+    const char*    envG      = getenv("GMM_ALIGN_GROUP");
+    const uint32_t groupSegs = envG ? (uint32_t)std::max(1, atoi(envG)) : (uint32_t)h->smCount * 2;
+    const bool     twoLanes  = nSeg > groupSegs;
+    AlignDeferred  fin[2];
+    int            rc = GMM_OK, lane = 0;
+    if (twoLanes) {  // the second lane starts after whatever the handle's stream holds so far (model upload, ...)
+        if ((rc = h->useLane(1)) || (rc = h->useLane(0)))
+            return rc;
+        GMM_CUDA_TRY(h, cudaEventRecord(h->laneEvent, h->stream));
+        GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->laneStream, h->laneEvent, 0));
+    }
+    uint32_t s0 = 0;
+    while (s0 < nSeg && rc == GMM_OK) {
         uint32_t s1 = s0 + 1;
-        while (s1 < nSeg && (size_t)(frameOffsets[s1 + 1] - frameOffsets[s0]) <= maxFrames)
+        while (s1 < nSeg && s1 - s0 < groupSegs && (size_t)(frameOffsets[s1 + 1] - frameOffsets[s0]) <= maxFrames)
             ++s1;
-        const uint32_t f0 = frameOffsets[s0], T = frameOffsets[s1] - f0, n = s1 - s0;
-        std::vector<uint32_t> fo(n + 1), so(n + 1);
-        for (uint32_t i = 0; i <= n; ++i) {
-            fo[i] = frameOffsets[s0 + i] - f0;
-            so[i] = stateOffsets[s0 + i] - stateOffsets[s0];
-        }
-        std::vector<uint32_t> ao(so[n] + 1);
-        const uint32_t        st0 = stateOffsets[s0], a0 = arcOffsets[st0];
-        for (uint32_t s = 0; s <= so[n]; ++s)
-            ao[s] = arcOffsets[st0 + s] - a0;
-        void *dx = nullptr, *ds = nullptr;
-        const uint32_t* dPath = nullptr;
-        int   rc;
-        const uint32_t inDim = h->lda.valid ? h->lda.baseDim : h->D;
-        if ((rc = uploadFrames(h, h->D, n, fo.data(), x + (size_t)f0 * inDim, &dx)))
-            return rc;
-        // Lazy evaluation as the reference's cached context scorers do it (FeatureScorer.hh:170-230): only the
-        // emissions a segment's automaton can ask for are scored, into a compact block whose column j is entry j of
-        // the segment's emission list; the bits are those of the full pass.  Taken when it saves tensor work.
-        std::vector<uint32_t> emOff, emList;
-        bool                  compact = false;
-        size_t                ldUse   = devLd;
-        const char*           env     = getenv("GMM_ALIGN_SUBSET");
-        if (T && gmm_tc_subset_capable(h) && !(env && env[0] == '0') && arcEmission &&
-            gmm_align_emission_lists(n, so.data(), ao.data(), arcEmission + a0, h->M, emOff, emList)) {
-            uint32_t maxList = 0;
-            double   subsetWork = 0, fullWork = (double)((T + 127) / 128) * ((h->M + h->tensor.mixPerTile - 1) / h->tensor.mixPerTile);
-            for (uint32_t i = 0; i < n; ++i) {
-                const uint32_t len = emOff[i + 1] - emOff[i];
-                maxList            = std::max(maxList, len);
-                subsetWork += (double)((fo[i + 1] - fo[i] + 127) / 128) * ((len + h->tensor.mixPerTile - 1) / h->tensor.mixPerTile);
-            }
-            compact = (env && env[0] == '1') || subsetWork < 0.6 * fullWork;
-            if (compact)
-                ldUse = gmm_tc_subset_ld(h, std::max(1u, maxList));
-        }
-        if ((rc = h->reserve(SCR_SCORE, (size_t)std::max(1u, T) * ldUse * 4, &ds)))
-            return rc;
-        if (T) {
-            if (compact)
-                rc = gmm_tc_score_subset(h, n, fo.data(), emOff.data(), emList.data(), (const float*)dx, (float*)ds, ldUse);
-            else
-                rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, nullptr, devLd);
-            if (rc)
-                return rc;
-        }
-        if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, ldUse, so.data(), ao.data(),
-                                   arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
-                                   arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0,
-                                   pathEmission ? pathEmission + f0 : nullptr, pathState ? pathState + f0 : nullptr,
-                                   pathScore ? pathScore + s0 : nullptr, &dPath, compact, h->M)))
-            return rc;
-        // the aligned frames go straight into the estimators: the path is the per-frame mixture (kNoArc: skip)
-        if (accumulate && T && (rc = gmm_accum_launch(h, T, (const float*)dx, dPath, nullptr, nullptr)))
-            return rc;
+        if (twoLanes)
+            rc = h->useLane(lane);
+        const auto tw0 = std::chrono::steady_clock::now();
+        if (rc == GMM_OK)
+            rc = gmm_align_finish(h, fin[lane]);  // the lane's previous group: its scratch is about to be reused
+        if (getenv("GMM_TRACE"))
+            fprintf(stderr, "[gmm] lane %d: waited %.3f ms for its previous group\n", lane,
+                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tw0).count());
+        if (rc == GMM_OK)
+            rc = scoreAlignGroup(h, accumulate, s0, s1, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission,
+                                 arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore, &fin[lane]);
+        if (twoLanes)
+            lane ^= 1;
         s0 = s1;
     }
-    return GMM_OK;
+    for (int k = 0; k < 2; ++k) {  // oldest group first; on an error still drain both lanes
+        const int l = twoLanes ? (lane + k) & 1 : k;
+        if (twoLanes)
+            h->useLane(l);
+        if (l == 0 || twoLanes) {
+            const int r = gmm_align_finish(h, fin[l]);
+            if (twoLanes)
+                cudaStreamSynchronize(h->stream);
+            if (rc == GMM_OK)
+                rc = r;
+        }
+    }
+    h->useLane(0);
+    return rc;
 }
 
 extern "C" {

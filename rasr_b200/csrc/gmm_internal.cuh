@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../include/gmm_b200.h"
+#include "gmm_host_pool.h"
 
 #define GMM_CUDA_TRY(h, expr)                                                                          \
     do {                                                                                               \
@@ -136,6 +137,31 @@ struct gmm_handle {
     // scratch (grown on demand)
     void*  scratch[12]      = {};
     size_t scratchBytes[12] = {};
+    // Second lane of the pipelined host entry points (gmm_score_align_*_host): its own stream and scratch, so that
+    // one group of segments is uploaded and prepared while the previous one is scored and aligned.  useLane() makes a
+    // lane the one `stream` / `scratch` refer to; every kernel launcher keeps using those two names.
+    cudaStream_t laneStream          = nullptr;
+    void*        laneScratch[12]     = {};
+    size_t       laneScratchBytes[12] = {};
+    cudaEvent_t  laneEvent           = nullptr;
+    int          lane                = 0;
+    void*        pinned[2]           = {};  // host staging blocks (tables built in place, one copy per launch) ...
+    size_t       pinnedBytes[2]      = {};
+    void*        lanePinned[2]       = {};  // ... and the second lane's
+    size_t       lanePinnedBytes[2]  = {};
+    cudaEvent_t  pinEvent[2]         = {};  // recorded behind the copy out of a staging block: reservePinned waits
+    cudaEvent_t  lanePinEvent[2]     = {};  // for it before the block is written again
+    HostPool*    pool                = nullptr;  // host threads of the table builders (hostPool())
+    std::vector<std::vector<uint32_t>> workerWords;  // ... and one work space per thread
+    struct EmissionStamps {                           // per thread: slot of an emission in the segment being listed,
+        uint32_t              counter = 0;            // valid while stamp[e] == counter
+        std::vector<uint32_t> slotOf, stamp;
+    };
+    std::vector<EmissionStamps> workerStamps;
+    HostPool&    hostPool();
+    int  pinnedCopied(int slot);
+    int  useLane(int which);
+    int  reservePinned(int slot, size_t bytes, void** out);
     std::vector<void*> owned;       // device allocations of the float model
     std::vector<void*> ownedQuant;  // device allocations of the quantized model
 
@@ -145,8 +171,13 @@ struct gmm_handle {
     int  upload(void** p, const void* src, size_t bytes, bool quant = false);
 };
 
+enum { PIN_ALIGN = 0, PIN_SUBSET = 1 };
 enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7, SCR_BASE = 8, SCR_TILES = 9, SCR_VTILES = 10, SCR_TAB = 11, SCR_COUNT = 12 };
 
+// gmm_align_emission_lists' results, handed to gmm_align_launch by a caller that already needed them
+struct AlignLists {
+    std::vector<uint32_t> emOff, emList, arcSlot, scratch;
+};
 // gmm_direct.cu
 int gmm_direct_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
 int gmm_direct_posteriors(gmm_handle* h, uint32_t T, const float* d_x, float* d_post);
@@ -158,12 +189,22 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
-                     const uint32_t** d_pathEmission = nullptr, bool compact = false, uint32_t nEmissions = 0);
+                     const uint32_t** d_pathEmission = nullptr, bool compact = false, uint32_t nEmissions = 0,
+                     struct AlignDeferred* defer = nullptr, const struct AlignLists* lists = nullptr);
+// With `defer` gmm_align_launch returns once everything is enqueued; gmm_align_finish (same lane active) copies the
+// outputs to the host arrays and waits.
+struct AlignDeferred {
+    bool           pending = false;
+    const uint8_t *dPathEmission = nullptr, *dPathState = nullptr, *dPathScore = nullptr, *dOrdered = nullptr;
+    uint32_t       nFrames = 0, nSeg = 0;
+    uint32_t *     pathEmission = nullptr, *pathState = nullptr;
+    float*         pathScore = nullptr;
+};
+int gmm_align_finish(gmm_handle* h, AlignDeferred& d);
 // the distinct emissions of every segment's automaton in order of first use (the column order of a compact score
 // block: gmm_tc_score_subset writes it, gmm_align_launch(compact) reads it)
-bool gmm_align_emission_lists(uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
-                              const uint32_t* arcEmission, uint32_t nEmissions, std::vector<uint32_t>& emOff,
-                              std::vector<uint32_t>& emList, uint32_t* arcSlot = nullptr);
+bool gmm_align_emission_lists(gmm_handle* h, uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                              const uint32_t* arcEmission, uint32_t nEmissions, struct AlignLists& lists);
 int gmm_lda_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_base, float* d_x);
 int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
                      uint32_t* d_best);

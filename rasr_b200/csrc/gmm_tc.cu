@@ -517,7 +517,8 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ 
         float vmax = 0.f, ssq = 0.f;
         // row t of the tile space holds frame `src` (subset scoring: tiles are aligned to segments, rowMap names the
         // frame of every row, 0xFFFFFFFF for padding)
-        const uint32_t src = rowMap ? rowMap[t] : (t < T ? t : 0xFFFFFFFFu);
+        const uint32_t src = rowMap ? ((t % kTileM) < rowMap[2 * (t / kTileM) + 1] ? rowMap[2 * (t / kTileM)] + (t % kTileM) : 0xFFFFFFFFu)
+                                    : (t < T ? t : 0xFFFFFFFFu);
         const float*   xr  = x + (size_t)(src == 0xFFFFFFFFu ? 0 : src) * D;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -869,7 +870,7 @@ namespace {
 struct TcJob {
     uint32_t        T, FT;
     const float*    d_x;
-    const uint32_t* rowMap;   // device, [FT * 128] or null
+    const uint32_t* rowMap;   // device, per frame tile {first frame, frames}, or null
     const uint8_t*  bTiles;
     uint32_t        nTiles;
     const uint32_t* itemTab;  // device, 8 words per item, or null
@@ -1088,9 +1089,9 @@ int gmm_tc_score_subset(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffse
     if (!gmm_tc_subset_capable(h))
         return GMM_ERR_UNSUPPORTED;
     const uint32_t mpt = tm.mixPerTile, parts = kTileN / tm.partW, mixPerPart = tm.partW / tm.mixCols;
-    // tile-aligned row space, virtual tiles and items, segment by segment
-    std::vector<uint32_t> rowMap, vtMix, vtBase, items;
-    uint32_t              FT = 0;
+    // tile-aligned row space, virtual tiles and items, segment by segment; the tables are built in one pinned block
+    // laid out like its device copy (one asynchronous copy per call)
+    uint32_t FT = 0, nVt = 0;
     for (uint32_t s = 0; s < nSeg; ++s) {
         const uint32_t f0 = frameOffsets[s], f1 = frameOffsets[s + 1], n = emOff[s + 1] - emOff[s];
         if (f1 <= f0 || n == 0)
@@ -1099,14 +1100,32 @@ int gmm_tc_score_subset(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffse
             h->setError("subset scoring: score block narrower than the segment's emission list");
             return GMM_ERR_ARG;
         }
-        const uint32_t ft0 = FT, nFt = (f1 - f0 + kTileM - 1) / kTileM;
-        FT += nFt;
-        rowMap.resize((size_t)FT * kTileM, 0xFFFFFFFFu);
-        for (uint32_t t = f0; t < f1; ++t)
-            rowMap[(size_t)ft0 * kTileM + (t - f0)] = t;
-        for (uint32_t v = 0; v * mpt < n; ++v) {
-            const uint32_t vt = (uint32_t)vtBase.size();
-            vtBase.push_back(v * mpt);
+        FT += (f1 - f0 + kTileM - 1) / kTileM;
+        nVt += (n + mpt - 1) / mpt;
+    }
+    if (nVt == 0)
+        return GMM_OK;
+    auto         al   = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t oMap = 0, oMix = al((size_t)FT * 8), oBase = oMix + al((size_t)nVt * mpt * 4),
+                 oItem = oBase + al((size_t)nVt * 4), total = oItem + al((size_t)nVt * 32);
+    void *tab = nullptr, *vtiles = nullptr, *pin = nullptr;
+    int   rc;
+    if ((rc = h->reservePinned(PIN_SUBSET, total, &pin)))
+        return rc;
+    uint32_t *tileMap = (uint32_t*)((char*)pin + oMap), *vtMix = (uint32_t*)((char*)pin + oMix),
+             *vtBase = (uint32_t*)((char*)pin + oBase), *items = (uint32_t*)((char*)pin + oItem);
+    uint32_t ft = 0, vt = 0;
+    for (uint32_t s = 0; s < nSeg; ++s) {
+        const uint32_t f0 = frameOffsets[s], f1 = frameOffsets[s + 1], n = emOff[s + 1] - emOff[s];
+        if (f1 <= f0 || n == 0)
+            continue;
+        const uint32_t ft0 = ft, nFt = (f1 - f0 + kTileM - 1) / kTileM;
+        for (uint32_t k = 0; k < nFt; ++k, ++ft) {  // frame tile ft holds frames [first, first + count)
+            tileMap[2 * ft]     = f0 + k * kTileM;
+            tileMap[2 * ft + 1] = std::min<uint32_t>(kTileM, f1 - f0 - k * kTileM);
+        }
+        for (uint32_t v = 0; v * mpt < n; ++v, ++vt) {
+            vtBase[vt] = v * mpt;
             for (uint32_t j = 0; j < mpt; ++j) {
                 const uint32_t k = v * mpt + j;
                 const uint32_t m = emList[emOff[s] + (k < n ? k : 0)];  // spare places repeat the first mixture
@@ -1114,29 +1133,20 @@ int gmm_tc_score_subset(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffse
                     h->setError("subset scoring: mixture index out of range");
                     return GMM_ERR_ARG;
                 }
-                vtMix.push_back(m);
+                vtMix[(size_t)vt * mpt + j] = m;
             }
-            const uint32_t it[8] = {vt, ft0, ft0 + nFt, f0, f1, 0, 0, 0};
-            items.insert(items.end(), it, it + 8);
+            uint32_t* it = items + (size_t)vt * 8;
+            it[0] = vt, it[1] = ft0, it[2] = ft0 + nFt, it[3] = f0, it[4] = f1, it[5] = it[6] = it[7] = 0;
         }
     }
-    if (items.empty())
-        return GMM_OK;
-    const uint32_t nVt = (uint32_t)vtBase.size();
-    auto           al  = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    const size_t   oMap = 0, oMix = al(rowMap.size() * 4), oBase = oMix + al(vtMix.size() * 4),
-                 oItem = oBase + al(vtBase.size() * 4), total = oItem + al(items.size() * 4);
-    void *tab = nullptr, *vtiles = nullptr;
-    int   rc;
     if ((rc = h->reserve(SCR_TAB, total, &tab)))
         return rc;
     if ((rc = h->reserve(SCR_VTILES, (size_t)nVt * tm.tileBytes, &vtiles)))
         return rc;
     char* d = (char*)tab;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oMap, rowMap.data(), rowMap.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oMix, vtMix.data(), vtMix.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oBase, vtBase.data(), vtBase.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d + oItem, items.data(), items.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(d, pin, total, cudaMemcpyHostToDevice, h->stream));
+    if ((rc = h->pinnedCopied(PIN_SUBSET)))
+        return rc;
     gather_tiles_kernel<<<(int)std::min<uint32_t>(nVt, (uint32_t)h->smCount * 8), 256, 0, h->stream>>>(
             tm.bTiles, tm.tileBytes, tm.nAtoms, tm.swz, tm.mixCols, mpt, mixPerPart, parts, (const uint32_t*)(d + oMix),
             (const uint32_t*)(d + oBase), nVt, (uint8_t*)vtiles);
