@@ -213,8 +213,10 @@ def ncu_traffic(summary_name):
     return None
 
 
-def float_roofline(ms, frames, kernel_sec, peaks, kernel_name, step_sec=None, traffic=None, sustained=False):
-    """kernel_sec: average duration of ONE launch of the scoring kernel (CUDA events around the launch).
+def float_roofline(ms, frames, kernel_sec, peaks, kernel_name, step_sec=None, traffic=None, sustained=False,
+                   launches_per_step=1):
+    """frames, kernel_sec: frames of ONE launch of the scoring kernel and its average duration (CUDA events around the
+    launch; a step of `launches_per_step` launches: long batches go out in L2-sized launches).
     sustained: the kernel ran back to back for >= 100 ms (power-capped clocks) -> the sustained cuBLAS figure is
     the denominator; a kernel timed in a short burst is compared with the burst figure."""
     flops = 2.0 * (2 * ms.D + 1) * ms.G * frames  # algorithmic, SURVEY.md 8(d)
@@ -223,7 +225,8 @@ def float_roofline(ms, frames, kernel_sec, peaks, kernel_name, step_sec=None, tr
     return {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
             "frac": ach / peak, "traffic": traffic, "kernel": kernel_name,
             "kernel_ms_per_launch": kernel_sec * 1e3,
-            "kernel_share_of_step": (kernel_sec / step_sec) if step_sec else None,
+            "launches_per_step": launches_per_step, "frames_per_launch": frames,
+            "kernel_share_of_step": (kernel_sec * launches_per_step / step_sec) if step_sec else None,
             "frac_of_burst_peak": ach / peaks["tensor"],
             "executed_over_algorithmic": 3.0 * (16 * (((ms.D if ms.variances.shape[0] == 1 else 2 * ms.D) + 3 + 15) // 16))
                                          / (2 * ms.D + 1),
@@ -303,7 +306,8 @@ def run_ours(args):
         step()
     kernel_ms, kernel_n = eng.kernel_time()
     eng.kernel_timing(False)
-    kernel_sec = kernel_ms / 1e3 / max(1, args.steps)  # one launch per step on the tensor path
+    kernel_sec = kernel_ms / 1e3 / max(1, kernel_n)  # per launch; a step is kernel_n / steps launches
+    launches_per_step = max(1, kernel_n // max(1, args.steps))
 
     # end to end through the host API: pinned features in, host scores out, every step
     e2e_frames = min(frames, 8 * SEG_FRAMES)
@@ -404,9 +408,9 @@ def run_ours(args):
                                          "every step ends with the all-reduce that combines the ranks' estimators"},
             "clocks": clocks}
     if rank == 0:
-        line["roofline"] = float_roofline(ms, frames, kernel_sec, peaks, kname, sec_per_step,
+        line["roofline"] = float_roofline(ms, frames / launches_per_step, kernel_sec, peaks, kname, sec_per_step,
                                           ncu_traffic("prof_tc_cfg1_bench_r01.txt") if frames == 512000 else None,
-                                          sustained=sec >= 0.1)
+                                          sustained=sec >= 0.1, launches_per_step=launches_per_step)
         if world == 1 and not args.no_cpu:
             os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core again
             cores = len(os.sched_getaffinity(0))

@@ -180,9 +180,14 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
     uint8_t*       sB        = smem;
     uint8_t*       sA        = sB + (size_t)p.buffersB * bBytes;
     uint32_t*      sStage    = reinterpret_cast<uint32_t*>(sA + (size_t)p.stagesA * p.aTileBytes);
-    const uint32_t stageWarp = 32 * p.stagePitch;  // words per warp and plane
+    // staging: one [32 rows x stagePitch] block per store group and plane.  8 warps: a group is one warp.  16 warps:
+    // the four warps of a TMEM lane quarter stage the 64-column parts of their 32 rows side by side (two blocks,
+    // alternating by tile, so one named barrier per tile is enough) and store the rows together: pieces of a whole
+    // tile's mixtures (64 bytes per row at 16 densities per mixture), not of a part's (16 bytes)
+    constexpr int  kGroups = NE == 16 ? 4 : 8, kBufs = NE == 16 ? 2 : 1, GW = NE == 16 ? 128 : 32;
+    const uint32_t stageWarp = 32 * p.stagePitch;  // words per block
     uint64_t*      bars      = reinterpret_cast<uint64_t*>(
-            (reinterpret_cast<uintptr_t>(sStage + 2 * NE * stageWarp) + 15) & ~(uintptr_t)15);
+            (reinterpret_cast<uintptr_t>(sStage + 2 * kGroups * kBufs * stageWarp) + 15) & ~(uintptr_t)15);
     uint64_t* ready    = bars;              // [kRing] tile t may be issued (A landed, accumulator drained)
     uint64_t* done     = bars + kRing;      // [kRing] the MMAs of tile t have retired
     uint64_t* fullB    = bars + 2 * kRing;  // [2]
@@ -285,9 +290,10 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
     else {
         // ===== epilogue: TMEM -> registers -> packed-key min per mixture -> staged -> global =====
         const int      e = warp - kEpiWarp0, qd = warp & 3, part = e >> 2;
-        const uint32_t stWarp = smem_u32(sStage) + (uint32_t)e * stageWarp * 4;
-        const uint32_t stRow  = stWarp + (uint32_t)lane * p.stagePitch * 4;
-        const uint32_t offB   = NE * stageWarp * 4;
+        const uint32_t gi     = NE == 16 ? (uint32_t)qd : (uint32_t)e;       // store group
+        const uint32_t gl     = NE == 16 ? (uint32_t)(part * 32 + lane) : (uint32_t)lane;  // thread within the group
+        const uint32_t stGrp  = smem_u32(sStage) + gi * kBufs * stageWarp * 4;
+        const uint32_t offB   = kGroups * kBufs * stageWarp * 4;
         // the three outputs share one indexing: address everything relative to a base array that is present
         char* const     gBase = reinterpret_cast<char*>(p.q ? (void*)p.q : p.best ? (void*)p.best : (void*)p.score);
         const ptrdiff_t bestDelta  = p.best ? reinterpret_cast<char*>(p.best) - gBase : 0;
@@ -309,13 +315,26 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
             const uint32_t* meta = reinterpret_cast<const uint32_t*>(tile + kTileN * 4);  // TileMeta words
             constexpr uint32_t segMask = (1u << SEGS) - 1u;
             const uint32_t  segEnd  = (meta[0] >> (SEGS * part)) & segMask;
-            const uint32_t  mixBase = meta[2 + part];
-            const uint32_t  nMix    = __popc(segEnd);
-            const uint32_t  adv_r = 32 / max(nMix, 1u), adv_j = 32 - adv_r * nMix;
-            const uint32_t  lr0 = lane / max(nMix, 1u), lj0 = lane - lr0 * nMix;
+            const uint32_t  nMixW   = __popc(segEnd);  // mixtures this warp closes
+            // the store group's mixtures: this warp's (8 warps), or the whole tile's (16 warps; colOff = where this
+            // warp's mixtures start among them)
+            uint32_t nMix = nMixW, colOff = 0, mixBase = meta[2 + part];
+            if (NE == 16) {
+                const uint32_t all = meta[0];
+                nMix               = __popc(all);
+                colOff             = __popc(all & ((1u << (SEGS * part)) - 1u));
+                mixBase            = 0;
+                for (int pp = 3; pp >= 0; --pp)  // mixtures of a tile are consecutive: any part that has some gives the base
+                    if ((all >> (SEGS * pp)) & segMask)
+                        mixBase = meta[2 + pp] - __popc(all & ((1u << (SEGS * pp)) - 1u));
+            }
+            const uint32_t  adv_r = GW / max(nMix, 1u), adv_j = GW - adv_r * nMix;
+            const uint32_t  lr0 = gl / max(nMix, 1u), lj0 = gl - lr0 * nMix;
             const size_t    gStep = ((size_t)adv_r * p.ld + adv_j) * 4, gStepW = gStep + (p.ld - nMix) * 4;  // bytes
             const uint32_t  sStep = (adv_r * p.stagePitch + adv_j) * 4, sStepW = sStep + (p.stagePitch - nMix) * 4;
-            const uint32_t  ssLane = stWarp + (lr0 * p.stagePitch + lj0) * 4;
+            const uint32_t  ssOff = (lr0 * p.stagePitch + lj0) * 4;
+            const uint32_t  stOff = ((uint32_t)lane * p.stagePitch + colOff) * 4;
+            const uint32_t  passes = (32 * nMix + GW - 1) / GW;
             size_t          gTile = ((size_t)(f0 * kTileM + qd * 32 + lr0) * p.ld + mixBase + lj0) * 4;
             const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
             const uint32_t* xxp = p.rowXX + (size_t)f0 * kTileM + qd * 32 + lane;
@@ -332,8 +351,9 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                     tc_fence_after();
                     const uint32_t taddr   = tmemBase + ((uint32_t)(qd * 32) << 16) + acc * kTileN + part * PW;
                     const uint32_t drained = smem_u32(&ready[(t + 2) % kRing]);
-                    QEpiState st;
-                    st.run = kNoKey, st.sp = stRow;
+                    const uint32_t stBuf = stGrp + (kBufs == 2 ? (t & 1) * stageWarp * 4 : 0u);
+                    QEpiState      st;
+                    st.run = kNoKey, st.sp = stBuf + stOff;
                     uint32_t va[32];
                     if (NE == 16) {
                         // 96 registers per thread: one 32-column chunk (+ its 32 constants) live at a time
@@ -367,12 +387,15 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                             mbar_arrive(drained);
                         qepi_chunk<SP>(vb, 3, kcAddr, segEnd, xxBase, offB, st);
                     }
-                    __syncwarp();
-                    // coalesced store of the staged [32 rows x nMix] blocks: nMix passes of 32 consecutive elements
+                    if (NE == 16)  // the quarter's four warps have staged their parts of these 32 rows
+                        asm volatile("bar.sync %0, 128;" ::"r"(1 + qd) : "memory");
+                    else
+                        __syncwarp();
+                    // coalesced store of the staged [32 rows x nMix] block: passes of GW consecutive elements
                     const uint32_t rbase = f * kTileM + qd * 32;
                     const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
-                    char*          g     = gBase + gTile;  // byte address of this lane's first element in q[]
-                    uint32_t       ss    = ssLane;
+                    char*          g     = gBase + gTile;  // byte address of this thread's first element in q[]
+                    uint32_t       ss    = stBuf + ssOff;
                     gTile += gTileStep;
                     auto put = [&](uint32_t r) {
                         if (r < rows) {
@@ -387,14 +410,14 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                     };
                     if (adv_j == 0) {  // nMix divides 32: a lane keeps its column
 #pragma unroll 4
-                        for (uint32_t i = 0, r = lr0; i < nMix; ++i, r += adv_r) {
+                        for (uint32_t i = 0, r = lr0; i < passes; ++i, r += adv_r) {
                             put(r);
                             g += gStep, ss += sStep;
                         }
                     }
                     else {
                         uint32_t r = lr0, j = lj0;
-                        for (uint32_t i = 0; i < nMix; ++i) {
+                        for (uint32_t i = 0; i < passes; ++i) {
                             put(r);
                             const bool w = j + adv_j >= nMix;
                             j            = w ? j + adv_j - nMix : j + adv_j;
@@ -402,7 +425,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                             g += w ? gStepW : gStep, ss += w ? sStepW : sStep;
                         }
                     }
-                    __syncwarp();
+                    if (NE != 16)
+                        __syncwarp();
                 }
             };
             const uint32_t uni = (meta[10] >> (8 * part)) & 0xFFu;  // TileMeta::uni
@@ -432,7 +456,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
 static uint32_t qSmemNeed(uint32_t bTileBytes, uint32_t aTileBytes, uint32_t buffersB, uint32_t stagesA,
                           uint32_t pitch, uint32_t epiWarps) {
     const uint32_t bBytes = (bTileBytes + 1023u) & ~1023u;
-    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 2 * epiWarps * 32 * pitch * 4 + 512;
+    (void)epiWarps;  // 8 staging blocks per plane either way: 8 warps x 1, or 4 lane quarters x 2
+    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 2 * 8 * 32 * pitch * 4 + 512;
 }
 
 // Packs the quantized model for the tensor kernel; leaves h->qtensor.valid false when the model does not meet the
@@ -470,7 +495,7 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
     const char* envW = getenv("GMM_QTC_EPI_WARPS");
     // 8 epilogue warps (128-column parts) by default: the 16-warp variant is faster on small batches (48 vs 41 M
     // frames/s at 8000 frames, 4501x16) but its 16-byte output pieces collapse on large ones (20 vs 38 M at 64000)
-    tm.partW         = (maxN <= 64 && envW && atoi(envW) == 16) ? 64 : 128;
+    tm.partW         = (maxN <= 64 && !(envW && atoi(envW) == 8)) ? 64 : 128;
     const uint32_t        partW = tm.partW, partsPerTile = kTileN / partW;
     std::vector<Col>      cols;
     std::vector<TileMeta> metas;
@@ -527,9 +552,13 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
             }
         }
     }
-    tm.maxMixPerPart = 1;
-    for (uint32_t v : mixPerPart)
+    tm.maxMixPerPart = 1;  // mixtures per store group: a part (8 warps), a whole tile (16 warps)
+    for (size_t i = 0; i < mixPerPart.size(); i += (partW == 64 ? partsPerTile : 1)) {
+        uint32_t v = 0;
+        for (size_t j = i; j < mixPerPart.size() && j < i + (partW == 64 ? partsPerTile : 1); ++j)
+            v += mixPerPart[j];
         tm.maxMixPerPart = std::max(tm.maxMixPerPart, v);
+    }
 
     // ---- shared-memory configuration ----
     const uint32_t pitch = tm.maxMixPerPart + 1, epiWarps = 4 * partsPerTile;
@@ -571,8 +600,32 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
     return GMM_OK;
 }
 
+static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
+                      uint8_t* d_qx, size_t ld);
+
 int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
                   uint8_t* d_qx, size_t ld) {
+    // launches of at most kChunk frames, as in gmm_tc_score (49.6 M frames/s at 64000 frames per launch, 32.5 M in
+    // one 512000-frame launch on the 4501x16 model)
+    static const uint32_t kChunk = [] {
+        const char* e = getenv("GMM_QTC_CHUNK");
+        const long  v = e ? atol(e) : 65536;
+        return (uint32_t)std::max<long>(kTileM, v / kTileM * kTileM);
+    }();
+    const QuantModel& qm = h->quant;
+    for (uint32_t t0 = 0; t0 < T; t0 += kChunk) {
+        const size_t o  = (size_t)t0 * ld;
+        const int    rc = qtc_launch(h, std::min(kChunk, T - t0), d_x + (size_t)t0 * qm.D, d_q ? d_q + o : nullptr,
+                                     d_best ? d_best + o : nullptr, d_score ? d_score + o : nullptr,
+                                     d_qx ? d_qx + (size_t)t0 * qm.C * qm.Dpad : nullptr, ld);
+        if (rc)
+            return rc;
+    }
+    return GMM_OK;
+}
+
+static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
+                      uint8_t* d_qx, size_t ld) {
     const QTensorModel& tm = h->qtensor;
     const QuantModel&   qm = h->quant;
     if (T == 0)

@@ -1013,21 +1013,33 @@ int tc_run(gmm_handle* h, const TcJob& job) {
 }  // namespace
 
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld) {
-    if (T == 0)
-        return GMM_OK;
-    TcJob job;
-    job.T       = T;
-    job.FT      = (T + kTileM - 1) / kTileM;
-    job.d_x     = d_x;
-    job.rowMap  = nullptr;
-    job.bTiles  = h->tensor.bTiles;
-    job.nTiles  = h->tensor.nTiles;
-    job.itemTab = nullptr;
-    job.nItems  = 0;
-    job.scores  = d_scores;
-    job.best    = d_best;
-    job.ld      = ld;
-    return tc_run(h, job);
+    // Long batches go out as launches of at most kChunk frames: the A tiles of one launch (256 bytes per frame) and
+    // the model's B tiles then stay in L2 across the B-tile passes, instead of being streamed from HBM once per pass
+    // (4501x16 model, sustained: 57.0 M frames/s in one 512000-frame launch, 62.3 M in 32000-frame launches).
+    static const uint32_t kChunk = [] {
+        const char* e = getenv("GMM_TC_CHUNK");
+        const long  v = e ? atol(e) : 32768;
+        return (uint32_t)std::max<long>(kTileM, v / kTileM * kTileM);
+    }();
+    for (uint32_t t0 = 0; t0 < T; t0 += kChunk) {
+        const uint32_t n = std::min(kChunk, T - t0);
+        TcJob          job;
+        job.T       = n;
+        job.FT      = (n + kTileM - 1) / kTileM;
+        job.d_x     = d_x + (size_t)t0 * h->D;
+        job.rowMap  = nullptr;
+        job.bTiles  = h->tensor.bTiles;
+        job.nTiles  = h->tensor.nTiles;
+        job.itemTab = nullptr;
+        job.nItems  = 0;
+        job.scores  = d_scores + (size_t)t0 * ld;
+        job.best    = d_best ? d_best + (size_t)t0 * ld : nullptr;
+        job.ld      = ld;
+        const int rc = tc_run(h, job);
+        if (rc)
+            return rc;
+    }
+    return GMM_OK;
 }
 
 // ---- subset scoring --------------------------------------------------------------------------------------------

@@ -114,12 +114,15 @@ MODELS = [
 ]
 
 
-@pytest.mark.parametrize("kernel", ["auto", "dp4a"])
+@pytest.mark.parametrize("kernel", ["auto", "tensor8", "dp4a"])
 @pytest.mark.parametrize("T", [1, 130, 700])
 def test_quantized_kernels_agree_with_oracle(eng, oracle, kernel, T, monkeypatch):
-    """Pooled-covariance model: the integer tensor path (auto) and the forced dp4a kernel are both bit-exact."""
+    """Pooled-covariance model: the integer tensor path (auto: 16 epilogue warps storing per lane quarter; tensor8:
+    8 epilogue warps) and the forced dp4a kernel are all bit-exact."""
     if kernel == "dp4a":
         monkeypatch.setenv("GMM_QUANT_KERNEL", "dp4a")
+    if kernel == "tensor8":
+        monkeypatch.setenv("GMM_QTC_EPI_WARPS", "8")
     ms = synth.make_model(M=300, K=16, D=45, ragged=True, seed=11)
     x = synth.make_features(ms, T)
     x[-1] *= -40.0
