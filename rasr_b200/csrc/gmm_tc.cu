@@ -160,6 +160,58 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
     }
 }
 
+// Full-sum scorer on a column part whose mixtures all span SP segments (TileMeta::uni): the mixture's values are all
+// in this thread's registers, so the log-sum-exp is two passes -- the minimum first (a min tree, as cheap as the
+// maximum approximation), then one exp2 per live density against that fixed reference -- instead of the online form
+// with its running-minimum updates and rescaling.  A segment whose densities lie, for every frame of the warp, more
+// than 40 above the mixture's best is skipped: exp(-40 / 2) < 2^-28 cannot change an f32 sum that is >= 1.
+// Measured and dropped: moving a share of the exponentials from the special-function unit to a polynomial on the FMA
+// pipe (12001x64 model, 10000 frames: 2.91 ms with none, 3.83 / 4.88 / 5.93 ms with 2 / 4 / 6 of 8) -- the epilogue is
+// bound by instruction issue, not by the 16 exp2 per clock of the SFU.
+// get(i) = accumulator value i of the part (compile-time i), N = columns of the part held in registers.
+template<bool BEST, int SP, int NSEG, typename Get>
+__device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, const uint16_t* __restrict__ slots,
+                                                uint64_t liveBits, float rt, float rs, uint32_t offB, EpiState& st) {
+    constexpr float kLn2 = 0.69314718055994530942f;
+    const float     hl2e = 0.72134752044448170368f * rs;  // 0.5 * log2(e) * rowScale
+#pragma unroll
+    for (int m0 = 0; m0 < NSEG; m0 += SP) {  // one mixture: segments [m0, m0 + SP) of the registers
+        float segMin[SP];
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            const int b = (m0 + s) * 8;
+            segMin[s]   = fminf(fminf(fminf(get(b), get(b + 1)), fminf(get(b + 2), get(b + 3))),
+                                fminf(fminf(get(b + 4), get(b + 5)), fminf(get(b + 6), get(b + 7))));
+        }
+        float best = segMin[0];
+#pragma unroll
+        for (int s = 1; s < SP; ++s)
+            best = fminf(best, segMin[s]);
+        const float bestL = best * hl2e;
+        float       sum   = 0.f;
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            const int live = (int)((liveBits >> ((seg0 + m0 + s) * 4)) & 15ull) + 1;  // uniform
+            if (__any_sync(0xffffffffu, !((segMin[s] - best) * rs >= 40.f))) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (j < live)  // (best - u) * hl2e as one fused multiply-add: the epilogue is issue-bound
+                        sum += ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
+            }
+        }
+        const float b2 = fminf(best * rs, FLT_MAX);
+        sts_f32(st.sp, 0.5f * (b2 + rt) - kLn2 * __log2f(sum));
+        if (BEST) {
+            uint32_t idx = 0;
+#pragma unroll
+            for (int i = SP * 8 - 1; i >= 0; --i)  // first density that reaches the minimum
+                idx = get(m0 * 8 + i) == best ? (uint32_t)i : idx;
+            sts_u32(st.sp + offB, (uint32_t)slots[colBase + (seg0 + m0) * 8 + idx]);
+        }
+        st.sp += 4;
+    }
+}
+
 // MODE 0 = max, 1 = sum.  BEST: also write the index of the winning density.
 // NE = epilogue warps (8 or 16): warp e handles TMEM lane quarter (warp & 3) and column part e / 4 of
 // 1024 / NE columns (128 or 64).  16 warps give every scheduler four epilogue warps to hide the latencies of
@@ -392,8 +444,14 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                        epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        if (MODE == 1 && SP > 0) {
+                            auto get = [&](int i) { return __uint_as_float(i < 32 ? va[i & 31] : vb[i & 31]); };
+                            epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st);
+                        }
+                        else {
+                            epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                            epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        }
                     }
                     else {
                         // 128 columns in four 32-column chunks, the next load in flight while one is reduced
@@ -451,7 +509,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     __syncwarp();
                 }
             };
-            const uint32_t uni = (MODE == 0) ? ((meta[10] >> (8 * part)) & 0xFFu) : 0u;  // TileMeta::uni
+            // TileMeta::uni; the full-sum scorer is specialised on it with 16 epilogue warps (its default)
+            const uint32_t uni = (MODE == 0 || NE == 16) ? ((meta[10] >> (8 * part)) & 0xFFu) : 0u;
             switch (uni) {
                 case 1: tiles(std::integral_constant<int, 1>{}); break;
                 case 2: tiles(std::integral_constant<int, 2>{}); break;
