@@ -409,7 +409,7 @@ def run_ours(args):
             "clocks": clocks}
     if rank == 0:
         line["roofline"] = float_roofline(ms, frames / launches_per_step, kernel_sec, peaks, kname, sec_per_step,
-                                          ncu_traffic("prof_tc_cfg1_bench_r01.txt") if frames == 512000 else None,
+                                          ncu_traffic("prof_tc_cfg1_max_32768_r01.txt") if launches_per_step > 1 else None,
                                           sustained=sec >= 0.1, launches_per_step=launches_per_step)
         if world == 1 and not args.no_cpu:
             os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core again

@@ -28,6 +28,8 @@ x = x[:segs * T].contiguous().pin_memory().numpy()
 eng.create_accumulators(tables.mean_index(ms), ms.n_means)
 ref = None
 cases = [("0", "100000"), ("1", "100000"), ("1", "296"), ("1", "148"), ("1", "74")]
+if os.environ.get("PIPELINE_CASES"):  # e.g. "1:296" -- compact blocks, groups of 296 segments (the defaults) only
+    cases = [tuple(c.split(":")) for c in os.environ["PIPELINE_CASES"].split(",")]
 for flag, group in cases:
     os.environ["GMM_ALIGN_SUBSET"] = flag
     os.environ["GMM_ALIGN_GROUP"] = group
