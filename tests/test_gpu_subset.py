@@ -102,3 +102,42 @@ def test_alignment_over_compact_score_blocks(eng, oracle, monkeypatch, align_ker
     emo, sto, sco = oracle.viterbi_align(fo, s, au)
     assert np.array_equal(out["1"][0], emo) and np.array_equal(out["1"][1], sto)
     assert np.array_equal(out["1"][2].view(np.uint32), sco.view(np.uint32))
+
+
+@pytest.mark.parametrize("subset", ["0", "1"])
+def test_alignment_pipeline_across_two_lanes(oracle, monkeypatch, subset):
+    """Groups of segments alternate between the handle's two lanes (stream + scratch + pinned staging each): with
+    groups of 2 segments a 9-segment call runs 5 groups, reuses each lane twice, and must give the paths of the
+    one-group call and of the oracle; the training pass must accumulate every aligned frame exactly once."""
+    from rasr_b200.align import AlignmentAutomata, linear_hmm
+    monkeypatch.setenv("GMM_ALIGN_SUBSET", subset)
+    monkeypatch.setenv("GMM_HOST_THREADS", "3")
+    e = capi.Engine(0)
+    try:
+        ms = synth.make_model(M=700, K=16, D=45, seed=8)
+        rng = np.random.default_rng(5)
+        lens = [200, 129, 0, 64, 333, 1, 128, 90, 257]
+        fo = np.cumsum([0] + lens).astype(np.uint32)
+        x = synth.make_features(ms, int(fo[-1]), seed=4)
+        segs = [linear_hmm(rng.integers(0, ms.M, n), loop=3.0, forward=0.0, skip=30.0)
+                for n in (50, 30, 4, 20, 120, 1, 60, 25, 100)]
+        au = AlignmentAutomata.from_arc_lists(segs)
+        upload(e, ms)
+        monkeypatch.setenv("GMM_ALIGN_GROUP", "1000")
+        one = e.score_align_host(fo, x, au)
+        monkeypatch.setenv("GMM_ALIGN_GROUP", "2")
+        two = e.score_align_host(fo, x, au)
+        for a, b in zip(one, two):
+            assert np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+        s, _ = e.score_host(x, want_best=False)
+        emo, sto, sco = oracle.viterbi_align(fo, s, au)
+        assert np.array_equal(two[0], emo) and np.array_equal(two[1], sto)
+        assert np.array_equal(two[2].view(np.uint32), sco.view(np.uint32))
+        # training pass over the lanes: unweighted counts are exact, one per aligned frame
+        e.create_accumulators(tables.mean_index(ms), ms.n_means)
+        e.score_align_host(fo, x, au, accumulate=True, want_paths=False)
+        acc = e.read_accumulators(ms.variances.shape[0])
+        aligned = int(np.sum(emo != 0xFFFFFFFF))
+        assert int(round(float(np.sum(acc["mix_weight"])))) == aligned
+    finally:
+        e.close()
