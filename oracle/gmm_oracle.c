@@ -555,3 +555,104 @@ void orc_lda(const float* base, uint32_t nSeg, const uint32_t* frameOffsets, uin
     }
     free(win);
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Baum-Welch alignment (Search::Aligner in mode baum-welch, unpruned, min-weight 0).  PARITY UNPINNED, as
+ * orc_viterbi_align: restated from the source, the aligner and the Fsa library it uses cannot be compiled here.
+ *   Search/Aligner.cc:160-187  activateOrUpdateStateHypothesisBaumWelch: the forward potential of a state is
+ *                              collected in the log semiring over its incoming arcs; the traceback lattice keeps
+ *                              one arc per (frame, automaton arc) with weight transition + emission score
+ *   Search/Aligner.cc:438-452  getAlignmentFsaBaumWelch: final weights close the lattice
+ *   Search/Aligner.cc:757-772  getAlignmentPosteriorFsa: Fsa::posterior64 -- arc posteriors (f64 forward / backward),
+ *                              as -log probabilities
+ *   Search/Aligner.cc:693-716  getAlignment: items (time, emission, -log posterior) combined per (time, emission) in
+ *                              the log semiring, clipped to >= 0, shifted, exp(-.), normalised per time frame, > 0 kept
+ *   Speech/Alignment.cc:455-566 combineItems / clipWeights / shiftMinToZeroWeights / expm / normalizeWeights
+ * Here in f64 throughout: weights[t][j] = posterior of emission emList[j] at frame t (0 where none), emList = the
+ * distinct emissions of the automaton in order of first use by an arc.  Returns the total score -log p(x | automaton)
+ * (FLT_MAX and all-zero weights when no final state is reached: empty alignment, Aligner.cc:734-735).
+ * ------------------------------------------------------------------------------------------- */
+static double orc_log_add(double a, double b) { /* Fsa::LogSemiring::collect: -log(exp(-a) + exp(-b)) */
+    if (isinf(a) && a > 0)
+        return b;
+    if (isinf(b) && b > 0)
+        return a;
+    const double m = a < b ? a : b, d = a < b ? b - a : a - b;
+    return m - log1p(exp(-d));
+}
+
+double orc_baum_welch_align(uint32_t T, const float* scores, size_t ld, uint32_t S, const uint32_t* arcOffsets,
+                            const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
+                            uint32_t initial, const float* finalWeight, uint32_t nList, const uint32_t* emList,
+                            float* weights /* [T x ldW] */, size_t ldW) {
+    double* alpha = (double*)malloc(sizeof(double) * (size_t)(T + 1) * (S ? S : 1));
+    double* beta  = (double*)malloc(sizeof(double) * 2 * (S ? S : 1));
+    double* gamma = (double*)malloc(sizeof(double) * (nList ? nList : 1));
+    for (size_t i = 0; i < (size_t)(T + 1) * S; ++i)
+        alpha[i] = INFINITY;
+    for (uint32_t t = 0; t < T; ++t)
+        for (uint32_t j = 0; j < nList; ++j)
+            weights[(size_t)t * ldW + j] = 0.f;
+    if (S == 0) {
+        free(alpha), free(beta), free(gamma);
+        return FLT_MAX;
+    }
+    alpha[initial] = 0.0;
+    for (uint32_t t = 0; t < T; ++t) {
+        const float* row = scores + (size_t)t * ld;
+        for (uint32_t s = 0; s < S; ++s) {
+            const double from = alpha[(size_t)t * S + s];
+            if (isinf(from))
+                continue;
+            for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a) {
+                /* Aligner.cc:228-230: arcScore = transition + emission (f32), potential = score + arcScore */
+                const float arcScore = arcWeight[a] + row[arcEmission[a]];
+                double*     to       = &alpha[(size_t)(t + 1) * S + arcTarget[a]];
+                *to                  = orc_log_add(*to, from + (double)arcScore);
+            }
+        }
+    }
+    double total = INFINITY;
+    for (uint32_t s = 0; s < S; ++s)
+        if (!isinf(finalWeight[s]))
+            total = orc_log_add(total, alpha[(size_t)T * S + s] + (double)finalWeight[s]);
+    if (isinf(total)) {
+        free(alpha), free(beta), free(gamma);
+        return FLT_MAX;
+    }
+    double *bNext = beta, *bCur = beta + S;
+    for (uint32_t s = 0; s < S; ++s)
+        bNext[s] = isinf(finalWeight[s]) ? INFINITY : (double)finalWeight[s];
+    for (uint32_t t = T; t-- > 0;) {
+        const float* row = scores + (size_t)t * ld;
+        for (uint32_t j = 0; j < nList; ++j)
+            gamma[j] = INFINITY;
+        for (uint32_t s = 0; s < S; ++s) {
+            bCur[s]           = INFINITY;
+            const double from = alpha[(size_t)t * S + s];
+            for (uint32_t a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a) {
+                const float  arcScore = arcWeight[a] + row[arcEmission[a]];
+                const double rest     = (double)arcScore + bNext[arcTarget[a]];
+                bCur[s]               = orc_log_add(bCur[s], rest);
+                if (isinf(from) || isinf(rest))
+                    continue;
+                uint32_t j = 0;
+                while (j < nList && emList[j] != arcEmission[a])
+                    ++j;
+                if (j < nList)
+                    gamma[j] = orc_log_add(gamma[j], from + rest - total); /* combineItems, log semiring */
+            }
+        }
+        double sum = 0.0; /* clip to >= 0, exp(-.), normalise over the frame (the shift cancels) */
+        for (uint32_t j = 0; j < nList; ++j)
+            sum += isinf(gamma[j]) ? 0.0 : exp(-(gamma[j] < 0.0 ? 0.0 : gamma[j]));
+        for (uint32_t j = 0; j < nList; ++j)
+            weights[(size_t)t * ldW + j] =
+                    (isinf(gamma[j]) || sum == 0.0) ? 0.f : (float)(exp(-(gamma[j] < 0.0 ? 0.0 : gamma[j])) / sum);
+        double* sw = bNext;
+        bNext      = bCur;
+        bCur       = sw;
+    }
+    free(alpha), free(beta), free(gamma);
+    return total;
+}

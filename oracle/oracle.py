@@ -285,3 +285,49 @@ def run_ref(ms, x, scorer="max", *, threads=0, repeat=1, dump=True, workdir=None
             with open(op + ".timing.json") as f:
                 out["timing"] = json.load(f)
         return out
+
+
+def emission_lists(automata, i):
+    """Distinct emissions of segment i's automaton in order of first use by an arc (column order of the compact
+    score / posterior blocks, include/gmm_b200.h)."""
+    a = automata
+    s0, s1 = int(a.state_offsets[i]), int(a.state_offsets[i + 1])
+    a0, a1 = int(a.arc_offsets[s0]), int(a.arc_offsets[s1])
+    seen, out = set(), []
+    for e in a.arc_emission[a0:a1].tolist():
+        if e not in seen:
+            seen.add(e)
+            out.append(e)
+    return np.asarray(out, np.uint32)
+
+
+def baum_welch_align(frame_offsets, scores, automata):
+    """orc_baum_welch_align per segment -> (weights: list of [frames_i x len(list_i)] f32, lists: list of u32 arrays,
+    total [segments] f64)."""
+    L = lib()
+    L.orc_baum_welch_align.restype = C.c_double
+    fo = np.ascontiguousarray(frame_offsets, np.uint32)
+    scores = np.ascontiguousarray(scores, np.float32)
+    a = automata
+    n_seg = fo.shape[0] - 1
+    ld = scores.shape[1] if scores.ndim == 2 else 1
+    weights, lists, total = [], [], np.empty(n_seg, np.float64)
+    for i in range(n_seg):
+        f0, f1 = int(fo[i]), int(fo[i + 1])
+        s0, s1 = int(a.state_offsets[i]), int(a.state_offsets[i + 1])
+        a0 = int(a.arc_offsets[s0])
+        ao = np.ascontiguousarray(a.arc_offsets[s0:s1 + 1] - np.uint32(a0))
+        tg = np.ascontiguousarray(a.arc_target[a0:])
+        ae = np.ascontiguousarray(a.arc_emission[a0:])
+        aw = np.ascontiguousarray(a.arc_weight[a0:])
+        fw = np.ascontiguousarray(a.final_weight[s0:s1])
+        lst = emission_lists(a, i)
+        rows = scores[f0:f1]
+        w = np.zeros((f1 - f0, max(1, lst.shape[0])), np.float32)
+        total[i] = L.orc_baum_welch_align(C.c_uint32(f1 - f0), _p(rows) if f1 > f0 else C.c_void_p(0), C.c_size_t(ld),
+                                          C.c_uint32(s1 - s0), _p(ao), _p(tg), _p(ae), _p(aw),
+                                          C.c_uint32(int(a.initial_state[i])), _p(fw), C.c_uint32(lst.shape[0]),
+                                          _p(lst) if lst.shape[0] else C.c_void_p(0), _p(w), C.c_size_t(w.shape[1]))
+        weights.append(w[:, :lst.shape[0]])
+        lists.append(lst)
+    return weights, lists, total

@@ -110,3 +110,62 @@ def test_automata_slice_is_segment_sharding(oracle):
         e2, t2, c2 = oracle.viterbi_align(fo[s0:s1 + 1] - fo[s0], scores[fo[s0]:fo[s1]], sub)
         assert np.array_equal(e2, em[fo[s0]:fo[s1]]) and np.array_equal(t2, st[fo[s0]:fo[s1]])
         assert np.array_equal(c2, sc[s0:s1])
+
+
+def _all_paths_posteriors(T, scores, states, initial, final):
+    """Brute force: enumerate every path of T arcs from `initial` to a final state; -> (posterior[t][emission], total)."""
+    import itertools
+    import math
+    paths = []
+
+    def walk(s, t, cost, ems):
+        if t == T:
+            if s in final:
+                paths.append((cost + float(np.float32(final[s])), tuple(ems)))
+            return
+        for (tg, e, w) in states[s]:
+            walk(tg, t + 1, cost + float(np.float32(np.float32(w) + scores[t, e])), ems + [e])
+
+    walk(initial, 0, 0.0, [])
+    if not paths:
+        return None, None
+    z = sum(math.exp(-c) for c, _ in paths)
+    post = [dict() for _ in range(T)]
+    for c, ems in paths:
+        for t, e in enumerate(ems):
+            post[t][e] = post[t].get(e, 0.0) + math.exp(-c) / z
+    return post, -math.log(z)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_oracle_baum_welch_matches_path_enumeration(oracle, seed):
+    """The forward-backward restatement against a sum over all paths on automata small enough to enumerate."""
+    rng = np.random.default_rng(seed)
+    M, T, S = 9, 6, 5
+    states = []
+    for s in range(S):
+        states.append([(int(rng.integers(0, S)), int(rng.integers(0, M)), float(rng.uniform(0, 3)))
+                       for _ in range(int(rng.integers(1, 4)))])
+    final = {int(s): float(rng.uniform(0, 2)) for s in rng.choice(S, size=2, replace=False)}
+    scores = rng.uniform(0, 6, (T, M)).astype(np.float32)
+    au = AlignmentAutomata.from_arc_lists([(states, 0, final)])
+    w, lists, total = oracle.baum_welch_align(np.array([0, T], np.uint32), scores, au)
+    post, tot = _all_paths_posteriors(T, scores, states, 0, final)
+    if post is None:
+        assert total[0] == np.finfo(np.float32).max and not w[0].any()
+        return
+    assert abs(total[0] - tot) < 1e-9
+    for t in range(T):
+        np.testing.assert_allclose(w[0][t].sum(), 1.0, rtol=1e-6)
+        for j, e in enumerate(lists[0]):
+            assert abs(w[0][t, j] - post[t].get(int(e), 0.0)) < 1e-6
+
+
+def test_oracle_baum_welch_unreachable(oracle):
+    states = [[(1, 0, 0.0)], []]                       # one arc, final state 1: exactly one frame fits
+    au = AlignmentAutomata.from_arc_lists([(states, 0, {1: 0.0})])
+    scores = np.ones((3, 2), np.float32)
+    w, lists, total = oracle.baum_welch_align(np.array([0, 3], np.uint32), scores, au)
+    assert total[0] == np.finfo(np.float32).max and not w[0].any()
+    w, lists, total = oracle.baum_welch_align(np.array([0, 1], np.uint32), scores[:1], au)
+    assert abs(total[0] - 1.0) < 1e-12 and w[0][0, 0] == 1.0
