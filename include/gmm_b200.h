@@ -142,6 +142,38 @@ int gmm_score_align_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t
                                     const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState,
                                     float* pathScore);
 
+/* ---- device-resident consumer, second mode: Baum-Welch alignment ------------------------------------------------
+ * Replaces, for unpruned Baum-Welch alignment with min-weight 0 (the defaults), Search::Aligner in mode baum-welch:
+ * SearchSpace::activateOrUpdateStateHypothesisBaumWelch / expand (src/Search/Aligner.cc:160-187, 190-239: forward
+ * potentials collected in the log semiring), getAlignmentFsaBaumWelch + getAlignmentPosteriorFsa (:438-452, 757-772:
+ * arc posteriors, Fsa::posterior64) and getAlignment (:693-716 with Speech/Alignment.cc:455-566: items combined per
+ * frame and emission, clipped, exponentiated).  Automata as for gmm_align_device.
+ * What comes back is, per frame, the weight of every alignment item the reference would emit: row t of `weights`
+ * holds in column j the posterior of emission list[listOffsets[s] + j] of the frame's segment s (0 where the
+ * reference has no item) -- the lists are the distinct emissions of each automaton in order of first use by an arc,
+ * gmm_emission_lists computes them (host arrays; `list` needs room for one entry per arc).  ldW >= the longest list.
+ * totalScore[s] (host, may be NULL) = -log p(segment | automaton), FLT_MAX and an all-zero block for a segment whose
+ * automaton cannot reach a final state (the reference's empty alignment). */
+int gmm_emission_lists(gmm_handle* h, uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                       const uint32_t* arcEmission, uint32_t nEmissions, uint32_t* listOffsets, uint32_t* list);
+/* scores and weights are DEVICE blocks ([frames x ld] as gmm_score_device wrote them, [frames x ldW]). */
+int gmm_baum_welch_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
+                          const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                          const float* finalWeight, float* d_weights, size_t ldW, double* totalScore);
+/* Host features -> float scorer (only the emissions each automaton names) -> posteriors; weights is a HOST block. */
+int gmm_score_baum_welch_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                              const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                              const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                              const float* finalWeight, float* weights, size_t ldW, double* totalScore);
+/* The Baum-Welch training pass: as above, and every (frame, emission) item with a positive weight is accumulated
+ * into the estimators of gmm_accumulator_create with that weight (AlignmentNode -> KeyedEstimator::processAlignedFeature
+ * with weighted items, src/Speech/KeyedEstimator.cc:108-121); nothing returns per frame. */
+int gmm_score_baum_welch_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                         const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                                         const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
+                                         const uint32_t* initialState, const float* finalWeight, double* totalScore);
+
 /* ---- training E-step on the device ----------------------------------------------------
  * Replaces Speech::KeyedEstimator::processAlignedFeature (src/Speech/KeyedEstimator.cc:108-121) and
  * Mm::AbstractMixtureSetEstimator::accumulate (src/Mm/AbstractMixtureSetEstimator.cc:117-147): for every frame t

@@ -31,6 +31,10 @@ SYMBOLS = [
     ("gmm_upload_quant", _i, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, C.c_float]),
     ("gmm_quant_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_quant_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
+    ("gmm_emission_lists", _i, [_vp, _u32, _vp, _vp, _vp, _u32, _vp, _vp]),
+    ("gmm_baum_welch_device", _i, [_vp, _u32, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    ("gmm_score_baum_welch_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    ("gmm_score_baum_welch_accumulate_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("gmm_score_subset_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_score_subset_ld", _u32, [_vp, _u32]),
     ("gmm_align_device", _i, [_vp, _u32, _vp, _vp, _sz] + [_vp] * 10),
@@ -247,6 +251,56 @@ class Engine:
                                                    _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight),
                                                    _ptr(em), _ptr(st), _ptr(sc)), "gmm_score_align_host")
         return em, st, sc
+
+    # -- Baum-Welch alignment ----------------------------------------------------------------------
+    def emission_lists(self, automata, n_emissions):
+        """-> (list_offsets [segments + 1], lists): the distinct emissions of every automaton in order of first use,
+        the column order of compact score blocks and of the Baum-Welch posterior rows."""
+        a = automata
+        n_seg = a.segments
+        lo = np.empty(n_seg + 1, np.uint32)
+        lst = np.empty(max(1, int(a.arc_emission.shape[0])), np.uint32)
+        self._check(self._lib.gmm_emission_lists(self._h, n_seg, _ptr(a.state_offsets), _ptr(a.arc_offsets),
+                                                 _ptr(a.arc_emission), int(n_emissions), _ptr(lo), _ptr(lst)),
+                    "gmm_emission_lists")
+        return lo, lst[:int(lo[-1])]
+
+    def baum_welch_device(self, frame_offsets, d_scores, automata, d_weights, ld=None, ld_w=None):
+        """Scores [frames, ld] and weights [frames, ld_w] on the device -> total score per segment (f64)."""
+        fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
+        a = automata
+        total = np.empty(max(n_seg, 0), np.float64)
+        self._check(self._lib.gmm_baum_welch_device(
+            self._h, n_seg, _ptr(fo), _ptr(d_scores), int(ld if ld is not None else d_scores.shape[1]),
+            _ptr(a.state_offsets), _ptr(a.arc_offsets), _ptr(a.arc_target), _ptr(a.arc_emission), _ptr(a.arc_weight),
+            _ptr(a.initial_state), _ptr(a.final_weight), _ptr(d_weights),
+            int(ld_w if ld_w is not None else d_weights.shape[1]), _ptr(total)), "gmm_baum_welch_device")
+        return total
+
+    def score_baum_welch_host(self, frame_offsets, x, automata, ld_w=None, accumulate=False, want_weights=True):
+        """Host features -> posterior rows [frames, ld_w] (f32, host) and total scores; accumulate=True with
+        want_weights=False is the Baum-Welch training pass (nothing but the totals comes back)."""
+        fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
+        a = automata
+        x = _np(x, np.float32)
+        if x.ndim != 2 or x.shape != (n_frames, self._in_dim(self.D)):
+            raise ValueError(f"features must be [{n_frames}, {self._in_dim(self.D)}]")
+        total = np.empty(max(n_seg, 0), np.float64)
+        if accumulate:
+            self._check(self._lib.gmm_score_baum_welch_accumulate_host(
+                self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets), _ptr(a.arc_offsets), _ptr(a.arc_target),
+                _ptr(a.arc_emission), _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight), _ptr(total)),
+                "gmm_score_baum_welch_accumulate_host")
+            return None, total
+        if ld_w is None:
+            lo, _ = self.emission_lists(a, self.M)
+            ld_w = max(1, int(np.max(np.diff(lo)))) if n_seg else 1
+        w = np.zeros((n_frames, int(ld_w)), np.float32)
+        self._check(self._lib.gmm_score_baum_welch_host(
+            self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets), _ptr(a.arc_offsets), _ptr(a.arc_target),
+            _ptr(a.arc_emission), _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight), _ptr(w), int(ld_w),
+            _ptr(total)), "gmm_score_baum_welch_host")
+        return w, total
 
     @property
     def align_ordered_count(self) -> int:

@@ -22,6 +22,7 @@
 // and adds it once at the end.
 #include <float.h>
 #include <math.h>
+#include <string.h>
 
 #include "gmm_distance.cuh"
 #include "gmm_internal.cuh"
@@ -34,6 +35,12 @@ struct AccumParams {
     const float*    x;
     const uint32_t* mixture;  // [T] mixture of every frame, kSkip: not aligned
     const double*   weight;   // [T] or null (1)
+    // posterior rows (Baum-Welch alignment): when rowW is set, frame t goes into EVERY mixture emList[emOff[s] + j] of
+    // its segment s whose weight rowW[t * ldW + j] is positive, instead of into mixture[t]
+    const float*    rowW;
+    size_t          ldW;
+    const uint32_t *segFrameOff, *emOff, *emList;
+    uint32_t        nSeg;
     uint32_t*       best;     // [T] or null: chosen density (index in mixture)
     uint32_t        T, D;
     const float *   mean, *isr, *w2, *logNorm;
@@ -55,12 +62,9 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const AccumParams p) {
 #pragma unroll
     for (int j = 0; j < (DP + 31) / 32; ++j)
         cov[j] = 0.0;
-    for (uint32_t t = warp; t < p.T; t += nWarps) {
-        const uint32_t m = p.mixture[t];
-        if (m == kSkip)
-            continue;
+    // frame t into mixture m with weight w (`weighted`: the weighted accumulation formulas)
+    auto process = [&](uint32_t t, uint32_t m, double w, bool weightedItem) {
         const uint32_t a = p.offsets[m], K = p.offsets[m + 1] - a;
-        const double   w = p.weight ? p.weight[t] : 1.0;
         Frames<DP, 1>  f;
 #pragma unroll
         for (int d = 0; d < DP; ++d)
@@ -136,7 +140,7 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const AccumParams p) {
             p.best[t] = bestDns;
         if (p.viterbi) {
             if (bestDns != kSkip)  // no density below FLT_MAX: nothing the reference could index either
-                accumulate(bestDns, w, p.weight != nullptr);
+                accumulate(bestDns, w, weightedItem);
         }
         else if (SUM) {
             // score = best - log sum_k exp(best - s_k), posteriors exp(score - s_k) (.cc:276-298), each density
@@ -162,6 +166,36 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const AccumParams p) {
                         accumulate(k0 + j, fin, true);
                 }
             }
+        }
+    };
+    if (p.rowW) {
+        for (uint32_t t = warp; t < p.T; t += nWarps) {
+            uint32_t lo = 0, hi = p.nSeg;  // segment of frame t: last s with segFrameOff[s] <= t
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (p.segFrameOff[mid] <= t)
+                    lo = mid;
+                else
+                    hi = mid;
+            }
+            const uint32_t e0 = p.emOff[lo], n = p.emOff[lo + 1] - e0;
+            const float*   row = p.rowW + (size_t)t * p.ldW;
+            for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+                const float wj   = j0 + lane < n ? row[j0 + lane] : 0.f;
+                uint32_t    mask = __ballot_sync(0xFFFFFFFFu, wj > 0.f);
+                while (mask) {
+                    const int j = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    process(t, p.emList[e0 + j0 + j], (double)__shfl_sync(0xFFFFFFFFu, wj, j), true);
+                }
+            }
+        }
+    }
+    else {
+        for (uint32_t t = warp; t < p.T; t += nWarps) {
+            const uint32_t m = p.mixture[t];
+            if (m != kSkip)
+                process(t, m, p.weight ? p.weight[t] : 1.0, p.weight != nullptr);
         }
     }
     if (p.pooled) {
@@ -192,18 +226,9 @@ int launch(gmm_handle* h, const AccumParams& p) {
 
 }  // namespace
 
-int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
-                     uint32_t* d_best) {
-    if (T == 0)
-        return GMM_OK;
+static int accumRun(gmm_handle* h, AccumParams& p) {
     const DirectModel& dm = h->direct;
     const AccumModel&  am = h->accum;
-    AccumParams        p;
-    p.x               = d_x;
-    p.mixture         = d_mixture;
-    p.weight          = d_weight;
-    p.best            = d_best;
-    p.T               = T;
     p.D               = h->D;
     p.mean            = dm.mean;
     p.isr             = dm.isr;
@@ -231,4 +256,35 @@ int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t
         h->setError("accumulate kernel: feature dimension above 128 is not supported");
         return GMM_ERR_UNSUPPORTED;
     }
+}
+
+int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
+                     uint32_t* d_best) {
+    if (T == 0)
+        return GMM_OK;
+    AccumParams p;
+    memset(&p, 0, sizeof(p));
+    p.x       = d_x;
+    p.mixture = d_mixture;
+    p.weight  = d_weight;
+    p.best    = d_best;
+    p.T       = T;
+    return accumRun(h, p);
+}
+
+int gmm_accum_rows_launch(gmm_handle* h, uint32_t nSeg, uint32_t T, const float* d_x, const uint32_t* d_frameOff,
+                          const uint32_t* d_emOff, const uint32_t* d_emList, const float* d_rowWeights, size_t ldW) {
+    if (T == 0 || nSeg == 0)
+        return GMM_OK;
+    AccumParams p;
+    memset(&p, 0, sizeof(p));
+    p.x           = d_x;
+    p.T           = T;
+    p.rowW        = d_rowWeights;
+    p.ldW         = ldW;
+    p.segFrameOff = d_frameOff;
+    p.emOff       = d_emOff;
+    p.emList      = d_emList;
+    p.nSeg        = nSeg;
+    return accumRun(h, p);
 }

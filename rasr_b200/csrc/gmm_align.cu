@@ -839,8 +839,14 @@ int gmm_align_finish(gmm_handle* h, AlignDeferred& f) {
         GMM_CUDA_TRY(h, cudaMemcpyAsync(f.pathState, f.dPathState, (size_t)f.nFrames * 4, cudaMemcpyDeviceToHost, h->stream));
     if (f.pathScore)
         GMM_CUDA_TRY(h, cudaMemcpyAsync(f.pathScore, f.dPathScore, (size_t)f.nSeg * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (f.weights && f.wRows && f.wCols)
+        GMM_CUDA_TRY(h, cudaMemcpy2DAsync(f.weights, f.ldWhost * 4, f.dWeights, f.ldWdev * 4, (size_t)f.wCols * 4, f.wRows,
+                                          cudaMemcpyDeviceToHost, h->stream));
+    if (f.total)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(f.total, f.dTotal, (size_t)f.nSeg * 8, cudaMemcpyDeviceToHost, h->stream));
     uint32_t ordered = 0;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(&ordered, f.dOrdered, 4, cudaMemcpyDeviceToHost, h->stream));
+    if (f.dOrdered)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(&ordered, f.dOrdered, 4, cudaMemcpyDeviceToHost, h->stream));
     GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     h->alignOrdered += ordered;
     return GMM_OK;

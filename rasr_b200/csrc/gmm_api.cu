@@ -525,11 +525,19 @@ uint64_t gmm_align_ordered_count(const gmm_handle* h) {
 
 // One group of whole segments: upload, score (compact block when that saves tensor work), align, accumulate --
 // everything enqueued on the active lane, nothing waited for; `fin` completes it (gmm_align_finish).
+// Baum-Welch groups (bw != null): posterior rows instead of a best path; rows go to bw->weights (host, may be NULL)
+// and, with `accumulate`, into the estimators with the posterior as weight.
+struct BwRequest {
+    float*  weights;  // host [frames x ldW] or NULL
+    size_t  ldW;
+    double* total;    // host [nSeg] or NULL
+};
+
 static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t s1, const uint32_t* frameOffsets,
                            const float* x, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
                            const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
                            const uint32_t* initialState, const float* finalWeight, uint32_t* pathEmission,
-                           uint32_t* pathState, float* pathScore, AlignDeferred* fin) {
+                           uint32_t* pathState, float* pathScore, AlignDeferred* fin, const BwRequest* bw = nullptr) {
     const size_t   devLd = h->M;
     const uint32_t f0 = frameOffsets[s0], T = frameOffsets[s1] - f0, n = s1 - s0;
     static const bool trace = getenv("GMM_TRACE") != nullptr;
@@ -587,6 +595,44 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
             return rc;
     }
     tr[3] = clk();
+    if (bw) {
+        if (!haveLists && !gmm_align_emission_lists(h, n, so.data(), ao.data(), arcEmission ? arcEmission + a0 : nullptr,
+                                                    h->M, lists)) {
+            h->setError("gmm_score_baum_welch: arc offsets not ascending or emission index >= M");
+            return GMM_ERR_ARG;
+        }
+        uint32_t maxList = 1;
+        for (uint32_t i = 0; i < n; ++i)
+            maxList = std::max(maxList, lists.emOff[i + 1] - lists.emOff[i]);
+        if (bw->weights && bw->ldW < maxList) {
+            h->setError("gmm_score_baum_welch: weights block narrower than a segment's emission list");
+            return GMM_ERR_ARG;
+        }
+        const size_t ldP = (maxList + 31) & ~(size_t)31;
+        void*        dp  = nullptr;
+        BwDevice     dev;
+        if ((rc = h->reserve(SCR_POST, (size_t)std::max(1u, T) * ldP * 4, &dp)))
+            return rc;
+        if ((rc = gmm_bw_launch(h, n, fo.data(), (const float*)ds, ldUse, so.data(), ao.data(),
+                                arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
+                                arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0, (float*)dp, ldP,
+                                nullptr, compact, h->M, &lists, false, &dev)))
+            return rc;
+        if (accumulate && T &&
+            (rc = gmm_accum_rows_launch(h, n, T, (const float*)dx, dev.frameOff, dev.emOff, dev.emList, (const float*)dp, ldP)))
+            return rc;
+        fin->pending  = true;
+        fin->nSeg     = n;
+        fin->dWeights = (const float*)dp;
+        fin->weights  = bw->weights ? bw->weights + (size_t)f0 * bw->ldW : nullptr;
+        fin->ldWdev   = ldP;
+        fin->ldWhost  = bw->ldW;
+        fin->wRows    = T;
+        fin->wCols    = bw->weights ? (uint32_t)std::min<size_t>(bw->ldW, ldP) : 0;
+        fin->dTotal   = dev.total;
+        fin->total    = bw->total ? bw->total + s0 : nullptr;
+        return GMM_OK;
+    }
     if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, ldUse, so.data(), ao.data(),
                                arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
                                arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0,
@@ -607,7 +653,8 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
 static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
                          const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
-                         const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore) {
+                         const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
+                         const BwRequest* bw = nullptr) {
     if (!h)
         return GMM_ERR_ARG;
     if (!h->floatValid) {
@@ -621,7 +668,7 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
         return GMM_ERR_ARG;
     }
     if (!frameOffsets || !stateOffsets || !arcOffsets || !initialState || !finalWeight ||
-        (!accumulate && (!pathEmission || !pathScore)) || (frameOffsets[nSeg] && !x)) {
+        (!accumulate && !bw && (!pathEmission || !pathScore)) || (frameOffsets[nSeg] && !x)) {
         h->setError("gmm_score_align: NULL argument");
         return GMM_ERR_ARG;
     }
@@ -657,7 +704,7 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tw0).count());
         if (rc == GMM_OK)
             rc = scoreAlignGroup(h, accumulate, s0, s1, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission,
-                                 arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore, &fin[lane]);
+                                 arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore, &fin[lane], bw);
         if (twoLanes)
             lane ^= 1;
         s0 = s1;
@@ -695,6 +742,67 @@ int gmm_score_align_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t
                                     float* pathScore) {
     return scoreAlign(h, true, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
                       initialState, finalWeight, pathEmission, pathState, pathScore);
+}
+
+// ---- Baum-Welch alignment ---------------------------------------------------------------------------------------
+int gmm_emission_lists(gmm_handle* h, uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                       const uint32_t* arcEmission, uint32_t nEmissions, uint32_t* listOffsets, uint32_t* list) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!stateOffsets || !arcOffsets || !listOffsets || (nSeg && arcOffsets[stateOffsets[nSeg]] && (!arcEmission || !list))) {
+        h->setError("gmm_emission_lists: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    AlignLists L;
+    if (!gmm_align_emission_lists(h, nSeg, stateOffsets, arcOffsets, arcEmission, nEmissions, L)) {
+        h->setError("gmm_emission_lists: arc offsets not ascending or emission index >= nEmissions");
+        return GMM_ERR_ARG;
+    }
+    memcpy(listOffsets, L.emOff.data(), (size_t)(nSeg + 1) * 4);
+    if (!L.emList.empty())
+        memcpy(list, L.emList.data(), L.emList.size() * 4);
+    return GMM_OK;
+}
+
+int gmm_baum_welch_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
+                          const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                          const float* finalWeight, float* d_weights, size_t ldW, double* totalScore) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (nSeg == 0)
+        return GMM_OK;
+    if (!frameOffsets || !stateOffsets || !arcOffsets || !initialState || !finalWeight ||
+        (frameOffsets[nSeg] && (!d_scores || !d_weights)) ||
+        (arcOffsets[stateOffsets[nSeg]] && (!arcTarget || !arcEmission || !arcWeight))) {
+        h->setError("gmm_baum_welch: NULL argument");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return gmm_bw_launch(h, nSeg, frameOffsets, d_scores, ld, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
+                         initialState, finalWeight, d_weights, ldW, totalScore, false, 0, nullptr, true);
+}
+
+int gmm_score_baum_welch_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                              const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                              const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                              const float* finalWeight, float* weights, size_t ldW, double* totalScore) {
+    if (h && nSeg && frameOffsets && frameOffsets[nSeg] && !weights) {
+        h->setError("gmm_score_baum_welch: weights is NULL");
+        return GMM_ERR_ARG;
+    }
+    const BwRequest bw = {weights, ldW, totalScore};
+    return scoreAlign(h, false, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
+                      initialState, finalWeight, nullptr, nullptr, nullptr, &bw);
+}
+
+int gmm_score_baum_welch_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                         const uint32_t* stateOffsets, const uint32_t* arcOffsets,
+                                         const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
+                                         const uint32_t* initialState, const float* finalWeight, double* totalScore) {
+    const BwRequest bw = {nullptr, 0, totalScore};
+    return scoreAlign(h, true, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
+                      initialState, finalWeight, nullptr, nullptr, nullptr, &bw);
 }
 
 // ---- front end on the device -------------------------------------------------------------------------------------

@@ -135,14 +135,14 @@ struct gmm_handle {
     LdaModel     lda;
 
     // scratch (grown on demand)
-    void*  scratch[12]      = {};
-    size_t scratchBytes[12] = {};
+    void*  scratch[16]      = {};
+    size_t scratchBytes[16] = {};
     // Second lane of the pipelined host entry points (gmm_score_align_*_host): its own stream and scratch, so that
     // one group of segments is uploaded and prepared while the previous one is scored and aligned.  useLane() makes a
     // lane the one `stream` / `scratch` refer to; every kernel launcher keeps using those two names.
     cudaStream_t laneStream          = nullptr;
-    void*        laneScratch[12]     = {};
-    size_t       laneScratchBytes[12] = {};
+    void*        laneScratch[16]     = {};
+    size_t       laneScratchBytes[16] = {};
     cudaEvent_t  laneEvent           = nullptr;
     int          lane                = 0;
     void*        pinned[2]           = {};  // host staging blocks (tables built in place, one copy per launch) ...
@@ -172,7 +172,7 @@ struct gmm_handle {
 };
 
 enum { PIN_ALIGN = 0, PIN_SUBSET = 1 };
-enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7, SCR_BASE = 8, SCR_TILES = 9, SCR_VTILES = 10, SCR_TAB = 11, SCR_COUNT = 12 };
+enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5, SCR_ROW = 6, SCR_MISC = 7, SCR_BASE = 8, SCR_TILES = 9, SCR_VTILES = 10, SCR_TAB = 11, SCR_POST = 12, SCR_COUNT = 13 };
 
 // gmm_align_emission_lists' results, handed to gmm_align_launch by a caller that already needed them
 struct AlignLists {
@@ -199,12 +199,34 @@ struct AlignDeferred {
     uint32_t       nFrames = 0, nSeg = 0;
     uint32_t *     pathEmission = nullptr, *pathState = nullptr;
     float*         pathScore = nullptr;
+    // Baum-Welch groups: posterior rows [wRows x wCols] (device pitch ldWdev, host pitch ldWhost floats), total scores
+    const float*   dWeights = nullptr;
+    float*         weights = nullptr;
+    size_t         ldWdev = 0, ldWhost = 0;
+    uint32_t       wRows = 0, wCols = 0;
+    const double*  dTotal = nullptr;
+    double*        total = nullptr;
+};
+// device copies of a Baum-Welch launch's segment tables, for the E-step over its posterior rows
+struct BwDevice {
+    const uint32_t *frameOff = nullptr, *emOff = nullptr, *emList = nullptr;
+    const double*   total = nullptr;
 };
 int gmm_align_finish(gmm_handle* h, AlignDeferred& d);
 // the distinct emissions of every segment's automaton in order of first use (the column order of a compact score
 // block: gmm_tc_score_subset writes it, gmm_align_launch(compact) reads it)
 bool gmm_align_emission_lists(gmm_handle* h, uint32_t nSeg, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
                               const uint32_t* arcEmission, uint32_t nEmissions, struct AlignLists& lists);
+// gmm_bw.cu
+int gmm_bw_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
+                  const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                  const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
+                  const float* finalWeight, float* d_weights, size_t ldW, double* totalScore, bool compact,
+                  uint32_t nEmissions, const struct AlignLists* lists, bool wait, struct BwDevice* dev = nullptr);
+// E-step over posterior rows: frame t of segment s is accumulated into mixture emList[emOff[s] + j] with weight
+// d_rowWeights[t * ldW + j] for every j whose weight is positive (device arrays; frameOff / emOff [nSeg + 1])
+int gmm_accum_rows_launch(gmm_handle* h, uint32_t nSeg, uint32_t T, const float* d_x, const uint32_t* d_frameOff,
+                          const uint32_t* d_emOff, const uint32_t* d_emList, const float* d_rowWeights, size_t ldW);
 int gmm_lda_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_base, float* d_x);
 int gmm_accum_launch(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, const double* d_weight,
                      uint32_t* d_best);
