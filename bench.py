@@ -379,6 +379,24 @@ def run_ours(args):
         tr_sec = float(t.item())
     tr_value = world * al_frames * al_steps / tr_sec
 
+    # the Baum-Welch training pass: compact scores -> forward-backward posteriors -> weighted E-step, on the device
+    for _ in range(2):
+        eng.score_baum_welch_host(al_fo, xal, automata, accumulate=True)
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(al_steps):
+        eng.score_baum_welch_host(al_fo, xal, automata, accumulate=True)
+        if dist is not None:
+            sharded.all_reduce_accumulators(eng, dist)
+    eng.sync()
+    bw_sec = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([bw_sec], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        bw_sec = float(t.item())
+    bw_value = world * al_frames * al_steps / bw_sec
+
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec_per_step * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32 (fp16x3 split operands, f32 accumulate)" if
@@ -408,6 +426,12 @@ def run_ours(args):
                                          "path -> best density of the aligned mixture -> f64 estimator sums, all in "
                                          "HBM; the estimators are read once per pass (gmm_accumulator_read); at N > 1 "
                                          "every step ends with the all-reduce that combines the ranks' estimators"},
+            "e2e_baum_welch_training_pass": {
+                "value": bw_value, "unit": UNIT, "h2d_bytes_per_step": al_frames * ms.D * 4, "d2h_bytes_per_step": al_segs * 8,
+                "frames_per_step_per_gpu": al_frames,
+                "api": "gmm_score_baum_welch_accumulate_host (C-ABI): host features -> compact scores -> forward-backward "
+                       "posteriors per frame and emission -> posterior-weighted E-step, all in HBM; only the segments' "
+                       "total scores return"},
             "clocks": clocks}
     if rank == 0:
         line["roofline"] = float_roofline(ms, frames / launches_per_step, kernel_sec, peaks, kname, sec_per_step,

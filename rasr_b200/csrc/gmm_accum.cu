@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const AccumParams p) {
         }
     };
     if (p.rowW) {
+        const float itemCut = (float)fmax(0.0, p.weightThreshold);
         for (uint32_t t = warp; t < p.T; t += nWarps) {
             uint32_t lo = 0, hi = p.nSeg;  // segment of frame t: last s with segFrameOff[s] <= t
             while (hi - lo > 1) {
@@ -182,7 +183,9 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const AccumParams p) {
             const float*   row = p.rowW + (size_t)t * p.ldW;
             for (uint32_t j0 = 0; j0 < n; j0 += 32) {
                 const float wj   = j0 + lane < n ? row[j0 + lane] : 0.f;
-                uint32_t    mask = __ballot_sync(0xFFFFFFFFu, wj > 0.f);
+                // items at or below the estimators' weight threshold are dropped (the reference's knob for this is the
+                // aligner's min-weight, default 0: create the accumulators with threshold 0 for the literal behaviour)
+                uint32_t    mask = __ballot_sync(0xFFFFFFFFu, wj > itemCut);
                 while (mask) {
                     const int j = __ffs(mask) - 1;
                     mask &= mask - 1;
