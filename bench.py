@@ -443,7 +443,10 @@ def run_ours(args):
             line["cpu_baseline"] = cpu_reference_run(ms, max(512, 96 * cores), "max", 2)
         if world == 1 and not args.no_extra:
             line["extra"] = extra_cases(torch, eng, peaks, args)
+        sys.stdout.flush()
+        os.dup2(args.stdout_fd, 1)
         print(json.dumps(line))
+        sys.stdout.flush()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -513,6 +516,11 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         return run_reference_arm(args)
+    # stdout carries the one JSON line only: whatever native libraries print there meanwhile (NCCL's version banner at
+    # communicator creation) is sent to stderr; the descriptor is restored just before the line is printed
+    sys.stdout.flush()
+    args.stdout_fd = os.dup(1)
+    os.dup2(2, 1)
     return run_ours(args)
 
 
