@@ -769,7 +769,8 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     if ((rc = h->reserve(SCR_MISC, off, &base)))
         return rc;
     char* d = (char*)base;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d, hp, inFlight ? rankedBytes : tableBytes, cudaMemcpyHostToDevice, h->stream));
+    if ((rc = gmm_copy_tables(h, d, hp, inFlight ? rankedBytes : tableBytes)))
+        return rc;
     if ((rc = h->pinnedCopied(PIN_ALIGN)))
         return rc;
     AlignParams p;

@@ -12,6 +12,25 @@
 
 static std::string g_createError;
 
+// GMM_TRACE: device-side timeline of the pipelined host entry points (events on the lanes' streams, printed per call)
+struct TraceMark {
+    cudaEvent_t ev;
+    int         group, lane;
+    const char* what;
+};
+static std::vector<TraceMark> g_trace;
+static cudaEvent_t            g_traceStart = nullptr;
+static void traceMark(gmm_handle* h, int group, const char* what) {
+    static const bool on = getenv("GMM_TRACE") != nullptr;
+    if (!on || !g_traceStart)
+        return;
+    TraceMark m;
+    cudaEventCreate(&m.ev);
+    cudaEventRecord(m.ev, h->stream);
+    m.group = group, m.lane = h->lane, m.what = what;
+    g_trace.push_back(m);
+}
+
 int gmm_handle::devAlloc(void** p, size_t bytes, bool quant) {
     *p = nullptr;
     if (bytes == 0)
@@ -61,6 +80,31 @@ HostPool& gmm_handle::hostPool() {
     return *pool;
 }
 
+static __global__ void __launch_bounds__(256) table_copy_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src,
+                                                                size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        dst[i] = src[i];
+}
+
+int gmm_copy_tables(gmm_handle* h, void* d_dst, const void* pinnedSrc, size_t bytes) {
+    static const bool dma = [] {
+        const char* e = getenv("GMM_TABLE_COPY");
+        return e && !strcmp(e, "dma");
+    }();
+    if (bytes == 0)
+        return GMM_OK;
+    if (dma || (bytes & 15) || ((uintptr_t)d_dst & 15) || ((uintptr_t)pinnedSrc & 15)) {
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(d_dst, pinnedSrc, bytes, cudaMemcpyHostToDevice, h->stream));
+        return GMM_OK;
+    }
+    const size_t n    = bytes / 16;
+    const int    grid = (int)std::min<size_t>((n + 255) / 256, (size_t)h->smCount * 4);
+    table_copy_kernel<<<grid, 256, 0, h->stream>>>((uint4*)d_dst, (const uint4*)pinnedSrc, n);
+    h->launches++;
+    GMM_CUDA_TRY(h, cudaGetLastError());
+    return GMM_OK;
+}
+
 int gmm_handle::pinnedCopied(int slot) {
     if (!pinEvent[slot])
         GMM_CUDA_TRY(this, cudaEventCreateWithFlags(&pinEvent[slot], cudaEventDisableTiming));
@@ -88,19 +132,26 @@ int gmm_handle::reservePinned(int slot, size_t bytes, void** out) {
 int gmm_handle::useLane(int which) {
     if (which == lane)
         return GMM_OK;
-    if (!laneStream) {
-        GMM_CUDA_TRY(this, cudaStreamCreateWithFlags(&laneStream, cudaStreamNonBlocking));
+    if (which < 0 || which >= kMaxLanes)
+        return GMM_ERR_ARG;
+    if (!laneEvent)
         GMM_CUDA_TRY(this, cudaEventCreateWithFlags(&laneEvent, cudaEventDisableTiming));
-    }
-    std::swap(stream, laneStream);
+    LaneState& out = parked[lane];  // park the active lane ...
+    LaneState& in  = parked[which];  // ... and take the other one's state
+    if (which != 0 && !in.stream)
+        GMM_CUDA_TRY(this, cudaStreamCreateWithFlags(&in.stream, cudaStreamNonBlocking));
+    out.stream = stream;
+    stream     = in.stream;
+    in.stream  = nullptr;
     for (int i = 0; i < SCR_COUNT; ++i) {
-        std::swap(scratch[i], laneScratch[i]);
-        std::swap(scratchBytes[i], laneScratchBytes[i]);
+        out.scratch[i] = scratch[i], out.scratchBytes[i] = scratchBytes[i];
+        scratch[i] = in.scratch[i], scratchBytes[i] = in.scratchBytes[i];
+        in.scratch[i] = nullptr, in.scratchBytes[i] = 0;
     }
     for (int i = 0; i < 2; ++i) {
-        std::swap(pinned[i], lanePinned[i]);
-        std::swap(pinnedBytes[i], lanePinnedBytes[i]);
-        std::swap(pinEvent[i], lanePinEvent[i]);
+        out.pinned[i] = pinned[i], out.pinnedBytes[i] = pinnedBytes[i], out.pinEvent[i] = pinEvent[i];
+        pinned[i] = in.pinned[i], pinnedBytes[i] = in.pinnedBytes[i], pinEvent[i] = in.pinEvent[i];
+        in.pinned[i] = nullptr, in.pinnedBytes[i] = 0, in.pinEvent[i] = nullptr;
     }
     lane = which;
     return GMM_OK;
@@ -213,25 +264,30 @@ void gmm_destroy(gmm_handle* h) {
         cudaEventDestroy(h->timed[i].second);
     }
     h->useLane(0);
-    for (int i = 0; i < SCR_COUNT; ++i) {
+    for (int i = 0; i < SCR_COUNT; ++i)
         if (h->scratch[i])
             cudaFree(h->scratch[i]);
-        if (h->laneScratch[i])
-            cudaFree(h->laneScratch[i]);
-    }
     for (int i = 0; i < 2; ++i) {
         if (h->pinned[i])
             cudaFreeHost(h->pinned[i]);
-        if (h->lanePinned[i])
-            cudaFreeHost(h->lanePinned[i]);
         if (h->pinEvent[i])
             cudaEventDestroy(h->pinEvent[i]);
-        if (h->lanePinEvent[i])
-            cudaEventDestroy(h->lanePinEvent[i]);
+    }
+    for (int l = 1; l < gmm_handle::kMaxLanes; ++l) {
+        gmm_handle::LaneState& ls = h->parked[l];
+        for (int i = 0; i < SCR_COUNT; ++i)
+            if (ls.scratch[i])
+                cudaFree(ls.scratch[i]);
+        for (int i = 0; i < 2; ++i) {
+            if (ls.pinned[i])
+                cudaFreeHost(ls.pinned[i]);
+            if (ls.pinEvent[i])
+                cudaEventDestroy(ls.pinEvent[i]);
+        }
+        if (ls.stream)
+            cudaStreamDestroy(ls.stream);
     }
     delete h->pool;
-    if (h->laneStream)
-        cudaStreamDestroy(h->laneStream);
     if (h->laneEvent)
         cudaEventDestroy(h->laneEvent);
     if (h->lda.matrix)
@@ -556,8 +612,10 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
     const uint32_t* dPath = nullptr;
     int   rc;
     const uint32_t inDim = h->lda.valid ? h->lda.baseDim : h->D;
+    traceMark(h, (int)s0, "group start");
     if ((rc = uploadFrames(h, h->D, n, fo.data(), x + (size_t)f0 * inDim, &dx)))
         return rc;
+    traceMark(h, (int)s0, "features on device");
     tr[1] = clk();
     // Lazy evaluation as the reference's cached context scorers do it (FeatureScorer.hh:170-230): only the
     // emissions a segment's automaton can ask for are scored, into a compact block whose column j is entry j of
@@ -594,6 +652,7 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
         if (rc)
             return rc;
     }
+    traceMark(h, (int)s0, "scored");
     tr[3] = clk();
     if (bw) {
         if (!haveLists && !gmm_align_emission_lists(h, n, so.data(), ao.data(), arcEmission ? arcEmission + a0 : nullptr,
@@ -640,6 +699,7 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
                                pathScore ? pathScore + s0 : nullptr, &dPath, compact, h->M, fin,
                                haveLists ? &lists : nullptr)))
         return rc;
+    traceMark(h, (int)s0, "aligned");
     // the aligned frames go straight into the estimators: the path is the per-frame mixture (kNoArc: skip)
     tr[4] = clk();
     if (accumulate && T && (rc = gmm_accum_launch(h, T, (const float*)dx, dPath, nullptr, nullptr)))
@@ -680,14 +740,24 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
     const size_t   maxFrames = std::max<size_t>(1, ((size_t)10 << 30) / ((size_t)h->M * 4));
     const char*    envG      = getenv("GMM_ALIGN_GROUP");
     const uint32_t groupSegs = envG ? (uint32_t)std::max(1, atoi(envG)) : (uint32_t)h->smCount * 2;
-    const bool     twoLanes  = nSeg > groupSegs;
-    AlignDeferred  fin[2];
+    // three lanes by default: with two, a lane's next upload cannot be enqueued before its previous group is complete
+    // (the group's frames are read until its last kernel), and PCIe idles for that long
+    const char*    envL      = getenv("GMM_LANES");
+    const int      nLanes    = nSeg > groupSegs ? std::min(gmm_handle::kMaxLanes, std::max(2, envL ? atoi(envL) : 3)) : 1;
+    const bool     twoLanes  = nLanes > 1;
+    AlignDeferred  fin[gmm_handle::kMaxLanes];
     int            rc = GMM_OK, lane = 0;
-    if (twoLanes) {  // the second lane starts after whatever the handle's stream holds so far (model upload, ...)
-        if ((rc = h->useLane(1)) || (rc = h->useLane(0)))
-            return rc;
+    if (getenv("GMM_TRACE")) {
+        cudaEventCreate(&g_traceStart);
+        cudaEventRecord(g_traceStart, h->stream);
+    }
+    if (twoLanes) {  // the other lanes start after whatever the handle's stream holds so far (model upload, ...)
+        for (int l = nLanes - 1; l >= 0; --l)
+            if ((rc = h->useLane(l)))
+                return rc;
         GMM_CUDA_TRY(h, cudaEventRecord(h->laneEvent, h->stream));
-        GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->laneStream, h->laneEvent, 0));
+        for (int l = 1; l < nLanes; ++l)
+            GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->parked[l].stream, h->laneEvent, 0));
     }
     uint32_t s0 = 0;
     while (s0 < nSeg && rc == GMM_OK) {
@@ -706,22 +776,31 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
             rc = scoreAlignGroup(h, accumulate, s0, s1, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission,
                                  arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore, &fin[lane], bw);
         if (twoLanes)
-            lane ^= 1;
+            lane = (lane + 1) % nLanes;
         s0 = s1;
     }
-    for (int k = 0; k < 2; ++k) {  // oldest group first; on an error still drain both lanes
-        const int l = twoLanes ? (lane + k) & 1 : k;
+    for (int k = 0; k < nLanes; ++k) {  // oldest group first; on an error still drain every lane
+        const int l = (lane + k) % nLanes;
         if (twoLanes)
             h->useLane(l);
-        if (l == 0 || twoLanes) {
-            const int r = gmm_align_finish(h, fin[l]);
-            if (twoLanes)
-                cudaStreamSynchronize(h->stream);
-            if (rc == GMM_OK)
-                rc = r;
-        }
+        const int r = gmm_align_finish(h, fin[l]);
+        if (twoLanes)
+            cudaStreamSynchronize(h->stream);
+        if (rc == GMM_OK)
+            rc = r;
     }
     h->useLane(0);
+    if (g_traceStart) {
+        for (const TraceMark& m : g_trace) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, g_traceStart, m.ev);
+            fprintf(stderr, "[gmm-timeline] %8.3f ms  lane %d  segment %5d  %s\n", ms, m.lane, m.group, m.what);
+            cudaEventDestroy(m.ev);
+        }
+        g_trace.clear();
+        cudaEventDestroy(g_traceStart);
+        g_traceStart = nullptr;
+    }
     return rc;
 }
 

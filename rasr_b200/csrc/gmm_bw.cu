@@ -429,7 +429,8 @@ int gmm_bw_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, co
     if ((rc = h->reserve(SCR_MISC, off, &base)))
         return rc;
     char* d = (char*)base;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d, hp, tableBytes, cudaMemcpyHostToDevice, h->stream));
+    if ((rc = gmm_copy_tables(h, d, hp, tableBytes)))
+        return rc;
     if ((rc = h->pinnedCopied(PIN_ALIGN)))
         return rc;
     BwParams p;

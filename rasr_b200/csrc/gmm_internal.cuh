@@ -137,20 +137,25 @@ struct gmm_handle {
     // scratch (grown on demand)
     void*  scratch[16]      = {};
     size_t scratchBytes[16] = {};
-    // Second lane of the pipelined host entry points (gmm_score_align_*_host): its own stream and scratch, so that
-    // one group of segments is uploaded and prepared while the previous one is scored and aligned.  useLane() makes a
-    // lane the one `stream` / `scratch` refer to; every kernel launcher keeps using those two names.
-    cudaStream_t laneStream          = nullptr;
-    void*        laneScratch[16]     = {};
-    size_t       laneScratchBytes[16] = {};
+    // Lanes of the pipelined host entry points (gmm_score_align_*_host): each its own stream, scratch and staging, so
+    // that one group of segments is uploaded and prepared while the previous ones are scored and aligned.  useLane()
+    // makes a lane the one `stream` / `scratch` refer to; every kernel launcher keeps using those two names.
+    struct LaneState {  // a parked lane: its stream, scratch set and pinned staging blocks
+        cudaStream_t stream           = nullptr;
+        void*        scratch[16]      = {};
+        size_t       scratchBytes[16] = {};
+        void*        pinned[2]        = {};
+        size_t       pinnedBytes[2]   = {};
+        cudaEvent_t  pinEvent[2]      = {};
+    };
+    static constexpr int kMaxLanes = 4;
+    LaneState    parked[kMaxLanes];          // parked[i] holds lane i's state while another lane is active
     cudaEvent_t  laneEvent           = nullptr;
-    int          lane                = 0;
-    void*        pinned[2]           = {};  // host staging blocks (tables built in place, one copy per launch) ...
+    int          lane                = 0;    // the active lane: `stream`, `scratch`, `pinned`, `pinEvent` are its
+    void*        pinned[2]           = {};   // host staging blocks (tables built in place, one copy per launch)
     size_t       pinnedBytes[2]      = {};
-    void*        lanePinned[2]       = {};  // ... and the second lane's
-    size_t       lanePinnedBytes[2]  = {};
-    cudaEvent_t  pinEvent[2]         = {};  // recorded behind the copy out of a staging block: reservePinned waits
-    cudaEvent_t  lanePinEvent[2]     = {};  // for it before the block is written again
+    cudaEvent_t  pinEvent[2]         = {};   // recorded behind the copy out of a staging block: reservePinned waits
+                                             // for it before the block is written again
     HostPool*    pool                = nullptr;  // host threads of the table builders (hostPool())
     std::vector<std::vector<uint32_t>> workerWords;  // ... and one work space per thread
     struct EmissionStamps {                           // per thread: slot of an emission in the segment being listed,
@@ -178,6 +183,10 @@ enum { SCR_X = 0, SCR_SCORE = 1, SCR_BEST = 2, SCR_Q = 3, SCR_QX = 4, SCR_A = 5,
 struct AlignLists {
     std::vector<uint32_t> emOff, emList, arcSlot, scratch;
 };
+// Tables built in a page-locked block (reservePinned) -> their device copy, by a kernel that reads the block over PCIe
+// instead of a DMA copy: in the pipelined entry points a DMA copy of a few MB would queue behind the other lane's
+// 50 MB feature upload on the host-to-device engine and hold the kernels back for a millisecond.
+int gmm_copy_tables(gmm_handle* h, void* d_dst, const void* pinnedSrc, size_t bytes);
 // gmm_direct.cu
 int gmm_direct_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
 int gmm_direct_posteriors(gmm_handle* h, uint32_t T, const float* d_x, float* d_post);

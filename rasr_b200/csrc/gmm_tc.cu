@@ -1215,7 +1215,8 @@ int gmm_tc_score_subset(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffse
     if ((rc = h->reserve(SCR_VTILES, (size_t)nVt * tm.tileBytes, &vtiles)))
         return rc;
     char* d = (char*)tab;
-    GMM_CUDA_TRY(h, cudaMemcpyAsync(d, pin, total, cudaMemcpyHostToDevice, h->stream));
+    if ((rc = gmm_copy_tables(h, d, pin, total)))
+        return rc;
     if ((rc = h->pinnedCopied(PIN_SUBSET)))
         return rc;
     gather_tiles_kernel<<<(int)std::min<uint32_t>(nVt, (uint32_t)h->smCount * 8), 256, 0, h->stream>>>(

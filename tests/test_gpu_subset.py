@@ -94,7 +94,7 @@ def test_alignment_over_compact_score_blocks(eng, oracle, monkeypatch, align_ker
         out[flag + "n"] = eng.launch_count - n0
     for a, b in zip(out["0"], out["1"]):
         assert np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
-    assert out["1n"] == out["0n"] + 1            # the tile gather is the one extra launch of the compact path
+    assert out["1n"] == out["0n"] + 2            # the compact path adds the tile gather and its table copy
     monkeypatch.delenv("GMM_ALIGN_SUBSET")
     auto = eng.score_align_host(fo, x, au)       # the work estimate picks the compact path here by itself
     assert np.array_equal(auto[0], out["1"][0])
