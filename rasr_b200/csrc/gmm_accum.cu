@@ -54,7 +54,7 @@ struct AccumParams {
 // SUM = 0: maximum scorer (s_k in f64 against the f32-stored best, GaussDiagonalMaximumFeatureScorer.cc:116-142);
 // SUM = 1: sum scorer (s_k = f32(0.5 * (w2 + L + dist)), first minimum, .cc:262-288).
 template<int DP, int SUM>
-__global__ void __launch_bounds__(256) accumulate_kernel(const AccumParams p) {
+__global__ void __launch_bounds__(256, 4) accumulate_kernel(const AccumParams p) {
     const int      lane = threadIdx.x & 31;
     const uint32_t warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), nWarps = gridDim.x * (blockDim.x >> 5);
     const int      D = (int)p.D, eff = D & ~3;
