@@ -316,6 +316,30 @@ def test_cfg2_full_size_quantized(eng, oracle):
     assert np.array_equal(bits(r["score"]), bits(oracle.simd_final_score(q, raw["scaling_squared"])))
 
 
+def test_batches_beyond_one_launch(eng, oracle):
+    """Long batches go out as several L2-sized launches (32768 frames float, 65536 quantized): rows on either side of
+    every launch boundary must be the oracle's, and a frame's result must not depend on where the batch was cut."""
+    ms = synth.make_model(M=260, K=16, D=45, seed=31)
+    T = 70001
+    x = synth.make_features(ms, T, seed=8)
+    tab = tables.float_tables(ms)
+    upload_float(eng, tab, kernel=capi.KERNEL_TENSOR)
+    s, b = eng.score_host(x)
+    rows = np.r_[0:4, 32760:32776, 65530:65544, T - 5:T]
+    so, bo = oracle.score_max(ms, x[rows], tables=(tab["isr"], tab["log_norm"], tab["w2"]))
+    assert_float_close(s[rows], so)
+    s2, b2 = eng.score_host(x[40000:])               # other cut points: 40000 + 32768, ...
+    assert np.array_equal(bits(s2), bits(s[40000:])) and np.array_equal(b2, b[40000:])
+    t, raw = oracle_quant_tables(ms)
+    upload_quant(eng, t)
+    r = eng.quant_score_host(x)
+    rows = np.r_[0:4, 65530:65544, T - 5:T]
+    q, bq = oracle.simd_score(ms.mix_offsets, raw, oracle.simd_quantize_features(x[rows], raw["isrs"]))
+    assert np.array_equal(r["q"][rows], q) and np.array_equal(r["best"][rows], bq)
+    r2 = eng.quant_score_host(x[30000:])
+    assert np.array_equal(r2["q"], r["q"][30000:]) and np.array_equal(r2["best"], r["best"][30000:])
+
+
 @pytest.mark.parametrize("mode", [capi.MODE_MAX, capi.MODE_SUM])
 def test_cfg3_large_model_properties(eng, oracle, mode):
     """12001 x 64: oracle on a frame sample; batch-split invariance and frame-permutation equivariance at T=10k."""
