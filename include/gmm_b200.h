@@ -96,6 +96,30 @@ int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, 
 int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,
                            float* d_score, uint8_t* d_qx, size_t ld);
 
+/* ---- mixture-sharded variant (BASELINE.json configs[4]): scoring with its exchange step --------------------------
+ * Rank r of N holds mixtures [r*Mp, (r+1)*Mp) and scores the same frames as every other rank; afterwards every rank
+ * needs every column.  The reference has no multi-GPU scorer (Mm::FeatureScorer::Scorer::score(e) is answered from
+ * one process' own mixture set, src/Mm/FeatureScorer.hh:71-116); this is the all-gather configs[4] names, done by
+ * the scoring call itself over peer-mapped memory (CUDA IPC; NVLink / NVSwitch), without NCCL or a host barrier.
+ * d_blocks[0..world): every rank's block (own at index rank, the others mapped with gmm_peer_open): score rows
+ * [maxFrames x ld] f32 followed, flagsOffsetBytes (a multiple of 128, >= T*ld*4) behind the start, by 32 flag words
+ * (gmm_peer_alloc zeroes them).  The call (1) tells the peers that this rank's earlier work on the handle's stream
+ * has finished reading its block, (2) scores the shard into columns [colOffset, colOffset + M) of the own block, one
+ * range of B tiles at a time (`chunks` ranges, 1..8; ranges need a model whose mixtures all have the same number of
+ * densities, else one range), and pushes each finished range into the peers' blocks from a second stream while the
+ * next range is being scored, (3) makes the handle's stream wait until every peer's columns have landed.  Work
+ * queued on the stream afterwards sees the complete [T x ld] rows; all ranks must make the same sequence of calls.
+ * Tensor kernel only, T <= 32768.  A peer that does not show up within ~2 s ends the wait and sets flag word 17. */
+int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
+                            void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
+                            uint32_t chunks);
+/* Device memory other processes of the same box can map: allocate (zeroed) + export (ipcHandle: 64 bytes), map,
+ * unmap, free. */
+int gmm_peer_alloc(gmm_handle* h, size_t bytes, void** d_ptr, void* ipcHandle);
+int gmm_peer_open(gmm_handle* h, const void* ipcHandle, void** d_ptr);
+int gmm_peer_close(gmm_handle* h, void* d_ptr);
+int gmm_peer_free(gmm_handle* h, void* d_ptr);
+
 /* ---- subset scoring ---------------------------------------------------------------------------------------------
  * The reference's context scorers evaluate a mixture when a consumer first asks for it (CachedContextScorer::score,
  * src/Mm/FeatureScorer.hh:170-230): an aligner pays for the few hundred emissions of the segment's automaton, not

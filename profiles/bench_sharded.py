@@ -42,6 +42,7 @@ t = torch.tensor([e0.elapsed_time(e1), e1.elapsed_time(e2)], device="cuda", dtyp
 dist.all_reduce(t, op=dist.ReduceOp.MAX)
 # correctness: gathered block equals a single-engine score of a sample of mixtures
 ok = True
+ms_total, ms_kernel = t[0].item() / steps, t[1].item() / steps
 if rank == 0:
     fm = sharded.to_frame_major(g, M)
     from rasr_b200 import capi
@@ -50,12 +51,46 @@ if rank == 0:
     e.upload_float(probe["offsets"], probe["mean"], probe["isr"], probe["cov_idx"], probe["w2"], probe["log_norm"])
     s, _ = e.score_host(x, want_best=False)
     ok = bool(np.allclose(fm[:, M - 7:].cpu().numpy(), s, rtol=1e-4, atol=1e-4))
-    ms_total, ms_kernel = t[0].item() / steps, t[1].item() / steps
     print(json.dumps({"workload": f"mixture-sharded {M}x{K}x45, T={T}", "n_gpus": world, "ms_per_step": ms_total,
                       "ms_kernel": ms_kernel, "ms_all_gather": ms_total - ms_kernel,
                       "frames_per_s": T / (ms_total * 1e-3), "gather_bytes_per_rank": T * mp_ * 4,
                       "gathered_bytes": world * T * mp_ * 4,
                       "allgather_busbw_GBs": (world - 1) * T * mp_ * 4 / max(1e-9, (ms_total - ms_kernel) * 1e-3) / 1e9,
                       "gaussians_per_rank": (m1 - m0) * K, "check": ok}))
+# ---- push variant: column ranges pushed into the peers' blocks while the next range is scored, flags on device ----
+def timed_loop(fn):
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); dist.barrier()
+    ev0.record(stream)
+    for _ in range(steps):
+        fn()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    tt = torch.tensor([ev0.elapsed_time(ev1) / steps], device="cuda", dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    return tt.item()
+
+ref_fm = sharded.to_frame_major(sc.score(dx), M).clone()
+torch.cuda.synchronize()
+out = {"workload": f"mixture-sharded {M}x{K}x45, T={T}, push variant (no NCCL call)", "n_gpus": world,
+       "ms_per_step_all_gather": ms_total}
+for chunks in (1, 2, 4, 8):
+    ps = sharded.PushMixtureShardedScorer(tab, rank, world, dist, local, max_frames=T, chunks=chunks)
+    ps.engine.set_stream(stream.cuda_stream)
+    for _ in range(3):
+        fm = ps.score(dx)
+    ms = timed_loop(lambda: ps.score(dx))
+    fm = ps.score(dx)
+    torch.cuda.synchronize()
+    same = torch.tensor([1.0 if torch.equal(fm[:, :M], ref_fm) and not ps.timed_out() else 0.0], device="cuda")
+    dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    out[f"ms_per_step_push_{chunks}_ranges"] = ms
+    out[f"bit_identical_{chunks}_ranges"] = bool(same.item() == 1.0)
+    ps.close()
+best = min(v for k, v in out.items() if k.startswith("ms_per_step_push"))
+out["frames_per_s_push"] = T / (best * 1e-3)
+out["speedup_over_all_gather"] = ms_total / best
+if rank == 0:
+    print(json.dumps(out))
 dist.barrier()
 dist.destroy_process_group()

@@ -35,6 +35,11 @@ SYMBOLS = [
     ("gmm_baum_welch_device", _i, [_vp, _u32, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     ("gmm_score_baum_welch_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     ("gmm_score_baum_welch_accumulate_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("gmm_score_device_gather", _i, [_vp, _u32, _vp, _u32, _u32, _vp, _sz, _u32, _sz, _u32]),
+    ("gmm_peer_alloc", _i, [_vp, _sz, _vp, _vp]),
+    ("gmm_peer_open", _i, [_vp, _vp, _vp]),
+    ("gmm_peer_close", _i, [_vp, _vp]),
+    ("gmm_peer_free", _i, [_vp, _vp]),
     ("gmm_score_subset_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_score_subset_ld", _u32, [_vp, _u32]),
     ("gmm_align_device", _i, [_vp, _u32, _vp, _vp, _sz] + [_vp] * 10),
@@ -251,6 +256,34 @@ class Engine:
                                                    _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight),
                                                    _ptr(em), _ptr(st), _ptr(sc)), "gmm_score_align_host")
         return em, st, sc
+
+    # -- mixture-sharded variant: scoring with its exchange step -------------------------------------
+    def peer_alloc(self, nbytes: int):
+        """Zeroed device memory other processes of this box can map -> (device pointer, 64-byte IPC handle)."""
+        ptr = C.c_void_p(0)
+        handle = C.create_string_buffer(64)
+        self._check(self._lib.gmm_peer_alloc(self._h, int(nbytes), C.addressof(ptr), C.addressof(handle)),
+                    "gmm_peer_alloc")
+        return int(ptr.value), bytes(handle.raw)
+
+    def peer_open(self, handle: bytes) -> int:
+        ptr = C.c_void_p(0)
+        buf = C.create_string_buffer(handle, 64)
+        self._check(self._lib.gmm_peer_open(self._h, C.addressof(buf), C.addressof(ptr)), "gmm_peer_open")
+        return int(ptr.value)
+
+    def peer_close(self, ptr: int):
+        self._check(self._lib.gmm_peer_close(self._h, int(ptr)), "gmm_peer_close")
+
+    def peer_free(self, ptr: int):
+        self._check(self._lib.gmm_peer_free(self._h, int(ptr)), "gmm_peer_free")
+
+    def score_device_gather(self, T, d_x, rank, blocks, ld, col_offset, flags_offset, chunks=4):
+        """Score the shard into the own block and push its columns into the peers' blocks (stream-ordered)."""
+        arr = (C.c_void_p * len(blocks))(*[int(p) for p in blocks])
+        self._check(self._lib.gmm_score_device_gather(self._h, int(T), _ptr(d_x), int(rank), len(blocks),
+                                                      C.addressof(arr), int(ld), int(col_offset), int(flags_offset),
+                                                      int(chunks)), "gmm_score_device_gather")
 
     # -- Baum-Welch alignment ----------------------------------------------------------------------
     def emission_lists(self, automata, n_emissions):

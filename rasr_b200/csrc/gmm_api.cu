@@ -288,6 +288,12 @@ void gmm_destroy(gmm_handle* h) {
             cudaStreamDestroy(ls.stream);
     }
     delete h->pool;
+    if (h->gatherStream) {
+        cudaStreamDestroy(h->gatherStream);
+        for (int i = 0; i < gmm_handle::kGatherEvents; ++i)
+            if (h->gatherEvent[i])
+                cudaEventDestroy(h->gatherEvent[i]);
+    }
     if (h->laneEvent)
         cudaEventDestroy(h->laneEvent);
     if (h->lda.matrix)
@@ -483,6 +489,74 @@ int gmm_score_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_score
     if (h->kernel == GMM_KERNEL_TENSOR)
         return gmm_tc_score(h, T, d_x, d_scores, d_best, ld);
     return gmm_direct_score(h, T, d_x, d_scores, d_best, ld);
+}
+
+int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
+                            void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
+                            uint32_t chunks) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid || h->kernel != GMM_KERNEL_TENSOR || !h->tensor.valid) {
+        h->setError("gmm_score_device_gather: needs a float model on the tensor kernel");
+        return GMM_ERR_UNSUPPORTED;
+    }
+    if (world == 0 || world > 8 || rank >= world || !d_blocks || flagsOffsetBytes % 128 || (size_t)colOffset + h->M > ld ||
+        flagsOffsetBytes < (size_t)T * ld * 4) {
+        h->setError("gmm_score_device_gather: 1..8 ranks, rank < world, the shard's columns inside ld, flag words "
+                    "128-byte aligned behind the score rows");
+        return GMM_ERR_ARG;
+    }
+    if (T > 32768) {
+        h->setError("gmm_score_device_gather: at most 32768 frames per call (one launch)");
+        return GMM_ERR_ARG;
+    }
+    if (T == 0)
+        return GMM_OK;
+    if (!d_x) {
+        h->setError("gmm_score_device_gather: NULL frames");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return gmm_gather_score(h, T, d_x, rank, world, d_blocks, ld, colOffset, flagsOffsetBytes, chunks);
+}
+
+int gmm_peer_alloc(gmm_handle* h, size_t bytes, void** d_ptr, void* ipcHandle) {
+    if (!h || !d_ptr || !ipcHandle)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    *d_ptr = nullptr;
+    GMM_CUDA_TRY(h, cudaMalloc(d_ptr, bytes ? bytes : 16));
+    GMM_CUDA_TRY(h, cudaMemset(*d_ptr, 0, bytes ? bytes : 16));  // the flag words of a gathered block start at 0
+    cudaIpcMemHandle_t hd;
+    GMM_CUDA_TRY(h, cudaIpcGetMemHandle(&hd, *d_ptr));
+    memcpy(ipcHandle, &hd, sizeof(hd));
+    return GMM_OK;
+}
+
+int gmm_peer_open(gmm_handle* h, const void* ipcHandle, void** d_ptr) {
+    if (!h || !d_ptr || !ipcHandle)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, ipcHandle, sizeof(hd));
+    GMM_CUDA_TRY(h, cudaIpcOpenMemHandle(d_ptr, hd, cudaIpcMemLazyEnablePeerAccess));
+    return GMM_OK;
+}
+
+int gmm_peer_close(gmm_handle* h, void* d_ptr) {
+    if (!h)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    GMM_CUDA_TRY(h, cudaIpcCloseMemHandle(d_ptr));
+    return GMM_OK;
+}
+
+int gmm_peer_free(gmm_handle* h, void* d_ptr) {
+    if (!h)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    GMM_CUDA_TRY(h, cudaFree(d_ptr));
+    return GMM_OK;
 }
 
 int gmm_score_subset_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const uint32_t* listOffsets,

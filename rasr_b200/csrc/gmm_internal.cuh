@@ -156,6 +156,10 @@ struct gmm_handle {
     size_t       pinnedBytes[2]      = {};
     cudaEvent_t  pinEvent[2]         = {};   // recorded behind the copy out of a staging block: reservePinned waits
                                              // for it before the block is written again
+    static constexpr int kGatherEvents = 9;  // mixture-sharded scoring (gmm_gather.cu): push stream, one event per
+    cudaStream_t gatherStream        = nullptr;  // column range + one for the join, epoch of the flag words
+    cudaEvent_t  gatherEvent[kGatherEvents] = {};
+    uint32_t     gatherEpoch         = 0;
     HostPool*    pool                = nullptr;  // host threads of the table builders (hostPool())
     std::vector<std::vector<uint32_t>> workerWords;  // ... and one work space per thread
     struct EmissionStamps {                           // per thread: slot of an emission in the segment being listed,
@@ -244,6 +248,10 @@ int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uin
                   uint8_t* d_qx, size_t ld);
 int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
                 const float* w2, const float* logNorm, bool force);
+int gmm_tc_score_tiles(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, size_t ld, uint32_t tile0,
+                       uint32_t tile1, bool prep);
+int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
+                     void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks);
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
 // scores of a per-segment subset of mixtures: column j of segment s's rows = mixture emList[emOff[s] + j]
 // (host arrays); GMM_ERR_UNSUPPORTED when the model is not regular (the caller scores everything instead)

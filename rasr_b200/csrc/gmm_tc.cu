@@ -937,6 +937,7 @@ struct TcJob {
     float*          scores;
     uint32_t*       best;
     size_t          ld;
+    bool            prep = true;  // false: the frame images of the previous run over the same frames are reused
 };
 
 int tc_run(gmm_handle* h, const TcJob& job) {
@@ -952,7 +953,7 @@ int tc_run(gmm_handle* h, const TcJob& job) {
         return rc;
     if ((rc = h->reserve(SCR_ROW, (size_t)FT * kTileM * 8, &rT)))
         return rc;
-    {
+    if (job.prep) {
         const uint32_t chunks = tm.kSteps * 2;
         const uint32_t lpf    = chunks <= 8 ? 8 : chunks <= 16 ? 16 : 32;
         const uint32_t fpb    = 8 * (32 / lpf);  // frames per 256-thread block
@@ -1070,6 +1071,28 @@ int tc_run(gmm_handle* h, const TcJob& job) {
 }
 
 }  // namespace
+
+// B tiles [tile0, tile1) of the model over one launch worth of frames (gmm_gather.cu scores a shard one column range
+// at a time); prep = false reuses the frame images the previous call over the same frames left in the scratch.
+int gmm_tc_score_tiles(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, size_t ld, uint32_t tile0,
+                       uint32_t tile1, bool prep) {
+    if (T == 0 || tile1 <= tile0)
+        return GMM_OK;
+    TcJob job;
+    job.T       = T;
+    job.FT      = (T + kTileM - 1) / kTileM;
+    job.d_x     = d_x;
+    job.rowMap  = nullptr;
+    job.bTiles  = h->tensor.bTiles + (size_t)tile0 * h->tensor.tileBytes;
+    job.nTiles  = tile1 - tile0;
+    job.itemTab = nullptr;
+    job.nItems  = 0;
+    job.scores  = d_scores;
+    job.best    = nullptr;
+    job.ld      = ld;
+    job.prep    = prep;
+    return tc_run(h, job);
+}
 
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld) {
     // Long batches go out as launches of at most kChunk frames: the A tiles of one launch (256 bytes per frame) and

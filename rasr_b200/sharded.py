@@ -15,6 +15,11 @@
   /root/reference/src/Mm/AbstractMixtureSetEstimator.cc:149-169); here it is one ``all_reduce`` over the packed
   f64 block on the device (``all_reduce_accumulators``).
 
+* Push variant of mixture sharding (``PushMixtureShardedScorer``): no collective call at all -- each rank pushes its
+  finished column ranges into every rank's frame-major block ``[T][N*Mp]`` through peer-mapped memory while it
+  scores the next range, and the ranks synchronise through flag words on the device (include/gmm_b200.h
+  gmm_score_device_gather); torch.distributed only exchanges the IPC handles.
+
 torch.distributed is plumbing only; the scores come from the C-ABI engine (rasr_b200.capi).
 """
 from __future__ import annotations
@@ -115,6 +120,78 @@ class MixtureShardedScorer:
         if not self._bound:
             self.engine.sync()  # the engine's own stream is not the one the collective runs on
         return all_gather_scores(self._local, self.dist, self.world)
+
+
+class _DeviceBlock:
+    """A device allocation of the engine seen as a CUDA array (torch.as_tensor takes it without a copy)."""
+
+    def __init__(self, ptr: int, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 3}
+
+
+class PushMixtureShardedScorer:
+    """Mixture-sharded float scorer whose exchange step runs inside the scoring call, without NCCL and without a
+    host barrier: every rank scores its shard into its own frame-major block [T][N*Mp], one range of B tiles at a
+    time, and a push kernel on a second stream copies each finished column range into the peers' blocks (mapped
+    through CUDA IPC; full-line stores over NVLink / NVSwitch) while the tensor kernel scores the next range.  The
+    ranks synchronise on the device through flag words behind the score rows (include/gmm_b200.h
+    gmm_score_device_gather); torch.distributed only carries the IPC handles at set-up."""
+
+    FLAG_WORDS = 32
+
+    def __init__(self, float_tables: dict, rank: int, world: int, dist, device: int, max_frames: int, mode=0,
+                 chunks: int = 4):
+        import torch
+        from . import capi
+        if world > 8:
+            raise ValueError("at most 8 ranks")
+        self.M = int(len(float_tables["offsets"]) - 1)
+        self.rank, self.world, self.dist = rank, world, dist
+        self.Mp = shard_width(self.M, world)
+        self.ld = self.Mp * world
+        self.m0, self.m1 = mixture_range(self.M, rank, world)
+        if self.m1 <= self.m0:
+            raise ValueError("a rank without mixtures: use fewer ranks")
+        sub = shard_float_tables(float_tables, self.m0, self.m1)
+        self.engine = capi.Engine(device)
+        self.engine.upload_float(sub["offsets"], sub["mean"], sub["isr"], sub["cov_idx"], sub["w2"], sub["log_norm"],
+                                 mode=mode, kernel=capi.KERNEL_TENSOR)
+        self.max_frames, self.chunks = int(max_frames), int(chunks)
+        self.flags_offset = (self.max_frames * self.ld * 4 + 127) // 128 * 128
+        self._own, handle = self.engine.peer_alloc(self.flags_offset + self.FLAG_WORDS * 4)
+        handles = [None] * world
+        dist.all_gather_object(handles, handle)
+        self._bases = [self._own if r == rank else self.engine.peer_open(handles[r]) for r in range(world)]
+        dev = f"cuda:{device}"
+        self.block = torch.as_tensor(_DeviceBlock(self._own, (self.max_frames, self.ld)), device=dev)
+        self.flags = torch.as_tensor(_DeviceBlock(self._own + self.flags_offset, (self.FLAG_WORDS,)),
+                                     device=dev).view(torch.int32)
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def score(self, d_x):
+        """d_x: CUDA tensor [T, D] (identical on every rank) -> frame-major [T][N*Mp] view of this rank's block,
+        complete for work queued on the engine's stream after the call."""
+        T = d_x.shape[0]
+        if T > self.max_frames:
+            raise ValueError("more frames than the gathered block holds")
+        self.engine.score_device_gather(T, d_x, self.rank, self._bases, self.ld, self.rank * self.Mp,
+                                        self.flags_offset, self.chunks)
+        return self.block[:T]
+
+    def timed_out(self) -> bool:
+        """A peer did not show up within the device-side limit (call after a sync)."""
+        return bool(self.flags[17].item() != 0)
+
+    def close(self):
+        self.engine.sync()
+        self.dist.barrier()
+        for r, b in enumerate(self._bases):
+            if r != self.rank:
+                self.engine.peer_close(b)
+        self.dist.barrier()
+        self.engine.peer_free(self._own)
+        self.engine.close()
 
 
 # ---- training pass: combine the ranks' estimators ----------------------------------------------------------

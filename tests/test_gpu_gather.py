@@ -1,0 +1,84 @@
+"""GPU: the mixture-sharded scoring call with its exchange step (gmm_score_device_gather).  On one GPU it runs with
+world = 1 (the shard scored one range of B tiles at a time into a block the library allocated) and must give the very
+bits of gmm_score_device; with two GPUs visible, two processes push their columns into each other's blocks and every
+rank must hold the frame-major scores of the whole model (profiles/bench_sharded.py measures the same path)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from rasr_b200 import capi, sharded, synth, tables
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def upload(eng, ms, mode=capi.MODE_MAX):
+    t = tables.float_tables(ms)
+    eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=mode,
+                     kernel=capi.KERNEL_TENSOR)
+
+
+@pytest.mark.parametrize("M,K,D,ragged,mode,chunks", [(4501, 16, 45, False, capi.MODE_MAX, 4), (4501, 16, 45, False, capi.MODE_MAX, 8),
+                                                      (300, 8, 20, False, capi.MODE_SUM, 3), (97, 5, 12, True, capi.MODE_MAX, 4),
+                                                      (33, 64, 45, False, capi.MODE_MAX, 1)])
+def test_ranges_of_tiles_equal_one_pass(M, K, D, ragged, mode, chunks):
+    ms = synth.make_model(M=M, K=K, D=D, seed=M + K, ragged=ragged)
+    T = 1000
+    x = synth.make_features(ms, T, seed=5)
+    eng = capi.Engine(0)
+    try:
+        upload(eng, ms, mode)
+        dx = torch.from_numpy(x).cuda()
+        full = torch.empty((T, M), device="cuda")
+        eng.score_device(T, dx, full)
+        col, ld = 8, M + 24  # the shard's columns sit inside a wider row
+        flags_offset = (T * ld * 4 + 127) // 128 * 128
+        base, _ = eng.peer_alloc(flags_offset + 128)
+        block = torch.as_tensor(sharded._DeviceBlock(base, (T, ld)), device="cuda:0")
+        n0 = eng.launch_count
+        eng.score_device_gather(T, dx, 0, [base], ld, col, flags_offset, chunks)
+        eng.sync()
+        assert eng.launch_count > n0
+        got = block[:, col:col + M]
+        assert torch.equal(got.view(torch.int32), full.view(torch.int32))
+        assert float(block[:, :col].abs().max()) == 0.0 and float(block[:, col + M:].abs().max()) == 0.0
+        del block, got
+        eng.peer_free(base)
+    finally:
+        eng.close()
+
+
+def test_gather_rejects_bad_arguments():
+    ms = synth.make_model(M=40, K=4, D=10, seed=1)
+    eng = capi.Engine(0)
+    try:
+        upload(eng, ms)
+        dx = torch.zeros((8, 10), device="cuda")
+        base, _ = eng.peer_alloc(8 * 64 * 4 + 128)
+        with pytest.raises(capi.GmmError):  # the shard's columns do not fit in ld
+            eng.score_device_gather(8, dx, 0, [base], 32, 0, 8 * 32 * 4, 1)
+        with pytest.raises(capi.GmmError):  # flag words inside the score rows
+            eng.score_device_gather(8, dx, 0, [base], 64, 0, 128, 1)
+        with pytest.raises(capi.GmmError):  # rank outside the world
+            eng.score_device_gather(8, dx, 1, [base], 64, 0, 8 * 64 * 4, 1)
+        eng.peer_free(base)
+    finally:
+        eng.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_ranks_push_into_each_other():
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "profiles", "bench_sharded.py"), "2048", "16", "640", "3"]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    import json
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    push = [l for l in lines if "push variant" in l["workload"]][0]
+    for c in (1, 2, 4, 8):
+        assert push[f"bit_identical_{c}_ranges"] is True
