@@ -15,6 +15,7 @@
 #include "gmm_internal.cuh"
 
 #include <algorithm>
+#include <type_traits>
 #include <cstdlib>
 
 namespace {
@@ -60,8 +61,40 @@ __global__ void gather_signal_ready(GatherPeers peers, uint32_t rank, uint32_t w
 }
 
 // Copy columns [col0, col1) of rows [0, T) of the own block into the same place of every peer's block.
-// VEC = floats per access (4 when the range and ld are 16-byte aligned).
-template<int VEC>
+// VEC = floats per access (4 when the range and ld are 16-byte aligned).  A thread reads kUnroll accesses (the own
+// block is an L2 hit for short calls, HBM for long ones: several loads in flight per thread) and stores each of them
+// to all peers in turn, so the source is read once and consecutive stores leave on different links.
+template<int VEC, int kUnroll, typename IDX>
+__device__ __forceinline__ void push_range(const GatherPeers& peers, uint32_t rank, uint32_t world, IDX total, uint32_t w,
+                                           size_t ld, uint32_t col0) {
+    typedef typename std::conditional<VEC == 4, float4, float>::type V;
+    const float* src    = peers.block[rank];
+    const IDX    stride = (IDX)gridDim.x * blockDim.x;
+    for (IDX i0 = (IDX)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += stride * kUnroll) {
+        V      v[kUnroll];
+        size_t off[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const IDX i = i0 + (IDX)u * stride;
+            if (i < total) {
+                const IDX row = i / w, c = i - row * w;
+                off[u]        = (size_t)row * ld + col0 + (size_t)c * VEC;
+                v[u]          = *reinterpret_cast<const V*>(src + off[u]);
+            }
+        }
+        for (uint32_t k = 1; k < world; ++k) {
+            uint32_t r = rank + k;
+            r          = r >= world ? r - world : r;
+            float* dst = peers.block[r];
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u)
+                if (i0 + (IDX)u * stride < total)
+                    *reinterpret_cast<V*>(dst + off[u]) = v[u];
+        }
+    }
+}
+
+template<int VEC, int kUnroll>
 __global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t T,
                                                           size_t ld, uint32_t col0, uint32_t col1, uint32_t epoch,
                                                           int last) {
@@ -77,20 +110,10 @@ __global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uin
     if (ok) {
         const uint32_t w     = (col1 - col0) / VEC;  // accesses per row
         const size_t   total = (size_t)T * w;
-        const float*   src   = peers.block[rank];
-        for (uint32_t k = 1; k < world; ++k) {
-            // CTAs start on different peers so that all links carry data from the first pass on
-            const uint32_t r   = (rank + 1 + (k - 1 + blockIdx.x) % (world - 1)) % world;
-            float*         dst = peers.block[r];
-            for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-                const size_t row = i / w, c = i - row * w;
-                const size_t off = row * ld + col0 + c * VEC;
-                if (VEC == 4)
-                    *reinterpret_cast<float4*>(dst + off) = *reinterpret_cast<const float4*>(src + off);
-                else
-                    dst[off] = src[off];
-            }
-        }
+        if (total + (size_t)gridDim.x * blockDim.x * kUnroll <= 0xFFFFFFFFull)
+            push_range<VEC, kUnroll, uint32_t>(peers, rank, world, (uint32_t)total, w, ld, col0);
+        else
+            push_range<VEC, kUnroll, size_t>(peers, rank, world, total, w, ld, col0);
     }
     if (!last)
         return;
@@ -141,6 +164,9 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
     chunks = std::min<uint32_t>(std::min<uint32_t>(chunks, gmm_handle::kGatherEvents - 1), std::max(1u, tm.nTiles));
     static const int pushCtas = getenv("GMM_GATHER_CTAS") ? std::max(1, atoi(getenv("GMM_GATHER_CTAS"))) : 64;
 
+    static const int unrollEnv = getenv("GMM_GATHER_UNROLL") ? atoi(getenv("GMM_GATHER_UNROLL")) : 0;
+    const int        unroll    = unrollEnv ? unrollEnv : 4;
+
     gather_signal_ready<<<1, 32, 0, h->stream>>>(peers, rank, world, epoch);
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
@@ -158,10 +184,19 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             for (uint32_t r = 0; r < world && vec; ++r)
                 vec = reinterpret_cast<uintptr_t>(peers.block[r]) % 16 == 0;
             const int last = c + 1 == chunks;
-            if (vec)
-                gather_push_kernel<4><<<pushCtas, 256, 0, h->gatherStream>>>(peers, rank, world, T, ld, col0, col1, epoch, last);
+#define GMM_PUSH(V, U) \
+    gather_push_kernel<V, U><<<pushCtas, 256, 0, h->gatherStream>>>(peers, rank, world, T, ld, col0, col1, epoch, last)
+            if (vec) {
+                if (unroll == 1)
+                    GMM_PUSH(4, 1);
+                else if (unroll == 2)
+                    GMM_PUSH(4, 2);
+                else
+                    GMM_PUSH(4, 4);
+            }
             else
-                gather_push_kernel<1><<<pushCtas, 256, 0, h->gatherStream>>>(peers, rank, world, T, ld, col0, col1, epoch, last);
+                GMM_PUSH(1, 1);
+#undef GMM_PUSH
             h->launches++;
             GMM_CUDA_TRY(h, cudaGetLastError());
         }
