@@ -162,10 +162,12 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
     if (!tm.regular || chunks == 0)
         chunks = 1;
     chunks = std::min<uint32_t>(std::min<uint32_t>(chunks, gmm_handle::kGatherEvents - 1), std::max(1u, tm.nTiles));
-    static const int pushCtas = getenv("GMM_GATHER_CTAS") ? std::max(1, atoi(getenv("GMM_GATHER_CTAS"))) : 64;
+    static const int pushCtas = getenv("GMM_GATHER_CTAS") ? std::max(1, atoi(getenv("GMM_GATHER_CTAS"))) : 128;
 
     static const int unrollEnv = getenv("GMM_GATHER_UNROLL") ? atoi(getenv("GMM_GATHER_UNROLL")) : 0;
-    const int        unroll    = unrollEnv ? unrollEnv : 4;
+    // measured at N=2 (profiles/sweep_push_n2_*_r01.txt): one load in flight per thread and 128 CTAs disturb the tensor
+    // kernel running beside the push least (T=8192, 8 ranges: 0.951 ms; four loads in flight: 1.065 ms)
+    const int        unroll    = unrollEnv ? unrollEnv : 1;
 
     gather_signal_ready<<<1, 32, 0, h->stream>>>(peers, rank, world, epoch);
     h->launches++;
