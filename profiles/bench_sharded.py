@@ -75,7 +75,8 @@ torch.cuda.synchronize()
 out = {"workload": f"mixture-sharded {M}x{K}x45, T={T}, push variant (no NCCL call)", "n_gpus": world,
        "ms_per_step_all_gather": ms_total}
 for chunks in (1, 2, 4, 8):
-    ps = sharded.PushMixtureShardedScorer(tab, rank, world, dist, local, max_frames=T, chunks=chunks)
+    ps = sharded.PushMixtureShardedScorer(tab, rank, world, dist, local, max_frames=T, chunks=chunks,
+                                          row_pad=int(os.environ.get("PUSH_ROW_PAD", "0")))
     ps.engine.set_stream(stream.cuda_stream)
     for _ in range(3):
         fm = ps.score(dx)

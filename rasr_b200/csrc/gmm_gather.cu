@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <type_traits>
 #include <cstdlib>
+#include <cstring>
 
 namespace {
 
@@ -60,13 +61,13 @@ __global__ void gather_signal_ready(GatherPeers peers, uint32_t rank, uint32_t w
         st_release_sys(peers.flags[r] + kFlagReady + rank, epoch);
 }
 
-// Copy columns [col0, col1) of rows [0, T) of the own block into the same place of every peer's block.
+// Copy columns [col0, col1) of rows [row0, row0 + T) of the own block into the same place of every peer's block.
 // VEC = floats per access (4 when the range and ld are 16-byte aligned).  A thread reads kUnroll accesses (the own
 // block is an L2 hit for short calls, HBM for long ones: several loads in flight per thread) and stores each of them
 // to all peers in turn, so the source is read once and consecutive stores leave on different links.
 template<int VEC, int kUnroll, typename IDX>
 __device__ __forceinline__ void push_range(const GatherPeers& peers, uint32_t rank, uint32_t world, IDX total, uint32_t w,
-                                           size_t ld, uint32_t col0) {
+                                           size_t ld, uint32_t col0, uint32_t row0) {
     typedef typename std::conditional<VEC == 4, float4, float>::type V;
     const float* src    = peers.block[rank];
     const IDX    stride = (IDX)gridDim.x * blockDim.x;
@@ -78,7 +79,7 @@ __device__ __forceinline__ void push_range(const GatherPeers& peers, uint32_t ra
             const IDX i = i0 + (IDX)u * stride;
             if (i < total) {
                 const IDX row = i / w, c = i - row * w;
-                off[u]        = (size_t)row * ld + col0 + (size_t)c * VEC;
+                off[u]        = ((size_t)row0 + row) * ld + col0 + (size_t)c * VEC;
                 v[u]          = *reinterpret_cast<const V*>(src + off[u]);
             }
         }
@@ -95,9 +96,9 @@ __device__ __forceinline__ void push_range(const GatherPeers& peers, uint32_t ra
 }
 
 template<int VEC, int kUnroll>
-__global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t T,
-                                                          size_t ld, uint32_t col0, uint32_t col1, uint32_t epoch,
-                                                          int last) {
+__global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t row0,
+                                                          uint32_t T, size_t ld, uint32_t col0, uint32_t col1,
+                                                          uint32_t epoch, int last) {
     uint32_t* own = peers.flags[rank];
     __shared__ int ok;
     if (threadIdx.x == 0)
@@ -111,9 +112,9 @@ __global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uin
         const uint32_t w     = (col1 - col0) / VEC;  // accesses per row
         const size_t   total = (size_t)T * w;
         if (total + (size_t)gridDim.x * blockDim.x * kUnroll <= 0xFFFFFFFFull)
-            push_range<VEC, kUnroll, uint32_t>(peers, rank, world, (uint32_t)total, w, ld, col0);
+            push_range<VEC, kUnroll, uint32_t>(peers, rank, world, (uint32_t)total, w, ld, col0, row0);
         else
-            push_range<VEC, kUnroll, size_t>(peers, rank, world, total, w, ld, col0);
+            push_range<VEC, kUnroll, size_t>(peers, rank, world, total, w, ld, col0, row0);
     }
     if (!last)
         return;
@@ -158,10 +159,24 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
     }
     const uint32_t epoch = ++h->gatherEpoch;
     float*         own   = peers.block[rank] + colOffset;
-    // column ranges follow whole B tiles; only a regular model has its tiles at known columns
-    if (!tm.regular || chunks == 0)
+    // The exchange is overlapped range by range.  Short calls are cut into column ranges (whole B tiles over all the
+    // frames; only a regular model has its tiles at known columns), long ones into frame ranges (whole 128-row tiles
+    // over all the columns): the pushes of a frame range are long contiguous row pieces, which matters with seven
+    // peers -- 8192 frames at N=8 in 8 column ranges of 4 KB row pieces took 7.4 ms, in one range 3.7 ms
+    // (profiles/sweep_push_n8_T8192_r01.txt) -- while a frame range of fewer than ~1024 frames starves the tensor
+    // kernel (the model's B tiles are re-read for every range).
+    constexpr uint32_t kTileRows = 128;
+    const uint32_t     FT        = (T + kTileRows - 1) / kTileRows;
+    static const char* splitEnv  = getenv("GMM_GATHER_SPLIT");
+    if (chunks == 0)
         chunks = 1;
-    chunks = std::min<uint32_t>(std::min<uint32_t>(chunks, gmm_handle::kGatherEvents - 1), std::max(1u, tm.nTiles));
+    chunks = std::min<uint32_t>(chunks, gmm_handle::kGatherEvents - 1);
+    bool byFrames = T / chunks >= 1024;
+    if (splitEnv)
+        byFrames = !strcmp(splitEnv, "frames");
+    if (!byFrames && !tm.regular)
+        chunks = 1;
+    chunks = std::min<uint32_t>(chunks, byFrames ? FT : std::max(1u, tm.nTiles));
     static const int pushCtas = getenv("GMM_GATHER_CTAS") ? std::max(1, atoi(getenv("GMM_GATHER_CTAS"))) : 128;
 
     static const int unrollEnv = getenv("GMM_GATHER_UNROLL") ? atoi(getenv("GMM_GATHER_UNROLL")) : 0;
@@ -173,12 +188,27 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
     for (uint32_t c = 0; c < chunks; ++c) {
-        const uint32_t t0 = (uint32_t)((uint64_t)tm.nTiles * c / chunks), t1 = (uint32_t)((uint64_t)tm.nTiles * (c + 1) / chunks);
-        const int      rc = gmm_tc_score_tiles(h, T, d_x, own, ld, t0, t1, c == 0);
+        uint32_t row0 = 0, rows = T, col0 = colOffset, col1 = colOffset + h->M;
+        int      rc;
+        if (byFrames) {
+            row0 = (uint32_t)((uint64_t)FT * c / chunks) * kTileRows;
+            rows = std::min<uint32_t>(T, (uint32_t)((uint64_t)FT * (c + 1) / chunks) * kTileRows) - row0;
+            // all frames are prepared by the first range's call: with a preparation kernel between the ranges the
+            // push CTAs settle on the SMs first and the next range's scoring CTAs (all of an SM's shared memory)
+            // wait for them -- measured: no overlap at all
+            rc = gmm_tc_score_tiles(h, rows, c == 0 ? d_x : d_x + (size_t)row0 * h->D, own + (size_t)row0 * ld, ld, 0,
+                                    tm.nTiles, c == 0, c == 0 ? T : 0, row0 / kTileRows);
+        }
+        else {
+            const uint32_t t0 = (uint32_t)((uint64_t)tm.nTiles * c / chunks), t1 = (uint32_t)((uint64_t)tm.nTiles * (c + 1) / chunks);
+            rc = gmm_tc_score_tiles(h, T, d_x, own, ld, t0, t1, c == 0);
+            if (chunks > 1) {
+                col0 = colOffset + t0 * tm.mixPerTile;
+                col1 = t1 == tm.nTiles ? colOffset + h->M : colOffset + t1 * tm.mixPerTile;
+            }
+        }
         if (rc)
             return rc;
-        const uint32_t col0 = colOffset + (chunks == 1 ? 0u : t0 * tm.mixPerTile);
-        const uint32_t col1 = colOffset + (chunks == 1 || t1 == tm.nTiles ? h->M : t1 * tm.mixPerTile);
         if (world > 1) {
             GMM_CUDA_TRY(h, cudaEventRecord(h->gatherEvent[c], h->stream));
             GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->gatherStream, h->gatherEvent[c], 0));
@@ -186,8 +216,9 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             for (uint32_t r = 0; r < world && vec; ++r)
                 vec = reinterpret_cast<uintptr_t>(peers.block[r]) % 16 == 0;
             const int last = c + 1 == chunks;
-#define GMM_PUSH(V, U) \
-    gather_push_kernel<V, U><<<pushCtas, 256, 0, h->gatherStream>>>(peers, rank, world, T, ld, col0, col1, epoch, last)
+#define GMM_PUSH(V, U)                                                                                             \
+    gather_push_kernel<V, U><<<pushCtas, 256, 0, h->gatherStream>>>(peers, rank, world, row0, rows, ld, col0, col1, \
+                                                                    epoch, last)
             if (vec) {
                 if (unroll == 1)
                     GMM_PUSH(4, 1);

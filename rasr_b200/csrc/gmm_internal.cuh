@@ -249,7 +249,7 @@ int gmm_qtc_score(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uin
 int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const float* isr, const uint32_t* covIdx,
                 const float* w2, const float* logNorm, bool force);
 int gmm_tc_score_tiles(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, size_t ld, uint32_t tile0,
-                       uint32_t tile1, bool prep);
+                       uint32_t tile1, bool prep, uint32_t prepFrames = 0, uint32_t frameTile0 = 0);
 int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
                      void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks);
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);

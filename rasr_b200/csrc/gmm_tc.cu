@@ -938,6 +938,8 @@ struct TcJob {
     uint32_t*       best;
     size_t          ld;
     bool            prep = true;  // false: the frame images of the previous run over the same frames are reused
+    uint32_t        prepT = 0;    // prep: frames to prepare from d_x on (0: T); the run itself may cover fewer
+    uint32_t        aTile0 = 0;   // first frame tile of the run among the prepared ones
 };
 
 int tc_run(gmm_handle* h, const TcJob& job) {
@@ -949,11 +951,15 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     const size_t       ld       = job.ld;
     void *         aT = nullptr, *rT = nullptr;
     int            rc;
-    if ((rc = h->reserve(SCR_A, (size_t)FT * tm.aTileBytes, &aT)))
+    const uint32_t prepT  = job.prepT ? job.prepT : T;
+    const uint32_t prepFT = job.prepT ? (job.prepT + kTileM - 1) / kTileM : FT;
+    const uint32_t holdFT = std::max(job.aTile0 + FT, job.prep ? prepFT : 0u);
+    if ((rc = h->reserve(SCR_A, (size_t)holdFT * tm.aTileBytes, &aT)))
         return rc;
-    if ((rc = h->reserve(SCR_ROW, (size_t)FT * kTileM * 8, &rT)))
+    if ((rc = h->reserve(SCR_ROW, (size_t)holdFT * kTileM * 8, &rT)))
         return rc;
     if (job.prep) {
+        const uint32_t T = prepT, FT = prepFT;  // the preparation may run ahead of the frames scored below
         const uint32_t chunks = tm.kSteps * 2;
         const uint32_t lpf    = chunks <= 8 ? 8 : chunks <= 16 ? 16 : 32;
         const uint32_t fpb    = 8 * (32 / lpf);  // frames per 256-thread block
@@ -985,8 +991,8 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     p.bTiles     = job.bTiles;
     p.itemTab    = job.itemTab;
     p.nItems     = job.nItems;
-    p.aTiles     = (const uint8_t*)aT;
-    p.rowInfo    = (const float2*)rT;
+    p.aTiles     = (const uint8_t*)aT + (size_t)job.aTile0 * tm.aTileBytes;
+    p.rowInfo    = (const float2*)rT + (size_t)job.aTile0 * kTileM;
     p.scores     = d_scores;
     p.best       = d_best;
     p.ld         = ld;
@@ -1073,9 +1079,11 @@ int tc_run(gmm_handle* h, const TcJob& job) {
 }  // namespace
 
 // B tiles [tile0, tile1) of the model over one launch worth of frames (gmm_gather.cu scores a shard one column range
-// at a time); prep = false reuses the frame images the previous call over the same frames left in the scratch.
+// at a time); prep = false reuses the frame images an earlier call left in the scratch.  A call over a range of
+// frames passes the range's frames as d_x / T / d_scores and names its first frame tile among the prepared ones
+// (frameTile0); the preparing call passes the start of ALL frames as d_x and their number as prepFrames.
 int gmm_tc_score_tiles(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, size_t ld, uint32_t tile0,
-                       uint32_t tile1, bool prep) {
+                       uint32_t tile1, bool prep, uint32_t prepFrames, uint32_t frameTile0) {
     if (T == 0 || tile1 <= tile0)
         return GMM_OK;
     TcJob job;
@@ -1091,6 +1099,8 @@ int gmm_tc_score_tiles(gmm_handle* h, uint32_t T, const float* d_x, float* d_sco
     job.best    = nullptr;
     job.ld      = ld;
     job.prep    = prep;
+    job.prepT   = prepFrames;
+    job.aTile0  = frameTile0;
     return tc_run(h, job);
 }
 

@@ -140,7 +140,7 @@ class PushMixtureShardedScorer:
     FLAG_WORDS = 32
 
     def __init__(self, float_tables: dict, rank: int, world: int, dist, device: int, max_frames: int, mode=0,
-                 chunks: int = 4):
+                 chunks: int = 4, row_pad: int = 0):
         import torch
         from . import capi
         if world > 8:
@@ -148,7 +148,7 @@ class PushMixtureShardedScorer:
         self.M = int(len(float_tables["offsets"]) - 1)
         self.rank, self.world, self.dist = rank, world, dist
         self.Mp = shard_width(self.M, world)
-        self.ld = self.Mp * world
+        self.ld = self.Mp * world + int(row_pad)  # row_pad floats behind every row (a row stride off the power of two)
         self.m0, self.m1 = mixture_range(self.M, rank, world)
         if self.m1 <= self.m0:
             raise ValueError("a rank without mixtures: use fewer ranks")

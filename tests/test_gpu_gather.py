@@ -22,12 +22,13 @@ def upload(eng, ms, mode=capi.MODE_MAX):
                      kernel=capi.KERNEL_TENSOR)
 
 
-@pytest.mark.parametrize("M,K,D,ragged,mode,chunks", [(4501, 16, 45, False, capi.MODE_MAX, 4), (4501, 16, 45, False, capi.MODE_MAX, 8),
-                                                      (300, 8, 20, False, capi.MODE_SUM, 3), (97, 5, 12, True, capi.MODE_MAX, 4),
-                                                      (33, 64, 45, False, capi.MODE_MAX, 1)])
-def test_ranges_of_tiles_equal_one_pass(M, K, D, ragged, mode, chunks):
+# T / chunks >= 1024 frames: the call is cut into frame ranges, else into column ranges (gmm_gather.cu)
+@pytest.mark.parametrize("M,K,D,ragged,mode,chunks,T", [(4501, 16, 45, False, capi.MODE_MAX, 4, 1000), (4501, 16, 45, False, capi.MODE_MAX, 8, 1000),
+                                                        (300, 8, 20, False, capi.MODE_SUM, 3, 1000), (97, 5, 12, True, capi.MODE_MAX, 4, 1000),
+                                                        (33, 64, 45, False, capi.MODE_MAX, 1, 1000), (300, 8, 20, False, capi.MODE_MAX, 2, 2500),
+                                                        (97, 5, 12, True, capi.MODE_SUM, 3, 3333)])
+def test_ranges_equal_one_pass(M, K, D, ragged, mode, chunks, T):
     ms = synth.make_model(M=M, K=K, D=D, seed=M + K, ragged=ragged)
-    T = 1000
     x = synth.make_features(ms, T, seed=5)
     eng = capi.Engine(0)
     try:
