@@ -105,9 +105,9 @@ int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t*
  * [maxFrames x ld] f32 followed, flagsOffsetBytes (a multiple of 128, >= T*ld*4) behind the start, by 32 flag words
  * (gmm_peer_alloc zeroes them).  The call (1) tells the peers that this rank's earlier work on the handle's stream
  * has finished reading its block, (2) scores the shard into columns [colOffset, colOffset + M) of the own block, one
- * range of B tiles at a time (`chunks` ranges, 1..8; ranges need a model whose mixtures all have the same number of
- * densities, else one range), and pushes each finished range into the peers' blocks from a second stream while the
- * next range is being scored, (3) makes the handle's stream wait until every peer's columns have landed.  Work
+ * range at a time (`chunks` ranges, 1..8: frame ranges when a range has at least 1024 frames, else ranges of B tiles
+ * = columns, which need a model whose mixtures all have the same number of densities, else one range), and pushes
+ * each finished range into the peers' blocks from a second stream while the next range is being scored, (3) makes the handle's stream wait until every peer's columns have landed.  Work
  * queued on the stream afterwards sees the complete [T x ld] rows; all ranks must make the same sequence of calls.
  * Tensor kernel only, T <= 32768.  A peer that does not show up within ~2 s ends the wait and sets flag word 17. */
 int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
