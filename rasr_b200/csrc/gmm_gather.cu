@@ -1,6 +1,6 @@
 // Mixture-sharded scoring with its exchange step: every rank scores its own mixtures into its own frame-major block
 // [T][ld] and PUSHES those columns into the peers' blocks (mapped through CUDA IPC) with full-line stores over
-// NVLink, one column range at a time while the tensor kernel is already scoring the next range.  The ranks
+// NVLink, one range (of columns or of frames) at a time while the tensor kernel is already scoring the next.  The ranks
 // synchronise on the device through flag words in the blocks themselves; there is no host barrier and no NCCL call.
 //
 // Replaces the all-gather of per-frame score columns of BASELINE.json configs[4] (the reference has no multi-GPU
