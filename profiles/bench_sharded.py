@@ -88,6 +88,24 @@ for chunks in (1, 2, 4, 8):
     out[f"ms_per_step_push_{chunks}_ranges"] = ms
     out[f"bit_identical_{chunks}_ranges"] = bool(same.item() == 1.0)
     ps.close()
+# ---- scores consumed on the HOST: every rank copies its own [T][Mp] columns to its own pinned block
+# over its own PCIe link, against exchanging first and copying the whole [T][N*Mp] block from one GPU ----
+own_host = torch.empty((T, sc.Mp), dtype=torch.float32, pin_memory=True)
+def score_and_copy_own():
+    sc.engine.score_device(T, dx, sc._local, None, ld=sc.Mp)
+    own_host.copy_(sc._local.view(T, sc.Mp), non_blocking=True)
+for _ in range(2):
+    score_and_copy_own()
+out["ms_per_step_host_consumed_own_columns_d2h"] = timed_loop(score_and_copy_own)
+ps = sharded.PushMixtureShardedScorer(tab, rank, world, dist, local, max_frames=T, chunks=4)
+ps.engine.set_stream(stream.cuda_stream)
+all_host = torch.empty((T, ps.ld), dtype=torch.float32, pin_memory=True)
+def exchange_and_copy_all():
+    all_host.copy_(ps.score(dx), non_blocking=True)
+for _ in range(2):
+    exchange_and_copy_all()
+out["ms_per_step_host_consumed_exchange_then_d2h_all"] = timed_loop(exchange_and_copy_all)
+ps.close()
 best = min(v for k, v in out.items() if k.startswith("ms_per_step_push"))
 out["frames_per_s_push"] = T / (best * 1e-3)
 out["speedup_over_all_gather"] = ms_total / best
