@@ -109,7 +109,8 @@ int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t*
  * = columns, which need a model whose mixtures all have the same number of densities, else one range), and pushes
  * each finished range into the peers' blocks from a second stream while the next range is being scored, (3) makes the handle's stream wait until every peer's columns have landed.  Work
  * queued on the stream afterwards sees the complete [T x ld] rows; all ranks must make the same sequence of calls.
- * Tensor kernel only, T <= 32768.  A peer that does not show up within ~2 s ends the wait and sets flag word 17. */
+ * Tensor kernel only, T <= 32768.  A peer that does not show up within ~2 s ends the wait and sets flag word 17 (sticky; the rows
+ * are then incomplete and the rank stops announcing its columns as complete, so its peers time out as well). */
 int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
                             void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
                             uint32_t chunks);

@@ -130,7 +130,10 @@ __global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uin
         __threadfence_system();
         if (threadIdx.x == 0)
             own[kFlagCount] = 0;
-        if (threadIdx.x < world && threadIdx.x != rank)
+        // after a time-out (this or an earlier range of the call) the columns are NOT complete: say nothing, the
+        // peers then run into their own time-out instead of reading stale scores
+        const bool complete = *reinterpret_cast<volatile uint32_t*>(own + kFlagTimeout) == 0;
+        if (complete && threadIdx.x < world && threadIdx.x != rank)
             st_release_sys(peers.flags[threadIdx.x] + kFlagDone + rank, epoch);
     }
 }

@@ -71,6 +71,89 @@ def test_gather_rejects_bad_arguments():
         eng.close()
 
 
+def _shard_engines(ms, world, mode=capi.MODE_MAX):
+    tab = tables.float_tables(ms)
+    M = len(tab["offsets"]) - 1
+    engines = []
+    for r in range(world):
+        m0, m1 = sharded.mixture_range(M, r, world)
+        sub = sharded.shard_float_tables(tab, m0, m1)
+        e = capi.Engine(0)
+        e.upload_float(sub["offsets"], sub["mean"], sub["isr"], sub["cov_idx"], sub["w2"], sub["log_norm"], mode=mode,
+                       kernel=capi.KERNEL_TENSOR)
+        engines.append((e, m0, m1))
+    return engines, M
+
+
+# two handles only: with more, their streams share hardware queues and a spinning wait kernel of one handle sits in
+# front of another handle's scoring kernels (again a one-GPU artefact)
+@pytest.mark.parametrize("world,chunks,T", [(2, 4, 900), (2, 2, 2304), (2, 1, 130)])
+def test_ranks_on_one_gpu_exchange_their_columns(world, chunks, T):
+    """Push / DONE / wait between `world` handles of ONE process on one GPU: every handle has its own streams and its
+    own block, the blocks are plain device pointers to each other.  The READY words are preset: on one GPU a push
+    kernel spinning for a peer's READY keeps the SMs the next scoring kernel wants, and the peer's signal kernel
+    queues behind that one -- a scheduling dead end that separate GPUs do not have (the READY handshake is covered
+    by the two-GPU test below and by profiles/bench_sharded.py)."""
+    ms = synth.make_model(M=1000, K=8, D=24, seed=77)
+    x = synth.make_features(ms, T, seed=9)
+    engines, M = _shard_engines(ms, world)
+    Mp = sharded.shard_width(M, world)
+    ld = Mp * world
+    flags_offset = (T * ld * 4 + 127) // 128 * 128
+    try:
+        dx = torch.from_numpy(x).cuda()
+        want = torch.zeros((T, ld), device="cuda")
+        for r, (e, m0, m1) in enumerate(engines):
+            own = torch.empty((T, m1 - m0), device="cuda")
+            e.score_device(T, dx, own)
+            e.sync()
+            want[:, r * Mp:r * Mp + (m1 - m0)] = own
+        bases = [e.peer_alloc(flags_offset + 128)[0] for e, _, _ in engines]
+        blocks = [torch.as_tensor(sharded._DeviceBlock(b, (T, ld)), device="cuda:0") for b in bases]
+        flags = [torch.as_tensor(sharded._DeviceBlock(b + flags_offset, (32,)), device="cuda:0").view(torch.int32) for b in bases]
+        for f in flags:
+            f[:8] = 1 << 20
+        torch.cuda.synchronize()
+        for rep in range(3):
+            for r, (e, _, _) in enumerate(engines):
+                e.score_device_gather(T, dx, r, bases, ld, r * Mp, flags_offset, chunks)
+            for e, _, _ in engines:
+                e.sync()
+            for r in range(world):
+                assert int(flags[r][17]) == 0, "time-out"
+                assert torch.equal(blocks[r].view(torch.int32), want.view(torch.int32)), (rep, r)
+                blocks[r].zero_()
+            torch.cuda.synchronize()
+        del blocks, flags
+        for (e, _, _), b in zip(engines, bases):
+            e.peer_free(b)
+    finally:
+        for e, _, _ in engines:
+            e.close()
+
+
+def test_a_missing_peer_ends_the_wait():
+    ms = synth.make_model(M=64, K=4, D=10, seed=3)
+    engines, M = _shard_engines(ms, 2)
+    T, ld = 64, 64
+    flags_offset = T * ld * 4
+    try:
+        dx = torch.from_numpy(synth.make_features(ms, T, seed=1)).cuda()
+        e0 = engines[0][0]
+        bases = [e0.peer_alloc(flags_offset + 128)[0] for _ in range(2)]
+        flags = [torch.as_tensor(sharded._DeviceBlock(b + flags_offset, (32,)), device="cuda:0").view(torch.int32) for b in bases]
+        e0.score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)  # rank 1 never calls
+        e0.sync()
+        assert int(flags[0][17]) == 1          # marked on the waiting rank ...
+        assert int(flags[1][8 + 0]) == 0       # ... which did not announce its columns as complete
+        del flags
+        for b in bases:
+            e0.peer_free(b)
+    finally:
+        for e, _, _ in engines:
+            e.close()
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 def test_two_ranks_push_into_each_other():
     env = dict(os.environ, PYTHONPATH=ROOT)
