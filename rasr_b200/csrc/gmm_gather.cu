@@ -187,6 +187,25 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
     // kernel running beside the push least (T=8192, 8 ranges: 0.951 ms; four loads in flight: 1.065 ms)
     const int        unroll    = unrollEnv ? unrollEnv : 1;
 
+    // Frame ranges: range c of n takes n - c parts of n(n+1)/2 -- what the call pays for the exchange is the push of
+    // the LAST range, so that one is kept small (N=2, T=8192, 4 ranges: 0.995 -> 0.947 ms).  Column ranges stay even:
+    // the same cut made short calls slower (T=1024, 2 ranges: 0.168 -> 0.180 ms; profiles/sweep_push_n2_*_uneven_r01.txt).
+    static const bool evenEnv    = getenv("GMM_GATHER_EVEN") != nullptr;
+    const bool        evenRanges = evenEnv || !byFrames;
+    auto cut = [&](uint32_t total, uint32_t c) -> uint32_t {  // first unit of range c; every range keeps >= 1 unit
+        if (c >= chunks)
+            return total;
+        uint64_t b;
+        if (evenRanges)
+            b = (uint64_t)total * c / chunks;
+        else {
+            const uint64_t done = (uint64_t)c * chunks - (uint64_t)c * (c - 1) / 2;  // sum of (n - i), i < c
+            b                   = (uint64_t)total * done / ((uint64_t)chunks * (chunks + 1) / 2);
+        }
+        b = std::max<uint64_t>(b, c);
+        return (uint32_t)std::min<uint64_t>(b, total - (chunks - c));
+    };
+
     gather_signal_ready<<<1, 32, 0, h->stream>>>(peers, rank, world, epoch);
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
@@ -194,8 +213,8 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
         uint32_t row0 = 0, rows = T, col0 = colOffset, col1 = colOffset + h->M;
         int      rc;
         if (byFrames) {
-            row0 = (uint32_t)((uint64_t)FT * c / chunks) * kTileRows;
-            rows = std::min<uint32_t>(T, (uint32_t)((uint64_t)FT * (c + 1) / chunks) * kTileRows) - row0;
+            row0 = cut(FT, c) * kTileRows;
+            rows = std::min<uint32_t>(T, cut(FT, c + 1) * kTileRows) - row0;
             // all frames are prepared by the first range's call: with a preparation kernel between the ranges the
             // push CTAs settle on the SMs first and the next range's scoring CTAs (all of an SM's shared memory)
             // wait for them -- measured: no overlap at all
@@ -203,7 +222,7 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
                                     tm.nTiles, c == 0, c == 0 ? T : 0, row0 / kTileRows);
         }
         else {
-            const uint32_t t0 = (uint32_t)((uint64_t)tm.nTiles * c / chunks), t1 = (uint32_t)((uint64_t)tm.nTiles * (c + 1) / chunks);
+            const uint32_t t0 = cut(tm.nTiles, c), t1 = cut(tm.nTiles, c + 1);
             rc = gmm_tc_score_tiles(h, T, d_x, own, ld, t0, t1, c == 0);
             if (chunks > 1) {
                 col0 = colOffset + t0 * tm.mixPerTile;
