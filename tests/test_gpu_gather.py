@@ -53,6 +53,35 @@ def test_ranges_equal_one_pass(M, K, D, ragged, mode, chunks, T):
         eng.close()
 
 
+def test_aligner_reads_the_gathered_block_in_place():
+    """Column m of the block is mixture m: the device-resident aligner takes the block (pointer + ld) like any score
+    matrix and finds the path it finds over gmm_score_device's scores."""
+    from rasr_b200.align import AlignmentAutomata, linear_hmm
+    ms = synth.make_model(M=600, K=8, D=24, seed=21)
+    T = 700
+    x = synth.make_features(ms, T, seed=4)
+    rng = np.random.default_rng(5)
+    fo = np.array([0, 300, 700], np.uint32)
+    au = AlignmentAutomata.from_arc_lists([linear_hmm(rng.integers(0, ms.M, n)) for n in (70, 120)])
+    eng = capi.Engine(0)
+    try:
+        upload(eng, ms)
+        dx = torch.from_numpy(x).cuda()
+        full = torch.empty((T, ms.M), device="cuda")
+        eng.score_device(T, dx, full)
+        want = eng.align_device(fo, full, au, ld=ms.M)
+        ld = ms.M + 40
+        flags_offset = (T * ld * 4 + 127) // 128 * 128
+        base, _ = eng.peer_alloc(flags_offset + 128)
+        eng.score_device_gather(T, dx, 0, [base], ld, 0, flags_offset, 4)
+        got = eng.align_device(fo, base, au, ld=ld)
+        for g, w in zip(got, want):
+            assert np.array_equal(g.view(np.uint32), w.view(np.uint32))
+        eng.peer_free(base)
+    finally:
+        eng.close()
+
+
 def test_gather_rejects_bad_arguments():
     ms = synth.make_model(M=40, K=4, D=10, seed=1)
     eng = capi.Engine(0)
