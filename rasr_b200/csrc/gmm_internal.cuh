@@ -50,6 +50,10 @@ struct TensorModel {
     // regular model: every mixture takes the same number of packed columns (mixCols, a divisor of partW) and none
     // is empty, so mixture m sits at rows (m % mixPerTile) * mixCols of tile m / mixPerTile and a tile over ANY
     // set of mixtures can be assembled from whole swizzle atoms of the canonical image (subset scoring)
+    // GMM_TC_SPLIT=fp8 (experimental, pooled models): part 2 of the operand rows holds e5m2 bytes -- per 32-byte
+    // k-step 16 x lo and 16 x hi of the same dimensions (A: lo | hi, B: hi | lo) -- and ONE kind::f8f6f4 instruction
+    // per k-step adds both correction products: 6 MMA instructions per tile instead of 9
+    bool      fp8       = false;
     bool      regular   = false;
     uint32_t  mixCols   = 0, mixPerTile = 0;
 };

@@ -30,6 +30,7 @@
 // 256-column accumulators in TMEM double-buffer MMA against the epilogue.  Synchronisation: tile-indexed mbarrier
 // rings ready[] / done[] (see tc_score_body).  DESIGN.md 4.1 lists the measurements behind these choices.
 #include <cuda_fp16.h>
+#include <cuda_fp8.h>
 #include <float.h>
 #include <math.h>
 #include <stdio.h>
@@ -54,6 +55,7 @@ struct KParams {
     uint32_t       T;
     uint32_t       nTiles, frameTiles, split;  // items = nTiles * split
     uint32_t       kSteps;                     // k-steps (16 elements) per precision part
+    uint32_t       fp8;                        // part 2 holds e5m2 corrections (TensorModel::fp8)
     uint32_t       atoms;                      // swizzle atoms per operand row
     uint32_t       aTileBytes, bTileBytes;     // bTileBytes includes c / slot / meta
     uint32_t       stagesA, buffersB;
@@ -351,7 +353,23 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                 if (p.dbg) { const long long t1 = clock64(); wR += t1 - t0; t0 = t1; }
                 const uint32_t aLo   = (smem_u32(sA + (size_t)stage * p.aTileBytes) & 0x3FFFF) >> 4;
                 const uint32_t dTmem = tmemBase + (t & 1) * kTileN;
-                if (leader) {
+                if (leader && p.fp8) {
+                    // per k-step: hi.hi in fp16, then ONE e5m2 instruction over part 2 (x_lo.mu_hi + x_hi.mu_lo)
+                    constexpr uint32_t idesc8 = idesc | (1u << 7) | (1u << 10);
+                    for (uint32_t ks = 0; ks < kS; ++ks) {
+                        const uint32_t kl = kS + ks;
+                        const uint32_t ah = aLo + (ks / kPerAtom) * (kTileM * SWZ / 16) + (ks % kPerAtom) * 2;
+                        const uint32_t al = aLo + (kl / kPerAtom) * (kTileM * SWZ / 16) + (kl % kPerAtom) * 2;
+                        const uint32_t bh = bLo + (ks / kPerAtom) * (kTileN * SWZ / 16) + (ks % kPerAtom) * 2;
+                        const uint32_t bl = bLo + (kl / kPerAtom) * (kTileN * SWZ / 16) + (kl % kPerAtom) * 2;
+                        tc_mma_f16(dTmem, ((uint64_t)descHi << 32) | ah, ((uint64_t)descHi << 32) | bh, idesc, ks ? 1u : 0u);
+                        tc_mma_f8(dTmem, ((uint64_t)descHi << 32) | al, ((uint64_t)descHi << 32) | bl, idesc8, 1u);
+                    }
+                    tc_commit(smem_u32(&done[t % kRing]));
+                    if (f + 1 == f1)
+                        tc_commit(smem_u32(&emptyB[b]));
+                }
+                else if (leader) {
                     // per k-step: hi.hi, lo.hi, hi.lo (hi part = k-step ks, lo part = k-step kS + ks of the image)
                     for (uint32_t ks = 0; ks < kS; ++ks) {
                         const uint32_t kl = kS + ks;
@@ -562,7 +580,7 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ 
                                                       const float* __restrict__ scale, uint32_t kSteps, uint32_t atoms,
                                                       uint32_t swz, uint8_t* __restrict__ aTiles,
                                                       float2* __restrict__ rowInfo,
-                                                      const uint32_t* __restrict__ rowMap) {
+                                                      const uint32_t* __restrict__ rowMap, uint32_t fp8) {
     const uint32_t chunks = kSteps * 2;  // 8-element chunks per precision part
     const uint32_t epa    = swz / 2;     // fp16 elements per atom row
     const uint32_t lane   = threadIdx.x & 31, c = lane % LPF;
@@ -627,8 +645,25 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ 
             const uint32_t kHi = c * 8, kLo = kSteps * 16 + c * 8;
             *reinterpret_cast<uint4*>(base + (size_t)(kHi / epa) * kTileM * swz +
                                       swz_offset(row, (kHi % epa) / 8, swz)) = *reinterpret_cast<const uint4*>(hi);
-            *reinterpret_cast<uint4*>(base + (size_t)(kLo / epa) * kTileM * swz +
-                                      swz_offset(row, (kLo % epa) / 8, swz)) = *reinterpret_cast<const uint4*>(lo);
+            if (fp8) {
+                // part 2, k-step c / 2: 16-byte chunk of the lo bytes, then the chunk of the hi bytes; this lane's 8
+                // dimensions are the lower or the upper half of both
+                __align__(8) uint8_t l8[8], h8[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float a = v[j] * inv;
+                    l8[j]         = (uint8_t)__nv_cvt_float_to_fp8(a - __half2float(hi[j]), __NV_SATFINITE, __NV_E5M2);
+                    h8[j]         = (uint8_t)__nv_cvt_float_to_fp8(a, __NV_SATFINITE, __NV_E5M2);
+                }
+                const uint32_t cpa = swz / 16, cLo = kSteps * 2 + (c / 2) * 2, cHi = cLo + 1, half8 = (c & 1) * 8;
+                *reinterpret_cast<uint2*>(base + (size_t)(cLo / cpa) * kTileM * swz + swz_offset(row, cLo % cpa, swz) + half8) =
+                        *reinterpret_cast<const uint2*>(l8);
+                *reinterpret_cast<uint2*>(base + (size_t)(cHi / cpa) * kTileM * swz + swz_offset(row, cHi % cpa, swz) + half8) =
+                        *reinterpret_cast<const uint2*>(h8);
+            }
+            else
+                *reinterpret_cast<uint4*>(base + (size_t)(kLo / epa) * kTileM * swz +
+                                          swz_offset(row, (kLo % epa) / 8, swz)) = *reinterpret_cast<const uint4*>(lo);
         }
         // zero the unused tail of the last atom
         const uint32_t used = chunks * 2, all = atoms * (swz / 16);  // 16-byte chunks per row
@@ -677,6 +712,10 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     const char* env = getenv("GMM_TC_SWIZZLE");
     tm.swz          = (env && atoi(env) == 64) ? 64 : 128;
     tm.pooled       = (C == 1);
+    {
+        const char* split = getenv("GMM_TC_SPLIT");
+        tm.fp8            = split && !strcmp(split, "fp8") && tm.pooled;
+    }
     const uint32_t kel = tm.pooled ? D : 2 * D;
     tm.kSteps          = (kel + 3 + 15) / 16;  // 3 spare K columns carry the per-Gaussian constant
     if (tm.kSteps > (uint32_t)kMaxKSteps)
@@ -894,7 +933,19 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
                 uint8_t* pHi = base + (size_t)(k / epa) * kTileN * tm.swz + swz_offset(r, (k % epa) / 8, tm.swz) + (k % 8) * 2;
                 uint8_t* pLo = base + (size_t)(kl / epa) * kTileN * tm.swz + swz_offset(r, (kl % epa) / 8, tm.swz) + (kl % 8) * 2;
                 memcpy(pHi, &hi, 2);
-                memcpy(pLo, &lo, 2);
+                if (tm.fp8) {
+                    // part 2, k-step k / 16: chunk of the hi bytes, then chunk of the lo bytes (mirrors tc_prep_kernel)
+                    __half hh;
+                    memcpy(&hh, &hi, 2);
+                    const float    v   = std::min(std::max(row[k], -60000.f), 60000.f);
+                    const uint8_t  h8  = (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E5M2);
+                    const uint8_t  l8  = (uint8_t)__nv_cvt_float_to_fp8(v - __half2float(hh), __NV_SATFINITE, __NV_E5M2);
+                    const uint32_t cpa = tm.swz / 16, cH = tm.kSteps * 2 + (k / 16) * 2, cL = cH + 1;
+                    base[(size_t)(cH / cpa) * kTileN * tm.swz + swz_offset(r, cH % cpa, tm.swz) + k % 16] = h8;
+                    base[(size_t)(cL / cpa) * kTileN * tm.swz + swz_offset(r, cL % cpa, tm.swz) + k % 16] = l8;
+                }
+                else
+                    memcpy(pLo, &lo, 2);
             }
         }
     }
@@ -966,7 +1017,7 @@ int tc_run(gmm_handle* h, const TcJob& job) {
         int blocks = (int)std::min<uint32_t>((FT * kTileM + fpb - 1) / fpb, (uint32_t)h->smCount * 16);
 #define GMM_PREP(P, L)                                                                                          \
     tc_prep_kernel<P, L><<<blocks, 256, 0, h->stream>>>(d_x, T, h->D, FT, tm.center, tm.scale, tm.kSteps, tm.nAtoms, \
-                                                        tm.swz, (uint8_t*)aT, (float2*)rT, job.rowMap)
+                                                        tm.swz, (uint8_t*)aT, (float2*)rT, job.rowMap, tm.fp8 ? 1u : 0u)
         if (tm.pooled) {
             if (lpf == 8)
                 GMM_PREP(true, 8);
@@ -1000,6 +1051,7 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     p.nTiles     = job.nTiles;
     p.frameTiles = FT;
     p.kSteps     = tm.kSteps;
+    p.fp8        = tm.fp8 ? 1u : 0u;
     p.atoms      = tm.nAtoms;
     p.aTileBytes = tm.aTileBytes;
     p.bTileBytes = tm.tileBytes;

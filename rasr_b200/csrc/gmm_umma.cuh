@@ -82,6 +82,15 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t dTmem, uint64_t aDesc, uint6
             "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
             : "memory");
 }
+// 8-bit floating point operands (formats in the instruction descriptor), K = 32 bytes per instruction
+__device__ __forceinline__ void tc_mma_f8(uint32_t dTmem, uint64_t aDesc, uint64_t bDesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(dTmem),
+            "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
+            : "memory");
+}
 __device__ __forceinline__ bool elect_one() {  // true in exactly one lane of the (converged) warp
     uint32_t pred;
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
