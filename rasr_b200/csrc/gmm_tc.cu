@@ -712,9 +712,11 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     const char* env = getenv("GMM_TC_SWIZZLE");
     tm.swz          = (env && atoi(env) == 64) ? 64 : 128;
     tm.pooled       = (C == 1);
+    bool fp8Forced  = false;
     {
-        const char* split = getenv("GMM_TC_SPLIT");
-        tm.fp8            = split && !strcmp(split, "fp8") && tm.pooled;
+        const char* split = getenv("GMM_TC_SPLIT");  // "fp8": where its guard allows, "fp8!": regardless (experiments)
+        fp8Forced         = split && !strcmp(split, "fp8!");
+        tm.fp8            = split && (!strcmp(split, "fp8") || fp8Forced) && tm.pooled;
     }
     const uint32_t kel = tm.pooled ? D : 2 * D;
     tm.kSteps          = (kel + 3 + 15) / 16;  // 3 spare K columns carry the per-Gaussian constant
@@ -860,6 +862,23 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     std::vector<float> ctrF(D), scaleF(D);
     for (uint32_t d = 0; d < D; ++d)
         ctrF[d] = nLive ? (float)(ctr[d] / (double)nLive) : 0.f;
+    if (tm.fp8 && !fp8Forced) {
+        // The e5m2 corrections hold the 1e-4 bar only for compact models (profiles/split_error_sweep_r01.txt):
+        // centred whitened means within kappa / D <= 8 at D >= 24 (emulated error there <= 7e-5), <= 3 at 9 <= D < 24;
+        // anything else keeps three products.
+        double kap8 = 0.0;
+        for (const Col& c : cols)
+            if (c.g != 0xFFFFFFFFu) {
+                double k = 0.0;
+                for (uint32_t d = 0; d < D; ++d) {
+                    const double b = ((double)mean[(size_t)c.g * D + d] - (double)ctrF[d]) * (double)isr[d];
+                    k += b * b;
+                }
+                kap8 = std::max(kap8, k);
+            }
+        if (D < 9 || kap8 > (D >= 24 ? 8.0 : 3.0) * D)
+            tm.fp8 = false;
+    }
     if (tm.pooled) {
         for (uint32_t d = 0; d < D; ++d)
             scaleF[d] = isr[d];
