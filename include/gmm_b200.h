@@ -254,6 +254,10 @@ int gmm_kernel_timing(gmm_handle* h, int on);
 int gmm_kernel_time(gmm_handle* h, double* total_ms, uint64_t* launches);
 /* 1 = direct, 2 = tensor: the float kernel the last gmm_upload_float selected. */
 int         gmm_float_kernel(const gmm_handle* h);
+/* Tensor kernel only: MMA products per algorithmic product of the uploaded float model -- 3 (fp16 hi.hi + lo.hi +
+ * hi.lo, the default) or 2 (fp16 hi.hi + one e5m2 product for both corrections: GMM_TC_SPLIT=fp8 was set at upload
+ * and the model passed the split's guard); 0 when the model is not on the tensor kernel. */
+int         gmm_float_split(const gmm_handle* h);
 /* 1 = dp4a (CUDA cores), 2 = integer tensor path: the kernel the last gmm_upload_quant selected (0: no model).
  * Both are bit-identical to the reference; environment GMM_QUANT_KERNEL=dp4a at upload time forces the former. */
 int         gmm_quant_kernel(const gmm_handle* h);

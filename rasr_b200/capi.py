@@ -63,6 +63,7 @@ SYMBOLS = [
     ("gmm_kernel_timing", _i, [_vp, _i]),
     ("gmm_kernel_time", _i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     ("gmm_float_kernel", _i, [_vp]),
+    ("gmm_float_split", _i, [_vp]),
     ("gmm_quant_kernel", _i, [_vp]),
     ("gmm_version", C.c_char_p, []),
 ]
@@ -156,6 +157,11 @@ class Engine:
     @property
     def float_kernel(self) -> int:
         return int(self._lib.gmm_float_kernel(self._h))
+
+    @property
+    def float_split(self) -> int:
+        """3: three fp16 products (default); 2: fp16 + e5m2 corrections (GMM_TC_SPLIT=fp8); 0: not on the tensor kernel."""
+        return int(self._lib.gmm_float_split(self._h))
 
     @property
     def quant_kernel(self) -> int:

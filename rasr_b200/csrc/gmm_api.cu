@@ -374,6 +374,12 @@ int gmm_float_kernel(const gmm_handle* h) {
     return (h && h->floatValid) ? h->kernel : 0;
 }
 
+int gmm_float_split(const gmm_handle* h) {
+    if (!h || !h->floatValid || h->kernel != GMM_KERNEL_TENSOR || !h->tensor.valid)
+        return 0;
+    return h->tensor.fp8 ? 2 : 3;
+}
+
 void* gmm_host_alloc(size_t bytes) {
     void* p = nullptr;
     if (cudaMallocHost(&p, bytes ? bytes : 16) != cudaSuccess)
