@@ -96,6 +96,22 @@ int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, 
 int gmm_quant_score_device(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,
                            float* d_score, uint8_t* d_qx, size_t ld);
 
+/* gmm_quant_score_device without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and bit-identical results (q, best, score as gmm_quant_score_device; it always runs
+ * the dp4a kernel), but the one scratch array the kernel needs -- the quantized frames, T * C * Dpad bytes -- lives in
+ * a file-scope `static __device__` array of GMM_QUANT_STATIC_SCRATCH_BYTES that every GPU which loads the library
+ * holds until exit, and the call is two kernel launches on the handle's stream: no cudaMalloc / cudaFree / allocating
+ * library routine.  (The first call on a device also resolves the array's device address, cudaGetSymbolAddress:
+ * make that call once before a stream capture begins.)
+ * Limit: T * C * Dpad <= GMM_QUANT_STATIC_SCRATCH_BYTES (87 381 frames at C = 1, Dpad = 48); more is rejected with
+ * GMM_ERR_ARG and a message naming the limit.  All calls on a device share the array and it keeps the last call's
+ * bytes (every byte read is rewritten first, nothing needs clearing): calls whose kernels OVERLAP on the GPU --
+ * different streams or handles of one device -- race; calls ordered on one stream do not. */
+#define GMM_QUANT_STATIC_SCRATCH_BYTES (4u << 20)
+int gmm_quant_score_device_static(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best,
+                                  float* d_score, size_t ld);
+
 /* ---- mixture-sharded variant (BASELINE.json configs[4]): scoring with its exchange step --------------------------
  * Rank r of N holds mixtures [r*Mp, (r+1)*Mp) and scores the same frames as every other rank; afterwards every rank
  * needs every column.  The reference has no multi-GPU scorer (Mm::FeatureScorer::Scorer::score(e) is answered from

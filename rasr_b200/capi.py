@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(HERE, "libgmm_b200.so")
 
 MODE_MAX, MODE_SUM = 0, 1
 KERNEL_AUTO, KERNEL_DIRECT, KERNEL_TENSOR = 0, 1, 2
+QUANT_STATIC_SCRATCH_BYTES = 4 << 20  # GMM_QUANT_STATIC_SCRATCH_BYTES
 
 # every symbol include/gmm_b200.h declares: (name, restype, argtypes)
 _vp, _u32, _sz, _i = C.c_void_p, C.c_uint32, C.c_size_t, C.c_int
@@ -31,6 +32,7 @@ SYMBOLS = [
     ("gmm_upload_quant", _i, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, C.c_float]),
     ("gmm_quant_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_quant_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
+    ("gmm_quant_score_device_static", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_emission_lists", _i, [_vp, _u32, _vp, _vp, _vp, _u32, _vp, _vp]),
     ("gmm_baum_welch_device", _i, [_vp, _u32, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     ("gmm_score_baum_welch_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
@@ -451,3 +453,9 @@ class Engine:
         ld = self.qM if ld is None else int(ld)
         self._check(self._lib.gmm_quant_score_device(self._h, int(T), _ptr(d_x), _ptr(d_q), _ptr(d_best),
                                                      _ptr(d_score), _ptr(d_qx), ld), "gmm_quant_score_device")
+
+    def quant_score_device_static(self, T, d_x, d_q=None, d_best=None, d_score=None, ld=None):
+        """gmm_quant_score_device without any allocation (scratch in a static device array; include/gmm_b200.h)."""
+        ld = self.qM if ld is None else int(ld)
+        self._check(self._lib.gmm_quant_score_device_static(self._h, int(T), _ptr(d_x), _ptr(d_q), _ptr(d_best),
+                                                            _ptr(d_score), ld), "gmm_quant_score_device_static")

@@ -15,6 +15,9 @@
 // in order reading each quantized mean once (uniform 128-bit loads) for 32*FR frames.
 #include "gmm_internal.cuh"
 
+#include <algorithm>
+#include <mutex>
+
 namespace {
 
 __device__ __forceinline__ uint8_t quantize_u8(float v) {
@@ -241,4 +244,121 @@ int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, 
         }
     }
     return GMM_OK;
+}
+
+// ---- entry point that allocates nothing (no counterpart in the reference,
+// see include/gmm_b200.h) ---------------------------------------------------------------------------
+// The dp4a scorer above needs one scratch array, the quantized frames qx [T x C x Dpad].  gmm_quant_launch takes it from
+// the handle's grow-on-demand scratch (cudaMalloc); this variant keeps it in a file-scope device array instead, so the
+// call consists of two kernel launches and nothing else: usable under stream capture and from loops that must not
+// call cudaMalloc.  Every GPU that loads the library holds the array (GMM_QUANT_STATIC_SCRATCH_BYTES) until exit.
+// All calls on a device share it and it keeps the previous call's bytes: quantize_kernel rewrites every byte the
+// scoring kernel reads (padding included), so nothing has to be cleared, but two calls whose kernels overlap on
+// the GPU (different streams / handles of one device) race on it.
+static __device__ __align__(256) uint8_t g_quantStaticScratch[GMM_QUANT_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+// In host code `g_quantStaticScratch` is the host-side stand-in of the symbol, not a device address: the address a
+// kernel may use comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kMaxDevices = 64;
+uint8_t*      g_staticScratchAddr[kMaxDevices] = {};
+std::mutex    g_staticScratchLock;
+
+int staticScratchSetUp(gmm_handle* h, uint8_t** out) {
+    if (h->device < 0 || h->device >= kMaxDevices) {
+        h->setError("gmm_quant_score_device_static: device ordinal out of range");
+        return GMM_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> guard(g_staticScratchLock);
+    if (!g_staticScratchAddr[h->device]) {
+        void* p = nullptr;
+        GMM_CUDA_TRY(h, cudaSetDevice(h->device));
+        GMM_CUDA_TRY(h, cudaGetSymbolAddress(&p, g_quantStaticScratch));
+        if (!p) {
+            h->setError("gmm_quant_score_device_static: cudaGetSymbolAddress returned a null address");
+            return GMM_ERR_CUDA;
+        }
+        g_staticScratchAddr[h->device] = (uint8_t*)p;
+    }
+    *out = g_staticScratchAddr[h->device];
+    return GMM_OK;
+}
+
+// launchScore without the timing brackets (those create CUDA events when gmm_kernel_timing is on)
+template<int DW, int FR>
+int launchScoreStatic(gmm_handle* h, uint32_t T, const uint8_t* d_qx, int32_t* d_q, uint32_t* d_best, float* d_score,
+                      size_t ld) {
+    const QuantModel& qm             = h->quant;
+    const int         framesPerBlock = 8 * 32 * FR;
+    const int         gy             = (T + framesPerBlock - 1) / framesPerBlock;
+    const int         wantX          = std::max(1, (4 * h->smCount + gy - 1) / gy);
+    const int         mixPerBlock    = std::max(1, (int)((qm.M + wantX - 1) / wantX));
+    dim3              grid((qm.M + mixPerBlock - 1) / mixPerBlock, gy), block(256);
+    if (qm.C == 1)
+        quant_score_kernel<DW, FR, true><<<grid, block, 0, h->stream>>>(
+                d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
+                (double)qm.scalingSquared, d_q, d_best, d_score, ld);
+    else
+        quant_score_kernel<DW, FR, false><<<grid, block, 0, h->stream>>>(
+                d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
+                (double)qm.scalingSquared, d_q, d_best, d_score, ld);
+    h->launches++;
+    GMM_CUDA_TRY(h, cudaGetLastError());
+    return GMM_OK;
+}
+
+}  // namespace
+
+extern "C" int gmm_quant_score_device_static(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
+                                             uint32_t* d_best, float* d_score, size_t ld) {
+    if (!h)
+        return GMM_ERR_ARG;
+    const QuantModel& qm = h->quant;
+    if (!qm.valid) {
+        h->setError("gmm_quant_score_device_static: no quantized model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (ld < qm.M || (T && !d_x)) {
+        h->setError("gmm_quant_score_device_static: invalid argument (ld < M or NULL features)");
+        return GMM_ERR_ARG;
+    }
+    const size_t need = (size_t)T * qm.C * qm.Dpad;
+    if (need > (size_t)GMM_QUANT_STATIC_SCRATCH_BYTES) {
+        char msg[256];
+        snprintf(msg, sizeof msg,
+                 "gmm_quant_score_device_static: %u frames x %u covariances x %u padded dims = %zu bytes of quantized "
+                 "frames exceed the static scratch of %zu bytes (at most %zu frames per call for this model)",
+                 T, qm.C, qm.Dpad, need, (size_t)GMM_QUANT_STATIC_SCRATCH_BYTES,
+                 (size_t)GMM_QUANT_STATIC_SCRATCH_BYTES / ((size_t)qm.C * qm.Dpad));
+        h->setError(msg);
+        return GMM_ERR_ARG;
+    }
+    uint8_t* qx = nullptr;
+    int      rc = staticScratchSetUp(h, &qx);
+    if (rc)
+        return rc;
+    if (T == 0)
+        return GMM_OK;
+    GMM_CUDA_TRY(h, cudaSetDevice(h->device));
+    const size_t total  = (size_t)T * qm.C * (qm.Dpad / 4);
+    const int    blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)h->smCount * 16);
+    quantize_kernel<<<blocks, 256, 0, h->stream>>>(d_x, (int)T, (int)qm.D, (int)qm.Dpad, (int)qm.C, qm.isrS, qx);
+    h->launches++;
+    GMM_CUDA_TRY(h, cudaGetLastError());
+    if (!d_q && !d_best && !d_score)
+        return GMM_OK;
+    switch (qm.Dpad / 4) {
+    case 4: return launchScoreStatic<4, 4>(h, T, qx, d_q, d_best, d_score, ld);
+    case 8: return launchScoreStatic<8, 4>(h, T, qx, d_q, d_best, d_score, ld);
+    case 12: return launchScoreStatic<12, 4>(h, T, qx, d_q, d_best, d_score, ld);
+    case 16: return launchScoreStatic<16, 2>(h, T, qx, d_q, d_best, d_score, ld);
+    case 20: return launchScoreStatic<20, 2>(h, T, qx, d_q, d_best, d_score, ld);
+    case 24: return launchScoreStatic<24, 2>(h, T, qx, d_q, d_best, d_score, ld);
+    case 28: return launchScoreStatic<28, 2>(h, T, qx, d_q, d_best, d_score, ld);
+    case 32: return launchScoreStatic<32, 2>(h, T, qx, d_q, d_best, d_score, ld);
+    default: break;
+    }
+    h->setError("gmm_quant_score_device_static: padded dimension above 128 is not supported");
+    return GMM_ERR_UNSUPPORTED;
 }
