@@ -1,0 +1,63 @@
+"""Calibration of the packing-time guard of the default operand split of the float tensor kernel (fp16 hi.hi + ONE
+e5m2 product for both corrections; gmm_tc_pack in rasr_b200/csrc/gmm_tc.cu).  CPU emulation as in split_error.py.
+
+pred = 2^-13 * rms_g q(b_g) / sMin,  q(b)^2 = sum_d (b_d^2 + 1) b_d^2  (b: centred whitened mean),
+sMin = max(1, (min_g (w2 + L) + D - 3 sqrt(2D)) / 2): the predicted size of the split's error on the score of a frame
+drawn near a Gaussian.  The table relates it to the largest relative error the emulation finds over a whole batch.
+Run: python profiles/split_guard.py > profiles/split_guard_r02.txt"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from rasr_b200 import synth, tables
+
+
+def e5m2(a):
+    a = np.asarray(a, np.float64)
+    m, e = np.frexp(a)
+    q = np.ldexp(np.round(m * 8) / 8, e)
+    q = np.where(np.abs(a) < 2.0 ** -14, np.round(a * 2.0 ** 16) / 2.0 ** 16, q)
+    return np.clip(q, -57344.0, 57344.0)
+
+
+def split(a):
+    hi = a.astype(np.float16)
+    return hi.astype(np.float64), (a - hi.astype(np.float32)).astype(np.float64)
+
+
+def run(ms, x, label):
+    t = tables.float_tables(ms)
+    mean, isr, w2, ln, off = t["mean"], t["isr"], t["w2"], t["log_norm"], t["offsets"]
+    c = mean.mean(0)
+    xt = ((x - c) * isr[0]).astype(np.float32)
+    mt = ((mean - c) * isr[0]).astype(np.float32)
+    cw = w2.astype(np.float64) + ln[t["cov_idx"]].astype(np.float64)
+    const = (mt.astype(np.float64) ** 2).sum(1) + cw
+    x2 = (xt.astype(np.float64) ** 2).sum(1)[:, None]
+    K = int(off[1] - off[0])
+
+    def mixture_min(dot):
+        s = 0.5 * (x2 - 2 * dot + const[None, :])
+        return s.reshape(s.shape[0], -1, K).min(2)
+
+    ref = mixture_min(xt.astype(np.float64) @ mt.astype(np.float64).T)
+    (xh, xl), (mh, ml) = split(xt), split(mt)
+    d5 = mixture_min(xh @ mh.T + e5m2(xl) @ e5m2(mh).T + e5m2(xh) @ e5m2(ml).T)
+    r5 = (np.abs(d5 - ref) / np.abs(ref)).max()
+    b = mt.astype(np.float64)
+    D = ms.D
+    q2 = ((b * b + 1) * b * b).sum(1)
+    s_min = max(1.0, 0.5 * cw.min() + 0.5 * max(0.0, D - 3 * np.sqrt(2 * D)))
+    pred = 2.0 ** -13 * np.sqrt(q2.mean()) / s_min
+    take = D >= 9 and pred <= 1.5e-4
+    print(f"{label:14s} kappa_max/D {(b * b).sum(1).max() / D:6.1f}  emulated max rel err {r5:.2e}  pred {pred:.2e}  "
+          f"err/pred {r5 / pred:.2f}  guard: {'e5m2 split' if take else 'three products'}"
+          f"{'   <-- BEYOND 1e-4' if take and r5 > 1e-4 else ''}")
+
+
+for D in (4, 9, 16, 24, 45, 64):
+    for scale in (0.5, 1.0, 1.5, 2.0, 2.25, 2.5, 3.0, 4.0):
+        ms = synth.make_model(M=400, K=16, D=D, seed=7, mean_scale=scale)
+        run(ms, synth.make_features(ms, 300, seed=8).astype(np.float32), f"D={D} s={scale}")
+for cfg, T in (("cfg1", 600), ("cfg3", 60)):
+    ms, x = synth.make_config(cfg)
+    run(ms, x[:T].astype(np.float32), cfg)

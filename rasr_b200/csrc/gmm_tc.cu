@@ -714,9 +714,11 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     tm.pooled       = (C == 1);
     bool fp8Forced  = false;
     {
-        const char* split = getenv("GMM_TC_SPLIT");  // "fp8": where its guard allows, "fp8!": regardless (experiments)
+        // Default: fp16 hi.hi + ONE e5m2 product for both corrections wherever the guard below allows it (pooled models);
+        // "fp16": always three fp16 products; "fp8!": the e5m2 split regardless of the guard (experiments)
+        const char* split = getenv("GMM_TC_SPLIT");
         fp8Forced         = split && !strcmp(split, "fp8!");
-        tm.fp8            = split && (!strcmp(split, "fp8") || fp8Forced) && tm.pooled;
+        tm.fp8            = !(split && !strcmp(split, "fp16")) && tm.pooled;
     }
     const uint32_t kel = tm.pooled ? D : 2 * D;
     tm.kSteps          = (kel + 3 + 15) / 16;  // 3 spare K columns carry the per-Gaussian constant
@@ -863,20 +865,30 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     for (uint32_t d = 0; d < D; ++d)
         ctrF[d] = nLive ? (float)(ctr[d] / (double)nLive) : 0.f;
     if (tm.fp8 && !fp8Forced) {
-        // The e5m2 corrections hold the 1e-4 bar only for compact models (profiles/split_error_sweep_r01.txt):
-        // centred whitened means within kappa / D <= 8 at D >= 24 (emulated error there <= 7e-5), <= 3 at 9 <= D < 24;
-        // anything else keeps three products.
-        double kap8 = 0.0;
+        // The e5m2 corrections hold the 1e-4 bar only for compact models.  Predicted error of a score:
+        // both correction products carry a relative rounding error of up to 2^-4 + 2^-4 on terms of size 2^-12 |a_d b_d|,
+        // i.e. about 2^-13 sqrt(sum_d a_d^2 b_d^2) per score when the roundings are independent; for a frame drawn near
+        // Gaussian b (a = b + unit noise, the pairs with the SMALLEST scores) that is 2^-13 q(b), q(b)^2 = sum_d (b_d^2 + 1)
+        // b_d^2, against a score of at least sMin = (min_g (w2 + L) + D - 3 sqrt(2D)) / 2.  Emulation over D = 9..64 and
+        // mean spreads 0.5..6 sigma (profiles/split_guard_r02.txt) finds the largest relative error of a whole batch at
+        // 0.34..0.65 of  pred = 2^-13 rms_g q / sMin  once it matters (pred >= 6e-5): the split is taken for pred <= 1.5e-4
+        // (cfg1 / cfg3: 1.3e-4, emulated and measured errors 5e-5).  D < 9 averages too few roundings: three products.
+        double q2 = 0.0, cMin = 1e300;
+        size_t n  = 0;
         for (const Col& c : cols)
-            if (c.g != 0xFFFFFFFFu) {
-                double k = 0.0;
+            if (c.g != 0xFFFFFFFFu && c.slot != 0xFFFF) {
+                double q = 0.0;
                 for (uint32_t d = 0; d < D; ++d) {
                     const double b = ((double)mean[(size_t)c.g * D + d] - (double)ctrF[d]) * (double)isr[d];
-                    k += b * b;
+                    q += (b * b + 1.0) * b * b;
                 }
-                kap8 = std::max(kap8, k);
+                q2 += q;
+                cMin = std::min(cMin, (double)w2[c.g] + (double)logNorm[covIdx[c.g]]);
+                ++n;
             }
-        if (D < 9 || kap8 > (D >= 24 ? 8.0 : 3.0) * D)
+        const double sMin = std::max(1.0, 0.5 * cMin + 0.5 * std::max(0.0, (double)D - 3.0 * sqrt(2.0 * D)));
+        const double pred = n ? ldexp(sqrt(q2 / (double)n), -13) / sMin : 0.0;
+        if (D < 9 || !(pred <= 1.5e-4))
             tm.fp8 = false;
     }
     if (tm.pooled) {
