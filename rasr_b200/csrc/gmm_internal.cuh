@@ -101,6 +101,7 @@ struct QTensorModel {
     uint32_t  maxMixPerPart = 0;
     uint32_t  buffersB   = 0, stagesA = 0;
     uint32_t  qBase      = 0;       // min c2 - 2 Dmax (wrapping)
+    uint32_t  qAbsMax    = 0;       // bound on |q| over all frames (f32 path of the final score needs < 2^24)
 };
 
 struct gmm_handle {

@@ -27,6 +27,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cmath>
 #include <type_traits>
 
 #include "gmm_internal.cuh"
@@ -47,6 +48,7 @@ struct QKParams {
     float*          score;
     size_t          ld;
     double          scalingSquared;
+    float           twoScalingSquared;  // f32 path of the final score (OUT & 4): q / (2 s^2), see qtc_launch
     uint32_t        T;
     uint32_t        nTiles, frameTiles, split;
     uint32_t        kSteps;      // 32-byte k-steps
@@ -125,7 +127,7 @@ struct QEpiState {
 
 // One 32-column chunk (four 8-column segments) of a row's s32 accumulator.  SP as in the float kernel: > 0 when
 // every mixture of the column part spans exactly SP segments (closing positions become compile-time constants).
-template<int SP>
+template<int SP, bool WB>
 __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t xxBase,
                                            uint32_t offB, QEpiState& st) {
     // the chunk's 32 per-column constants first (eight 128-bit loads in flight together), then the arithmetic
@@ -157,7 +159,8 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
         if (close) {  // uniform across the warp
             const bool none = m == kNoKey;  // mixture without densities: the reference leaves INT_MAX / no density
             sts_u32(st.sp, none ? 0x7FFFFFFFu : (m >> 8) + xxBase);
-            sts_u32(st.sp + offB, none ? 0xFFFFFFFFu : (m & 255u));
+            if (WB)
+                sts_u32(st.sp + offB, none ? 0xFFFFFFFFu : (m & 255u));
             st.sp += 4;
             m = kNoKey;
         }
@@ -168,8 +171,12 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
 // Persistent kernel: warp 0 bulk-copy producer (+ TMEM allocation), warp 1 MMA issuer, NE = 8 or 16 epilogue warps
 // (TMEM lane quarter = warp & 3, column part of 1024 / NE columns = (warp - 2) / 4; 16 warps when no mixture has more
 // than 64 densities: the epilogue, not the two MMAs per tile, bounds this kernel).  Barrier protocol as in gmm_tc.cu.
-template<int NE>
+// OUT: which arrays the caller asked for, fixed at compile time so that the store loop is branch-free -- bit 0 q, bit 1
+// arg-min, bit 2 final f32 score by ONE f32 division (exact, see qtc_launch); OUT = 0 keeps all three as run-time tests
+// and the score as the reference's f64 expression (any other combination, or |q| beyond 2^24).
+template<int NE, int OUT>
 __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(const QKParams p) {
+    constexpr bool WQ = OUT == 0 || (OUT & 1), WB = OUT == 0 || (OUT & 2), WS = OUT == 0 || (OUT & 4);
     extern __shared__ uint8_t smemRaw[];
     uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -359,33 +366,33 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                         // 96 registers per thread: one 32-column chunk (+ its 32 constants) live at a time
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
-                        qepi_chunk<SP>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st);
                         tmem_ld32(taddr + 32, va);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP>(va, 1, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 1, kcAddr, segEnd, xxBase, offB, st);
                     }
                     else {
                         uint32_t vb[32];
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 32, vb);
-                        qepi_chunk<SP>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 64, va);
-                        qepi_chunk<SP>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 96, vb);
-                        qepi_chunk<SP>(va, 2, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 2, kcAddr, segEnd, xxBase, offB, st);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP>(vb, 3, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(vb, 3, kcAddr, segEnd, xxBase, offB, st);
                     }
                     if (NE == 16)  // the quarter's four warps have staged their parts of these 32 rows
                         asm volatile("bar.sync %0, 128;" ::"r"(1 + qd) : "memory");
@@ -400,12 +407,17 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                     auto put = [&](uint32_t r) {
                         if (r < rows) {
                             const uint32_t qv = lds_u32(ss);
-                            if (p.q)
+                            if (OUT == 0 ? p.q != nullptr : WQ)
                                 *reinterpret_cast<uint32_t*>(g) = qv;
-                            if (p.best)
+                            if (OUT == 0 ? p.best != nullptr : WB)
                                 *reinterpret_cast<uint32_t*>(g + bestDelta) = lds_u32(ss + offB);
-                            if (p.score)  // f32( 0.5 * q / scalingSquared ) in double, SimdFeatureScorer.cc:135-145
-                                *reinterpret_cast<float*>(g + scoreDelta) = (float)(0.5 * (double)(int32_t)qv / p.scalingSquared);
+                            if (OUT == 0) {
+                                if (p.score)  // f32( 0.5 * q / scalingSquared ) in double, SimdFeatureScorer.cc:135-145
+                                    *reinterpret_cast<float*>(g + scoreDelta) =
+                                            (float)(0.5 * (double)(int32_t)qv / p.scalingSquared);
+                            }
+                            else if (WS)  // the same bits from one f32 division (|q| < 2^24, see qtc_launch)
+                                *reinterpret_cast<float*>(g + scoreDelta) = __fdiv_rn((float)(int32_t)qv, p.twoScalingSquared);
                         }
                     };
                     if (adv_j == 0) {  // nMix divides 32: a lane keeps its column
@@ -592,6 +604,9 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
         }
     }
     tm.qBase = (uint32_t)(cmin - 2 * dmax);
+    // |q| <= max(|cmin|, |cmax + Dmax|): q = c2 - 2 dot + |qx|^2 = qconst + |qmean - qx|^2 with the distance in [0, Dmax]
+    // and qconst = c2 - |qmean|^2 >= cmin - Dmax
+    tm.qAbsMax = (uint32_t)std::min<int64_t>(0x7FFFFFFF, std::max<int64_t>(std::llabs(cmin - dmax), std::llabs(cmax + dmax)));
     int rc;
     if ((rc = h->upload((void**)&tm.bTiles, img.data(), img.size(), true)))
         return rc;
@@ -685,7 +700,25 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     }
     p.split        = bestS;
     const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
-    void (*kernel)(const QKParams) = epiWarps == 16 ? qtc_score_kernel<16> : qtc_score_kernel<8>;
+    // Output set fixed at compile time for the combinations callers use (tests / bench: q + arg-min; the RASR plugin:
+    // score, or score + arg-min; everything).  The final score there is ONE f32 division q / (2 s^2): for |q| < 2^24 the
+    // integer is exact in f32 and the correctly rounded f32 quotient equals the reference's f32(0.5 * q / s^2) evaluated
+    // in f64 (SimdFeatureScorer.cc:135-145) -- q / d with a 24-bit d lies at least 2^-49 (relative) away from every f32
+    // rounding boundary it does not hit exactly, so the intermediate f64 rounding (2^-53) cannot change the result.
+    // tm.qAbsMax bounds |q| over all frames (packing); larger constants keep the f64 expression (OUT = 0).
+    int out = (d_q ? 1 : 0) | (d_best ? 2 : 0) | (d_score ? 4 : 0);
+    p.twoScalingSquared = 2.0f * qm.scalingSquared;
+    const bool generic = getenv("GMM_QTC_GENERIC") != nullptr;  // tests: force the run-time variant
+    if (generic || (out != 3 && out != 4 && out != 6 && out != 7) ||
+        ((out & 4) && (tm.qAbsMax >= (1u << 24) || !std::isfinite(p.twoScalingSquared) || !(qm.scalingSquared > 0.f))))
+        out = 0;
+    void (*kernel)(const QKParams) = nullptr;
+    if (epiWarps == 16)
+        kernel = out == 3 ? qtc_score_kernel<16, 3> : out == 4 ? qtc_score_kernel<16, 4> : out == 6 ? qtc_score_kernel<16, 6>
+               : out == 7 ? qtc_score_kernel<16, 7> : qtc_score_kernel<16, 0>;
+    else
+        kernel = out == 3 ? qtc_score_kernel<8, 3> : out == 4 ? qtc_score_kernel<8, 4> : out == 6 ? qtc_score_kernel<8, 6>
+               : out == 7 ? qtc_score_kernel<8, 7> : qtc_score_kernel<8, 0>;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     GMM_CUDA_TRY(h, e);
     h->timeBegin();

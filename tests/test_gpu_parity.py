@@ -138,6 +138,35 @@ def test_quantized_kernels_agree_with_oracle(eng, oracle, kernel, T, monkeypatch
     assert np.array_equal(bits(r["score"]), bits(oracle.simd_final_score(q, raw["scaling_squared"])))
 
 
+@pytest.mark.parametrize("warps", ["16", "8"])
+@pytest.mark.parametrize("want", ["q+best", "score", "score+best", "q+best+score", "q", "generic"])
+def test_quantized_output_sets_bit_exact(eng, oracle, want, warps, monkeypatch):
+    """The integer tensor kernel is compiled per set of requested arrays (q + arg-min; score; score + arg-min; all;
+    anything else and GMM_QTC_GENERIC take the run-time variant); the compiled sets produce the final f32 score by ONE
+    f32 division instead of the reference's f64 expression (SimdFeatureScorer.cc:135-145): same bits required."""
+    if want == "generic":
+        monkeypatch.setenv("GMM_QTC_GENERIC", "1")
+    if warps == "8":
+        monkeypatch.setenv("GMM_QTC_EPI_WARPS", "8")
+    ms = synth.make_model(M=301, K=16, D=45, seed=12)
+    x = synth.make_features(ms, 391)
+    x[7] *= 30.0
+    t, raw = oracle_quant_tables(ms)
+    upload_quant(eng, t)
+    assert eng.quant_kernel == 2
+    qx = oracle.simd_quantize_features(x, raw["isrs"])
+    q, b = oracle.simd_score(ms.mix_offsets, raw, qx)
+    sc = oracle.simd_final_score(q, raw["scaling_squared"])
+    r = eng.quant_score_host(x, want_q="q" in want or want == "generic", want_best="best" in want or want == "generic",
+                             want_score="score" in want or want == "generic")
+    if r["q"] is not None:
+        assert np.array_equal(r["q"], q)
+    if r["best"] is not None:
+        assert np.array_equal(r["best"], b)
+    if r["score"] is not None:
+        assert np.array_equal(bits(r["score"]), bits(sc))
+
+
 @pytest.mark.parametrize("kw", MODELS)
 @pytest.mark.parametrize("T", [1, 33, 300])
 def test_quantized_bit_exact_vs_oracle(eng, oracle, kw, T):
