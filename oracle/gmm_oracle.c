@@ -429,7 +429,8 @@ float orc_viterbi_align(uint32_t T, const float* scores, size_t ld, uint32_t S, 
  *   Speech/KeyedEstimator.cc:108-121 processAlignedFeature
  *   AbstractMixtureSetEstimator.cc:117-147 accumulate (viterbi / posterior-weighted with weightThreshold)
  *   MixtureEstimator.cc:86-97, GaussDensityEstimator.cc:22-32, VectorAccumulator.hh:60-67,
- *   Utilities.hh:110-146 (sum + y, sum + y*y, sum + w*y, sum + w*y*y evaluated left to right)
+ *   Utilities.hh:110-146 (sum + y, sum + y*y, sum + w*y; the source's sum + w*y*y is evaluated as sum + w*(y*y) by the
+ *   reference build, -ffast-math: checked bit for bit against oracle/_ref/ref_estimator's accumulator files)
  * sumScorer = 0: GaussDiagonalMaximumFeatureScorer's best density; 1: GaussDiagonalSumFeatureScorer's.
  * viterbi = 0 needs sumScorer = 1 (only the sum scorer has density posteriors).
  * mixture[t] = 0xFFFFFFFF skips frame t; weight may be NULL (the unweighted overloads).
@@ -442,7 +443,7 @@ static void orc_accumulate_density(const orc_model* m, uint32_t slot, const floa
         double y = (double)xt[d];
         if (weighted) {
             meanSum[(size_t)mean * m->D + d] = meanSum[(size_t)mean * m->D + d] + w * y;
-            covSum[(size_t)cov * m->D + d]   = covSum[(size_t)cov * m->D + d] + w * y * y;
+            covSum[(size_t)cov * m->D + d]   = covSum[(size_t)cov * m->D + d] + w * (y * y);
         }
         else {
             meanSum[(size_t)mean * m->D + d] = meanSum[(size_t)mean * m->D + d] + y;

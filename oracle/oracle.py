@@ -33,7 +33,7 @@ def build_ref(force: bool = False) -> str | None:
     """Compile the reference scorer classes from /root/reference (build container only)."""
     if not os.path.isdir(REFERENCE_ROOT):
         return REF_BIN if os.path.exists(REF_BIN) else None
-    if force or not os.path.exists(REF_BIN):
+    if force or not all(os.path.exists(os.path.join(HERE, "_ref", b)) for b in ("ref_scorer", "ref_matmul", "ref_estimator")):
         subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(HERE, "ref_build")])
     return REF_BIN
 
@@ -284,6 +284,50 @@ def run_ref(ms, x, scorer="max", *, threads=0, repeat=1, dump=True, workdir=None
         if threads > 0:
             with open(op + ".timing.json") as f:
                 out["timing"] = json.load(f)
+        return out
+
+
+REF_EST_BIN = os.path.join(HERE, "_ref", "ref_estimator")
+
+
+def ref_estimator_available() -> bool:
+    return os.path.exists(REF_EST_BIN) and os.access(REF_EST_BIN, os.X_OK)
+
+
+def run_ref_estimator(ms, x=None, mixture=None, weight=None, *, mode="viterbi", scorer="max", min_variance=None,
+                      threshold=None, workdir=None):
+    """Run the unmodified reference text writer / reader and estimator stack (oracle/ref_build/ref_estimator.cc).
+    -> dict(pms, reread_pms [, best, mixset, mixset2, est_pms]): the files as bytes (best: u32 array)."""
+    if not ref_estimator_available():
+        raise RuntimeError("oracle/_ref/ref_estimator is not built (needs /root/reference: oracle.build_ref())")
+    with tempfile.TemporaryDirectory(dir=workdir) as tmp:
+        mp, op = os.path.join(tmp, "model.gms"), os.path.join(tmp, "out")
+        ms.save(mp)
+        cmd = [REF_EST_BIN, f"model={mp}", f"out={op}"]
+        if x is not None:
+            fp, ap = os.path.join(tmp, "feat.f32"), os.path.join(tmp, "align.u32")
+            np.ascontiguousarray(x, np.float32).tofile(fp)
+            np.ascontiguousarray(mixture, np.uint32).tofile(ap)
+            cmd += [f"features={fp}", f"align={ap}", f"mode={mode}", f"scorer={scorer}"]
+            if weight is not None:
+                wp = os.path.join(tmp, "weight.f64")
+                np.ascontiguousarray(weight, np.float64).tofile(wp)
+                cmd.append(f"weights={wp}")
+            if min_variance is not None:
+                cmd.append(f"min-variance={min_variance!r}")
+            if threshold is not None:
+                cmd.append(f"threshold={threshold!r}")
+        r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"ref_estimator failed ({r.returncode}):\n{r.stdout[-2000:]}")
+        out = {"log": r.stdout}
+        for key, ext in (("pms", ".pms"), ("reread_pms", ".reread.pms"), ("mixset", ".mixset"), ("mixset2", ".mixset2"),
+                         ("est_pms", ".est.pms")):
+            if os.path.exists(op + ext):
+                with open(op + ext, "rb") as f:
+                    out[key] = f.read()
+        if os.path.exists(op + ".best.u32"):
+            out["best"] = np.fromfile(op + ".best.u32", np.uint32)
         return out
 
 

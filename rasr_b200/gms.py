@@ -80,9 +80,16 @@ class MixtureSetData:
             raise ValueError("density index out of range")
         if self.n_densities and (int(self.dens_mean.max()) >= self.n_means or int(self.dens_cov.max()) >= self.n_cov):
             raise ValueError("mean / covariance index out of range")
+        if not np.all(self.variances >= 0):
+            raise ValueError("variances must not be negative")
+
+    def check_scorable(self) -> None:
+        """A SCORER needs strictly positive variances (reference: require(checkDiagonal(diagonal)) in
+        CovarianceFeatureScorerElement.cc:23,41-44).  A mixture set as such may hold zeros: the reference's estimate()
+        returns them for a covariance seen with one observation when minimum-variance is 0
+        (AbstractMixtureSetEstimator.cc:299-335), and such a set can be written and read."""
         if np.any(self.variances <= 0):
-            # reference: require(checkDiagonal(diagonal)) in CovarianceFeatureScorerElement.cc:23,41-44
-            raise ValueError("variances must be strictly positive")
+            raise ValueError("variances must be strictly positive (raise minimum-variance in the M-step)")
 
     # -- file io ------------------------------------------------------------------------------
     def save(self, path: str) -> None:

@@ -50,6 +50,7 @@ def _log_norm(variances: np.ndarray) -> np.ndarray:
 
 def float_tables(ms: MixtureSetData, *, mixture_weight_scale: float = 1.0, gaussian_scale: float = 1.0):
     """-> dict(offsets, mean [G,D], cov_idx [G], isr [C,D], log_norm [C], w2 [G])."""
+    ms.check_scorable()
     mean, cov_idx = flatten(ms)
     factor = F32(np.sqrt(np.float64(gaussian_scale)))
     with np.errstate(over="ignore"):
@@ -92,6 +93,7 @@ def simd_padded_dimension(D: int) -> int:
 
 def quant_tables(ms: MixtureSetData):
     """-> dict(offsets, qmean [G,Dpad] u8, cov_idx [G], qconst [G] s32, isr_scaled [C,D], scaling_squared)."""
+    ms.check_scorable()
     mean, cov_idx = flatten(ms)
     D, Dpad = ms.D, simd_padded_dimension(ms.D)
     with np.errstate(over="ignore", invalid="ignore"):

@@ -17,9 +17,18 @@ def pytest_configure(config):
 
 
 def golden_names():
-    """Model fixtures (scorer goldens); lda_*.npz are front-end fixtures with their own tests."""
+    """Model fixtures (scorer goldens); lda_*.npz (front end) and est_*.npz (estimators, model files) are fixtures
+    with their own tests."""
     names = (os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return sorted(n for n in names if not n.startswith("lda_"))
+    return sorted(n for n in names if not n.startswith(("lda_", "est_")))
+
+
+def estimator_golden_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "est_*.npz")))
+
+
+ESTIMATOR_CASES = {"vit": ("max", True, False), "vitw": ("max", True, True), "vitsum": ("sum", True, True),
+                   "bw": ("sum", False, True)}   # case -> (scorer, viterbi, weighted); tests/golden/make_estimator_golden.py
 
 
 def load_golden(name):

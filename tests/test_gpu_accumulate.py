@@ -187,3 +187,41 @@ def test_export_import_block_layout(eng, oracle):
     assert all(np.array_equal(twice[k], 2 * acc[k]) for k in acc)
     back = sharded.unpack_accumulators(block.cpu().numpy(), ms.n_means, ms.n_cov, ms.D, ms.G)
     assert all(np.array_equal(back[k], acc[k]) for k in acc)
+
+
+# ---------------------------------------------------------------------------------------------------
+# the reference's own accumulator files (tests/golden/est_*.npz, written by oracle/_ref/ref_estimator)
+# ---------------------------------------------------------------------------------------------------
+from conftest import ESTIMATOR_CASES, estimator_golden_names, load_golden  # noqa: E402
+from rasr_b200 import model_io  # noqa: E402
+
+
+@pytest.mark.parametrize("case", sorted(ESTIMATOR_CASES))
+@pytest.mark.parametrize("name", estimator_golden_names())
+def test_e_step_against_reference_accumulator_files(tmp_path, eng, name, case):
+    """gmm_accumulate_host -> MIXSET file -> M-step against AbstractMixtureSetEstimator::accumulate / write / estimate
+    of the unmodified reference (AbstractMixtureSetEstimator.cc:117-147, 482-506, 299-335)."""
+    ms, z = load_golden(name)
+    scorer, viterbi, weighted = ESTIMATOR_CASES[case]
+    upload(eng, ms, capi.MODE_SUM if scorer == "sum" else capi.MODE_MAX)
+    eng.create_accumulators(tables.mean_index(ms), ms.n_means, viterbi=viterbi)
+    best = eng.accumulate_host(z["x"], z["mixture"], z["weight"] if weighted else None)
+    (tmp_path / "ref.mixset").write_bytes(bytes(z["mixset_" + case]))
+    ref = model_io.read_mixset(tmp_path / "ref.mixset")
+    got = model_io.MixtureSetEstimatorData.from_accumulators(ms, eng.read_accumulators(ms.n_cov))
+    model_io.write_mixset(got, tmp_path / "gpu.mixset")          # renumbers the estimators as the reference's writer does
+    got = model_io.read_mixset(tmp_path / "gpu.mixset")
+    assert got.equal_topology(ref)
+    if viterbi:
+        live = z["mixture"] != SKIP
+        assert np.array_equal(best[live], z["best_" + case][live])
+    # viterbi: same terms, added by atomics in another order (1e-12); posterior weights: device expf / logf (2e-5)
+    rtol = SUM_RTOL if viterbi else 2e-5
+    for f in ("mix_weight", "mean_weight", "cov_weight", "mean_sum", "cov_sum"):
+        a, b = getattr(got, f), getattr(ref, f)
+        assert np.max(np.abs(a - b)) <= rtol * np.max(np.abs(b)), f
+    if viterbi and not weighted:
+        assert np.array_equal(got.mix_weight, ref.mix_weight)    # counts are exact
+        # the M-step of the GPU's accumulators, printed like the reference prints its own: identical text
+        model_io.write_mixture_set_text(got.estimate(), tmp_path / "est.pms")
+        assert (tmp_path / "est.pms").read_bytes() == bytes(z["est_" + case])

@@ -178,3 +178,17 @@ def test_m_step_removes_light_densities_but_keeps_the_heaviest(oracle):
     with pytest.raises(ValueError, match="zero weight"):
         est.estimate()
     est.estimate(allow_zero_weights=True)
+
+
+def test_m_step_may_return_zero_variances_like_the_reference(tmp_path):
+    """minimum-variance defaults to 0 (AbstractMixtureSetEstimator.cc:35-38): a covariance estimated from identical
+    observations comes out as 0, the set can still be written and read; only building a scorer from it is refused
+    (CovarianceFeatureScorerElement.cc:23,41-44)."""
+    est = model_io.MixtureSetEstimatorData(2, [0, 1], [0], [6.0], [0], [0], [[6.0, 12.0]], [6.0], [[6.0, 24.0]], [6.0])
+    ms = est.estimate()
+    assert np.array_equal(ms.variances, np.zeros((1, 2), np.float32))
+    model_io.write_mixture_set_text(ms, tmp_path / "z.pms")
+    assert np.array_equal(model_io.read_mixture_set_text(tmp_path / "z.pms").variances, ms.variances)
+    with pytest.raises(ValueError, match="strictly positive"):
+        tables.float_tables(ms)
+    assert np.all(est.estimate(min_variance=0.01).variances == np.float32(0.01))
