@@ -117,11 +117,12 @@ def segment_features(ms, seg_ids):
 # -------------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the reference's own CPU scorer on the host cores
 # -------------------------------------------------------------------------------------------------
-def cpu_reference_run(ms, frames: int, scorer: str, repeat: int):
+def cpu_reference_run(ms, frames: int, scorer: str, repeat: int, threads: int | None = None):
     """Times oracle/_ref/ref_scorer (kind "reference") or, if it was not built, the oracle port ("port")."""
     from oracle import oracle as O
     from rasr_b200 import synth
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = cores if threads is None else min(cores, threads)
     x = synth.make_features(ms, frames, seed=3000)
     if O.ref_available():
         r = O.run_ref(ms, x, scorer, threads=cores, repeat=repeat, dump=False)
@@ -137,9 +138,29 @@ def cpu_reference_run(ms, frames: int, scorer: str, repeat: int):
             f(ms, x)
             best = min(best, time.perf_counter() - t0)
         fps, kind = frames / best, "port"
-    return dict(value=fps, unit=UNIT, cores=cores, kind=kind,
+    return dict(value=fps, unit=UNIT, cores=cores, kind=kind, scorer=scorer,
                 sample=f"{frames} frames of the same model/features, all {ms.M} mixtures per frame, "
                        f"one scorer instance per thread on {cores} threads, best of {repeat}")
+
+
+def cpu_reference_legs(ms, cores: int, scorers=("max", "sum", "simd", "batchint")):
+    """the reference's scorers on one thread and on all host cores, bounded samples (about a
+    second each).  Only with the compiled reference (oracle/_ref/ref_scorer); reported beside the GPU numbers."""
+    from oracle import oracle as O
+    if not O.ref_available():
+        return None
+    out = {}
+    per_thread = max(16, int(400e6 / max(1, ms.G) / 45))   # frames per thread: about 0.7 s of the float scorer
+    for name in scorers:
+        try:
+            one = cpu_reference_run(ms, per_thread, name, 1, threads=1)
+            allc = cpu_reference_run(ms, per_thread * cores, name, 1)
+        except Exception as e:  # a scorer the reference refuses for this model (batch-int needs a pooled covariance)
+            out[name] = {"unavailable": str(e)[:200]}
+            continue
+        out[name] = {"one_thread_frames_per_s": one["value"], "all_cores_frames_per_s": allc["value"],
+                     "cores": allc["cores"], "frames_one_thread": per_thread, "frames_all_cores": per_thread * cores}
+    return out
 
 
 def run_reference_arm(args):
@@ -162,7 +183,9 @@ def run_reference_arm(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * frames / fps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "cfg4-slice: 4501x16x45 float diagonal-maximum, reference CPU scorer",
-                       "frames_per_step": frames, "wall_s": wall},
+                       "frames_per_step": frames, "wall_s": wall,
+                       "note": "a bounded sample of the GPU arm's workload: the CPU scorer evaluates frame by frame, "
+                               "its frames/s does not depend on how many frames a step holds"},
             "cpu_baseline": cb, "gpu_launches": 0,
             "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -214,7 +237,7 @@ def ncu_traffic(summary_name):
 
 
 def float_roofline(ms, frames, kernel_sec, peaks, kernel_name, step_sec=None, traffic=None, sustained=False,
-                   launches_per_step=1):
+                   launches_per_step=1, split=3):
     """frames, kernel_sec: frames of ONE launch of the scoring kernel and its average duration (CUDA events around the
     launch; a step of `launches_per_step` launches: long batches go out in L2-sized launches).
     sustained: the kernel ran back to back for >= 100 ms (power-capped clocks) -> the sustained cuBLAS figure is
@@ -228,19 +251,23 @@ def float_roofline(ms, frames, kernel_sec, peaks, kernel_name, step_sec=None, tr
             "launches_per_step": launches_per_step, "frames_per_launch": frames,
             "kernel_share_of_step": (kernel_sec * launches_per_step / step_sec) if step_sec else None,
             "frac_of_burst_peak": ach / peaks["tensor"],
-            "executed_over_algorithmic": 3.0 * (16 * (((ms.D if ms.variances.shape[0] == 1 else 2 * ms.D) + 3 + 15) // 16))
+            # MMA instruction times per tile in fp16-K16 equivalents over the algorithmic contraction length: `split`
+            # products (3: fp16 hi.hi + lo.hi + hi.lo; 2: fp16 hi.hi + one e5m2 instruction for both corrections)
+            "mma_products_per_algorithmic_product": split,
+            "executed_over_algorithmic": float(split) * (16 * (((ms.D if ms.variances.shape[0] == 1 else 2 * ms.D) + 3 + 15) // 16))
                                          / (2 * ms.D + 1),
             "peak_source": f"{peaks['source']} bf16 dense {'sustained' if sustained else 'burst'} (MEASURED_PEAKS.json)",
             "algorithmic_flops_per_launch": flops,
             "gaussian_evals_per_s_kernel": ms.G * frames / kernel_sec}
 
 
-def quant_roofline(ms, frames, kernel_sec, peaks, outputs=2, traffic=None):
+def quant_roofline(ms, frames, kernel_sec, peaks, outputs=2, traffic=None, kernel_name="quant_score_kernel"):
     dpad = ((ms.D + 15) // 16) * 16
     nbytes = ms.G * (dpad + 4) + frames * dpad + frames * ms.M * 4 * outputs
     ach = nbytes / kernel_sec / 1e9
     return {"bound": "hbm", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s", "frac": ach / peaks["hbm"],
-            "traffic": traffic, "kernel": "quant_score_kernel", "kernel_ms_per_launch": kernel_sec * 1e3,
+            "traffic": traffic, "kernel": kernel_name, "kernel_ms_per_launch": kernel_sec * 1e3,
+            "outputs_written": outputs,
             "algorithmic_bytes_per_launch": nbytes,
             "peak_source": f"{peaks['source']} copy bandwidth (MEASURED_PEAKS.json)"}
 
@@ -273,18 +300,24 @@ def run_ours(args):
     eng.set_stream(stream.cuda_stream)
     eng.upload_float(tab["offsets"], tab["mean"], tab["isr"], tab["cov_idx"], tab["w2"], tab["log_norm"],
                      mode=capi.MODE_MAX, kernel=capi.KERNEL_AUTO)
+    split = eng.float_split
     kname = {capi.KERNEL_DIRECT: "direct_kernel (CUDA cores, reference order)",
-             capi.KERNEL_TENSOR: "tc_score_kernel (tcgen05 split-fp16 + fused min)"}[eng.float_kernel]
+             capi.KERNEL_TENSOR: "tc_score_kernel8 (tcgen05: fp16 hi.hi + " +
+                                 ("one e5m2 product for both corrections" if split == 2 else "fp16 lo.hi + hi.lo") +
+                                 ", fused per-mixture min)"}[eng.float_kernel]
 
     # this rank's segments: i -> rank i mod N; two alternating batches so consecutive steps read fresh inputs
     seg_ids = [rank + world * i for i in range(2 * segs)]
     x_host = torch.from_numpy(segment_features(ms, seg_ids)).pin_memory()
     xa, xb = x_host[:frames].cuda(), x_host[frames:].cuda()
-    scores = torch.empty((frames, ms.M), dtype=torch.float32, device="cuda")
+    # score block [frames][ld]: rows padded to a multiple of 4 floats (ld >= M is the API's layout, include/gmm_b200.h),
+    # so every row piece is 16-byte aligned and the kernel's lanes store them with 128-bit stores
+    ld = (ms.M + 3) // 4 * 4
+    scores = torch.empty((frames, ld), dtype=torch.float32, device="cuda")
     state = {"i": 0}
 
     def step():
-        eng.score_device(frames, xa if state["i"] % 2 == 0 else xb, scores)
+        eng.score_device(frames, xa if state["i"] % 2 == 0 else xb, scores, ld=ld)
         state["i"] += 1
 
     step()
@@ -312,13 +345,13 @@ def run_ours(args):
     launches_per_step = max(1, kernel_n // max(1, args.steps))
 
     # end to end through the host API: pinned features in, host scores out, every step
-    e2e_frames = min(frames, 8 * SEG_FRAMES)
-    out_host = torch.empty((e2e_frames, ms.M), dtype=torch.float32).pin_memory()
+    e2e_frames = min(frames, args.e2e_segments * SEG_FRAMES)
+    out_host = torch.empty((e2e_frames, ld), dtype=torch.float32).pin_memory()
     xh = x_host[:e2e_frames].numpy()
     oh = out_host.numpy()
 
     def e2e_step():
-        eng.score_host(xh, want_best=False, out=oh)
+        eng.score_host(xh, want_best=False, out=oh, ld=ld)
 
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(2):
@@ -419,19 +452,26 @@ def run_ours(args):
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec_per_step * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32 (fp16x3 split operands, f32 accumulate)" if
+            "vs_baseline": None, "dtype": ("f32 (split operands: fp16 hi.hi + e5m2 corrections, f32 accumulate; <= 1e-4 rel. "
+                                           "vs the reference's f32)" if split == 2 else
+                                           "f32 (fp16x3 split operands, f32 accumulate)") if
             eng.float_kernel == capi.KERNEL_TENSOR else "f32", "data": "synthetic",
             "config": {"workload": "cfg4-slice: 4501 mixtures x 16 densities x 45 dims, float diagonal-maximum, "
                                    f"{segs} segments x {SEG_FRAMES} frames per GPU per step",
                        "frames_per_step_per_gpu": frames, "segment_sharding": "segment i -> rank i mod N, no collective",
-                       "l2": f"scores written per step {frames * ms.M * 4 / 2**20:.0f} MiB > 126 MiB L2; "
+                       "l2": f"scores written per step {frames * ld * 4 / 2**20:.0f} MiB > 126 MiB L2; "
                              "inputs alternate between two batches",
+                       "score_block": f"[frames][{ld}] f32, rows padded from M = {ms.M} to a multiple of 4",
+                       "e2e_frames_per_step_per_gpu": e2e_frames,
                        "kernel": kname},
             "gpu_launches": launches_timed,
             "gaussian_evals_per_s": value * ms.G,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": e2e_frames * ms.D * 4,
-                    "d2h_bytes_per_step": e2e_frames * ms.M * 4, "frames_per_step_per_gpu": e2e_frames,
-                    "api": "gmm_score_host (C-ABI, pinned host buffers)"},
+                    "d2h_bytes_per_step": e2e_frames * ld * 4, "frames_per_step_per_gpu": e2e_frames,
+                    "d2h_GBps_per_gpu": e2e_value / world * ld * 4 / 1e9,
+                    "api": "gmm_score_host (C-ABI, pinned host buffers; the call pipelines kernel launches and "
+                           "device-to-host copies in chunks)",
+                    "bound": "PCIe: every scored frame returns 4 * ld bytes of scores over the GPU's host link"},
             "e2e_alignment": {"value": al_value, "unit": UNIT, "h2d_bytes_per_step": al_frames * ms.D * 4,
                               "d2h_bytes_per_step": al_frames * 4 + al_segs * 4, "frames_per_step_per_gpu": al_frames,
                               "api": "gmm_score_align_host (C-ABI): host features -> scores of the emissions each "
@@ -458,14 +498,24 @@ def run_ours(args):
                        "posteriors per frame and emission -> posterior-weighted E-step, all in HBM; only the segments' "
                        "total scores return"},
             "clocks": clocks}
+    if world > 1 and not args.no_extra:
+        # every rank takes part; rank 0 reports.  A failure here (e.g. peer access unavailable) must not lose the line.
+        try:
+            cfg5 = cfg5_mixture_sharded(torch, dist, rank, world, local, stream, steps=max(3, min(args.steps, 10)))
+        except Exception as e:  # noqa: BLE001
+            cfg5 = {"error": f"{type(e).__name__}: {e}"[:300]}
+        line["extra"] = {"cfg5_mixture_sharded": cfg5}
     if rank == 0:
         line["roofline"] = float_roofline(ms, frames / launches_per_step, kernel_sec, peaks, kname, sec_per_step,
-                                          ncu_traffic("prof_tc_cfg1_max_32768_r01.txt") if launches_per_step > 1 else None,
-                                          sustained=sec >= 0.1, launches_per_step=launches_per_step)
+                                          ncu_traffic("prof_tc_cfg1_max_32768_r02.txt") if launches_per_step > 1 else None,
+                                          sustained=sec >= 0.1, launches_per_step=launches_per_step, split=split or 3)
         if world == 1 and not args.no_cpu:
             os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core again
             cores = len(os.sched_getaffinity(0))
             line["cpu_baseline"] = cpu_reference_run(ms, max(512, 96 * cores), "max", 2)
+            legs = cpu_reference_legs(ms, cores)
+            if legs:
+                line["cpu_baseline"]["other_scorers"] = legs
         if world == 1 and not args.no_extra:
             line["extra"] = extra_cases(torch, eng, peaks, args)
         sys.stdout.flush()
@@ -477,6 +527,75 @@ def run_ours(args):
         dist.destroy_process_group()
     eng.close()
     return 0
+
+
+def cfg5_mixture_sharded(torch, dist, rank, world, local, stream, steps=10):
+    """BASELINE.json configs[4] at N > 1: a 65536 x 64 x 45 model (4.2 M Gaussians), mixtures sharded N ways, every
+    rank scores the same T frames against its shard and ends up with all columns.  Kernel alone / score + NCCL
+    all-gather / score with its exchange step inside the call (push over peer memory, no NCCL), T = 1024 and 8192.
+    Every rank generates only ITS shard (seed 1001 + rank): scores of different shards are independent, so the model
+    is the concatenation of the shards."""
+    from rasr_b200 import sharded, synth, tables
+    M, K, D = 65536, 64, 45
+    mp = sharded.shard_width(M, world)
+    m0, m1 = sharded.mixture_range(M, rank, world)
+    shard = synth.make_model(m1 - m0, K, D, seed=1001 + rank)
+    tab = tables.float_tables(shard)
+    res = {"model": f"{M} x {K} x {D} ({M * K} Gaussians), {mp} mixtures ({mp * K} Gaussians) per rank", "n_gpus": world}
+
+    def timed_loop(fn, n):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        ev0.record(stream)
+        for _ in range(n):
+            fn()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        tt = torch.tensor([ev0.elapsed_time(ev1) / n], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    sc = sharded.MixtureShardedScorer(tab, rank, world, dist, local, total_mixtures=M)
+    sc.bind_stream(stream)
+    for T in (1024, 8192):
+        x = synth.make_features(shard, T, seed=77)  # the same frames on every rank (seeded by rank 0's shard below)
+        dx = torch.from_numpy(x).cuda()
+        dist.broadcast(dx, 0)
+        for _ in range(2):
+            g = sc.score(dx)
+        ms_ag = timed_loop(lambda: sc.score(dx), steps)
+        ms_k = timed_loop(lambda: sc.engine.score_device(T, dx, sc._local, None, ld=sc.Mp), steps)
+        ref = sharded.to_frame_major(sc.score(dx), M).clone()
+        case = {"ms_kernel_alone": ms_k, "ms_score_plus_nccl_all_gather": ms_ag,
+                "all_gather_bus_GBps": (world - 1) * T * mp * 4 / max(1e-9, (ms_ag - ms_k) * 1e-3) / 1e9,
+                "exchange_bytes_sent_per_rank": (world - 1) * T * mp * 4}
+        best_ms, best_chunks, same_all = 1e30, 0, True
+        for chunks in (2, 4):
+            ps = sharded.PushMixtureShardedScorer(tab, rank, world, dist, local, max_frames=T, chunks=chunks,
+                                                  total_mixtures=M)
+            ps.engine.set_stream(stream.cuda_stream)
+            for _ in range(2):
+                ps.score(dx)
+            ms_p = timed_loop(lambda: ps.score(dx), steps)
+            fm = ps.score(dx)
+            torch.cuda.synchronize()
+            same = torch.tensor([1.0 if torch.equal(fm[:, :M], ref) and not ps.timed_out() else 0.0], device="cuda")
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            same_all = same_all and bool(same.item() == 1.0)
+            case[f"ms_push_{chunks}_ranges"] = ms_p
+            if ms_p < best_ms:
+                best_ms, best_chunks = ms_p, chunks
+            ps.close()
+        case.update({"ms_push_best": best_ms, "push_ranges": best_chunks, "push_bit_identical_to_all_gather": same_all,
+                     "frames_per_s_push": T / (best_ms * 1e-3), "frames_per_s_all_gather": T / (ms_ag * 1e-3),
+                     "push_egress_GBps_per_rank": (world - 1) * T * mp * 4 / (best_ms * 1e-3) / 1e9,
+                     "nvlink_GBps_per_direction": 900.0,
+                     "speedup_over_all_gather": ms_ag / best_ms})
+        res[f"T{T}"] = case
+        del dx, g, ref
+    sc.engine.close()
+    return res
 
 
 def timed_kernel(eng, fn, steps):
@@ -500,31 +619,51 @@ def extra_cases(torch, eng, peaks, args):
     qt = tables.quant_tables(ms)
     eng.upload_quant(qt["offsets"], qt["qmean"], qt["cov_idx"], qt["qconst"], qt["isr_scaled"], qt["scaling_squared"])
     T = x.shape[0]
+    ld = (ms.M + 3) // 4 * 4
     dx = torch.from_numpy(x).cuda()
-    dq = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
-    db = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
-    sec, _, _ = time_device(torch, lambda: eng.quant_score_device(T, dx, dq, db), steps, warmup)
-    ksec = timed_kernel(eng, lambda: eng.quant_score_device(T, dx, dq, db), steps)
+    dq = torch.empty((T, ld), dtype=torch.int32, device="cuda")
+    db = torch.empty((T, ld), dtype=torch.int32, device="cuda")
+    dsc = torch.empty((T, ld), dtype=torch.float32, device="cuda")
+    qname = {1: "quant_score_kernel (dp4a, CUDA cores)",
+             2: "qtc_score_kernel<16> (tcgen05 kind::i8, constants inside the contraction)"}[eng.quant_kernel]
+    sec, _, _ = time_device(torch, lambda: eng.quant_score_device(T, dx, dq, db, ld=ld), steps, warmup)
+    ksec = timed_kernel(eng, lambda: eng.quant_score_device(T, dx, dq, db, ld=ld), steps)
     out["cfg2_quantized"] = {"frames_per_s": T * steps / sec, "ms_per_step": 1e3 * sec / steps, "frames": T,
-                             "roofline": quant_roofline(ms, T, ksec, peaks,
-                                                        traffic=ncu_traffic("prof_quant_cfg2_r01.txt"))}
-    del dq, db
+                             "outputs": "q (s32) + arg-min (u32)",
+                             "roofline": quant_roofline(ms, T, ksec, peaks, kernel_name=qname,
+                                                        traffic=ncu_traffic("prof_quant_cfg2_r02.txt"))}
+    # what the RASR plugin asks for: the final f32 score only (one array)
+    sec1, _, _ = time_device(torch, lambda: eng.quant_score_device(T, dx, None, None, dsc, ld=ld), steps, warmup)
+    ksec1 = timed_kernel(eng, lambda: eng.quant_score_device(T, dx, None, None, dsc, ld=ld), steps)
+    out["cfg2_quantized_score_only"] = {"frames_per_s": T * steps / sec1, "ms_per_step": 1e3 * sec1 / steps, "frames": T,
+                                        "outputs": "final f32 score",
+                                        "roofline": quant_roofline(ms, T, ksec1, peaks, outputs=1, kernel_name=qname)}
+    del dq, db, dsc
     # cfg3: 12001 x 64, 10k-frame batches, max and sum
     ms, x = synth.make_config("cfg3", T=10000)
     tab = tables.float_tables(ms)
     T = x.shape[0]
+    ld = (ms.M + 3) // 4 * 4
     dx = torch.from_numpy(x).cuda()
-    ds = torch.empty((T, ms.M), dtype=torch.float32, device="cuda")
+    ds = torch.empty((T, ld), dtype=torch.float32, device="cuda")
     for mode, name in ((capi.MODE_MAX, "cfg3_max"), (capi.MODE_SUM, "cfg3_sum")):
         eng.upload_float(tab["offsets"], tab["mean"], tab["isr"], tab["cov_idx"], tab["w2"], tab["log_norm"],
                          mode=mode, kernel=capi.KERNEL_AUTO)
         st = steps if eng.float_kernel == capi.KERNEL_TENSOR else 2
-        sec, _, _ = time_device(torch, lambda: eng.score_device(T, dx, ds), st, 1 if st == 2 else warmup)
-        ksec = timed_kernel(eng, lambda: eng.score_device(T, dx, ds), st)
-        prof = {"cfg3_max": "prof_tc_cfg3_max_10000_r01.txt", "cfg3_sum": "prof_tc_cfg3_sum_10000_r01.txt"}[name]
+        sec, _, _ = time_device(torch, lambda: eng.score_device(T, dx, ds, ld=ld), st, 1 if st == 2 else warmup)
+        ksec = timed_kernel(eng, lambda: eng.score_device(T, dx, ds, ld=ld), st)
+        prof = {"cfg3_max": "prof_tc_cfg3_max_10000_r02.txt", "cfg3_sum": "prof_tc_cfg3_sum_10000_r02.txt"}[name]
+        kn = {capi.KERNEL_DIRECT: "direct_kernel", capi.KERNEL_TENSOR:
+              ("tc_score_kernel8" if mode == capi.MODE_MAX else "tc_score_kernel16") + f" ({eng.float_split} MMA products)"}
         out[name] = {"frames_per_s": T * st / sec, "ms_per_step": 1e3 * sec / st, "frames": T,
                      "kernel": eng.float_kernel,
-                     "roofline": float_roofline(ms, T, ksec, peaks, str(eng.float_kernel), sec / st, ncu_traffic(prof))}
+                     "roofline": float_roofline(ms, T, ksec, peaks, kn[eng.float_kernel], sec / st, ncu_traffic(prof),
+                                                split=eng.float_split or 3)}
+    if not args.no_cpu:
+        cores = len(os.sched_getaffinity(0))
+        legs = cpu_reference_legs(ms, cores, scorers=("max", "sum"))
+        if legs:
+            out["cfg3_cpu_reference"] = legs
     return out
 
 
@@ -535,6 +674,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--segments", type=int, default=512, help="1000-frame segments per GPU per step")
+    ap.add_argument("--e2e-segments", type=int, default=32, help="segments per host-API call of the e2e leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the cfg2 / cfg3 side measurements")
     args = ap.parse_args()

@@ -75,13 +75,32 @@ int gmm_upload_float(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t
                      const float* log_norm, int mode, int kernel);
 
 /* Score T frames held in HOST memory: x [T x D] -> scores [T x ld] (ld >= M), best [T x ld] or NULL.
- * Copies H2D, launches, copies D2H on the handle's stream and waits.  best = index of the winning
+ * Copies H2D, scores in chunks, copies each finished chunk D2H while the next one is scored, and waits.  best = index of the winning
  * density within its mixture (first minimum), 0xFFFFFFFF for a mixture without a finite density. */
 int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld);
+/* The asynchronous pair (precedent: the buffered scorers score a batch while search consumes the
+ * previous one, src/Nn/BatchFeatureScorer.cc:92-170): gmm_score_async enqueues what gmm_score_host does -- copy in,
+ * score, copy out -- and returns at once with a token; gmm_wait(token) returns when that call's scores (and best) are
+ * in the caller's arrays.  x, scores and best must stay valid until then, and should be page-locked (gmm_host_alloc):
+ * with pageable memory the copies degrade to synchronous ones.  Two calls may be in flight (each on a lane of its own:
+ * stream and device scratch); a third waits for the first.  Between a gmm_score_async and its gmm_wait only
+ * gmm_score_async, gmm_wait and gmm_sync (which also waits for every outstanding token) may be called on the handle. */
+int gmm_score_async(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld,
+                    uint64_t* token);
+int gmm_wait(gmm_handle* h, uint64_t token);
 /* Same with DEVICE pointers; asynchronous on the handle's stream (call gmm_sync to wait). */
 int gmm_score_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
 /* Density posteriors of the sum scorer for T frames: post [T x G] (device pointers), exp(score - s_k). */
 int gmm_posteriors_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_post);
+
+/* The same for ONE mixture per frame, host arrays: what AssigningContextScorer::getDensityPosteriorProbabilities(e, result)
+ * (AssigningFeatureScorer.hh:46-47,126-128) asks of the sum scorer when AbstractMixtureSetEstimator accumulates in
+ * baum-welch mode (AbstractMixtureSetEstimator.cc:134-146,386-395).  Frame t: post[t * ldP + k] = exp(score - s_k) for the
+ * densities k of mixture[t] (0 beyond the mixture's densities; a frame with mixture 0xFFFFFFFF is skipped), and
+ * score[t] (may be NULL) = the sum scorer's score of that mixture, evaluated in the reference's operation order.
+ * ldP >= the largest mixture's density count. */
+int gmm_mixture_posteriors_host(gmm_handle* h, uint32_t T, const float* x, const uint32_t* mixture, float* post,
+                                size_t ldP, float* score);
 
 /* ---- quantized engine (bit-exact SIMD-diagonal-maximum) -------------------------------------- */
 /* qmean [G x Dpad] u8, cov_idx [G], qconst [G] s32, isr_scaled [C x D] f32: the tables exactly as the
@@ -270,9 +289,10 @@ int gmm_kernel_timing(gmm_handle* h, int on);
 int gmm_kernel_time(gmm_handle* h, double* total_ms, uint64_t* launches);
 /* 1 = direct, 2 = tensor: the float kernel the last gmm_upload_float selected. */
 int         gmm_float_kernel(const gmm_handle* h);
-/* Tensor kernel only: MMA products per algorithmic product of the uploaded float model -- 3 (fp16 hi.hi + lo.hi +
- * hi.lo, the default) or 2 (fp16 hi.hi + one e5m2 product for both corrections: GMM_TC_SPLIT=fp8 was set at upload
- * and the model passed the split's guard); 0 when the model is not on the tensor kernel. */
+/* Tensor kernel only: MMA products per algorithmic product of the uploaded float model -- 2 (fp16 hi.hi + one e4m3
+ * product for both corrections: the default for pooled models that pass the packing-time accuracy guard) or 3 (fp16
+ * hi.hi + lo.hi + hi.lo: everything else, and always with GMM_TC_SPLIT=fp16 set at upload); 0 when the model is not on
+ * the tensor kernel. */
 int         gmm_float_split(const gmm_handle* h);
 /* 1 = dp4a (CUDA cores), 2 = integer tensor path: the kernel the last gmm_upload_quant selected (0: no model).
  * Both are bit-identical to the reference; environment GMM_QUANT_KERNEL=dp4a at upload time forces the former. */

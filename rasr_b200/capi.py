@@ -27,8 +27,11 @@ SYMBOLS = [
     ("gmm_set_stream", _i, [_vp, _vp]),
     ("gmm_upload_float", _i, [_vp, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i]),
     ("gmm_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _sz]),
+    ("gmm_score_async", _i, [_vp, _u32, _vp, _vp, _vp, _sz, C.POINTER(C.c_uint64)]),
+    ("gmm_wait", _i, [_vp, C.c_uint64]),
     ("gmm_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _sz]),
     ("gmm_posteriors_device", _i, [_vp, _u32, _vp, _vp]),
+    ("gmm_mixture_posteriors_host", _i, [_vp, _u32, _vp, _vp, _vp, _sz, _vp]),
     ("gmm_upload_quant", _i, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, C.c_float]),
     ("gmm_quant_score_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
     ("gmm_quant_score_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _sz]),
@@ -198,6 +201,19 @@ class Engine:
         self._check(self._lib.gmm_score_host(self._h, T, _ptr(x), _ptr(scores), _ptr(best), ld), "gmm_score_host")
         return scores, best
 
+    def score_async(self, x, scores, best=None, ld=None) -> int:
+        """gmm_score_async: x [T, D], scores [T, ld] (and best) are HOST arrays the caller keeps alive (page-locked for
+        real overlap) until wait(token); returns the token."""
+        T = x.shape[0]
+        ld = self.M if ld is None else int(ld)
+        tok = C.c_uint64(0)
+        self._check(self._lib.gmm_score_async(self._h, int(T), _ptr(x), _ptr(scores), _ptr(best), ld, C.byref(tok)),
+                    "gmm_score_async")
+        return int(tok.value)
+
+    def wait(self, token: int):
+        self._check(self._lib.gmm_wait(self._h, C.c_uint64(int(token))), "gmm_wait")
+
     def score_device(self, T, d_x, d_scores, d_best=None, ld=None):
         """Device pointers (ints or torch tensors); asynchronous on the handle's stream."""
         ld = self.M if ld is None else int(ld)
@@ -207,6 +223,17 @@ class Engine:
     def posteriors_device(self, T, d_x, d_post):
         self._check(self._lib.gmm_posteriors_device(self._h, int(T), _ptr(d_x), _ptr(d_post)),
                     "gmm_posteriors_device")
+
+    def mixture_posteriors_host(self, x, mixture, max_k: int):
+        """Sum scorer: density posteriors of mixture[t] for frame t -> (post [T, max_k] f32, score [T] f32)."""
+        x = _np(x, np.float32)
+        mixture = _np(mixture, np.uint32)
+        T = x.shape[0]
+        post = np.zeros((T, int(max_k)), np.float32)
+        score = np.zeros(T, np.float32)
+        self._check(self._lib.gmm_mixture_posteriors_host(self._h, T, _ptr(x), _ptr(mixture), _ptr(post), int(max_k),
+                                                          _ptr(score)), "gmm_mixture_posteriors_host")
+        return post, score
 
     def subset_ld(self, max_list_length: int) -> int:
         return int(self._lib.gmm_score_subset_ld(self._h, int(max_list_length)))

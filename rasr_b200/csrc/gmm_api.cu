@@ -296,6 +296,14 @@ void gmm_destroy(gmm_handle* h) {
     }
     if (h->laneEvent)
         cudaEventDestroy(h->laneEvent);
+    if (h->copyStream)
+        cudaStreamDestroy(h->copyStream);
+    for (cudaEvent_t e : h->copyEvent)
+        if (e)
+            cudaEventDestroy(e);
+    for (cudaEvent_t e : h->asyncEvent)
+        if (e)
+            cudaEventDestroy(e);
     if (h->lda.matrix)
         cudaFree(h->lda.matrix);
     if (h->ownStream && h->stream)
@@ -329,6 +337,9 @@ int gmm_sync(gmm_handle* h) {
     if (!h)
         return GMM_ERR_ARG;
     GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < gmm_handle::kAsyncLanes; ++i)  // outstanding gmm_score_async calls
+        if (h->asyncToken[i])
+            GMM_CUDA_TRY(h, cudaEventSynchronize(h->asyncEvent[i]));
     return GMM_OK;
 }
 
@@ -430,6 +441,9 @@ int gmm_upload_float(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t
     h->D    = D;
     h->C    = C;
     h->mode = mode;
+    h->maxK = 0;
+    for (uint32_t m = 0; m < M; ++m)
+        h->maxK = std::max(h->maxK, offsets[m + 1] - offsets[m]);
 
     // direct layout: rows padded to a multiple of 4 floats (16/32/48/64/96/128 kernel variants)
     uint32_t DP = D <= 16 ? 16 : D <= 32 ? 32 : D <= 48 ? 48 : D <= 64 ? 64 : D <= 96 ? 96 : 128;
@@ -592,32 +606,29 @@ uint32_t gmm_score_subset_ld(const gmm_handle* h, uint32_t maxListLength) {
     return (h && h->floatValid && h->tensor.valid) ? gmm_tc_subset_ld(h, maxListLength) : 0;
 }
 
-static int copyOut(gmm_handle* h, void* host, const void* dev, uint32_t T, uint32_t M, size_t ld, size_t devLd) {
+static int copyOut(gmm_handle* h, void* host, const void* dev, uint32_t T, uint32_t M, size_t ld, size_t devLd,
+                   cudaStream_t stream = nullptr) {
+    if (!stream)
+        stream = h->stream;
     if (ld == devLd)
-        GMM_CUDA_TRY(h, cudaMemcpyAsync(host, dev, (size_t)T * ld * 4, cudaMemcpyDeviceToHost, h->stream));
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(host, dev, (size_t)T * ld * 4, cudaMemcpyDeviceToHost, stream));
     else
-        GMM_CUDA_TRY(h, cudaMemcpy2DAsync(host, ld * 4, dev, devLd * 4, (size_t)M * 4, T, cudaMemcpyDeviceToHost,
-                                          h->stream));
+        GMM_CUDA_TRY(h, cudaMemcpy2DAsync(host, ld * 4, dev, devLd * 4, (size_t)M * 4, T, cudaMemcpyDeviceToHost, stream));
     return GMM_OK;
 }
 
-int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld) {
-    if (!h)
-        return GMM_ERR_ARG;
-    if (!h->floatValid) {
-        h->setError("gmm_score: no float model uploaded");
-        return GMM_ERR_ARG;
-    }
-    if (T == 0)
-        return GMM_OK;
-    if (ld < h->M || !x || !scores) {
-        h->setError("gmm_score_host: invalid argument");
-        return GMM_ERR_ARG;
-    }
-    cudaSetDevice(h->device);
+// Host frames in, host scores out, everything enqueued and nothing waited for: the body of gmm_score_host and
+// gmm_score_async.  The frames go up in one copy; the batch is scored in up to kCopyEvents chunks on the handle's
+// stream, and every finished chunk's rows go back on a copy stream of their own while the next chunk is scored (the
+// device-to-host copy of 4 * ld bytes per frame is what bounds the call: PCIe).  On return `done` (an
+// event on the copy stream, or the handle's stream for a single chunk) marks the last copy.
+static int scoreHostEnqueue(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld,
+                            cudaStream_t* doneStream) {
     void *dx = nullptr, *ds = nullptr, *db = nullptr;
     int   rc;
-    const size_t devLd = h->M;
+    // device rows: the caller's pitch when it keeps row pieces 16-byte aligned (then one contiguous copy per chunk),
+    // else M rounded up to a multiple of 4 -- the tensor kernel stores aligned row pieces straight from registers
+    const size_t   devLd  = (ld % 4 == 0 && ld <= (size_t)h->M + 1024) ? ld : ((size_t)h->M + 3) / 4 * 4;
     const uint32_t one[2] = {0, T};
     if ((rc = uploadFrames(h, h->D, 1, one, x, &dx)))
         return rc;
@@ -625,14 +636,114 @@ int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uin
         return rc;
     if (best && (rc = h->reserve(SCR_BEST, (size_t)T * devLd * 4, &db)))
         return rc;
-    if ((rc = gmm_score_device(h, T, (const float*)dx, (float*)ds, (uint32_t*)db, devLd)))
-        return rc;
-    if ((rc = copyOut(h, scores, ds, T, h->M, ld, devLd)))
-        return rc;
-    if (best && (rc = copyOut(h, best, db, T, h->M, ld, devLd)))
-        return rc;
-    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    uint32_t nChunks = 1;
+    {
+        const char* e = getenv("GMM_HOST_CHUNKS");
+        nChunks       = e ? (uint32_t)std::max(1, atoi(e)) : (T >= 8192 ? std::min<uint32_t>(8, T / 4096) : 1);
+        nChunks       = std::min<uint32_t>(nChunks, gmm_handle::kCopyEvents);
+    }
+    if (nChunks > 1 && !h->copyStream)
+        GMM_CUDA_TRY(h, cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking));
+    const uint32_t per = ((T + nChunks - 1) / nChunks + 127) / 128 * 128;
+    uint32_t       c   = 0;
+    for (uint32_t t0 = 0; t0 < T; t0 += per, ++c) {
+        const uint32_t n = std::min(per, T - t0);
+        const size_t   o = (size_t)t0 * devLd;
+        if ((rc = gmm_score_device(h, n, (const float*)dx + (size_t)t0 * h->D, (float*)ds + o,
+                                   db ? (uint32_t*)db + o : nullptr, devLd)))
+            return rc;
+        cudaStream_t cs = h->stream;
+        if (nChunks > 1) {
+            if (!h->copyEvent[c])
+                GMM_CUDA_TRY(h, cudaEventCreateWithFlags(&h->copyEvent[c], cudaEventDisableTiming));
+            GMM_CUDA_TRY(h, cudaEventRecord(h->copyEvent[c], h->stream));
+            GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->copyStream, h->copyEvent[c], 0));
+            cs = h->copyStream;
+        }
+        if ((rc = copyOut(h, scores + (size_t)t0 * ld, (float*)ds + o, n, h->M, ld, devLd, cs)))
+            return rc;
+        if (best && (rc = copyOut(h, best + (size_t)t0 * ld, (uint32_t*)db + o, n, h->M, ld, devLd, cs)))
+            return rc;
+    }
+    if (nChunks > 1) {
+        // later work on the handle's stream (it may overwrite the scratch) comes after the copies
+        cudaEvent_t& e = h->copyEvent[gmm_handle::kCopyEvents];
+        if (!e)
+            GMM_CUDA_TRY(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        GMM_CUDA_TRY(h, cudaEventRecord(e, h->copyStream));
+        GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->stream, e, 0));
+    }
+    *doneStream = h->stream;
     return GMM_OK;
+}
+
+static int checkScoreHostArgs(gmm_handle* h, uint32_t T, const float* x, float* scores, size_t ld, const char* who) {
+    if (!h->floatValid) {
+        h->setError(std::string(who) + ": no float model uploaded");
+        return GMM_ERR_ARG;
+    }
+    if (T && (ld < h->M || !x || !scores)) {
+        h->setError(std::string(who) + ": invalid argument");
+        return GMM_ERR_ARG;
+    }
+    return GMM_OK;
+}
+
+int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld) {
+    if (!h)
+        return GMM_ERR_ARG;
+    int rc = checkScoreHostArgs(h, T, x, scores, ld, "gmm_score_host");
+    if (rc || T == 0)
+        return rc;
+    cudaSetDevice(h->device);
+    cudaStream_t done = nullptr;
+    if ((rc = scoreHostEnqueue(h, T, x, scores, best, ld, &done)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(done));
+    return GMM_OK;
+}
+
+int gmm_score_async(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld,
+                    uint64_t* token) {
+    if (!h || !token)
+        return GMM_ERR_ARG;
+    int rc = checkScoreHostArgs(h, T, x, scores, ld, "gmm_score_async");
+    if (rc)
+        return rc;
+    cudaSetDevice(h->device);
+    const int slot = (int)(h->asyncSeq % gmm_handle::kAsyncLanes);
+    if (!h->asyncEvent[slot])
+        GMM_CUDA_TRY(h, cudaEventCreateWithFlags(&h->asyncEvent[slot], cudaEventDisableTiming));
+    if (h->asyncToken[slot])  // the lane's previous call still owns its scratch
+        GMM_CUDA_TRY(h, cudaEventSynchronize(h->asyncEvent[slot]));
+    const int back = h->lane;
+    if ((rc = h->useLane(1 + slot)))
+        return rc;
+    cudaStream_t done = h->stream;
+    if (T)
+        rc = scoreHostEnqueue(h, T, x, scores, best, ld, &done);
+    cudaError_t e = rc ? cudaSuccess : cudaEventRecord(h->asyncEvent[slot], done);
+    h->useLane(back);
+    if (rc)
+        return rc;
+    GMM_CUDA_TRY(h, e);
+    h->asyncToken[slot] = ++h->asyncSeq;
+    *token              = h->asyncToken[slot];
+    return GMM_OK;
+}
+
+int gmm_wait(gmm_handle* h, uint64_t token) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (token == 0 || token > h->asyncSeq) {
+        h->setError("gmm_wait: unknown token");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    for (int i = 0; i < gmm_handle::kAsyncLanes; ++i)
+        if (h->asyncToken[i] == token)
+            GMM_CUDA_TRY(h, cudaEventSynchronize(h->asyncEvent[i]));
+    return GMM_OK;  // an older token: its lane has been reused, which waited for it
 }
 
 int gmm_align_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* d_scores, size_t ld,
@@ -1188,6 +1299,46 @@ int gmm_posteriors_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_
     }
     cudaSetDevice(h->device);
     return gmm_direct_posteriors(h, T, d_x, d_post);
+}
+
+int gmm_mixture_posteriors_host(gmm_handle* h, uint32_t T, const float* x, const uint32_t* mixture, float* post,
+                                size_t ldP, float* score) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!h->floatValid || h->mode != GMM_MODE_SUM) {
+        h->setError("gmm_mixture_posteriors_host: needs a float model uploaded with GMM_MODE_SUM (only the sum scorer "
+                    "has density posteriors, GaussDiagonalMaximumFeatureScorer.cc:291-298)");
+        return GMM_ERR_ARG;
+    }
+    if (T == 0)
+        return GMM_OK;
+    if (!x || !mixture || !post || ldP < h->maxK || (size_t)h->maxK * 4 > 48 * 1024) {
+        h->setError("gmm_mixture_posteriors_host: invalid argument (ldP below the largest mixture?)");
+        return GMM_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    void *dx = nullptr, *dm = nullptr, *dp = nullptr, *ds = nullptr;
+    int   rc;
+    const uint32_t one[2] = {0, T};
+    if ((rc = uploadFrames(h, h->D, 1, one, x, &dx)))
+        return rc;
+    if ((rc = h->reserve(SCR_MISC, (size_t)T * 4, &dm)))
+        return rc;
+    if ((rc = h->reserve(SCR_POST, (size_t)T * h->maxK * 4, &dp)))
+        return rc;
+    if (score && (rc = h->reserve(SCR_ROW, (size_t)T * 4, &ds)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaMemcpyAsync(dm, mixture, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+    GMM_CUDA_TRY(h, cudaMemsetAsync(dp, 0, (size_t)T * h->maxK * 4, h->stream));
+    if ((rc = gmm_direct_mixture_posteriors(h, T, (const float*)dx, (const uint32_t*)dm, (float*)dp, h->maxK, (float*)ds,
+                                            h->maxK)))
+        return rc;
+    GMM_CUDA_TRY(h, cudaMemcpy2DAsync(post, ldP * 4, dp, (size_t)h->maxK * 4, (size_t)h->maxK * 4, T,
+                                      cudaMemcpyDeviceToHost, h->stream));
+    if (score)
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(score, ds, (size_t)T * 4, cudaMemcpyDeviceToHost, h->stream));
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return GMM_OK;
 }
 
 int gmm_upload_quant(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t Dpad, uint32_t C,

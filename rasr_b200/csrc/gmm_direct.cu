@@ -172,7 +172,88 @@ int dispatch(gmm_handle* h, int mode, uint32_t T, const float* d_x, float* d_sco
     }
 }
 
+// Density posteriors of ONE mixture per frame (the training consumer asks for the mixture a frame is aligned to):
+// GaussDiagonalSumFeatureScorer::calculateScoresAndNumberOfDensities / calculateScoreAndDensity /
+// calculateDensityPosteriorProbabilities (GaussDiagonalMaximumFeatureScorer.cc:239-298) in the reference's order:
+// s_k = 0.5f * (w2 + L + dist) in f32 with the 4-lane distance, best = first minimum, sumExp accumulated density by
+// density, score = best - log(sumExp), p_k = exp(score - s_k).  One CTA per frame, one thread per density for the
+// distances, thread 0 for the two sequential passes (K is small; this is not a throughput path).
+// post [T x ldP]: columns >= the mixture's density count are left untouched; frames with mixture 0xFFFFFFFF are skipped.
+__global__ void __launch_bounds__(128) mixture_posteriors_kernel(const float* __restrict__ x, int T, int D, int DP,
+                                                                 const float* __restrict__ mean, const float* __restrict__ isr,
+                                                                 const uint32_t* __restrict__ covIdx,
+                                                                 const float* __restrict__ w2,
+                                                                 const float* __restrict__ logNorm,
+                                                                 const uint32_t* __restrict__ offsets,
+                                                                 const uint32_t* __restrict__ mixture, int M,
+                                                                 float* __restrict__ post, size_t ldP,
+                                                                 float* __restrict__ score) {
+    extern __shared__ float sc[];  // density scores of the frame's mixture
+    const int t = blockIdx.x;
+    if (t >= T)
+        return;
+    const uint32_t m = mixture[t];
+    if (m >= (uint32_t)M)
+        return;
+    const uint32_t a = offsets[m], b = offsets[m + 1];
+    const float*   xt  = x + (size_t)t * D;
+    const int      eff = D & ~3;
+    for (uint32_t g = a + threadIdx.x; g < b; g += blockDim.x) {
+        const uint32_t c  = covIdx[g];
+        const float*   mu = mean + (size_t)g * DP;
+        const float*   is = isr + (size_t)c * DP;
+        float          l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+        for (int d = 0; d < eff; d += 4) {
+            const float d0 = __fmul_rn(__fsub_rn(mu[d], xt[d]), is[d]);
+            const float d1 = __fmul_rn(__fsub_rn(mu[d + 1], xt[d + 1]), is[d + 1]);
+            const float d2 = __fmul_rn(__fsub_rn(mu[d + 2], xt[d + 2]), is[d + 2]);
+            const float d3 = __fmul_rn(__fsub_rn(mu[d + 3], xt[d + 3]), is[d + 3]);
+            l0 = __fadd_rn(l0, __fmul_rn(d0, d0));
+            l1 = __fadd_rn(l1, __fmul_rn(d1, d1));
+            l2 = __fadd_rn(l2, __fmul_rn(d2, d2));
+            l3 = __fadd_rn(l3, __fmul_rn(d3, d3));
+        }
+        float dist = __fadd_rn(0.f, __fadd_rn(__fadd_rn(l0, l1), __fadd_rn(l2, l3)));
+        for (int d = eff; d < D; ++d) {
+            const float dd = __fmul_rn(__fsub_rn(mu[d], xt[d]), is[d]);
+            dist           = __fadd_rn(dist, __fmul_rn(dd, dd));
+        }
+        const float s = __fadd_rn(__fadd_rn(w2[g], logNorm[c]), dist);
+        sc[g - a]     = __fmul_rn(0.5f, s);
+    }
+    __syncthreads();
+    __shared__ float fin;
+    if (threadIdx.x == 0) {
+        float best = 3.402823466e+38f;
+        for (uint32_t k = 0; k < b - a; ++k)
+            if (best > sc[k])
+                best = sc[k];
+        float sumExp = 0.f;
+        for (uint32_t k = 0; k < b - a; ++k)
+            sumExp += expf(best - sc[k]);
+        fin = best - logf(sumExp);
+        if (score)
+            score[t] = fin;
+    }
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < b - a; k += blockDim.x)
+        post[(size_t)t * ldP + k] = expf(fin - sc[k]);
+}
+
 }  // namespace
+
+int gmm_direct_mixture_posteriors(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, float* d_post,
+                                  size_t ldP, float* d_score, uint32_t maxK) {
+    if (T == 0)
+        return GMM_OK;
+    const DirectModel& dm = h->direct;
+    mixture_posteriors_kernel<<<T, 128, (size_t)std::max(1u, maxK) * sizeof(float), h->stream>>>(
+            d_x, (int)T, (int)h->D, (int)dm.DP, dm.mean, dm.isr, dm.covIdx, dm.w2, dm.logNorm, dm.offsets, d_mixture,
+            (int)h->M, d_post, ldP, d_score);
+    h->launches++;
+    GMM_CUDA_TRY(h, cudaGetLastError());
+    return GMM_OK;
+}
 
 int gmm_direct_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld) {
     return dispatch(h, h->mode == GMM_MODE_SUM ? 1 : 0, T, d_x, d_scores, d_best, ld, nullptr);

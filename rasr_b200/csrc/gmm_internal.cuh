@@ -50,7 +50,7 @@ struct TensorModel {
     // regular model: every mixture takes the same number of packed columns (mixCols, a divisor of partW) and none
     // is empty, so mixture m sits at rows (m % mixPerTile) * mixCols of tile m / mixPerTile and a tile over ANY
     // set of mixtures can be assembled from whole swizzle atoms of the canonical image (subset scoring)
-    // GMM_TC_SPLIT=fp8 (experimental, pooled models): part 2 of the operand rows holds e5m2 bytes -- per 32-byte
+    // GMM_TC_SPLIT=fp8 (experimental, pooled models): part 2 of the operand rows holds e4m3 bytes (lo parts times 2^8) -- per 32-byte
     // k-step 16 x lo and 16 x hi of the same dimensions (A: lo | hi, B: hi | lo) -- and ONE kind::f8f6f4 instruction
     // per k-step adds both correction products: 6 MMA instructions per tile instead of 9
     bool      fp8       = false;
@@ -91,8 +91,10 @@ struct LdaModel {
 // quantized scorer on the integer tensor path (gmm_qtc.cu); valid only for models that meet its requirements
 struct QTensorModel {
     bool      valid      = false;
-    uint32_t  kSteps     = 0;       // 32-byte k-steps (K = Dpad rounded up to 32)
-    uint32_t  nAtoms     = 0;       // 64-byte swizzle atoms per operand row
+    uint32_t  K          = 0;       // operand row bytes: Dpad + 16 or 32 spare bytes that carry the constants
+    uint32_t  kSteps     = 0;       // 32-byte k-steps of the contraction (K / 32)
+    uint32_t  nAtoms     = 0;       // 64-byte swizzle atoms per A operand row
+    uint32_t  nAtomsB    = 0;       // ... per B operand row (one more k-step: the variant of the last)
     uint32_t  nTiles     = 0;       // 256-column tiles of the packed B operand
     uint32_t  tileBytes  = 0;       // bytes per B tile image (operand rows, Kc table, TileMeta)
     uint32_t  aTileBytes = 0;
@@ -100,7 +102,7 @@ struct QTensorModel {
     uint32_t  partW      = 128;     // packed columns reduced by one epilogue warp (64: 16 warps)
     uint32_t  maxMixPerPart = 0;
     uint32_t  buffersB   = 0, stagesA = 0;
-    uint32_t  qBase      = 0;       // min c2 - 2 Dmax (wrapping)
+    uint32_t  qBase      = 0;       // max c2 (wrapping)
     uint32_t  qAbsMax    = 0;       // bound on |q| over all frames (f32 path of the final score needs < 2^24)
 };
 
@@ -131,6 +133,7 @@ struct gmm_handle {
     // float engine
     bool        floatValid = false;
     uint32_t    M = 0, G = 0, D = 0, C = 0;
+    uint32_t    maxK = 0;  // most densities in one mixture
     int         mode = GMM_MODE_MAX, kernel = GMM_KERNEL_DIRECT;
     DirectModel direct;
     TensorModel tensor;
@@ -165,6 +168,15 @@ struct gmm_handle {
     cudaStream_t gatherStream        = nullptr;  // column range + one for the join, epoch of the flag words
     cudaEvent_t  gatherEvent[kGatherEvents] = {};
     uint32_t     gatherEpoch         = 0;
+    // gmm_score_host: device-to-host copies of finished chunks run on a stream of their own while the next chunk is
+    // scored; gmm_score_async / gmm_wait: two lanes in turn, one event and token per lane
+    static constexpr int kCopyEvents = 8;
+    cudaStream_t copyStream          = nullptr;
+    cudaEvent_t  copyEvent[kCopyEvents + 1] = {};
+    static constexpr int kAsyncLanes = 2;        // lanes 1 and 2 (kMaxLanes - 1 at most)
+    uint64_t     asyncSeq            = 0;        // tokens handed out so far
+    uint64_t     asyncToken[kAsyncLanes] = {};   // token of the call last enqueued on async lane i (0: none)
+    cudaEvent_t  asyncEvent[kAsyncLanes] = {};   // recorded behind that call's last copy
     HostPool*    pool                = nullptr;  // host threads of the table builders (hostPool())
     std::vector<std::vector<uint32_t>> workerWords;  // ... and one work space per thread
     struct EmissionStamps {                           // per thread: slot of an emission in the segment being listed,
@@ -199,6 +211,8 @@ int gmm_copy_tables(gmm_handle* h, void* d_dst, const void* pinnedSrc, size_t by
 // gmm_direct.cu
 int gmm_direct_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
 int gmm_direct_posteriors(gmm_handle* h, uint32_t T, const float* d_x, float* d_post);
+int gmm_direct_mixture_posteriors(gmm_handle* h, uint32_t T, const float* d_x, const uint32_t* d_mixture, float* d_post,
+                                  size_t ldP, float* d_score, uint32_t maxK);
 // gmm_quant.cu
 int gmm_quant_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q, uint32_t* d_best, float* d_score,
                      uint8_t* d_qx, size_t ld);

@@ -5,23 +5,30 @@
 //
 //   q[t][m] = min_k( qconst_k + sum_d (qmean_k[d] - qx_t[d])^2 )              (first strict minimum)
 //           = min_k( c2_k - 2 dot(qmean_k, qx_t) ) + |qx_t|^2,                  c2_k = qconst_k + |qmean_k|^2
-// The contraction dot() is one dense u8 GEMM: frames x Gaussians, K = Dpad rounded up to 32 bytes, accumulated
-// in s32 in TMEM.  Every partial is an exact integer (dot <= K * 255^2 < 2^23), so nothing is approximated.
+// The contraction dot() is one dense u8 GEMM: frames x Gaussians, accumulated in s32 in TMEM.  Every partial is an
+// exact integer, so nothing is approximated.
 //
-// Arg-min without compare/select chains: with cmin = min_k c2_k over the model and Dmax = K * 255^2,
-//   u_k = (c2_k - cmin) + 2 Dmax - 2 dot_k  >= 0            and   key_k = (u_k << 8) | slot_k
-// orders columns by score first and by density index second, so an unsigned min over keys IS the reference's
-// first-strict-minimum rule.  key_k = Kc_k - (dot_k << 9) with the per-column constant Kc_k = ((c2_k - cmin + 2 Dmax)
-// << 8) | slot_k shipped next to the operand tile: one integer op per accumulator element plus a 3-input min tree.
-// Requirements checked at packing time (else the model is left to the dp4a kernel): one covariance, mixtures of
-// at most 128 densities, (max c2 - min c2) + 2 Dmax < 2^24 - 1 (no wrap-around anywhere: zero-weight densities,
-// whose reference constant is the x86 "integer indefinite" 0x80000000, fail this test and take the exact
-// wrapping path of gmm_quant.cu).
+// No per-column arithmetic in the epilogue: the tensor core adds the per-Gaussian constant itself.  The operand rows
+// are K = Dpad + S bytes long (S = 16 or 32 spare bytes); the frames carry 255, ..., 255, 1 there and column k carries
+// the base-255 digits of a constant, so the contraction over the spare bytes yields that constant exactly.  The k-steps
+// are issued TWICE into the same accumulator, the second time with a variant of the last k-step whose spare bytes hold
+// a second constant:
+//   acc_k = 2 dot_k + E_k,   E_k = E1_k + E2_k = cmax - c2_k >= 0   (cmax = max_k c2_k over the model)
+//   s_k   = c2_k - 2 dot_k = cmax - acc_k,        q = (cmax + |qx|^2) - max_k acc_k
+// so the maximum approximation is a bare unsigned max tree over the TMEM values (VIMNMX3), and the reference's first
+// strict minimum (lowest density index among equal scores) is the max over  key_k = (acc_k << 8) | (255 - slot_k):
+// one integer multiply-add per element, needed only when the arg-min is asked for.  On tiles whose mixtures all have the
+// same shape the (255 - slot) term is a compile-time immediate; other tiles read it from a table shipped with the tile.
+// Requirements checked at packing time (else the model is left to the dp4a kernel): one covariance, mixtures of at most
+// 128 densities, K <= 128, cmax - cmin within what two sets of spare bytes can hold (2 * (255 * 255 * (S - 1) + 254)),
+// 2 Dpad 255^2 + (cmax - cmin) < 2^24 (the key fits 32 bits; nothing wraps: zero-weight densities, whose reference
+// constant is the x86 "integer indefinite" 0x80000000, fail this and take the exact wrapping path of gmm_quant.cu).
 //
 // Layout and pipeline are those of the float tensor kernel (gmm_tc.cu): pre-swizzled tile images in HBM staged
 // by cp.async.bulk, B tile resident per work item, A tiles streaming through a ring, two accumulators in TMEM,
-// tile-indexed ready/done barrier rings, one MMA-issuing lane, eight epilogue warps.
-//   B tile = 256 packed columns: [atoms][256 rows][64 B] u8 | Kc[256] u32 | TileMeta
+// tile-indexed ready/done barrier rings, one MMA-issuing lane, eight or sixteen epilogue warps.
+//   B tile = 256 packed columns: [atoms][256 rows][64 B] u8 (k-steps 0 .. kS-1, then the variant of k-step kS-1)
+//                                | Kc[256] u32 (255 - slot; 0 for a pad column) | TileMeta
 //   A tile = 128 frames:         [atoms][128 rows][64 B] u8          + per-frame |qx|^2 (u32)
 #include <stdlib.h>
 #include <string.h>
@@ -37,7 +44,7 @@ namespace {
 
 constexpr int      kQSwz       = 64;                   // swizzle atom: 64-byte rows hold two 32-byte k-steps
 constexpr int      kQMetaBytes = kTileN * 4 + 48;      // Kc[256] u32, TileMeta
-constexpr uint32_t kNoKey      = 0xFFFFFFFFu;          // pad / filler column: never the minimum
+constexpr uint32_t kNoKey      = 0u;                   // pad / filler column (zero operand row, Kc = 0): never the maximum
 
 struct QKParams {
     const uint8_t*  bTiles;
@@ -51,12 +58,13 @@ struct QKParams {
     float           twoScalingSquared;  // f32 path of the final score (OUT & 4): q / (2 s^2), see qtc_launch
     uint32_t        T;
     uint32_t        nTiles, frameTiles, split;
-    uint32_t        kSteps;      // 32-byte k-steps
-    uint32_t        atoms;       // 64-byte swizzle atoms per operand row
+    uint32_t        kSteps;      // 32-byte k-steps of the contraction (the B image holds one more: the variant)
+    uint32_t        atoms;       // 64-byte swizzle atoms per A operand row
+    uint32_t        atomsB;      // ... per B operand row (k-steps 0 .. kSteps, the last being the variant)
     uint32_t        aTileBytes, bTileBytes;
     uint32_t        stagesA, buffersB;
     uint32_t        stagePitch;  // words per staging row (maxMixPerPart + 1)
-    uint32_t        qBase;       // cmin - 2 Dmax (wrapping u32): q = (key >> 8) + qBase + |qx|^2
+    uint32_t        qBase;       // cmax (wrapping u32): q = qBase + |qx|^2 - max_k acc_k
 };
 
 __device__ __forceinline__ uint8_t quantize_u8(float v) {
@@ -69,10 +77,11 @@ __device__ __forceinline__ uint8_t quantize_u8(float v) {
     return (uint8_t)s;
 }
 
-// Frame preparation: x [T x D] -> A tile images (quantized bytes, swizzled) + |qx|^2 per frame; optionally the plain
-// quantized frames [T x Dpad] for the caller.  Eight lanes share a frame, lane c owns bytes [16c, 16c + 16).
+// Frame preparation: x [T x D] -> A tile images (quantized bytes, swizzled; spare bytes [Dpad, K) = 255, ..., 255, 1,
+// the multipliers of the constants' digits in the B rows) + |qx|^2 per frame; optionally the plain quantized frames
+// [T x Dpad] for the caller.  Eight lanes share a frame, lane c owns bytes [16c, 16c + 16) (K <= 128).
 __global__ void __launch_bounds__(256) qtc_prep_kernel(const float* __restrict__ x, uint32_t T, uint32_t D,
-                                                       uint32_t Dpad, uint32_t frameTiles,
+                                                       uint32_t Dpad, uint32_t K, uint32_t frameTiles,
                                                        const float* __restrict__ isrS, uint32_t atoms,
                                                        uint8_t* __restrict__ aTiles, uint32_t* __restrict__ rowXX,
                                                        uint8_t* __restrict__ qxOut) {
@@ -101,13 +110,17 @@ __global__ void __launch_bounds__(256) qtc_prep_kernel(const float* __restrict__
             xx += __shfl_xor_sync(0xffffffffu, xx, o);
         if (c == 0)
             rowXX[t] = xx;
-        const uint32_t tile = t / kTileM, row = t % kTileM;
-        uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * kQSwz;
-        if (c < chunksAll)  // bytes past Dpad inside the last atom are written as zeros (w == 0)
-            *reinterpret_cast<uint4*>(base + (size_t)(c / 4) * kTileM * kQSwz + swz_offset(row, c % 4, kQSwz)) =
-                    make_uint4(w[0], w[1], w[2], w[3]);
         if (qxOut && t < T && c * 16 < Dpad)
             *reinterpret_cast<uint4*>(qxOut + (size_t)t * Dpad + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        if (c * 16 >= Dpad && c * 16 < K) {  // spare bytes (rows past T as well: their results are never stored)
+            w[0] = w[1] = w[2] = 0xFFFFFFFFu;
+            w[3] = (c * 16 + 16 == K) ? 0x01FFFFFFu : 0xFFFFFFFFu;
+        }
+        const uint32_t tile = t / kTileM, row = t % kTileM;
+        uint8_t*       base = aTiles + (size_t)tile * atoms * kTileM * kQSwz;
+        if (c < chunksAll)  // bytes past K inside the last atom are written as zeros (w == 0)
+            *reinterpret_cast<uint4*>(base + (size_t)(c / 4) * kTileM * kQSwz + swz_offset(row, c % 4, kQSwz)) =
+                    make_uint4(w[0], w[1], w[2], w[3]);
     }
 }
 
@@ -121,46 +134,62 @@ __device__ __forceinline__ void tc_mma_i8(uint32_t dTmem, uint64_t aDesc, uint64
 }
 
 struct QEpiState {
-    uint32_t run;  // running minimum key of the open mixture
+    uint32_t run;  // running maximum (key or raw accumulator) of the open mixture
     uint32_t sp;   // shared-memory address of this row's next staged q (the arg-min plane lies offB behind)
 };
 
-// One 32-column chunk (four 8-column segments) of a row's s32 accumulator.  SP as in the float kernel: > 0 when
-// every mixture of the column part spans exactly SP segments (closing positions become compile-time constants).
+// One 32-column chunk (four 8-column segments) of a row's s32 accumulator (acc = 2 dot + E >= 0).
+// SP > 0: every mixture of the column part spans exactly SP segments and none is empty (TileMeta::uni): closing
+// positions are compile-time constants, and
+//   !WB: the reduction is a max tree over the raw TMEM values, nothing else;
+//    WB: key = (acc << 8) + (255 - slot) with the slot term an immediate.
+// SP = 0: key = (acc << 8) + Kc with Kc read from the tile's table; segEnd bits close the mixtures; a mixture without
+// densities (all its columns pads: key 0) yields the reference's INT_MAX / no density.
 template<int SP, bool WB>
-__device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t xxBase,
+__device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t qbx,
                                            uint32_t offB, QEpiState& st) {
-    // the chunk's 32 per-column constants first (eight 128-bit loads in flight together), then the arithmetic
     uint32_t kc[32];
+    if (SP == 0) {  // the chunk's 32 per-column terms first (eight 128-bit loads in flight together)
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
-        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                     : "=r"(kc[4 * i]), "=r"(kc[4 * i + 1]), "=r"(kc[4 * i + 2]), "=r"(kc[4 * i + 3])
-                     : "r"(kcAddr + ch * 128 + i * 16));
+        for (int i = 0; i < 8; ++i)
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(kc[4 * i]), "=r"(kc[4 * i + 1]), "=r"(kc[4 * i + 2]), "=r"(kc[4 * i + 3])
+                         : "r"(kcAddr + ch * 128 + i * 16));
+    }
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
         const int seg = ch * 4 + s;
         uint32_t  key[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-            key[j] = kc[s * 8 + j] - (v[s * 8 + j] << 9);  // pads: Kc = 0xFFFFFFFF and dot = 0
-        const uint32_t m6 = __vimin3_u32(__vimin3_u32(key[0], key[1], key[2]), __vimin3_u32(key[3], key[4], key[5]),
-                                         min(key[6], key[7]));
+        for (int j = 0; j < 8; ++j) {
+            if (SP > 0 && !WB)
+                key[j] = v[s * 8 + j];
+            else if (SP > 0)
+                key[j] = (v[s * 8 + j] << 8) + (uint32_t)(255 - ((seg % SP) * 8 + j));
+            else
+                key[j] = (v[s * 8 + j] << 8) + kc[s * 8 + j];
+        }
+        const uint32_t m6 = __vimax3_u32(__vimax3_u32(key[0], key[1], key[2]), __vimax3_u32(key[3], key[4], key[5]),
+                                         max(key[6], key[7]));
         bool     close;
         uint32_t m;
         if (SP > 0) {
-            m     = (seg % SP) == 0 ? m6 : min(m6, st.run);
+            m     = (seg % SP) == 0 ? m6 : max(m6, st.run);
             close = (seg % SP) == SP - 1;
         }
         else {
-            m     = min(m6, st.run);
+            m     = max(m6, st.run);
             close = (segEnd >> seg) & 1u;
         }
         if (close) {  // uniform across the warp
-            const bool none = m == kNoKey;  // mixture without densities: the reference leaves INT_MAX / no density
-            sts_u32(st.sp, none ? 0x7FFFFFFFu : (m >> 8) + xxBase);
-            if (WB)
-                sts_u32(st.sp + offB, none ? 0xFFFFFFFFu : (m & 255u));
+            if (SP > 0 && !WB)
+                sts_u32(st.sp, qbx - m);
+            else {
+                const bool none = SP == 0 && m == kNoKey;
+                sts_u32(st.sp, none ? 0x7FFFFFFFu : qbx - (m >> 8));
+                if (WB)
+                    sts_u32(st.sp + offB, none ? 0xFFFFFFFFu : 255u - (m & 255u));
+            }
             st.sp += 4;
             m = kNoKey;
         }
@@ -278,10 +307,13 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                 const uint32_t aLo   = (smem_u32(sA + (size_t)stage * p.aTileBytes) & 0x3FFFF) >> 4;
                 const uint32_t dTmem = tmemBase + (t & 1) * kTileN;
                 if (leader) {
-                    for (uint32_t ks = 0; ks < kS; ++ks) {
+                    // every k-step twice (acc = 2 dot + E1 + E2): the second pass reads the variant of the last k-step,
+                    // stored behind the others in the B image, whose spare bytes hold the second constant
+                    for (uint32_t i = 0; i < 2 * kS; ++i) {
+                        const uint32_t ks = i < kS ? i : i - kS, kb = (i == 2 * kS - 1) ? kS : ks;
                         const uint32_t ao = aLo + (ks / kPerAtom) * (kTileM * SWZ / 16) + (ks % kPerAtom) * 2;
-                        const uint32_t bo = bLo + (ks / kPerAtom) * (kTileN * SWZ / 16) + (ks % kPerAtom) * 2;
-                        tc_mma_i8(dTmem, ((uint64_t)descHi << 32) | ao, ((uint64_t)descHi << 32) | bo, idesc, ks ? 1u : 0u);
+                        const uint32_t bo = bLo + (kb / kPerAtom) * (kTileN * SWZ / 16) + (kb % kPerAtom) * 2;
+                        tc_mma_i8(dTmem, ((uint64_t)descHi << 32) | ao, ((uint64_t)descHi << 32) | bo, idesc, i ? 1u : 0u);
                     }
                     tc_commit(smem_u32(&done[t % kRing]));
                     if (f + 1 == f1)
@@ -317,7 +349,7 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                 continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
-            const uint8_t*  tile = sB + (size_t)b * bBytes + (size_t)p.atoms * kTileN * SWZ;
+            const uint8_t*  tile = sB + (size_t)b * bBytes + (size_t)p.atomsB * kTileN * SWZ;
             const uint32_t  kcAddr = smem_u32(tile) + (uint32_t)part * PW * 4;  // Kc of this warp's columns
             const uint32_t* meta = reinterpret_cast<const uint32_t*>(tile + kTileN * 4);  // TileMeta words
             constexpr uint32_t segMask = (1u << SEGS) - 1u;
@@ -360,10 +392,23 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                     const uint32_t drained = smem_u32(&ready[(t + 2) % kRing]);
                     const uint32_t stBuf = stGrp + (kBufs == 2 ? (t & 1) * stageWarp * 4 : 0u);
                     QEpiState      st;
-                    st.run = kNoKey, st.sp = stBuf + stOff;
+                    st.run = kNoKey, st.sp = stBuf + stOff;  // SP > 0 never reads run before writing it
                     uint32_t va[32];
-                    if (NE == 16) {
-                        // 96 registers per thread: one 32-column chunk (+ its 32 constants) live at a time
+                    if (NE == 16 && SP > 0) {
+                        // no per-column table: both 32-column chunks in flight, the accumulator goes straight back
+                        uint32_t vb[32];
+                        tmem_ld32(taddr, va);
+                        tmem_ld32(taddr + 32, vb);
+                        tmem_ld_wait();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(drained);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
+                    }
+                    else if (NE == 16) {
+                        // 96 registers per thread: one 32-column chunk (+ its 32 table entries) live at a time
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
                         qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st);
@@ -482,18 +527,28 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
     const char*    env = getenv("GMM_QUANT_KERNEL");
     if (G == 0 || M == 0 || qm.C != 1 || (env && !strcmp(env, "dp4a")))
         return GMM_OK;
-    tm.kSteps     = (Dpad + 31) / 32;
+    // K = Dpad + S bytes with S = 16 or 32 spare bytes for the constants' digits; the B image holds one more k-step
+    uint32_t K = (Dpad + 31) / 32 * 32;
+    if (K - Dpad < 16)
+        K += 32;
+    if (K > 128)
+        return GMM_OK;  // qtc_prep_kernel: eight 16-byte chunks per frame
+    const uint32_t S = K - Dpad;
+    tm.K          = K;
+    tm.kSteps     = K / 32;
     tm.nAtoms     = (tm.kSteps * 32 + kQSwz - 1) / kQSwz;
+    tm.nAtomsB    = ((tm.kSteps + 1) * 32 + kQSwz - 1) / kQSwz;
     tm.aTileBytes = tm.nAtoms * kTileM * kQSwz;
-    tm.tileBytes  = tm.nAtoms * kTileN * kQSwz + kQMetaBytes;
-    // value ranges: everything must stay far from 32-bit wrap-around and the key must fit 24 + 8 bits
-    const int64_t dmax = (int64_t)tm.kSteps * 32 * 255 * 255;
+    tm.tileBytes  = tm.nAtomsB * kTileN * kQSwz + kQMetaBytes;
+    // value ranges: the constants must fit the spare bytes, the key 32 bits, and nothing may come near wrap-around
+    const int64_t dmax = (int64_t)Dpad * 255 * 255;
     int64_t       cmin = INT64_MAX, cmax = INT64_MIN;
     for (uint32_t g = 0; g < G; ++g) {
         cmin = std::min<int64_t>(cmin, c2[g]);
         cmax = std::max<int64_t>(cmax, c2[g]);
     }
-    if (cmin < -(1ll << 30) || cmax > (1ll << 30) || (cmax - cmin) + 2 * dmax >= (1ll << 24) - 1)
+    const int64_t cap = (int64_t)255 * 255 * (S - 1) + 254;  // one set of spare bytes: 255 * (b_0 + .. + b_{S-2}) + b_{S-1}
+    if (cmin < -(1ll << 30) || cmax > (1ll << 30) || cmax - cmin > 2 * cap || 2 * dmax + (cmax - cmin) >= (1ll << 24))
         return GMM_OK;
 
     // ---- column assignment: densities of a mixture consecutive, padded to 8, never straddling a 128-column half
@@ -545,6 +600,8 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
             cols.push_back(c);
         }
         mt.segEnd |= 1u << (seg0 + padded / 8 - 1);
+        if (n == 0)
+            mt.segEmpty |= 1u << (seg0 + padded / 8 - 1);
     }
     while (cols.size() % kTileN)
         cols.push_back(pad);
@@ -554,13 +611,13 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
         const uint32_t segsPerPart = partW / 8;
         for (uint32_t pp = 0; pp < partsPerTile; ++pp) {
             const uint32_t mask = (1u << segsPerPart) - 1u;
-            const uint32_t ends = (mt.segEnd >> (pp * segsPerPart)) & mask;
-            for (uint32_t S = 1; S <= 8 && S <= segsPerPart; S *= 2) {
+            const uint32_t ends = (mt.segEnd >> (pp * segsPerPart)) & mask, empt = (mt.segEmpty >> (pp * segsPerPart)) & mask;
+            for (uint32_t SP = 1; SP <= 8 && SP <= segsPerPart; SP *= 2) {
                 uint32_t pat = 0;
-                for (uint32_t b = S - 1; b < segsPerPart; b += S)
+                for (uint32_t b = SP - 1; b < segsPerPart; b += SP)
                     pat |= 1u << b;
-                if (ends == pat)
-                    mt.uni |= S << (8 * pp);
+                if (ends == pat && empt == 0)
+                    mt.uni |= SP << (8 * pp);
             }
         }
     }
@@ -586,26 +643,45 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
 
     // ---- tile images ----
     std::vector<uint8_t> img((size_t)tm.nTiles * tm.tileBytes, 0);
+    auto at = [&](uint8_t* base, uint32_t r, uint32_t byte) -> uint8_t& {  // byte `byte` of operand row r (64-byte atoms)
+        return base[(size_t)(byte / kQSwz) * kTileN * kQSwz + swz_offset(r, (byte % kQSwz) / 16, kQSwz) + (byte % 16)];
+    };
+    auto digits = [&](uint8_t* base, uint32_t r, uint32_t byte0, int64_t v) {  // v = 255 * (b_0 + .. + b_{S-2}) + b_{S-1}
+        int64_t hi = v / 255;
+        for (uint32_t i = 0; i + 1 < S; ++i) {
+            const int64_t b = std::min<int64_t>(255, hi);
+            at(base, r, byte0 + i) = (uint8_t)b;
+            hi -= b;
+        }
+        at(base, r, byte0 + S - 1) = (uint8_t)(v % 255);
+    };
+    const uint32_t last = (tm.kSteps - 1) * 32, var = tm.kSteps * 32;  // byte offsets of the last k-step and its variant
     for (uint32_t t = 0; t < tm.nTiles; ++t) {
         uint8_t*  base = img.data() + (size_t)t * tm.tileBytes;
-        uint32_t* kc   = reinterpret_cast<uint32_t*>(base + (size_t)tm.nAtoms * kTileN * kQSwz);
+        uint32_t* kc   = reinterpret_cast<uint32_t*>(base + (size_t)tm.nAtomsB * kTileN * kQSwz);
         TileMeta* mOut = reinterpret_cast<TileMeta*>(reinterpret_cast<uint8_t*>(kc) + kTileN * 4);
         *mOut          = metas[t];
         for (uint32_t r = 0; r < (uint32_t)kTileN; ++r) {
             const Col& col = cols[(size_t)t * kTileN + r];
             if (col.g == 0xFFFFFFFFu) {
-                kc[r] = kNoKey;  // zero operand row: dot = 0, key stays 0xFFFFFFFF
+                kc[r] = kNoKey;  // zero operand row: acc = 0, key 0
                 continue;
             }
-            kc[r] = (uint32_t)((((int64_t)c2[col.g] - cmin + 2 * dmax) << 8) | col.slot);
+            kc[r] = 255u - col.slot;
             const uint8_t* mu = qmean + (size_t)col.g * Dpad;
-            for (uint32_t d = 0; d < Dpad; ++d)
-                base[(size_t)(d / kQSwz) * kTileN * kQSwz + swz_offset(r, (d % kQSwz) / 16, kQSwz) + (d % 16)] = mu[d];
+            for (uint32_t d = 0; d < Dpad; ++d) {
+                at(base, r, d) = mu[d];
+                if (d >= last)
+                    at(base, r, var + (d - last)) = mu[d];  // the variant repeats the last k-step's data bytes
+            }
+            const int64_t E = cmax - (int64_t)c2[col.g], E1 = std::min(E, cap);
+            digits(base, r, Dpad, E1);
+            digits(base, r, var + (Dpad - last), E - E1);
         }
     }
-    tm.qBase = (uint32_t)(cmin - 2 * dmax);
-    // |q| <= max(|cmin|, |cmax + Dmax|): q = c2 - 2 dot + |qx|^2 = qconst + |qmean - qx|^2 with the distance in [0, Dmax]
-    // and qconst = c2 - |qmean|^2 >= cmin - Dmax
+    tm.qBase = (uint32_t)cmax;
+    // |q| <= max(|cmin - Dmax|, |cmax + Dmax|): q = qconst + |qmean - qx|^2 with the distance in [0, Dmax] and
+    // qconst = c2 - |qmean|^2 >= cmin - Dmax
     tm.qAbsMax = (uint32_t)std::min<int64_t>(0x7FFFFFFF, std::max<int64_t>(std::llabs(cmin - dmax), std::llabs(cmax + dmax)));
     int rc;
     if ((rc = h->upload((void**)&tm.bTiles, img.data(), img.size(), true)))
@@ -654,7 +730,7 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
         return rc;
     {
         const int blocks = (int)std::min<uint32_t>((FT * kTileM + 31) / 32, (uint32_t)h->smCount * 16);
-        qtc_prep_kernel<<<blocks, 256, 0, h->stream>>>(d_x, T, qm.D, qm.Dpad, FT, qm.isrS, tm.nAtoms, (uint8_t*)aT,
+        qtc_prep_kernel<<<blocks, 256, 0, h->stream>>>(d_x, T, qm.D, qm.Dpad, tm.K, FT, qm.isrS, tm.nAtoms, (uint8_t*)aT,
                                                        (uint32_t*)rT, d_qx);
         h->launches++;
         GMM_CUDA_TRY(h, cudaGetLastError());
@@ -673,6 +749,7 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     p.frameTiles     = FT;
     p.kSteps         = tm.kSteps;
     p.atoms          = tm.nAtoms;
+    p.atomsB         = tm.nAtomsB;
     p.aTileBytes     = tm.aTileBytes;
     p.bTileBytes     = tm.tileBytes;
     p.stagesA        = tm.stagesA;

@@ -45,6 +45,13 @@
 
 namespace {
 
+// The 6-instruction operand split: the correction operands are e4m3 (4 significant bits).  A lo part is ~2^-12 of its
+// value, far below e4m3's range next to the hi parts it multiplies, so lo parts are stored times 2^kLoShift: the e4m3
+// instructions leave 2^kLoShift * (x_lo.mu_hi + x_hi.mu_lo) in the accumulator and the FIRST fp16 instruction, issued
+// after them, scales the accumulator input back (tcgen05.mma scale-input-d: D = A.B + D * 2^-kLoShift, exact).
+constexpr int   kLoShift = 8;
+constexpr float kLoScale = 256.f;
+
 struct KParams {
     const uint8_t* bTiles;
     const uint8_t* aTiles;
@@ -55,7 +62,7 @@ struct KParams {
     uint32_t       T;
     uint32_t       nTiles, frameTiles, split;  // items = nTiles * split
     uint32_t       kSteps;                     // k-steps (16 elements) per precision part
-    uint32_t       fp8;                        // part 2 holds e5m2 corrections (TensorModel::fp8)
+    uint32_t       fp8;                        // part 2 holds e4m3 corrections (TensorModel::fp8)
     uint32_t       atoms;                      // swizzle atoms per operand row
     uint32_t       aTileBytes, bTileBytes;     // bTileBytes includes c / slot / meta
     uint32_t       stagesA, buffersB;
@@ -63,6 +70,7 @@ struct KParams {
     const uint32_t* itemTab;                   // subset scoring: 8 words per item {B tile, f0, f1, rowBase, rowEnd}
     uint32_t       nItems;
     unsigned long long* dbg;                   // GMM_TC_DEBUG: per-CTA cycle counters of the MMA thread
+    uint32_t       directStores;               // 0: always stage and store coalesced (GMM_TC_STORES=staged)
 };
 
 struct EpiState {
@@ -76,10 +84,12 @@ struct EpiState {
 // approximation is a bare min tree over TMEM values; a closing segment stages the mixture's score.
 // SP > 0: every mixture of this column part spans exactly SP segments and none is empty (a property of the packed
 // tile, TileMeta::uni), so the closing positions are compile-time constants; SP = 0: driven by the segEnd bits.
+// res != nullptr (SP > 0, maximum approximation without arg-min): the mixture scores stay in registers, res[seg / SP],
+// and the caller stores the row piece straight from them (no staging).
 template<int MODE, bool BEST, int SP>
 __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase, const uint16_t* __restrict__ slots,
                                           uint32_t segEnd, uint32_t segEmpty, uint64_t liveBits, float rt, float rs,
-                                          uint32_t offB, EpiState& st) {
+                                          uint32_t offB, EpiState& st, float* res = nullptr) {
     constexpr float kLn2 = 0.69314718055994530942f;
     const float     hl2e = 0.72134752044448170368f * rs;  // 0.5 * log2(e) * rowScale
 #pragma unroll
@@ -92,18 +102,25 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
         if (MODE == 0 && !BEST) {
             // three-input min tree; a closing segment stores 0.5 * (min * rowScale + rowTerm)
             // = fma(min, 0.5 rowScale, 0.5 rowTerm) (rowScale is a power of two, so both roundings agree)
-            const float m6 = fminf(fminf(fminf(u[0], u[1]), u[2]), fminf(fminf(u[3], u[4]), u[5]));
+            // four 3-input minima per segment: (u0 u1 u2) (u3 u4 u5) (u6 u7 run) and the three results
+            const float ma = fminf(fminf(u[0], u[1]), u[2]), mb = fminf(fminf(u[3], u[4]), u[5]);
             if (SP > 0) {
                 const bool  first = (seg % SP) == 0, last = (seg % SP) == SP - 1;  // compile-time after unrolling
-                const float m = first ? fminf(m6, fminf(u[6], u[7])) : fminf(m6, fminf(fminf(u[6], u[7]), st.run));
+                const float mc = first ? fminf(u[6], u[7]) : fminf(fminf(u[6], u[7]), st.run);
+                const float m  = fminf(fminf(ma, mb), mc);
                 if (last) {
-                    sts_f32(st.sp, fminf(fmaf(m, 0.5f * rs, 0.5f * rt), 0.5f * (FLT_MAX + rt)));
-                    st.sp += 4;
+                    const float sc = fminf(fmaf(m, 0.5f * rs, 0.5f * rt), 0.5f * (FLT_MAX + rt));
+                    if (res)
+                        res[seg / SP] = sc;
+                    else {
+                        sts_f32(st.sp, sc);
+                        st.sp += 4;
+                    }
                 }
                 st.run = m;
                 continue;
             }
-            const float m = fminf(m6, fminf(fminf(u[6], u[7]), st.run));
+            const float m = fminf(fminf(ma, mb), fminf(fminf(u[6], u[7]), st.run));
             const bool  close = (segEnd >> seg) & 1u;
             float       sc    = fminf(fmaf(m, 0.5f * rs, 0.5f * rt), 0.5f * (FLT_MAX + rt));
             sc                = ((segEmpty >> seg) & 1u) ? 0.5f * (FLT_MAX + rt) : sc;
@@ -354,16 +371,22 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                 const uint32_t aLo   = (smem_u32(sA + (size_t)stage * p.aTileBytes) & 0x3FFFF) >> 4;
                 const uint32_t dTmem = tmemBase + (t & 1) * kTileN;
                 if (leader && p.fp8) {
-                    // per k-step: hi.hi in fp16, then ONE e5m2 instruction over part 2 (x_lo.mu_hi + x_hi.mu_lo)
-                    constexpr uint32_t idesc8 = idesc | (1u << 7) | (1u << 10);
+                    // first ONE e4m3 instruction per k-step over part 2 (2^8 (x_lo.mu_hi + x_hi.mu_lo)), then hi.hi in
+                    // fp16, whose first instruction takes the accumulator scaled by 2^-8; the e4m3 formats are code 0 of
+                    // kind::f8f6f4, so the instruction descriptor is the fp16 one
                     for (uint32_t ks = 0; ks < kS; ++ks) {
                         const uint32_t kl = kS + ks;
-                        const uint32_t ah = aLo + (ks / kPerAtom) * (kTileM * SWZ / 16) + (ks % kPerAtom) * 2;
                         const uint32_t al = aLo + (kl / kPerAtom) * (kTileM * SWZ / 16) + (kl % kPerAtom) * 2;
-                        const uint32_t bh = bLo + (ks / kPerAtom) * (kTileN * SWZ / 16) + (ks % kPerAtom) * 2;
                         const uint32_t bl = bLo + (kl / kPerAtom) * (kTileN * SWZ / 16) + (kl % kPerAtom) * 2;
-                        tc_mma_f16(dTmem, ((uint64_t)descHi << 32) | ah, ((uint64_t)descHi << 32) | bh, idesc, ks ? 1u : 0u);
-                        tc_mma_f8(dTmem, ((uint64_t)descHi << 32) | al, ((uint64_t)descHi << 32) | bl, idesc8, 1u);
+                        tc_mma_f8(dTmem, ((uint64_t)descHi << 32) | al, ((uint64_t)descHi << 32) | bl, idesc, ks ? 1u : 0u);
+                    }
+                    for (uint32_t ks = 0; ks < kS; ++ks) {
+                        const uint32_t ah = aLo + (ks / kPerAtom) * (kTileM * SWZ / 16) + (ks % kPerAtom) * 2;
+                        const uint32_t bh = bLo + (ks / kPerAtom) * (kTileN * SWZ / 16) + (ks % kPerAtom) * 2;
+                        if (ks == 0)
+                            tc_mma_f16_scaled<kLoShift>(dTmem, ((uint64_t)descHi << 32) | ah, ((uint64_t)descHi << 32) | bh, idesc);
+                        else
+                            tc_mma_f16(dTmem, ((uint64_t)descHi << 32) | ah, ((uint64_t)descHi << 32) | bh, idesc, 1u);
                     }
                     tc_commit(smem_u32(&done[t % kRing]));
                     if (f + 1 == f1)
@@ -394,7 +417,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             }
         }
         if (p.dbg && leader) {
-            unsigned long long* d = p.dbg + blockIdx.x * 8;
+            unsigned long long* d = p.dbg + blockIdx.x * 16;
             d[0] = clock64() - tStart, d[1] = wR, d[2] = wI, d[3] = 0, d[4] = t, d[5] = itemCount;
         }
     }
@@ -406,6 +429,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
         const uint32_t offB   = NE * stageWarp * 4;                              // index plane behind the scores
         const ptrdiff_t bestDelta = BEST ? reinterpret_cast<const char*>(p.best) - reinterpret_cast<const char*>(p.scores) : 0;
         uint32_t       itemCount = 0, t = 0;
+        long long      eW = 0, eL = 0, eC = 0, eS = 0, ec0 = 0;  // GMM_TC_DEBUG: where this warp's cycles go
         if (lane == 0) {  // both accumulators start out drained
             mbar_arrive(smem_u32(&ready[0]));
             mbar_arrive(smem_u32(&ready[1]));
@@ -437,8 +461,17 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
             const float2*   rip = p.rowInfo + (size_t)f0 * kTileM + q * 32 + lane;
             // the tile loop, specialised on the tile's mixture shape when it is uniform (see epi_chunk)
-            auto tiles = [&](auto spTag) {
-                constexpr int SP = decltype(spTag)::value;
+            // DIRECT (maximum approximation without arg-min on uniform parts, row pieces 8- / 16-byte aligned): a lane
+            // keeps its frame's R = SEGS / SP mixture scores in registers and writes the row piece itself with 64- /
+            // 128-bit stores -- no staging, no shared-memory round trip, a fifth of the store path's instructions (the
+            // epilogue is bound by the ALU pipe: 2 warps per scheduler at one instruction per 2 cycles)
+            char* gLane = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + q * 32 + lane) * p.ld + mixBase);
+            auto tiles = [&](auto spTag, auto dirTag) {
+                constexpr int  SP     = decltype(spTag)::value;
+                constexpr bool DIRECT = decltype(dirTag)::value && MODE == 0 && !BEST && SP > 0;
+                constexpr int  R      = DIRECT ? SEGS / SP : 1;
+                float          res[R];
+                float* const   resp = DIRECT ? res : nullptr;
                 float2 riNext = *rip;  // row term / scale of the next tile's row, fetched one tile ahead
                 for (uint32_t f = f0; f < f1; ++f, ++t) {
                     const uint32_t acc = t & 1;
@@ -446,8 +479,10 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     rip += kTileM;
                     if (f + 1 < f1)
                         riNext = *rip;
+                    if (p.dbg) ec0 = clock64();
                     mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
                     tc_fence_after();
+                    if (p.dbg) { const long long c1 = clock64(); eW += c1 - ec0; ec0 = c1; }
                     const uint32_t taddr    = tmemBase + ((uint32_t)(q * 32) << 16) + acc * kTileN + part * PW;
                     const uint32_t drained  = smem_u32(&ready[(t + 2) % kRing]);  // tile t + 2 reuses this accumulator
                     EpiState st;
@@ -467,8 +502,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                             epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st);
                         }
                         else {
-                            epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
-                            epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                            epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
+                            epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
                         }
                     }
                     else {
@@ -476,26 +511,43 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 32, vb);
-                        epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 64, va);
-                        epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 96, vb);
-                        epi_chunk<MODE, BEST, SP>(va, 2, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        epi_chunk<MODE, BEST, SP>(va, 2, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
                         tmem_ld_wait();
                         // accumulator drained into registers: hand it back to the MMA warp before finishing the tile
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        epi_chunk<MODE, BEST, SP>(vb, 3, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st);
+                        if (p.dbg) { const long long c1 = clock64(); eL += c1 - ec0; ec0 = c1; }
+                        epi_chunk<MODE, BEST, SP>(vb, 3, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
+                    }
+                    if (p.dbg) { const long long c1 = clock64(); eC += c1 - ec0; ec0 = c1; }
+                    const uint32_t rbase = ir.rowBase + (f - f0) * kTileM + q * 32;
+                    const uint32_t rows  = min(32u, ir.rowEnd > rbase ? ir.rowEnd - rbase : 0u);
+                    if (DIRECT) {
+                        if ((uint32_t)lane < rows) {
+                            if (R >= 4) {
+#pragma unroll
+                                for (int i = 0; i < R / 4; ++i)
+                                    reinterpret_cast<float4*>(gLane)[i] =
+                                            make_float4(res[4 * i], res[4 * i + 1], res[4 * i + 2], res[4 * i + 3]);
+                            }
+                            else
+                                *reinterpret_cast<float2*>(gLane) = make_float2(res[0], res[R > 1 ? 1 : 0]);
+                        }
+                        gLane += gTileStep;
+                        if (p.dbg) eS += clock64() - ec0;
+                        continue;
                     }
                     __syncwarp();
                     // coalesced store of the staged [32 rows x nMix] block: nMix passes of 32 consecutive elements;
                     // pointers advance by per-item constants (a pass that wraps past a row end takes the `w` step)
-                    const uint32_t rbase = ir.rowBase + (f - f0) * kTileM + q * 32;
-                    const uint32_t rows  = min(32u, ir.rowEnd > rbase ? ir.rowEnd - rbase : 0u);
                     char*          gs    = gTile;
                     uint32_t       ss    = ssLane;
                     gTile += gTileStep;
@@ -525,20 +577,37 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                         }
                     }
                     __syncwarp();
+                    if (p.dbg) eS += clock64() - ec0;
                 }
             };
             // TileMeta::uni; the full-sum scorer is specialised on it with 16 epilogue warps (its default)
             const uint32_t uni = (MODE == 0 || NE == 16) ? ((meta[10] >> (8 * part)) & 0xFFu) : 0u;
+            // row pieces of R = SEGS / uni floats: 16-byte stores for R >= 4, 8-byte for R = 2
+            const uint32_t piece  = uni ? min(16u, (uint32_t)(SEGS / max(uni, 1u)) * 4u) : 0u;
+            const bool     direct = MODE == 0 && !BEST && piece >= 8 && p.directStores &&
+                                ((p.ld * 4) % piece) == 0 && ((mixBase * 4) % piece) == 0 &&
+                                (reinterpret_cast<uintptr_t>(p.scores) % piece) == 0;
+            auto run = [&](auto spTag) {
+                if constexpr (MODE == 0 && !BEST && decltype(spTag)::value > 0) {
+                    if (direct)
+                        return tiles(spTag, std::true_type{});
+                }
+                tiles(spTag, std::false_type{});
+            };
             switch (uni) {
-                case 1: tiles(std::integral_constant<int, 1>{}); break;
-                case 2: tiles(std::integral_constant<int, 2>{}); break;
-                case 4: tiles(std::integral_constant<int, 4>{}); break;
-                case 8: tiles(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
-                default: tiles(std::integral_constant<int, 0>{}); break;
+                case 1: run(std::integral_constant<int, 1>{}); break;
+                case 2: run(std::integral_constant<int, 2>{}); break;
+                case 4: run(std::integral_constant<int, 4>{}); break;
+                case 8: run(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
+                default: run(std::integral_constant<int, 0>{}); break;
             }
             // this warp no longer reads slot / meta of the B buffer
             if (lane == 0)
                 mbar_arrive(smem_u32(&emptyB[b]));
+        }
+        if (p.dbg && e == 0 && lane == 0) {
+            unsigned long long* d = p.dbg + blockIdx.x * 16;
+            d[8] = eW, d[9] = eL, d[10] = eC, d[11] = eS;
         }
     }
 
@@ -559,7 +628,6 @@ template<int SWZ, int MODE, bool BEST>
 __global__ void __launch_bounds__(32 * (kEpiWarp0 + 16), 1) tc_score_kernel16(const KParams p) {
     tc_score_body<SWZ, MODE, BEST, 16>(p);
 }
-
 __device__ __forceinline__ void split_fp16(float v, __half& hi, __half& lo) {
     v  = fminf(fmaxf(v, -60000.f), 60000.f);
     hi = __float2half_rn(v);
@@ -625,12 +693,14 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ 
             vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
             ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
         }
-        // power-of-two row scale: largest |a| / rs <= 16384 (non-finite frames are passed through clamped)
-        float rs = 1.f;
-        if (vmax > 16384.f && vmax < 3.0e38f) {
+        // power-of-two row scale: largest |a| / rs <= 16384 (non-finite frames are passed through clamped); with the
+        // e4m3 correction operands <= 256, their largest finite value being 448
+        float       rs    = 1.f;
+        const float limit = fp8 ? 256.f : 16384.f;
+        if (vmax > limit && vmax < 3.0e38f) {
             int e;
             frexpf(vmax, &e);  // vmax = m * 2^e, m in [0.5, 1)
-            rs = ldexpf(1.f, e - 14);
+            rs = ldexpf(1.f, e - (fp8 ? 8 : 14));
         }
         const float inv = 1.f / rs;
         if (c == 0)
@@ -652,8 +722,8 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(const float* __restrict__ 
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const float a = v[j] * inv;
-                    l8[j]         = (uint8_t)__nv_cvt_float_to_fp8(a - __half2float(hi[j]), __NV_SATFINITE, __NV_E5M2);
-                    h8[j]         = (uint8_t)__nv_cvt_float_to_fp8(a, __NV_SATFINITE, __NV_E5M2);
+                    l8[j] = (uint8_t)__nv_cvt_float_to_fp8((a - __half2float(hi[j])) * kLoScale, __NV_SATFINITE, __NV_E4M3);
+                    h8[j] = (uint8_t)__nv_cvt_float_to_fp8(a, __NV_SATFINITE, __NV_E4M3);
                 }
                 const uint32_t cpa = swz / 16, cLo = kSteps * 2 + (c / 2) * 2, cHi = cLo + 1, half8 = (c & 1) * 8;
                 *reinterpret_cast<uint2*>(base + (size_t)(cLo / cpa) * kTileM * swz + swz_offset(row, cLo % cpa, swz) + half8) =
@@ -709,13 +779,16 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     const uint32_t M = h->M, G = h->G, D = h->D, C = h->C;
     if (G == 0 || M == 0)
         return GMM_OK;
+    // 64-byte swizzle atoms by default: an operand row of 45 dimensions is 192 bytes = three 64-byte atoms (two 128-byte
+    // atoms would carry 64 bytes of padding per row), which leaves room for four A stages beside two B buffers instead of
+    // two -- 4501x16: 0.391 -> 0.368 ms per 32000 frames, 12001x64: 1.086 -> 1.033 ms.  GMM_TC_SWIZZLE=128 selects the other.
     const char* env = getenv("GMM_TC_SWIZZLE");
-    tm.swz          = (env && atoi(env) == 64) ? 64 : 128;
+    tm.swz          = (env && atoi(env) == 128) ? 128 : 64;
     tm.pooled       = (C == 1);
     bool fp8Forced  = false;
     {
-        // Default: fp16 hi.hi + ONE e5m2 product for both corrections wherever the guard below allows it (pooled models);
-        // "fp16": always three fp16 products; "fp8!": the e5m2 split regardless of the guard (experiments)
+        // Default: fp16 hi.hi + ONE e4m3 product for both corrections wherever the guard below allows it (pooled models);
+        // "fp16": always three fp16 products; "fp8!": the e4m3 split regardless of the guard (experiments)
         const char* split = getenv("GMM_TC_SPLIT");
         fp8Forced         = split && !strcmp(split, "fp8!");
         tm.fp8            = !(split && !strcmp(split, "fp16")) && tm.pooled;
@@ -865,14 +938,16 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     for (uint32_t d = 0; d < D; ++d)
         ctrF[d] = nLive ? (float)(ctr[d] / (double)nLive) : 0.f;
     if (tm.fp8 && !fp8Forced) {
-        // The e5m2 corrections hold the 1e-4 bar only for compact models.  Predicted error of a score:
-        // both correction products carry a relative rounding error of up to 2^-4 + 2^-4 on terms of size 2^-12 |a_d b_d|,
-        // i.e. about 2^-13 sqrt(sum_d a_d^2 b_d^2) per score when the roundings are independent; for a frame drawn near
-        // Gaussian b (a = b + unit noise, the pairs with the SMALLEST scores) that is 2^-13 q(b), q(b)^2 = sum_d (b_d^2 + 1)
-        // b_d^2, against a score of at least sMin = (min_g (w2 + L) + D - 3 sqrt(2D)) / 2.  Emulation over D = 9..64 and
-        // mean spreads 0.5..6 sigma (profiles/split_guard_r02.txt) finds the largest relative error of a whole batch at
-        // 0.34..0.65 of  pred = 2^-13 rms_g q / sMin  once it matters (pred >= 6e-5): the split is taken for pred <= 1.5e-4
-        // (cfg1 / cfg3: 1.3e-4, emulated and measured errors 5e-5).  D < 9 averages too few roundings: three products.
+        // The e4m3 corrections hold the 1e-4 bar only for compact models.  Predicted error of a score:
+        // the correction products carry relative rounding errors on terms of size 2^-12 |a_d b_d|, about
+        // 2^-13 sqrt(sum_d a_d^2 b_d^2) per score when the roundings are independent; for a frame drawn near Gaussian b
+        // (a = b + unit noise, the pairs with the SMALLEST scores) that is 2^-13 q(b), q(b)^2 = sum_d (b_d^2 + 1) b_d^2,
+        // against a score of at least sMin = (min_g (w2 + L) + D - 3 sqrt(2D)) / 2.  Emulation over D = 9..64, mean spreads
+        // 0.5..4 sigma and 21 seeds at the 2-sigma spread of the benchmark models (profiles/split_guard_r02.txt) finds the
+        // largest relative error of a whole batch at <= 0.33 of  pred = 2^-13 rms_g q / sMin  for D >= 16 (<= 0.51 at D = 9):
+        // the split is taken for pred <= 1.5e-4 (D >= 16; expected worst error 5e-5) or 1.0e-4 (9 <= D < 16); cfg1 / cfg3:
+        // pred 1.3e-4, emulated errors 1.9..3.7e-5.  D < 9 averages too few roundings: three products.
+        // (e5m2 operands, the first version of this split, reached 1.13e-4 on one of those seeds: not enough margin.)
         double q2 = 0.0, cMin = 1e300;
         size_t n  = 0;
         for (const Col& c : cols)
@@ -888,7 +963,7 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
             }
         const double sMin = std::max(1.0, 0.5 * cMin + 0.5 * std::max(0.0, (double)D - 3.0 * sqrt(2.0 * D)));
         const double pred = n ? ldexp(sqrt(q2 / (double)n), -13) / sMin : 0.0;
-        if (D < 9 || !(pred <= 1.5e-4))
+        if (D < 9 || !(pred <= (D >= 16 ? 1.5e-4 : 1.0e-4)))
             tm.fp8 = false;
     }
     if (tm.pooled) {
@@ -969,8 +1044,8 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
                     __half hh;
                     memcpy(&hh, &hi, 2);
                     const float    v   = std::min(std::max(row[k], -60000.f), 60000.f);
-                    const uint8_t  h8  = (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E5M2);
-                    const uint8_t  l8  = (uint8_t)__nv_cvt_float_to_fp8(v - __half2float(hh), __NV_SATFINITE, __NV_E5M2);
+                    const uint8_t  h8  = (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E4M3);
+                    const uint8_t  l8  = (uint8_t)__nv_cvt_float_to_fp8((v - __half2float(hh)) * kLoScale, __NV_SATFINITE, __NV_E4M3);
                     const uint32_t cpa = tm.swz / 16, cH = tm.kSteps * 2 + (k / 16) * 2, cL = cH + 1;
                     base[(size_t)(cH / cpa) * kTileN * tm.swz + swz_offset(r, cH % cpa, tm.swz) + k % 16] = h8;
                     base[(size_t)(cL / cpa) * kTileN * tm.swz + swz_offset(r, cL % cpa, tm.swz) + k % 16] = l8;
@@ -1089,10 +1164,14 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     p.buffersB   = tm.buffersB;
     p.stagePitch = tm.maxMixPerPart + 1;
     p.dbg        = nullptr;
+    {
+        const char* e  = getenv("GMM_TC_STORES");
+        p.directStores = (e && !strcmp(e, "staged")) ? 0u : 1u;
+    }
     const bool debug = getenv("GMM_TC_DEBUG") != nullptr;
     if (debug) {
         void* d = nullptr;
-        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 64, &d)))
+        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 128, &d)))
             return rc;
         p.dbg = (unsigned long long*)d;
     }
@@ -1143,13 +1222,20 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     h->launches++;
     GMM_CUDA_TRY(h, e);
     if (debug) {  // development aid: where the MMA-issuing thread spends its cycles
-        std::vector<unsigned long long> d((size_t)h->smCount * 8);
+        std::vector<unsigned long long> d((size_t)h->smCount * 16);
         GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
         GMM_CUDA_TRY(h, cudaMemcpy(d.data(), p.dbg, d.size() * 8, cudaMemcpyDeviceToHost));
         double tot = 0, wR = 0, wI = 0, wC = 0, tiles = 0;
-        for (int c = 0; c < grid; ++c)
-            tot += d[c * 8], wR += d[c * 8 + 1], wI += d[c * 8 + 2], wC += d[c * 8 + 3], tiles += d[c * 8 + 4];
+        double eW = 0, eL = 0, eC = 0, eS = 0;
+        for (int c = 0; c < grid; ++c) {
+            tot += d[c * 16], wR += d[c * 16 + 1], wI += d[c * 16 + 2], wC += d[c * 16 + 3], tiles += d[c * 16 + 4];
+            eW += d[c * 16 + 8], eL += d[c * 16 + 9], eC += d[c * 16 + 10], eS += d[c * 16 + 11];
+        }
         tiles = std::max(1.0, tiles);
+        fprintf(stderr,
+                "[gmm_tc] epilogue warp 0, cycles per tile: wait-for-MMA %.0f + TMEM drain (loads, first three chunks) %.0f + "
+                "last chunk %.0f + stores %.0f\n",
+                eW / tiles, eL / tiles, eC / tiles, eS / tiles);
         fprintf(stderr,
                 "[gmm_tc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u | MMA thread, cycles per tile: "
                 "total %.0f = wait-ready %.0f + issue+commit %.0f + other (%.0f)\n",

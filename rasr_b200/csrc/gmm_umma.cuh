@@ -82,6 +82,15 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t dTmem, uint64_t aDesc, uint6
             "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
             : "memory");
 }
+// accumulating fp16 MMA whose accumulator INPUT is scaled: D = A.B + D * 2^-SHIFT (scale-input-d, kind::f16 / tf32 only)
+template<int SHIFT>
+__device__ __forceinline__ void tc_mma_f16_scaled(uint32_t dTmem, uint64_t aDesc, uint64_t bDesc, uint32_t idesc) {
+    asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, 1, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p, %4;\n\t}" ::"r"(dTmem),
+            "l"(aDesc), "l"(bDesc), "r"(idesc), "n"(SHIFT)
+            : "memory");
+}
 // 8-bit floating point operands (formats in the instruction descriptor), K = 32 bytes per instruction
 __device__ __forceinline__ void tc_mma_f8(uint32_t dTmem, uint64_t aDesc, uint64_t bDesc, uint32_t idesc,
                                           uint32_t accumulate) {

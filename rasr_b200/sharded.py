@@ -90,14 +90,19 @@ def to_frame_major(gathered, M: int):
 class MixtureShardedScorer:
     """One rank of the mixture-sharded float scorer: its own engine over mixtures [m0, m1)."""
 
-    def __init__(self, float_tables: dict, rank: int, world: int, dist, device: int, mode=0, kernel=0):
+    def __init__(self, float_tables: dict, rank: int, world: int, dist, device: int, mode=0, kernel=0,
+                 total_mixtures: int | None = None):
+        """float_tables: the whole model (sharded here), or -- with total_mixtures = M given -- this rank's shard only
+        (mixtures [m0, m1) of an M-mixture model: a rank of a large model need not hold the other shards' tables)."""
         import torch
         from . import capi
-        self.M = int(len(float_tables["offsets"]) - 1)
+        self.M = int(len(float_tables["offsets"]) - 1) if total_mixtures is None else int(total_mixtures)
         self.rank, self.world, self.dist = rank, world, dist
         self.Mp = shard_width(self.M, world)
         self.m0, self.m1 = mixture_range(self.M, rank, world)
-        sub = shard_float_tables(float_tables, self.m0, self.m1)
+        sub = shard_float_tables(float_tables, self.m0, self.m1) if total_mixtures is None else float_tables
+        if int(len(sub["offsets"]) - 1) != self.m1 - self.m0:
+            raise ValueError("the shard's tables do not hold this rank's mixtures")
         self.engine = capi.Engine(device)
         self.engine.upload_float(sub["offsets"], sub["mean"], sub["isr"], sub["cov_idx"], sub["w2"], sub["log_norm"],
                                  mode=mode, kernel=kernel)
@@ -140,19 +145,21 @@ class PushMixtureShardedScorer:
     FLAG_WORDS = 32
 
     def __init__(self, float_tables: dict, rank: int, world: int, dist, device: int, max_frames: int, mode=0,
-                 chunks: int = 4, row_pad: int = 0):
+                 chunks: int = 4, row_pad: int = 0, total_mixtures: int | None = None):
         import torch
         from . import capi
         if world > 8:
             raise ValueError("at most 8 ranks")
-        self.M = int(len(float_tables["offsets"]) - 1)
+        self.M = int(len(float_tables["offsets"]) - 1) if total_mixtures is None else int(total_mixtures)
         self.rank, self.world, self.dist = rank, world, dist
         self.Mp = shard_width(self.M, world)
         self.ld = self.Mp * world + int(row_pad)  # row_pad floats behind every row (a row stride off the power of two)
         self.m0, self.m1 = mixture_range(self.M, rank, world)
         if self.m1 <= self.m0:
             raise ValueError("a rank without mixtures: use fewer ranks")
-        sub = shard_float_tables(float_tables, self.m0, self.m1)
+        sub = shard_float_tables(float_tables, self.m0, self.m1) if total_mixtures is None else float_tables
+        if int(len(sub["offsets"]) - 1) != self.m1 - self.m0:
+            raise ValueError("the shard's tables do not hold this rank's mixtures")
         self.engine = capi.Engine(device)
         self.engine.upload_float(sub["offsets"], sub["mean"], sub["isr"], sub["cov_idx"], sub["w2"], sub["log_norm"],
                                  mode=mode, kernel=capi.KERNEL_TENSOR)

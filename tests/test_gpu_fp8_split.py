@@ -1,4 +1,4 @@
-"""GPU: the default operand split of the float tensor kernel (fp16 hi.hi plus ONE e5m2 product for both corrections,
+"""GPU: the default operand split of the float tensor kernel (fp16 hi.hi plus ONE e4m3 product for both corrections,
 DESIGN.md 4.1) and its packing-time guard: taken where the predicted error allows, three fp16 products otherwise
 (GMM_TC_SPLIT=fp16 opts out everywhere, GMM_TC_SPLIT=fp8! bypasses the guard for experiments).  The bar is the float
 scorer's: 1e-4 relative against the oracle (GaussDiagonalMaximumFeatureScorer.cc:116-218)."""
@@ -63,7 +63,7 @@ def test_guard_keeps_three_products(oracle, D, mean_scale):
 
 @pytest.mark.parametrize("D", [45, 24, 9])
 def test_parity_at_the_guards_edge(oracle, D):
-    """The widest mean spread (in steps of 1/16 sigma) the guard still gives to the e5m2 split, against the oracle."""
+    """The widest mean spread (in steps of 1/16 sigma) the guard still gives to the e4m3 split, against the oracle."""
     edge = None
     for i in range(8, 80):
         ms = synth.make_model(M=400, K=16, D=D, seed=7, mean_scale=i / 16.0)
@@ -76,5 +76,5 @@ def test_parity_at_the_guards_edge(oracle, D):
     scale, ms, x, s = edge
     ref, _ = oracle.score_max(ms, x)
     err = _rel(s, ref)
-    print(f"D={D}: last mean_scale on the e5m2 split {scale}, max rel err {err:.2e}")
+    print(f"D={D}: last mean_scale on the e4m3 split {scale}, max rel err {err:.2e}")
     assert err <= 1e-4

@@ -7,6 +7,7 @@ on the -log scores (BASELINE.json north_star), arg-min equal wherever the runner
 """
 import numpy as np
 import pytest
+import torch
 
 from conftest import (golden_names, load_golden, oracle_float_tables, oracle_quant_tables, ref_quant_tables)
 from rasr_b200 import capi, feature_scorer, synth, tables
@@ -236,7 +237,34 @@ def test_posteriors(eng, oracle):
     eng.posteriors_device(70, dx, post)
     eng.sync()
     _, _, po = oracle.score_sum(ms, x, tables=(tab["isr"], tab["log_norm"], tab["w2"]), posterior=True)
-    np.testing.assert_allclose(post.cpu().numpy(), po, rtol=1e-3, atol=1e-6)
+    np.testing.assert_allclose(post.cpu().numpy(), po, rtol=1e-4, atol=1e-7)  # f32 exp / log of scores around D
+
+
+def test_mixture_posteriors_host(eng, oracle):
+    """gmm_mixture_posteriors_host (getDensityPosteriorProbabilities of the sum scorer for the mixture a frame is aligned
+    to) against the oracle's posteriors: 1e-4 relative (f32 exp / log of scores around D)."""
+    ms = synth.make_model(M=40, K=9, D=45, ragged=True, seed=8)
+    T = 200
+    x = synth.make_features(ms, T)
+    tab = oracle_float_tables(ms)
+    upload_float(eng, tab, mode=capi.MODE_SUM)
+    rng = np.random.default_rng(4)
+    mixture = rng.integers(0, ms.M, T).astype(np.uint32)
+    mixture[5] = 0xFFFFFFFF
+    max_k = int(np.max(np.diff(ms.mix_offsets)))
+    post, score = eng.mixture_posteriors_host(x, mixture, max_k)
+    so, _, po = oracle.score_sum(ms, x, tables=(tab["isr"], tab["log_norm"], tab["w2"]), posterior=True)
+    for t in range(T):
+        if mixture[t] == 0xFFFFFFFF:
+            assert not post[t].any()
+            continue
+        a, b = int(ms.mix_offsets[mixture[t]]), int(ms.mix_offsets[mixture[t] + 1])
+        np.testing.assert_allclose(post[t, :b - a], po[t, a:b], rtol=1e-4, atol=1e-7)
+        assert not post[t, b - a:].any()
+        assert abs(score[t] - so[t, mixture[t]]) <= 1e-5 * max(1.0, abs(so[t, mixture[t]]))
+    upload_float(eng, tab, mode=capi.MODE_MAX)
+    with pytest.raises(capi.GmmError):
+        eng.mixture_posteriors_host(x, mixture, max_k)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -294,6 +322,32 @@ def test_padded_leading_dimension(eng, oracle):
     s, b = eng.score_host(x, ld=64)
     so, bo = oracle.score_max(ms, x)
     assert_float_close(s[:, :37], so)
+
+
+@pytest.mark.parametrize("K,ld", [(16, 308), (64, 302), (32, 304), (8, 320), (16, 301), (16, 306)])
+def test_direct_row_piece_stores_equal_staged_stores(eng, oracle, K, ld, monkeypatch):
+    """Maximum approximation without arg-min on uniform tiles: with 8- / 16-byte aligned row pieces (ld a multiple of
+    2 / 4) the tensor kernel's lanes store their row pieces straight from registers; otherwise results are staged in
+    shared memory and stored coalesced (GMM_TC_STORES=staged forces that).  Same bits, nothing written beyond column M."""
+    ms = synth.make_model(M=301, K=K, D=45, seed=20 + K)
+    T = 333
+    x = synth.make_features(ms, T)
+    upload_float(eng, tables.float_tables(ms), kernel=capi.KERNEL_TENSOR)
+    dx = torch.from_numpy(x).cuda()
+
+    def run():
+        d = torch.full((T, ld), -123.0, dtype=torch.float32, device="cuda")
+        eng.score_device(T, dx, d, None, ld=ld)
+        eng.sync()
+        return d.cpu().numpy()
+
+    direct = run()
+    monkeypatch.setenv("GMM_TC_STORES", "staged")
+    staged = run()
+    assert np.array_equal(bits(direct), bits(staged))
+    assert np.all(direct[:, ms.M:] == -123.0)
+    so, _ = oracle.score_max(ms, x)
+    assert_float_close(direct[:, :ms.M], so)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -414,3 +468,48 @@ def test_feature_scorer_interface_on_gpu(oracle):
     for t_ in range(50):
         c = fq.flush()
         assert c.score(3) == sc[t_, 3] and c.bestDensity(3) == bq[t_, 3]
+
+
+# ---------------------------------------------------------------------------------------------------
+# host entry points: chunked pipeline and the asynchronous pair
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ld", [257, 260])
+def test_chunked_host_call_equals_one_chunk(eng, oracle, ld, monkeypatch):
+    """gmm_score_host scores long batches in chunks and copies finished chunks back on a second stream; the result is
+    the single-chunk call's, bit for bit (rows and arg-min), for an unaligned and an aligned row pitch."""
+    ms = synth.make_model(M=257, K=16, D=45, seed=31)
+    T = 9000
+    x = synth.make_features(ms, T)
+    upload_float(eng, tables.float_tables(ms), kernel=capi.KERNEL_AUTO)
+    monkeypatch.setenv("GMM_HOST_CHUNKS", "1")
+    s1, b1 = eng.score_host(x, ld=ld)
+    monkeypatch.setenv("GMM_HOST_CHUNKS", "5")
+    s5, b5 = eng.score_host(x, ld=ld)
+    monkeypatch.delenv("GMM_HOST_CHUNKS")
+    sd, bd = eng.score_host(x, ld=ld)      # default plan (2 chunks at this size)
+    for s, b in ((s5, b5), (sd, bd)):
+        assert np.array_equal(bits(s[:, :ms.M]), bits(s1[:, :ms.M])) and np.array_equal(b[:, :ms.M], b1[:, :ms.M])
+    so, _ = oracle.score_max(ms, x[:300])
+    assert_float_close(s1[:300, :ms.M], so)
+
+
+def test_async_pair_overlaps_calls_and_matches_blocking_call(eng):
+    """gmm_score_async / gmm_wait: three calls enqueued back to back on page-locked buffers (the third
+    reuses the first one's lane), waited for out of order; each equals the blocking call on the same frames."""
+    ms = synth.make_model(M=301, K=16, D=45, seed=32)
+    upload_float(eng, tables.float_tables(ms), kernel=capi.KERNEL_AUTO)
+    T, ld = 1500, 304
+    xs = [torch.from_numpy(synth.make_features(ms, T, seed=40 + i)).pin_memory() for i in range(3)]
+    outs = [torch.full((T, ld), -1.0, dtype=torch.float32).pin_memory() for _ in range(3)]
+    bests = [torch.zeros((T, ld), dtype=torch.int32).pin_memory() for _ in range(3)]
+    toks = [eng.score_async(xs[i].numpy(), outs[i].numpy(), bests[i].numpy(), ld=ld) for i in range(3)]
+    assert toks == sorted(toks) and len(set(toks)) == 3
+    for i in (2, 0, 1):
+        eng.wait(toks[i])
+    eng.sync()
+    for i in range(3):
+        s, b = eng.score_host(xs[i].numpy(), ld=ld)
+        assert np.array_equal(bits(outs[i].numpy()[:, :ms.M]), bits(s[:, :ms.M]))
+        assert np.array_equal(bests[i].numpy().view(np.uint32)[:, :ms.M], b[:, :ms.M])
+    with pytest.raises(capi.GmmError):
+        eng.wait(10 ** 9)
