@@ -65,6 +65,8 @@ struct QKParams {
     uint32_t        stagesA, buffersB;
     uint32_t        stagePitch;  // words per staging row (maxMixPerPart + 1)
     uint32_t        qBase;       // cmax (wrapping u32): q = qBase + |qx|^2 - max_k acc_k
+    unsigned long long* dbg;     // GMM_QTC_DEBUG: per-CTA cycle counters (16 words per CTA)
+    uint32_t        vecStores;   // 0: always the scalar staged store path (GMM_QTC_STORES=scalar)
 };
 
 __device__ __forceinline__ uint8_t quantize_u8(float v) {
@@ -145,9 +147,12 @@ struct QEpiState {
 //    WB: key = (acc << 8) + (255 - slot) with the slot term an immediate.
 // SP = 0: key = (acc << 8) + Kc with Kc read from the tile's table; segEnd bits close the mixtures; a mixture without
 // densities (all its columns pads: key 0) yields the reference's INT_MAX / no density.
+// resQ != nullptr (SP > 0 only): the closed mixtures' q (and arg-min, resB) stay in registers, index seg / SP, for the
+// vector store path instead of being staged one by one.
 template<int SP, bool WB>
 __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t qbx,
-                                           uint32_t offB, QEpiState& st) {
+                                           uint32_t offB, QEpiState& st, uint32_t* resQ = nullptr,
+                                           uint32_t* resB = nullptr) {
     uint32_t kc[32];
     if (SP == 0) {  // the chunk's 32 per-column terms first (eight 128-bit loads in flight together)
 #pragma unroll
@@ -182,7 +187,12 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
             close = (segEnd >> seg) & 1u;
         }
         if (close) {  // uniform across the warp
-            if (SP > 0 && !WB)
+            if (SP > 0 && resQ) {
+                resQ[seg / SP] = WB ? qbx - (m >> 8) : qbx - m;
+                if (WB)
+                    resB[seg / SP] = 255u - (m & 255u);
+            }
+            else if (SP > 0 && !WB)
                 sts_u32(st.sp, qbx - m);
             else {
                 const bool none = SP == 0 && m == kNoKey;
@@ -292,6 +302,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
         const uint32_t     kS       = p.kSteps;
         uint32_t           itemCount = 0, t = 0, stage = 0;
         bool               have = false;
+        long long          mW = 0, mI = 0, mc0 = 0;
+        const long long    mStart = clock64();
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
             const uint32_t chunk = item % p.split;
             const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
@@ -301,9 +313,11 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
             const uint32_t bLo = (smem_u32(sB + (size_t)b * bBytes) & 0x3FFFF) >> 4;
             for (uint32_t f = f0; f < f1; ++f, ++t) {
+                if (p.dbg) mc0 = clock64();
                 if (!have)
                     mbar_wait(smem_u32(&ready[t % kRing]), (t / kRing) & 1);
                 tc_fence_after();
+                if (p.dbg) { const long long c1 = clock64(); mW += c1 - mc0; mc0 = c1; }
                 const uint32_t aLo   = (smem_u32(sA + (size_t)stage * p.aTileBytes) & 0x3FFFF) >> 4;
                 const uint32_t dTmem = tmemBase + (t & 1) * kTileN;
                 if (leader) {
@@ -323,7 +337,12 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                 __syncwarp();
                 if (++stage == p.stagesA)
                     stage = 0;
+                if (p.dbg) mI += clock64() - mc0;
             }
+        }
+        if (p.dbg && leader) {
+            unsigned long long* d = p.dbg + blockIdx.x * 16;
+            d[0] = clock64() - mStart, d[1] = mW, d[2] = mI, d[4] = t;
         }
     }
     else {
@@ -338,6 +357,7 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
         const ptrdiff_t bestDelta  = p.best ? reinterpret_cast<char*>(p.best) - gBase : 0;
         const ptrdiff_t scoreDelta = p.score ? reinterpret_cast<char*>(p.score) - gBase : 0;
         uint32_t       itemCount = 0, t = 0;
+        long long      eW = 0, eL = 0, eB = 0, eS = 0, ec0 = 0;
         if (lane == 0) {
             mbar_arrive(smem_u32(&ready[0]));
             mbar_arrive(smem_u32(&ready[1]));
@@ -377,8 +397,25 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
             size_t          gTile = ((size_t)(f0 * kTileM + qd * 32 + lr0) * p.ld + mixBase + lj0) * 4;
             const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
             const uint32_t* xxp = p.rowXX + (size_t)f0 * kTileM + qd * 32 + lane;
-            auto tiles = [&](auto spTag) {
-                constexpr int SP = decltype(spTag)::value;
+            // VEC (uniform tile, 16-byte aligned row pieces): a lane keeps its R = SEGS / SP results in registers, stages
+            // them with 128-bit stores into rows of W + 4 words (W = the group's results per row), and the group writes
+            // the block out with one 128-bit load and store per thread and array and pass -- a handful of instructions
+            // where the scalar path below spends a hundred (the epilogue is bound by the half-rate integer pipes)
+            auto tiles = [&](auto spTag, auto vecTag) {
+                constexpr int  SP  = decltype(spTag)::value;
+                constexpr bool VEC = decltype(vecTag)::value && SP > 0 && (SEGS / (SP > 0 ? SP : 1)) % 4 == 0;
+                constexpr int  R   = SP > 0 ? SEGS / SP : 1;          // results per lane and tile
+                constexpr int  W   = NE == 16 ? 4 * R : R;            // results per row of the store group
+                constexpr int  PV  = W + 4;                           // staging pitch of the vector path (words)
+                constexpr int  WQ4 = W / 4 > 0 ? W / 4 : 1;           // 16-byte pieces per row
+                uint32_t       resQ[VEC ? R : 1], resB[VEC ? R : 1];
+                uint32_t* const rq = VEC ? resQ : nullptr;
+                uint32_t* const rb = VEC ? resB : nullptr;
+                // vector path: this thread's piece and first row, its global offset (bytes) and the staging offsets
+                const uint32_t vqi = gl % WQ4, vr0 = gl / WQ4;
+                size_t         gVec = ((size_t)(f0 * kTileM + qd * 32 + vr0) * p.ld + mixBase + vqi * 4) * 4;
+                const uint32_t vRead  = (vr0 * PV + vqi * 4) * 4;
+                const uint32_t vWrite = ((uint32_t)lane * PV + (NE == 16 ? (uint32_t)part * R : 0u)) * 4;
                 uint32_t xxNext = *xxp;  // |qx|^2 of the next tile's row, fetched one tile ahead
                 for (uint32_t f = f0; f < f1; ++f, ++t) {
                     const uint32_t acc    = t & 1;
@@ -386,8 +423,10 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                     xxp += kTileM;
                     if (f + 1 < f1)
                         xxNext = *xxp;
+                    if (p.dbg) ec0 = clock64();
                     mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
                     tc_fence_after();
+                    if (p.dbg) { const long long c1 = clock64(); eW += c1 - ec0; ec0 = c1; }
                     const uint32_t taddr   = tmemBase + ((uint32_t)(qd * 32) << 16) + acc * kTileN + part * PW;
                     const uint32_t drained = smem_u32(&ready[(t + 2) % kRing]);
                     const uint32_t stBuf = stGrp + (kBufs == 2 ? (t & 1) * stageWarp * 4 : 0u);
@@ -404,48 +443,85 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st);
-                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, rq, rb);
                     }
                     else if (NE == 16) {
                         // 96 registers per thread: one 32-column chunk (+ its 32 table entries) live at a time
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, rq, rb);
                         tmem_ld32(taddr + 32, va);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(va, 1, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 1, kcAddr, segEnd, xxBase, offB, st, rq, rb);
                     }
                     else {
                         uint32_t vb[32];
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 32, vb);
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, rq, rb);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 64, va);
-                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, rq, rb);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 96, vb);
-                        qepi_chunk<SP, WB>(va, 2, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(va, 2, kcAddr, segEnd, xxBase, offB, st, rq, rb);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(vb, 3, kcAddr, segEnd, xxBase, offB, st);
+                        qepi_chunk<SP, WB>(vb, 3, kcAddr, segEnd, xxBase, offB, st, rq, rb);
                     }
+                    if (VEC) {
+#pragma unroll
+                        for (int i = 0; i < R / 4; ++i) {
+                            sts_v4(stBuf + vWrite + i * 16, resQ[4 * i], resQ[4 * i + 1], resQ[4 * i + 2], resQ[4 * i + 3]);
+                            if (WB)
+                                sts_v4(stBuf + offB + vWrite + i * 16, resB[4 * i], resB[4 * i + 1], resB[4 * i + 2],
+                                       resB[4 * i + 3]);
+                        }
+                    }
+                    if (p.dbg) { const long long c1 = clock64(); eL += c1 - ec0; ec0 = c1; }
                     if (NE == 16)  // the quarter's four warps have staged their parts of these 32 rows
                         asm volatile("bar.sync %0, 128;" ::"r"(1 + qd) : "memory");
                     else
                         __syncwarp();
-                    // coalesced store of the staged [32 rows x nMix] block: passes of GW consecutive elements
+                    if (p.dbg) { const long long c1 = clock64(); eB += c1 - ec0; ec0 = c1; }
                     const uint32_t rbase = f * kTileM + qd * 32;
                     const uint32_t rows  = min(32u, p.T > rbase ? p.T - rbase : 0u);
+                    if (VEC) {
+                        constexpr int RPP = GW / WQ4;  // rows per pass
+                        char*         g   = gBase + gVec;
+                        gVec += gTileStep;
+#pragma unroll
+                        for (int ps = 0; ps < 32 / RPP; ++ps) {
+                            if (vr0 + ps * RPP < rows) {
+                                const uint4 qv = lds_v4(stBuf + vRead + ps * RPP * PV * 4);
+                                char*       gp = g + (size_t)ps * RPP * p.ld * 4;
+                                if (WQ)
+                                    *reinterpret_cast<uint4*>(gp) = qv;
+                                if (WB)
+                                    *reinterpret_cast<uint4*>(gp + bestDelta) = lds_v4(stBuf + offB + vRead + ps * RPP * PV * 4);
+                                if (WS)
+                                    *reinterpret_cast<float4*>(gp + scoreDelta) =
+                                            make_float4(__fdiv_rn((float)(int32_t)qv.x, p.twoScalingSquared),
+                                                        __fdiv_rn((float)(int32_t)qv.y, p.twoScalingSquared),
+                                                        __fdiv_rn((float)(int32_t)qv.z, p.twoScalingSquared),
+                                                        __fdiv_rn((float)(int32_t)qv.w, p.twoScalingSquared));
+                            }
+                        }
+                        if (NE != 16)
+                            __syncwarp();
+                        if (p.dbg) eS += clock64() - ec0;
+                        continue;
+                    }
+                    // coalesced store of the staged [32 rows x nMix] block: passes of GW consecutive elements
                     char*          g     = gBase + gTile;  // byte address of this thread's first element in q[]
                     uint32_t       ss    = stBuf + ssOff;
                     gTile += gTileStep;
@@ -484,18 +560,35 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                     }
                     if (NE != 16)
                         __syncwarp();
+                    if (p.dbg) eS += clock64() - ec0;
                 }
             };
             const uint32_t uni = (meta[10] >> (8 * part)) & 0xFFu;  // TileMeta::uni
+            // vector stores: the whole store group uniform with the same shape (16 warps: all four parts of the tile),
+            // a compiled output set (not the run-time variant), 16-byte aligned row pieces in every array
+            const bool vec = OUT != 0 && p.vecStores && uni != 0 && (NE == 8 || meta[10] == uni * 0x01010101u) &&
+                             (p.ld % 4) == 0 && (mixBase % 4) == 0 && (reinterpret_cast<uintptr_t>(gBase) % 16) == 0 &&
+                             (bestDelta % 16) == 0 && (scoreDelta % 16) == 0;
+            auto run = [&](auto spTag) {
+                if constexpr (OUT != 0 && decltype(spTag)::value > 0 && (SEGS / (decltype(spTag)::value > 0 ? decltype(spTag)::value : 1)) % 4 == 0) {
+                    if (vec)
+                        return tiles(spTag, std::true_type{});
+                }
+                tiles(spTag, std::false_type{});
+            };
             switch (uni) {
-                case 1: tiles(std::integral_constant<int, 1>{}); break;
-                case 2: tiles(std::integral_constant<int, 2>{}); break;
-                case 4: tiles(std::integral_constant<int, 4>{}); break;
-                case 8: tiles(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
-                default: tiles(std::integral_constant<int, 0>{}); break;
+                case 1: run(std::integral_constant<int, 1>{}); break;
+                case 2: run(std::integral_constant<int, 2>{}); break;
+                case 4: run(std::integral_constant<int, 4>{}); break;
+                case 8: run(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
+                default: run(std::integral_constant<int, 0>{}); break;
             }
             if (lane == 0)
                 mbar_arrive(smem_u32(&emptyB[b]));
+        }
+        if (p.dbg && e == 0 && lane == 0) {
+            unsigned long long* d = p.dbg + blockIdx.x * 16;
+            d[8] = eW, d[9] = eL, d[10] = eB, d[11] = eS;
         }
     }
 
@@ -630,7 +723,7 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
     }
 
     // ---- shared-memory configuration ----
-    const uint32_t pitch = tm.maxMixPerPart + 1, epiWarps = 4 * partsPerTile;
+    const uint32_t pitch = (tm.maxMixPerPart + 3) / 4 * 4 + 5, epiWarps = 4 * partsPerTile;
     for (uint32_t nb = 2; nb >= 1 && !tm.buffersB; --nb)
         for (uint32_t sa = kMaxStagesA; sa >= 2; --sa)
             if (qSmemNeed(tm.tileBytes, tm.aTileBytes, nb, sa, pitch, epiWarps) <= kSmemLimit) {
@@ -754,8 +847,21 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     p.bTileBytes     = tm.tileBytes;
     p.stagesA        = tm.stagesA;
     p.buffersB       = tm.buffersB;
-    p.stagePitch     = tm.maxMixPerPart + 1;
+    p.stagePitch     = (tm.maxMixPerPart + 3) / 4 * 4 + 5;  // odd, and >= W + 4 of the vector store path
     p.qBase          = tm.qBase;
+    p.dbg            = nullptr;
+    {
+        const char* e = getenv("GMM_QTC_STORES");
+        p.vecStores   = (e && !strcmp(e, "scalar")) ? 0u : 1u;
+    }
+    const bool debug = getenv("GMM_QTC_DEBUG") != nullptr;
+    if (debug) {
+        void* d = nullptr;
+        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 128, &d)))
+            return rc;
+        GMM_CUDA_TRY(h, cudaMemsetAsync(d, 0, (size_t)h->smCount * 128, h->stream));
+        p.dbg = (unsigned long long*)d;
+    }
     const uint32_t epiWarps = 4 * (kTileN / tm.partW);
     const size_t   smemBytes = qSmemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, tm.stagesA, p.stagePitch, epiWarps);
     // frame range split so that the items fill the SMs evenly (round-robin items keep adjacent B tiles together in
@@ -803,5 +909,22 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
+    if (debug) {  // development aid: where the MMA thread and epilogue warp 0 spend their cycles
+        std::vector<unsigned long long> d((size_t)h->smCount * 16);
+        GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+        GMM_CUDA_TRY(h, cudaMemcpy(d.data(), p.dbg, d.size() * 8, cudaMemcpyDeviceToHost));
+        double tot = 0, mW = 0, mI = 0, tiles = 0, eW = 0, eL = 0, eB = 0, eS = 0;
+        for (int c = 0; c < grid; ++c) {
+            tot += d[c * 16], mW += d[c * 16 + 1], mI += d[c * 16 + 2], tiles += d[c * 16 + 4];
+            eW += d[c * 16 + 8], eL += d[c * 16 + 9], eB += d[c * 16 + 10], eS += d[c * 16 + 11];
+        }
+        tiles = std::max(1.0, tiles);
+        fprintf(stderr,
+                "[gmm_qtc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u out %d | cycles per tile: MMA thread "
+                "total %.0f = wait-ready %.0f + issue %.0f | epilogue warp 0: wait-for-MMA %.0f + loads and reduction %.0f + "
+                "group barrier %.0f + stores %.0f\n",
+                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, out, tot / tiles, mW / tiles, mI / tiles,
+                eW / tiles, eL / tiles, eB / tiles, eS / tiles);
+    }
     return GMM_OK;
 }

@@ -168,6 +168,47 @@ def test_quantized_output_sets_bit_exact(eng, oracle, want, warps, monkeypatch):
         assert np.array_equal(bits(r["score"]), bits(sc))
 
 
+@pytest.mark.parametrize("warps", ["16", "8"])
+@pytest.mark.parametrize("K,ld", [(16, 304), (8, 308), (32, 304), (64, 312), (16, 301)])
+def test_quantized_vector_stores_equal_scalar_stores(eng, oracle, K, ld, warps, monkeypatch):
+    """Uniform tiles with 16-byte aligned row pieces take the vector store path of the integer tensor kernel (results
+    in registers, 128-bit staging and stores); GMM_QTC_STORES=scalar forces the element-wise path.  Same bits in every
+    requested array, nothing written beyond column M, and both equal the oracle."""
+    if warps == "8":
+        monkeypatch.setenv("GMM_QTC_EPI_WARPS", "8")
+    ms = synth.make_model(M=301, K=K, D=45, seed=40 + K)
+    T = 417
+    x = synth.make_features(ms, T)
+    x[3] *= 25.0
+    t, raw = oracle_quant_tables(ms)
+    upload_quant(eng, t)
+    assert eng.quant_kernel == 2
+    dx = torch.from_numpy(x).cuda()
+    qx = oracle.simd_quantize_features(x, raw["isrs"])
+    q, b = oracle.simd_score(ms.mix_offsets, raw, qx)
+    sc = oracle.simd_final_score(q, raw["scaling_squared"])
+
+    def run(want_q, want_b, want_s):
+        dq = torch.full((T, ld), -5, dtype=torch.int32, device="cuda") if want_q else None
+        db = torch.full((T, ld), -5, dtype=torch.int32, device="cuda") if want_b else None
+        ds = torch.full((T, ld), -5.0, dtype=torch.float32, device="cuda") if want_s else None
+        eng.quant_score_device(T, dx, dq, db, ds, ld=ld)
+        eng.sync()
+        return [None if a is None else a.cpu().numpy() for a in (dq, db, ds)]
+
+    for want in ((True, True, False), (False, False, True), (False, True, True), (True, True, True)):
+        monkeypatch.delenv("GMM_QTC_STORES", raising=False)
+        vec = run(*want)
+        monkeypatch.setenv("GMM_QTC_STORES", "scalar")
+        sca = run(*want)
+        for a, c, ref in zip(vec, sca, (q, b.astype(np.int32), sc)):
+            if a is None:
+                continue
+            assert np.array_equal(bits(a), bits(c))
+            assert np.array_equal(bits(a[:, :ms.M]), bits(ref))
+            assert np.all(a[:, ms.M:] == -5)
+
+
 @pytest.mark.parametrize("kw", MODELS)
 @pytest.mark.parametrize("T", [1, 33, 300])
 def test_quantized_bit_exact_vs_oracle(eng, oracle, kw, T):
