@@ -252,7 +252,7 @@ def float_roofline(ms, frames, kernel_sec, peaks, kernel_name, step_sec=None, tr
             "kernel_share_of_step": (kernel_sec * launches_per_step / step_sec) if step_sec else None,
             "frac_of_burst_peak": ach / peaks["tensor"],
             # MMA instruction times per tile in fp16-K16 equivalents over the algorithmic contraction length: `split`
-            # products (3: fp16 hi.hi + lo.hi + hi.lo; 2: fp16 hi.hi + one e5m2 instruction for both corrections)
+            # products (3: fp16 hi.hi + lo.hi + hi.lo; 2: fp16 hi.hi + one e4m3 instruction for both corrections)
             "mma_products_per_algorithmic_product": split,
             "executed_over_algorithmic": float(split) * (16 * (((ms.D if ms.variances.shape[0] == 1 else 2 * ms.D) + 3 + 15) // 16))
                                          / (2 * ms.D + 1),
@@ -303,7 +303,7 @@ def run_ours(args):
     split = eng.float_split
     kname = {capi.KERNEL_DIRECT: "direct_kernel (CUDA cores, reference order)",
              capi.KERNEL_TENSOR: "tc_score_kernel8 (tcgen05: fp16 hi.hi + " +
-                                 ("one e5m2 product for both corrections" if split == 2 else "fp16 lo.hi + hi.lo") +
+                                 ("one e4m3 product for both corrections (lo parts x 2^8, undone by scale-input-d)" if split == 2 else "fp16 lo.hi + hi.lo") +
                                  ", fused per-mixture min)"}[eng.float_kernel]
 
     # this rank's segments: i -> rank i mod N; two alternating batches so consecutive steps read fresh inputs
@@ -452,7 +452,7 @@ def run_ours(args):
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec_per_step * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": ("f32 (split operands: fp16 hi.hi + e5m2 corrections, f32 accumulate; <= 1e-4 rel. "
+            "vs_baseline": None, "dtype": ("f32 (split operands: fp16 hi.hi + e4m3 corrections, f32 accumulate; <= 1e-4 rel. "
                                            "vs the reference's f32)" if split == 2 else
                                            "f32 (fp16x3 split operands, f32 accumulate)") if
             eng.float_kernel == capi.KERNEL_TENSOR else "f32", "data": "synthetic",

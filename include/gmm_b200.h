@@ -14,6 +14,7 @@
  *   gmm_score_*  (sum)  GaussDiagonalSumFeatureScorer::calculateScoreAndDensity                  .cc:239-289
  *   gmm_posteriors      GaussDiagonalSumFeatureScorer::calculateDensityPosteriorProbabilities    .cc:291-298
  *   gmm_upload_quant    SimdGaussDiagonalMaximumFeatureScorer::init/buildMixtureTable  SimdFeatureScorer.cc:64-104
+ *                       BatchIntFeatureScorer::init (with gmm_quant_final_score_rule)  BatchFeatureScorer.cc:337-376
  *   gmm_quant_* (qx)    SimdGaussDiagonalMaximumFeatureScorer::Context ctor            SimdFeatureScorer.cc:22-35
  *                       FeatureScorerIntelOptimization::multiplyAndQuantize            IntelOptimization.cc:50-67
  *   gmm_quant_* (q)     quantizedScore + FeatureScorerIntelOptimization::distance      SimdFeatureScorer.cc:158-176,
@@ -43,7 +44,8 @@ enum {
     GMM_ERR_ARG       = -1, /* invalid argument / model not uploaded */
     GMM_ERR_CUDA      = -2, /* CUDA runtime error (message in gmm_last_error) */
     GMM_ERR_NO_DEVICE = -3, /* no usable sm_100 device */
-    GMM_ERR_UNSUPPORTED = -4
+    GMM_ERR_UNSUPPORTED = -4,
+    GMM_ERR_TIMEOUT   = -5  /* a peer of a mixture-sharded exchange did not show up (gmm_gather_status / _reset) */
 };
 
 /* scoring mode of the float engine */
@@ -108,6 +110,15 @@ int gmm_mixture_posteriors_host(gmm_handle* h, uint32_t T, const float* x, const
 int gmm_upload_quant(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t Dpad, uint32_t C,
                      const uint32_t* offsets, const uint8_t* qmean, const uint32_t* cov_idx, const int32_t* qconst,
                      const float* isr_scaled, float scaling_squared);
+/* How q becomes the final f32 score, per uploaded quantized model (gmm_upload_quant resets it to SIMD):
+ *   GMM_QUANT_RULE_SIMD       f32(0.5 * q / s^2) evaluated in IEEE double   SimdFeatureScorer.cc:135-145
+ *   GMM_QUANT_RULE_BATCH_INT  f32(q) / f32(2 s^2), one f32 division         BatchFeatureScorer.cc:468
+ * The two agree for |q| < 2^24; they differ beyond (f32(q) rounds first), e.g. for the 0x80000000 constant of a
+ * zero-weight density.  With the tables of BatchIntFeatureScorer::init (BatchFeatureScorer.cc:337-376; scaling_squared
+ * = scale^2) the second rule makes the engine the reference's `batch-diagonal-maximum-int` scorer, bit for bit. */
+#define GMM_QUANT_RULE_SIMD 0
+#define GMM_QUANT_RULE_BATCH_INT 1
+int gmm_quant_final_score_rule(gmm_handle* h, int rule);
 /* x [T x D] f32 -> q [T x ld] s32 (may be NULL), best [T x ld] (may be NULL), score [T x ld] f32 (may
  * be NULL; f32(0.5 * q / scalingSquared) evaluated in IEEE double), qx [T x C x Dpad] u8 (may be NULL). */
 int gmm_quant_score_host(gmm_handle* h, uint32_t T, const float* x, int32_t* q, uint32_t* best, float* score,
@@ -144,11 +155,24 @@ int gmm_quant_score_device_static(gmm_handle* h, uint32_t T, const float* d_x, i
  * = columns, which need a model whose mixtures all have the same number of densities, else one range), and pushes
  * each finished range into the peers' blocks from a second stream while the next range is being scored, (3) makes the handle's stream wait until every peer's columns have landed.  Work
  * queued on the stream afterwards sees the complete [T x ld] rows; all ranks must make the same sequence of calls.
- * Tensor kernel only, T <= 32768.  A peer that does not show up within ~2 s ends the wait and sets flag word 17 (sticky; the rows
- * are then incomplete and the rank stops announcing its columns as complete, so its peers time out as well). */
+ * Tensor kernel only, T <= 32768.
+ * Flag words: [r] READY from rank r, [8 + r] DONE from rank r, [16] CTA counter, [17] time-out marker, [18] the number
+ * of calls this rank has made on the block.  The call counter lives with the block, not with the handle: a new
+ * handle over used blocks (model re-upload, restarted rank) reads it at its first call and stays in step with its
+ * peers; it advances only when a call was enqueued completely, so a call that returned an error is simply repeated.
+ * A peer that does not show up within ~2 s (GMM_GATHER_TIMEOUT_MS) ends the wait.  This is neither silent nor
+ * permanent: the waiting kernel (a) sets word 17 and stops announcing this rank's columns as complete, so the peers
+ * time out too, (b) overwrites every column of the call's rows that is not this rank's own with +inf, so a consumer
+ * already queued behind the call sees impossible scores, never stale ones, (c) stores the call's number into a
+ * page-locked word: gmm_gather_status reads it (0 = no time-out; meaningful after a gmm_sync), and from then on
+ * gmm_score_device_gather, gmm_align_device and gmm_baum_welch_device return GMM_ERR_TIMEOUT on this handle until
+ * gmm_gather_reset.  The reset is collective by contract: every rank calls it between two host barriers (no call in
+ * flight anywhere); it zeroes the flag words of the blocks this handle has called on and restarts their numbering. */
 int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
                             void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
                             uint32_t chunks);
+int gmm_gather_status(gmm_handle* h, uint32_t* timedOutCall);
+int gmm_gather_reset(gmm_handle* h);
 /* Device memory other processes of the same box can map: allocate (zeroed) + export (ipcHandle: 64 bytes), map,
  * unmap, free. */
 int gmm_peer_alloc(gmm_handle* h, size_t bytes, void** d_ptr, void* ipcHandle);
@@ -294,6 +318,11 @@ int         gmm_float_kernel(const gmm_handle* h);
  * hi.hi + lo.hi + hi.lo: everything else, and always with GMM_TC_SPLIT=fp16 set at upload); 0 when the model is not on
  * the tensor kernel. */
 int         gmm_float_split(const gmm_handle* h);
+/* 1: the uploaded float model keeps the 1e-4 relative bar on the kernel it runs on.  0 only when the tensor kernel
+ * was FORCED (kernel = GMM_KERNEL_TENSOR at upload) for a model whose centred, whitened means lie further out than
+ * 8 sigma rms -- the automatic choice sends such a model to the direct kernel; a caller that forces the tensor
+ * kernel (the mixture-sharded scorer has no direct variant) must check this and refuse or warn. */
+int         gmm_float_accuracy_ok(const gmm_handle* h);
 /* 1 = dp4a (CUDA cores), 2 = integer tensor path: the kernel the last gmm_upload_quant selected (0: no model).
  * Both are bit-identical to the reference; environment GMM_QUANT_KERNEL=dp4a at upload time forces the former. */
 int         gmm_quant_kernel(const gmm_handle* h);

@@ -270,6 +270,55 @@ void orc_simd_prepare(const orc_model* m, int exactRsqrt, float* isrS, float* lo
     }
 }
 
+/* BatchFeatureScorer.cc:319-376 BatchIntFeatureScorer::quantizationScale / init (`batch-diagonal-maximum-int`):
+ * the same u8 grid as the SIMD scorer -- variance_ = isr * scale, means and frames through quantize(a * b) -- but
+ * its own constants: c = (s32)(logNormFactor - scale_ * logWeight) with logNormFactor = L * scale^2 (f32),
+ * scale_ = 2 * scale^2 (f32), logWeight f64, evaluated in double and truncated (cvttsd2si: 0x80000000 when out of
+ * range -- a zero-weight density then WINS every minimum, as it does in the reference).  Pooled covariance only
+ * (:340-342 criticalError): returns -1 otherwise.
+ * Outputs: isrS [D], scale2 (= scale_, the divisor of the final score, :468), qmean [G x Dpad], qconst [G]. */
+int orc_batchint_prepare(const orc_model* m, int exactRsqrt, float* isrS, float* scale2, uint8_t* qmean,
+                         int32_t* qconst) {
+    if (m->nCov != 1)
+        return -1;
+    const uint32_t D = m->D, Dpad = orc_simd_padded_dimension(D); /* BlockSize = 16 (:293) */
+    float          logNorm;
+    orc_covariance_tables(m, 1.0f, exactRsqrt, isrS, &logNorm);
+    float minMean = FLT_MAX, maxMean = -FLT_MAX;
+    for (uint32_t i = 0; i < m->nDens; ++i) {
+        const float* mean = m->means + (size_t)m->densMean[i] * D;
+        for (uint32_t d = 0; d < D; ++d) {
+            float dividedMean = mean[d] * isrS[d];
+            minMean           = dividedMean < minMean ? dividedMean : minMean;
+            maxMean           = maxMean < dividedMean ? dividedMean : maxMean;
+        }
+    }
+    float a = fabsf(minMean), b = fabsf(maxMean);
+    float intervalSize = 2 * (a < b ? b : a);
+    float scale        = (float)((double)(float)255 / (1.25 * (double)intervalSize));
+    float scaleSquared = scale * scale;
+    *scale2            = (float)(2.0 * (double)scaleSquared);
+    for (uint32_t d = 0; d < D; ++d)
+        isrS[d] = isrS[d] * scale;
+    const float logNormFactor = logNorm * scaleSquared;
+    for (uint32_t mix = 0; mix < m->M; ++mix) {
+        for (uint32_t k = m->mixOffsets[mix]; k < m->mixOffsets[mix + 1]; ++k) {
+            uint32_t dns = m->mixDensity[k];
+            orc_multiply_and_quantize(m->means + (size_t)m->densMean[dns] * D, isrS, D, Dpad, qmean + (size_t)k * Dpad);
+            qconst[k] = _mm_cvttsd_si32(_mm_set_sd((double)logNormFactor - (double)*scale2 * m->mixLogWeight[k]));
+        }
+    }
+    return 0;
+}
+
+/* BatchFeatureScorer.cc:468: *result = static_cast<f32>(best) / scale_  (f32 division) */
+void orc_batchint_final_score(const int32_t* q, size_t n, float scale2, float* score) {
+    for (size_t i = 0; i < n; ++i) {
+        volatile float num = (float)q[i]; /* keeps the division a division under any optimisation flags */
+        score[i]           = num / scale2;
+    }
+}
+
 /* SimdFeatureScorer.cc:22-35 Context ctor: the frame is quantized once per covariance.
  * qx [T x nCov x Dpad]. */
 void orc_simd_quantize_features(const float* x, size_t T, uint32_t D, uint32_t nCov, const float* isrS,

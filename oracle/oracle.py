@@ -117,6 +117,27 @@ def simd_prepare(ms, exact_rsqrt=False):
                 qcov=qcov, Dpad=Dpad)
 
 
+def batchint_prepare(ms, exact_rsqrt=False):
+    """Quantized tables of BatchIntFeatureScorer::init (`batch-diagonal-maximum-int`); pooled covariance only."""
+    cm = _cmodel(ms)
+    Dpad = int(lib().orc_simd_padded_dimension(ms.D))
+    isrs = np.empty((1, ms.D), np.float32)
+    scale2 = C.c_float(0)
+    qmean = np.empty((ms.G, Dpad), np.uint8)
+    qconst = np.empty(ms.G, np.int32)
+    if lib().orc_batchint_prepare(C.byref(cm), int(exact_rsqrt), _p(isrs), C.byref(scale2), _p(qmean), _p(qconst)) != 0:
+        raise ValueError("feature scorer supports only globally pooled variance")
+    return dict(isrs=isrs, scale2=np.float32(scale2.value), qmean=qmean, qconst=qconst,
+                qcov=np.zeros(ms.G, np.uint32), Dpad=Dpad)
+
+
+def batchint_final_score(q, scale2):
+    q = np.ascontiguousarray(q, np.int32)
+    out = np.empty(q.shape, np.float32)
+    lib().orc_batchint_final_score(_p(q), C.c_size_t(q.size), C.c_float(float(scale2)), _p(out))
+    return out
+
+
 def simd_quantize_features(x, isrs):
     x = np.ascontiguousarray(x, np.float32)
     T, D = x.shape

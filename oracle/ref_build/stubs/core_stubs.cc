@@ -2,6 +2,7 @@
 // DependencySet::read needs libxml2 (absent here).  Only the symbols other Core TUs link
 // against are provided; none is on the scoring path.
 #include <Core/Dependency.hh>
+#include <Core/StringUtilities.hh>
 
 namespace Core {
 const std::string DependencySet::nameSeparator_(".");
@@ -14,6 +15,9 @@ void DependencySet::add(const std::string& name, const Dependency& d) {
 }
 void DependencySet::add(const std::string& name, const std::string& value) {
     add(name, Dependency(value));
+}
+void DependencySet::add(const std::string& name, const double value) {
+    add(name, Dependency(Core::form("%f", value)));
 }
 bool DependencySet::read(const Configuration&, const std::string&) {
     return false;

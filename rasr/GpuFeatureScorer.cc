@@ -9,6 +9,7 @@
 #include <Mm/CovarianceFeatureScorerElement.hh>
 #include <Mm/IntelOptimization.hh>
 #include <Mm/MixtureFeatureScorerElement.hh>
+#include <Mm/Utilities.hh>
 
 #include <gmm_b200.h>
 
@@ -23,53 +24,139 @@ const Core::ParameterFloat GpuFeatureScorer::paramMixtureWeightScale(
         "mixture-weight-scale", "scaling of the logarithmized mixture weights", 1.0, Core::Type<Mm::Score>::epsilon);
 const Core::ParameterFloat GpuFeatureScorer::paramGaussianScale(
         "gaussian-scale", "scaling of the logarithmized gaussian probability", 1.0, Core::Type<Mm::Score>::epsilon);
+const Core::ParameterBool GpuFeatureScorer::paramDensityAssignment(
+        "with-density-assignment",
+        "compute the best density of every mixture with every batch (training consumers ask for score AND bestDensity, "
+        "src/Mm/AbstractMixtureSetEstimator.cc:377-393); otherwise it costs a second pass when first asked for",
+        false);
 
 // ---- score blocks ----------------------------------------------------------------------------------------
 
-GpuFeatureScorer::ScoreBlock::ScoreBlock(u32 T, u32 M)
-        : scores(0), best(0), nFrames(T), nMixtures(M) {
-    scores = static_cast<Mm::Score*>(gmm_host_alloc(size_t(T) * M * sizeof(Mm::Score)));
+GpuFeatureScorer::PinnedPool::~PinnedPool() {
+    for (size_t i = 0; i < free_.size(); ++i)
+        gmm_host_free(free_[i].ptr);
+}
+
+void* GpuFeatureScorer::PinnedPool::acquire(size_t bytes, size_t& capacity) {
+    size_t bestI = free_.size();
+    for (size_t i = 0; i < free_.size(); ++i)  // smallest buffer that fits
+        if (free_[i].bytes >= bytes && (bestI == free_.size() || free_[i].bytes < free_[bestI].bytes))
+            bestI = i;
+    if (bestI != free_.size()) {
+        void* p  = free_[bestI].ptr;
+        capacity = free_[bestI].bytes;
+        free_.erase(free_.begin() + bestI);
+        return p;
+    }
+    capacity = bytes + bytes / 4 + 4096;  // segments differ in length: leave room so that the next one fits too
+    return gmm_host_alloc(capacity);
+}
+
+void GpuFeatureScorer::PinnedPool::release(void* ptr, size_t capacity) {
+    if (!ptr)
+        return;
+    if (free_.size() >= 12) {  // bounded: a few batches in flight plus the blocks a caller holds on to
+        gmm_host_free(ptr);
+        return;
+    }
+    Buffer b = {ptr, capacity};
+    free_.push_back(b);
+}
+
+GpuFeatureScorer::ScoreBlock::ScoreBlock(Core::Ref<PinnedPool> pl, u32 cap, u32 M, u32 D)
+        : pool(pl), scores(0), best(0), features(0), scoresCap(0), bestCap(0), featuresCap(0), nFrames(0), capacity(cap),
+          dimension(D),
+          ld((M + 3) / 4 * 4),  // rows padded to 16 bytes: aligned row pieces on the device (include/gmm_b200.h)
+          token(0) {
+    features = static_cast<float*>(pool->acquire(size_t(capacity) * D * sizeof(float), featuresCap));
+    capacity = featuresCap / (D * sizeof(float));
+}
+
+/** Next frame of the batch, written where the H2D copy will read it.  A full block grows by half (segment mode:
+ *  the length of a segment is not known in advance). */
+bool GpuFeatureScorer::ScoreBlock::append(const Mm::FeatureVector& f) {
+    if (nFrames == capacity) {
+        size_t cap   = 0;
+        float* grown = static_cast<float*>(pool->acquire((size_t(capacity) + capacity / 2 + 64) * dimension * sizeof(float), cap));
+        if (!grown)
+            return false;
+        memcpy(grown, features, size_t(nFrames) * dimension * sizeof(float));
+        pool->release(features, featuresCap);
+        features    = grown;
+        featuresCap = cap;
+        capacity    = cap / (dimension * sizeof(float));
+    }
+    if (!features)
+        return false;
+    std::copy(f.begin(), f.end(), features + size_t(nFrames) * dimension);
+    ++nFrames;
+    return true;
+}
+
+void GpuFeatureScorer::ScoreBlock::allocateScores() {
+    if (!scores)
+        scores = static_cast<Mm::Score*>(pool->acquire(size_t(nFrames) * ld * sizeof(Mm::Score), scoresCap));
+}
+
+void GpuFeatureScorer::ScoreBlock::allocateBest() {
+    if (!best)
+        best = static_cast<u32*>(pool->acquire(size_t(nFrames) * ld * sizeof(u32), bestCap));
 }
 
 GpuFeatureScorer::ScoreBlock::~ScoreBlock() {
-    gmm_host_free(scores);
-    gmm_host_free(best);
+    pool->release(scores, scoresCap);
+    pool->release(best, bestCap);
+    pool->release(features, featuresCap);
 }
 
 // ---- context scorer --------------------------------------------------------------------------------------
-
-GpuFeatureScorer::Context::Context(const GpuFeatureScorer* parent, const Mm::FeatureVector& f)
-        : parent_(parent), row_(0), pending_(f.begin(), f.end()) {
-    require(f.size() == parent->dimension());  // as GaussDiagonalMaximumFeatureScorer.cc:32
-}
 
 Mm::EmissionIndex GpuFeatureScorer::Context::nEmissions() const {
     return parent_->nMixtures();
 }
 
+/** The first request for a frame without scores sends its whole batch to the GPU; a batch that is still in flight
+ *  (gmm_score_async) is waited for. */
+inline void GpuFeatureScorer::Context::ready(bool withBest) const {
+    if (!block_->scores)
+        parent_->scoreBlock(*block_, withBest);
+    if (block_->token)
+        parent_->complete(*block_);
+}
+
 Mm::Score GpuFeatureScorer::Context::score(Mm::EmissionIndex e) const {
     require_(0 <= e && e < nEmissions());
-    if (!block_)
-        parent_->scorePending(false);
-    return block_->scores[size_t(row_) * block_->nMixtures + e];
+    ready(false);
+    return block_->scores[size_t(row_) * block_->ld + e];
 }
 
 Mm::DensityInMixture GpuFeatureScorer::Context::bestDensity(Mm::EmissionIndex e) const {
     require_(0 <= e && e < nEmissions());
-    if (!block_)
-        parent_->scorePending(true);
+    ready(true);
     if (!block_->best)
         parent_->assignDensities(*block_);
-    return block_->best[size_t(row_) * block_->nMixtures + e];
+    return block_->best[size_t(row_) * block_->ld + e];
 }
 
+/** Not offered by the reference's diagonal scorers either: CachedAssigningFeatureScorer::calculateScore(cs, e, dns) is
+ *  a criticalError unless a subclass overrides it (src/Mm/AssigningFeatureScorer.hh:131-134), and neither
+ *  GaussDiagonalMaximumFeatureScorer nor GaussDiagonalSumFeatureScorer does. */
 Mm::Score GpuFeatureScorer::Context::score(Mm::EmissionIndex, Mm::DensityIndex) const {
-    parent_->criticalError("score(emission, density) is not available from the GPU feature scorer");
+    parent_->criticalError("This feature scorer does not support the calculation of scores given a density in the mixture");
     return Core::Type<Mm::Score>::max;
 }
 
-void GpuFeatureScorer::Context::getDensityPosteriorProbabilities(Mm::EmissionIndex, std::vector<Mm::Weight>&) const {
-    parent_->criticalError("getDensityPosteriorProbabilities() is not available from the GPU feature scorer");
+/** The sum scorer's density posteriors exp(score - s_k) (GaussDiagonalMaximumFeatureScorer.cc:291-298), which
+ *  AbstractMixtureSetEstimator accumulates in baum-welch mode (AbstractMixtureSetEstimator.cc:134-146,386-395).  The
+ *  maximum and the quantized scorers answer with the reference's criticalError (AssigningFeatureScorer.hh:135-138). */
+void GpuFeatureScorer::Context::getDensityPosteriorProbabilities(Mm::EmissionIndex e, std::vector<Mm::Weight>& result) const {
+    require_(0 <= e && e < nEmissions());
+    if (parent_->kind_ != kindSum) {
+        parent_->criticalError("This feature scorer does not support the calculation of density posterior probabilities");
+        return;
+    }
+    ready(false);
+    parent_->densityPosteriors(*block_, row_, e, result);
 }
 
 // ---- construction: pack the mixture set --------------------------------------------------------------------
@@ -80,10 +167,14 @@ GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const
           kind_(kind),
           handle_(0),
           bufferSize_(paramBufferSize(c)),
+          withBest_(paramDensityAssignment(c)),
+          pool_(new PinnedPool),
           nMixtures_(mixtureSet->nMixtures()),
           dimension_(mixtureSet->dimension()),
           nDensities_(0),
-          nBatches_(0) {
+          maxDensities_(0),
+          nBatches_(0),
+          nAssignmentPasses_(0) {
     if (gmm_create(&handle_, paramDevice(config)) != GMM_OK)
         criticalError("cannot create the GPU scoring engine: %s", gmm_last_error(0));
     // flat (mixture, density) slots, as BatchFeatureScorerBase::initialize (BatchFeatureScorer.cc:62-75)
@@ -91,21 +182,24 @@ GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const
     for (Mm::MixtureIndex m = 0; m < nMixtures_; ++m) {
         offsets_[m] = nDensities_;
         nDensities_ += mixtureSet->mixture(m)->nDensities();
+        maxDensities_ = std::max<u32>(maxDensities_, mixtureSet->mixture(m)->nDensities());
     }
     offsets_[nMixtures_] = nDensities_;
     if (kind_ == kindQuantized)
         initQuantized(*mixtureSet);
+    else if (kind_ == kindBatchInt)
+        initBatchInt(*mixtureSet);
     else
         initFloat(*mixtureSet);
     log("GPU feature scorer: %d mixtures, %d densities, dimension %d, %s, buffer size %d", int(nMixtures_),
         int(nDensities_), int(dimension_),
-        kind_ == kindQuantized ? "u8 quantized" : (gmm_float_kernel(handle_) == GMM_KERNEL_TENSOR ? "tensor-core kernel" : "direct kernel"),
+        quantized() ? "u8 quantized" : (gmm_float_kernel(handle_) == GMM_KERNEL_TENSOR ? "tensor-core kernel" : "direct kernel"),
         int(bufferSize_));
 }
 
 GpuFeatureScorer::~GpuFeatureScorer() {
     fifo_.clear();
-    pending_.clear();
+    staging_.reset();
     segment_.clear();
     gmm_destroy(handle_);
 }
@@ -206,20 +300,77 @@ void GpuFeatureScorer::initQuantized(const Mm::MixtureSet& ms) {
           "gmm_upload_quant");
 }
 
+/** tables of BatchIntFeatureScorer::quantizationScale / init (BatchFeatureScorer.cc:319-376), from the same
+ *  expressions under the same flags: the u8 grid of the SIMD scorer, constants (s32)(L s^2 - 2 s^2 logWeight), final
+ *  score q / (2 s^2) (:468).  The device kernel is the quantized scorer's. */
+void GpuFeatureScorer::initBatchInt(const Mm::MixtureSet& ms) {
+    if (ms.nCovariances() != 1)
+        criticalError("feature scorer supports only globally pooled variance");  // as BatchFeatureScorer.cc:340-342
+    const size_t                       D = dimension_, Dpad = ((D + 15) / 16) * 16;
+    Mm::CovarianceFeatureScorerElement covariance;
+    covariance = *ms.covariance(0);
+    std::vector<f32> variance(covariance.inverseSquareRootDiagonal().begin(), covariance.inverseSquareRootDiagonal().end());
+    Mm::MeanType     minMean = Core::Type<Mm::MeanType>::max, maxMean = Core::Type<Mm::MeanType>::min;
+    for (Mm::DensityIndex i = 0; i < ms.nDensities(); ++i) {
+        const Mm::Mean& mu = *ms.mean(ms.density(i)->meanIndex());
+        for (Mm::ComponentIndex d = 0; d < mu.size(); ++d) {
+            Mm::MeanType v = mu[d] * variance[d];
+            minMean        = std::min(minMean, v);
+            maxMean        = std::max(maxMean, v);
+        }
+    }
+    const int quantizedIntervalSize = (int)Core::Type<u8>::max - (int)Core::Type<u8>::min;
+    f32       intervalSize          = 2 * std::max(Core::abs(minMean), Core::abs(maxMean));
+    f32       scale                 = static_cast<f32>(quantizedIntervalSize) / (1.25 * intervalSize);
+    f32       scaleSquared          = scale * scale;
+    f32       scale2                = 2.0 * scaleSquared;
+    for (size_t d = 0; d < D; ++d)
+        variance[d] = variance[d] * scale;
+    const float      logNormFactor = covariance.logNormalizationFactor() * scaleSquared;
+    std::vector<u8>  qmean(size_t(nDensities_) * Dpad, 0);
+    std::vector<s32> qconst(nDensities_);
+    std::vector<u32> covIdx(nDensities_, 0);
+    Mm::quantize<f32, u8> quantize;
+    for (Mm::MixtureIndex m = 0; m < nMixtures_; ++m) {
+        const Mm::Mixture& mixture = *ms.mixture(m);
+        for (size_t k = 0; k < mixture.nDensities(); ++k) {
+            const size_t    g  = offsets_[m] + k;
+            const Mm::Mean& mu = *ms.mean(ms.density(mixture.densityIndex(k))->meanIndex());
+            for (size_t d = 0; d < D; ++d)
+                qmean[g * Dpad + d] = quantize(mu[d] * variance[d]);
+            qconst[g] = static_cast<s32>(logNormFactor - scale2 * mixture.logWeight(k));
+        }
+    }
+    check(gmm_upload_quant(handle_, nMixtures_, nDensities_, D, Dpad, 1, &offsets_[0], qmean.empty() ? 0 : &qmean[0],
+                           &covIdx[0], &qconst[0], &variance[0], scale2 * 0.5f),
+          "gmm_upload_quant");
+    check(gmm_quant_final_score_rule(handle_, GMM_QUANT_RULE_BATCH_INT), "gmm_quant_final_score_rule");
+}
+
 // ---- buffered protocol (FeatureScorer.hh:86-134; state machine of BatchFeatureScorer.cc:40-105) -------------
 
 void GpuFeatureScorer::reset() const {
     fifo_.clear();
-    pending_.clear();
+    staging_.reset();  // contexts a caller still holds keep their block and can still be scored
     segment_.clear();
 }
 
 void GpuFeatureScorer::push(const Mm::FeatureVector& f) const {
-    ContextRef c(new Context(this, f));
+    require(f.size() == dimension_);  // as GaussDiagonalMaximumFeatureScorer.cc:32
+    if (!staging_)
+        staging_ = Core::Ref<ScoreBlock>(new ScoreBlock(pool_, bufferSize_ ? bufferSize_ : 1024, nMixtures_, dimension_));
+    if (!staging_->append(f))
+        criticalError("cannot allocate page-locked memory for %d frames", int(staging_->nFrames + 1));
+    ContextRef c(new Context(this, staging_, staging_->nFrames - 1));
     fifo_.push_back(c);
-    pending_.push_back(c);
     if (bufferSize_ == 0)
         segment_.push_back(c);
+    // Frames go to the GPU while the caller is still handing in (or consuming) others (gmm_score_async; the precedent
+    // is src/Nn/BatchFeatureScorer.cc:92-170): in streaming mode half a buffer at a time, in segment mode every
+    // kSegmentBatch frames, so that the scores of a long segment are already on their way over the host link when the
+    // first one is asked for.  The float engine only.
+    if (!quantized() && staging_->nFrames >= (bufferSize_ ? std::max<u32>(2, bufferSize_ / 2) : u32(kSegmentBatch)))
+        scoreBlock(*staging_, withBest_, true);
 }
 
 void GpuFeatureScorer::addFeature(const Mm::FeatureVector& f) const {
@@ -247,47 +398,59 @@ Mm::FeatureScorer::Scorer GpuFeatureScorer::getTimeIndexedScorer(u32 time) const
     return Scorer(segment_[time].get());
 }
 
-/** One GPU batch over every frame that has no scores yet. */
-void GpuFeatureScorer::scorePending(bool withBest) const {
-    const u32 T = pending_.size();
-    if (T == 0)
-        return;
-    Core::Ref<ScoreBlock> block(new ScoreBlock(T, nMixtures_));
-    if (!block->scores)
-        criticalError("cannot allocate page-locked memory for %d x %d scores", int(T), int(nMixtures_));
-    block->features.resize(size_t(T) * dimension_);
-    for (u32 t = 0; t < T; ++t)
-        std::copy(pending_[t]->pending_.begin(), pending_[t]->pending_.end(),
-                  block->features.begin() + size_t(t) * dimension_);
-    if (withBest) {
-        block->best = static_cast<u32*>(gmm_host_alloc(size_t(T) * nMixtures_ * sizeof(u32)));
-        if (!block->best)
-            criticalError("cannot allocate page-locked memory for the density assignment");
+/** One GPU batch over the frames of a block.  async: enqueue only (gmm_score_async); the first score() of one of its
+ *  frames waits for the token.  The block stops taking frames: the next frame opens a new one. */
+void GpuFeatureScorer::scoreBlock(ScoreBlock& block, bool withBest, bool async) const {
+    if (staging_.get() == &block)
+        staging_.reset();  // the contexts hold the block
+    withBest = withBest || withBest_;
+    block.allocateScores();
+    if (withBest)
+        block.allocateBest();
+    if (!block.scores || (withBest && !block.best))
+        criticalError("cannot allocate page-locked memory for %d x %d scores", int(block.nFrames), int(nMixtures_));
+    const u32 T = block.nFrames;
+    if (quantized())
+        check(gmm_quant_score_host(handle_, T, block.features, 0, block.best, block.scores, 0, block.ld), "gmm_quant_score_host");
+    else if (async) {
+        uint64_t token = 0;
+        check(gmm_score_async(handle_, T, block.features, block.scores, block.best, block.ld, &token), "gmm_score_async");
+        block.token = token;
     }
-    if (kind_ == kindQuantized)
-        check(gmm_quant_score_host(handle_, T, &block->features[0], 0, block->best, block->scores, 0, nMixtures_),
-              "gmm_quant_score_host");
     else
-        check(gmm_score_host(handle_, T, &block->features[0], block->scores, block->best, nMixtures_), "gmm_score_host");
-    for (u32 t = 0; t < T; ++t) {
-        pending_[t]->block_ = block;
-        pending_[t]->row_   = t;
-        std::vector<float>().swap(pending_[t]->pending_);
-    }
-    pending_.clear();
+        check(gmm_score_host(handle_, T, block.features, block.scores, block.best, block.ld), "gmm_score_host");
     ++nBatches_;
+}
+
+/** The block's asynchronous call has finished (its scores are in host memory). */
+void GpuFeatureScorer::complete(ScoreBlock& block) const {
+    check(gmm_wait(handle_, block.token), "gmm_wait");
+    block.token = 0;
 }
 
 /** bestDensity() on a block that was scored without the assignment: one more pass over its frames. */
 void GpuFeatureScorer::assignDensities(ScoreBlock& block) const {
-    const size_t n = size_t(block.nFrames) * block.nMixtures;
-    block.best     = static_cast<u32*>(gmm_host_alloc(n * sizeof(u32)));
+    block.allocateBest();
     if (!block.best)
         criticalError("cannot allocate page-locked memory for the density assignment");
-    if (kind_ == kindQuantized)
-        check(gmm_quant_score_host(handle_, block.nFrames, &block.features[0], 0, block.best, 0, 0, block.nMixtures),
+    check(gmm_sync(handle_), "gmm_sync");  // no asynchronous call in flight while a blocking one runs
+    ++nAssignmentPasses_;
+    if (quantized())
+        check(gmm_quant_score_host(handle_, block.nFrames, block.features, 0, block.best, 0, 0, block.ld),
               "gmm_quant_score_host");
     else
-        check(gmm_score_host(handle_, block.nFrames, &block.features[0], block.scores, block.best, block.nMixtures),
-              "gmm_score_host");
+        check(gmm_score_host(handle_, block.nFrames, block.features, block.scores, block.best, block.ld), "gmm_score_host");
+}
+
+/** Density posteriors of emission e for one frame of a scored block (sum scorer). */
+void GpuFeatureScorer::densityPosteriors(const ScoreBlock& block, u32 row, Mm::EmissionIndex e,
+                                         std::vector<Mm::Weight>& result) const {
+    const u32          K = offsets_[e + 1] - offsets_[e];
+    std::vector<float> post(std::max<u32>(1, maxDensities_), 0.f);
+    const uint32_t     mixture = e;
+    check(gmm_sync(handle_), "gmm_sync");
+    check(gmm_mixture_posteriors_host(handle_, 1, block.features + size_t(row) * dimension_, &mixture, &post[0],
+                                      post.size(), 0),
+          "gmm_mixture_posteriors_host");
+    result.assign(post.begin(), post.begin() + K);
 }

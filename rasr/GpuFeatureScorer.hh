@@ -1,11 +1,12 @@
 /** RASR-side plugin: GPU GMM feature scorers behind Mm::FeatureScorerFactory.
  *
  *  Compiled INTO RASR (module MODULE_MM_GPU, see rasr/Module.hh and INTEGRATION.md); binds only to the C-ABI of
- *  include/gmm_b200.h (libgmm_b200.so, hand-written CUDA for sm_100a).  Three scorers, drop-in for
+ *  include/gmm_b200.h (libgmm_b200.so, hand-written CUDA for sm_100a).  Four scorers, drop-in for
  *
  *    gpu-diagonal-maximum        Mm::GaussDiagonalMaximumFeatureScorer      (src/Mm/GaussDiagonalMaximumFeatureScorer.hh:31-92)
  *    gpu-diagonal-sum            Mm::GaussDiagonalSumFeatureScorer          (src/Mm/GaussDiagonalMaximumFeatureScorer.hh:96-115)
  *    gpu-SIMD-diagonal-maximum   Mm::SimdGaussDiagonalMaximumFeatureScorer  (src/Mm/SimdFeatureScorer.hh:35-139)
+ *    gpu-batch-diagonal-maximum-int  Mm::BatchIntFeatureScorer              (src/Mm/BatchFeatureScorer.hh:292-340)
  *
  *  They implement the buffered protocol of Mm::FeatureScorer (src/Mm/FeatureScorer.hh:86-134) so that
  *  Speech::OfflineRecognizer / DelayedRecognizer / AlignmentNode / FeatureScorerNode and Flf's recognizer feed
@@ -33,35 +34,61 @@ class GpuFeatureScorer : public Mm::AssigningFeatureScorer {
     typedef Mm::AssigningFeatureScorer Precursor;
 
 public:
-    enum Kind { kindMaximum, kindSum, kindQuantized };
+    enum Kind { kindMaximum, kindSum, kindQuantized, kindBatchInt };
 
     static const Core::ParameterInt   paramBufferSize;          // "buffer-size", as BatchFeatureScorer.cc:28-29
     static const Core::ParameterInt   paramDevice;              // "device"
     static const Core::ParameterInt   paramKernel;              // "kernel": 0 auto, 1 direct, 2 tensor
     static const Core::ParameterFloat paramMixtureWeightScale;  // as GaussDiagonalMaximumFeatureScorer.cc:37-39
     static const Core::ParameterFloat paramGaussianScale;       // as GaussDiagonalMaximumFeatureScorer.cc:41-43
+    static const Core::ParameterBool  paramDensityAssignment;   // "with-density-assignment": training consumers
 
 protected:
-    /** Scores of one GPU batch in page-locked host memory; kept alive by the contexts that point into it
-     *  (callers keep Scorer handles of a whole segment, src/Speech/AlignmentNode.cc:281-306). */
+    /** Page-locked host buffers, recycled: cudaMallocHost is a page-locking system call (milliseconds for the 18 MB of
+     *  a 1000-frame segment), so blocks return their memory here instead of freeing it.  Shared by the scorer and its
+     *  blocks, which may outlive it. */
+    class PinnedPool : public Core::ReferenceCounted {
+        struct Buffer {
+            void*  ptr;
+            size_t bytes;
+        };
+        std::vector<Buffer> free_;
+
+    public:
+        ~PinnedPool();
+        void* acquire(size_t bytes, size_t& capacity);
+        void  release(void* ptr, size_t capacity);
+    };
+
+    /** One GPU batch in page-locked host memory: the frames as they are handed in, and, once scored, their scores.
+     *  Kept alive by the contexts that point into it (callers keep Scorer handles of a whole segment,
+     *  src/Speech/AlignmentNode.cc:281-306).  Frames are written straight into the page-locked block the H2D copy
+     *  reads, and contexts point at their block from the start: scoring a batch touches no context. */
     struct ScoreBlock : public Core::ReferenceCounted {
-        Mm::Score*         scores;
-        u32*               best;  // 0 until a density assignment was requested
-        std::vector<float> features;
-        u32                nFrames, nMixtures;
-        ScoreBlock(u32 T, u32 M);
+        Core::Ref<PinnedPool> pool;
+        Mm::Score*            scores;    // [nFrames x ld]; 0 until the batch went to the GPU
+        u32*                  best;      // [nFrames x ld]; 0 until a density assignment was requested
+        float*                features;  // [capacity x dimension]
+        size_t                scoresCap, bestCap, featuresCap;
+        u32                   nFrames, capacity, dimension, ld;
+        u64                   token;     // != 0: an asynchronous call is still filling the block (gmm_wait)
+        ScoreBlock(Core::Ref<PinnedPool> pool, u32 capacity, u32 M, u32 D);
         ~ScoreBlock();
+        bool append(const Mm::FeatureVector& f);
+        void allocateScores();
+        void allocateBest();
     };
 
     class Context : public AssigningContextScorer {
         friend class GpuFeatureScorer;
-        const GpuFeatureScorer*   parent_;
-        mutable Core::Ref<ScoreBlock> block_;
-        mutable u32               row_;
-        mutable std::vector<float> pending_;  // the frame until its batch has been scored
+        const GpuFeatureScorer* parent_;
+        Core::Ref<ScoreBlock>   block_;
+        u32                     row_;
+        void ready(bool withBest) const;
 
     public:
-        Context(const GpuFeatureScorer* parent, const Mm::FeatureVector& f);
+        Context(const GpuFeatureScorer* parent, Core::Ref<ScoreBlock> block, u32 row)
+                : parent_(parent), block_(block), row_(row) {}
         virtual ~Context() {}
         virtual Mm::EmissionIndex    nEmissions() const;
         virtual Mm::Score            score(Mm::EmissionIndex e) const;
@@ -116,28 +143,46 @@ public:
     u32 nBatches() const {
         return nBatches_;
     }
+    /** second passes over a batch for a density assignment that was not computed with its scores */
+    u32 nAssignmentPasses() const {
+        return nAssignmentPasses_;
+    }
+    /** the engine behind this scorer (include/gmm_b200.h), for callers that time or share it */
+    gmm_handle* handle() const {
+        return handle_;
+    }
 
 private:
     void initFloat(const Mm::MixtureSet& mixtureSet);
     void initQuantized(const Mm::MixtureSet& mixtureSet);
+    void initBatchInt(const Mm::MixtureSet& mixtureSet);
+    bool quantized() const {
+        return kind_ == kindQuantized || kind_ == kindBatchInt;
+    }
     void push(const Mm::FeatureVector& f) const;
-    void scorePending(bool withBest) const;
+    void scoreBlock(ScoreBlock& block, bool withBest, bool async = false) const;
     void assignDensities(ScoreBlock& block) const;
+    void complete(ScoreBlock& block) const;
+    void densityPosteriors(const ScoreBlock& block, u32 row, Mm::EmissionIndex e, std::vector<Mm::Weight>& result) const;
     void check(int rc, const char* what) const;
 
+    enum { kSegmentBatch = 1024 };  // segment mode: frames per asynchronous batch
     Kind               kind_;
     gmm_handle*        handle_;
     u32                bufferSize_;
+    bool               withBest_;
+    Core::Ref<PinnedPool> pool_;
     Mm::EmissionIndex  nMixtures_;
     Mm::ComponentIndex dimension_;
     Mm::DensityIndex   nDensities_;
+    u32                maxDensities_;  // most densities in one mixture
     std::vector<u32>   offsets_;
 
     typedef Core::Ref<const Context>       ContextRef;
     mutable std::deque<ContextRef>         fifo_;     // frames handed in, oldest first, not yet handed out
-    mutable std::vector<ContextRef>        pending_;  // frames without scores yet (time order)
+    mutable Core::Ref<ScoreBlock>          staging_;  // frames handed in since the last batch (no scores yet)
     mutable std::vector<ContextRef>        segment_;  // segment mode: every frame since reset()
-    mutable u32                            nBatches_;
+    mutable u32                            nBatches_, nAssignmentPasses_;
 };
 
 class GpuGaussDiagonalMaximumFeatureScorer : public GpuFeatureScorer {
@@ -156,6 +201,13 @@ class GpuSimdGaussDiagonalMaximumFeatureScorer : public GpuFeatureScorer {
 public:
     GpuSimdGaussDiagonalMaximumFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> m)
             : Core::Component(c), GpuFeatureScorer(c, m, kindQuantized) {}
+};
+
+/** The u8 kernel with the constants and the final scale of Mm::BatchIntFeatureScorer; pooled covariance only. */
+class GpuBatchIntFeatureScorer : public GpuFeatureScorer {
+public:
+    GpuBatchIntFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> m)
+            : Core::Component(c), GpuFeatureScorer(c, m, kindBatchInt) {}
 };
 
 }  // namespace MmGpu

@@ -17,4 +17,6 @@ Module_::Module_() {
             gpuDiagonalSum, "gpu-diagonal-sum");
     factory->registerFeatureScorer<GpuSimdGaussDiagonalMaximumFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(
             gpuSimdDiagonalMaximum, "gpu-SIMD-diagonal-maximum");
+    factory->registerFeatureScorer<GpuBatchIntFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(
+            gpuBatchIntDiagonalMaximum, "gpu-batch-diagonal-maximum-int");
 }

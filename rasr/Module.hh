@@ -18,6 +18,7 @@ public:
         gpuDiagonalMaximum     = FeatureScorerTypeOffset,
         gpuDiagonalSum         = FeatureScorerTypeOffset + 1,
         gpuSimdDiagonalMaximum = FeatureScorerTypeOffset + 2,
+        gpuBatchIntDiagonalMaximum = FeatureScorerTypeOffset + 3,
     };
 };
 

@@ -1,14 +1,23 @@
-// TEST HARNESS: the GPU scorers and the reference's own scorers side by side INSIDE a RASR process, created through
-// Mm::FeatureScorerFactory exactly as Mm::Module_::createFeatureScorer does (src/Mm/Module.cc:301-309) and driven by
-// the buffered caller loop of Speech::AlignmentNode (src/Speech/AlignmentNode.cc:283-306).  Links the unmodified
-// reference objects built by oracle/ref_build/Makefile; lives next to them in oracle/_ref/ (not product code).
+// TEST HARNESS: the GPU scorers and the reference's own scorers side by side INSIDE a RASR process.  Both come out of
+// the reference's own Mm::Module_ -- the factory MmGpu::Module_ registers in (rasr/Module.cc, as src/Nn/Module.cc:47-65
+// does), selected by `feature-scorer-type` (src/Mm/Module.cc:78-80,301-309) and wrapped in Mm::FeatureScorerScaling
+// (createScaledFeatureScorer, src/Mm/Module.cc:326-328), i.e. exactly what Am::ClassicAcousticModel::loadMixtureSet
+// hands to Speech and Search (src/Am/ClassicAcousticModel.cc:153-165).  Links the unmodified reference objects built by
+// oracle/ref_build/Makefile; lives next to them in oracle/_ref/ (not product code).
 //
 //   rasr_gpu_check model=<gms> features=<f32> [buffer-size=N]
-// exit code 0 iff: quantized scorer bit-identical, float direct kernel bit-identical, tensor kernel and sum scorer
-// within 1e-4 relative, density assignments equal (float: up to ties within tolerance).
+// One line per case, PASS / FAIL; exit code 0 iff all pass:
+//   quantized scorer and float direct kernel bit-identical to the reference, tensor kernel and sum scorer within 1e-4
+//   relative, density assignments equal (float: up to ties within tolerance) -- all through the scaled wrapper and the
+//   buffered caller loop of Speech::AlignmentNode (src/Speech/AlignmentNode.cc:283-306); then the delayed-recognizer
+//   loop (src/Speech/DelayedRecognizer.cc:72-175), the time-indexed cache (src/Mm/FeatureScorer.hh:157-163), the sum
+//   scorer's density posteriors (src/Mm/AssigningFeatureScorer.hh:46-47) and with-density-assignment; and a TIMING line.
+#include <chrono>
+#include <cstdarg>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <fstream>
 #include <iostream>
 #include <map>
@@ -18,17 +27,14 @@
 #include <Mm/GaussDiagonalMaximumFeatureScorer.hh>
 #include <Mm/MixtureSet.hh>
 #include <Mm/MixtureSetLoader.hh>
+#include <Mm/Module.hh>
+#include <Mm/ScaledFeatureScorer.hh>
 #include <Mm/SimdFeatureScorer.hh>
+
+#include <gmm_b200.h>
 
 #include "GpuFeatureScorer.hh"
 #include "Module.hh"
-
-// Harness stub (like oracle/ref_build/stubs): the factory only stores a loader object per scorer id; the file loaders
-// themselves (src/Mm/MixtureSetLoader.cc -> Mm::Module_::readMixtureSet) pull in the whole estimator stack and are
-// not needed here because the mixture set is built in memory.
-Core::Ref<Mm::AbstractMixtureSet> Mm::AbstractMixtureSetLoader::load(const std::string&, const Core::Configuration&) const {
-    return Core::Ref<Mm::AbstractMixtureSet>();
-}
 
 namespace {
 
@@ -79,13 +85,18 @@ Core::Ref<Mm::MixtureSet> loadGms(const std::string& path) {
     return ms;
 }
 
+// the assigning context scorer's class name is protected; its public handle type names it
+typedef std::remove_reference<decltype(*std::declval<Mm::AssigningFeatureScorer::AssigningScorer>())>::type AssigningContext;
+
 struct Result {
     std::vector<f32> score;
     std::vector<u32> best;
 };
 
-// the caller loop of Speech/AlignmentNode.cc:283-306, then eager evaluation of every emission
-Result drive(const Mm::FeatureScorer& fs, const std::vector<Mm::FeatureVector>& X, bool assigning) {
+// the caller loop of Speech/AlignmentNode.cc:283-306, then eager evaluation of every emission; `assign` (the scorer
+// inside the scaling wrapper) answers the density assignment through the unbuffered assigning interface
+// (AssigningFeatureScorer.hh:66-70), as the estimators use it (src/Mm/AbstractMixtureSetEstimator.cc:377-393)
+Result drive(const Mm::FeatureScorer& fs, const Mm::FeatureScorer* assign, const std::vector<Mm::FeatureVector>& X) {
     std::vector<Mm::FeatureScorer::Scorer> scorers;
     fs.reset();
     for (size_t t = 0; t < X.size(); ++t) {
@@ -101,11 +112,9 @@ Result drive(const Mm::FeatureScorer& fs, const std::vector<Mm::FeatureVector>& 
     for (size_t t = 0; t < scorers.size(); ++t)
         for (u32 m = 0; m < M; ++m)
             r.score.push_back(scorers[t]->score(m));
-    // density assignment through the unbuffered assigning interface (AssigningFeatureScorer.hh:66-70), as the
-    // estimators use it (src/Mm/AbstractMixtureSetEstimator.cc:377-393)
-    const Mm::AssigningFeatureScorer* afs = assigning ? dynamic_cast<const Mm::AssigningFeatureScorer*>(&fs) : 0;
+    const Mm::AssigningFeatureScorer* afs = dynamic_cast<const Mm::AssigningFeatureScorer*>(assign);
     if (afs) {
-        fs.reset();
+        afs->reset();
         for (size_t t = 0; t < X.size(); ++t) {
             Mm::AssigningFeatureScorer::AssigningScorer a = afs->getAssigningScorer(X[t]);
             for (u32 m = 0; m < M; ++m)
@@ -115,11 +124,92 @@ Result drive(const Mm::FeatureScorer& fs, const std::vector<Mm::FeatureVector>& 
     return r;
 }
 
+// Speech::RecognizerDelayHandler (src/Speech/DelayedRecognizer.cc:72-175) without a cache and with look-ahead length 0:
+// a feature buffer of scorer->bufferSize() frames, initializeBatchScorer() primes the scorer with addFeature() until
+// bufferFilled(), every further frame goes in through getScorer(), the rest comes out through flush().
+Result driveDelayed(const Mm::FeatureScorer& fs, const std::vector<Mm::FeatureVector>& X) {
+    Result                        r;
+    const u32                     M = fs.nMixtures();
+    const size_t                  bufferSize = std::min<size_t>(fs.bufferSize(), X.size() + 1);
+    std::deque<Mm::FeatureVector> buffer;
+    size_t                        offset = 0;
+    bool                          initialize = true;
+    fs.reset();
+    auto prime = [&]() {  // initializeBatchScorer
+        size_t pos = 0;
+        while (!fs.bufferFilled() && pos < buffer.size())
+            fs.addFeature(buffer[pos++]);
+        offset     = pos;
+        initialize = false;
+    };
+    auto feed = [&](Mm::FeatureScorer::Scorer sc) {
+        for (u32 m = 0; m < M; ++m)
+            r.score.push_back(sc->score(m));
+    };
+    for (size_t t = 0; t < X.size(); ++t) {  // add()
+        if (buffer.size() < bufferSize) {
+            buffer.push_back(X[t]);
+            continue;
+        }
+        if (fs.isBuffered() && initialize)
+            prime();
+        buffer.push_back(X[t]);
+        Mm::FeatureScorer::Scorer sc = fs.getScorer(buffer[offset]);
+        buffer.pop_front();
+        feed(sc);
+    }
+    while (!buffer.empty()) {  // flush()
+        if (fs.isBuffered() && initialize)
+            prime();
+        Mm::FeatureScorer::Scorer sc = buffer.size() > offset ? fs.getScorer(buffer[offset]) : fs.flush();
+        buffer.pop_front();
+        feed(sc);
+    }
+    return r;
+}
+
+struct Diff {
+    size_t nBits, nBest;
+    double maxRel;
+    bool   shape;
+};
+
+Diff compare(const Result& a, const Result& b) {
+    Diff d = {0, 0, 0.0, a.score.size() == b.score.size() && a.best.size() == b.best.size()};
+    for (size_t i = 0; d.shape && i < a.score.size(); ++i) {
+        if (memcmp(&a.score[i], &b.score[i], 4))
+            ++d.nBits;
+        if (std::isfinite(a.score[i]) && std::fabs(a.score[i]) < 1e37)
+            d.maxRel = std::max(d.maxRel, (double)std::fabs(a.score[i] - b.score[i]) / std::max(1e-3, (double)std::fabs(a.score[i])));
+    }
+    for (size_t i = 0; d.shape && i < a.best.size(); ++i)
+        if (a.best[i] != b.best[i])
+            ++d.nBest;
+    return d;
+}
+
+double now() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 }  // namespace
 
 class CheckApp : public Core::Application {
+    int failures_;
+
+    void report(const char* name, bool ok, const char* fmt, ...) {
+        char    buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        printf("%-44s %s  %s\n", name, ok ? "PASS" : "FAIL", buf);
+        failures_ += !ok;
+    }
+
 public:
-    CheckApp() {
+    CheckApp()
+            : failures_(0) {
         setTitle("rasr-gpu-check");
         setDefaultLoadConfigurationFile(false);
         setDefaultOutputXmlHeader(false);
@@ -128,15 +218,17 @@ public:
         return "rasr_gpu_check model=<gms> features=<f32> [buffer-size=N]\n";
     }
 
-    Mm::FeatureScorer* create(const Mm::FeatureScorerFactory& factory, u32 id, const std::string& sel, int kernel,
-                              int bufferSize, Core::Ref<const Mm::MixtureSet> ms) {
+    // `*.mixture-set.feature-scorer-type = <name>` and the scorer's own parameters, as a RASR config file would set them
+    Core::Configuration scorerConfig(const std::string& sel, const std::string& type, int kernel, int bufferSize,
+                                     bool withAssignment = false) {
         Core::Configuration c(config, sel);
-        c.set(c.getSelection() + ".kernel", Core::form("%d", kernel));
-        c.set(c.getSelection() + ".buffer-size", Core::form("%d", bufferSize));
-        Mm::FeatureScorer* fs = factory.createFeatureScorer(id, c, ms);
-        if (!fs)
-            criticalError("Cannot create feature scorer!");  // as Mm/Module.cc:303-307
-        return fs;
+        const std::string   s = c.getSelection();
+        c.set(s + ".feature-scorer-type", type);
+        c.set(s + ".kernel", Core::form("%d", kernel));
+        c.set(s + ".buffer-size", Core::form("%d", bufferSize));
+        c.set(s + ".with-density-assignment", withAssignment ? "true" : "false");
+        c.set(s + ".scale", "0.75");  // Mc::Component::paramScale of the scaling wrapper
+        return c;
     }
 
     int main(const std::vector<std::string>& arguments) {
@@ -160,56 +252,198 @@ public:
         std::vector<f32> flat(size_t(in.tellg()) / 4);
         in.seekg(0);
         in.read(reinterpret_cast<char*>(&flat[0]), flat.size() * 4);
-        const u32                      D = ms->dimension();
+        const u32                      D = ms->dimension(), M = ms->nMixtures();
         std::vector<Mm::FeatureVector> X(flat.size() / D, Mm::FeatureVector(D));
         for (size_t t = 0; t < X.size(); ++t)
             std::copy(flat.begin() + t * D, flat.begin() + (t + 1) * D, X[t].begin());
         const int bufferSize = args.count("buffer-size") ? atoi(args["buffer-size"].c_str()) : 0;
 
-        // the factory, filled the way Mm::Module_::Module_ and MmGpu::Module_::Module_ fill it
-        Mm::FeatureScorerFactory factory;
-        enum { refMax = 1, refSum = 2, refSimd = 3 };
-        factory.registerFeatureScorer<Mm::GaussDiagonalMaximumFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(refMax, "diagonal-maximum");
-        factory.registerFeatureScorer<Mm::GaussDiagonalSumFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(refSum, "diagonal-sum");
-        factory.registerFeatureScorer<Mm::SimdGaussDiagonalMaximumFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(refSimd, "SIMD-diagonal-maximum");
-        typedef MmGpu::Module_ G;
-        factory.registerFeatureScorer<MmGpu::GpuGaussDiagonalMaximumFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(G::gpuDiagonalMaximum, "gpu-diagonal-maximum");
-        factory.registerFeatureScorer<MmGpu::GpuGaussDiagonalSumFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(G::gpuDiagonalSum, "gpu-diagonal-sum");
-        factory.registerFeatureScorer<MmGpu::GpuSimdGaussDiagonalMaximumFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(G::gpuSimdDiagonalMaximum, "gpu-SIMD-diagonal-maximum");
+        // INIT_MODULE(Mm); INIT_MODULE(MmGpu);  (src/Tools/SpeechRecognizer/SpeechRecognizer.cc:46-56)
+        Mm::Module::instance();
+        MmGpu::Module::instance();
+        const Mm::Module_& mm = Mm::Module::instance();
 
-        int failures = 0;
+        // ---- 1-5: every scorer pair through factory + scaling wrapper + the AlignmentNode loop ----------------------
         struct Case {
-            const char* name;
-            u32         refId, gpuId;
+            const char *name, *refType, *gpuType;
             int         kernel;
-            bool        exact;
-        } cases[] = {{"diagonal-maximum / direct kernel", refMax, G::gpuDiagonalMaximum, 1, true},
-                     {"diagonal-maximum / auto kernel", refMax, G::gpuDiagonalMaximum, 0, false},
-                     {"diagonal-sum / auto kernel", refSum, G::gpuDiagonalSum, 0, false},
-                     {"SIMD-diagonal-maximum", refSimd, G::gpuSimdDiagonalMaximum, 0, true}};
+            bool        exact, pooledOnly;
+        } cases[] = {{"diagonal-maximum / direct kernel", "diagonal-maximum", "gpu-diagonal-maximum", 1, true, false},
+                     {"diagonal-maximum / auto kernel", "diagonal-maximum", "gpu-diagonal-maximum", 0, false, false},
+                     {"diagonal-sum / auto kernel", 0, "gpu-diagonal-sum", 0, false, false},
+                     {"SIMD-diagonal-maximum", "SIMD-diagonal-maximum", "gpu-SIMD-diagonal-maximum", 0, true, false},
+                     // the reference's scorer is a plain buffered FeatureScorer without a density assignment
+                     {"batch-diagonal-maximum-int", "batch-diagonal-maximum-int", "gpu-batch-diagonal-maximum-int", 0, true, true}};
         for (size_t ci = 0; ci < sizeof(cases) / sizeof(cases[0]); ++ci) {
-            const Case&                    k = cases[ci];
-            Core::Ref<Mm::FeatureScorer>   ref(create(factory, k.refId, "ref", 0, 0, ms));
-            Core::Ref<Mm::FeatureScorer>   gpu(create(factory, k.gpuId, "gpu", k.kernel, bufferSize, ms));
-            Result                         a = drive(*ref, X, true), b = drive(*gpu, X, true);
-            size_t                         nBits = 0, nBest = 0;
-            double                         maxRel = 0.0;
-            bool                           shape  = a.score.size() == b.score.size() && a.best.size() == b.best.size();
-            for (size_t i = 0; shape && i < a.score.size(); ++i) {
-                if (memcmp(&a.score[i], &b.score[i], 4))
-                    ++nBits;
-                if (std::isfinite(a.score[i]) && std::fabs(a.score[i]) < 1e37)
-                    maxRel = std::max(maxRel, (double)std::fabs(a.score[i] - b.score[i]) / std::max(1.0, (double)std::fabs(a.score[i])));
-                if (a.best[i] != b.best[i])
-                    ++nBest;
+            const Case&                  k = cases[ci];
+            if (k.pooledOnly && ms->nCovariances() != 1) {
+                printf("%-44s SKIP  needs a globally pooled variance (criticalError in both, BatchFeatureScorer.cc:340-342)\n", k.name);
+                continue;
             }
-            bool ok = shape && (k.exact ? (nBits == 0 && nBest == 0) : (maxRel <= 1e-4 && nBest * 1000 <= a.best.size()));
-            printf("%-36s %s  frames=%zu values=%zu differing-bits=%zu max-rel=%.3e best-mismatch=%zu batches=%u\n", k.name,
-                   ok ? "PASS" : "FAIL", X.size(), a.score.size(), nBits, maxRel, nBest,
-                   dynamic_cast<const MmGpu::GpuFeatureScorer*>(gpu.get())->nBatches());
-            failures += !ok;
+            // (the reference's batch scorers need a ring of at least one frame: their default buffer-size, 4)
+            Core::Configuration          rc = scorerConfig("ref", k.refType ? k.refType : "diagonal-maximum", 0, k.pooledOnly ? 4 : 0);
+            Core::Configuration          gc = scorerConfig("gpu", k.gpuType, k.kernel, bufferSize);
+            // the reference does not register its sum scorer: constructed directly
+            Core::Ref<Mm::FeatureScorer> ref = k.refType ? mm.createFeatureScorer(rc, ms)
+                                                         : Core::Ref<Mm::FeatureScorer>(new Mm::GaussDiagonalSumFeatureScorer(rc, ms));
+            Core::Ref<Mm::FeatureScorer> gpu = mm.createFeatureScorer(gc, ms);
+            Core::Ref<Mm::ScaledFeatureScorer> refScaled = mm.createScaledFeatureScorer(rc, ref);
+            Core::Ref<Mm::ScaledFeatureScorer> gpuScaled = mm.createScaledFeatureScorer(gc, gpu);
+            // the reference's batch scorers keep the frames in a ring of buffer-size entries: a context scorer must
+            // be read before the ring comes round, as the recognizers do -- the delayed loop reads at once
+            Result a = k.pooledOnly ? driveDelayed(*refScaled, X) : drive(*refScaled, ref.get(), X);
+            Result b = k.pooledOnly ? driveDelayed(*gpuScaled, X) : drive(*gpuScaled, gpu.get(), X);
+            Diff   d = compare(a, b);
+            bool   ok = d.shape && (k.exact ? (d.nBits == 0 && d.nBest == 0) : (d.maxRel <= 1e-4 && d.nBest * 1000 <= a.best.size()));
+            // the wrapper multiplies by its scale (ScaledFeatureScorer.hh:62-64): spot-check against the bare scorer
+            gpu->reset();
+            Mm::FeatureScorer::Scorer bare = gpu->isBuffered() ? (gpu->addFeature(X[0]), gpu->flush()) : gpu->getScorer(X[0]);
+            ok = ok && b.score[0] == Mm::Score(0.75) * bare->score(0);
+            report(k.name, ok, "frames=%zu values=%zu differing-bits=%zu max-rel=%.3e best-mismatch=%zu batches=%u", X.size(),
+                   a.score.size(), d.nBits, d.maxRel, d.nBest, dynamic_cast<const MmGpu::GpuFeatureScorer*>(gpu.get())->nBatches());
         }
-        return failures ? 1 : 0;
+
+        // ---- 5: the delayed-recognizer loop (look-ahead / Flf recognizers), streaming and segment mode ---------------
+        {
+            Core::Configuration          rc = scorerConfig("ref", "diagonal-maximum", 0, 0);
+            Core::Ref<Mm::FeatureScorer> ref = mm.createFeatureScorer(rc, ms);
+            Result                       a   = driveDelayed(*mm.createScaledFeatureScorer(rc, ref), X);
+            bool                         ok  = true;
+            double                       worst = 0.0;
+            u32                          batches = 0;
+            const int                    sizes[] = {bufferSize > 0 ? bufferSize : 16, 0};
+            for (int i = 0; i < 2; ++i) {
+                Core::Configuration          gc  = scorerConfig("gpu", "gpu-diagonal-maximum", 1, sizes[i]);
+                Core::Ref<Mm::FeatureScorer> gpu = mm.createFeatureScorer(gc, ms);
+                Diff                         d   = compare(a, driveDelayed(*mm.createScaledFeatureScorer(gc, gpu), X));
+                ok      = ok && d.shape && d.nBits == 0;
+                worst   = std::max(worst, d.maxRel);
+                batches = dynamic_cast<const MmGpu::GpuFeatureScorer*>(gpu.get())->nBatches();
+            }
+            report("delayed-recognizer loop (direct kernel)", ok, "buffer sizes %d and 0: bit-identical=%d max-rel=%.3e batches(segment mode)=%u",
+                   sizes[0], int(ok), worst, batches);
+        }
+
+        // ---- 6: time-indexed cache of the segment mode (SegmentwiseAlignmentGenerator.cc:90-156) ----------------------
+        {
+            Core::Configuration          gc  = scorerConfig("gpu", "gpu-diagonal-maximum", 0, 0);
+            Core::Ref<Mm::FeatureScorer> gpu = mm.createFeatureScorer(gc, ms);
+            bool                         ok  = gpu->hasTimeIndexedCache();
+            gpu->reset();
+            for (size_t t = 0; t < X.size(); ++t)
+                gpu->addFeature(X[t]);
+            std::vector<Mm::FeatureScorer::Scorer> byFlush;
+            size_t                                 bad = 0;
+            for (size_t t = X.size(); ok && t-- > 0;) {  // random access by time, backwards
+                Mm::FeatureScorer::Scorer s = gpu->getTimeIndexedScorer(t);
+                byFlush.push_back(s);
+            }
+            std::vector<Mm::FeatureScorer::Scorer> inOrder;
+            while (ok && !gpu->bufferEmpty())
+                inOrder.push_back(gpu->flush());
+            for (size_t t = 0; ok && t < X.size(); ++t)
+                for (u32 m = 0; m < M; m += 7)
+                    bad += byFlush[X.size() - 1 - t]->score(m) != inOrder[t]->score(m);
+            ok = ok && bad == 0 && inOrder.size() == X.size();
+            report("time-indexed scorers (segment mode)", ok, "frames=%zu mismatches=%zu batches=%u", X.size(), bad,
+                   dynamic_cast<const MmGpu::GpuFeatureScorer*>(gpu.get())->nBatches());
+        }
+
+        // ---- 7: density posteriors of the sum scorer (AssigningFeatureScorer.hh:46-47; consumer
+        //         AbstractMixtureSetEstimator.cc:386-395) ---------------------------------------------------------------
+        {
+            Core::Configuration                     rc = scorerConfig("ref", "diagonal-maximum", 0, 0);
+            Core::Configuration                     gc = scorerConfig("gpu", "gpu-diagonal-sum", 0, 0);
+            Core::Ref<Mm::AssigningFeatureScorer>   ref(new Mm::GaussDiagonalSumFeatureScorer(rc, ms));
+            Core::Ref<Mm::AssigningFeatureScorer>   gpu = mm.createAssigningFeatureScorer(gc, ms);
+            double                                  worst = 0.0;
+            size_t                                  n = 0, sizeBad = 0;
+            // the reference's sum scorer caches density scores by context ADDRESS (GaussDiagonalMaximumFeatureScorer.cc:
+            // 239-246): keep every context alive so that no address is reused with stale scores
+            std::vector<Mm::AssigningFeatureScorer::AssigningScorer> keep;
+            for (size_t t = 0; t < X.size(); t += 3) {
+                Mm::AssigningFeatureScorer::AssigningScorer a = ref->getAssigningScorer(X[t]);
+                Mm::AssigningFeatureScorer::AssigningScorer b = gpu->getAssigningScorer(X[t]);
+                keep.push_back(a);
+                for (int j = 0; j < 3; ++j) {
+                    const Mm::EmissionIndex e = (t * 7 + j * 13) % M;
+                    std::vector<Mm::Weight> pa, pb;
+                    a->getDensityPosteriorProbabilities(e, pa);
+                    b->getDensityPosteriorProbabilities(e, pb);
+                    sizeBad += pa.size() != pb.size();
+                    for (size_t k = 0; k < pa.size() && k < pb.size(); ++k, ++n)
+                        worst = std::max(worst, std::fabs(pa[k] - pb[k]) / std::max(1e-6, std::fabs(pa[k])));
+                }
+            }
+            report("density posteriors (sum scorer)", sizeBad == 0 && n > 0 && worst <= 1e-4, "values=%zu max-rel=%.3e size-mismatch=%zu",
+                   n, worst, sizeBad);
+        }
+
+        // ---- 8: with-density-assignment: score AND bestDensity of buffered frames from ONE pass -----------------------
+        {
+            u32    passes[2], batches[2];
+            Result r[2];
+            for (int i = 0; i < 2; ++i) {
+                Core::Configuration          gc  = scorerConfig("gpu", "gpu-diagonal-maximum", 1, 0, i == 1);
+                Core::Ref<Mm::FeatureScorer> gpu = mm.createFeatureScorer(gc, ms);
+                gpu->reset();
+                for (size_t t = 0; t < X.size(); ++t)
+                    gpu->addFeature(X[t]);
+                while (!gpu->bufferEmpty()) {
+                    Mm::FeatureScorer::Scorer s  = gpu->flush();
+                    const AssigningContext*   as = dynamic_cast<const AssigningContext*>(s.get());
+                    for (u32 m = 0; as && m < M; m += 5) {
+                        r[i].score.push_back(as->score(m));  // score first, then the assignment, as
+                        r[i].best.push_back(as->bestDensity(m));  // AbstractMixtureSetEstimator.cc:377-393 asks
+                    }
+                }
+                const MmGpu::GpuFeatureScorer* g = dynamic_cast<const MmGpu::GpuFeatureScorer*>(gpu.get());
+                passes[i]  = g->nAssignmentPasses();
+                batches[i] = g->nBatches();
+            }
+            Diff d = compare(r[0], r[1]);
+            report("with-density-assignment", d.shape && !r[0].best.empty() && d.nBits == 0 && d.nBest == 0 && batches[1] == 1 && passes[1] == 0,
+                   "identical=%d; GPU passes: %u with, %u without", int(d.nBits == 0 && d.nBest == 0), batches[1] + passes[1],
+                   batches[0] + passes[0]);
+        }
+
+        // ---- 9: frames/s of the plugin path against the C-ABI call it wraps ------------------------------------------
+        const size_t timingFrames = args.count("timing-frames") ? atoi(args["timing-frames"].c_str()) : 0;
+        if (timingFrames > 0) {
+            Core::Configuration            gc  = scorerConfig("gpu", "gpu-diagonal-maximum", 0, 0);
+            Core::Ref<Mm::FeatureScorer>   gpu = mm.createFeatureScorer(gc, ms);
+            const MmGpu::GpuFeatureScorer* g   = dynamic_cast<const MmGpu::GpuFeatureScorer*>(gpu.get());
+            const u32                      ld  = (M + 3) / 4 * 4;
+            const int                      reps = 12;
+            float* hx = static_cast<float*>(gmm_host_alloc(timingFrames * D * sizeof(float)));
+            float* hs = static_cast<float*>(gmm_host_alloc(timingFrames * size_t(ld) * sizeof(float)));
+            for (size_t t = 0; t < timingFrames; ++t)
+                std::copy(X[t % X.size()].begin(), X[t % X.size()].end(), hx + t * D);
+            double best[2] = {1e30, 1e30};
+            double sink    = 0.0;
+            for (int r = 0; r < reps; ++r) {  // the first repetitions warm the pinned pool and the device buffers
+                double t0 = now();
+                gpu->reset();
+                for (size_t t = 0; t < timingFrames; ++t)
+                    gpu->addFeature(X[t % X.size()]);
+                while (!gpu->bufferEmpty())
+                    sink += gpu->flush()->score(0);  // the first read sends the segment to the GPU
+                double t1 = now();
+                if (gmm_score_host(g->handle(), timingFrames, hx, hs, 0, ld) != GMM_OK)
+                    sink = std::nan("");
+                double t2 = now();
+                best[0] = std::min(best[0], t1 - t0);
+                best[1] = std::min(best[1], t2 - t1);
+            }
+            gmm_host_free(hx);
+            gmm_host_free(hs);
+            const double plugin = timingFrames / best[0], direct = timingFrames / best[1];
+            printf("TIMING frames=%zu mixtures=%u plugin_frames_per_s=%.0f gmm_score_host_frames_per_s=%.0f ratio=%.3f\n",
+                   timingFrames, M, plugin, direct, plugin / direct);
+            report("plugin path timing", std::isfinite(sink) && plugin >= 0.8 * direct, "ratio=%.3f (segment mode, one read per frame)",
+                   plugin / direct);
+        }
+        return failures_ ? 1 : 0;
     }
 };
 

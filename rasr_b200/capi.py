@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(HERE, "libgmm_b200.so")
 
 MODE_MAX, MODE_SUM = 0, 1
 KERNEL_AUTO, KERNEL_DIRECT, KERNEL_TENSOR = 0, 1, 2
+QUANT_RULE_SIMD, QUANT_RULE_BATCH_INT = 0, 1  # gmm_quant_final_score_rule
 QUANT_STATIC_SCRATCH_BYTES = 4 << 20  # GMM_QUANT_STATIC_SCRATCH_BYTES
 
 # every symbol include/gmm_b200.h declares: (name, restype, argtypes)
@@ -41,6 +42,8 @@ SYMBOLS = [
     ("gmm_score_baum_welch_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     ("gmm_score_baum_welch_accumulate_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("gmm_score_device_gather", _i, [_vp, _u32, _vp, _u32, _u32, _vp, _sz, _u32, _sz, _u32]),
+    ("gmm_gather_status", _i, [_vp, _vp]),
+    ("gmm_gather_reset", _i, [_vp]),
     ("gmm_peer_alloc", _i, [_vp, _sz, _vp, _vp]),
     ("gmm_peer_open", _i, [_vp, _vp, _vp]),
     ("gmm_peer_close", _i, [_vp, _vp]),
@@ -69,6 +72,8 @@ SYMBOLS = [
     ("gmm_kernel_time", _i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     ("gmm_float_kernel", _i, [_vp]),
     ("gmm_float_split", _i, [_vp]),
+    ("gmm_float_accuracy_ok", _i, [_vp]),
+    ("gmm_quant_final_score_rule", _i, [_vp, _i]),
     ("gmm_quant_kernel", _i, [_vp]),
     ("gmm_version", C.c_char_p, []),
 ]
@@ -167,6 +172,11 @@ class Engine:
     def float_split(self) -> int:
         """3: three fp16 products (default); 2: fp16 + e5m2 corrections (GMM_TC_SPLIT=fp8); 0: not on the tensor kernel."""
         return int(self._lib.gmm_float_split(self._h))
+
+    @property
+    def float_accuracy_ok(self) -> bool:
+        """False only when the tensor kernel was forced for a model the automatic choice sends to the direct kernel."""
+        return bool(self._lib.gmm_float_accuracy_ok(self._h))
 
     @property
     def quant_kernel(self) -> int:
@@ -320,6 +330,17 @@ class Engine:
                                                       C.addressof(arr), int(ld), int(col_offset), int(flags_offset),
                                                       int(chunks)), "gmm_score_device_gather")
 
+    def gather_status(self) -> int:
+        """Number of the first mixture-sharded call on this handle whose exchange timed out (0: none).  Meaningful
+        after sync()."""
+        v = C.c_uint32(0)
+        self._check(self._lib.gmm_gather_status(self._h, C.addressof(v)), "gmm_gather_status")
+        return int(v.value)
+
+    def gather_reset(self):
+        """Collective by contract: every rank, between two host barriers."""
+        self._check(self._lib.gmm_gather_reset(self._h), "gmm_gather_reset")
+
     # -- Baum-Welch alignment ----------------------------------------------------------------------
     def emission_lists(self, automata, n_emissions):
         """-> (list_offsets [segments + 1], lists): the distinct emissions of every automaton in order of first use,
@@ -447,7 +468,8 @@ class Engine:
         return out
 
     # -- quantized engine -------------------------------------------------------------------------
-    def upload_quant(self, offsets, qmean, cov_idx, qconst, isr_scaled, scaling_squared):
+    def upload_quant(self, offsets, qmean, cov_idx, qconst, isr_scaled, scaling_squared, rule=0):
+        """rule: QUANT_RULE_SIMD (f64 expression of the SIMD scorer) or QUANT_RULE_BATCH_INT (one f32 division)."""
         offsets = _np(offsets, np.uint32)
         qmean = _np(qmean, np.uint8)
         cov_idx = _np(cov_idx, np.uint32)
@@ -461,6 +483,8 @@ class Engine:
         self._check(self._lib.gmm_upload_quant(self._h, M, G, D, Dpad, Cn, _ptr(offsets), _ptr(qmean), _ptr(cov_idx),
                                                _ptr(qconst), _ptr(isr_scaled), C.c_float(float(scaling_squared))),
                     "gmm_upload_quant")
+        if rule:
+            self._check(self._lib.gmm_quant_final_score_rule(self._h, int(rule)), "gmm_quant_final_score_rule")
         self.qM, self.qD, self.qC, self.qDpad = M, D, Cn, Dpad
 
     def quant_score_host(self, x, want_q=True, want_best=True, want_score=True, want_qx=False):

@@ -294,6 +294,8 @@ void gmm_destroy(gmm_handle* h) {
             if (h->gatherEvent[i])
                 cudaEventDestroy(h->gatherEvent[i]);
     }
+    if (h->gatherStatus)
+        cudaFreeHost(h->gatherStatus);
     if (h->laneEvent)
         cudaEventDestroy(h->laneEvent);
     if (h->copyStream)
@@ -389,6 +391,26 @@ int gmm_float_split(const gmm_handle* h) {
     if (!h || !h->floatValid || h->kernel != GMM_KERNEL_TENSOR || !h->tensor.valid)
         return 0;
     return h->tensor.fp8 ? 2 : 3;
+}
+
+int gmm_quant_final_score_rule(gmm_handle* h, int rule) {
+    if (!h || (rule != GMM_QUANT_RULE_SIMD && rule != GMM_QUANT_RULE_BATCH_INT)) {
+        if (h)
+            h->setError("gmm_quant_final_score_rule: unknown rule");
+        return GMM_ERR_ARG;
+    }
+    if (!h->quant.valid) {
+        h->setError("gmm_quant_final_score_rule: no quantized model uploaded");
+        return GMM_ERR_ARG;
+    }
+    h->quant.scoreRule = rule;
+    return GMM_OK;
+}
+
+int gmm_float_accuracy_ok(const gmm_handle* h) {
+    if (!h || !h->floatValid)
+        return 0;
+    return h->kernel != GMM_KERNEL_TENSOR || h->tensor.accuracyOk;
 }
 
 void* gmm_host_alloc(size_t bytes) {
@@ -540,9 +562,30 @@ int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_
     return gmm_gather_score(h, T, d_x, rank, world, d_blocks, ld, colOffset, flagsOffsetBytes, chunks);
 }
 
+int gmm_gather_status(gmm_handle* h, uint32_t* timedOutCall) {
+    if (!h || !timedOutCall)
+        return GMM_ERR_ARG;
+    *timedOutCall = h->gatherStatus ? *reinterpret_cast<volatile uint32_t*>(h->gatherStatus) : 0;
+    return GMM_OK;
+}
+
+int gmm_gather_reset(gmm_handle* h) {
+    if (!h)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    return gmm_gather_reset_impl(h);
+}
+
+// a block that is allocated, mapped or released may sit where another one was: forget what was read from blocks
+static void forgetGatherBlocks(gmm_handle* h) {
+    for (auto& b : h->gatherBound)
+        b = gmm_handle::GatherBinding();
+}
+
 int gmm_peer_alloc(gmm_handle* h, size_t bytes, void** d_ptr, void* ipcHandle) {
     if (!h || !d_ptr || !ipcHandle)
         return GMM_ERR_ARG;
+    forgetGatherBlocks(h);
     cudaSetDevice(h->device);
     *d_ptr = nullptr;
     GMM_CUDA_TRY(h, cudaMalloc(d_ptr, bytes ? bytes : 16));
@@ -556,6 +599,7 @@ int gmm_peer_alloc(gmm_handle* h, size_t bytes, void** d_ptr, void* ipcHandle) {
 int gmm_peer_open(gmm_handle* h, const void* ipcHandle, void** d_ptr) {
     if (!h || !d_ptr || !ipcHandle)
         return GMM_ERR_ARG;
+    forgetGatherBlocks(h);
     cudaSetDevice(h->device);
     cudaIpcMemHandle_t hd;
     memcpy(&hd, ipcHandle, sizeof(hd));
@@ -566,6 +610,7 @@ int gmm_peer_open(gmm_handle* h, const void* ipcHandle, void** d_ptr) {
 int gmm_peer_close(gmm_handle* h, void* d_ptr) {
     if (!h)
         return GMM_ERR_ARG;
+    forgetGatherBlocks(h);
     cudaSetDevice(h->device);
     GMM_CUDA_TRY(h, cudaIpcCloseMemHandle(d_ptr));
     return GMM_OK;
@@ -574,6 +619,7 @@ int gmm_peer_close(gmm_handle* h, void* d_ptr) {
 int gmm_peer_free(gmm_handle* h, void* d_ptr) {
     if (!h)
         return GMM_ERR_ARG;
+    forgetGatherBlocks(h);
     cudaSetDevice(h->device);
     GMM_CUDA_TRY(h, cudaFree(d_ptr));
     return GMM_OK;
@@ -759,6 +805,8 @@ int gmm_align_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
         h->setError("gmm_align: NULL argument");
         return GMM_ERR_ARG;
     }
+    if (int rc = gmm_gather_check(h, "gmm_align_device"))
+        return rc;
     cudaSetDevice(h->device);
     return gmm_align_launch(h, nSeg, frameOffsets, d_scores, ld, stateOffsets, arcOffsets, arcTarget, arcEmission,
                             arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore);
@@ -1048,6 +1096,8 @@ int gmm_baum_welch_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOff
         h->setError("gmm_baum_welch: NULL argument");
         return GMM_ERR_ARG;
     }
+    if (int rc = gmm_gather_check(h, "gmm_baum_welch_device"))
+        return rc;
     cudaSetDevice(h->device);
     return gmm_bw_launch(h, nSeg, frameOffsets, d_scores, ld, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
                          initialState, finalWeight, d_weights, ldW, totalScore, false, 0, nullptr, true);
@@ -1364,6 +1414,7 @@ int gmm_upload_quant(gmm_handle* h, uint32_t M, uint32_t G, uint32_t D, uint32_t
     QuantModel& qm = h->quant;
     qm.M = M, qm.G = G, qm.D = D, qm.Dpad = Dpad, qm.C = C;
     qm.scalingSquared = scaling_squared;
+    qm.scoreRule      = GMM_QUANT_RULE_SIMD;
     // qconst2 = qconst + |qmean|^2 with wrapping adds (the kernel adds |qx|^2 - 2 a.b)
     std::vector<int32_t> c2(G);
     for (size_t g = 0; g < G; ++g) {

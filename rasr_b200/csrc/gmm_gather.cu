@@ -11,17 +11,23 @@
 //   [r]      READY from rank r: r has finished reading the previous result in r's own block, which may now be
 //            overwritten (written by r into every peer's flags; the push kernel waits for it before it writes to r)
 //   [8 + r]  DONE from rank r: all of r's columns of this epoch have landed in this block
-//   [16]     CTA counter of the push kernel, [17] time-out marker
+//   [16]     CTA counter of the push kernel, [17] time-out marker, [18] epoch of the last call this rank made on
+//            the block (the epoch lives WITH the flag words: a new handle over a used block continues its sequence)
+// A time-out is not silent: the waiting kernel stores the epoch into a page-locked word the host can read
+// (gmm_gather_status), fills every column of the call's rows that is not this rank's own with +inf -- a consumer already
+// queued behind the call sees impossible scores, never stale ones -- and the next call on the handle that scores or
+// consumes scores returns GMM_ERR_TIMEOUT until gmm_gather_reset.
 #include "gmm_internal.cuh"
 
 #include <algorithm>
 #include <type_traits>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
 namespace {
 
-constexpr uint32_t kFlagReady = 0, kFlagDone = 8, kFlagCount = 16, kFlagTimeout = 17;
+constexpr uint32_t kFlagReady = 0, kFlagDone = 8, kFlagCount = 16, kFlagTimeout = 17, kFlagEpoch = 18, kFlagWords = 32;
 constexpr long long kSpinLimit = 4000000000ll;  // ~2 s of SM clocks: a missing peer ends the wait instead of hanging
 
 struct GatherPeers {
@@ -41,11 +47,14 @@ __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
 // epochs wrap: "reached" = not behind
 __device__ __forceinline__ bool reached(uint32_t have, uint32_t want) { return (int32_t)(have - want) >= 0; }
 
-__device__ bool spin_until(const uint32_t* flag, uint32_t epoch, uint32_t* timeoutMark) {
+__device__ bool spin_until(const uint32_t* flag, uint32_t epoch, uint32_t* timeoutMark, uint32_t* hostStatus,
+                           long long limit) {
     const long long t0 = clock64();
     while (!reached(ld_acquire_sys(flag), epoch)) {
-        if (clock64() - t0 > kSpinLimit) {
+        if (clock64() - t0 > limit) {
             *timeoutMark = 1;
+            *reinterpret_cast<volatile uint32_t*>(hostStatus) = epoch ? epoch : 1u;  // page-locked host word
+            __threadfence_system();
             return false;
         }
         __nanosleep(64);
@@ -98,14 +107,15 @@ __device__ __forceinline__ void push_range(const GatherPeers& peers, uint32_t ra
 template<int VEC, int kUnroll>
 __global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t row0,
                                                           uint32_t T, size_t ld, uint32_t col0, uint32_t col1,
-                                                          uint32_t epoch, int last) {
+                                                          uint32_t epoch, int last, uint32_t* hostStatus,
+                                                          long long limit) {
     uint32_t* own = peers.flags[rank];
     __shared__ int ok;
     if (threadIdx.x == 0)
         ok = 1;
     __syncthreads();
     if (threadIdx.x < world && threadIdx.x != rank)
-        if (!spin_until(own + kFlagReady + threadIdx.x, epoch, own + kFlagTimeout))
+        if (!spin_until(own + kFlagReady + threadIdx.x, epoch, own + kFlagTimeout, hostStatus, limit))
             ok = 0;
     __syncthreads();
     if (ok) {
@@ -138,14 +148,62 @@ __global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uin
     }
 }
 
-// Every peer's columns of this epoch have landed in the own block.
-__global__ void gather_wait_done(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t epoch) {
+// Every peer's columns of this epoch have landed in the own block -- or, after a time-out here or in one of the call's
+// push kernels, none of them counts: rows [0, T) keep the own columns [col0, col1) and read +inf everywhere else.
+__global__ void __launch_bounds__(256) gather_wait_done(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t epoch,
+                                                        uint32_t T, size_t ld, uint32_t col0, uint32_t col1,
+                                                        uint32_t* hostStatus, long long limit) {
     uint32_t* own = peers.flags[rank];
     if (threadIdx.x < world && threadIdx.x != rank)
-        spin_until(own + kFlagDone + threadIdx.x, epoch, own + kFlagTimeout);
+        spin_until(own + kFlagDone + threadIdx.x, epoch, own + kFlagTimeout, hostStatus, limit);
+    __syncthreads();
+    if (*reinterpret_cast<volatile uint32_t*>(own + kFlagTimeout) != 0) {
+        if (threadIdx.x == 0) {
+            *reinterpret_cast<volatile uint32_t*>(hostStatus) = epoch ? epoch : 1u;
+            __threadfence_system();
+        }
+        float*       block = peers.block[rank];
+        const float  inf   = __int_as_float(0x7f800000);
+        const size_t other = ld - (col1 - col0);
+        for (size_t i = threadIdx.x; i < (size_t)T * other; i += blockDim.x) {
+            const size_t row = i / other, c = i - row * other;
+            block[row * ld + (c < col0 ? c : c + (col1 - col0))] = inf;
+        }
+    }
+    if (threadIdx.x == 0)
+        own[kFlagEpoch] = epoch;
 }
 
 }  // namespace
+
+int gmm_gather_check(gmm_handle* h, const char* who) {
+    if (h->gatherStatus && *reinterpret_cast<volatile uint32_t*>(h->gatherStatus) != 0) {
+        char msg[256];
+        snprintf(msg, sizeof msg,
+                 "%s: the mixture-sharded exchange of call %u on this handle timed out (a peer did not show up); the "
+                 "other ranks' columns of that call read +inf.  gmm_gather_reset on every rank clears the condition",
+                 who, *h->gatherStatus);
+        h->setError(msg);
+        return GMM_ERR_TIMEOUT;
+    }
+    return GMM_OK;
+}
+
+/** Collective by contract: every rank calls it, with a host barrier before (no call in flight anywhere) and after. */
+int gmm_gather_reset_impl(gmm_handle* h) {
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    if (h->gatherStream)
+        GMM_CUDA_TRY(h, cudaStreamSynchronize(h->gatherStream));
+    for (auto& b : h->gatherBound) {
+        if (b.flags)
+            GMM_CUDA_TRY(h, cudaMemsetAsync(b.flags, 0, kFlagWords * sizeof(uint32_t), h->stream));
+        b = gmm_handle::GatherBinding();
+    }
+    GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    if (h->gatherStatus)
+        *reinterpret_cast<volatile uint32_t*>(h->gatherStatus) = 0;
+    return GMM_OK;
+}
 
 int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
                      void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks) {
@@ -160,7 +218,37 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
         for (int i = 0; i < gmm_handle::kGatherEvents; ++i)
             GMM_CUDA_TRY(h, cudaEventCreateWithFlags(&h->gatherEvent[i], cudaEventDisableTiming));
     }
-    const uint32_t epoch = ++h->gatherEpoch;
+    if (!h->gatherStatus) {
+        GMM_CUDA_TRY(h, cudaHostAlloc(reinterpret_cast<void**>(&h->gatherStatus), 64, cudaHostAllocMapped));
+        *h->gatherStatus = 0;
+        GMM_CUDA_TRY(h, cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->gatherStatusDev), h->gatherStatus, 0));
+    }
+    if (int rc = gmm_gather_check(h, "gmm_score_device_gather"))
+        return rc;
+    // The epoch continues the BLOCK's sequence: a handle that meets a block for the first time reads the block's own
+    // epoch word (0 in a fresh block) -- a new engine over used blocks, or a restarted rank, stays in step with its peers.
+    gmm_handle::GatherBinding* bound = nullptr;
+    for (auto& b : h->gatherBound)
+        if (b.flags == peers.flags[rank])
+            bound = &b;
+    if (!bound) {
+        uint32_t words[kFlagWords];
+        GMM_CUDA_TRY(h, cudaMemcpyAsync(words, peers.flags[rank], sizeof words, cudaMemcpyDeviceToHost, h->stream));
+        GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+        if (words[kFlagTimeout] != 0) {
+            h->setError("gmm_score_device_gather: the block carries the marker of a timed-out exchange; gmm_gather_reset "
+                        "on every rank (or fresh blocks) first");
+            return GMM_ERR_TIMEOUT;
+        }
+        bound        = &h->gatherBound[h->gatherBoundNext];
+        h->gatherBoundNext = (h->gatherBoundNext + 1) % gmm_handle::kGatherBindings;
+        bound->flags = peers.flags[rank];
+        bound->epoch = words[kFlagEpoch];
+    }
+    // bumped only when the call is fully enqueued (below): a call that fails half way is repeated under the same epoch
+    const uint32_t epoch = bound->epoch + 1;
+    static const long long spinLimit =
+            getenv("GMM_GATHER_TIMEOUT_MS") ? std::max(1ll, atoll(getenv("GMM_GATHER_TIMEOUT_MS"))) * 2000000ll : kSpinLimit;
     float*         own   = peers.block[rank] + colOffset;
     // The exchange is overlapped range by range.  Short calls are cut into column ranges (whole B tiles over all the
     // frames; only a regular model has its tiles at known columns), long ones into frame ranges (whole 128-row tiles
@@ -240,7 +328,7 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             const int last = c + 1 == chunks;
 #define GMM_PUSH(V, U)                                                                                             \
     gather_push_kernel<V, U><<<pushCtas, 256, 0, h->gatherStream>>>(peers, rank, world, row0, rows, ld, col0, col1, \
-                                                                    epoch, last)
+                                                                    epoch, last, h->gatherStatusDev, spinLimit)
             if (vec) {
                 if (unroll == 1)
                     GMM_PUSH(4, 1);
@@ -260,9 +348,11 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
         cudaEvent_t done = h->gatherEvent[gmm_handle::kGatherEvents - 1];
         GMM_CUDA_TRY(h, cudaEventRecord(done, h->gatherStream));
         GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->stream, done, 0));
-        gather_wait_done<<<1, 32, 0, h->stream>>>(peers, rank, world, epoch);
+        gather_wait_done<<<1, 256, 0, h->stream>>>(peers, rank, world, epoch, T, ld, colOffset, colOffset + h->M,
+                                                   h->gatherStatusDev, spinLimit);
         h->launches++;
         GMM_CUDA_TRY(h, cudaGetLastError());
     }
+    bound->epoch = epoch;
     return GMM_OK;
 }

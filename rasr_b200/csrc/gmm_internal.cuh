@@ -54,6 +54,7 @@ struct TensorModel {
     // k-step 16 x lo and 16 x hi of the same dimensions (A: lo | hi, B: hi | lo) -- and ONE kind::f8f6f4 instruction
     // per k-step adds both correction products: 6 MMA instructions per tile instead of 9
     bool      fp8       = false;
+    bool      accuracyOk = true;   // centred, whitened means within 8 sigma rms: the expanded form keeps 1e-4 relative
     bool      regular   = false;
     uint32_t  mixCols   = 0, mixPerTile = 0;
 };
@@ -62,6 +63,9 @@ struct QuantModel {
     bool      valid   = false;
     uint32_t  M = 0, G = 0, D = 0, Dpad = 0, C = 0;
     float     scalingSquared = 0.f;
+    int       scoreRule      = 0;    // GMM_QUANT_RULE_*: how q becomes the final f32 score
+    // what the kernels take: s^2, negated when the final score is the batch-int scorer's f32 division q / (2 s^2)
+    double finalScoreArg() const { return scoreRule ? -(double)scalingSquared : (double)scalingSquared; }
     uint8_t*  qmean   = nullptr;  // [G x Dpad]
     uint32_t* covIdx  = nullptr;  // [G]
     int32_t*  qconst2 = nullptr;  // [G] qconst + sum_d qmean^2 (wrapping)
@@ -167,7 +171,15 @@ struct gmm_handle {
     static constexpr int kGatherEvents = 9;  // mixture-sharded scoring (gmm_gather.cu): push stream, one event per
     cudaStream_t gatherStream        = nullptr;  // column range + one for the join, epoch of the flag words
     cudaEvent_t  gatherEvent[kGatherEvents] = {};
-    uint32_t     gatherEpoch         = 0;
+    struct GatherBinding {               // a gathered block this handle has called on: its flag words and the epoch of
+        uint32_t* flags = nullptr;       // the last call that was fully enqueued (read from the block's own epoch word
+        uint32_t  epoch = 0;             // when the handle first meets the block)
+    };
+    static constexpr int kGatherBindings = 4;
+    GatherBinding gatherBound[kGatherBindings];
+    int           gatherBoundNext  = 0;
+    uint32_t*     gatherStatus     = nullptr;  // page-locked, device-mapped: epoch of the first exchange that timed out
+    uint32_t*     gatherStatusDev  = nullptr;
     // gmm_score_host: device-to-host copies of finished chunks run on a stream of their own while the next chunk is
     // scored; gmm_score_async / gmm_wait: two lanes in turn, one event and token per lane
     static constexpr int kCopyEvents = 8;
@@ -269,6 +281,8 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
                 const float* w2, const float* logNorm, bool force);
 int gmm_tc_score_tiles(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, size_t ld, uint32_t tile0,
                        uint32_t tile1, bool prep, uint32_t prepFrames = 0, uint32_t frameTile0 = 0);
+int gmm_gather_check(gmm_handle* h, const char* who);  // GMM_ERR_TIMEOUT after a timed-out exchange, until reset
+int gmm_gather_reset_impl(gmm_handle* h);
 int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
                      void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks);
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);

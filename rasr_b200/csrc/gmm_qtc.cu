@@ -67,6 +67,7 @@ struct QKParams {
     uint32_t        qBase;       // cmax (wrapping u32): q = qBase + |qx|^2 - max_k acc_k
     unsigned long long* dbg;     // GMM_QTC_DEBUG: per-CTA cycle counters (16 words per CTA)
     uint32_t        vecStores;   // 0: always the scalar staged store path (GMM_QTC_STORES=scalar)
+    uint32_t        keyMul;      // 256, as a run-time value: key = acc * keyMul + term compiles to IMAD (FMA pipe)
 };
 
 __device__ __forceinline__ uint8_t quantize_u8(float v) {
@@ -149,9 +150,17 @@ struct QEpiState {
 // densities (all its columns pads: key 0) yields the reference's INT_MAX / no density.
 // resQ != nullptr (SP > 0 only): the closed mixtures' q (and arg-min, resB) stay in registers, index seg / SP, for the
 // vector store path instead of being staged one by one.
+// The epilogue is bound by instruction issue on the two half-rate integer pipes: shifts, LEA and the three-input maxima
+// go to the ALU pipe, IMAD to the FMA pipe.  Three of four keys are therefore built by a multiply-add whose factor 256
+// arrives as a run-time value (ptxas turns a literal 256 back into a shift): 0.5 + 0.25 ALU and 0.75 FMA instructions
+// per column instead of 1.5 ALU.
+__device__ __forceinline__ uint32_t qkey(uint32_t v, uint32_t term, uint32_t mul, bool viaMad) {
+    return viaMad ? v * mul + term : (v << 8) + term;
+}
+
 template<int SP, bool WB>
 __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t qbx,
-                                           uint32_t offB, QEpiState& st, uint32_t* resQ = nullptr,
+                                           uint32_t offB, QEpiState& st, uint32_t mul, uint32_t* resQ = nullptr,
                                            uint32_t* resB = nullptr) {
     uint32_t kc[32];
     if (SP == 0) {  // the chunk's 32 per-column terms first (eight 128-bit loads in flight together)
@@ -170,22 +179,19 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
             if (SP > 0 && !WB)
                 key[j] = v[s * 8 + j];
             else if (SP > 0)
-                key[j] = (v[s * 8 + j] << 8) + (uint32_t)(255 - ((seg % SP) * 8 + j));
+                key[j] = qkey(v[s * 8 + j], (uint32_t)(255 - ((seg % SP) * 8 + j)), mul, (j & 3) != 3);
             else
-                key[j] = (v[s * 8 + j] << 8) + kc[s * 8 + j];
+                key[j] = qkey(v[s * 8 + j], kc[s * 8 + j], mul, (j & 3) != 3);
         }
-        const uint32_t m6 = __vimax3_u32(__vimax3_u32(key[0], key[1], key[2]), __vimax3_u32(key[3], key[4], key[5]),
-                                         max(key[6], key[7]));
-        bool     close;
-        uint32_t m;
-        if (SP > 0) {
-            m     = (seg % SP) == 0 ? m6 : max(m6, st.run);
+        // eight keys and the running maximum of the open mixture: four three-input maxima
+        const bool     first = SP > 0 && (seg % SP) == 0;
+        const uint32_t m     = __vimax3_u32(__vimax3_u32(key[0], key[1], key[2]), __vimax3_u32(key[3], key[4], key[5]),
+                                            first ? max(key[6], key[7]) : __vimax3_u32(key[6], key[7], st.run));
+        bool close;
+        if (SP > 0)
             close = (seg % SP) == SP - 1;
-        }
-        else {
-            m     = max(m6, st.run);
+        else
             close = (segEnd >> seg) & 1u;
-        }
         if (close) {  // uniform across the warp
             if (SP > 0 && resQ) {
                 resQ[seg / SP] = WB ? qbx - (m >> 8) : qbx - m;
@@ -201,9 +207,10 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
                     sts_u32(st.sp + offB, none ? 0xFFFFFFFFu : 255u - (m & 255u));
             }
             st.sp += 4;
-            m = kNoKey;
+            st.run = kNoKey;
         }
-        st.run = m;
+        else
+            st.run = m;
     }
 }
 
@@ -213,8 +220,12 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
 // OUT: which arrays the caller asked for, fixed at compile time so that the store loop is branch-free -- bit 0 q, bit 1
 // arg-min, bit 2 final f32 score by ONE f32 division (exact, see qtc_launch); OUT = 0 keeps all three as run-time tests
 // and the score as the reference's f64 expression (any other combination, or |q| beyond 2^24).
-template<int NE, int OUT>
-__global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(const QKParams p) {
+// NG = 2 (NE = 8 only): TWO epilogue groups of eight warps; group g drains the accumulator of the tiles with t % 2 == g,
+// so one group's reduction (integer pipes) runs while the other group's row pieces leave (load/store unit, memory
+// latency) -- with one group the two phases alternate and each pipe idles half the time.
+template<int NE, int NG, int OUT>
+__global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kernel(const QKParams p) {
+    static_assert(NG == 1 || (NG == 2 && NE == 8 && kRing % 2 == 0), "two groups: eight warps each, ring index parity = tile parity");
     constexpr bool WQ = OUT == 0 || (OUT & 1), WB = OUT == 0 || (OUT & 2), WS = OUT == 0 || (OUT & 4);
     extern __shared__ uint8_t smemRaw[];
     uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
@@ -233,7 +244,7 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
     constexpr int  kGroups = NE == 16 ? 4 : 8, kBufs = NE == 16 ? 2 : 1, GW = NE == 16 ? 128 : 32;
     const uint32_t stageWarp = 32 * p.stagePitch;  // words per block
     uint64_t*      bars      = reinterpret_cast<uint64_t*>(
-            (reinterpret_cast<uintptr_t>(sStage + 2 * kGroups * kBufs * stageWarp) + 15) & ~(uintptr_t)15);
+            (reinterpret_cast<uintptr_t>(sStage + 2 * kGroups * kBufs * NG * stageWarp) + 15) & ~(uintptr_t)15);
     uint64_t* ready    = bars;              // [kRing] tile t may be issued (A landed, accumulator drained)
     uint64_t* done     = bars + kRing;      // [kRing] the MMAs of tile t have retired
     uint64_t* fullB    = bars + 2 * kRing;  // [2]
@@ -247,7 +258,7 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(smem_u32(&fullB[i]), 1);
-            mbar_init(smem_u32(&emptyB[i]), 1 + NE);
+            mbar_init(smem_u32(&emptyB[i]), 1 + NE * NG);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -347,10 +358,10 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
     }
     else {
         // ===== epilogue: TMEM -> registers -> packed-key min per mixture -> staged -> global =====
-        const int      e = warp - kEpiWarp0, qd = warp & 3, part = e >> 2;
+        const int      grp = (warp - kEpiWarp0) / NE, e = (warp - kEpiWarp0) % NE, qd = warp & 3, part = e >> 2;
         const uint32_t gi     = NE == 16 ? (uint32_t)qd : (uint32_t)e;       // store group
         const uint32_t gl     = NE == 16 ? (uint32_t)(part * 32 + lane) : (uint32_t)lane;  // thread within the group
-        const uint32_t stGrp  = smem_u32(sStage) + gi * kBufs * stageWarp * 4;
+        const uint32_t stGrp  = smem_u32(sStage) + ((uint32_t)grp * 2 * kGroups + gi) * kBufs * stageWarp * 4;
         const uint32_t offB   = kGroups * kBufs * stageWarp * 4;
         // the three outputs share one indexing: address everything relative to a base array that is present
         char* const     gBase = reinterpret_cast<char*>(p.q ? (void*)p.q : p.best ? (void*)p.best : (void*)p.score);
@@ -358,9 +369,11 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
         const ptrdiff_t scoreDelta = p.score ? reinterpret_cast<char*>(p.score) - gBase : 0;
         uint32_t       itemCount = 0, t = 0;
         long long      eW = 0, eL = 0, eB = 0, eS = 0, ec0 = 0;
-        if (lane == 0) {
-            mbar_arrive(smem_u32(&ready[0]));
-            mbar_arrive(smem_u32(&ready[1]));
+        if (lane == 0) {  // both accumulators start drained (two groups: each speaks for its own)
+            if (NG == 1 || grp == 0)
+                mbar_arrive(smem_u32(&ready[0]));
+            if (NG == 1 || grp == 1)
+                mbar_arrive(smem_u32(&ready[1]));
         }
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
             const uint32_t chunk = item % p.split;
@@ -369,6 +382,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                 continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            // this group's first tile of the item (tiles alternate between the groups across items as well)
+            const uint32_t  fG = NG == 2 ? f0 + ((t ^ (uint32_t)grp) & 1u) : f0;
             const uint8_t*  tile = sB + (size_t)b * bBytes + (size_t)p.atomsB * kTileN * SWZ;
             const uint32_t  kcAddr = smem_u32(tile) + (uint32_t)part * PW * 4;  // Kc of this warp's columns
             const uint32_t* meta = reinterpret_cast<const uint32_t*>(tile + kTileN * 4);  // TileMeta words
@@ -394,13 +409,14 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
             const uint32_t  ssOff = (lr0 * p.stagePitch + lj0) * 4;
             const uint32_t  stOff = ((uint32_t)lane * p.stagePitch + colOff) * 4;
             const uint32_t  passes = (32 * nMix + GW - 1) / GW;
-            size_t          gTile = ((size_t)(f0 * kTileM + qd * 32 + lr0) * p.ld + mixBase + lj0) * 4;
-            const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
-            const uint32_t* xxp = p.rowXX + (size_t)f0 * kTileM + qd * 32 + lane;
+            size_t          gTile = ((size_t)(fG * kTileM + qd * 32 + lr0) * p.ld + mixBase + lj0) * 4;
+            const size_t    gTileStep = (size_t)NG * kTileM * p.ld * 4;
+            const uint32_t* xxp = p.rowXX + (size_t)fG * kTileM + qd * 32 + lane;
             // VEC (uniform tile, 16-byte aligned row pieces): a lane keeps its R = SEGS / SP results in registers, stages
             // them with 128-bit stores into rows of W + 4 words (W = the group's results per row), and the group writes
             // the block out with one 128-bit load and store per thread and array and pass -- a handful of instructions
             // where the scalar path below spends a hundred (the epilogue is bound by the half-rate integer pipes)
+            const uint32_t tItem = t;
             auto tiles = [&](auto spTag, auto vecTag) {
                 constexpr int  SP  = decltype(spTag)::value;
                 constexpr bool VEC = decltype(vecTag)::value && SP > 0 && (SEGS / (SP > 0 ? SP : 1)) % 4 == 0;
@@ -413,15 +429,16 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                 uint32_t* const rb = VEC ? resB : nullptr;
                 // vector path: this thread's piece and first row, its global offset (bytes) and the staging offsets
                 const uint32_t vqi = gl % WQ4, vr0 = gl / WQ4;
-                size_t         gVec = ((size_t)(f0 * kTileM + qd * 32 + vr0) * p.ld + mixBase + vqi * 4) * 4;
+                size_t         gVec = ((size_t)(fG * kTileM + qd * 32 + vr0) * p.ld + mixBase + vqi * 4) * 4;
                 const uint32_t vRead  = (vr0 * PV + vqi * 4) * 4;
                 const uint32_t vWrite = ((uint32_t)lane * PV + (NE == 16 ? (uint32_t)part * R : 0u)) * 4;
-                uint32_t xxNext = *xxp;  // |qx|^2 of the next tile's row, fetched one tile ahead
-                for (uint32_t f = f0; f < f1; ++f, ++t) {
+                uint32_t xxNext = fG < f1 ? *xxp : 0u;  // |qx|^2 of the next tile's row, fetched one tile ahead
+                for (uint32_t f = fG; f < f1; f += NG) {
+                    const uint32_t t      = tItem + (f - f0);  // tile counter of the CTA (shadows the item-level one)
                     const uint32_t acc    = t & 1;
                     const uint32_t xxBase = xxNext + p.qBase;
-                    xxp += kTileM;
-                    if (f + 1 < f1)
+                    xxp += NG * kTileM;
+                    if (f + NG < f1)
                         xxNext = *xxp;
                     if (p.dbg) ec0 = clock64();
                     mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
@@ -443,40 +460,56 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, rq, rb);
-                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                     }
                     else if (NE == 16) {
                         // 96 registers per thread: one 32-column chunk (+ its 32 table entries) live at a time
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld32(taddr + 32, va);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(va, 1, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(va, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                    }
+                    else if (NG == 2) {
+                        // 96 registers per thread (18 warps): one 32-column chunk live at a time; the other warps of the
+                        // scheduler (its second group among them) cover the TMEM load latency
+#pragma unroll
+                        for (int ch = 0; ch < 4; ++ch) {
+                            tmem_ld32(taddr + 32 * ch, va);
+                            tmem_ld_wait();
+                            if (ch == 3) {
+                                tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0)
+                                    mbar_arrive(drained);
+                            }
+                            qepi_chunk<SP, WB>(va, ch, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        }
                     }
                     else {
                         uint32_t vb[32];
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 32, vb);
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 64, va);
-                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 96, vb);
-                        qepi_chunk<SP, WB>(va, 2, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(va, 2, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(vb, 3, kcAddr, segEnd, xxBase, offB, st, rq, rb);
+                        qepi_chunk<SP, WB>(vb, 3, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                     }
                     if (VEC) {
 #pragma unroll
@@ -535,7 +568,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                             if (OUT == 0) {
                                 if (p.score)  // f32( 0.5 * q / scalingSquared ) in double, SimdFeatureScorer.cc:135-145
                                     *reinterpret_cast<float*>(g + scoreDelta) =
-                                            (float)(0.5 * (double)(int32_t)qv / p.scalingSquared);
+                                            p.scalingSquared < 0.0 ? __fdiv_rn((float)(int32_t)qv, p.twoScalingSquared)
+                                                                   : (float)(0.5 * (double)(int32_t)qv / p.scalingSquared);
                             }
                             else if (WS)  // the same bits from one f32 division (|q| < 2^24, see qtc_launch)
                                 *reinterpret_cast<float*>(g + scoreDelta) = __fdiv_rn((float)(int32_t)qv, p.twoScalingSquared);
@@ -583,10 +617,11 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
                 case 8: run(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
                 default: run(std::integral_constant<int, 0>{}); break;
             }
+            t += f1 - f0;
             if (lane == 0)
                 mbar_arrive(smem_u32(&emptyB[b]));
         }
-        if (p.dbg && e == 0 && lane == 0) {
+        if (p.dbg && e == 0 && grp == 0 && lane == 0) {
             unsigned long long* d = p.dbg + blockIdx.x * 16;
             d[8] = eW, d[9] = eL, d[10] = eB, d[11] = eS;
         }
@@ -606,8 +641,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE), 1) qtc_score_kernel(con
 static uint32_t qSmemNeed(uint32_t bTileBytes, uint32_t aTileBytes, uint32_t buffersB, uint32_t stagesA,
                           uint32_t pitch, uint32_t epiWarps) {
     const uint32_t bBytes = (bTileBytes + 1023u) & ~1023u;
-    (void)epiWarps;  // 8 staging blocks per plane either way: 8 warps x 1, or 4 lane quarters x 2
-    return 1024 + buffersB * bBytes + stagesA * aTileBytes + 2 * 8 * 32 * pitch * 4 + 512;
+    // 8 staging blocks per plane either way: 8 warps x 1, or 4 lane quarters x 2; eight-warp epilogues come in two groups
+    return 1024 + buffersB * bBytes + stagesA * aTileBytes + (epiWarps == 8 ? 2 : 1) * 2 * 8 * 32 * pitch * 4 + 512;
 }
 
 // Packs the quantized model for the tensor kernel; leaves h->qtensor.valid false when the model does not meet the
@@ -655,7 +690,9 @@ int gmm_qtc_pack(gmm_handle* h, const uint32_t* offsets, const uint8_t* qmean, c
     const char* envW = getenv("GMM_QTC_EPI_WARPS");
     // 8 epilogue warps (128-column parts) by default: the 16-warp variant is faster on small batches (48 vs 41 M
     // frames/s at 8000 frames, 4501x16) but its 16-byte output pieces collapse on large ones (20 vs 38 M at 64000)
-    tm.partW         = (maxN <= 64 && !(envW && atoi(envW) == 8)) ? 64 : 128;
+    // default: 128-column parts = eight-warp epilogue groups, two of them on alternate tiles (GMM_QTC_GROUPS=1: one);
+    // GMM_QTC_EPI_WARPS=16 at upload: 64-column parts, one group of sixteen warps (needs mixtures of <= 64 columns)
+    tm.partW         = (maxN <= 64 && envW && atoi(envW) == 16) ? 64 : 128;
     const uint32_t        partW = tm.partW, partsPerTile = kTileN / partW;
     std::vector<Col>      cols;
     std::vector<TileMeta> metas;
@@ -836,7 +873,7 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     p.best           = d_best;
     p.score          = d_score;
     p.ld             = ld;
-    p.scalingSquared = (double)qm.scalingSquared;
+    p.scalingSquared = qm.finalScoreArg();
     p.T              = T;
     p.nTiles         = tm.nTiles;
     p.frameTiles     = FT;
@@ -893,19 +930,30 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     p.twoScalingSquared = 2.0f * qm.scalingSquared;
     const bool generic = getenv("GMM_QTC_GENERIC") != nullptr;  // tests: force the run-time variant
     if (generic || (out != 3 && out != 4 && out != 6 && out != 7) ||
-        ((out & 4) && (tm.qAbsMax >= (1u << 24) || !std::isfinite(p.twoScalingSquared) || !(qm.scalingSquared > 0.f))))
+        ((out & 4) && !qm.scoreRule &&
+         (tm.qAbsMax >= (1u << 24) || !std::isfinite(p.twoScalingSquared) || !(qm.scalingSquared > 0.f))))
         out = 0;
     void (*kernel)(const QKParams) = nullptr;
+    uint32_t groups = 1;
+    {
+        const char* e = getenv("GMM_QTC_GROUPS");
+        if (epiWarps == 8 && !(e && atoi(e) == 1))
+            groups = 2;
+    }
+    p.keyMul = 256;
     if (epiWarps == 16)
-        kernel = out == 3 ? qtc_score_kernel<16, 3> : out == 4 ? qtc_score_kernel<16, 4> : out == 6 ? qtc_score_kernel<16, 6>
-               : out == 7 ? qtc_score_kernel<16, 7> : qtc_score_kernel<16, 0>;
+        kernel = out == 3 ? qtc_score_kernel<16, 1, 3> : out == 4 ? qtc_score_kernel<16, 1, 4> : out == 6 ? qtc_score_kernel<16, 1, 6>
+               : out == 7 ? qtc_score_kernel<16, 1, 7> : qtc_score_kernel<16, 1, 0>;
+    else if (groups == 2)
+        kernel = out == 3 ? qtc_score_kernel<8, 2, 3> : out == 4 ? qtc_score_kernel<8, 2, 4> : out == 6 ? qtc_score_kernel<8, 2, 6>
+               : out == 7 ? qtc_score_kernel<8, 2, 7> : qtc_score_kernel<8, 2, 0>;
     else
-        kernel = out == 3 ? qtc_score_kernel<8, 3> : out == 4 ? qtc_score_kernel<8, 4> : out == 6 ? qtc_score_kernel<8, 6>
-               : out == 7 ? qtc_score_kernel<8, 7> : qtc_score_kernel<8, 0>;
+        kernel = out == 3 ? qtc_score_kernel<8, 1, 3> : out == 4 ? qtc_score_kernel<8, 1, 4> : out == 6 ? qtc_score_kernel<8, 1, 6>
+               : out == 7 ? qtc_score_kernel<8, 1, 7> : qtc_score_kernel<8, 1, 0>;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     GMM_CUDA_TRY(h, e);
     h->timeBegin();
-    kernel<<<grid, 32 * (kEpiWarp0 + epiWarps), smemBytes, h->stream>>>(p);
+    kernel<<<grid, 32 * (kEpiWarp0 + epiWarps * groups), smemBytes, h->stream>>>(p);
     h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
@@ -920,10 +968,10 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
         }
         tiles = std::max(1.0, tiles);
         fprintf(stderr,
-                "[gmm_qtc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u out %d | cycles per tile: MMA thread "
+                "[gmm_qtc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u x %u out %d | cycles per tile: MMA thread "
                 "total %.0f = wait-ready %.0f + issue %.0f | epilogue warp 0: wait-for-MMA %.0f + loads and reduction %.0f + "
                 "group barrier %.0f + stores %.0f\n",
-                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, out, tot / tiles, mW / tiles, mI / tiles,
+                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, groups, out, tot / tiles, mW / tiles, mI / tiles,
                 eW / tiles, eL / tiles, eB / tiles, eS / tiles);
     }
     return GMM_OK;

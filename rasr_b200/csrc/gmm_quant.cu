@@ -150,7 +150,9 @@ __global__ void __launch_bounds__(256) quant_score_kernel(const uint8_t* __restr
                 if (best)
                     best[o] = bestDns[r];
                 if (score)
-                    score[o] = (float)(0.5 * (double)minScore[r] / scalingSquared);
+                    score[o] = scalingSquared < 0.0  // batch-int rule (gmm_quant_final_score_rule): one f32 division
+                                       ? __fdiv_rn((float)minScore[r], (float)(-2.0 * scalingSquared))
+                                       : (float)(0.5 * (double)minScore[r] / scalingSquared);
             }
         }
     }
@@ -172,11 +174,11 @@ int launchScore(gmm_handle* h, uint32_t T, const uint8_t* d_qx, int32_t* d_q, ui
     if (qm.C == 1)
         quant_score_kernel<DW, FR, true><<<grid, block, 0, h->stream>>>(
                 d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
-                (double)qm.scalingSquared, d_q, d_best, d_score, ld);
+                qm.finalScoreArg(), d_q, d_best, d_score, ld);
     else
         quant_score_kernel<DW, FR, false><<<grid, block, 0, h->stream>>>(
                 d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
-                (double)qm.scalingSquared, d_q, d_best, d_score, ld);
+                qm.finalScoreArg(), d_q, d_best, d_score, ld);
     h->timeEnd();
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
@@ -298,11 +300,11 @@ int launchScoreStatic(gmm_handle* h, uint32_t T, const uint8_t* d_qx, int32_t* d
     if (qm.C == 1)
         quant_score_kernel<DW, FR, true><<<grid, block, 0, h->stream>>>(
                 d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
-                (double)qm.scalingSquared, d_q, d_best, d_score, ld);
+                qm.finalScoreArg(), d_q, d_best, d_score, ld);
     else
         quant_score_kernel<DW, FR, false><<<grid, block, 0, h->stream>>>(
                 d_qx, (int)T, (int)qm.M, (int)qm.C, qm.qmean, qm.covIdx, qm.qconst2, qm.offsets, mixPerBlock,
-                (double)qm.scalingSquared, d_q, d_best, d_score, ld);
+                qm.finalScoreArg(), d_q, d_best, d_score, ld);
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
     return GMM_OK;

@@ -1058,7 +1058,8 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     // The expanded form |a|^2 + |b|^2 - 2 a.b cancels in f32: its absolute error grows like 2^-22 * |b|^2 while a
     // frame next to such a mean has a score of order D/2.  Models whose centred, whitened means are further out
     // than 8 sigma (rms per dimension) keep the 1e-4 relative bar only in the direct kernel.
-    if (!force && kappa > 64.0 * D)
+    tm.accuracyOk = !(kappa > 64.0 * D);  // reported even when the tensor kernel is forced (gmm_float_accuracy_ok)
+    if (!force && !tm.accuracyOk)
         return GMM_OK;
     if (!cRange) {
         if (force) {

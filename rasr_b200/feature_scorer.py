@@ -72,12 +72,15 @@ class GpuFeatureScorer:
     ``diagonal-maximum``       float, maximum approximation         (GaussDiagonalMaximumFeatureScorer)
     ``diagonal-sum``           float, full sum / log-sum-exp        (GaussDiagonalSumFeatureScorer)
     ``SIMD-diagonal-maximum``  u8 quantized, bit-exact integer path (SimdGaussDiagonalMaximumFeatureScorer)
+    ``batch-diagonal-maximum-int``  the same u8 kernel with the constants and the final scale of
+                               BatchIntFeatureScorer (BatchFeatureScorer.cc:319-376,468); pooled covariance only
 
     ``buffer_size`` mirrors the reference's ``buffer-size`` parameter; 0 selects segment mode (the buffer
     never reports filled, everything is scored in one launch when the first score is requested).
     """
 
-    SCORER_TYPES = ("diagonal-maximum", "diagonal-sum", "SIMD-diagonal-maximum")
+    SCORER_TYPES = ("diagonal-maximum", "diagonal-sum", "SIMD-diagonal-maximum", "batch-diagonal-maximum-int")
+    QUANTIZED_TYPES = ("SIMD-diagonal-maximum", "batch-diagonal-maximum-int")
 
     def __init__(self, mixture_set: MixtureSetData, scorer_type: str = "diagonal-maximum", *, buffer_size: int = 0,
                  device: int = 0, assigning: bool = True, kernel: int = capi.KERNEL_AUTO,
@@ -93,10 +96,17 @@ class GpuFeatureScorer:
         self._buffer_size = int(buffer_size)
         self._assigning = assigning
         self._engine = capi.Engine(device)
-        if scorer_type == "SIMD-diagonal-maximum":
-            t = quant_tables if quant_tables is not None else tables.quant_tables(mixture_set)
+        if scorer_type in self.QUANTIZED_TYPES:
+            if quant_tables is not None:
+                t = quant_tables
+            elif scorer_type == "SIMD-diagonal-maximum":
+                t = tables.quant_tables(mixture_set)
+            else:
+                t = tables.batchint_tables(mixture_set)
             self._engine.upload_quant(t["offsets"], t["qmean"], t["cov_idx"], t["qconst"], t["isr_scaled"],
-                                      t["scaling_squared"])
+                                      t["scaling_squared"],
+                                      rule=capi.QUANT_RULE_BATCH_INT if scorer_type == "batch-diagonal-maximum-int"
+                                      else capi.QUANT_RULE_SIMD)
             self.scaling_squared = np.float32(t["scaling_squared"])
         else:
             t = float_tables if float_tables is not None else tables.float_tables(
@@ -189,7 +199,7 @@ class GpuFeatureScorer:
 
     def scoreBatch(self, x: np.ndarray):
         """Eager scoring of a [T, D] block: (scores [T, M] f32, best [T, M] u32 or None)."""
-        if self._type == "SIMD-diagonal-maximum":
+        if self._type in self.QUANTIZED_TYPES:
             r = self._engine.quant_score_host(x, want_q=False, want_best=self._assigning, want_score=True)
             return r["score"], r["best"]
         return self._engine.score_host(x, want_best=self._assigning)

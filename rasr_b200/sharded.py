@@ -163,7 +163,14 @@ class PushMixtureShardedScorer:
         self.engine = capi.Engine(device)
         self.engine.upload_float(sub["offsets"], sub["mean"], sub["isr"], sub["cov_idx"], sub["w2"], sub["log_norm"],
                                  mode=mode, kernel=capi.KERNEL_TENSOR)
+        if not self.engine.float_accuracy_ok:
+            # the automatic kernel choice would have sent this shard to the direct kernel (means further out than
+            # 8 sigma rms: the expanded form loses the 1e-4 relative bar); there is no direct variant of the push
+            self.engine.close()
+            raise ValueError("this shard's means are too far out for the tensor kernel's accuracy bar; use "
+                             "MixtureShardedScorer (direct kernel + all-gather) for this model")
         self.max_frames, self.chunks = int(max_frames), int(chunks)
+        self._consumer = None
         self.flags_offset = (self.max_frames * self.ld * 4 + 127) // 128 * 128
         self._own, handle = self.engine.peer_alloc(self.flags_offset + self.FLAG_WORDS * 4)
         handles = [None] * world
@@ -176,9 +183,19 @@ class PushMixtureShardedScorer:
         torch.cuda.synchronize()
         dist.barrier()
 
+    def bind_stream(self, stream):
+        """Run the engine on the torch stream whose work consumes the returned block (gmm_set_stream).  The READY
+        signal of the next score() is then ordered behind every reader of the previous result, and readers queued
+        after score() behind the wait for the peers' columns.  Without a bound stream the engine works on a stream of
+        its own and the caller orders its consumers itself: engine.sync() after score(), and the consumers'
+        stream synchronised before the next score()."""
+        self.engine.set_stream(stream.cuda_stream)
+        self._consumer = stream
+
     def score(self, d_x):
         """d_x: CUDA tensor [T, D] (identical on every rank) -> frame-major [T][N*Mp] view of this rank's block,
-        complete for work queued on the engine's stream after the call."""
+        complete for work queued on the engine's stream after the call (see bind_stream).  The view is
+        peer-writable memory: the next score() lets the peers overwrite it."""
         T = d_x.shape[0]
         if T > self.max_frames:
             raise ValueError("more frames than the gathered block holds")
@@ -187,8 +204,16 @@ class PushMixtureShardedScorer:
         return self.block[:T]
 
     def timed_out(self) -> bool:
-        """A peer did not show up within the device-side limit (call after a sync)."""
-        return bool(self.flags[17].item() != 0)
+        """A peer did not show up within the device-side limit (call after a sync).  The other ranks' columns of
+        that call read +inf, and scoring calls raise until reset()."""
+        return self.engine.gather_status() != 0
+
+    def reset(self):
+        """After a time-out, on every rank: clears the flag words and the condition."""
+        self.engine.sync()
+        self.dist.barrier()
+        self.engine.gather_reset()
+        self.dist.barrier()
 
     def close(self):
         self.engine.sync()

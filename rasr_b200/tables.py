@@ -116,3 +116,38 @@ def quant_tables(ms: MixtureSetData):
         qconst = _cvtt_s32((w + log_norm_s[cov_idx]).astype(F32))
     return dict(offsets=ms.mix_offsets.copy(), qmean=qmean, cov_idx=cov_idx, qconst=qconst, isr_scaled=isr_s,
                 scaling_squared=s2)
+
+
+def batchint_tables(ms: MixtureSetData):
+    """Tables of BatchIntFeatureScorer::init (`batch-diagonal-maximum-int`, src/Mm/BatchFeatureScorer.cc:319-376):
+    the u8 grid of the SIMD scorer with its own constants, c = (s32)(L * scale^2 - 2 scale^2 * logWeight) evaluated in
+    double, and the final score q / (2 scale^2) (:468).  Pooled covariance only, like the reference (:340-342).
+    Same dict as quant_tables: the device kernel is the same; scaling_squared is scale^2 (the kernel divides by
+    2 * scaling_squared)."""
+    ms.check_scorable()
+    if ms.n_cov != 1:
+        raise ValueError("feature scorer supports only globally pooled variance")
+    mean, cov_idx = flatten(ms)
+    D, Dpad = ms.D, simd_padded_dimension(ms.D)
+    with np.errstate(over="ignore", invalid="ignore"):
+        isr = (F32(1) / np.sqrt(ms.variances.astype(F32))).astype(F32)
+        log_norm = _log_norm(ms.variances)
+        dm = (ms.means[ms.dens_mean] * isr[0]).astype(F32)
+        if dm.size:
+            mn, mx = F32(dm.min()), F32(dm.max())
+        else:
+            mn, mx = F32(np.finfo(F32).max), F32(-np.finfo(F32).max)
+        interval = F32(2) * max(F32(abs(mn)), F32(abs(mx)))
+        scale = F32(np.float64(F32(255)) / (1.25 * np.float64(interval)))
+        s2 = F32(scale * scale)
+        scale2 = F32(2.0 * np.float64(s2))
+        isr_s = (isr * scale).astype(F32)
+        log_norm_factor = F32(log_norm[0] * s2)
+        qmean = np.zeros((ms.G, Dpad), np.uint8)
+        qmean[:, :D] = quantize_u8((mean * isr_s[0]).astype(F32))
+        c = np.float64(log_norm_factor) - np.float64(scale2) * ms.mix_logw.astype(np.float64)
+        ok = np.isfinite(c) & (np.abs(c) < 2147483648.0)
+        qconst = np.full(c.shape, INT_INDEFINITE, np.int32)  # cvttsd2si out of range
+        qconst[ok] = np.trunc(c[ok]).astype(np.int32)
+    return dict(offsets=ms.mix_offsets.copy(), qmean=qmean, cov_idx=cov_idx, qconst=qconst, isr_scaled=isr_s,
+                scaling_squared=F32(scale2 * F32(0.5)), rule=1)  # capi.QUANT_RULE_BATCH_INT

@@ -20,7 +20,11 @@ def golden_names():
     """Model fixtures (scorer goldens); lda_*.npz (front end) and est_*.npz (estimators, model files) are fixtures
     with their own tests."""
     names = (os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return sorted(n for n in names if not n.startswith(("lda_", "est_")))
+    return sorted(n for n in names if not n.startswith(("lda_", "est_", "batchint_")))
+
+
+def batchint_golden_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "batchint_*.npz")))
 
 
 def estimator_golden_names():
@@ -52,6 +56,14 @@ def oracle_float_tables(ms, **kw):
     isr, logn, w2 = O.float_tables(ms, **kw)
     mean, cov_idx = tables.flatten(ms)
     return dict(offsets=ms.mix_offsets, mean=mean, cov_idx=cov_idx, isr=isr, log_norm=logn, w2=w2)
+
+
+def oracle_batchint_tables(ms, exact_rsqrt=False):
+    """Tables of the reference's batch-diagonal-maximum-int scorer (oracle restatement), in upload_quant's layout."""
+    from oracle import oracle as O
+    t = O.batchint_prepare(ms, exact_rsqrt=exact_rsqrt)
+    return dict(offsets=ms.mix_offsets, qmean=t["qmean"], cov_idx=t["qcov"], qconst=t["qconst"], isr_scaled=t["isrs"],
+                scaling_squared=np.float32(t["scale2"] * np.float32(0.5))), t
 
 
 def oracle_quant_tables(ms, exact_rsqrt=False):

@@ -161,26 +161,99 @@ def test_ranks_on_one_gpu_exchange_their_columns(world, chunks, T):
             e.close()
 
 
-def test_a_missing_peer_ends_the_wait():
+def test_a_missing_peer_is_reported_poisoned_and_recoverable(monkeypatch):
+    """A peer that never shows up: the wait ends, the caller can SEE it (gmm_gather_status, GMM_ERR_TIMEOUT from the
+    next scoring / consuming call), a consumer already queued cannot read stale columns (+inf), and after
+    gmm_gather_reset the handle works again."""
+    monkeypatch.setenv("GMM_GATHER_TIMEOUT_MS", "150")
     ms = synth.make_model(M=64, K=4, D=10, seed=3)
     engines, M = _shard_engines(ms, 2)
     T, ld = 64, 64
+    Mp = 32
     flags_offset = T * ld * 4
     try:
         dx = torch.from_numpy(synth.make_features(ms, T, seed=1)).cuda()
         e0 = engines[0][0]
         bases = [e0.peer_alloc(flags_offset + 128)[0] for _ in range(2)]
+        blocks = [torch.as_tensor(sharded._DeviceBlock(b, (T, ld)), device="cuda:0") for b in bases]
         flags = [torch.as_tensor(sharded._DeviceBlock(b + flags_offset, (32,)), device="cuda:0").view(torch.int32) for b in bases]
-        e0.score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)  # rank 1 never calls
+        blocks[0].fill_(-7.0)  # "stale scores of an earlier call"
+        torch.cuda.synchronize()
+        assert e0.gather_status() == 0
+        e0.score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)  # rank 1 never calls: returns, no error yet
         e0.sync()
         assert int(flags[0][17]) == 1          # marked on the waiting rank ...
         assert int(flags[1][8 + 0]) == 0       # ... which did not announce its columns as complete
-        del flags
+        assert e0.gather_status() == 1         # ... and says so to the host: call number 1
+        own = torch.empty((T, Mp), device="cuda")
+        e0.score_device(T, dx, own)
+        e0.sync()
+        assert torch.equal(blocks[0][:, :Mp], own)                  # own columns are the real scores
+        assert bool(torch.isinf(blocks[0][:, Mp:]).all())           # the peer's columns: +inf, not the stale -7
+        with pytest.raises(capi.GmmError, match="timed out"):
+            e0.score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)
+        from rasr_b200.align import AlignmentAutomata, linear_hmm
+        au = AlignmentAutomata.from_arc_lists([linear_hmm(np.arange(10) % Mp)])
+        with pytest.raises(capi.GmmError, match="timed out"):  # a consumer of the block on this handle
+            e0.align_device(np.array([0, T], np.uint32), bases[0], au, ld=ld)
+        # a second handle that meets the marked block refuses too
+        with pytest.raises(capi.GmmError, match="timed-out"):
+            engines[1][0].score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)
+        e0.gather_reset()
+        assert e0.gather_status() == 0 and int(flags[0][17]) == 0
+        flags[0][:8] = 1 << 20                 # play the peer: READY and DONE far ahead
+        flags[0][8:16] = 1 << 20
+        torch.cuda.synchronize()
+        e0.score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)
+        e0.sync()
+        assert e0.gather_status() == 0
+        assert torch.equal(blocks[0][:, :Mp], own)
+        del flags, blocks
         for b in bases:
             e0.peer_free(b)
     finally:
         for e, _, _ in engines:
             e.close()
+
+
+def test_a_new_handle_continues_the_blocks_call_numbering():
+    """The call counter lives with the flag words: a fresh handle over used blocks does not start again at 1 (where
+    every wait would be satisfied at once by the words of earlier calls)."""
+    ms = synth.make_model(M=64, K=4, D=10, seed=3)
+    T, ld, Mp = 64, 64, 32
+    flags_offset = T * ld * 4
+    engines, M = _shard_engines(ms, 2)
+    try:
+        dx = torch.from_numpy(synth.make_features(ms, T, seed=1)).cuda()
+        e0 = engines[0][0]
+        bases = [e0.peer_alloc(flags_offset + 128)[0] for _ in range(2)]
+        flags = [torch.as_tensor(sharded._DeviceBlock(b + flags_offset, (32,)), device="cuda:0").view(torch.int32) for b in bases]
+        for f in flags:
+            f[:16] = 1 << 20
+        torch.cuda.synchronize()
+        for _ in range(3):
+            e0.score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)
+        e0.sync()
+        assert int(flags[0][18]) == 3 and int(flags[1][8 + 0]) == 3
+        e0.close()
+        engines[0] = (None, 0, 0)
+        # a new engine for the same rank over the same blocks: its first call is number 4
+        fresh, _ = _shard_engines(ms, 2)
+        e0b = fresh[0][0]
+        fresh[1][0].close()
+        try:
+            e0b.score_device_gather(T, dx, 0, bases, ld, 0, flags_offset, 1)
+            e0b.sync()
+            assert int(flags[0][18]) == 4 and int(flags[1][8 + 0]) == 4
+            del flags
+            for b in bases:
+                e0b.peer_free(b)
+        finally:
+            e0b.close()
+    finally:
+        for e, _, _ in engines:
+            if e is not None:
+                e.close()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")

@@ -9,7 +9,8 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import (golden_names, load_golden, oracle_float_tables, oracle_quant_tables, ref_quant_tables)
+from conftest import (batchint_golden_names, golden_names, load_golden, oracle_batchint_tables, oracle_float_tables,
+                      oracle_quant_tables, ref_quant_tables)
 from rasr_b200 import capi, feature_scorer, synth, tables
 
 pytestmark = pytest.mark.gpu
@@ -73,6 +74,40 @@ def test_golden_quantized_bit_exact(eng, name):
     assert np.array_equal(r["q"], z["simd_q"])
     assert np.array_equal(r["best"], z["simd_best"])
     assert np.array_equal(bits(r["score"]), bits(z["simd_score"]))
+
+
+@pytest.mark.parametrize("name", batchint_golden_names())
+def test_golden_batch_int_bit_exact(eng, oracle, name):
+    """`batch-diagonal-maximum-int` (BatchFeatureScorer.cc:300-472) on the quantized kernel: the reference's own
+    constants and final scale, scores bit-identical to the compiled reference's buffered scorer -- including the
+    zero-weight densities whose 0x80000000 constant wins the minimum there."""
+    ms, z = load_golden(name)
+    t, raw = oracle_batchint_tables(ms)
+    eng.upload_quant(t["offsets"], t["qmean"], t["cov_idx"], t["qconst"], t["isr_scaled"], t["scaling_squared"],
+                     rule=capi.QUANT_RULE_BATCH_INT)
+    r = eng.quant_score_host(z["x"])
+    assert np.array_equal(bits(r["score"]), bits(z["score"]))
+    qx = oracle.simd_quantize_features(z["x"], raw["isrs"])
+    q, best = oracle.simd_score(ms.mix_offsets, raw, qx)
+    assert np.array_equal(r["q"], q) and np.array_equal(r["best"], best)
+
+
+def test_batch_int_scorer_type_of_the_host_mirror(oracle):
+    """feature-scorer-type = batch-diagonal-maximum-int through the buffered interface, at a size where the tensor
+    kernel runs: equal to the oracle's restatement of the reference scorer."""
+    ms = synth.make_model(M=301, K=16, D=45, seed=8)
+    x = synth.make_features(ms, 200, seed=3)
+    t, raw = oracle_batchint_tables(ms)
+    fs = feature_scorer.GpuFeatureScorer(ms, "batch-diagonal-maximum-int", quant_tables=t)
+    fs.reset()
+    for f in x:
+        fs.addFeature(f)
+    got = np.stack([fs.flush().scores() for _ in range(len(x))])
+    q, _ = oracle.simd_score(ms.mix_offsets, raw, oracle.simd_quantize_features(x, raw["isrs"]))
+    assert np.array_equal(bits(got), bits(oracle.batchint_final_score(q, raw["scale2"])))
+    assert fs.n_batches == 1
+    with pytest.raises(ValueError, match="pooled"):
+        feature_scorer.GpuFeatureScorer(synth.make_model(M=4, K=2, D=5, covariance="density"), "batch-diagonal-maximum-int")
 
 
 @pytest.mark.parametrize("name", golden_names())

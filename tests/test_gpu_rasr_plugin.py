@@ -1,6 +1,7 @@
 """GPU: the RASR-side plugin classes (rasr/GpuFeatureScorer.cc) against the reference's own scorer classes, both
-created through Mm::FeatureScorerFactory inside one RASR process and driven by the buffered caller loop of
-Speech::AlignmentNode.  The binary (oracle/_ref/rasr_gpu_check) is built by rasr/Makefile in the build container
+created by the reference's own Mm::Module_ (feature-scorer-type -> factory -> scaling wrapper; rasr/Module.cc registers
+the GPU scorers in it) inside one RASR process and driven by the buffered caller loops of Speech::AlignmentNode and
+Speech::RecognizerDelayHandler.  The binary (oracle/_ref/rasr_gpu_check) is built by rasr/Makefile in the build container
 from the unmodified reference objects; it travels to the GPU box with the snapshot."""
 import os
 import subprocess
@@ -31,4 +32,27 @@ def test_plugin_matches_reference_scorers_in_process(tmp_path, kw, T, buffer_siz
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     print(r.stdout)
     assert r.returncode == 0, r.stdout[-3000:]
-    assert r.stdout.count("PASS") == 4
+    # 5 scorer pairs (the batch-int pair needs a pooled covariance), delayed-recognizer loop, time-indexed scorers,
+    # density posteriors, with-density-assignment
+    assert r.stdout.count("PASS") == (8 if kw.get("covariance") else 9) and "FAIL" not in r.stdout
+
+
+@pytest.mark.skipif(not os.path.exists(CHECK), reason="oracle/_ref/rasr_gpu_check not built (needs /root/reference)")
+def test_plugin_path_is_within_20_percent_of_the_call_it_wraps(tmp_path):
+    """BASELINE.json configs[0]: 4501 x 16 x 45, one 1000-frame segment; segments of 4000 frames for the timing.  The
+    plugin path (addFeature per frame -> one batch -> flush + one read per frame) against gmm_score_host on the same
+    engine, best of 12 repetitions each, in the same process."""
+    ms = synth.make_model(M=4501, K=16, D=45)
+    x = synth.make_features(ms, 64)
+    mp, fp = str(tmp_path / "m.gms"), str(tmp_path / "x.f32")
+    ms.save(mp)
+    x.tofile(fp)
+    r = subprocess.run([CHECK, f"model={mp}", f"features={fp}", "buffer-size=0", "timing-frames=4000"], cwd=str(tmp_path),
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    print(r.stdout)
+    assert r.returncode == 0, r.stdout[-3000:]
+    timing = [l for l in r.stdout.splitlines() if l.startswith("TIMING")]
+    assert len(timing) == 1
+    ratio = float(timing[0].split("ratio=")[1])
+    assert ratio >= 0.8, timing[0]
+    assert r.stdout.count("PASS") == 10 and "FAIL" not in r.stdout

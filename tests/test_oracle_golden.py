@@ -2,7 +2,7 @@
 import numpy as np
 import pytest
 
-from conftest import golden_names, load_golden
+from conftest import batchint_golden_names, golden_names, load_golden
 
 
 def bits(a):
@@ -41,6 +41,38 @@ def test_simd_scorer_bit_exact(oracle, name):
     assert np.array_equal(q, z["simd_q"])
     assert np.array_equal(b, z["simd_best"])
     assert np.array_equal(bits(oracle.simd_final_score(q, t["scaling_squared"])), bits(z["simd_score"]))
+
+
+@pytest.mark.parametrize("name", batchint_golden_names())
+def test_batch_int_scorer_bit_exact(oracle, name):
+    """`batch-diagonal-maximum-int` (BatchFeatureScorer.cc:300-472): restated tables + the SIMD scorer's u8 distance
+    + the f32 division by 2 scale^2, against the compiled reference's buffered scorer."""
+    ms, z = load_golden(name)
+    t = oracle.batchint_prepare(ms)
+    qx = oracle.simd_quantize_features(z["x"], t["isrs"])
+    q, _ = oracle.simd_score(ms.mix_offsets, t, qx)
+    assert np.array_equal(bits(oracle.batchint_final_score(q, t["scale2"])), bits(z["score"]))
+
+
+def test_batch_int_scorer_refuses_unpooled_covariances(oracle):
+    ms, _ = load_golden("density_cov_ragged_shared")
+    with pytest.raises(ValueError, match="pooled"):
+        oracle.batchint_prepare(ms)
+    from rasr_b200 import tables
+    with pytest.raises(ValueError, match="pooled"):
+        tables.batchint_tables(ms)
+
+
+def test_batch_int_tables_of_the_package_match_the_oracle(oracle):
+    """rasr_b200.tables.batchint_tables (numpy, exact inverse square roots) against the oracle's restatement built
+    with exact inverse square roots (the reference build's rsqrt differs per build)."""
+    from rasr_b200 import tables
+    for name in batchint_golden_names():
+        ms, _ = load_golden(name)
+        t, m = oracle.batchint_prepare(ms, exact_rsqrt=True), tables.batchint_tables(ms)
+        assert np.array_equal(t["qmean"], m["qmean"]) and np.array_equal(t["qconst"], m["qconst"])
+        assert np.array_equal(bits(t["isrs"][0]), bits(m["isr_scaled"][0]))
+        assert np.float32(m["scaling_squared"]) * np.float32(2) == t["scale2"]
 
 
 def test_posteriors_sum_to_one(oracle):
