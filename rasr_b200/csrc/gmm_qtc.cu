@@ -67,6 +67,8 @@ struct QKParams {
     uint32_t        qBase;       // cmax (wrapping u32): q = qBase + |qx|^2 - max_k acc_k
     unsigned long long* dbg;     // GMM_QTC_DEBUG: per-CTA cycle counters (16 words per CTA)
     uint32_t        vecStores;   // 0: always the scalar staged store path (GMM_QTC_STORES=scalar)
+    uint32_t        dbgSkip;     // GMM_QTC_DEBUG_SKIP (timing experiments only, results are NOT written): 1 = the epilogue
+                                 // only hands the accumulator back, 2 = it loads and reduces but stores nothing
     uint32_t        keyMul;      // 256, as a run-time value: key = acc * keyMul + term compiles to IMAD (FMA pipe)
 };
 
@@ -158,7 +160,7 @@ __device__ __forceinline__ uint32_t qkey(uint32_t v, uint32_t term, uint32_t mul
     return viaMad ? v * mul + term : (v << 8) + term;
 }
 
-template<int SP, bool WB>
+template<int SP, bool WB, int MAD = 3>
 __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t kcAddr, uint32_t segEnd, uint32_t qbx,
                                            uint32_t offB, QEpiState& st, uint32_t mul, uint32_t* resQ = nullptr,
                                            uint32_t* resB = nullptr) {
@@ -179,9 +181,9 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
             if (SP > 0 && !WB)
                 key[j] = v[s * 8 + j];
             else if (SP > 0)
-                key[j] = qkey(v[s * 8 + j], (uint32_t)(255 - ((seg % SP) * 8 + j)), mul, (j & 3) != 3);
+                key[j] = qkey(v[s * 8 + j], (uint32_t)(255 - ((seg % SP) * 8 + j)), mul, (j & 3) < MAD);
             else
-                key[j] = qkey(v[s * 8 + j], kc[s * 8 + j], mul, (j & 3) != 3);
+                key[j] = qkey(v[s * 8 + j], kc[s * 8 + j], mul, (j & 3) < MAD);
         }
         // eight keys and the running maximum of the open mixture: four three-input maxima
         const bool     first = SP > 0 && (seg % SP) == 0;
@@ -223,7 +225,7 @@ __device__ __forceinline__ void qepi_chunk(const uint32_t* v, int ch, uint32_t k
 // NG = 2 (NE = 8 only): TWO epilogue groups of eight warps; group g drains the accumulator of the tiles with t % 2 == g,
 // so one group's reduction (integer pipes) runs while the other group's row pieces leave (load/store unit, memory
 // latency) -- with one group the two phases alternate and each pipe idles half the time.
-template<int NE, int NG, int OUT>
+template<int NE, int NG, int OUT, int MAD = 3>
 __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kernel(const QKParams p) {
     static_assert(NG == 1 || (NG == 2 && NE == 8 && kRing % 2 == 0), "two groups: eight warps each, ring index parity = tile parity");
     constexpr bool WQ = OUT == 0 || (OUT & 1), WB = OUT == 0 || (OUT & 2), WS = OUT == 0 || (OUT & 4);
@@ -315,6 +317,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
         bool               have = false;
         long long          mW = 0, mI = 0, mc0 = 0;
         const long long    mStart = clock64();
+        unsigned long long gt0 = 0;
+        if (p.dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
             const uint32_t chunk = item % p.split;
             const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
@@ -352,8 +356,10 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
             }
         }
         if (p.dbg && leader) {
-            unsigned long long* d = p.dbg + blockIdx.x * 16;
-            d[0] = clock64() - mStart, d[1] = mW, d[2] = mI, d[4] = t;
+            unsigned long long* d = p.dbg + blockIdx.x * 128;
+            unsigned long long gt1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt1));
+            d[0] = clock64() - mStart, d[1] = mW, d[2] = mI, d[4] = t, d[5] = gt0, d[6] = gt1;
         }
     }
     else {
@@ -368,7 +374,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
         const ptrdiff_t bestDelta  = p.best ? reinterpret_cast<char*>(p.best) - gBase : 0;
         const ptrdiff_t scoreDelta = p.score ? reinterpret_cast<char*>(p.score) - gBase : 0;
         uint32_t       itemCount = 0, t = 0;
-        long long      eW = 0, eL = 0, eB = 0, eS = 0, ec0 = 0;
+        long long      eW = 0, eL = 0, eB = 0, eS = 0, ec0 = 0, eI = 0;
+        const long long eStart = clock64();
         if (lane == 0) {  // both accumulators start drained (two groups: each speaks for its own)
             if (NG == 1 || grp == 0)
                 mbar_arrive(smem_u32(&ready[0]));
@@ -381,7 +388,9 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
             if (f0 >= f1)
                 continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+            if (p.dbg) ec0 = clock64();
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            if (p.dbg) eI += clock64() - ec0;
             // this group's first tile of the item (tiles alternate between the groups across items as well)
             const uint32_t  fG = NG == 2 ? f0 + ((t ^ (uint32_t)grp) & 1u) : f0;
             const uint8_t*  tile = sB + (size_t)b * bBytes + (size_t)p.atomsB * kTileN * SWZ;
@@ -446,6 +455,13 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
                     if (p.dbg) { const long long c1 = clock64(); eW += c1 - ec0; ec0 = c1; }
                     const uint32_t taddr   = tmemBase + ((uint32_t)(qd * 32) << 16) + acc * kTileN + part * PW;
                     const uint32_t drained = smem_u32(&ready[(t + 2) % kRing]);
+                    if (p.dbgSkip == 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(drained);
+                        continue;
+                    }
                     const uint32_t stBuf = stGrp + (kBufs == 2 ? (t & 1) * stageWarp * 4 : 0u);
                     QEpiState      st;
                     st.run = kNoKey, st.sp = stBuf + stOff;  // SP > 0 never reads run before writing it
@@ -460,21 +476,21 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
-                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(vb, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                     }
                     else if (NE == 16) {
                         // 96 registers per thread: one 32-column chunk (+ its 32 table entries) live at a time
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld32(taddr + 32, va);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(va, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(va, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                     }
                     else if (NG == 2) {
                         // 96 registers per thread (18 warps): one 32-column chunk live at a time; the other warps of the
@@ -489,7 +505,7 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
                                 if (lane == 0)
                                     mbar_arrive(drained);
                             }
-                            qepi_chunk<SP, WB>(va, ch, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                            qepi_chunk<SP, WB, MAD>(va, ch, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         }
                     }
                     else {
@@ -497,19 +513,19 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 32, vb);
-                        qepi_chunk<SP, WB>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(va, 0, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 64, va);
-                        qepi_chunk<SP, WB>(vb, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(vb, 1, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 96, vb);
-                        qepi_chunk<SP, WB>(va, 2, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(va, 2, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                         tmem_ld_wait();
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0)
                             mbar_arrive(drained);
-                        qepi_chunk<SP, WB>(vb, 3, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
+                        qepi_chunk<SP, WB, MAD>(vb, 3, kcAddr, segEnd, xxBase, offB, st, p.keyMul, rq, rb);
                     }
                     if (VEC) {
 #pragma unroll
@@ -521,6 +537,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
                         }
                     }
                     if (p.dbg) { const long long c1 = clock64(); eL += c1 - ec0; ec0 = c1; }
+                    if (p.dbgSkip == 2)
+                        continue;
                     if (NE == 16)  // the quarter's four warps have staged their parts of these 32 rows
                         asm volatile("bar.sync %0, 128;" ::"r"(1 + qd) : "memory");
                     else
@@ -621,9 +639,9 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
             if (lane == 0)
                 mbar_arrive(smem_u32(&emptyB[b]));
         }
-        if (p.dbg && e == 0 && grp == 0 && lane == 0) {
-            unsigned long long* d = p.dbg + blockIdx.x * 16;
-            d[8] = eW, d[9] = eL, d[10] = eB, d[11] = eS;
+        if (p.dbg && lane == 0) {  // per epilogue warp: waits, phases, whole loop
+            unsigned long long* d = p.dbg + blockIdx.x * 128 + 16 + (warp - kEpiWarp0) * 6;
+            d[0] = eW, d[1] = eL, d[2] = eB, d[3] = eS, d[4] = clock64() - eStart, d[5] = eI;
         }
     }
 
@@ -894,9 +912,9 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     const bool debug = getenv("GMM_QTC_DEBUG") != nullptr;
     if (debug) {
         void* d = nullptr;
-        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 128, &d)))
+        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 1024, &d)))
             return rc;
-        GMM_CUDA_TRY(h, cudaMemsetAsync(d, 0, (size_t)h->smCount * 128, h->stream));
+        GMM_CUDA_TRY(h, cudaMemsetAsync(d, 0, (size_t)h->smCount * 1024, h->stream));
         p.dbg = (unsigned long long*)d;
     }
     const uint32_t epiWarps = 4 * (kTileN / tm.partW);
@@ -918,6 +936,8 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
             bestS    = S;
         }
     }
+    if (const char* e = getenv("GMM_QTC_SPLIT"))  // experiments: frame ranges per B tile
+        bestS = std::max(1u, std::min<uint32_t>(FT, (uint32_t)atoi(e)));
     p.split        = bestS;
     const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
     // Output set fixed at compile time for the combinations callers use (tests / bench: q + arg-min; the RASR plugin:
@@ -941,6 +961,7 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
             groups = 2;
     }
     p.keyMul = 256;
+    p.dbgSkip = getenv("GMM_QTC_DEBUG_SKIP") ? (uint32_t)atoi(getenv("GMM_QTC_DEBUG_SKIP")) : 0u;
     if (epiWarps == 16)
         kernel = out == 3 ? qtc_score_kernel<16, 1, 3> : out == 4 ? qtc_score_kernel<16, 1, 4> : out == 6 ? qtc_score_kernel<16, 1, 6>
                : out == 7 ? qtc_score_kernel<16, 1, 7> : qtc_score_kernel<16, 1, 0>;
@@ -958,21 +979,52 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
     if (debug) {  // development aid: where the MMA thread and epilogue warp 0 spend their cycles
-        std::vector<unsigned long long> d((size_t)h->smCount * 16);
+        std::vector<unsigned long long> d((size_t)h->smCount * 128);
         GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
         GMM_CUDA_TRY(h, cudaMemcpy(d.data(), p.dbg, d.size() * 8, cudaMemcpyDeviceToHost));
-        double tot = 0, mW = 0, mI = 0, tiles = 0, eW = 0, eL = 0, eB = 0, eS = 0;
+        double tot = 0, mW = 0, mI = 0, tiles = 0, ns = 0;
+        unsigned long long g0 = ~0ull, g1 = 0;
         for (int c = 0; c < grid; ++c) {
-            tot += d[c * 16], mW += d[c * 16 + 1], mI += d[c * 16 + 2], tiles += d[c * 16 + 4];
-            eW += d[c * 16 + 8], eL += d[c * 16 + 9], eB += d[c * 16 + 10], eS += d[c * 16 + 11];
+            tot += d[c * 128], mW += d[c * 128 + 1], mI += d[c * 128 + 2], tiles += d[c * 128 + 4];
+            ns += (double)(d[c * 128 + 6] - d[c * 128 + 5]);
+            g0 = std::min(g0, d[c * 128 + 5]), g1 = std::max(g1, d[c * 128 + 6]);
+        }
+        fprintf(stderr, "[gmm_qtc] MMA loops: %.1f us first start to last end, SM clock %.0f MHz (cycles / globaltimer)\n",
+                (double)(g1 - g0) * 1e-3, ns > 0 ? tot / ns * 1e3 : 0.0);
+        {  // per CTA: start offset, duration, tiles -- by number of tiles
+            double dmin[2] = {1e30, 1e30}, dmax[2] = {0, 0}, dsum[2] = {0, 0}, smax = 0, emin = 1e30;
+            int    n[2] = {0, 0};
+            unsigned long long tmax = 0;
+            for (int c = 0; c < grid; ++c)
+                tmax = std::max(tmax, d[c * 128 + 4]);
+            for (int c = 0; c < grid; ++c) {
+                const int    k   = d[c * 128 + 4] == tmax ? 1 : 0;
+                const double dur = (double)(d[c * 128 + 6] - d[c * 128 + 5]) * 1e-3;
+                dmin[k] = std::min(dmin[k], dur), dmax[k] = std::max(dmax[k], dur), dsum[k] += dur, n[k]++;
+                smax = std::max(smax, (double)(d[c * 128 + 5] - g0) * 1e-3);
+                emin = std::min(emin, (double)(d[c * 128 + 6] - g0) * 1e-3);
+            }
+            fprintf(stderr, "[gmm_qtc]   %d CTAs with %llu tiles: loop %.1f / %.1f / %.1f us (min / mean / max); %d CTAs with fewer: "
+                    "%.1f / %.1f / %.1f us; latest start +%.1f us, earliest end +%.1f us\n",
+                    n[1], tmax, dmin[1], dsum[1] / std::max(1, n[1]), dmax[1], n[0], n[0] ? dmin[0] : 0.0,
+                    dsum[0] / std::max(1, n[0]), dmax[0], smax, emin);
         }
         tiles = std::max(1.0, tiles);
         fprintf(stderr,
-                "[gmm_qtc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u x %u out %d | cycles per tile: MMA thread "
-                "total %.0f = wait-ready %.0f + issue %.0f | epilogue warp 0: wait-for-MMA %.0f + loads and reduction %.0f + "
-                "group barrier %.0f + stores %.0f\n",
-                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, groups, out, tot / tiles, mW / tiles, mI / tiles,
-                eW / tiles, eL / tiles, eB / tiles, eS / tiles);
+                "[gmm_qtc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u x %u out %d | cycles per tile: MMA "
+                "thread total %.0f = wait-ready %.0f + issue %.0f\n",
+                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, groups, out, tot / tiles, mW / tiles, mI / tiles);
+        for (uint32_t w = 0; w < epiWarps * groups; ++w) {  // per CTA tile (a group of two sees every other tile)
+            double v[6] = {0, 0, 0, 0, 0, 0};
+            for (int c = 0; c < grid; ++c)
+                for (int k = 0; k < 6; ++k)
+                    v[k] += d[c * 128 + 16 + w * 6 + k];
+            fprintf(stderr,
+                    "[gmm_qtc]   epilogue warp %2u: wait-for-MMA %.0f + loads and reduction %.0f + barrier %.0f + stores %.0f "
+                    "= %.0f of loop %.0f (B-tile wait %.0f)\n",
+                    w, v[0] / tiles, v[1] / tiles, v[2] / tiles, v[3] / tiles, (v[0] + v[1] + v[2] + v[3]) / tiles,
+                    v[4] / tiles, v[5] / tiles);
+        }
     }
     return GMM_OK;
 }
