@@ -1,6 +1,7 @@
 """CPU, world_size 2, gloo: the multi-GPU host logic -- segment ownership, mixture-shard tables and the all-gather
 assembly of per-shard score blocks.  The per-shard scores come from the oracle here (test infrastructure); on GPUs
-they come from the engine (tests/test_gpu_sharded.py / bench.py --sharded)."""
+they come from the engine (tests/test_gpu_gather.py, profiles/bench_sharded.py, and bench.py's
+extra.cfg5_mixture_sharded at N > 1)."""
 import os
 
 import numpy as np
