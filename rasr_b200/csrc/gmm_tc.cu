@@ -66,7 +66,7 @@ struct KParams {
     uint32_t       atoms;                      // swizzle atoms per operand row
     uint32_t       aTileBytes, bTileBytes;     // bTileBytes includes c / slot / meta
     uint32_t       stagesA, buffersB;
-    uint32_t       stagePitch;                 // floats per staging row (maxMixPerPart + 1)
+    uint32_t       stagePitch;                 // floats per staging row (odd, >= maxMixPerPart + 5)
     const uint32_t* itemTab;                   // subset scoring: 8 words per item {B tile, f0, f1, rowBase, rowEnd}
     uint32_t       nItems;
     unsigned long long* dbg;                   // GMM_TC_DEBUG: per-CTA cycle counters of the MMA thread
@@ -260,8 +260,13 @@ __device__ __forceinline__ ItemRange item_range(const KParams& p, uint32_t item,
     return r;
 }
 
-template<int SWZ, int MODE, bool BEST, int NE>
+// NG = 2 (NE = 8 only): TWO epilogue groups of eight warps; group g drains the accumulator of the tiles with t % 2 == g.
+// With one group the epilogue's phases alternate -- TMEM loads and the min tree (ALU pipe), then the row pieces (load /
+// store unit, memory latency) -- and the MMA warp waits for the accumulator a third of the time (4501x16 model: 337 of
+// 1189 cycles per tile); with two, one group's stores run under the other group's reduction.
+template<int SWZ, int MODE, bool BEST, int NE, int NG = 1>
 __device__ __forceinline__ void tc_score_body(const KParams& p) {
+    static_assert(NG == 1 || (NG == 2 && NE == 8 && kRing % 2 == 0), "two groups: eight warps each, ring parity = tile parity");
     extern __shared__ uint8_t smemRaw[];
     // swizzled operand tiles need 1024-byte alignment of the shared-memory address itself
     uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
@@ -275,9 +280,9 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     uint8_t*       sA        = sB + (size_t)p.buffersB * bBytes;
     float*         sStage    = reinterpret_cast<float*>(sA + (size_t)p.stagesA * p.aTileBytes);
     const uint32_t stageWarp = 32 * p.stagePitch;  // floats per warp
-    uint32_t*      sStageB   = reinterpret_cast<uint32_t*>(sStage + NE * stageWarp);
+    uint32_t*      sStageB   = reinterpret_cast<uint32_t*>(sStage + NE * NG * stageWarp);
     uint64_t*      bars      = reinterpret_cast<uint64_t*>(
-            (reinterpret_cast<uintptr_t>(sStageB + (BEST ? NE * stageWarp : 0)) + 15) & ~(uintptr_t)15);
+            (reinterpret_cast<uintptr_t>(sStageB + (BEST ? NE * NG * stageWarp : 0)) + 15) & ~(uintptr_t)15);
     // Barriers.  Tiles are numbered t = 0, 1, ... per CTA across its items; rings of kRing follow t % kRing.
     //   ready[t % 4]: tile t may be issued = its A operand has landed (producer arrive + bytes) AND the
     //                 accumulator t & 1 was drained by every epilogue warp (after tile t - 2)
@@ -296,7 +301,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(smem_u32(&fullB[i]), 1);
-            mbar_init(smem_u32(&emptyB[i]), 1 + NE);  // MMA commit + the epilogue warps
+            mbar_init(smem_u32(&emptyB[i]), 1 + NE * NG);  // MMA commit + the epilogue warps
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -423,16 +428,18 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     }
     else {
         // ===== epilogue: TMEM -> registers -> (min / log-sum-exp per mixture) -> staged -> global =====
-        const int      e = warp - kEpiWarp0, q = warp & 3, part = e >> 2;
-        const uint32_t stWarp = smem_u32(sStage) + (uint32_t)e * stageWarp * 4;  // this warp's staging block
+        const int      grp = (warp - kEpiWarp0) / NE, e = (warp - kEpiWarp0) % NE, q = warp & 3, part = e >> 2;
+        const uint32_t stWarp = smem_u32(sStage) + (uint32_t)(grp * NE + e) * stageWarp * 4;  // this warp's staging block
         const uint32_t stRow  = stWarp + (uint32_t)lane * p.stagePitch * 4;      // this lane's (frame's) row in it
-        const uint32_t offB   = NE * stageWarp * 4;                              // index plane behind the scores
+        const uint32_t offB   = NE * NG * stageWarp * 4;                         // index plane behind the scores
         const ptrdiff_t bestDelta = BEST ? reinterpret_cast<const char*>(p.best) - reinterpret_cast<const char*>(p.scores) : 0;
         uint32_t       itemCount = 0, t = 0;
         long long      eW = 0, eL = 0, eC = 0, eS = 0, ec0 = 0;  // GMM_TC_DEBUG: where this warp's cycles go
-        if (lane == 0) {  // both accumulators start out drained
-            mbar_arrive(smem_u32(&ready[0]));
-            mbar_arrive(smem_u32(&ready[1]));
+        if (lane == 0) {  // both accumulators start out drained (two groups: each speaks for its own)
+            if (NG == 1 || grp == 0)
+                mbar_arrive(smem_u32(&ready[0]));
+            if (NG == 1 || grp == 1)
+                mbar_arrive(smem_u32(&ready[1]));
         }
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
             const ItemRange ir = item_range(p, item, tilesPerItem);
@@ -441,6 +448,9 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                 continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            // this group's first tile of the item (tiles alternate between the groups across items as well)
+            const uint32_t  fG = NG == 2 ? f0 + ((t ^ (uint32_t)grp) & 1u) : f0;
+            const uint32_t  tItem = t;
             const uint8_t*  tile  = sB + (size_t)b * bBytes + (size_t)p.atoms * kTileN * SWZ;
             const uint16_t* slots = reinterpret_cast<const uint16_t*>(tile);
             const uint32_t* meta  = reinterpret_cast<const uint32_t*>(tile + kTileN * 2);  // TileMeta words
@@ -457,27 +467,38 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             const size_t    gStep = ((size_t)adv_r * p.ld + adv_j) * 4, gStepW = gStep + (p.ld - nMix) * 4;  // bytes
             const uint32_t  sStep = (adv_r * p.stagePitch + adv_j) * 4, sStepW = sStep + (p.stagePitch - nMix) * 4;
             const uint32_t  ssLane = stWarp + (lr0 * p.stagePitch + lj0) * 4;
-            char*           gTile  = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + q * 32 + lr0) * p.ld + mixBase + lj0);
-            const size_t    gTileStep = (size_t)kTileM * p.ld * 4;
-            const float2*   rip = p.rowInfo + (size_t)f0 * kTileM + q * 32 + lane;
+            char*           gTile  = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + (fG - f0) * kTileM + q * 32 + lr0) * p.ld + mixBase + lj0);
+            const size_t    gTileStep = (size_t)NG * kTileM * p.ld * 4;
+            const float2*   rip = p.rowInfo + (size_t)fG * kTileM + q * 32 + lane;
             // the tile loop, specialised on the tile's mixture shape when it is uniform (see epi_chunk)
             // DIRECT (maximum approximation without arg-min on uniform parts, row pieces 8- / 16-byte aligned): a lane
             // keeps its frame's R = SEGS / SP mixture scores in registers and writes the row piece itself with 64- /
             // 128-bit stores -- no staging, no shared-memory round trip, a fifth of the store path's instructions (the
             // epilogue is bound by the ALU pipe: 2 warps per scheduler at one instruction per 2 cycles)
-            char* gLane = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + q * 32 + lane) * p.ld + mixBase);
+            char* gLane = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + (fG - f0) * kTileM + q * 32 + lane) * p.ld + mixBase);
             auto tiles = [&](auto spTag, auto dirTag) {
                 constexpr int  SP     = decltype(spTag)::value;
                 constexpr bool DIRECT = decltype(dirTag)::value && MODE == 0 && !BEST && SP > 0;
                 constexpr int  R      = DIRECT ? SEGS / SP : 1;
+                // VEC (R a multiple of 4): the R results go through the warp's staging block ([32 rows][R + 4] floats,
+                // 128-bit writes) and leave as 128-bit stores of R / 4 lanes per row -- a store instruction then touches
+                // 32 * 4 / R lines instead of 32 (the load/store unit takes one line per cycle: 512 -> 256 line slots per
+                // tile at R = 8).  R = 2: the lane writes its 8 bytes itself.
+                constexpr bool VEC    = DIRECT && R % 4 == 0;
+                constexpr int  PV     = R + 4, WQ4 = R / 4 > 0 ? R / 4 : 1, RPP = 32 / WQ4;
+                const uint32_t vqi = (uint32_t)lane % WQ4, vr0 = (uint32_t)lane / WQ4;
+                const uint32_t vRead = stWarp + (vr0 * PV + vqi * 4) * 4, vWrite = stWarp + (uint32_t)lane * PV * 4;
+                char* gVec = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + (fG - f0) * kTileM + q * 32 + vr0) * p.ld +
+                                                     mixBase + vqi * 4);
                 float          res[R];
                 float* const   resp = DIRECT ? res : nullptr;
-                float2 riNext = *rip;  // row term / scale of the next tile's row, fetched one tile ahead
-                for (uint32_t f = f0; f < f1; ++f, ++t) {
+                float2 riNext = fG < f1 ? *rip : make_float2(0.f, 0.f);  // row term / scale, fetched one tile ahead
+                for (uint32_t f = fG; f < f1; f += NG) {
+                    const uint32_t t   = tItem + (f - f0);  // tile counter of the CTA (shadows the item-level one)
                     const uint32_t acc = t & 1;
                     const float    rt = riNext.x, rs = riNext.y;
-                    rip += kTileM;
-                    if (f + 1 < f1)
+                    rip += NG * kTileM;
+                    if (f + NG < f1)
                         riNext = *rip;
                     if (p.dbg) ec0 = clock64();
                     mbar_wait(smem_u32(&done[t % kRing]), (t / kRing) & 1);
@@ -487,8 +508,9 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     const uint32_t drained  = smem_u32(&ready[(t + 2) % kRing]);  // tile t + 2 reuses this accumulator
                     EpiState st;
                     st.run = INFINITY, st.sum = 0.f, st.idx = 0xFFFFFFFFu, st.sp = stRow;
-                    uint32_t va[32], vb[32];
+                    uint32_t va[32];
                     if (NE == 16) {
+                        uint32_t vb[32];
                         // 64 columns: both loads in flight, then the accumulator goes straight back to the MMA warp
                         tmem_ld32(taddr, va);
                         tmem_ld32(taddr + 32, vb);
@@ -506,8 +528,26 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                             epi_chunk<MODE, BEST, SP>(vb, 1, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
                         }
                     }
+                    else if (NG == 2) {
+                        // 96 registers per thread (18 warps): one 32-column chunk live at a time; the scheduler's other
+                        // warps (its second group among them) cover the TMEM load latency
+#pragma unroll
+                        for (int ch = 0; ch < 4; ++ch) {
+                            tmem_ld32(taddr + 32 * ch, va);
+                            tmem_ld_wait();
+                            if (ch == 3) {
+                                tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0)
+                                    mbar_arrive(drained);
+                                if (p.dbg) { const long long c1 = clock64(); eL += c1 - ec0; ec0 = c1; }
+                            }
+                            epi_chunk<MODE, BEST, SP>(va, ch, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
+                        }
+                    }
                     else {
                         // 128 columns in four 32-column chunks, the next load in flight while one is reduced
+                        uint32_t vb[32];
                         tmem_ld32(taddr, va);
                         tmem_ld_wait();
                         tmem_ld32(taddr + 32, vb);
@@ -530,6 +570,21 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                     if (p.dbg) { const long long c1 = clock64(); eC += c1 - ec0; ec0 = c1; }
                     const uint32_t rbase = ir.rowBase + (f - f0) * kTileM + q * 32;
                     const uint32_t rows  = min(32u, ir.rowEnd > rbase ? ir.rowEnd - rbase : 0u);
+                    if (VEC && p.directStores == 1) {
+#pragma unroll
+                        for (int i = 0; i < R / 4; ++i)
+                            sts_v4(vWrite + i * 16, __float_as_uint(res[4 * i]), __float_as_uint(res[4 * i + 1]),
+                                   __float_as_uint(res[4 * i + 2]), __float_as_uint(res[4 * i + 3]));
+                        __syncwarp();
+#pragma unroll
+                        for (int ps = 0; ps < 32 / RPP; ++ps)
+                            if (vr0 + ps * RPP < rows)
+                                *reinterpret_cast<uint4*>(gVec + (size_t)ps * RPP * p.ld * 4) = lds_v4(vRead + ps * RPP * PV * 4);
+                        gVec += gTileStep;
+                        __syncwarp();
+                        if (p.dbg) eS += clock64() - ec0;
+                        continue;
+                    }
                     if (DIRECT) {
                         if ((uint32_t)lane < rows) {
                             if (R >= 4) {
@@ -601,11 +656,12 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                 case 8: run(std::integral_constant<int, (SEGS >= 8 ? 8 : 0)>{}); break;
                 default: run(std::integral_constant<int, 0>{}); break;
             }
+            t += f1 - f0;
             // this warp no longer reads slot / meta of the B buffer
             if (lane == 0)
                 mbar_arrive(smem_u32(&emptyB[b]));
         }
-        if (p.dbg && e == 0 && lane == 0) {
+        if (p.dbg && e == 0 && grp == 0 && lane == 0) {
             unsigned long long* d = p.dbg + blockIdx.x * 16;
             d[8] = eW, d[9] = eL, d[10] = eC, d[11] = eS;
         }
@@ -627,6 +683,11 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + 8), 1) tc_score_kernel8(cons
 template<int SWZ, int MODE, bool BEST>
 __global__ void __launch_bounds__(32 * (kEpiWarp0 + 16), 1) tc_score_kernel16(const KParams p) {
     tc_score_body<SWZ, MODE, BEST, 16>(p);
+}
+// two epilogue groups of eight warps (maximum approximation): 576 threads, 96 registers
+template<int SWZ, int MODE, bool BEST>
+__global__ void __launch_bounds__(32 * (kEpiWarp0 + 16), 1) tc_score_kernel8x2(const KParams p) {
+    tc_score_body<SWZ, MODE, BEST, 8, 2>(p);
 }
 __device__ __forceinline__ void split_fp16(float v, __half& hi, __half& lo) {
     v  = fminf(fmaxf(v, -60000.f), 60000.f);
@@ -753,13 +814,20 @@ void host_split(float v, uint16_t& hi, uint16_t& lo) {
     memcpy(&lo, &l, 2);
 }
 
+// NE = 8 / 16: one epilogue group of that many warps; NE = 82: two groups of eight
 template<int SWZ, int MODE, bool BEST, int NE>
 cudaError_t launch_tc(const KParams& p, int grid, size_t smemBytes, cudaStream_t stream) {
-    void (*kernel)(const KParams) = NE == 16 ? tc_score_kernel16<SWZ, MODE, BEST> : tc_score_kernel8<SWZ, MODE, BEST>;
+    void (*kernel)(const KParams) = nullptr;
+    if constexpr (NE == 16)
+        kernel = tc_score_kernel16<SWZ, MODE, BEST>;
+    else if constexpr (NE == 82 && MODE == 0)
+        kernel = tc_score_kernel8x2<SWZ, MODE, BEST>;
+    else
+        kernel = tc_score_kernel8<SWZ, MODE, BEST>;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     if (e != cudaSuccess)
         return e;
-    kernel<<<grid, 32 * (kEpiWarp0 + NE), smemBytes, stream>>>(p);
+    kernel<<<grid, 32 * (kEpiWarp0 + ((NE == 8 || (NE == 82 && MODE != 0)) ? 8 : 16)), smemBytes, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -913,7 +981,7 @@ int gmm_tc_pack(gmm_handle* h, const uint32_t* offsets, const float* mean, const
     }
 
     // ---- shared-memory configuration (sized for the arg-min variant) ----
-    const uint32_t pitch = tm.maxMixPerPart + 1, epiWarps = 4 * partsPerTile;
+    const uint32_t pitch = (tm.maxMixPerPart + 3) / 4 * 4 + 5, epiWarps = 4 * partsPerTile;  // odd, >= R + 4 (vector stores)
     tm.buffersB = 0;
     for (uint32_t nb = 2; nb >= 1 && !tm.buffersB; --nb)
         for (uint32_t sa = kMaxStagesA; sa >= 2; --sa)
@@ -1163,11 +1231,13 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     p.aTileBytes = tm.aTileBytes;
     p.bTileBytes = tm.tileBytes;
     p.buffersB   = tm.buffersB;
-    p.stagePitch = tm.maxMixPerPart + 1;
+    p.stagePitch = (tm.maxMixPerPart + 3) / 4 * 4 + 5;
     p.dbg        = nullptr;
     {
+        // row pieces of uniform tiles: 1 = 128-bit stores through the staging block (default), 2 = every lane writes its own
+        // piece (GMM_TC_STORES=lane), 0 = the general staged scalar path (GMM_TC_STORES=staged)
         const char* e  = getenv("GMM_TC_STORES");
-        p.directStores = (e && !strcmp(e, "staged")) ? 0u : 1u;
+        p.directStores = (e && !strcmp(e, "staged")) ? 0u : (e && !strcmp(e, "lane")) ? 2u : 1u;
     }
     const bool debug = getenv("GMM_TC_DEBUG") != nullptr;
     if (debug) {
@@ -1178,12 +1248,26 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     }
     const uint32_t epiWarps = 4 * (kTileN / tm.partW);
     const bool best = d_best != nullptr;
+    // GMM_TC_GROUPS=2: two eight-warp epilogue groups on alternate tiles.  Measured and left off: with the reduction of one
+    // group always running beside the MMAs the tensor instructions retire slower (issue + commit 694 -> 995 cycles per
+    // tile on the 4501x16 model; 0.385 -> 0.550 ms per 32000 frames), although the same arrangement helps the quantized
+    // kernel, whose tile is not bound by the tensor pipe (gmm_qtc.cu)
+    bool twoGroups = false;
+    if (const char* e = getenv("GMM_TC_GROUPS"))
+        twoGroups = epiWarps == 8 && h->mode != GMM_MODE_SUM && atoi(e) == 2;
+    const uint32_t stageWarps = twoGroups ? 16 : epiWarps;
     // A ring depth: whatever shared memory allows for this variant
     p.stagesA = tm.stagesA;
     while (p.stagesA < (uint32_t)kMaxStagesA &&
-           smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA + 1, p.stagePitch, best, epiWarps) <= kSmemLimit)
+           smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA + 1, p.stagePitch, best, stageWarps) <= kSmemLimit)
         p.stagesA++;
-    const size_t smemBytes = smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best, epiWarps);
+    while (p.stagesA > 2 &&
+           smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best, stageWarps) > kSmemLimit)
+        p.stagesA--;  // the second group's staging blocks may cost an A stage
+    if (twoGroups && smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best, stageWarps) > kSmemLimit)
+        twoGroups = false;
+    const size_t smemBytes = smemNeed(tm.tileBytes, tm.aTileBytes, tm.buffersB, p.stagesA, p.stagePitch, best,
+                                      twoGroups ? 16 : epiWarps);
     // split the frame range so that the items fill the SMs evenly: cost in A-tile MMA times.  Items are handed out
     // round-robin, so the CTAs running together hold ADJACENT B tiles over the same frames and their 16..64-byte row
     // pieces merge into full lines in L2.  (Giving every CTA one contiguous range of the linearised tile space
@@ -1215,9 +1299,9 @@ int tc_run(gmm_handle* h, const TcJob& job) {
                        : launch_tc<SWZ, 1, false, NE>(p, grid, smemBytes, h->stream)))
     h->timeBegin();
     if (tm.swz == 128)
-        e = epiWarps == 16 ? GMM_TC_LAUNCH(128, 16) : GMM_TC_LAUNCH(128, 8);
+        e = epiWarps == 16 ? GMM_TC_LAUNCH(128, 16) : twoGroups ? GMM_TC_LAUNCH(128, 82) : GMM_TC_LAUNCH(128, 8);
     else
-        e = epiWarps == 16 ? GMM_TC_LAUNCH(64, 16) : GMM_TC_LAUNCH(64, 8);
+        e = epiWarps == 16 ? GMM_TC_LAUNCH(64, 16) : twoGroups ? GMM_TC_LAUNCH(64, 82) : GMM_TC_LAUNCH(64, 8);
 #undef GMM_TC_LAUNCH
     h->timeEnd();
     h->launches++;
@@ -1238,9 +1322,9 @@ int tc_run(gmm_handle* h, const TcJob& job) {
                 "last chunk %.0f + stores %.0f\n",
                 eW / tiles, eL / tiles, eC / tiles, eS / tiles);
         fprintf(stderr,
-                "[gmm_tc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u | MMA thread, cycles per tile: "
+                "[gmm_tc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u x %d | MMA thread, cycles per tile: "
                 "total %.0f = wait-ready %.0f + issue+commit %.0f + other (%.0f)\n",
-                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, tot / tiles, wR / tiles, wI / tiles,
+                grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, twoGroups ? 2 : 1, tot / tiles, wR / tiles, wI / tiles,
                 wC / tiles);
     }
     return GMM_OK;

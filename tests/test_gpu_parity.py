@@ -423,10 +423,12 @@ def test_direct_row_piece_stores_equal_staged_stores(eng, oracle, K, ld, monkeyp
         eng.sync()
         return d.cpu().numpy()
 
-    direct = run()
+    direct = run()  # 128-bit stores through the staging block where a lane holds >= 4 results, else lane stores
+    monkeypatch.setenv("GMM_TC_STORES", "lane")
+    lane = run()    # every lane writes its own row piece
     monkeypatch.setenv("GMM_TC_STORES", "staged")
     staged = run()
-    assert np.array_equal(bits(direct), bits(staged))
+    assert np.array_equal(bits(direct), bits(staged)) and np.array_equal(bits(lane), bits(staged))
     assert np.all(direct[:, ms.M:] == -123.0)
     so, _ = oracle.score_max(ms, x)
     assert_float_close(direct[:, :ms.M], so)
