@@ -58,6 +58,7 @@ struct QKParams {
     float           twoScalingSquared;  // f32 path of the final score (OUT & 4): q / (2 s^2), see qtc_launch
     uint32_t        T;
     uint32_t        nTiles, frameTiles, split;
+    uint32_t        swapTile;    // B tile that trades places with the last one (nTiles - 1: none), see qtc_launch
     uint32_t        kSteps;      // 32-byte k-steps of the contraction (the B image holds one more: the variant)
     uint32_t        atoms;       // 64-byte swizzle atoms per A operand row
     uint32_t        atomsB;      // ... per B operand row (k-steps 0 .. kSteps, the last being the variant)
@@ -281,7 +282,8 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
         if (lane == 0) {
             uint32_t itemCount = 0, t = 0, stage = 0;
             for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
-                const uint32_t nt = item / p.split, chunk = item % p.split;
+                const uint32_t nt0 = item / p.split, chunk = item % p.split;
+                const uint32_t nt  = nt0 == p.nTiles - 1 ? p.swapTile : nt0 == p.swapTile ? p.nTiles - 1 : nt0;
                 const uint32_t f0 = chunk * tilesPerItem, f1 = min(p.frameTiles, f0 + tilesPerItem);
                 if (f0 >= f1)
                     continue;
@@ -359,7 +361,9 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + NE * NG), 1) qtc_score_kerne
             unsigned long long* d = p.dbg + blockIdx.x * 128;
             unsigned long long gt1;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt1));
-            d[0] = clock64() - mStart, d[1] = mW, d[2] = mI, d[4] = t, d[5] = gt0, d[6] = gt1;
+            uint32_t smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            d[0] = clock64() - mStart, d[1] = mW, d[2] = mI, d[4] = t, d[5] = gt0, d[6] = gt1, d[7] = smid;
         }
     }
     else {
@@ -940,6 +944,12 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
         bestS = std::max(1u, std::min<uint32_t>(FT, (uint32_t)atoi(e)));
     p.split        = bestS;
     const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount, (uint64_t)tm.nTiles * bestS);
+    // The last B tile is usually a partial one (pad columns: the ragged epilogue path, 1.2x the time of the others on the
+    // 4501x16 model, where it made CTA 133 finish 20 us after everybody else at 8000 frames).  With whole frame ranges per
+    // item it trades places with a first-round tile of a CTA that has one item fewer.
+    p.swapTile = tm.nTiles - 1;
+    if (bestS == 1 && tm.nTiles > (uint32_t)grid && tm.nTiles % grid != 0)
+        p.swapTile = grid - 1;
     // Output set fixed at compile time for the combinations callers use (tests / bench: q + arg-min; the RASR plugin:
     // score, or score + arg-min; everything).  The final score there is ONE f32 division q / (2 s^2): for |q| < 2^24 the
     // integer is exact in f32 and the correctly rounded f32 quotient equals the reference's f32(0.5 * q / s^2) evaluated
@@ -1003,6 +1013,18 @@ static int qtc_launch(gmm_handle* h, uint32_t T, const float* d_x, int32_t* d_q,
                 dmin[k] = std::min(dmin[k], dur), dmax[k] = std::max(dmax[k], dur), dsum[k] += dur, n[k]++;
                 smax = std::max(smax, (double)(d[c * 128 + 5] - g0) * 1e-3);
                 emin = std::min(emin, (double)(d[c * 128 + 6] - g0) * 1e-3);
+            }
+            std::vector<int> order(grid);
+            for (int c = 0; c < grid; ++c)
+                order[c] = c;
+            std::sort(order.begin(), order.end(), [&](int a, int b) {
+                return d[a * 128 + 6] - d[a * 128 + 5] > d[b * 128 + 6] - d[b * 128 + 5];
+            });
+            for (int i = 0; i < std::min(grid, 6); ++i) {
+                const int c = order[i];
+                fprintf(stderr, "[gmm_qtc]   slowest %d: CTA %d on SM %llu, %llu tiles, %.1f us, wait-ready %.0f issue %.0f per tile\n", i, c,
+                        d[c * 128 + 7], d[c * 128 + 4], (double)(d[c * 128 + 6] - d[c * 128 + 5]) * 1e-3,
+                        (double)d[c * 128 + 1] / std::max<double>(1, d[c * 128 + 4]), (double)d[c * 128 + 2] / std::max<double>(1, d[c * 128 + 4]));
             }
             fprintf(stderr, "[gmm_qtc]   %d CTAs with %llu tiles: loop %.1f / %.1f / %.1f us (min / mean / max); %d CTAs with fewer: "
                     "%.1f / %.1f / %.1f us; latest start +%.1f us, earliest end +%.1f us\n",

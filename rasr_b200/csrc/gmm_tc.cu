@@ -61,6 +61,7 @@ struct KParams {
     size_t         ld;
     uint32_t       T;
     uint32_t       nTiles, frameTiles, split;  // items = nTiles * split
+    uint32_t       swapTile;                   // B tile that trades places with the last one (nTiles - 1: none), see launch
     uint32_t       kSteps;                     // k-steps (16 elements) per precision part
     uint32_t       fp8;                        // part 2 holds e4m3 corrections (TensorModel::fp8)
     uint32_t       atoms;                      // swizzle atoms per operand row
@@ -252,6 +253,7 @@ __device__ __forceinline__ ItemRange item_range(const KParams& p, uint32_t item,
     else {
         const uint32_t chunk = item % p.split;
         r.nt      = item / p.split;
+        r.nt      = r.nt == p.nTiles - 1 ? p.swapTile : r.nt == p.swapTile ? p.nTiles - 1 : r.nt;
         r.f0      = chunk * tilesPerItem;
         r.f1      = min(p.frameTiles, r.f0 + tilesPerItem);
         r.rowBase = r.f0 * kTileM;
@@ -1290,6 +1292,12 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     p.split        = bestS;
     const int grid = (int)std::min<uint64_t>((uint64_t)h->smCount,
                                              job.itemTab ? (uint64_t)job.nItems : (uint64_t)job.nTiles * bestS);
+    // The model's last B tile is usually a partial one (pad columns: the ragged, slower epilogue path).  With whole frame
+    // ranges per item (split 1) it would be the LAST item of a CTA that already has the most items; it trades places
+    // with a first-round tile of a CTA that has one item fewer.
+    p.swapTile = job.nTiles - 1;
+    if (!job.itemTab && bestS == 1 && job.nTiles > (uint32_t)grid && job.nTiles % grid != 0)
+        p.swapTile = grid - 1;
     cudaError_t e;
     const int   mode = h->mode == GMM_MODE_SUM ? 1 : 0;
 #define GMM_TC_LAUNCH(SWZ, NE)                                                                               \
