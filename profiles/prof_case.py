@@ -14,17 +14,19 @@ dx = torch.from_numpy(x).cuda()
 if mode == "quant":
     t = tables.quant_tables(ms)
     eng.upload_quant(t["offsets"], t["qmean"], t["cov_idx"], t["qconst"], t["isr_scaled"], t["scaling_squared"])
-    q = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
-    b = torch.empty((T, ms.M), dtype=torch.int32, device="cuda")
+    ld = (ms.M + 3) // 4 * 4  # rows padded to 16 bytes, as bench.py
+    q = torch.empty((T, ld), dtype=torch.int32, device="cuda")
+    b = torch.empty((T, ld), dtype=torch.int32, device="cuda")
     for _ in range(n):
-        eng.quant_score_device(T, dx, q, b)
+        eng.quant_score_device(T, dx, q, b, ld=ld)
 else:
     t = tables.float_tables(ms)
     eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"],
                      mode=capi.MODE_SUM if mode == "sum" else capi.MODE_MAX, kernel=capi.KERNEL_AUTO)
-    s = torch.empty((T, ms.M), dtype=torch.float32, device="cuda")
+    ld = (ms.M + 3) // 4 * 4
+    s = torch.empty((T, ld), dtype=torch.float32, device="cuda")
     for _ in range(n):
-        eng.score_device(T, dx, s)
+        eng.score_device(T, dx, s, None, ld=ld)
 eng.sync()
 torch.cuda.synchronize()
 print("ok", cfg, mode, T, "kernel", eng.float_kernel if mode != "quant" else "quant")

@@ -213,10 +213,21 @@ __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, 
         for (int s = 0; s < SP; ++s) {
             const int live = (int)((liveBits >> ((seg0 + m0 + s) * 4)) & 15ull) + 1;  // uniform
             if (__any_sync(0xffffffffu, !((segMin[s] - best) * rs >= 40.f))) {
+                if (live == 8) {
+                    // a full segment (the common case): eight independent fma -> ex2 pairs and an add tree -- no
+                    // per-element predicate, no serial chain of adds behind the special-function unit's latency
+                    float e[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    if (j < live)  // (best - u) * hl2e as one fused multiply-add: the epilogue is issue-bound
-                        sum += ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
+                    for (int j = 0; j < 8; ++j)  // (best - u) * hl2e as one fused multiply-add
+                        e[j] = ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
+                    sum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
+                }
+                else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (j < live)
+                            sum += ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
+                }
             }
         }
         const float b2 = fminf(best * rs, FLT_MAX);
