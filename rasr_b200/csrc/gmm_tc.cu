@@ -188,6 +188,9 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
 // Measured and dropped: moving a share of the exponentials from the special-function unit to a polynomial on the FMA
 // pipe (12001x64 model, 10000 frames: 2.91 ms with none, 3.83 / 4.88 / 5.93 ms with 2 / 4 / 6 of 8) -- the epilogue is
 // bound by instruction issue, not by the 16 exp2 per clock of the SFU.
+// Also measured and dropped (round 2): a branch for full segments with eight unpredicated fma -> ex2 pairs and an add
+// tree instead of the predicated serial chain below -- 3.53 -> 4.16 ms (eight more live registers at the 96 the
+// 16-warp kernel has).
 // get(i) = accumulator value i of the part (compile-time i), N = columns of the part held in registers.
 template<bool BEST, int SP, int NSEG, typename Get>
 __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, const uint16_t* __restrict__ slots,
@@ -213,21 +216,10 @@ __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, 
         for (int s = 0; s < SP; ++s) {
             const int live = (int)((liveBits >> ((seg0 + m0 + s) * 4)) & 15ull) + 1;  // uniform
             if (__any_sync(0xffffffffu, !((segMin[s] - best) * rs >= 40.f))) {
-                if (live == 8) {
-                    // a full segment (the common case): eight independent fma -> ex2 pairs and an add tree -- no
-                    // per-element predicate, no serial chain of adds behind the special-function unit's latency
-                    float e[8];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)  // (best - u) * hl2e as one fused multiply-add
-                        e[j] = ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
-                    sum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
-                }
-                else {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (j < live)
-                            sum += ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
-                }
+                for (int j = 0; j < 8; ++j)
+                    if (j < live)  // (best - u) * hl2e as one fused multiply-add: the epilogue is issue-bound
+                        sum += ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
             }
         }
         const float b2 = fminf(best * rs, FLT_MAX);
