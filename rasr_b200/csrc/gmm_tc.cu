@@ -191,6 +191,8 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
 // Also measured and dropped (round 2): a branch for full segments with eight unpredicated fma -> ex2 pairs and an add
 // tree instead of the predicated serial chain below -- 3.53 -> 4.16 ms (eight more live registers at the 96 the
 // 16-warp kernel has).
+// The same tree with EIGHT epilogue warps (168 registers, the part's 128 columns as two 64-column halves): 4.54 ms -- two
+// warps per scheduler do not cover the special-function latency, sixteen do.
 // get(i) = accumulator value i of the part (compile-time i), N = columns of the part held in registers.
 template<bool BEST, int SP, int NSEG, typename Get>
 __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, const uint16_t* __restrict__ slots,
@@ -363,14 +365,18 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
         const uint32_t     kS       = p.kSteps;
         uint32_t  itemCount = 0, t = 0, stage = 0;
         bool      have = false;  // ready[t % kRing] was already seen complete (probed while tile t - 1 was being issued)
-        long long tStart = clock64(), wR = 0, wI = 0, t0 = 0;
+        long long tStart = clock64(), wR = 0, wI = 0, t0 = 0, wB = 0;
+        unsigned long long gt0 = 0;
+        if (p.dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
         for (uint32_t item = blockIdx.x; item < items; item += gridDim.x, ++itemCount) {
             const ItemRange ir = item_range(p, item, tilesPerItem);
             const uint32_t  f0 = ir.f0, f1 = ir.f1;
             if (f0 >= f1)
                 continue;
             const uint32_t b = itemCount % p.buffersB, useB = itemCount / p.buffersB;
+            if (p.dbg) t0 = clock64();
             mbar_wait(smem_u32(&fullB[b]), useB & 1);
+            if (p.dbg) wB += clock64() - t0;
             const uint32_t bLo = (smem_u32(sB + (size_t)b * bBytes) & 0x3FFFF) >> 4;
             for (uint32_t f = f0; f < f1; ++f, ++t) {
                 if (p.dbg) t0 = clock64();
@@ -428,7 +434,9 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
         }
         if (p.dbg && leader) {
             unsigned long long* d = p.dbg + blockIdx.x * 16;
-            d[0] = clock64() - tStart, d[1] = wR, d[2] = wI, d[3] = 0, d[4] = t, d[5] = itemCount;
+            unsigned long long gt1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt1));
+            d[0] = clock64() - tStart, d[1] = wR, d[2] = wI, d[3] = wB, d[4] = t, d[5] = itemCount, d[6] = gt0, d[7] = gt1;
         }
     }
     else {
@@ -1328,13 +1336,25 @@ int tc_run(gmm_handle* h, const TcJob& job) {
             eW += d[c * 16 + 8], eL += d[c * 16 + 9], eC += d[c * 16 + 10], eS += d[c * 16 + 11];
         }
         tiles = std::max(1.0, tiles);
+        {
+            unsigned long long g0 = ~0ull, g1 = 0;
+            double dmin = 1e30, dmax = 0, dsum = 0, ns = 0;
+            for (int c = 0; c < grid; ++c) {
+                g0 = std::min(g0, d[c * 16 + 6]), g1 = std::max(g1, d[c * 16 + 7]);
+                const double dur = (double)(d[c * 16 + 7] - d[c * 16 + 6]) * 1e-3;
+                dmin = std::min(dmin, dur), dmax = std::max(dmax, dur), dsum += dur, ns += dur * 1e3;
+            }
+            fprintf(stderr, "[gmm_tc] MMA loops: %.1f us first start to last end; per CTA %.1f / %.1f / %.1f us (min / mean / max); "
+                    "SM clock %.0f MHz (cycles / globaltimer)\n",
+                    (double)(g1 - g0) * 1e-3, dmin, dsum / grid, dmax, ns > 0 ? tot / ns * 1e3 : 0.0);
+        }
         fprintf(stderr,
                 "[gmm_tc] epilogue warp 0, cycles per tile: wait-for-MMA %.0f + TMEM drain (loads, first three chunks) %.0f + "
                 "last chunk %.0f + stores %.0f\n",
                 eW / tiles, eL / tiles, eC / tiles, eS / tiles);
         fprintf(stderr,
                 "[gmm_tc] grid %d split %u stagesA %u buffersB %u kSteps %u epiWarps %u x %d | MMA thread, cycles per tile: "
-                "total %.0f = wait-ready %.0f + issue+commit %.0f + other (%.0f)\n",
+                "total %.0f = wait-ready %.0f + issue+commit %.0f + wait for the B tile %.0f\n",
                 grid, p.split, p.stagesA, p.buffersB, p.kSteps, epiWarps, twoGroups ? 2 : 1, tot / tiles, wR / tiles, wI / tiles,
                 wC / tiles);
     }

@@ -61,6 +61,23 @@ class ContextScorer:
             raise ValueError("scorer was created without density assignment (assigning=False)")
         return int(b[self._row, e])
 
+    def scoreOfDensity(self, e: int, dns_in_mix: int) -> float:
+        """score(e, dnsInMix) (AssigningFeatureScorer.hh:46,122-134): a criticalError in both reference diagonal scorers
+        (neither overrides calculateScore(cs, e, dns)), a ValueError here, as in the C++ plugin."""
+        raise ValueError("This feature scorer does not support the calculation of scores given a density in the mixture")
+
+    def getDensityPosteriorProbabilities(self, e: int) -> np.ndarray:
+        """Density posteriors exp(score - s_k) of the sum scorer (GaussDiagonalMaximumFeatureScorer.cc:291-298, consumer
+        AbstractMixtureSetEstimator.cc:386-395); the other scorers answer like the reference (criticalError)."""
+        assert 0 <= e < self._parent.nMixtures()
+        if self._parent._type != "diagonal-sum":
+            raise ValueError("This feature scorer does not support the calculation of density posterior probabilities")
+        self._resolve()
+        k = self._parent.densitiesInMixture(e)
+        widest = int(np.max(np.diff(self._parent._offsets)))  # the call's row pitch covers the model's largest mixture
+        post, _ = self._parent._engine.mixture_posteriors_host(self._frame[None, :], np.array([e], np.uint32), max(1, widest))
+        return post[0, :k]
+
     def scores(self) -> np.ndarray:
         """All M scores of this frame (eager consumers, Speech/FeatureScorerNode.cc:95-155)."""
         return self._resolve().scores[self._row, : self._parent.nMixtures()]
@@ -192,8 +209,9 @@ class GpuFeatureScorer:
         x = np.stack([c._frame for c in self._pending])
         scores, best = self.scoreBatch(x)
         block = _ScoreBlock(scores, best)
+        keep = self._type == "diagonal-sum"  # its contexts answer density posteriors from the frame later
         for i, c in enumerate(self._pending):
-            c._block, c._row, c._frame = block, i, None
+            c._block, c._row, c._frame = block, i, (c._frame if keep else None)
         self._pending = []
         self.n_batches += 1
 

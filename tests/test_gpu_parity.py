@@ -98,6 +98,29 @@ def test_golden_batch_int_bit_exact(eng, oracle, name):
     assert np.array_equal(r["q"], q) and np.array_equal(r["best"], best)
 
 
+def test_density_posteriors_through_the_host_mirror(oracle):
+    """getDensityPosteriorProbabilities of a sum scorer's context (the plugin's binding, AssigningFeatureScorer.hh:47)
+    against the oracle's posteriors; the maximum scorer refuses like the reference."""
+    ms = synth.make_model(M=40, K=9, D=21, seed=31, ragged=True)
+    x = synth.make_features(ms, 12, seed=2)
+    fs = feature_scorer.GpuFeatureScorer(ms, "diagonal-sum", float_tables=oracle_float_tables(ms))
+    fs.reset()
+    for f in x:
+        fs.addFeature(f)
+    ctx = [fs.flush() for _ in range(len(x))]
+    _, _, post = oracle.score_sum(ms, x, posterior=True)
+    for t in (0, 5, 11):
+        for e in (0, 7, 39):
+            a, b = ms.mix_offsets[e], ms.mix_offsets[e + 1]
+            np.testing.assert_allclose(ctx[t].getDensityPosteriorProbabilities(e), post[t, a:b], rtol=1e-4, atol=1e-7)
+    assert fs.n_batches == 1
+    with pytest.raises(ValueError, match="density in the mixture"):
+        ctx[0].scoreOfDensity(0, 0)
+    fm = feature_scorer.GpuFeatureScorer(ms, "diagonal-maximum")
+    with pytest.raises(ValueError, match="posterior"):
+        fm.getScorer(x[0]).getDensityPosteriorProbabilities(0)
+
+
 def test_batch_int_scorer_type_of_the_host_mirror(oracle):
     """feature-scorer-type = batch-diagonal-maximum-int through the buffered interface, at a size where the tensor
     kernel runs: equal to the oracle's restatement of the reference scorer."""
