@@ -161,7 +161,8 @@ void GpuFeatureScorer::Context::getDensityPosteriorProbabilities(Mm::EmissionInd
 
 // ---- construction: pack the mixture set --------------------------------------------------------------------
 
-GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> mixtureSet, Kind kind)
+GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> mixtureSet, Kind kind,
+                                   u32 restrictions)
         : Core::Component(c),
           Precursor(c),
           kind_(kind),
@@ -175,6 +176,10 @@ GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const
           maxDensities_(0),
           nBatches_(0),
           nAssignmentPasses_(0) {
+    if ((restrictions & pooledCovarianceOnly) && mixtureSet->nCovariances() != 1)
+        criticalError("feature scorer supports only globally pooled covariance");  // as BatchFeatureScorer.cc:146-148
+    if ((restrictions & atMost48PaddedComponents) && ((dimension_ + 15) / 16) * 16 > 48)
+        criticalError("This feature scorer supports only features with max. %d components", 48);  // as :550-553
     if (gmm_create(&handle_, paramDevice(config)) != GMM_OK)
         criticalError("cannot create the GPU scoring engine: %s", gmm_last_error(0));
     // flat (mixture, density) slots, as BatchFeatureScorerBase::initialize (BatchFeatureScorer.cc:62-75)

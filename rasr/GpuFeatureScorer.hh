@@ -1,12 +1,14 @@
 /** RASR-side plugin: GPU GMM feature scorers behind Mm::FeatureScorerFactory.
  *
  *  Compiled INTO RASR (module MODULE_MM_GPU, see rasr/Module.hh and INTEGRATION.md); binds only to the C-ABI of
- *  include/gmm_b200.h (libgmm_b200.so, hand-written CUDA for sm_100a).  Four scorers, drop-in for
+ *  include/gmm_b200.h (libgmm_b200.so, hand-written CUDA for sm_100a).  Six names, drop-in for
  *
  *    gpu-diagonal-maximum        Mm::GaussDiagonalMaximumFeatureScorer      (src/Mm/GaussDiagonalMaximumFeatureScorer.hh:31-92)
  *    gpu-diagonal-sum            Mm::GaussDiagonalSumFeatureScorer          (src/Mm/GaussDiagonalMaximumFeatureScorer.hh:96-115)
  *    gpu-SIMD-diagonal-maximum   Mm::SimdGaussDiagonalMaximumFeatureScorer  (src/Mm/SimdFeatureScorer.hh:35-139)
  *    gpu-batch-diagonal-maximum-int  Mm::BatchIntFeatureScorer              (src/Mm/BatchFeatureScorer.hh:292-340)
+ *    gpu-batch-diagonal-maximum-fast   Mm::BatchUnrolledIntFeatureScorer    (src/Mm/BatchFeatureScorer.hh:362-375)
+ *    gpu-batch-diagonal-maximum-float  Mm::BatchFloatFeatureScorer          (src/Mm/BatchFeatureScorer.hh:226-290)
  *
  *  They implement the buffered protocol of Mm::FeatureScorer (src/Mm/FeatureScorer.hh:86-134) so that
  *  Speech::OfflineRecognizer / DelayedRecognizer / AlignmentNode / FeatureScorerNode and Flf's recognizer feed
@@ -99,7 +101,9 @@ protected:
     friend class Context;
 
 public:
-    GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> mixtureSet, Kind kind);
+    /** restrictions the reference's batch scorers put on the model (criticalError otherwise, as they do) */
+    enum { pooledCovarianceOnly = 1, atMost48PaddedComponents = 2 };
+    GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> mixtureSet, Kind kind, u32 restrictions = 0);
     virtual ~GpuFeatureScorer();
 
     virtual Mm::EmissionIndex nMixtures() const {
@@ -208,6 +212,24 @@ class GpuBatchIntFeatureScorer : public GpuFeatureScorer {
 public:
     GpuBatchIntFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> m)
             : Core::Component(c), GpuFeatureScorer(c, m, kindBatchInt) {}
+};
+
+/** Mm::BatchUnrolledIntFeatureScorer (`batch-diagonal-maximum-fast`, BatchFeatureScorer.cc:537-604): the numbers of the
+ *  batch-int scorer (same init) from a loop unrolled for at most 48 padded components -- the same restriction here. */
+class GpuBatchUnrolledIntFeatureScorer : public GpuFeatureScorer {
+public:
+    GpuBatchUnrolledIntFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> m)
+            : Core::Component(c), GpuFeatureScorer(c, m, kindBatchInt, atMost48PaddedComponents) {}
+};
+
+/** Mm::BatchFloatFeatureScorer (`batch-diagonal-maximum-float`, BatchFeatureScorer.cc:138-234): 0.5 min_k(L - 2 logw +
+ *  |mu isr - x isr|^2) over whitened operands, pooled covariance only -- the float maximum scorer (whose tensor kernel
+ *  contracts the same whitened operands) within the float tolerance; weight / gaussian scales are not applied there
+ *  and must be left at 1 here. */
+class GpuBatchFloatFeatureScorer : public GpuFeatureScorer {
+public:
+    GpuBatchFloatFeatureScorer(const Core::Configuration& c, Core::Ref<const Mm::MixtureSet> m)
+            : Core::Component(c), GpuFeatureScorer(c, m, kindMaximum, pooledCovarianceOnly) {}
 };
 
 }  // namespace MmGpu

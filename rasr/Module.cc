@@ -19,4 +19,8 @@ Module_::Module_() {
             gpuSimdDiagonalMaximum, "gpu-SIMD-diagonal-maximum");
     factory->registerFeatureScorer<GpuBatchIntFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(
             gpuBatchIntDiagonalMaximum, "gpu-batch-diagonal-maximum-int");
+    factory->registerFeatureScorer<GpuBatchUnrolledIntFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(
+            gpuBatchIntDiagonalMaximumFast, "gpu-batch-diagonal-maximum-fast");
+    factory->registerFeatureScorer<GpuBatchFloatFeatureScorer, Mm::MixtureSet, Mm::AbstractMixtureSetLoader>(
+            gpuBatchFloatDiagonalMaximum, "gpu-batch-diagonal-maximum-float");
 }

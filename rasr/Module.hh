@@ -19,6 +19,8 @@ public:
         gpuDiagonalSum         = FeatureScorerTypeOffset + 1,
         gpuSimdDiagonalMaximum = FeatureScorerTypeOffset + 2,
         gpuBatchIntDiagonalMaximum = FeatureScorerTypeOffset + 3,
+        gpuBatchIntDiagonalMaximumFast = FeatureScorerTypeOffset + 4,
+        gpuBatchFloatDiagonalMaximum   = FeatureScorerTypeOffset + 5,
     };
 };
 

@@ -263,7 +263,7 @@ public:
         MmGpu::Module::instance();
         const Mm::Module_& mm = Mm::Module::instance();
 
-        // ---- 1-5: every scorer pair through factory + scaling wrapper + the AlignmentNode loop ----------------------
+        // ---- 1-7: every scorer pair through factory + scaling wrapper + the AlignmentNode loop ----------------------
         struct Case {
             const char *name, *refType, *gpuType;
             int         kernel;
@@ -273,10 +273,12 @@ public:
                      {"diagonal-sum / auto kernel", 0, "gpu-diagonal-sum", 0, false, false},
                      {"SIMD-diagonal-maximum", "SIMD-diagonal-maximum", "gpu-SIMD-diagonal-maximum", 0, true, false},
                      // the reference's scorer is a plain buffered FeatureScorer without a density assignment
-                     {"batch-diagonal-maximum-int", "batch-diagonal-maximum-int", "gpu-batch-diagonal-maximum-int", 0, true, true}};
+                     {"batch-diagonal-maximum-int", "batch-diagonal-maximum-int", "gpu-batch-diagonal-maximum-int", 0, true, true},
+                     {"batch-diagonal-maximum-fast", "batch-diagonal-maximum-fast", "gpu-batch-diagonal-maximum-fast", 0, true, true},
+                     {"batch-diagonal-maximum-float", "batch-diagonal-maximum-float", "gpu-batch-diagonal-maximum-float", 0, false, true}};
         for (size_t ci = 0; ci < sizeof(cases) / sizeof(cases[0]); ++ci) {
             const Case&                  k = cases[ci];
-            if (k.pooledOnly && ms->nCovariances() != 1) {
+            if (k.pooledOnly && (ms->nCovariances() != 1 || (ci == 5 && D > 48))) {
                 printf("%-44s SKIP  needs a globally pooled variance (criticalError in both, BatchFeatureScorer.cc:340-342)\n", k.name);
                 continue;
             }

@@ -91,13 +91,19 @@ class GpuFeatureScorer:
     ``SIMD-diagonal-maximum``  u8 quantized, bit-exact integer path (SimdGaussDiagonalMaximumFeatureScorer)
     ``batch-diagonal-maximum-int``  the same u8 kernel with the constants and the final scale of
                                BatchIntFeatureScorer (BatchFeatureScorer.cc:319-376,468); pooled covariance only
+    ``batch-diagonal-maximum-fast`` BatchUnrolledIntFeatureScorer (:537-604): the batch-int numbers, at most 48 padded
+                               components
+    ``batch-diagonal-maximum-float`` BatchFloatFeatureScorer (:138-234): the float maximum scorer over whitened
+                               operands, pooled covariance only (within the float tolerance)
 
     ``buffer_size`` mirrors the reference's ``buffer-size`` parameter; 0 selects segment mode (the buffer
     never reports filled, everything is scored in one launch when the first score is requested).
     """
 
-    SCORER_TYPES = ("diagonal-maximum", "diagonal-sum", "SIMD-diagonal-maximum", "batch-diagonal-maximum-int")
-    QUANTIZED_TYPES = ("SIMD-diagonal-maximum", "batch-diagonal-maximum-int")
+    SCORER_TYPES = ("diagonal-maximum", "diagonal-sum", "SIMD-diagonal-maximum", "batch-diagonal-maximum-int",
+                    "batch-diagonal-maximum-fast", "batch-diagonal-maximum-float")
+    QUANTIZED_TYPES = ("SIMD-diagonal-maximum", "batch-diagonal-maximum-int", "batch-diagonal-maximum-fast")
+    BATCH_INT_TYPES = ("batch-diagonal-maximum-int", "batch-diagonal-maximum-fast")
 
     def __init__(self, mixture_set: MixtureSetData, scorer_type: str = "diagonal-maximum", *, buffer_size: int = 0,
                  device: int = 0, assigning: bool = True, kernel: int = capi.KERNEL_AUTO,
@@ -107,6 +113,12 @@ class GpuFeatureScorer:
             raise ValueError(f"unknown feature-scorer-type '{scorer_type}'")  # Module.cc:303-307
         if buffer_size < 0:
             raise ValueError("buffer-size must be >= 0")
+        if scorer_type == "batch-diagonal-maximum-float":
+            if mixture_set.n_cov != 1:
+                raise ValueError("feature scorer supports only globally pooled covariance")  # BatchFeatureScorer.cc:146-148
+            scorer_type = "diagonal-maximum"
+        if scorer_type == "batch-diagonal-maximum-fast" and tables.simd_padded_dimension(mixture_set.D) > 48:
+            raise ValueError("This feature scorer supports only features with max. 48 components")  # :550-553
         self._type = scorer_type
         self._M, self._D = mixture_set.M, mixture_set.D
         self._offsets = mixture_set.mix_offsets.copy()
@@ -122,7 +134,7 @@ class GpuFeatureScorer:
                 t = tables.batchint_tables(mixture_set)
             self._engine.upload_quant(t["offsets"], t["qmean"], t["cov_idx"], t["qconst"], t["isr_scaled"],
                                       t["scaling_squared"],
-                                      rule=capi.QUANT_RULE_BATCH_INT if scorer_type == "batch-diagonal-maximum-int"
+                                      rule=capi.QUANT_RULE_BATCH_INT if scorer_type in self.BATCH_INT_TYPES
                                       else capi.QUANT_RULE_SIMD)
             self.scaling_squared = np.float32(t["scaling_squared"])
         else:

@@ -32,9 +32,9 @@ def test_plugin_matches_reference_scorers_in_process(tmp_path, kw, T, buffer_siz
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     print(r.stdout)
     assert r.returncode == 0, r.stdout[-3000:]
-    # 5 scorer pairs (the batch-int pair needs a pooled covariance), delayed-recognizer loop, time-indexed scorers,
+    # 7 scorer pairs (the three batch scorers need a pooled covariance), delayed-recognizer loop, time-indexed scorers,
     # density posteriors, with-density-assignment
-    assert r.stdout.count("PASS") == (8 if kw.get("covariance") else 9) and "FAIL" not in r.stdout
+    assert r.stdout.count("PASS") == (8 if kw.get("covariance") else 11) and "FAIL" not in r.stdout
 
 
 @pytest.mark.skipif(not os.path.exists(CHECK), reason="oracle/_ref/rasr_gpu_check not built (needs /root/reference)")
@@ -55,4 +55,4 @@ def test_plugin_path_is_within_20_percent_of_the_call_it_wraps(tmp_path):
     assert len(timing) == 1
     ratio = float(timing[0].split("ratio=")[1])
     assert ratio >= 0.8, timing[0]
-    assert r.stdout.count("PASS") == 10 and "FAIL" not in r.stdout
+    assert r.stdout.count("PASS") == 12 and "FAIL" not in r.stdout
