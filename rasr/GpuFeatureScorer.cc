@@ -173,6 +173,7 @@ GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const
           nMixtures_(mixtureSet->nMixtures()),
           dimension_(mixtureSet->dimension()),
           nDensities_(0),
+          nModelDensities_(mixtureSet->nDensities()),
           maxDensities_(0),
           nBatches_(0),
           nAssignmentPasses_(0) {
@@ -190,6 +191,14 @@ GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const
         maxDensities_ = std::max<u32>(maxDensities_, mixtureSet->mixture(m)->nDensities());
     }
     offsets_[nMixtures_] = nDensities_;
+    // mixture elements as GaussDiagonalMaximumFeatureScorer::init keeps them (.cc:72-79): weights scaled for the float
+    // scorers, as they are for the quantized ones
+    mixtureTable_.resize(nMixtures_);
+    for (Mm::MixtureIndex m = 0; m < nMixtures_; ++m) {
+        mixtureTable_[m] = *mixtureSet->mixture(m);
+        if (!quantized())
+            mixtureTable_[m].scale(paramMixtureWeightScale(config));
+    }
     if (kind_ == kindQuantized)
         initQuantized(*mixtureSet);
     else if (kind_ == kindBatchInt)

@@ -26,6 +26,7 @@
 #include <Core/Parameter.hh>
 #include <Core/ReferenceCounting.hh>
 #include <Mm/AssigningFeatureScorer.hh>
+#include <Mm/MixtureFeatureScorerElement.hh>
 #include <Mm/MixtureSet.hh>
 
 struct gmm_handle;
@@ -112,8 +113,16 @@ public:
     virtual Mm::ComponentIndex dimension() const {
         return dimension_;
     }
+    /** the training consumers' view of the model, as GaussDiagonalMaximumFeatureScorer.hh:79-87 answers it
+     *  (wrapped e.g. by Mm::StatePosteriorFeatureScorer, StatePosteriorFeatureScorer.hh:205-236) */
     virtual Mm::DensityIndex nDensities() const {
-        return nDensities_;
+        return nModelDensities_;
+    }
+    virtual const Mm::MixtureFeatureScorerElement& mixture(Mm::MixtureIndex m) const {
+        return mixtureTable_[m];
+    }
+    virtual const std::vector<Mm::DensityIndex>& densitiesInMixture(Mm::MixtureIndex m) const {
+        return mixtureTable_[m].densityIndices();
     }
 
     using Precursor::getAssigningScorer;
@@ -178,7 +187,9 @@ private:
     Core::Ref<PinnedPool> pool_;
     Mm::EmissionIndex  nMixtures_;
     Mm::ComponentIndex dimension_;
-    Mm::DensityIndex   nDensities_;
+    Mm::DensityIndex   nDensities_;       // (mixture, density) slots = columns of the kernels
+    Mm::DensityIndex   nModelDensities_;  // distinct densities of the mixture set (shared ones once)
+    std::vector<Mm::MixtureFeatureScorerElement> mixtureTable_;
     u32                maxDensities_;  // most densities in one mixture
     std::vector<u32>   offsets_;
 

@@ -381,6 +381,22 @@ public:
                    n, worst, sizeBad);
         }
 
+        // ---- the model accessors of the assigning interface (GaussDiagonalMaximumFeatureScorer.hh:79-87) -----------------
+        {
+            Core::Configuration                   rc  = scorerConfig("ref", "diagonal-maximum", 0, 0);
+            Core::Configuration                   gc  = scorerConfig("gpu", "gpu-diagonal-maximum", 0, 0);
+            Core::Ref<Mm::AssigningFeatureScorer> ref = mm.createAssigningFeatureScorer(rc, ms);
+            Core::Ref<Mm::AssigningFeatureScorer> gpu = mm.createAssigningFeatureScorer(gc, ms);
+            size_t bad = (ref->nDensities() != gpu->nDensities()) + (ref->dimension() != gpu->dimension()) +
+                         (ref->nMixtures() != gpu->nMixtures());
+            for (u32 m = 0; m < M; ++m) {
+                bad += ref->densitiesInMixture(m) != gpu->densitiesInMixture(m);
+                bad += ref->mixture(m).minus2LogWeights() != gpu->mixture(m).minus2LogWeights();
+            }
+            report("nDensities / mixture(m) / densitiesInMixture(m)", bad == 0, "mismatches=%zu densities=%u", bad,
+                   u32(gpu->nDensities()));
+        }
+
         // ---- 8: with-density-assignment: score AND bestDensity of buffered frames from ONE pass -----------------------
         {
             u32    passes[2], batches[2];
