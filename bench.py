@@ -571,7 +571,7 @@ def cfg5_mixture_sharded(torch, dist, rank, world, local, stream, steps=10):
                 "all_gather_bus_GBps": (world - 1) * T * mp * 4 / max(1e-9, (ms_ag - ms_k) * 1e-3) / 1e9,
                 "exchange_bytes_sent_per_rank": (world - 1) * T * mp * 4}
         best_ms, best_chunks, same_all = 1e30, 0, True
-        for chunks in (2, 4):
+        for chunks in ((2, 4) if T < 4096 else (4, 8)):  # long calls: more, shorter frame ranges (profiles/sweep_push_n4_r02.txt)
             ps = sharded.PushMixtureShardedScorer(tab, rank, world, dist, local, max_frames=T, chunks=chunks,
                                                   total_mixtures=M)
             ps.engine.set_stream(stream.cuda_stream)
