@@ -587,6 +587,31 @@ def cfg5_mixture_sharded(torch, dist, rank, world, local, stream, steps=10):
             if ms_p < best_ms:
                 best_ms, best_chunks = ms_p, chunks
             ps.close()
+        # overlap across calls: two block sets in turn, a call's last push under the next call's scoring (one step of the
+        # loop = one call in steady state)
+        pp = sharded.PushMixtureShardedScorer(tab, rank, world, dist, local, max_frames=T, chunks=best_chunks,
+                                              total_mixtures=M, n_blocks=2)
+        pp.engine.set_stream(stream.cuda_stream)
+        turn = [0]
+        pp.begin(dx, 0)
+
+        def pipelined_step():
+            k = turn[0]
+            pp.begin(dx, 1 - k)
+            pp.finish(k)
+            turn[0] = 1 - k
+
+        for _ in range(2):
+            pipelined_step()
+        ms_pp = timed_loop(pipelined_step, steps)
+        pp.finish(turn[0])
+        torch.cuda.synchronize()
+        same = torch.tensor([1.0 if torch.equal(pp.blocks[0][:T, :M], ref) and torch.equal(pp.blocks[1][:T, :M], ref)
+                             and not pp.timed_out() else 0.0], device="cuda")
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        case.update({"ms_push_pipelined_two_blocks": ms_pp, "pipelined_bit_identical_to_all_gather": bool(same.item() == 1.0),
+                     "speedup_pipelined_over_all_gather": ms_ag / ms_pp})
+        pp.close()
         case.update({"ms_push_best": best_ms, "push_ranges": best_chunks, "push_bit_identical_to_all_gather": same_all,
                      "frames_per_s_push": T / (best_ms * 1e-3), "frames_per_s_all_gather": T / (ms_ag * 1e-3),
                      "push_egress_GBps_per_rank": (world - 1) * T * mp * 4 / (best_ms * 1e-3) / 1e9,

@@ -171,6 +171,16 @@ int gmm_quant_score_device_static(gmm_handle* h, uint32_t T, const float* d_x, i
 int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
                             void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
                             uint32_t chunks);
+/* The same call in two halves, for overlap ACROSS calls ("overlap tile i's gather with tile
+ * i+1's GEMM"): _begin does steps (1) and (2) and returns with the last range's push still running on the second
+ * stream; gmm_gather_finish(own block) is step (3).  With two block sets used in turn --
+ *     begin(A, x0); begin(B, x1); finish(A) -> consume A; begin(A, x2); finish(B) -> consume B; ...
+ * -- the last push of a call runs under the next call's scoring, and a call costs max(scoring, exchange) instead of
+ * their sum.  A block with a started call is joined automatically when the next call on it begins. */
+int gmm_score_device_gather_begin(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
+                                  void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
+                                  uint32_t chunks);
+int gmm_gather_finish(gmm_handle* h, void* d_own_block, size_t flagsOffsetBytes);
 int gmm_gather_status(gmm_handle* h, uint32_t* timedOutCall);
 int gmm_gather_reset(gmm_handle* h);
 /* Device memory other processes of the same box can map: allocate (zeroed) + export (ipcHandle: 64 bytes), map,

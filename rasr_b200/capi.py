@@ -42,6 +42,8 @@ SYMBOLS = [
     ("gmm_score_baum_welch_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     ("gmm_score_baum_welch_accumulate_host", _i, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("gmm_score_device_gather", _i, [_vp, _u32, _vp, _u32, _u32, _vp, _sz, _u32, _sz, _u32]),
+    ("gmm_score_device_gather_begin", _i, [_vp, _u32, _vp, _u32, _u32, _vp, _sz, _u32, _sz, _u32]),
+    ("gmm_gather_finish", _i, [_vp, _vp, _sz]),
     ("gmm_gather_status", _i, [_vp, _vp]),
     ("gmm_gather_reset", _i, [_vp]),
     ("gmm_peer_alloc", _i, [_vp, _sz, _vp, _vp]),
@@ -329,6 +331,17 @@ class Engine:
         self._check(self._lib.gmm_score_device_gather(self._h, int(T), _ptr(d_x), int(rank), len(blocks),
                                                       C.addressof(arr), int(ld), int(col_offset), int(flags_offset),
                                                       int(chunks)), "gmm_score_device_gather")
+
+    def score_device_gather_begin(self, T, d_x, rank, blocks, ld, col_offset, flags_offset, chunks=4):
+        """score_device_gather without the join: the last range's push is still running when this returns."""
+        arr = (C.c_void_p * len(blocks))(*[int(p) for p in blocks])
+        self._check(self._lib.gmm_score_device_gather_begin(self._h, int(T), _ptr(d_x), int(rank), len(blocks),
+                                                            C.addressof(arr), int(ld), int(col_offset), int(flags_offset),
+                                                            int(chunks)), "gmm_score_device_gather_begin")
+
+    def gather_finish(self, own_block: int, flags_offset: int):
+        """The join of a started call: work queued on the engine's stream afterwards sees every rank's columns."""
+        self._check(self._lib.gmm_gather_finish(self._h, int(own_block), int(flags_offset)), "gmm_gather_finish")
 
     def gather_status(self) -> int:
         """Number of the first mixture-sharded call on this handle whose exchange timed out (0: none).  Meaningful

@@ -294,6 +294,9 @@ void gmm_destroy(gmm_handle* h) {
             if (h->gatherEvent[i])
                 cudaEventDestroy(h->gatherEvent[i]);
     }
+    for (cudaEvent_t e : h->gatherDone)
+        if (e)
+            cudaEventDestroy(e);
     if (h->gatherStatus)
         cudaFreeHost(h->gatherStatus);
     if (h->laneEvent)
@@ -533,9 +536,9 @@ int gmm_score_device(gmm_handle* h, uint32_t T, const float* d_x, float* d_score
     return gmm_direct_score(h, T, d_x, d_scores, d_best, ld);
 }
 
-int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
-                            void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
-                            uint32_t chunks) {
+// argument checks of the mixture-sharded calls: < 0 = error, 1 = nothing to do (no frames), 0 = go
+static int gatherArgs(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world, void* const* d_blocks,
+                      size_t ld, uint32_t colOffset, size_t flagsOffsetBytes) {
     if (!h)
         return GMM_ERR_ARG;
     if (!h->floatValid || h->kernel != GMM_KERNEL_TENSOR || !h->tensor.valid) {
@@ -553,13 +556,37 @@ int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_
         return GMM_ERR_ARG;
     }
     if (T == 0)
-        return GMM_OK;
+        return 1;
     if (!d_x) {
         h->setError("gmm_score_device_gather: NULL frames");
         return GMM_ERR_ARG;
     }
+    return 0;
+}
+
+int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
+                            void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
+                            uint32_t chunks) {
+    if (int rc = gatherArgs(h, T, d_x, rank, world, d_blocks, ld, colOffset, flagsOffsetBytes))
+        return rc < 0 ? rc : GMM_OK;
     cudaSetDevice(h->device);
     return gmm_gather_score(h, T, d_x, rank, world, d_blocks, ld, colOffset, flagsOffsetBytes, chunks);
+}
+
+int gmm_score_device_gather_begin(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
+                                  void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,
+                                  uint32_t chunks) {
+    if (int rc = gatherArgs(h, T, d_x, rank, world, d_blocks, ld, colOffset, flagsOffsetBytes))
+        return rc < 0 ? rc : GMM_OK;
+    cudaSetDevice(h->device);
+    return gmm_gather_score(h, T, d_x, rank, world, d_blocks, ld, colOffset, flagsOffsetBytes, chunks, false);
+}
+
+int gmm_gather_finish(gmm_handle* h, void* d_own_block, size_t flagsOffsetBytes) {
+    if (!h || !d_own_block)
+        return GMM_ERR_ARG;
+    cudaSetDevice(h->device);
+    return gmm_gather_finish_impl(h, d_own_block, flagsOffsetBytes);
 }
 
 int gmm_gather_status(gmm_handle* h, uint32_t* timedOutCall) {

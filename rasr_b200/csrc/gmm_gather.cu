@@ -148,6 +148,25 @@ __global__ void __launch_bounds__(256) gather_push_kernel(GatherPeers peers, uin
     }
 }
 
+// Copy-engine variant of the push (long ranges): the READY wait and the DONE announcement as one-warp kernels around
+// cudaMemcpy2DAsync calls on the push stream.  The copy engines move a range at the NVLink rate without taking
+// registers or issue slots from the scoring kernel, which leaves a co-resident push kernel one thin CTA per SM
+// (measured: 275 GB/s leaving the GPU under the scoring kernel against 650-700 GB/s alone).
+__global__ void gather_wait_ready(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t epoch, uint32_t* hostStatus,
+                                  long long limit) {
+    uint32_t* own = peers.flags[rank];
+    if (threadIdx.x < world && threadIdx.x != rank)
+        spin_until(own + kFlagReady + threadIdx.x, epoch, own + kFlagTimeout, hostStatus, limit);
+}
+__global__ void gather_announce_done(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t epoch) {
+    uint32_t* own = peers.flags[rank];
+    __threadfence_system();
+    // after a time-out the columns are not complete: say nothing (the peers run into their own time-out)
+    const bool complete = *reinterpret_cast<volatile uint32_t*>(own + kFlagTimeout) == 0;
+    if (complete && threadIdx.x < world && threadIdx.x != rank)
+        st_release_sys(peers.flags[threadIdx.x] + kFlagDone + rank, epoch);
+}
+
 // Every peer's columns of this epoch have landed in the own block -- or, after a time-out here or in one of the call's
 // push kernels, none of them counts: rows [0, T) keep the own columns [col0, col1) and read +inf everywhere else.
 __global__ void __launch_bounds__(256) gather_wait_done(GatherPeers peers, uint32_t rank, uint32_t world, uint32_t epoch,
@@ -205,8 +224,36 @@ int gmm_gather_reset_impl(gmm_handle* h) {
     return GMM_OK;
 }
 
+// The join of a started call: the handle's stream waits for the call's last push, then for every peer's DONE.
+int gmm_gather_finish_impl(gmm_handle* h, void* d_own_block, size_t flagsOffsetBytes) {
+    uint32_t* flags = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(d_own_block) + flagsOffsetBytes);
+    for (int i = 0; i < gmm_handle::kGatherBindings; ++i) {
+        gmm_handle::GatherBinding& b = h->gatherBound[i];
+        if (b.flags != flags || !b.pending)
+            continue;
+        b.pending = false;
+        if (b.world <= 1)
+            return GMM_OK;
+        GatherPeers peers = {};
+        for (uint32_t r = 0; r < b.world; ++r) {
+            peers.block[r] = reinterpret_cast<float*>(b.blocks[r]);
+            peers.flags[r] = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(b.blocks[r]) + b.flagsOffset);
+        }
+        static const long long spinLimit =
+                getenv("GMM_GATHER_TIMEOUT_MS") ? std::max(1ll, atoll(getenv("GMM_GATHER_TIMEOUT_MS"))) * 2000000ll : kSpinLimit;
+        GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->gatherDone[i], 0));
+        gather_wait_done<<<1, 256, 0, h->stream>>>(peers, b.rank, b.world, b.epoch, b.T, b.ld, b.col0, b.col1,
+                                                   h->gatherStatusDev, spinLimit);
+        h->launches++;
+        GMM_CUDA_TRY(h, cudaGetLastError());
+        return GMM_OK;
+    }
+    return GMM_OK;  // nothing pending on this block
+}
+
 int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
-                     void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks) {
+                     void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks,
+                     bool join) {
     const TensorModel& tm = h->tensor;
     GatherPeers        peers = {};
     for (uint32_t r = 0; r < world; ++r) {
@@ -242,9 +289,16 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
         }
         bound        = &h->gatherBound[h->gatherBoundNext];
         h->gatherBoundNext = (h->gatherBoundNext + 1) % gmm_handle::kGatherBindings;
+        if (bound->pending)  // the slot's previous block still has a started call: join it before the slot is reused
+            if (int rc = gmm_gather_finish_impl(h, bound->blocks[bound->rank], bound->flagsOffset))
+                return rc;
+        *bound       = gmm_handle::GatherBinding();
         bound->flags = peers.flags[rank];
         bound->epoch = words[kFlagEpoch];
     }
+    if (bound->pending)  // a started call on this block was never joined
+        if (int rc = gmm_gather_finish_impl(h, d_blocks[rank], flagsOffsetBytes))
+            return rc;
     // bumped only when the call is fully enqueued (below): a call that fails half way is repeated under the same epoch
     const uint32_t epoch = bound->epoch + 1;
     static const long long spinLimit =
@@ -294,6 +348,7 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
         return (uint32_t)std::min<uint64_t>(b, total - (chunks - c));
     };
 
+    bool readyWaited = false;  // copy-engine pushes: the READY wait kernel runs once per call
     gather_signal_ready<<<1, 32, 0, h->stream>>>(peers, rank, world, epoch);
     h->launches++;
     GMM_CUDA_TRY(h, cudaGetLastError());
@@ -326,6 +381,30 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             for (uint32_t r = 0; r < world && vec; ++r)
                 vec = reinterpret_cast<uintptr_t>(peers.block[r]) % 16 == 0;
             const int last = c + 1 == chunks;
+            // ranges of at least 4 MB per peer go through the copy engines (GMM_GATHER_COPY=sm|ce forces either)
+            static const char* copyEnv = getenv("GMM_GATHER_COPY");
+            const size_t rangeBytes = (size_t)rows * (col1 - col0) * 4;
+            const bool   useCE = copyEnv ? !strcmp(copyEnv, "ce") : rangeBytes >= (4u << 20);
+            if (useCE) {
+                if (!readyWaited) {
+                    gather_wait_ready<<<1, 32, 0, h->gatherStream>>>(peers, rank, world, epoch, h->gatherStatusDev, spinLimit);
+                    h->launches++;
+                    readyWaited = true;
+                }
+                const size_t off = (size_t)row0 * ld + col0;
+                for (uint32_t k = 1; k < world; ++k) {
+                    const uint32_t r = (rank + k) % world;
+                    GMM_CUDA_TRY(h, cudaMemcpy2DAsync(peers.block[r] + off, ld * 4, peers.block[rank] + off, ld * 4,
+                                                      (size_t)(col1 - col0) * 4, rows, cudaMemcpyDeviceToDevice,
+                                                      h->gatherStream));
+                }
+                if (last) {
+                    gather_announce_done<<<1, 32, 0, h->gatherStream>>>(peers, rank, world, epoch);
+                    h->launches++;
+                }
+                GMM_CUDA_TRY(h, cudaGetLastError());
+                continue;
+            }
 #define GMM_PUSH(V, U)                                                                                             \
     gather_push_kernel<V, U><<<pushCtas, 256, 0, h->gatherStream>>>(peers, rank, world, row0, rows, ld, col0, col1, \
                                                                     epoch, last, h->gatherStatusDev, spinLimit)
@@ -344,15 +423,19 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             GMM_CUDA_TRY(h, cudaGetLastError());
         }
     }
+    const int slot = (int)(bound - h->gatherBound);
     if (world > 1) {
-        cudaEvent_t done = h->gatherEvent[gmm_handle::kGatherEvents - 1];
-        GMM_CUDA_TRY(h, cudaEventRecord(done, h->gatherStream));
-        GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->stream, done, 0));
-        gather_wait_done<<<1, 256, 0, h->stream>>>(peers, rank, world, epoch, T, ld, colOffset, colOffset + h->M,
-                                                   h->gatherStatusDev, spinLimit);
-        h->launches++;
-        GMM_CUDA_TRY(h, cudaGetLastError());
+        if (!h->gatherDone[slot])
+            GMM_CUDA_TRY(h, cudaEventCreateWithFlags(&h->gatherDone[slot], cudaEventDisableTiming));
+        GMM_CUDA_TRY(h, cudaEventRecord(h->gatherDone[slot], h->gatherStream));
     }
-    bound->epoch = epoch;
-    return GMM_OK;
+    bound->epoch   = epoch;
+    bound->pending = true;
+    bound->rank = rank, bound->world = world, bound->T = T, bound->ld = ld, bound->flagsOffset = flagsOffsetBytes;
+    bound->col0 = colOffset, bound->col1 = colOffset + h->M;
+    for (uint32_t r = 0; r < 8; ++r)
+        bound->blocks[r] = r < world ? d_blocks[r] : nullptr;
+    // begin only: the caller joins with gmm_gather_finish -- after it has started the NEXT call on another block, so that
+    // this call's last push runs under the next call's scoring
+    return join ? gmm_gather_finish_impl(h, d_blocks[rank], flagsOffsetBytes) : GMM_OK;
 }

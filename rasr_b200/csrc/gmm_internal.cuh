@@ -174,10 +174,16 @@ struct gmm_handle {
     struct GatherBinding {               // a gathered block this handle has called on: its flag words and the epoch of
         uint32_t* flags = nullptr;       // the last call that was fully enqueued (read from the block's own epoch word
         uint32_t  epoch = 0;             // when the handle first meets the block)
+        // a call whose exchange has been started but not joined yet (gmm_score_device_gather_begin / gmm_gather_finish)
+        bool      pending = false;
+        void*     blocks[8] = {};
+        uint32_t  rank = 0, world = 0, T = 0, col0 = 0, col1 = 0;
+        size_t    ld = 0, flagsOffset = 0;
     };
     static constexpr int kGatherBindings = 4;
     GatherBinding gatherBound[kGatherBindings];
     int           gatherBoundNext  = 0;
+    cudaEvent_t   gatherDone[kGatherBindings] = {};  // per binding: the last push of its pending call
     uint32_t*     gatherStatus     = nullptr;  // page-locked, device-mapped: epoch of the first exchange that timed out
     uint32_t*     gatherStatusDev  = nullptr;
     // gmm_score_host: device-to-host copies of finished chunks run on a stream of their own while the next chunk is
@@ -283,8 +289,9 @@ int gmm_tc_score_tiles(gmm_handle* h, uint32_t T, const float* d_x, float* d_sco
                        uint32_t tile1, bool prep, uint32_t prepFrames = 0, uint32_t frameTile0 = 0);
 int gmm_gather_check(gmm_handle* h, const char* who);  // GMM_ERR_TIMEOUT after a timed-out exchange, until reset
 int gmm_gather_reset_impl(gmm_handle* h);
+int gmm_gather_finish_impl(gmm_handle* h, void* d_own_block, size_t flagsOffsetBytes);
 int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
-                     void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks);
+                     void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes, uint32_t chunks, bool join = true);
 int gmm_tc_score(gmm_handle* h, uint32_t T, const float* d_x, float* d_scores, uint32_t* d_best, size_t ld);
 // scores of a per-segment subset of mixtures: column j of segment s's rows = mixture emList[emOff[s] + j]
 // (host arrays); GMM_ERR_UNSUPPORTED when the model is not regular (the caller scores everything instead)

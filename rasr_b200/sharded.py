@@ -145,7 +145,7 @@ class PushMixtureShardedScorer:
     FLAG_WORDS = 32
 
     def __init__(self, float_tables: dict, rank: int, world: int, dist, device: int, max_frames: int, mode=0,
-                 chunks: int = 4, row_pad: int = 0, total_mixtures: int | None = None):
+                 chunks: int = 4, row_pad: int = 0, total_mixtures: int | None = None, n_blocks: int = 1):
         import torch
         from . import capi
         if world > 8:
@@ -172,12 +172,18 @@ class PushMixtureShardedScorer:
         self.max_frames, self.chunks = int(max_frames), int(chunks)
         self._consumer = None
         self.flags_offset = (self.max_frames * self.ld * 4 + 127) // 128 * 128
-        self._own, handle = self.engine.peer_alloc(self.flags_offset + self.FLAG_WORDS * 4)
-        handles = [None] * world
-        dist.all_gather_object(handles, handle)
-        self._bases = [self._own if r == rank else self.engine.peer_open(handles[r]) for r in range(world)]
+        # n_blocks = 2: two block sets used in turn by begin() / finish(), so that a call's last push runs under the
+        # next call's scoring (include/gmm_b200.h gmm_score_device_gather_begin)
         dev = f"cuda:{device}"
-        self.block = torch.as_tensor(_DeviceBlock(self._own, (self.max_frames, self.ld)), device=dev)
+        self._owns, self._all_bases, self.blocks = [], [], []
+        for _ in range(max(1, int(n_blocks))):
+            own, handle = self.engine.peer_alloc(self.flags_offset + self.FLAG_WORDS * 4)
+            handles = [None] * world
+            dist.all_gather_object(handles, handle)
+            self._owns.append(own)
+            self._all_bases.append([own if r == rank else self.engine.peer_open(handles[r]) for r in range(world)])
+            self.blocks.append(torch.as_tensor(_DeviceBlock(own, (self.max_frames, self.ld)), device=dev))
+        self._own, self._bases, self.block = self._owns[0], self._all_bases[0], self.blocks[0]
         self.flags = torch.as_tensor(_DeviceBlock(self._own + self.flags_offset, (self.FLAG_WORDS,)),
                                      device=dev).view(torch.int32)
         torch.cuda.synchronize()
@@ -203,6 +209,23 @@ class PushMixtureShardedScorer:
                                         self.flags_offset, self.chunks)
         return self.block[:T]
 
+    def begin(self, d_x, k: int = 0):
+        """Start a call on block set k (scoring + pushes) without joining it; finish(k) joins.  Used in turn --
+        begin(x0, 0); begin(x1, 1); finish(0); begin(x2, 0); finish(1); ... -- a call's exchange runs under the next
+        call's scoring."""
+        T = d_x.shape[0]
+        if T > self.max_frames:
+            raise ValueError("more frames than the gathered block holds")
+        self.engine.score_device_gather_begin(T, d_x, self.rank, self._all_bases[k], self.ld, self.rank * self.Mp,
+                                              self.flags_offset, self.chunks)
+        return T
+
+    def finish(self, k: int = 0, T: int | None = None):
+        """Join the call started on block set k -> its frame-major view (complete for work queued on the engine's
+        stream after this)."""
+        self.engine.gather_finish(self._owns[k], self.flags_offset)
+        return self.blocks[k] if T is None else self.blocks[k][:T]
+
     def timed_out(self) -> bool:
         """A peer did not show up within the device-side limit (call after a sync).  The other ranks' columns of
         that call read +inf, and scoring calls raise until reset()."""
@@ -218,11 +241,14 @@ class PushMixtureShardedScorer:
     def close(self):
         self.engine.sync()
         self.dist.barrier()
-        for r, b in enumerate(self._bases):
-            if r != self.rank:
-                self.engine.peer_close(b)
+        for bases in self._all_bases:
+            for r, b in enumerate(bases):
+                if r != self.rank:
+                    self.engine.peer_close(b)
         self.dist.barrier()
-        self.engine.peer_free(self._own)
+        self.blocks, self.block = [], None
+        for own in self._owns:
+            self.engine.peer_free(own)
         self.engine.close()
 
 

@@ -161,6 +161,73 @@ def test_ranks_on_one_gpu_exchange_their_columns(world, chunks, T):
             e.close()
 
 
+def test_begin_and_finish_over_two_block_sets_in_turn():
+    """gmm_score_device_gather_begin / gmm_gather_finish: two handles of one process, two block sets each, calls started
+    on one set while the other is joined -- every joined block equals the scores of the frames its call was given, and a
+    begin on a block whose call was never joined joins it first."""
+    ms = synth.make_model(M=1000, K=8, D=24, seed=78)
+    world, T = 2, 700
+    engines, M = _shard_engines(ms, world)
+    Mp = sharded.shard_width(M, world)
+    ld = Mp * world
+    flags_offset = (T * ld * 4 + 127) // 128 * 128
+    try:
+        xs = [torch.from_numpy(synth.make_features(ms, T, seed=20 + i)).cuda() for i in range(3)]
+        wants = []
+        for dx in xs:
+            want = torch.zeros((T, ld), device="cuda")
+            for r, (e, m0, m1) in enumerate(engines):
+                own = torch.empty((T, m1 - m0), device="cuda")
+                e.score_device(T, dx, own)
+                e.sync()
+                want[:, r * Mp:r * Mp + (m1 - m0)] = own
+            wants.append(want)
+        sets = []  # [block set][rank] -> base pointer
+        for _ in range(2):
+            sets.append([e.peer_alloc(flags_offset + 128)[0] for e, _, _ in engines])
+        views = [[torch.as_tensor(sharded._DeviceBlock(b, (T, ld)), device="cuda:0") for b in bases] for bases in sets]
+        for bases in sets:
+            for b in bases:
+                f = torch.as_tensor(sharded._DeviceBlock(b + flags_offset, (32,)), device="cuda:0").view(torch.int32)
+                f[:8] = 1 << 20  # READY preset: one-GPU artefact, see test_ranks_on_one_gpu_exchange_their_columns
+        torch.cuda.synchronize()
+
+        def begin(k, i):
+            for r, (e, _, _) in enumerate(engines):
+                e.score_device_gather_begin(T, xs[i], r, sets[k], ld, r * Mp, flags_offset, 2)
+
+        def finish(k):
+            for r, (e, _, _) in enumerate(engines):
+                e.gather_finish(sets[k][r], flags_offset)
+            for e, _, _ in engines:
+                e.sync()
+
+        begin(0, 0)
+        begin(1, 1)
+        finish(0)
+        for r in range(world):
+            assert torch.equal(views[0][r].view(torch.int32), wants[0].view(torch.int32))
+        begin(0, 2)          # set 0 again while set 1 is still open
+        finish(1)
+        for r in range(world):
+            assert torch.equal(views[1][r].view(torch.int32), wants[1].view(torch.int32))
+        begin(1, 0)          # set 0's call (frames 2) is never joined explicitly ...
+        begin(0, 1)          # ... the next begin on it joins it first
+        finish(0)
+        finish(1)
+        for r in range(world):
+            assert torch.equal(views[0][r].view(torch.int32), wants[1].view(torch.int32))
+            assert torch.equal(views[1][r].view(torch.int32), wants[0].view(torch.int32))
+            assert engines[r][0].gather_status() == 0
+        del views
+        for bases in sets:
+            for (e, _, _), b in zip(engines, bases):
+                e.peer_free(b)
+    finally:
+        for e, _, _ in engines:
+            e.close()
+
+
 def test_a_missing_peer_is_reported_poisoned_and_recoverable(monkeypatch):
     """A peer that never shows up: the wait ends, the caller can SEE it (gmm_gather_status, GMM_ERR_TIMEOUT from the
     next scoring / consuming call), a consumer already queued cannot read stale columns (+inf), and after
