@@ -381,10 +381,14 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             for (uint32_t r = 0; r < world && vec; ++r)
                 vec = reinterpret_cast<uintptr_t>(peers.block[r]) % 16 == 0;
             const int last = c + 1 == chunks;
-            // ranges of at least 4 MB per peer go through the copy engines (GMM_GATHER_COPY=sm|ce forces either)
+            // With ONE peer, ranges of at least 4 MB go through the copy engine (GMM_GATHER_COPY=sm|ce forces either).  With
+            // more peers the copies of a range measured slower than the push kernel, one after the other on this stream
+            // (N = 4, 8192 frames: 4.03 against 3.04-3.46 ms) as well as side by side on a stream per peer (3.96-4.55 ms;
+            // profiles/bench_n4_ce_{serial,parallel}_r02.json): the copy engines deliver ~550 GB/s in total, the push
+            // kernel 650 once the exchange and not the scoring is what the call waits for.
             static const char* copyEnv = getenv("GMM_GATHER_COPY");
             const size_t rangeBytes = (size_t)rows * (col1 - col0) * 4;
-            const bool   useCE = copyEnv ? !strcmp(copyEnv, "ce") : rangeBytes >= (4u << 20);
+            const bool   useCE = copyEnv ? !strcmp(copyEnv, "ce") : (world == 2 && rangeBytes >= (4u << 20));
             if (useCE) {
                 if (!readyWaited) {
                     gather_wait_ready<<<1, 32, 0, h->gatherStream>>>(peers, rank, world, epoch, h->gatherStatusDev, spinLimit);
