@@ -85,8 +85,10 @@ int gmm_score_host(gmm_handle* h, uint32_t T, const float* x, float* scores, uin
  * score, copy out -- and returns at once with a token; gmm_wait(token) returns when that call's scores (and best) are
  * in the caller's arrays.  x, scores and best must stay valid until then, and should be page-locked (gmm_host_alloc):
  * with pageable memory the copies degrade to synchronous ones.  Two calls may be in flight (each on a lane of its own:
- * stream and device scratch); a third waits for the first.  Between a gmm_score_async and its gmm_wait only
- * gmm_score_async, gmm_wait and gmm_sync (which also waits for every outstanding token) may be called on the handle. */
+ * stream and device scratch); a third waits for the first.  Between a gmm_score_async and its gmm_wait the
+ * handle takes gmm_score_async, gmm_wait, gmm_sync (which also waits for every outstanding token), and the blocking
+ * gmm_score_host / gmm_mixture_posteriors_host, which work on the handle's own lane (the RASR plugin scores a few
+ * late frames that way while a batch is in flight); no model upload and no other scoring entry point. */
 int gmm_score_async(gmm_handle* h, uint32_t T, const float* x, float* scores, uint32_t* best, size_t ld,
                     uint64_t* token);
 int gmm_wait(gmm_handle* h, uint64_t token);
@@ -166,7 +168,9 @@ int gmm_quant_score_device_static(gmm_handle* h, uint32_t T, const float* d_x, i
  * already queued behind the call sees impossible scores, never stale ones, (c) stores the call's number into a
  * page-locked word: gmm_gather_status reads it (0 = no time-out; meaningful after a gmm_sync), and from then on
  * gmm_score_device_gather, gmm_align_device and gmm_baum_welch_device return GMM_ERR_TIMEOUT on this handle until
- * gmm_gather_reset.  The reset is collective by contract: every rank calls it between two host barriers (no call in
+ * gmm_gather_reset.  (With one peer, long ranges are pushed by the copy engines behind a kernel that waits for the
+ * peer's READY; if THAT wait times out the copies still run -- into the block of a peer that is already two seconds
+ * late and will find no DONE from this rank -- and the condition is reported the same way.)  The reset is collective by contract: every rank calls it between two host barriers (no call in
  * flight anywhere); it zeroes the flag words of the blocks this handle has called on and restarts their numbering. */
 int gmm_score_device_gather(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank, uint32_t world,
                             void* const* d_blocks, size_t ld, uint32_t colOffset, size_t flagsOffsetBytes,

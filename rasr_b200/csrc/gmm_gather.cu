@@ -239,7 +239,7 @@ int gmm_gather_finish_impl(gmm_handle* h, void* d_own_block, size_t flagsOffsetB
             peers.block[r] = reinterpret_cast<float*>(b.blocks[r]);
             peers.flags[r] = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(b.blocks[r]) + b.flagsOffset);
         }
-        static const long long spinLimit =
+        const long long spinLimit =
                 getenv("GMM_GATHER_TIMEOUT_MS") ? std::max(1ll, atoll(getenv("GMM_GATHER_TIMEOUT_MS"))) * 2000000ll : kSpinLimit;
         GMM_CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->gatherDone[i], 0));
         gather_wait_done<<<1, 256, 0, h->stream>>>(peers, b.rank, b.world, b.epoch, b.T, b.ld, b.col0, b.col1,
@@ -301,7 +301,7 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             return rc;
     // bumped only when the call is fully enqueued (below): a call that fails half way is repeated under the same epoch
     const uint32_t epoch = bound->epoch + 1;
-    static const long long spinLimit =
+    const long long spinLimit =
             getenv("GMM_GATHER_TIMEOUT_MS") ? std::max(1ll, atoll(getenv("GMM_GATHER_TIMEOUT_MS"))) * 2000000ll : kSpinLimit;
     float*         own   = peers.block[rank] + colOffset;
     // The exchange is overlapped range by range.  Short calls are cut into column ranges (whole B tiles over all the
@@ -386,7 +386,7 @@ int gmm_gather_score(gmm_handle* h, uint32_t T, const float* d_x, uint32_t rank,
             // (N = 4, 8192 frames: 4.03 against 3.04-3.46 ms) as well as side by side on a stream per peer (3.96-4.55 ms;
             // profiles/bench_n4_ce_{serial,parallel}_r02.json): the copy engines deliver ~550 GB/s in total, the push
             // kernel 650 once the exchange and not the scoring is what the call waits for.
-            static const char* copyEnv = getenv("GMM_GATHER_COPY");
+            const char* copyEnv = getenv("GMM_GATHER_COPY");
             const size_t rangeBytes = (size_t)rows * (col1 - col0) * 4;
             const bool   useCE = copyEnv ? !strcmp(copyEnv, "ce") : (world == 2 && rangeBytes >= (4u << 20));
             if (useCE) {
