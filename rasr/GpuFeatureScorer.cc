@@ -401,6 +401,10 @@ Mm::AssigningFeatureScorer::AssigningScorer GpuFeatureScorer::getAssigningScorer
 
 Mm::FeatureScorer::Scorer GpuFeatureScorer::flush() const {
     require(!bufferEmpty());
+    // the caller has begun to drain the buffer (end of the segment): the frames handed in since the last batch go to
+    // the GPU now, so that they are on their way while the earlier frames' scores are being read
+    if (staging_ && staging_->nFrames > 0 && !quantized())
+        scoreBlock(*staging_, withBest_, true);
     ContextRef c = fifo_.front();
     fifo_.pop_front();
     return Scorer(c.get());
