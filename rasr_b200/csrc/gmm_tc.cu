@@ -437,7 +437,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             }
         }
         if (p.dbg && leader) {
-            unsigned long long* d = p.dbg + blockIdx.x * 16;
+            unsigned long long* d = p.dbg + blockIdx.x * 128;
             unsigned long long gt1;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt1));
             d[0] = clock64() - tStart, d[1] = wR, d[2] = wI, d[3] = wB, d[4] = t, d[5] = itemCount, d[6] = gt0, d[7] = gt1;
@@ -678,9 +678,12 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             if (lane == 0)
                 mbar_arrive(smem_u32(&emptyB[b]));
         }
-        if (p.dbg && e == 0 && grp == 0 && lane == 0) {
-            unsigned long long* d = p.dbg + blockIdx.x * 16;
-            d[8] = eW, d[9] = eL, d[10] = eC, d[11] = eS;
+        if (p.dbg && lane == 0) {
+            unsigned long long* d = p.dbg + blockIdx.x * 128;
+            if (e == 0 && grp == 0)
+                d[8] = eW, d[9] = eL, d[10] = eC, d[11] = eS;
+            unsigned long long* w = d + 16 + (warp - kEpiWarp0) * 4;  // every epilogue warp
+            w[0] = eW, w[1] = eL, w[2] = eC, w[3] = eS;
         }
     }
 
@@ -1259,7 +1262,7 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     const bool debug = getenv("GMM_TC_DEBUG") != nullptr;
     if (debug) {
         void* d = nullptr;
-        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 128, &d)))
+        if ((rc = h->reserve(SCR_MISC, (size_t)h->smCount * 1024, &d)))
             return rc;
         p.dbg = (unsigned long long*)d;
     }
@@ -1330,27 +1333,35 @@ int tc_run(gmm_handle* h, const TcJob& job) {
     h->launches++;
     GMM_CUDA_TRY(h, e);
     if (debug) {  // development aid: where the MMA-issuing thread spends its cycles
-        std::vector<unsigned long long> d((size_t)h->smCount * 16);
+        std::vector<unsigned long long> d((size_t)h->smCount * 128);
         GMM_CUDA_TRY(h, cudaStreamSynchronize(h->stream));
         GMM_CUDA_TRY(h, cudaMemcpy(d.data(), p.dbg, d.size() * 8, cudaMemcpyDeviceToHost));
         double tot = 0, wR = 0, wI = 0, wC = 0, tiles = 0;
         double eW = 0, eL = 0, eC = 0, eS = 0;
         for (int c = 0; c < grid; ++c) {
-            tot += d[c * 16], wR += d[c * 16 + 1], wI += d[c * 16 + 2], wC += d[c * 16 + 3], tiles += d[c * 16 + 4];
-            eW += d[c * 16 + 8], eL += d[c * 16 + 9], eC += d[c * 16 + 10], eS += d[c * 16 + 11];
+            tot += d[c * 128], wR += d[c * 128 + 1], wI += d[c * 128 + 2], wC += d[c * 128 + 3], tiles += d[c * 128 + 4];
+            eW += d[c * 128 + 8], eL += d[c * 128 + 9], eC += d[c * 128 + 10], eS += d[c * 128 + 11];
         }
         tiles = std::max(1.0, tiles);
         {
             unsigned long long g0 = ~0ull, g1 = 0;
             double dmin = 1e30, dmax = 0, dsum = 0, ns = 0;
             for (int c = 0; c < grid; ++c) {
-                g0 = std::min(g0, d[c * 16 + 6]), g1 = std::max(g1, d[c * 16 + 7]);
-                const double dur = (double)(d[c * 16 + 7] - d[c * 16 + 6]) * 1e-3;
+                g0 = std::min(g0, d[c * 128 + 6]), g1 = std::max(g1, d[c * 128 + 7]);
+                const double dur = (double)(d[c * 128 + 7] - d[c * 128 + 6]) * 1e-3;
                 dmin = std::min(dmin, dur), dmax = std::max(dmax, dur), dsum += dur, ns += dur * 1e3;
             }
             fprintf(stderr, "[gmm_tc] MMA loops: %.1f us first start to last end; per CTA %.1f / %.1f / %.1f us (min / mean / max); "
                     "SM clock %.0f MHz (cycles / globaltimer)\n",
                     (double)(g1 - g0) * 1e-3, dmin, dsum / grid, dmax, ns > 0 ? tot / ns * 1e3 : 0.0);
+        }
+        for (uint32_t w = 0; w < epiWarps * (twoGroups ? 2 : 1); ++w) {
+            double v[4] = {0, 0, 0, 0};
+            for (int c = 0; c < grid; ++c)
+                for (int k = 0; k < 4; ++k)
+                    v[k] += d[c * 128 + 16 + w * 4 + k];
+            fprintf(stderr, "[gmm_tc]   epilogue warp %2u: wait-for-MMA %.0f + drain %.0f + last chunk %.0f + stores %.0f = %.0f\n", w,
+                    v[0] / tiles, v[1] / tiles, v[2] / tiles, v[3] / tiles, (v[0] + v[1] + v[2] + v[3]) / tiles);
         }
         fprintf(stderr,
                 "[gmm_tc] epilogue warp 0, cycles per tile: wait-for-MMA %.0f + TMEM drain (loads, first three chunks) %.0f + "
