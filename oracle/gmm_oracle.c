@@ -10,8 +10,8 @@
  * tests/test_oracle_vs_ref.py compares every function below with it, and tests/golden/ holds outputs
  * of that binary (generator: tests/golden/make_golden.py).
  *
- * Exception: orc_viterbi_align (the alignment consumer, end of file) is PARITY UNPINNED -- the
- * reference's Search::Aligner cannot be compiled here; see the note above that function.
+ * The alignment consumers (orc_viterbi_align, orc_baum_welch_align) are pinned the same way: against the
+ * unmodified Search::Aligner compiled into oracle/_ref/ref_aligner; see the notes above those functions.
  *
  * Compile WITHOUT -ffast-math: every operation is written in the order the reference binary executes
  * it (its -ffast-math build was inspected by disassembly where the source leaves the order open).
@@ -377,9 +377,13 @@ void orc_simd_final_score(const int32_t* q, size_t n, float scalingSquared, floa
 /* ---------------------------------------------------------------------------------------------
  * Viterbi alignment over a score block (the consumer of the scores)
  *
- * PARITY UNPINNED for this function: Search::Aligner needs the reference's Fsa, Am, Core and Speech
- * libraries (their own build system, libxml2, generated code), which cannot be compiled here, and the
- * reference holds no golden alignment.  The restatement follows the source line by line instead.
+ * PINNED against the reference itself: oracle/ref_build/Makefile compiles the unmodified Search/Aligner.cc with the
+ * reference's Fsa library, Speech/Alignment.cc and Am/AcousticModel.cc into oracle/_ref/ref_aligner (driver:
+ * oracle/ref_build/ref_aligner.cc -- a table-backed acoustic model and per-frame scorers stand in for the model files;
+ * libxml2 being absent, stubs/libxml/parser.h names the types the Core headers mention and no XML code is built).
+ * tests/test_oracle_vs_ref.py compares this function with it on fresh random automata -- same emission at every
+ * frame, same f32 score, exact ties included -- and tests/golden/aln_*.npz hold that binary's answers
+ * (generator: tests/golden/make_align_golden.py).  The reference holds no golden alignment of its own.
  * Paths relative to /root/reference/src/Search.
  * ------------------------------------------------------------------------------------------- */
 typedef struct {
@@ -472,9 +476,10 @@ float orc_viterbi_align(uint32_t T, const float* scores, size_t ld, uint32_t S, 
 /* ---------------------------------------------------------------------------------------------
  * Training E-step: best density of the aligned mixture + accumulation.
  *
- * PARITY UNPINNED for the accumulation itself (the estimator classes need Core's binary/XML streams and
- * Configuration, not compiled here); the best density and the posteriors are the pinned scorer functions above
- * restricted to one mixture.  Follows, in frame order and in f64 like the reference:
+ * PINNED: oracle/ref_build/ref_estimator.cc links the unmodified estimator classes; tests/test_oracle_vs_ref.py and
+ * tests/golden/est_*.npz compare the accumulators below with the MIXSET files it writes, bit for bit in viterbi mode.
+ * The best density and the posteriors are the pinned scorer functions above restricted to one mixture.  Follows, in
+ * frame order and in f64 like the reference:
  *   Speech/KeyedEstimator.cc:108-121 processAlignedFeature
  *   AbstractMixtureSetEstimator.cc:117-147 accumulate (viterbi / posterior-weighted with weightThreshold)
  *   MixtureEstimator.cc:86-97, GaussDensityEstimator.cc:22-32, VectorAccumulator.hh:60-67,
@@ -607,8 +612,11 @@ void orc_lda(const float* base, uint32_t nSeg, const uint32_t* frameOffsets, uin
 }
 
 /* ---------------------------------------------------------------------------------------------
- * Baum-Welch alignment (Search::Aligner in mode baum-welch, unpruned, min-weight 0).  PARITY UNPINNED, as
- * orc_viterbi_align: restated from the source, the aligner and the Fsa library it uses cannot be compiled here.
+ * Baum-Welch alignment (Search::Aligner in mode baum-welch, unpruned, min-weight 0).  PINNED as orc_viterbi_align:
+ * against oracle/_ref/ref_aligner = the unmodified aligner with Fsa::posterior64 and Speech::Alignment's combineItems /
+ * clipWeights / shiftMinToZeroWeights / expm / normalizeWeights (tests/test_oracle_vs_ref.py, tests/golden/aln_*.npz):
+ * state posteriors agree to 1e-5 absolute (the reference rounds arc posteriors to f32 -log values and combines them in
+ * the f32 log semiring; this restatement stays in f64), totals to 1e-6 relative.
  *   Search/Aligner.cc:160-187  activateOrUpdateStateHypothesisBaumWelch: the forward potential of a state is
  *                              collected in the log semiring over its incoming arcs; the traceback lattice keeps
  *                              one arc per (frame, automaton arc) with weight transition + emission score

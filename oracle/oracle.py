@@ -33,7 +33,7 @@ def build_ref(force: bool = False) -> str | None:
     """Compile the reference scorer classes from /root/reference (build container only)."""
     if not os.path.isdir(REFERENCE_ROOT):
         return REF_BIN if os.path.exists(REF_BIN) else None
-    if force or not all(os.path.exists(os.path.join(HERE, "_ref", b)) for b in ("ref_scorer", "ref_matmul", "ref_estimator")):
+    if force or not all(os.path.exists(os.path.join(HERE, "_ref", b)) for b in ("ref_scorer", "ref_matmul", "ref_estimator", "ref_aligner")):
         subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(HERE, "ref_build")])
     return REF_BIN
 
@@ -350,6 +350,48 @@ def run_ref_estimator(ms, x=None, mixture=None, weight=None, *, mode="viterbi", 
         if os.path.exists(op + ".best.u32"):
             out["best"] = np.fromfile(op + ".best.u32", np.uint32)
         return out
+
+
+REF_ALIGNER_BIN = os.path.join(HERE, "_ref", "ref_aligner")
+
+
+def ref_aligner_available() -> bool:
+    return os.path.exists(REF_ALIGNER_BIN) and os.access(REF_ALIGNER_BIN, os.X_OK)
+
+
+def run_ref_aligner(scores, automata, i=0, *, mode="viterbi", workdir=None):
+    """Run the unmodified reference Search::Aligner (oracle/ref_build/ref_aligner.cc) on segment i's automaton over the
+    score rows `scores` [frames x emissions], unpruned.
+    -> dict(time u32 [n], emission u32 [n], weight f64 [n], score f32 (Aligner::alignmentScore()),
+            total f32 (baum-welch: totalInv of Fsa::posterior64 = MINUS the total, Aligner.cc:757-772))."""
+    if not ref_aligner_available():
+        raise RuntimeError("oracle/_ref/ref_aligner is not built (needs /root/reference: oracle.build_ref())")
+    a = automata
+    scores = np.ascontiguousarray(scores, np.float32)
+    s0, s1 = int(a.state_offsets[i]), int(a.state_offsets[i + 1])
+    a0, a1 = int(a.arc_offsets[s0]), int(a.arc_offsets[s1])
+    with tempfile.TemporaryDirectory(dir=workdir) as tmp:
+        ip, op = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out")
+        with open(ip, "wb") as f:
+            np.asarray([scores.shape[0], scores.shape[1], s1 - s0, a1 - a0, int(a.initial_state[i])], np.uint32).tofile(f)
+            np.ascontiguousarray(a.arc_offsets[s0:s1 + 1] - np.uint32(a0), np.uint32).tofile(f)
+            np.ascontiguousarray(a.arc_target[a0:a1], np.uint32).tofile(f)
+            np.ascontiguousarray(a.arc_emission[a0:a1], np.uint32).tofile(f)
+            np.ascontiguousarray(a.arc_weight[a0:a1], np.float32).tofile(f)
+            np.ascontiguousarray(a.final_weight[s0:s1], np.float32).tofile(f)
+            scores.tofile(f)
+        cmd = [REF_ALIGNER_BIN, f"in={ip}", f"out={op}", f"mode={mode}", "--*.aligner.min-acoustic-pruning=1e30",
+               "--*.aligner.max-acoustic-pruning=1e30"]
+        r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"ref_aligner failed ({r.returncode}):\n{r.stdout[-2000:]}")
+        with open(op + ".items.bin", "rb") as f:
+            raw = f.read()
+        n = int(np.frombuffer(raw[:4], np.uint32)[0])
+        items = np.frombuffer(raw[4:], np.dtype([("t", "<u4"), ("e", "<u4"), ("w", "<f8")]), count=n)
+        sc = np.fromfile(op + ".score.f32", np.float32)
+    return {"time": items["t"].copy(), "emission": items["e"].copy(), "weight": items["w"].copy(), "score": sc[0],
+            "total": sc[1], "log": r.stdout}
 
 
 def emission_lists(automata, i):

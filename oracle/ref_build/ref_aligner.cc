@@ -1,0 +1,229 @@
+// TEST INFRASTRUCTURE (oracle/): drives the reference's own, UNMODIFIED Search::Aligner (src/Search/Aligner.cc) with
+// its Fsa library (Fsa::posterior64, Fsa::transpose, ...) and Speech::Alignment (combineItems, clipWeights,
+// shiftMinToZeroWeights, expm, normalizeWeights), compiled by oracle/ref_build/Makefile with the reference's flags, to
+// pin oracle/gmm_oracle.c orc_viterbi_align / orc_baum_welch_align and the fixtures tests/golden/align_*.npz.
+//
+// What is NOT the reference's here, and why it does not matter for the pin:
+//   * the acoustic model is a test double (TableAcousticModel): the aligner asks it for emissionIndex(label) only
+//     (Aligner.cc:225) and for the alphabet it attaches to the result (Aligner.cc:718); labels ARE emission indices;
+//   * the per-frame scorers are a test double (RowScorer) returning one row of a score block -- the block is what the
+//     scoring path hands the aligner, computed elsewhere (ref_scorer pins that part);
+//   * libxml2 is absent: stubs/libxml/parser.h holds the handful of type names Core/XmlParser.hh mentions so that the
+//     HEADERS parse; no XML parsing TU is compiled, stubs/align_stubs.cc aborts in the few word-lattice symbols
+//     (Aligner::WordLatticeBuilder) the aligner's object file refers to and this driver never reaches.
+//
+// usage: ref_aligner in=<file> out=<prefix> mode=viterbi|baum-welch
+//            --*.aligner.min-acoustic-pruning=1e30 --*.aligner.max-acoustic-pruning=1e30   (unpruned, one pass)
+//   in : u32 T, M, S, A, initial; u32 arcOffsets[S+1]; u32 arcTarget[A]; u32 arcEmission[A]; f32 arcWeight[A];
+//        f32 finalWeight[S] (+inf: not final); f32 scores[T*M]
+//   out: <prefix>.items.bin = u32 n, n x {u32 time, u32 emission, f64 weight} in the order Alignment holds them;
+//        <prefix>.score.f32 = {alignmentScore(), total of the posterior automaton (baum-welch) or the same (viterbi)}
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "ref_common.hh"  // Mm::FeatureScorer::ContextScorer is protected: the harness switch makes it reachable
+
+#include <Am/AcousticModel.hh>
+#include <Core/Application.hh>
+#include <Fsa/Static.hh>
+#include <Mm/FeatureScorer.hh>
+#include <Search/Aligner.hh>
+#include <Speech/Alignment.hh>
+
+namespace {
+
+class RowScorer : public Mm::FeatureScorer::ContextScorer {
+    const f32* row_;
+    u32        n_;
+
+public:
+    RowScorer(const f32* row, u32 n)
+            : row_(row), n_(n) {}
+    virtual Mm::EmissionIndex nEmissions() const {
+        return n_;
+    }
+    virtual Mm::Score score(Mm::EmissionIndex e) const {
+        return row_[e];
+    }
+};
+
+class TableAcousticModel : public Am::AcousticModel {
+    u32 n_;
+
+public:
+    TableAcousticModel(const Core::Configuration& c, u32 n)
+            : Core::Component(c), Am::AcousticModel(c), n_(n) {}
+    virtual void load(Mode) {}
+    virtual void getDependencies(Core::DependencySet&) const {}
+    virtual Core::Ref<Am::TransducerBuilder> createTransducerBuilder() const {
+        return Core::Ref<Am::TransducerBuilder>();
+    }
+    virtual Core::Ref<const Bliss::PhonemeInventory> phonemeInventory() const {
+        return Core::Ref<const Bliss::PhonemeInventory>();
+    }
+    virtual Core::Ref<const Am::AllophoneAlphabet> allophoneAlphabet() const {
+        return Core::Ref<const Am::AllophoneAlphabet>();
+    }
+    virtual Core::Ref<const Am::AllophoneStateAlphabet> allophoneStateAlphabet() const {
+        return Core::Ref<const Am::AllophoneStateAlphabet>();
+    }
+    virtual Core::Ref<const Am::Phonology> phonology() const {
+        return Core::Ref<const Am::Phonology>();
+    }
+    virtual Bliss::Phoneme::Id silence() const {
+        return 0;
+    }
+    virtual Am::AllophoneStateIndex silenceAllophoneStateIndex() const {
+        return 0;
+    }
+    virtual Core::Ref<Mm::AbstractMixtureSet> mixtureSet() {
+        return Core::Ref<Mm::AbstractMixtureSet>();
+    }
+    virtual Core::Ref<const Mm::ScaledFeatureScorer> featureScorer() {
+        return Core::Ref<const Mm::ScaledFeatureScorer>();
+    }
+    virtual Core::Ref<Mm::ScaledFeatureScorer> mutableFeatureScorer() {
+        return Core::Ref<Mm::ScaledFeatureScorer>();
+    }
+    virtual bool setFeatureScorer(Core::Ref<Mm::ScaledFeatureScorer>) {
+        return false;
+    }
+    virtual EmissionIndex emissionIndex(Am::AllophoneState) const {
+        abort();
+    }
+    virtual EmissionIndex emissionIndex(Am::AllophoneStateIndex i) const {
+        return i;  // labels of the automaton are emission indices
+    }
+    virtual EmissionIndex nEmissions() const {
+        return n_;
+    }
+    virtual StateTransitionIndex nStateTransitions() const {
+        return 0;
+    }
+    virtual const Am::StateTransitionModel* stateTransition(StateTransitionIndex) const {
+        return 0;
+    }
+    virtual StateTransitionIndex stateTransitionIndex(Am::AllophoneState, s8) const {
+        return 0;
+    }
+    virtual StateTransitionIndex stateTransitionIndex(Am::AllophoneStateIndex, s8) const {
+        return 0;
+    }
+    virtual Core::Ref<const Am::ClassicHmmTopologySet> hmmTopologySet() const {
+        return Core::Ref<const Am::ClassicHmmTopologySet>();
+    }
+    virtual const Am::ClassicHmmTopology* hmmTopology(Bliss::Phoneme::Id) const {
+        return 0;
+    }
+    virtual bool isAcrossWordModelEnabled() const {
+        return false;
+    }
+};
+
+}  // namespace
+
+class RefAlignerApp : public Core::Application {
+    std::map<std::string, std::string> args_;
+
+    std::string arg(const std::string& key, const std::string& dflt = "") const {
+        std::map<std::string, std::string>::const_iterator i = args_.find(key);
+        return i == args_.end() ? dflt : i->second;
+    }
+
+public:
+    RefAlignerApp() {
+        setTitle("ref-aligner");
+        setDefaultLoadConfigurationFile(false);
+        setDefaultOutputXmlHeader(false);
+    }
+    std::string getUsage() const {
+        return "ref_aligner in=<file> out=<prefix> mode=viterbi|baum-welch\n";
+    }
+
+    int main(const std::vector<std::string>& arguments) {
+        for (size_t i = 0; i < arguments.size(); ++i) {
+            size_t eq = arguments[i].find('=');
+            if (eq != std::string::npos)
+                args_[arguments[i].substr(0, eq)] = arguments[i].substr(eq + 1);
+        }
+        const std::string in = arg("in"), out = arg("out"), mode = arg("mode", "viterbi");
+        FILE*             f = fopen(in.c_str(), "rb");
+        if (!f || out.empty()) {
+            std::cerr << getUsage();
+            return 2;
+        }
+        u32 hdr[5];
+        if (fread(hdr, 4, 5, f) != 5)
+            return 3;
+        const u32        T = hdr[0], M = hdr[1], S = hdr[2], A = hdr[3], initial = hdr[4];
+        std::vector<u32> arcOffsets, arcTarget, arcEmission;
+        std::vector<f32> arcWeight, finalWeight, scores;
+        if (!readArray(f, arcOffsets, S + 1) || !readArray(f, arcTarget, A) || !readArray(f, arcEmission, A) ||
+            !readArray(f, arcWeight, A) || !readArray(f, finalWeight, S) || !readArray(f, scores, size_t(T) * M))
+            return 4;
+        fclose(f);
+
+        // the model acceptor: states in id order, arcs in the order given (= the order the aligner expands them)
+        Fsa::StaticAutomaton* model = new Fsa::StaticAutomaton();
+        model->setType(Fsa::TypeAcceptor);
+        model->setSemiring(Fsa::TropicalSemiring);
+        for (u32 s = 0; s < S; ++s) {
+            Fsa::State* sp = new Fsa::State(s);
+            u32 bits;  // -ffast-math folds isinf() away: test the bit pattern of +inf
+            memcpy(&bits, &finalWeight[s], 4);
+            if (bits != 0x7f800000u)
+                sp->setFinal(Fsa::Weight(finalWeight[s]));
+            for (u32 a = arcOffsets[s]; a < arcOffsets[s + 1]; ++a)
+                sp->newArc(arcTarget[a], Fsa::Weight(arcWeight[a]), arcEmission[a]);
+            model->setState(sp);
+        }
+        model->setInitialStateId(initial);
+        Fsa::ConstAutomatonRef modelRef(model);
+
+        // unpruned: one pass at a threshold nothing exceeds (Aligner.cc:584-611); min-weight 0 keeps every item
+        // (the caller passes --*.aligner.min-acoustic-pruning=1e30 --*.aligner.max-acoustic-pruning=1e30)
+        Core::Ref<const Am::AcousticModel> am(new TableAcousticModel(select("acoustic-model"), M));
+        Search::Aligner                    aligner(select("aligner"));
+        aligner.selectMode(mode == "viterbi" ? Search::Aligner::modeViterbi : Search::Aligner::modeBaumWelch);
+        aligner.setModel(modelRef, am);
+        std::vector<Mm::FeatureScorer::Scorer> scorers;
+        for (u32 t = 0; t < T; ++t)
+            scorers.push_back(Mm::FeatureScorer::Scorer(new RowScorer(scores.data() + size_t(t) * M, M)));
+        aligner.feed(scorers);
+
+        f32               result[2] = {aligner.alignmentScore(), aligner.alignmentScore()};
+        Speech::Alignment alignment;
+        if (aligner.reachedFinalState()) {
+            std::pair<Fsa::ConstAutomatonRef, Fsa::Weight> posterior =
+                    aligner.getAlignmentPosteriorFsa(aligner.getAlignmentFsa());
+            if (mode != "viterbi")
+                result[1] = f32(posterior.second);
+            aligner.getAlignment(alignment, posterior);
+        }
+        f = fopen((out + ".items.bin").c_str(), "wb");
+        if (!f)
+            return 5;
+        const u32 n = alignment.size();
+        fwrite(&n, 4, 1, f);
+        for (Speech::Alignment::const_iterator it = alignment.begin(); it != alignment.end(); ++it) {
+            const u32 te[2] = {u32(it->time), u32(it->emission)};
+            const f64 w     = it->weight;
+            fwrite(te, 4, 2, f);
+            fwrite(&w, 8, 1, f);
+        }
+        fclose(f);
+        f = fopen((out + ".score.f32").c_str(), "wb");
+        if (!f)
+            return 5;
+        fwrite(result, 4, 2, f);
+        fclose(f);
+        return 0;
+    }
+};
+
+APPLICATION(RefAlignerApp)

@@ -13,9 +13,9 @@ Reference (paths relative to /root/reference/src/Mm):
                 112-123, Mixture.cc:63-74 + Utilities.hh:44-51 (weights), GaussDensityEstimator.cc:148-156 (mean),
                 200-224 (covariance), Utilities.hh:93-106,148-159
 
-Parity: UNPINNED against the reference binaries (the estimator stack and MixtureSet text I/O need Core's
-Application / XML / configuration machinery, not compiled here); the formats and formulas are restated from the
-sources above and tested for round trips and against independent numpy formulas.
+Parity: pinned against the reference binaries -- tests/golden/est_*.npz hold the text mixture set, the MIXSET
+accumulator file and the estimate() output of the unmodified classes (oracle/ref_build/ref_estimator.cc); the writers
+here reproduce them byte for byte (tests/test_estimator_golden.py).
 """
 from __future__ import annotations
 

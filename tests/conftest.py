@@ -20,11 +20,25 @@ def golden_names():
     """Model fixtures (scorer goldens); lda_*.npz (front end) and est_*.npz (estimators, model files) are fixtures
     with their own tests."""
     names = (os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return sorted(n for n in names if not n.startswith(("lda_", "est_", "batchint_")))
+    return sorted(n for n in names if not n.startswith(("lda_", "est_", "batchint_", "aln_")))
 
 
 def batchint_golden_names():
     return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "batchint_*.npz")))
+
+
+def align_golden_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "aln_*.npz")))
+
+
+def load_align_golden(name):
+    """-> (frame_offsets, scores, AlignmentAutomata, fixture): what the reference's Search::Aligner was given and what
+    it answered (tests/golden/make_align_golden.py)."""
+    from rasr_b200.align import AlignmentAutomata
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    au = AlignmentAutomata(z["state_offsets"], z["arc_offsets"], z["arc_target"], z["arc_emission"], z["arc_weight"],
+                           z["initial_state"], z["final_weight"])
+    return z["frame_offsets"], z["scores"], au, z
 
 
 def estimator_golden_names():
