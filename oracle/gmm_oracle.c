@@ -574,8 +574,10 @@ void orc_accumulate(const orc_model* m, const float* isr, const float* logNorm, 
  *
  * The matrix product is PINNED: tests/test_oracle_vs_ref.py compares it with the reference's own
  * Math::Matrix<f32> * Math::Vector<f32> (oracle/_ref/ref_matmul, built by oracle/ref_build/Makefile);
- * tests/golden/lda_matmul.npz holds outputs of that binary.  The window (Flow DelayNode) is restated
- * from the source: parity unpinned for the margin handling.
+ * tests/golden/lda_matmul.npz holds outputs of that binary.  The window is PINNED too: oracle/_ref/ref_window runs the
+ * reference's own Signal::DelayNode (through signal-vector-f32-sequence-concatenation in a Flow::Network wired as
+ * share/lda.flow); tests/test_lda_oracle.py compares on fresh random shapes, tests/golden/lda_window.npz holds that
+ * binary's windows and, multiplied by ref_matmul, the whole front end's outputs.
  *   Signal/VectorSequenceConcatenation.hh:85-100  window of frames t-left .. t+right, oldest first
  *   Signal/Delay.hh:32-46, Delay.cc:30-31,171-174  margin-condition present-not-empty (lda.flow), margin-policy
  *                                                  copy: a missing frame is the closest existing one

@@ -33,7 +33,7 @@ def build_ref(force: bool = False) -> str | None:
     """Compile the reference scorer classes from /root/reference (build container only)."""
     if not os.path.isdir(REFERENCE_ROOT):
         return REF_BIN if os.path.exists(REF_BIN) else None
-    if force or not all(os.path.exists(os.path.join(HERE, "_ref", b)) for b in ("ref_scorer", "ref_matmul", "ref_estimator", "ref_aligner")):
+    if force or not all(os.path.exists(os.path.join(HERE, "_ref", b)) for b in ("ref_scorer", "ref_matmul", "ref_estimator", "ref_aligner", "ref_window")):
         subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(HERE, "ref_build")])
     return REF_BIN
 
@@ -306,6 +306,34 @@ def run_ref(ms, x, scorer="max", *, threads=0, repeat=1, dump=True, workdir=None
             with open(op + ".timing.json") as f:
                 out["timing"] = json.load(f)
         return out
+
+
+REF_WINDOW_BIN = os.path.join(HERE, "_ref", "ref_window")
+
+
+def ref_window_available() -> bool:
+    return os.path.exists(REF_WINDOW_BIN) and os.access(REF_WINDOW_BIN, os.X_OK)
+
+
+def run_ref_window(base, length, right, *, margin_policy="copy", margin_condition="present-not-empty", workdir=None):
+    """The reference's sliding-window node (Signal::DelayNode through signal-vector-f32-sequence-concatenation, wired as
+    share/lda.flow wires it; oracle/ref_build/ref_window.cc) over ONE segment `base` [frames x baseDim].
+    -> [outputs x baseDim*length] f32."""
+    if not ref_window_available():
+        raise RuntimeError("oracle/_ref/ref_window is not built (needs /root/reference: oracle.build_ref())")
+    base = np.ascontiguousarray(base, np.float32)
+    with tempfile.TemporaryDirectory(dir=workdir) as tmp:
+        ip, op = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
+        with open(ip, "wb") as f:
+            np.asarray([base.shape[0], base.shape[1], length, right], np.uint32).tofile(f)
+            base.tofile(f)
+        r = subprocess.run([REF_WINDOW_BIN, f"in={ip}", f"out={op}", f"margin-policy={margin_policy}",
+                            f"margin-condition={margin_condition}"], cwd=tmp, stdout=subprocess.PIPE,
+                           stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"ref_window failed ({r.returncode}):\n{r.stdout[-2000:]}")
+        n, width = np.fromfile(op, np.uint32, 2)
+        return np.fromfile(op, np.float32, offset=8).reshape(int(n), int(width)) if n else np.zeros((0, base.shape[1] * length), np.float32)
 
 
 REF_EST_BIN = os.path.join(HERE, "_ref", "ref_estimator")

@@ -42,6 +42,20 @@ def test_matrix_product_matches_reference_golden(eng):
         assert np.array_equal(bits(got), bits(want)), name
 
 
+@pytest.mark.parametrize("name", ["lda16x9", "causal7x3", "lookahead5x6", "wide3x17"])
+def test_window_and_product_match_reference_golden(eng, name):
+    """tests/golden/lda_window.npz: the reference's own sliding-window node (Signal::DelayNode, wired as lda.flow)
+    followed by its own matrix product -- the device front end against both, bit for bit."""
+    z = np.load(os.path.join(GOLDEN_DIR, "lda_window.npz"))
+    base, fo, m = z[name + "_base"], z[name + "_frame_offsets"], z[name + "_matrix"]
+    length, right = int(z[name + "_length"]), int(z[name + "_right"])
+    eng.set_lda(m, base.shape[1], length, right)
+    assert np.array_equal(bits(device_lda(eng, base, fo, m.shape[0])), bits(z[name + "_out"]))
+    eye = np.eye(base.shape[1] * length, dtype=np.float32)
+    eng.set_lda(eye, base.shape[1], length, right)
+    assert np.array_equal(bits(device_lda(eng, base, fo, eye.shape[0])), bits(z[name + "_window"]))
+
+
 @pytest.mark.parametrize("base_dim,length,right,D", [(16, 9, 4, 45), (16, 11, 5, 45), (7, 3, 0, 5), (40, 1, 0, 40),
                                                      (33, 17, 16, 128)])
 def test_windowed_lda_matches_oracle(eng, oracle, base_dim, length, right, D):

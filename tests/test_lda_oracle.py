@@ -1,5 +1,6 @@
 """CPU: the front end restatement (oracle/gmm_oracle.c orc_lda / orc_matrix_vector) against the golden outputs of
-the reference's Math::Matrix<f32> * Math::Vector<f32> and, where it is built, against that binary itself."""
+the reference's Math::Matrix<f32> * Math::Vector<f32> and of its sliding-window node (Signal::DelayNode in a
+Flow::Network wired as share/lda.flow) and, where they are built, against those binaries themselves."""
 import os
 
 import numpy as np
@@ -50,3 +51,31 @@ def test_lda_equals_window_then_product(oracle):
         b, e = fo[s], fo[s + 1]
         win = np.stack([np.concatenate([base[min(max(t + r, b), e - 1)] for r in range(-4, 5)]) for t in range(b, e)])
         assert np.array_equal(bits(out[b:e]), bits(oracle.matrix_vector(m, win)))
+
+
+WINDOW_CASES = ("lda16x9", "causal7x3", "lookahead5x6", "wide3x17")
+
+
+@pytest.mark.parametrize("name", WINDOW_CASES)
+def test_window_and_product_match_reference_golden(oracle, name):
+    """tests/golden/lda_window.npz: the reference's own window node followed by its own matrix product, per segment."""
+    z = np.load(os.path.join(GOLDEN_DIR, "lda_window.npz"))
+    base, fo, m = z[name + "_base"], z[name + "_frame_offsets"], z[name + "_matrix"]
+    length, right = int(z[name + "_length"]), int(z[name + "_right"])
+    eye = np.eye(base.shape[1] * length, dtype=np.float32)                    # output = the window itself
+    assert np.array_equal(bits(oracle.lda(base, fo, length, right, eye)), bits(z[name + "_window"]))
+    assert np.array_equal(bits(oracle.lda(base, fo, length, right, m)), bits(z[name + "_out"]))
+
+
+def test_window_matches_compiled_reference_node(oracle):
+    """Fresh random shapes through the unmodified Signal::DelayNode (segments shorter than the window included)."""
+    if not oracle.ref_window_available():
+        pytest.skip("oracle/_ref/ref_window not built")
+    rng = np.random.default_rng(7)
+    for _ in range(40):
+        T, bd, length = int(rng.integers(1, 40)), int(rng.integers(1, 9)), int(rng.integers(1, 14))
+        right = int(rng.integers(0, length))
+        base = rng.standard_normal((T, bd)).astype(np.float32)
+        want = oracle.run_ref_window(base, length, right)
+        got = oracle.lda(base, [0, T], length, right, np.eye(bd * length, dtype=np.float32))
+        assert want.shape == got.shape and np.array_equal(bits(got), bits(want)), (T, bd, length, right)
