@@ -272,6 +272,26 @@ int gmm_score_baum_welch_accumulate_host(gmm_handle* h, uint32_t nSeg, const uin
                                          const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
                                          const uint32_t* initialState, const float* finalWeight, double* totalScore);
 
+/* ---- the same two consumers for arcs that carry LABELS (what rasr/GpuAligner.cc binds) ----------------------------
+ * The reference's alignment items name the arc's label -- an allophone state (Aligner.cc:205 / :185 store a->input_) --
+ * and score it through acousticModel->emissionIndex(label) (Aligner.cc:225): several labels of one automaton may be
+ * tied to ONE mixture, and the items keep them apart (Speech/Alignment.cc combineItems merges per (time, label)).
+ * Here: arcLabel[a] is a SEGMENT-LOCAL label slot, labelMixture[labelOffsets[s] + slot] the mixture that scores it
+ * (the same mixture may appear under several slots).  pathLabel[t] = slot of the arc taken at frame t (0xFFFFFFFF: no
+ * final state reached); column j of row t of `weights` = posterior of label slot j.  Everything else as
+ * gmm_score_align_host / gmm_score_baum_welch_host; the scores are bit for bit those of the emission-index calls
+ * (a label's column is its mixture's column). */
+int gmm_score_align_labels_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                                const uint32_t* arcLabel, const float* arcWeight, const uint32_t* initialState,
+                                const float* finalWeight, const uint32_t* labelOffsets, const uint32_t* labelMixture,
+                                uint32_t* pathLabel, uint32_t* pathState, float* pathScore);
+int gmm_score_baum_welch_labels_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                     const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                                     const uint32_t* arcLabel, const float* arcWeight, const uint32_t* initialState,
+                                     const float* finalWeight, const uint32_t* labelOffsets,
+                                     const uint32_t* labelMixture, float* weights, size_t ldW, double* totalScore);
+
 /* ---- training E-step on the device ----------------------------------------------------
  * Replaces Speech::KeyedEstimator::processAlignedFeature (src/Speech/KeyedEstimator.cc:108-121) and
  * Mm::AbstractMixtureSetEstimator::accumulate (src/Mm/AbstractMixtureSetEstimator.cc:117-147): for every frame t

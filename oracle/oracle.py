@@ -387,9 +387,10 @@ def ref_aligner_available() -> bool:
     return os.path.exists(REF_ALIGNER_BIN) and os.access(REF_ALIGNER_BIN, os.X_OK)
 
 
-def run_ref_aligner(scores, automata, i=0, *, mode="viterbi", workdir=None):
+def run_ref_aligner(scores, automata, i=0, *, mode="viterbi", emission_of_label=None, workdir=None):
     """Run the unmodified reference Search::Aligner (oracle/ref_build/ref_aligner.cc) on segment i's automaton over the
-    score rows `scores` [frames x emissions], unpruned.
+    score rows `scores` [frames x emissions], unpruned.  With emission_of_label the arcs' "emission" field is a label
+    the acoustic model maps to an emission (state tying); the items then name labels.
     -> dict(time u32 [n], emission u32 [n], weight f64 [n], score f32 (Aligner::alignmentScore()),
             total f32 (baum-welch: totalInv of Fsa::posterior64 = MINUS the total, Aligner.cc:757-772))."""
     if not ref_aligner_available():
@@ -410,6 +411,12 @@ def run_ref_aligner(scores, automata, i=0, *, mode="viterbi", workdir=None):
             scores.tofile(f)
         cmd = [REF_ALIGNER_BIN, f"in={ip}", f"out={op}", f"mode={mode}", "--*.aligner.min-acoustic-pruning=1e30",
                "--*.aligner.max-acoustic-pruning=1e30"]
+        if emission_of_label is not None:   # arcs carry labels; the acoustic model ties label -> emission
+            lp = os.path.join(tmp, "labels.bin")
+            with open(lp, "wb") as f:
+                np.asarray([len(emission_of_label)], np.uint32).tofile(f)
+                np.ascontiguousarray(emission_of_label, np.uint32).tofile(f)
+            cmd.append(f"labels={lp}")
         r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"ref_aligner failed ({r.returncode}):\n{r.stdout[-2000:]}")

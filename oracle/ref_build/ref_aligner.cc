@@ -12,10 +12,12 @@
 //     HEADERS parse; no XML parsing TU is compiled, stubs/align_stubs.cc aborts in the few word-lattice symbols
 //     (Aligner::WordLatticeBuilder) the aligner's object file refers to and this driver never reaches.
 //
-// usage: ref_aligner in=<file> out=<prefix> mode=viterbi|baum-welch
+// usage: ref_aligner in=<file> out=<prefix> mode=viterbi|baum-welch [labels=<file>]
 //            --*.aligner.min-acoustic-pruning=1e30 --*.aligner.max-acoustic-pruning=1e30   (unpruned, one pass)
 //   in : u32 T, M, S, A, initial; u32 arcOffsets[S+1]; u32 arcTarget[A]; u32 arcEmission[A]; f32 arcWeight[A];
 //        f32 finalWeight[S] (+inf: not final); f32 scores[T*M]
+//   labels (optional): u32 nLabels; u32 emissionOfLabel[nLabels] -- the arcs' "emission" field is then a LABEL (an
+//        allophone state in RASR) the acoustic model ties to an emission; items name the label, as in RASR
 //   out: <prefix>.items.bin = u32 n, n x {u32 time, u32 emission, f64 weight} in the order Alignment holds them;
 //        <prefix>.score.f32 = {alignmentScore(), total of the posterior automaton (baum-welch) or the same (viterbi)}
 #include <cmath>
@@ -53,11 +55,12 @@ public:
 };
 
 class TableAcousticModel : public Am::AcousticModel {
-    u32 n_;
+    u32              n_;
+    std::vector<u32> emissionOfLabel_;  // empty: labels are emission indices
 
 public:
-    TableAcousticModel(const Core::Configuration& c, u32 n)
-            : Core::Component(c), Am::AcousticModel(c), n_(n) {}
+    TableAcousticModel(const Core::Configuration& c, u32 n, const std::vector<u32>& emissionOfLabel)
+            : Core::Component(c), Am::AcousticModel(c), n_(n), emissionOfLabel_(emissionOfLabel) {}
     virtual void load(Mode) {}
     virtual void getDependencies(Core::DependencySet&) const {}
     virtual Core::Ref<Am::TransducerBuilder> createTransducerBuilder() const {
@@ -97,7 +100,7 @@ public:
         abort();
     }
     virtual EmissionIndex emissionIndex(Am::AllophoneStateIndex i) const {
-        return i;  // labels of the automaton are emission indices
+        return emissionOfLabel_.empty() ? i : emissionOfLabel_[i];  // state tying: several labels, one emission
     }
     virtual EmissionIndex nEmissions() const {
         return n_;
@@ -187,7 +190,15 @@ public:
 
         // unpruned: one pass at a threshold nothing exceeds (Aligner.cc:584-611); min-weight 0 keeps every item
         // (the caller passes --*.aligner.min-acoustic-pruning=1e30 --*.aligner.max-acoustic-pruning=1e30)
-        Core::Ref<const Am::AcousticModel> am(new TableAcousticModel(select("acoustic-model"), M));
+        std::vector<u32> emissionOfLabel;
+        if (!arg("labels").empty()) {  // u32 nLabels; u32 emissionOfLabel[nLabels]: arcs then carry labels
+            FILE* lf = fopen(arg("labels").c_str(), "rb");
+            u32   nLabels = 0;
+            if (!lf || fread(&nLabels, 4, 1, lf) != 1 || !readArray(lf, emissionOfLabel, nLabels))
+                return 4;
+            fclose(lf);
+        }
+        Core::Ref<const Am::AcousticModel> am(new TableAcousticModel(select("acoustic-model"), M, emissionOfLabel));
         Search::Aligner                    aligner(select("aligner"));
         aligner.selectMode(mode == "viterbi" ? Search::Aligner::modeViterbi : Search::Aligner::modeBaumWelch);
         aligner.setModel(modelRef, am);

@@ -75,3 +75,30 @@ def linear_hmm(emissions, loop=3.0, forward=0.0, skip=30.0, exit_weight=0.0):
             arcs.append((s + 2, int(emissions[s + 1]), float(skip)))
         states.append(arcs)
     return states, 0, {n: float(exit_weight)}
+
+
+def label_slots(automata: AlignmentAutomata, emission_of_label):
+    """Arcs that carry LABELS (RASR: allophone states, `arc_emission` holds the label id) for the label entry points
+    (gmm_score_align_labels_host / gmm_score_baum_welch_labels_host): per segment the distinct labels in order of first
+    use by an arc become slots.  `emission_of_label[label]` = the mixture the acoustic model ties the label to
+    (Am::AcousticModel::emissionIndex).
+    -> (automata whose arc_emission is the segment-local slot, label_offsets [segments+1], label_ids, label_mixture)."""
+    a = automata
+    tie = np.asarray(emission_of_label, np.uint32)
+    slots = np.empty_like(a.arc_emission)
+    offsets, ids = [0], []
+    for i in range(a.segments):
+        s0, s1 = int(a.state_offsets[i]), int(a.state_offsets[i + 1])
+        a0, a1 = int(a.arc_offsets[s0]), int(a.arc_offsets[s1])
+        slot_of = {}
+        for k in range(a0, a1):
+            lab = int(a.arc_emission[k])
+            if lab not in slot_of:
+                slot_of[lab] = len(slot_of)
+                ids.append(lab)
+            slots[k] = slot_of[lab]
+        offsets.append(len(ids))
+    ids = np.asarray(ids, np.uint32)
+    out = AlignmentAutomata(a.state_offsets, a.arc_offsets, a.arc_target, slots, a.arc_weight, a.initial_state,
+                            a.final_weight)
+    return out, np.asarray(offsets, np.uint32), ids, tie[ids] if ids.size else np.zeros(0, np.uint32)

@@ -56,6 +56,8 @@ SYMBOLS = [
     ("gmm_align_ordered_count", C.c_uint64, [_vp]),
     ("gmm_score_align_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
     ("gmm_score_align_accumulate_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
+    ("gmm_score_align_labels_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 12),
+    ("gmm_score_baum_welch_labels_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10 + [_sz, _vp]),
     ("gmm_accumulator_create", _i, [_vp, _u32, _vp, _i, C.c_double]),
     ("gmm_accumulator_reset", _i, [_vp]),
     ("gmm_accumulate_device", _i, [_vp, _u32, _vp, _vp, _vp, _vp]),
@@ -402,6 +404,42 @@ class Engine:
             self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets), _ptr(a.arc_offsets), _ptr(a.arc_target),
             _ptr(a.arc_emission), _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight), _ptr(w), int(ld_w),
             _ptr(total)), "gmm_score_baum_welch_host")
+        return w, total
+
+    def score_align_labels_host(self, frame_offsets, x, automata, label_offsets, label_mixture, want_states=True):
+        """As score_align_host for arcs that carry labels: automata.arc_emission holds segment-local label slots,
+        label_mixture[label_offsets[s] + slot] the mixture scoring the label.  -> (path_label, path_state, score)."""
+        fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
+        a = automata
+        x = _np(x, np.float32)
+        if x.ndim != 2 or x.shape != (n_frames, self._in_dim(self.D)):
+            raise ValueError(f"features must be [{n_frames}, {self._in_dim(self.D)}]")
+        lo, lm = _np(label_offsets, np.uint32), _np(label_mixture, np.uint32)
+        lab = np.empty(n_frames, np.uint32)
+        st = np.empty(n_frames, np.uint32) if want_states else None
+        sc = np.empty(max(n_seg, 0), np.float32)
+        self._check(self._lib.gmm_score_align_labels_host(
+            self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets), _ptr(a.arc_offsets), _ptr(a.arc_target),
+            _ptr(a.arc_emission), _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight), _ptr(lo), _ptr(lm),
+            _ptr(lab), _ptr(st), _ptr(sc)), "gmm_score_align_labels_host")
+        return lab, st, sc
+
+    def score_baum_welch_labels_host(self, frame_offsets, x, automata, label_offsets, label_mixture):
+        """As score_baum_welch_host for arcs that carry labels -> (weights [frames, longest label list], totals);
+        column j of a frame's row = posterior of label slot j of its segment."""
+        fo, n_seg, n_frames = self._align_args(frame_offsets, automata)
+        a = automata
+        x = _np(x, np.float32)
+        if x.ndim != 2 or x.shape != (n_frames, self._in_dim(self.D)):
+            raise ValueError(f"features must be [{n_frames}, {self._in_dim(self.D)}]")
+        lo, lm = _np(label_offsets, np.uint32), _np(label_mixture, np.uint32)
+        ld_w = max(1, int(np.max(np.diff(lo)))) if n_seg else 1
+        w = np.zeros((n_frames, ld_w), np.float32)
+        total = np.empty(max(n_seg, 0), np.float64)
+        self._check(self._lib.gmm_score_baum_welch_labels_host(
+            self._h, n_seg, _ptr(fo), _ptr(x), _ptr(a.state_offsets), _ptr(a.arc_offsets), _ptr(a.arc_target),
+            _ptr(a.arc_emission), _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight), _ptr(lo), _ptr(lm),
+            _ptr(w), ld_w, _ptr(total)), "gmm_score_baum_welch_labels_host")
         return w, total
 
     @property

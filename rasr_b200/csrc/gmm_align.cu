@@ -81,6 +81,7 @@ struct AlignParams {
     uint32_t*       pathEmission;
     uint32_t*       pathState;
     float*          pathScore;
+    uint32_t        slotOutput;  // pathEmission receives the arc's position in its segment's emission list, not the id
 };
 
 // The reference's search space, literally (Aligner.cc:132-158 activateOrUpdateStateHypothesisViterbi, 190-239
@@ -217,7 +218,7 @@ __global__ void __launch_bounds__(256) align_generic_kernel(const AlignParams p)
                 if (s != kNoArc) {
                     const uint32_t a = p.back[sg.back0 + (size_t)t * S + s];
                     st               = s;
-                    em               = p.inEm[a];
+                    em               = p.slotOutput ? p.inEmSlot[a] : p.inEm[a];
                     s                = p.inSrc[a];
                 }
                 p.pathEmission[sg.frame0 + t] = em;
@@ -508,7 +509,7 @@ __global__ void __launch_bounds__(1024) align_ranked_kernel(const AlignParams p)
                 for (uint32_t t = tLast + 1; t-- > tFirst;) {
                     const uint32_t a              = p.back[sg.back0 + (size_t)t * S + s];
                     dState[t]                     = s;
-                    p.pathEmission[sg.frame0 + t] = emIds[tabEm[a]];
+                    p.pathEmission[sg.frame0 + t] = p.slotOutput ? (uint32_t)tabEm[a] : emIds[tabEm[a]];
                     s                             = tabSK[a] >> 16;
                 }
             }
@@ -581,7 +582,7 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
                      const uint32_t** d_pathEmission, bool compact, uint32_t nEmissions, AlignDeferred* defer,
-                     const AlignLists* lists) {
+                     const AlignLists* lists, bool slotOutput) {
     if (defer)
         defer->pending = false;
     if (d_pathEmission)
@@ -800,6 +801,7 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     p.pathEmission = (uint32_t*)(d + oPe);
     p.pathState    = (uint32_t*)(d + oPs);
     p.pathScore    = (float*)(d + oSc);
+    p.slotOutput   = slotOutput ? 1u : 0u;
     void (*kernel)(AlignParams) = inFlight == 8   ? align_ranked_kernel<8>
                                   : inFlight == 4 ? align_ranked_kernel<4>
                                   : inFlight == 2 ? align_ranked_kernel<2>

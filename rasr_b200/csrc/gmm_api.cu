@@ -855,11 +855,20 @@ struct BwRequest {
     double* total;    // host [nSeg] or NULL
 };
 
+// Callers whose arcs carry a LABEL that is not the emission index (RASR: allophone states, several of which may be
+// tied to one mixture): arcEmission then holds segment-local label slots, and mixture[offsets[s] + slot] is the
+// mixture that scores the label.  The label lists take the place of the emission lists: one column per label.
+struct LabelMap {
+    const uint32_t* offsets;  // [nSeg + 1]
+    const uint32_t* mixture;
+};
+
 static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t s1, const uint32_t* frameOffsets,
                            const float* x, const uint32_t* stateOffsets, const uint32_t* arcOffsets,
                            const uint32_t* arcTarget, const uint32_t* arcEmission, const float* arcWeight,
                            const uint32_t* initialState, const float* finalWeight, uint32_t* pathEmission,
-                           uint32_t* pathState, float* pathScore, AlignDeferred* fin, const BwRequest* bw = nullptr) {
+                           uint32_t* pathState, float* pathScore, AlignDeferred* fin, const BwRequest* bw = nullptr,
+                           const LabelMap* labels = nullptr) {
     const size_t   devLd = h->M;
     const uint32_t f0 = frameOffsets[s0], T = frameOffsets[s1] - f0, n = s1 - s0;
     static const bool trace = getenv("GMM_TRACE") != nullptr;
@@ -892,8 +901,40 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
     bool                  compact = false, haveLists = false;
     size_t                ldUse   = devLd;
     const char*           env     = getenv("GMM_ALIGN_SUBSET");
+    std::vector<uint32_t> arcMixture;  // label callers: the mixture behind every arc's label
+    if (labels) {
+        const uint32_t l0 = labels->offsets[s0], nGroupArcs = ao[so[n]];
+        emOff.resize(n + 1);
+        for (uint32_t i = 0; i <= n; ++i) {
+            if (labels->offsets[s0 + i] < (i ? labels->offsets[s0 + i - 1] : l0)) {
+                h->setError("gmm_score_align_labels: label offsets not ascending");
+                return GMM_ERR_ARG;
+            }
+            emOff[i] = labels->offsets[s0 + i] - l0;
+        }
+        emList.assign(labels->mixture + l0, labels->mixture + l0 + emOff[n]);
+        for (uint32_t m : emList)
+            if (m >= h->M) {
+                h->setError("gmm_score_align_labels: label mapped to a mixture >= M");
+                return GMM_ERR_ARG;
+            }
+        lists.arcSlot.assign(nGroupArcs ? arcEmission + a0 : nullptr, nGroupArcs ? arcEmission + a0 + nGroupArcs : nullptr);
+        arcMixture.resize(nGroupArcs);
+        for (uint32_t i = 0; i < n; ++i) {
+            const uint32_t len = emOff[i + 1] - emOff[i];
+            for (uint32_t a = ao[so[i]]; a < ao[so[i + 1]]; ++a) {
+                if (lists.arcSlot[a] >= len) {
+                    h->setError("gmm_score_align_labels: arc label outside its segment's label list");
+                    return GMM_ERR_ARG;
+                }
+                arcMixture[a] = emList[emOff[i] + lists.arcSlot[a]];
+            }
+        }
+        haveLists = true;
+    }
+    const uint32_t* arcEm = labels ? arcMixture.data() : arcEmission ? arcEmission + a0 : nullptr;
     if (T && gmm_tc_subset_capable(h) && !(env && env[0] == '0') && arcEmission &&
-        gmm_align_emission_lists(h, n, so.data(), ao.data(), arcEmission + a0, h->M, lists)) {
+        (haveLists || gmm_align_emission_lists(h, n, so.data(), ao.data(), arcEm, h->M, lists))) {
         haveLists = true;
         const uint32_t mpt = h->tensor.mixPerTile;
         uint32_t       maxList = 0;
@@ -921,8 +962,7 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
     traceMark(h, (int)s0, "scored");
     tr[3] = clk();
     if (bw) {
-        if (!haveLists && !gmm_align_emission_lists(h, n, so.data(), ao.data(), arcEmission ? arcEmission + a0 : nullptr,
-                                                    h->M, lists)) {
+        if (!haveLists && !gmm_align_emission_lists(h, n, so.data(), ao.data(), arcEm, h->M, lists)) {
             h->setError("gmm_score_baum_welch: arc offsets not ascending or emission index >= M");
             return GMM_ERR_ARG;
         }
@@ -939,7 +979,7 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
         if ((rc = h->reserve(SCR_POST, (size_t)std::max(1u, T) * ldP * 4, &dp)))
             return rc;
         if ((rc = gmm_bw_launch(h, n, fo.data(), (const float*)ds, ldUse, so.data(), ao.data(),
-                                arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
+                                arcTarget ? arcTarget + a0 : nullptr, arcEm,
                                 arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0, (float*)dp, ldP,
                                 nullptr, compact, h->M, &lists, false, &dev)))
             return rc;
@@ -959,11 +999,11 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
         return GMM_OK;
     }
     if ((rc = gmm_align_launch(h, n, fo.data(), (const float*)ds, ldUse, so.data(), ao.data(),
-                               arcTarget ? arcTarget + a0 : nullptr, arcEmission ? arcEmission + a0 : nullptr,
+                               arcTarget ? arcTarget + a0 : nullptr, arcEm,
                                arcWeight ? arcWeight + a0 : nullptr, initialState + s0, finalWeight + st0,
                                pathEmission ? pathEmission + f0 : nullptr, pathState ? pathState + f0 : nullptr,
                                pathScore ? pathScore + s0 : nullptr, &dPath, compact, h->M, fin,
-                               haveLists ? &lists : nullptr)))
+                               haveLists ? &lists : nullptr, labels != nullptr)))
         return rc;
     traceMark(h, (int)s0, "aligned");
     // the aligned frames go straight into the estimators: the path is the per-frame mixture (kNoArc: skip)
@@ -980,9 +1020,13 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
                          const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
                          const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                          const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
-                         const BwRequest* bw = nullptr) {
+                         const BwRequest* bw = nullptr, const LabelMap* labels = nullptr) {
     if (!h)
         return GMM_ERR_ARG;
+    if (labels && (!labels->offsets || (nSeg && labels->offsets[nSeg] > labels->offsets[0] && !labels->mixture))) {
+        h->setError("gmm_score_align_labels: NULL label list");
+        return GMM_ERR_ARG;
+    }
     if (!h->floatValid) {
         h->setError("gmm_score_align: no float model uploaded");
         return GMM_ERR_ARG;
@@ -1040,7 +1084,8 @@ static int scoreAlign(gmm_handle* h, bool accumulate, uint32_t nSeg, const uint3
                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tw0).count());
         if (rc == GMM_OK)
             rc = scoreAlignGroup(h, accumulate, s0, s1, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission,
-                                 arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore, &fin[lane], bw);
+                                 arcWeight, initialState, finalWeight, pathEmission, pathState, pathScore, &fin[lane], bw,
+                                 labels);
         if (twoLanes)
             lane = (lane + 1) % nLanes;
         s0 = s1;
@@ -1087,6 +1132,16 @@ int gmm_score_align_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t
                                     float* pathScore) {
     return scoreAlign(h, true, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
                       initialState, finalWeight, pathEmission, pathState, pathScore);
+}
+
+int gmm_score_align_labels_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                                const uint32_t* arcLabel, const float* arcWeight, const uint32_t* initialState,
+                                const float* finalWeight, const uint32_t* labelOffsets, const uint32_t* labelMixture,
+                                uint32_t* pathLabel, uint32_t* pathState, float* pathScore) {
+    const LabelMap labels = {labelOffsets, labelMixture};
+    return scoreAlign(h, false, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcLabel, arcWeight,
+                      initialState, finalWeight, pathLabel, pathState, pathScore, nullptr, &labels);
 }
 
 // ---- Baum-Welch alignment ---------------------------------------------------------------------------------------
@@ -1141,6 +1196,21 @@ int gmm_score_baum_welch_host(gmm_handle* h, uint32_t nSeg, const uint32_t* fram
     const BwRequest bw = {weights, ldW, totalScore};
     return scoreAlign(h, false, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcEmission, arcWeight,
                       initialState, finalWeight, nullptr, nullptr, nullptr, &bw);
+}
+
+int gmm_score_baum_welch_labels_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
+                                     const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,
+                                     const uint32_t* arcLabel, const float* arcWeight, const uint32_t* initialState,
+                                     const float* finalWeight, const uint32_t* labelOffsets,
+                                     const uint32_t* labelMixture, float* weights, size_t ldW, double* totalScore) {
+    if (h && nSeg && frameOffsets && frameOffsets[nSeg] && !weights) {
+        h->setError("gmm_score_baum_welch_labels: weights is NULL");
+        return GMM_ERR_ARG;
+    }
+    const BwRequest bw     = {weights, ldW, totalScore};
+    const LabelMap  labels = {labelOffsets, labelMixture};
+    return scoreAlign(h, false, nSeg, frameOffsets, x, stateOffsets, arcOffsets, arcTarget, arcLabel, arcWeight,
+                      initialState, finalWeight, nullptr, nullptr, nullptr, &bw, &labels);
 }
 
 int gmm_score_baum_welch_accumulate_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,

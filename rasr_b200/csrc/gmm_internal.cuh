@@ -240,7 +240,8 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t* arcEmission, const float* arcWeight, const uint32_t* initialState,
                      const float* finalWeight, uint32_t* pathEmission, uint32_t* pathState, float* pathScore,
                      const uint32_t** d_pathEmission = nullptr, bool compact = false, uint32_t nEmissions = 0,
-                     struct AlignDeferred* defer = nullptr, const struct AlignLists* lists = nullptr);
+                     struct AlignDeferred* defer = nullptr, const struct AlignLists* lists = nullptr,
+                     bool slotOutput = false);  // slotOutput: pathEmission = position in the segment's list (labels)
 // With `defer` gmm_align_launch returns once everything is enqueued; gmm_align_finish (same lane active) copies the
 // outputs to the host arrays and waits.
 struct AlignDeferred {

@@ -8,7 +8,9 @@ rasr_b200.align.AlignmentAutomata -- and what the reference answered per segment
   vit_score [segments] f32    Aligner::alignmentScore() in mode viterbi
   bw_item_offsets, bw_time (segment-local), bw_emission, bw_weight f64   the items of Speech::Alignment in mode baum-welch
   bw_score [segments] f32     Aligner::alignmentScore() in mode baum-welch (f32 log-semiring forward potential)
-  bw_total_inv [segments] f32 totalInv of Fsa::posterior64: MINUS the f64 forward-backward total, rounded once"""
+  bw_total_inv [segments] f32 totalInv of Fsa::posterior64: MINUS the f64 forward-backward total, rounded once
+aln_tied also holds emission_of_label: its arcs carry labels (arc_emission = label id, vit_emission / bw_emission name
+labels) which the acoustic model ties to the columns of `scores`."""
 import os
 import sys
 
@@ -80,7 +82,28 @@ def case_long():
     return lens, rng.uniform(20, 120, (400, M)).astype(np.float32), segs
 
 
-CASES = {"aln_linear": case_linear, "aln_graphs": case_graphs, "aln_ties": case_ties, "aln_edges": case_edges,
+def case_tied():
+    """State tying: arcs carry LABELS (allophone states), the acoustic model maps several labels to one emission, and
+    the reference's items name the label (Aligner.cc:185 / :205 store a->input_).  Parallel arcs between the same two
+    states whose labels share an emission, integer weights in some segments (ties between such arcs)."""
+    rng = np.random.default_rng(106)
+    M, n_labels, lens = 12, 40, [6, 14, 3, 25, 9, 18, 1, 11]
+    tie = rng.integers(0, M, n_labels).astype(np.uint32)
+    segs = []
+    for k, _ in enumerate(lens):
+        states, ini, fin = random_graph(rng, int(rng.integers(2, 16)), n_labels, integer_weights=bool(k & 1))
+        for arcs in states:                       # duplicate some arcs under another label of the same emission
+            for (tg, lab, w) in list(arcs):
+                same = np.flatnonzero(tie == tie[lab])
+                if same.size > 1 and rng.random() < 0.3:
+                    arcs.append((tg, int(rng.choice(same)), w if rng.random() < 0.5 else w + 1.0))
+        segs.append((states, ini, fin))
+    scores = np.where(rng.random((sum(lens), M)) < 0.5, rng.integers(0, 4, (sum(lens), M)),
+                      rng.uniform(0, 4, (sum(lens), M))).astype(np.float32)
+    return lens, scores, segs, tie
+
+
+CASES = {"aln_tied": case_tied, "aln_linear": case_linear, "aln_graphs": case_graphs, "aln_ties": case_ties, "aln_edges": case_edges,
          "aln_long": case_long}
 
 
@@ -88,7 +111,8 @@ def main():
     assert O.build_ref() and O.ref_aligner_available(), "needs /root/reference (build container)"
     out_dir = os.path.dirname(os.path.abspath(__file__))
     for name, make in CASES.items():
-        lens, scores, segs = make()
+        lens, scores, segs, *tie = make()
+        tie = tie[0] if tie else None
         au = AlignmentAutomata.from_arc_lists(segs)
         fo = np.cumsum([0] + list(lens)).astype(np.uint32)
         vit_em = np.full(int(fo[-1]), 0xFFFFFFFF, np.uint32)
@@ -96,12 +120,12 @@ def main():
         io, it, ie, iw = [0], [], [], []
         for i in range(len(lens)):
             rows = scores[fo[i]:fo[i + 1]]
-            v = O.run_ref_aligner(rows, au, i, mode="viterbi")
+            v = O.run_ref_aligner(rows, au, i, mode="viterbi", emission_of_label=tie)
             vit_sc[i] = v["score"]
             if v["time"].size:
                 assert np.array_equal(np.sort(v["time"]), np.arange(lens[i])) and np.all(v["weight"] == 1.0)
                 vit_em[int(fo[i]) + v["time"]] = v["emission"]
-            b = O.run_ref_aligner(rows, au, i, mode="baum-welch")
+            b = O.run_ref_aligner(rows, au, i, mode="baum-welch", emission_of_label=tie)
             bw_sc[i], bw_tot[i] = b["score"], b["total"]
             it.append(b["time"]), ie.append(b["emission"]), iw.append(b["weight"])
             io.append(io[-1] + b["time"].size)
@@ -111,7 +135,8 @@ def main():
                             final_weight=au.final_weight, vit_emission=vit_em, vit_score=vit_sc,
                             bw_item_offsets=np.asarray(io, np.uint32), bw_time=np.concatenate(it).astype(np.uint32),
                             bw_emission=np.concatenate(ie).astype(np.uint32), bw_weight=np.concatenate(iw),
-                            bw_score=bw_sc, bw_total_inv=bw_tot)
+                            bw_score=bw_sc, bw_total_inv=bw_tot,
+                            **({"emission_of_label": tie} if tie is not None else {}))
         print(name, "ok: segments", len(lens), "frames", int(fo[-1]), "baum-welch items", io[-1], "viterbi scores", vit_sc[:4])
 
 

@@ -170,3 +170,74 @@ def test_score_and_align_from_host_features(eng, oracle):
         emr, str_, scr = oracle.viterbi_align(fo, so, au)
         assert np.array_equal(em, emr) and np.array_equal(st, str_)
         np.testing.assert_allclose(sc, scr, rtol=1e-4)
+
+
+@pytest.mark.parametrize("subset", ["0", "1"])
+def test_label_entry_points_keep_tied_labels_apart(eng, oracle, monkeypatch, subset):
+    """gmm_score_align_labels_host / gmm_score_baum_welch_labels_host: arcs carry labels (allophone states) of which
+    several are tied to one mixture; the path / the posterior columns name the LABEL, as the reference's alignment
+    items do (tests/golden/aln_tied.npz pins that behaviour of the oracle against the reference's own aligner).
+    Oracle: the restated aligner over this engine's scores with one column per label (a label's score is its
+    mixture's, Aligner.cc:225).  Over the compact and the full score block."""
+    from rasr_b200.align import label_slots
+    monkeypatch.setenv("GMM_ALIGN_SUBSET", subset)
+    ms = synth.make_model(M=300, K=8, D=20, seed=33)
+    rng = np.random.default_rng(33)
+    n_labels = 900
+    tie = rng.integers(0, ms.M, n_labels).astype(np.uint32)
+    tie[:40] = tie[40:80]                                            # labels k and k+40 share a mixture
+    lens = [120, 0, 35, 1, 260, 64]
+    fo = np.cumsum([0] + lens).astype(np.uint32)
+    x = synth.make_features(ms, int(fo[-1]), seed=34)
+    segs = []
+    for n in lens:
+        labs = rng.integers(0, 80, max(1, n // 3))                  # mostly from the tied range
+        states, ini, fin = linear_hmm(labs, loop=3.0, forward=0.0, skip=30.0)
+        for s_, arcs in enumerate(states):                          # a parallel arc under the twin label, same weight
+            for (tg, lab, w) in list(arcs):
+                if lab < 80 and rng.random() < 0.5:
+                    arcs.append((tg, (lab + 40) % 80, w))
+        segs.append((states, ini, fin))
+    au = AlignmentAutomata.from_arc_lists(segs)                      # arc_emission = label id
+    t = tables.float_tables(ms)
+    eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=capi.MODE_MAX,
+                     kernel=capi.KERNEL_TENSOR)
+    s, _ = eng.score_host(x, want_best=False)
+    per_label = np.ascontiguousarray(s[:, tie])
+    emo, sto, sco = oracle.viterbi_align(fo, per_label, au)
+    slots, lo, ids, mix = label_slots(au, tie)
+    lab, st, sc = eng.score_align_labels_host(fo, x, slots, lo, mix)
+    assert np.array_equal(bits(sc), bits(sco)) and np.array_equal(st, sto)
+    for i in range(len(lens)):
+        rows = slice(int(fo[i]), int(fo[i + 1]))
+        got = lab[rows]
+        want = emo[rows]
+        if sco[i] == FLT_MAX:
+            assert np.all(got == 0xFFFFFFFF)
+        else:
+            assert np.array_equal(ids[lo[i]:lo[i + 1]][got], want)   # slot -> label id
+    assert len(set(emo[emo < 80].tolist())) > 20                     # the tied range is really used
+
+    wo, lists, to = oracle.baum_welch_align(fo, per_label, au)
+    w, total = eng.score_baum_welch_labels_host(fo, x, slots, lo, mix)
+    for i in range(len(lens)):
+        rows = slice(int(fo[i]), int(fo[i + 1]))
+        assert np.array_equal(lists[i], ids[lo[i]:lo[i + 1]])       # same first-use order: columns line up
+        n = len(lists[i])
+        if to[i] == FLT_MAX:
+            assert total[i] == FLT_MAX and not w[rows, :n].any()
+            continue
+        assert abs(total[i] - to[i]) <= 1e-5 * max(1.0, abs(to[i]))
+        assert np.max(np.abs(w[rows, :n] - wo[i]), initial=0.0) <= 1e-4
+
+
+def test_label_entry_points_reject_bad_lists(eng):
+    ms = synth.make_model(M=20, K=2, D=8, seed=35)
+    t = tables.float_tables(ms)
+    eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=capi.MODE_MAX)
+    au = AlignmentAutomata.from_arc_lists([linear_hmm([0, 1, 2])])
+    x = np.zeros((4, 8), np.float32)
+    with pytest.raises(capi.GmmError):                               # slot 2 outside a list of two labels
+        eng.score_align_labels_host([0, 4], x, au, [0, 2], [3, 4])
+    with pytest.raises(capi.GmmError):                               # label tied to a mixture the model lacks
+        eng.score_align_labels_host([0, 4], x, au, [0, 3], [3, 4, 20])
