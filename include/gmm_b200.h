@@ -225,6 +225,12 @@ int gmm_align_device(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
 /* Segments (since gmm_create) whose alignment met an exact f32 tie and was therefore replayed in the reference's
  * hypothesis order by the ordered pass (see gmm_align.cu); all other segments have a unique best path. */
 uint64_t gmm_align_ordered_count(const gmm_handle* h);
+/* RASR hands its aligner the scorers of the SCALED feature scorer: Mm::FeatureScorerScaling multiplies every score
+ * by the acoustic model's scale before the aligner adds the transition weight (src/Mm/ScaledFeatureScorer.hh:62-64, one
+ * f32 product).  With a scale != 1 (default 1) every gmm_score_*align*_host / gmm_score_baum_welch*_host call rounds
+ * fl(scale * score) into its device-resident score block before the consumer reads it; gmm_score_host, gmm_score_device
+ * and the *_device consumers (the caller's own block) are not affected. */
+int gmm_set_consumer_score_scale(gmm_handle* h, float scale);
 /* Features (host, [frameOffsets[nSeg] x D]) -> float scorer of this handle -> alignment, scores stay in HBM. */
 int gmm_score_align_host(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets, const float* x,
                          const uint32_t* stateOffsets, const uint32_t* arcOffsets, const uint32_t* arcTarget,

@@ -30,6 +30,13 @@ const Core::ParameterBool GpuFeatureScorer::paramDensityAssignment(
         "src/Mm/AbstractMixtureSetEstimator.cc:377-393); otherwise it costs a second pass when first asked for",
         false);
 
+const Core::ParameterBool GpuFeatureScorer::paramDeferredScoring(
+        "deferred-scoring",
+        "send no batch to the GPU before a score of one of its frames is asked for (default: batches go out while the "
+        "caller is still handing in frames).  For segments whose scorers go to MmGpu::GpuAligner, which scores on the "
+        "device only what its automaton names: the full score matrix is then never computed",
+        false);
+
 // ---- score blocks ----------------------------------------------------------------------------------------
 
 GpuFeatureScorer::PinnedPool::~PinnedPool() {
@@ -169,6 +176,7 @@ GpuFeatureScorer::GpuFeatureScorer(const Core::Configuration& c, Core::Ref<const
           handle_(0),
           bufferSize_(paramBufferSize(c)),
           withBest_(paramDensityAssignment(c)),
+          deferred_(paramDeferredScoring(c)),
           pool_(new PinnedPool),
           nMixtures_(mixtureSet->nMixtures()),
           dimension_(mixtureSet->dimension()),
@@ -383,7 +391,8 @@ void GpuFeatureScorer::push(const Mm::FeatureVector& f) const {
     // is src/Nn/BatchFeatureScorer.cc:92-170): in streaming mode half a buffer at a time, in segment mode every
     // kSegmentBatch frames, so that the scores of a long segment are already on their way over the host link when the
     // first one is asked for.  The float engine only.
-    if (!quantized() && staging_->nFrames >= (bufferSize_ ? std::max<u32>(2, bufferSize_ / 2) : u32(kSegmentBatch)))
+    if (!quantized() && !deferred_ &&
+        staging_->nFrames >= (bufferSize_ ? std::max<u32>(2, bufferSize_ / 2) : u32(kSegmentBatch)))
         scoreBlock(*staging_, withBest_, true);
 }
 
@@ -403,7 +412,7 @@ Mm::FeatureScorer::Scorer GpuFeatureScorer::flush() const {
     require(!bufferEmpty());
     // the caller has begun to drain the buffer (end of the segment): the frames handed in since the last batch go to
     // the GPU now, so that they are on their way while the earlier frames' scores are being read
-    if (staging_ && staging_->nFrames > 0 && !quantized())
+    if (staging_ && staging_->nFrames > 0 && !quantized() && !deferred_)
         scoreBlock(*staging_, withBest_, true);
     ContextRef c = fifo_.front();
     fifo_.pop_front();

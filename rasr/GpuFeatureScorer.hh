@@ -33,8 +33,11 @@ struct gmm_handle;
 
 namespace MmGpu {
 
+class GpuAligner;
+
 class GpuFeatureScorer : public Mm::AssigningFeatureScorer {
     typedef Mm::AssigningFeatureScorer Precursor;
+    friend class GpuAligner;  // rasr/GpuAligner.hh: takes the frames behind the context scorers to the device itself
 
 public:
     enum Kind { kindMaximum, kindSum, kindQuantized, kindBatchInt };
@@ -45,6 +48,7 @@ public:
     static const Core::ParameterFloat paramMixtureWeightScale;  // as GaussDiagonalMaximumFeatureScorer.cc:37-39
     static const Core::ParameterFloat paramGaussianScale;       // as GaussDiagonalMaximumFeatureScorer.cc:41-43
     static const Core::ParameterBool  paramDensityAssignment;   // "with-density-assignment": training consumers
+    static const Core::ParameterBool  paramDeferredScoring;     // "deferred-scoring": nothing is scored before it is asked for
 
 protected:
     /** Page-locked host buffers, recycled: cudaMallocHost is a page-locking system call (milliseconds for the 18 MB of
@@ -84,6 +88,7 @@ protected:
 
     class Context : public AssigningContextScorer {
         friend class GpuFeatureScorer;
+        friend class GpuAligner;
         const GpuFeatureScorer* parent_;
         Core::Ref<ScoreBlock>   block_;
         u32                     row_;
@@ -184,6 +189,7 @@ private:
     gmm_handle*        handle_;
     u32                bufferSize_;
     bool               withBest_;
+    bool               deferred_;
     Core::Ref<PinnedPool> pool_;
     Mm::EmissionIndex  nMixtures_;
     Mm::ComponentIndex dimension_;

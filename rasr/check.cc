@@ -31,8 +31,15 @@
 #include <Mm/ScaledFeatureScorer.hh>
 #include <Mm/SimdFeatureScorer.hh>
 
+#include <Fsa/Static.hh>
+#include <Search/Aligner.hh>
+#include <Speech/Alignment.hh>
+
 #include <gmm_b200.h>
 
+#include <ref_table_am.hh>  // oracle/ref_build: an acoustic model whose state tying is a table (test double)
+
+#include "GpuAligner.hh"
 #include "GpuFeatureScorer.hh"
 #include "Module.hh"
 
@@ -185,6 +192,72 @@ Diff compare(const Result& a, const Result& b) {
     for (size_t i = 0; d.shape && i < a.best.size(); ++i)
         if (a.best[i] != b.best[i])
             ++d.nBest;
+    return d;
+}
+
+// the caller loop of Speech/AlignmentNode.cc:283-306 for the frames [t0, t1): the scorers a segment's aligner is fed
+std::vector<Mm::FeatureScorer::Scorer> segmentScorers(const Mm::FeatureScorer& fs, const std::vector<Mm::FeatureVector>& X,
+                                                      size_t t0, size_t t1) {
+    std::vector<Mm::FeatureScorer::Scorer> scorers;
+    fs.reset();
+    for (size_t t = t0; t < t1; ++t) {
+        if (fs.isBuffered() && !fs.bufferFilled())
+            fs.addFeature(X[t]);
+        else
+            scorers.push_back(fs.getScorer(X[t]));
+    }
+    if (fs.isBuffered())
+        while (!fs.bufferEmpty())
+            scorers.push_back(fs.flush());
+    return scorers;
+}
+
+// Left-to-right allophone-state acceptor with loop / forward / skip transitions over a label sequence: the shape
+// Speech::AllophoneStateGraphBuilder gives a pronunciation; arcs carry LABELS (allophone states).
+Fsa::ConstAutomatonRef linearModel(const std::vector<u32>& labels, f32 loop, f32 forward, f32 skip) {
+    Fsa::StaticAutomaton* model = new Fsa::StaticAutomaton();
+    model->setType(Fsa::TypeAcceptor);
+    model->setSemiring(Fsa::TropicalSemiring);
+    const u32 n = labels.size();
+    for (u32 s = 0; s <= n; ++s) {
+        Fsa::State* sp = new Fsa::State(s);
+        if (s > 0)
+            sp->newArc(s, Fsa::Weight(loop), labels[s - 1]);
+        if (s < n)
+            sp->newArc(s + 1, Fsa::Weight(forward), labels[s]);
+        if (s + 1 < n)
+            sp->newArc(s + 2, Fsa::Weight(skip), labels[s + 1]);
+        if (s == n)
+            sp->setFinal(Fsa::Weight(0.0));
+        model->setState(sp);
+    }
+    model->setInitialStateId(0);
+    return Fsa::ConstAutomatonRef(model);
+}
+
+struct AlignDiff {
+    size_t items, differing;  // items of the reference; (time, label) pairs whose weight differs by more than tol
+    double maxDiff;
+    bool   scoreBits;
+    double scoreRel;
+};
+
+// item sets per (time, label): the reference's order within a frame is that of an unstable sort on the weight
+AlignDiff compareAlignments(const Speech::Alignment& a, const Speech::Alignment& b, double tol) {
+    std::map<std::pair<u32, u32>, std::pair<double, double> > w;
+    for (Speech::Alignment::const_iterator i = a.begin(); i != a.end(); ++i)
+        w[std::make_pair(u32(i->time), u32(i->emission))].first += i->weight;
+    for (Speech::Alignment::const_iterator i = b.begin(); i != b.end(); ++i)
+        w[std::make_pair(u32(i->time), u32(i->emission))].second += i->weight;
+    AlignDiff d = {a.size(), 0, 0.0, false, 0.0};
+    for (std::map<std::pair<u32, u32>, std::pair<double, double> >::const_iterator i = w.begin(); i != w.end(); ++i) {
+        const double diff = std::fabs(i->second.first - i->second.second);
+        d.maxDiff         = std::max(d.maxDiff, diff);
+        d.differing += diff > tol;
+    }
+    const f32 sa = a.score(), sb = b.score();
+    d.scoreBits = !memcmp(&sa, &sb, 4);
+    d.scoreRel  = std::fabs(double(sa) - double(sb)) / std::max(1.0, std::fabs(double(sa)));
     return d;
 }
 
@@ -425,7 +498,96 @@ public:
                    batches[0] + passes[0]);
         }
 
-        // ---- 9: frames/s of the plugin path against the C-ABI call it wraps ------------------------------------------
+        // ---- 9: MmGpu::GpuAligner against the reference's own Search::Aligner, inside this process --------------------
+        // Segments of the feature file, each with a left-to-right acceptor over random allophone-state LABELS; the
+        // acoustic model ties 3 labels to every mixture, so parallel labels of one mixture occur (they must stay apart in
+        // the items).  The reference aligner runs unpruned on the scorers of the SAME engine through the scaling wrapper
+        // (scale 0.75): it reads the full score matrix from the host; the GPU aligner gets the same scorers from a
+        // deferred-scoring instance and must never cause a full scoring pass.  Viterbi: items and score bit for bit
+        // (kernel 1 = direct: also against the reference's own CPU scorer).  Baum-Welch: weights within 1e-4.
+        {
+            const u32        nLabels = 3 * M;
+            std::vector<u32> tie(nLabels);
+            for (u32 l = 0; l < nLabels; ++l)
+                tie[l] = l % M;  // labels l, l + M, l + 2M share mixture l
+            Core::Ref<const Am::AcousticModel> am(new TableAcousticModel(select("acoustic-model"), M, tie));
+            Core::Configuration                ac(config, "aligner");
+            ac.set(ac.getSelection() + ".min-acoustic-pruning", "1e30");  // one unpruned pass (Aligner.cc:584-611)
+            ac.set(ac.getSelection() + ".max-acoustic-pruning", "1e30");
+            const size_t segLen[] = {1, 0, 37, 120, 250, 400};
+            for (int mode = 0; mode < 2; ++mode)
+                for (int kernel = 1; kernel >= 0; --kernel) {
+                    Core::Configuration gc = scorerConfig("gpu", "gpu-diagonal-maximum", kernel, 0);
+                    Core::Configuration dc = scorerConfig("gpu-deferred", "gpu-diagonal-maximum", kernel, 0);
+                    dc.set(dc.getSelection() + ".deferred-scoring", "true");
+                    Core::Configuration rc = scorerConfig("ref", "diagonal-maximum", 0, 0);
+                    Core::Ref<Mm::FeatureScorer>       gpu = mm.createFeatureScorer(gc, ms), dfr = mm.createFeatureScorer(dc, ms);
+                    Core::Ref<Mm::ScaledFeatureScorer> gpuScaled = mm.createScaledFeatureScorer(gc, gpu);
+                    Core::Ref<Mm::ScaledFeatureScorer> dfrScaled = mm.createScaledFeatureScorer(dc, dfr);
+                    Core::Ref<Mm::ScaledFeatureScorer> cpuScaled = mm.createScaledFeatureScorer(rc, mm.createFeatureScorer(rc, ms));
+                    Search::Aligner   refAligner(ac), cpuAligner(ac);
+                    MmGpu::GpuAligner gpuAligner(ac);
+                    refAligner.selectMode(mode ? Search::Aligner::modeBaumWelch : Search::Aligner::modeViterbi);
+                    cpuAligner.selectMode(mode ? Search::Aligner::modeBaumWelch : Search::Aligner::modeViterbi);
+                    gpuAligner.selectMode(mode ? MmGpu::GpuAligner::modeBaumWelch : MmGpu::GpuAligner::modeViterbi);
+                    size_t  t0 = 0, nItems = 0, nDiffer = 0, nCpuDiffer = 0, nScoreBits = 0, nSeg = 0, nReached = 0;
+                    double  maxDiff = 0, maxRel = 0, secRef = 0, secGpu = 0;
+                    u32     seed = 12345u + 17u * kernel + mode;
+                    for (size_t si = 0; si < sizeof(segLen) / sizeof(segLen[0]) && t0 + segLen[si] <= X.size(); ++si) {
+                        const size_t     T = segLen[si];
+                        std::vector<u32> labels(std::max<size_t>(1, T / 3));
+                        for (size_t i = 0; i < labels.size(); ++i) {
+                            seed      = seed * 1664525u + 1013904223u;
+                            labels[i] = (seed >> 8) % nLabels;
+                        }
+                        if (labels.size() > 4) {
+                            labels[2] = labels[1];                  // a repeated label
+                            labels[3] = (labels[1] + M) % nLabels;  // and a sibling tied to the same mixture
+                        }
+                        Fsa::ConstAutomatonRef model = linearModel(labels, 3.0f, 0.0f, 30.0f);
+                        Speech::Alignment      a, b, c;
+                        double                 w0 = now();
+                        refAligner.setModel(model, am);
+                        refAligner.feed(segmentScorers(*gpuScaled, X, t0, t0 + T));
+                        refAligner.getAlignment(a);
+                        double w1 = now();
+                        gpuAligner.setModel(model, am);
+                        gpuAligner.feed(segmentScorers(*dfrScaled, X, t0, t0 + T));
+                        gpuAligner.getAlignment(b);
+                        double w2 = now();
+                        secRef += w1 - w0;
+                        secGpu += w2 - w1;
+                        AlignDiff d = compareAlignments(a, b, mode ? 1e-4 : 0.0);
+                        nItems += d.items;
+                        nDiffer += d.differing + (refAligner.reachedFinalState() != gpuAligner.reachedFinalState());
+                        nScoreBits += !d.scoreBits;
+                        maxDiff = std::max(maxDiff, d.maxDiff);
+                        maxRel  = std::max(maxRel, d.scoreRel);
+                        nReached += gpuAligner.reachedFinalState();
+                        if (kernel == 1) {  // direct kernel: bit-identical scores to the reference's CPU scorer
+                            cpuAligner.setModel(model, am);
+                            cpuAligner.feed(segmentScorers(*cpuScaled, X, t0, t0 + T));
+                            cpuAligner.getAlignment(c);
+                            AlignDiff e = compareAlignments(c, b, mode ? 1e-4 : 0.0);
+                            nCpuDiffer += e.differing + (mode == 0 && !e.scoreBits);
+                        }
+                        t0 += T;
+                        ++nSeg;
+                    }
+                    const MmGpu::GpuFeatureScorer* g  = dynamic_cast<const MmGpu::GpuFeatureScorer*>(dfr.get());
+                    const bool                     ok = nSeg > 0 && nReached > 0 && nDiffer == 0 && nCpuDiffer == 0 &&
+                                    (mode ? maxRel <= 1e-5 : nScoreBits == 0) && g->nBatches() == 0;
+                    char name[96];
+                    snprintf(name, sizeof name, "GpuAligner %s / %s kernel", mode ? "baum-welch" : "viterbi", kernel ? "direct" : "auto");
+                    report(name, ok,
+                           "segments=%zu reached=%zu items=%zu differing=%zu (vs CPU scorer: %zu) max|dw|=%.2g score %s; full "
+                           "scoring passes=%u; s: reference %.3f, gpu %.3f",
+                           nSeg, nReached, nItems, nDiffer, nCpuDiffer, maxDiff, mode ? (maxRel <= 1e-5 ? "rel<=1e-5" : "DIFFERS") : (nScoreBits ? "DIFFERS" : "bit-equal"),
+                           g->nBatches(), secRef, secGpu);
+                }
+        }
+
+        // ---- 10: frames/s of the plugin path against the C-ABI call it wraps -----------------------------------------
         const size_t timingFrames = args.count("timing-frames") ? atoi(args["timing-frames"].c_str()) : 0;
         if (timingFrames > 0) {
             Core::Configuration            gc  = scorerConfig("gpu", "gpu-diagonal-maximum", 0, 0);

@@ -54,6 +54,7 @@ SYMBOLS = [
     ("gmm_score_subset_ld", _u32, [_vp, _u32]),
     ("gmm_align_device", _i, [_vp, _u32, _vp, _vp, _sz] + [_vp] * 10),
     ("gmm_align_ordered_count", C.c_uint64, [_vp]),
+    ("gmm_set_consumer_score_scale", _i, [_vp, C.c_float]),
     ("gmm_score_align_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
     ("gmm_score_align_accumulate_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 10),
     ("gmm_score_align_labels_host", _i, [_vp, _u32, _vp, _vp] + [_vp] * 12),
@@ -405,6 +406,10 @@ class Engine:
             _ptr(a.arc_emission), _ptr(a.arc_weight), _ptr(a.initial_state), _ptr(a.final_weight), _ptr(w), int(ld_w),
             _ptr(total)), "gmm_score_baum_welch_host")
         return w, total
+
+    def set_consumer_score_scale(self, scale: float):
+        """The host-level alignment consumers read fl(scale * score) (Mm::FeatureScorerScaling)."""
+        self._check(self._lib.gmm_set_consumer_score_scale(self._h, float(scale)), "gmm_set_consumer_score_scale")
 
     def score_align_labels_host(self, frame_offsets, x, automata, label_offsets, label_mixture, want_states=True):
         """As score_align_host for arcs that carry labels: automata.arc_emission holds segment-local label slots,

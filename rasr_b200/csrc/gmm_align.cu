@@ -832,6 +832,30 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
     return defer ? GMM_OK : gmm_align_finish(h, fin);
 }
 
+namespace {
+__global__ void __launch_bounds__(256) scale_block_kernel(float* d, size_t rows, size_t cols, size_t ld, float scale) {
+    const size_t total = rows * cols;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / cols, c = i - r * cols;
+        d[r * ld + c]  = __fmul_rn(scale, d[r * ld + c]);
+    }
+}
+}  // namespace
+
+// Mm::FeatureScorerScaling (ScaledFeatureScorer.hh:62-64): the aligner sees scale_ * score, one f32 product per score.
+int gmm_scale_block(gmm_handle* h, float* d, size_t rows, size_t cols, size_t ld, float scale) {
+    if (!rows || !cols)
+        return GMM_OK;
+    const size_t total = rows * cols;
+    const int    grid  = (int)std::min<size_t>((total + 255) / 256, (size_t)h->smCount * 8);
+    h->timeBegin();
+    scale_block_kernel<<<grid, 256, 0, h->stream>>>(d, rows, cols, ld, scale);
+    h->timeEnd();
+    h->launches++;
+    GMM_CUDA_TRY(h, cudaGetLastError());
+    return GMM_OK;
+}
+
 int gmm_align_finish(gmm_handle* h, AlignDeferred& f) {
     if (!f.pending)
         return GMM_OK;

@@ -843,6 +843,17 @@ uint64_t gmm_align_ordered_count(const gmm_handle* h) {
     return h ? h->alignOrdered : 0;
 }
 
+int gmm_set_consumer_score_scale(gmm_handle* h, float scale) {
+    if (!h)
+        return GMM_ERR_ARG;
+    if (!(scale > 0.f) || std::isinf(scale)) {
+        h->setError("gmm_set_consumer_score_scale: the scale must be positive and finite");
+        return GMM_ERR_ARG;
+    }
+    h->consumerScale = scale;
+    return GMM_OK;
+}
+
 }  // extern "C"
 
 // One group of whole segments: upload, score (compact block when that saves tensor work), align, accumulate --
@@ -959,6 +970,9 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
         if (rc)
             return rc;
     }
+    if (T && h->consumerScale != 1.f &&
+        (rc = gmm_scale_block(h, (float*)ds, T, compact ? ldUse : (size_t)h->M, ldUse, h->consumerScale)))
+        return rc;
     traceMark(h, (int)s0, "scored");
     tr[3] = clk();
     if (bw) {

@@ -117,6 +117,7 @@ struct gmm_handle {
     bool         ownStream  = false;
     uint64_t     launches   = 0;
     uint64_t     alignOrdered = 0;  // segments aligned by the ordered (tie-resolving) pass so far
+    float        consumerScale = 1.f;  // the *_host alignment consumers read fl(scale * score) (gmm_set_consumer_score_scale)
     bool         timing     = false;                            // gmm_kernel_timing
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed;     // brackets of scoring-kernel launches
     void timeBegin() {
@@ -242,6 +243,8 @@ int gmm_align_launch(gmm_handle* h, uint32_t nSeg, const uint32_t* frameOffsets,
                      const uint32_t** d_pathEmission = nullptr, bool compact = false, uint32_t nEmissions = 0,
                      struct AlignDeferred* defer = nullptr, const struct AlignLists* lists = nullptr,
                      bool slotOutput = false);  // slotOutput: pathEmission = position in the segment's list (labels)
+// d[r * ld + c] = fl(scale * d[r * ld + c]) for c < cols, on the handle's stream (the scaling wrapper of the reference)
+int gmm_scale_block(gmm_handle* h, float* d, size_t rows, size_t cols, size_t ld, float scale);
 // With `defer` gmm_align_launch returns once everything is enqueued; gmm_align_finish (same lane active) copies the
 // outputs to the host arrays and waits.
 struct AlignDeferred {

@@ -241,3 +241,39 @@ def test_label_entry_points_reject_bad_lists(eng):
         eng.score_align_labels_host([0, 4], x, au, [0, 2], [3, 4])
     with pytest.raises(capi.GmmError):                               # label tied to a mixture the model lacks
         eng.score_align_labels_host([0, 4], x, au, [0, 3], [3, 4, 20])
+
+
+@pytest.mark.parametrize("subset", ["0", "1"])
+def test_consumer_score_scale_is_the_scaling_wrapper(eng, oracle, monkeypatch, subset):
+    """gmm_set_consumer_score_scale: the aligner sees fl(scale * score), as behind Mm::FeatureScorerScaling
+    (ScaledFeatureScorer.hh:62-64) -- Viterbi bit-exact, Baum-Welch within its tolerance, on both block layouts."""
+    monkeypatch.setenv("GMM_ALIGN_SUBSET", subset)
+    ms = synth.make_model(M=400, K=8, D=24, seed=41)
+    rng = np.random.default_rng(41)
+    lens = [90, 33, 0, 150]
+    fo = np.cumsum([0] + lens).astype(np.uint32)
+    x = synth.make_features(ms, int(fo[-1]), seed=42)
+    au = AlignmentAutomata.from_arc_lists([linear_hmm(rng.integers(0, ms.M, max(1, n // 3)), loop=3.0, forward=0.0,
+                                                      skip=30.0) for n in lens])
+    t = tables.float_tables(ms)
+    eng.upload_float(t["offsets"], t["mean"], t["isr"], t["cov_idx"], t["w2"], t["log_norm"], mode=capi.MODE_MAX,
+                     kernel=capi.KERNEL_TENSOR)
+    s, _ = eng.score_host(x, want_best=False)
+    scaled = (np.float32(0.75) * s).astype(np.float32)
+    eng.set_consumer_score_scale(0.75)
+    try:
+        em, st, sc = eng.score_align_host(fo, x, au)
+        w, total = eng.score_baum_welch_host(fo, x, au)
+    finally:
+        eng.set_consumer_score_scale(1.0)
+    emo, sto, sco = oracle.viterbi_align(fo, scaled, au)
+    assert np.array_equal(em, emo) and np.array_equal(st, sto) and np.array_equal(bits(sc), bits(sco))
+    wo, lists, to = oracle.baum_welch_align(fo, scaled, au)
+    for i in range(len(lens)):
+        rows = slice(int(fo[i]), int(fo[i + 1]))
+        assert np.max(np.abs(w[rows, :len(lists[i])] - wo[i]), initial=0.0) <= 1e-4
+        assert abs(total[i] - to[i]) <= 1e-5 * max(1.0, abs(to[i]))
+    em1, _, sc1 = eng.score_align_host(fo, x, au)                    # back at scale 1
+    assert np.array_equal(bits(sc1), bits(oracle.viterbi_align(fo, s, au)[2]))
+    with pytest.raises(capi.GmmError):
+        eng.set_consumer_score_scale(0.0)

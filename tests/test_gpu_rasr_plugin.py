@@ -1,4 +1,5 @@
-"""GPU: the RASR-side plugin classes (rasr/GpuFeatureScorer.cc) against the reference's own scorer classes, both
+"""GPU: the RASR-side plugin classes (rasr/GpuFeatureScorer.cc, rasr/GpuAligner.cc) against the reference's own scorer
+classes and its own Search::Aligner: the scorers are
 created by the reference's own Mm::Module_ (feature-scorer-type -> factory -> scaling wrapper; rasr/Module.cc registers
 the GPU scorers in it) inside one RASR process and driven by the buffered caller loops of Speech::AlignmentNode and
 Speech::RecognizerDelayHandler.  The binary (oracle/_ref/rasr_gpu_check) is built by rasr/Makefile in the build container
@@ -33,8 +34,9 @@ def test_plugin_matches_reference_scorers_in_process(tmp_path, kw, T, buffer_siz
     print(r.stdout)
     assert r.returncode == 0, r.stdout[-3000:]
     # 7 scorer pairs (the three batch scorers need a pooled covariance), delayed-recognizer loop, time-indexed scorers,
-    # density posteriors, model accessors, with-density-assignment
-    assert r.stdout.count("PASS") == (9 if kw.get("covariance") else 12) and "FAIL" not in r.stdout
+    # density posteriors, model accessors, with-density-assignment, and MmGpu::GpuAligner against the reference's own
+    # Search::Aligner in both modes on both float kernels (4 lines)
+    assert r.stdout.count("PASS") == (13 if kw.get("covariance") else 16) and "FAIL" not in r.stdout
 
 
 @pytest.mark.skipif(not os.path.exists(CHECK), reason="oracle/_ref/rasr_gpu_check not built (needs /root/reference)")
@@ -56,4 +58,4 @@ def test_plugin_path_is_within_20_percent_of_the_call_it_wraps(tmp_path):
                         r.stdout)  # (RASR's own log lines share stdout and may end without a newline)
     assert len(timing) == 1, r.stdout[-2000:]
     assert float(timing[0]) >= 0.8, timing
-    assert r.stdout.count("PASS") == 13 and "FAIL" not in r.stdout
+    assert r.stdout.count("PASS") == 17 and "FAIL" not in r.stdout
