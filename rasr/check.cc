@@ -622,6 +622,51 @@ public:
                    timingFrames, M, plugin, direct, plugin / direct);
             report("plugin path timing", std::isfinite(sink) && plugin >= 0.8 * direct, "ratio=%.3f (segment mode, one read per frame)",
                    plugin / direct);
+
+            // the alignment of one segment of `timingFrames` frames, wall clock from the first addFeature to the items:
+            // (a) the reference's aligner on the GPU scorer (full score matrix over the host link, search on one core),
+            // (b) MmGpu::GpuAligner on a deferred-scoring GPU scorer (compact block in HBM, search on the device)
+            std::vector<Mm::FeatureVector> seg(timingFrames);
+            for (size_t t = 0; t < timingFrames; ++t)
+                seg[t] = X[t % X.size()];
+            std::vector<u32> tie(M), labels(std::max<size_t>(1, timingFrames / 3));
+            for (u32 l = 0; l < M; ++l)
+                tie[l] = l;
+            u32 seed = 99;
+            for (size_t i = 0; i < labels.size(); ++i) {
+                seed      = seed * 1664525u + 1013904223u;
+                labels[i] = (seed >> 8) % M;
+            }
+            Core::Ref<const Am::AcousticModel> am(new TableAcousticModel(select("acoustic-model"), M, tie));
+            Fsa::ConstAutomatonRef             model = linearModel(labels, 3.0f, 0.0f, 30.0f);
+            Core::Configuration                ac(config, "aligner");
+            ac.set(ac.getSelection() + ".min-acoustic-pruning", "1e30");
+            ac.set(ac.getSelection() + ".max-acoustic-pruning", "1e30");
+            Core::Configuration dc = scorerConfig("gpu-deferred", "gpu-diagonal-maximum", 0, 0);
+            dc.set(dc.getSelection() + ".deferred-scoring", "true");
+            Core::Ref<Mm::FeatureScorer> dfr = mm.createFeatureScorer(dc, ms);
+            Search::Aligner              refAligner(ac);
+            MmGpu::GpuAligner            gpuAligner(ac);
+            double                       alignBest[2] = {1e30, 1e30};
+            Speech::Alignment            a, b;
+            for (int r = 0; r < 6; ++r) {
+                double t0 = now();
+                refAligner.setModel(model, am);
+                refAligner.feed(segmentScorers(*gpu, seg, 0, timingFrames));
+                refAligner.getAlignment(a);
+                double t1 = now();
+                gpuAligner.setModel(model, am);
+                gpuAligner.feed(segmentScorers(*dfr, seg, 0, timingFrames));
+                gpuAligner.getAlignment(b);
+                double t2 = now();
+                alignBest[0] = std::min(alignBest[0], t1 - t0);
+                alignBest[1] = std::min(alignBest[1], t2 - t1);
+            }
+            AlignDiff d = compareAlignments(a, b, 0.0);
+            printf("ALIGN-TIMING frames=%zu mixtures=%u labels=%zu reference_aligner_on_gpu_scorer_ms=%.3f gpu_aligner_ms=%.3f speedup=%.2f\n",
+                   timingFrames, M, labels.size(), alignBest[0] * 1e3, alignBest[1] * 1e3, alignBest[0] / alignBest[1]);
+            report("GpuAligner timing segment", d.differing == 0 && d.scoreBits && gpuAligner.reachedFinalState(),
+                   "identical items=%zu; %.2fx the reference aligner fed by the same GPU scorer", d.items, alignBest[0] / alignBest[1]);
         }
         return failures_ ? 1 : 0;
     }

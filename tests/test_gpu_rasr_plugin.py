@@ -58,4 +58,4 @@ def test_plugin_path_is_within_20_percent_of_the_call_it_wraps(tmp_path):
                         r.stdout)  # (RASR's own log lines share stdout and may end without a newline)
     assert len(timing) == 1, r.stdout[-2000:]
     assert float(timing[0]) >= 0.8, timing
-    assert r.stdout.count("PASS") == 17 and "FAIL" not in r.stdout
+    assert r.stdout.count("PASS") == 18 and "FAIL" not in r.stdout
