@@ -108,7 +108,7 @@ class GpuFeatureScorer:
     def __init__(self, mixture_set: MixtureSetData, scorer_type: str = "diagonal-maximum", *, buffer_size: int = 0,
                  device: int = 0, assigning: bool = True, kernel: int = capi.KERNEL_AUTO,
                  mixture_weight_scale: float = 1.0, gaussian_scale: float = 1.0, quant_tables: dict | None = None,
-                 float_tables: dict | None = None):
+                 float_tables: dict | None = None, keep_frames: bool = False):
         if scorer_type not in self.SCORER_TYPES:
             raise ValueError(f"unknown feature-scorer-type '{scorer_type}'")  # Module.cc:303-307
         if buffer_size < 0:
@@ -124,6 +124,7 @@ class GpuFeatureScorer:
         self._offsets = mixture_set.mix_offsets.copy()
         self._buffer_size = int(buffer_size)
         self._assigning = assigning
+        self._keep_frames = keep_frames   # contexts keep their frame after scoring (rasr_b200.aligner.Aligner reads it)
         self._engine = capi.Engine(device)
         if scorer_type in self.QUANTIZED_TYPES:
             if quant_tables is not None:
@@ -221,7 +222,7 @@ class GpuFeatureScorer:
         x = np.stack([c._frame for c in self._pending])
         scores, best = self.scoreBatch(x)
         block = _ScoreBlock(scores, best)
-        keep = self._type == "diagonal-sum"  # its contexts answer density posteriors from the frame later
+        keep = self._type == "diagonal-sum" or self._keep_frames  # density posteriors / the aligner need the frame later
         for i, c in enumerate(self._pending):
             c._block, c._row, c._frame = block, i, (c._frame if keep else None)
         self._pending = []
