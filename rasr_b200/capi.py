@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgmm_b200.so")
+LIB_PATH = os.environ.get("GMM_B200_LIB") or os.path.join(HERE, "libgmm_b200.so")  # (override: kernel experiments)
 
 MODE_MAX, MODE_SUM = 0, 1
 KERNEL_AUTO, KERNEL_DIRECT, KERNEL_TENSOR = 0, 1, 2

@@ -72,6 +72,7 @@ struct KParams {
     uint32_t       nItems;
     unsigned long long* dbg;                   // GMM_TC_DEBUG: per-CTA cycle counters of the MMA thread
     uint32_t       directStores;               // 0: always stage and store coalesced (GMM_TC_STORES=staged)
+    uint32_t       sumFull;                    // full-sum scorer: parts without dead columns take the unpredicated pass
 };
 
 struct EpiState {
@@ -198,7 +199,23 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
 // (12001x64 synthetic model): a frame needs 41 % of its segments at the threshold of 40, a WARP of 32 independent frames
 // 99.99 % -- the vote skips nothing, the kernel pays all 64 exponentials per frame and mixture (>= 2048 cycles per tile).
 // get(i) = accumulator value i of the part (compile-time i), N = columns of the part held in registers.
-template<bool BEST, int SP, int NSEG, typename Get>
+// FULL: every column of the part is a live density (liveBits all 7) -- no predicates, no vote: the vote skips nothing on
+// independent frames (above), and without it and the `j < live` tests the loop is multiply-add, exp2, add per term
+// (12001x64 model, 10000 frames: 3.98 -> 3.32 ms in the same build; GMM_TC_SUM_FULL=0 switches it off).
+// Measured around this form at the end of round 2 (each as its own build, profiles/sum_epilogue_experiments_r02.txt):
+//   * ex2 replaced by the identity (timing only): 2.67 ms -- the special-function unit accounts for a fifth of the tile,
+//     not for the 2048 of its ~3500 cycles the 16-results-per-clock arithmetic suggested;
+//   * fma.rn.f32x2 / add.rn.f32x2 (FFMA2 / FADD2, half the FMA-pipe instructions): 3.56 ms, and 2.96 ms without ex2 --
+//     slower both times: neither the FMA pipe nor instruction issue is the bound;
+//   * 32 accumulator values live instead of 64 (mixtures of <= 32 columns chunk by chunk; 64-column mixtures with the
+//     first chunk read from TMEM twice): 3.85 ms;
+//   * the four epilogue warps of a scheduler started 300 .. 900 cycles apart: no change;
+//   * an event log of one CTA: the tensor core finishes a tile 530 cycles after its commit and runs two tiles ahead of
+//     the epilogue the whole time -- the epilogue warps never wait for it.
+// What remains is the per-warp dependency chain of a tile (TMEM load, min tree, 64 dependent adds behind 64 exp2
+// results, log2, staged store), which four warps per scheduler do not overlap: the next step is more, narrower
+// warps' worth of independent chains per scheduler, i.e. two mixtures' sums interleaved in one thread.
+template<bool BEST, int SP, int NSEG, bool FULL, typename Get>
 __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, const uint16_t* __restrict__ slots,
                                                 uint64_t liveBits, float rt, float rs, uint32_t offB, EpiState& st) {
     constexpr float kLn2 = 0.69314718055994530942f;
@@ -218,14 +235,21 @@ __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, 
             best = fminf(best, segMin[s]);
         const float bestL = best * hl2e;
         float       sum   = 0.f;
+        if (FULL) {
 #pragma unroll
-        for (int s = 0; s < SP; ++s) {
-            const int live = (int)((liveBits >> ((seg0 + m0 + s) * 4)) & 15ull) + 1;  // uniform
-            if (__any_sync(0xffffffffu, !((segMin[s] - best) * rs >= 40.f))) {
+            for (int i = 0; i < SP * 8; ++i)
+                sum += ex2(fmaf(get(m0 * 8 + i), -hl2e, bestL));
+        }
+        else {
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    if (j < live)  // (best - u) * hl2e as one fused multiply-add: the epilogue is issue-bound
-                        sum += ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
+            for (int s = 0; s < SP; ++s) {
+                const int live = (int)((liveBits >> ((seg0 + m0 + s) * 4)) & 15ull) + 1;  // uniform
+                if (__any_sync(0xffffffffu, !((segMin[s] - best) * rs >= 40.f))) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (j < live)  // (best - u) * hl2e as one fused multiply-add: the epilogue is issue-bound
+                            sum += ex2(fmaf(get((m0 + s) * 8 + j), -hl2e, bestL));
+                }
             }
         }
         const float b2 = fminf(best * rs, FLT_MAX);
@@ -477,6 +501,8 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             const uint32_t  mixBase  = meta[2 + part];
             const uint64_t  liveBits = (SEGS == 16) ? ((uint64_t)meta[6 + 2 * part + 1] << 32 | meta[6 + 2 * part])
                                                     : (uint64_t)meta[6 + part];
+            // full-sum scorer, 16 warps (8 segments per part): no dead column in the part
+            const bool      sumFull  = MODE == 1 && p.sumFull && (uint32_t)liveBits == 0x77777777u;
             const uint32_t  nMix     = __popc(segEnd);
             // staged block [32 rows x nMix] -> global: lane starts at element `lane`, every pass advances 32 elements
             const uint32_t  adv_r = 32 / max(nMix, 1u), adv_j = 32 - adv_r * nMix;
@@ -538,7 +564,10 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                             mbar_arrive(drained);
                         if (MODE == 1 && SP > 0) {
                             auto get = [&](int i) { return __uint_as_float(i < 32 ? va[i & 31] : vb[i & 31]); };
-                            epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st);
+                            if (sumFull)
+                                epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8, true>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st);
+                            else
+                                epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8, false>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st);
                         }
                         else {
                             epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
@@ -1258,6 +1287,8 @@ int tc_run(gmm_handle* h, const TcJob& job) {
         // piece (GMM_TC_STORES=lane), 0 = the general staged scalar path (GMM_TC_STORES=staged)
         const char* e  = getenv("GMM_TC_STORES");
         p.directStores = (e && !strcmp(e, "staged")) ? 0u : (e && !strcmp(e, "lane")) ? 2u : 1u;
+        const char* sf = getenv("GMM_TC_SUM_FULL");
+        p.sumFull      = (sf && sf[0] == '0') ? 0u : 1u;
     }
     const bool debug = getenv("GMM_TC_DEBUG") != nullptr;
     if (debug) {
