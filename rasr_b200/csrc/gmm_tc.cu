@@ -217,7 +217,8 @@ __device__ __forceinline__ void epi_chunk(const uint32_t* v, int ch, int colBase
 // warps' worth of independent chains per scheduler, i.e. two mixtures' sums interleaved in one thread.
 template<bool BEST, int SP, int NSEG, bool FULL, typename Get>
 __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, const uint16_t* __restrict__ slots,
-                                                uint64_t liveBits, float rt, float rs, uint32_t offB, EpiState& st) {
+                                                uint64_t liveBits, float rt, float rs, uint32_t offB, EpiState& st,
+                                                float* res = nullptr) {
     constexpr float kLn2 = 0.69314718055994530942f;
     const float     hl2e = 0.72134752044448170368f * rs;  // 0.5 * log2(e) * rowScale
 #pragma unroll
@@ -253,7 +254,11 @@ __device__ __forceinline__ void epi_sum_uniform(Get get, int seg0, int colBase, 
             }
         }
         const float b2 = fminf(best * rs, FLT_MAX);
-        sts_f32(st.sp, 0.5f * (b2 + rt) - kLn2 * __log2f(sum));
+        const float sc = 0.5f * (b2 + rt) - kLn2 * __log2f(sum);
+        if (res)  // the caller writes the row piece from registers (as the maximum approximation's direct stores)
+            res[m0 / SP] = sc;
+        else
+            sts_f32(st.sp, sc);
         if (BEST) {
             uint32_t idx = 0;
 #pragma unroll
@@ -514,14 +519,15 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             const size_t    gTileStep = (size_t)NG * kTileM * p.ld * 4;
             const float2*   rip = p.rowInfo + (size_t)fG * kTileM + q * 32 + lane;
             // the tile loop, specialised on the tile's mixture shape when it is uniform (see epi_chunk)
-            // DIRECT (maximum approximation without arg-min on uniform parts, row pieces 8- / 16-byte aligned): a lane
+            // DIRECT (no arg-min, uniform parts, row pieces 8- / 16-byte aligned; maximum approximation, and the full-sum scorer
+            // with its 16 warps): a lane
             // keeps its frame's R = SEGS / SP mixture scores in registers and writes the row piece itself with 64- /
             // 128-bit stores -- no staging, no shared-memory round trip, a fifth of the store path's instructions (the
             // epilogue is bound by the ALU pipe: 2 warps per scheduler at one instruction per 2 cycles)
             char* gLane = reinterpret_cast<char*>(p.scores + (size_t)(ir.rowBase + (fG - f0) * kTileM + q * 32 + lane) * p.ld + mixBase);
             auto tiles = [&](auto spTag, auto dirTag) {
                 constexpr int  SP     = decltype(spTag)::value;
-                constexpr bool DIRECT = decltype(dirTag)::value && MODE == 0 && !BEST && SP > 0;
+                constexpr bool DIRECT = decltype(dirTag)::value && (MODE == 0 || NE == 16) && !BEST && SP > 0;
                 constexpr int  R      = DIRECT ? SEGS / SP : 1;
                 // VEC (R a multiple of 4): the R results go through the warp's staging block ([32 rows][R + 4] floats,
                 // 128-bit writes) and leave as 128-bit stores of R / 4 lanes per row -- a store instruction then touches
@@ -565,9 +571,9 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
                         if (MODE == 1 && SP > 0) {
                             auto get = [&](int i) { return __uint_as_float(i < 32 ? va[i & 31] : vb[i & 31]); };
                             if (sumFull)
-                                epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8, true>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st);
+                                epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8, true>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st, resp);
                             else
-                                epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8, false>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st);
+                                epi_sum_uniform<BEST, (SP > 0 ? SP : 1), 8, false>(get, 0, part * PW, slots, liveBits, rt, rs, offB, st, resp);
                         }
                         else {
                             epi_chunk<MODE, BEST, SP>(va, 0, part * PW, slots, segEnd, segEmpty, liveBits, rt, rs, offB, st, resp);
@@ -685,11 +691,12 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             const uint32_t uni = (MODE == 0 || NE == 16) ? ((meta[10] >> (8 * part)) & 0xFFu) : 0u;
             // row pieces of R = SEGS / uni floats: 16-byte stores for R >= 4, 8-byte for R = 2
             const uint32_t piece  = uni ? min(16u, (uint32_t)(SEGS / max(uni, 1u)) * 4u) : 0u;
-            const bool     direct = MODE == 0 && !BEST && piece >= 8 && p.directStores &&
+            const bool     direct = (MODE == 0 || NE == 16) && !BEST && piece >= 8 && p.directStores &&
                                 ((p.ld * 4) % piece) == 0 && ((mixBase * 4) % piece) == 0 &&
                                 (reinterpret_cast<uintptr_t>(p.scores) % piece) == 0;
             auto run = [&](auto spTag) {
-                if constexpr (MODE == 0 && !BEST && decltype(spTag)::value > 0) {
+                // (full-sum scorer: 8 segments per part, so row pieces of at least two floats mean mixtures of <= 4 segments)
+                if constexpr ((MODE == 0 || (NE == 16 && decltype(spTag)::value <= 4)) && !BEST && decltype(spTag)::value > 0) {
                     if (direct)
                         return tiles(spTag, std::true_type{});
                 }
