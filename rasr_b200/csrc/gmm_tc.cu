@@ -307,6 +307,13 @@ __device__ __forceinline__ ItemRange item_range(const KParams& p, uint32_t item,
 template<int SWZ, int MODE, bool BEST, int NE, int NG = 1>
 __device__ __forceinline__ void tc_score_body(const KParams& p) {
     static_assert(NG == 1 || (NG == 2 && NE == 8 && kRing % 2 == 0), "two groups: eight warps each, ring parity = tile parity");
+    // First epilogue warp.  Sixteen epilogue warps in one group: the CTA is launched with TWENTY warps -- registers are
+    // handed out per four warps, so eighteen warps pay for twenty anyway (96 registers each) -- and the first warp group
+    // (producer, MMA issuer, two idle warps) gives registers back: setmaxnreg 32 there, 112 for the epilogue warps, at
+    // which the full-sum epilogue (64 accumulator values live per thread) no longer spills (ptxas: 228 bytes at 96).
+    // (Full-sum scorer without arg-min only: the other sixteen-warp variants need more than 112 registers somewhere, and
+    // a setmaxnreg region cannot spill -- ptxas refuses.)
+    constexpr int EW0 = (NE == 16 && NG == 1 && !BEST && MODE == 1) ? 4 : kEpiWarp0;
     extern __shared__ uint8_t smemRaw[];
     // swizzled operand tiles need 1024-byte alignment of the shared-memory address itself
     uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
@@ -357,6 +364,9 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     const uint32_t items        = p.itemTab ? p.nItems : p.nTiles * p.split;
     const uint32_t tilesPerItem = (p.frameTiles + p.split - 1) / p.split;
 
+    if (warp < EW0) {
+    if (EW0 == 4)
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     if (warp == 0) {
         // ===== producer: one lane issues the bulk copies =====
         if (lane == 0) {
@@ -472,9 +482,12 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             d[0] = clock64() - tStart, d[1] = wR, d[2] = wI, d[3] = wB, d[4] = t, d[5] = itemCount, d[6] = gt0, d[7] = gt1;
         }
     }
+    }
     else {
+        if (EW0 == 4)
+            asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
         // ===== epilogue: TMEM -> registers -> (min / log-sum-exp per mixture) -> staged -> global =====
-        const int      grp = (warp - kEpiWarp0) / NE, e = (warp - kEpiWarp0) % NE, q = warp & 3, part = e >> 2;
+        const int      grp = (warp - EW0) / NE, e = (warp - EW0) % NE, q = warp & 3, part = e >> 2;
         const uint32_t stWarp = smem_u32(sStage) + (uint32_t)(grp * NE + e) * stageWarp * 4;  // this warp's staging block
         const uint32_t stRow  = stWarp + (uint32_t)lane * p.stagePitch * 4;      // this lane's (frame's) row in it
         const uint32_t offB   = NE * NG * stageWarp * 4;                         // index plane behind the scores
@@ -718,7 +731,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
             unsigned long long* d = p.dbg + blockIdx.x * 128;
             if (e == 0 && grp == 0)
                 d[8] = eW, d[9] = eL, d[10] = eC, d[11] = eS;
-            unsigned long long* w = d + 16 + (warp - kEpiWarp0) * 4;  // every epilogue warp
+            unsigned long long* w = d + 16 + (warp - EW0) * 4;  // every epilogue warp
             w[0] = eW, w[1] = eL, w[2] = eC, w[3] = eS;
         }
     }
@@ -731,13 +744,14 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     }
 }
 
-// 8 epilogue warps: 320 threads, up to 204 registers; 16 epilogue warps: 576 threads (20 warp slots at allocation granularity 4), 96 registers
+// 8 epilogue warps: 320 threads, up to 204 registers; 16 epilogue warps: 640 threads launched with 96 registers, the
+// epilogue warps raise theirs to 112 (setmaxnreg, see EW0 in tc_score_body)
 template<int SWZ, int MODE, bool BEST>
 __global__ void __launch_bounds__(32 * (kEpiWarp0 + 8), 1) tc_score_kernel8(const KParams p) {
     tc_score_body<SWZ, MODE, BEST, 8>(p);
 }
 template<int SWZ, int MODE, bool BEST>
-__global__ void __launch_bounds__(32 * (kEpiWarp0 + 16), 1) tc_score_kernel16(const KParams p) {
+__global__ void __launch_bounds__(32 * (((BEST || MODE != 1) ? kEpiWarp0 : 4) + 16), 1) tc_score_kernel16(const KParams p) {  // see EW0
     tc_score_body<SWZ, MODE, BEST, 16>(p);
 }
 // two epilogue groups of eight warps (maximum approximation): 576 threads, 96 registers
@@ -883,7 +897,8 @@ cudaError_t launch_tc(const KParams& p, int grid, size_t smemBytes, cudaStream_t
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     if (e != cudaSuccess)
         return e;
-    kernel<<<grid, 32 * (kEpiWarp0 + ((NE == 8 || (NE == 82 && MODE != 0)) ? 8 : 16)), smemBytes, stream>>>(p);
+    kernel<<<grid, (NE == 16 && !BEST && MODE == 1) ? 32 * (4 + 16) : 32 * (kEpiWarp0 + ((NE == 8 || (NE == 82 && MODE != 0)) ? 8 : 16)),
+             smemBytes, stream>>>(p);
     return cudaGetLastError();
 }
 
