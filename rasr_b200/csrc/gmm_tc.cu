@@ -313,7 +313,7 @@ __device__ __forceinline__ void tc_score_body(const KParams& p) {
     // which the full-sum epilogue (64 accumulator values live per thread) no longer spills (ptxas: 228 bytes at 96).
     // (Full-sum scorer without arg-min only: the other sixteen-warp variants need more than 112 registers somewhere, and
     // a setmaxnreg region cannot spill -- ptxas refuses.)
-    constexpr int EW0 = (NE == 16 && NG == 1 && !BEST && MODE == 1) ? 4 : kEpiWarp0;
+    constexpr int EW0 = (NE == 16 && NG == 1 && !BEST) ? 4 : kEpiWarp0;
     extern __shared__ uint8_t smemRaw[];
     // swizzled operand tiles need 1024-byte alignment of the shared-memory address itself
     uint8_t*  smem = smemRaw + ((1024u - (smem_u32(smemRaw) & 1023u)) & 1023u);
@@ -751,7 +751,7 @@ __global__ void __launch_bounds__(32 * (kEpiWarp0 + 8), 1) tc_score_kernel8(cons
     tc_score_body<SWZ, MODE, BEST, 8>(p);
 }
 template<int SWZ, int MODE, bool BEST>
-__global__ void __launch_bounds__(32 * (((BEST || MODE != 1) ? kEpiWarp0 : 4) + 16), 1) tc_score_kernel16(const KParams p) {  // see EW0
+__global__ void __launch_bounds__(32 * ((BEST ? kEpiWarp0 : 4) + 16), 1) tc_score_kernel16(const KParams p) {  // see EW0
     tc_score_body<SWZ, MODE, BEST, 16>(p);
 }
 // two epilogue groups of eight warps (maximum approximation): 576 threads, 96 registers
@@ -897,7 +897,7 @@ cudaError_t launch_tc(const KParams& p, int grid, size_t smemBytes, cudaStream_t
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     if (e != cudaSuccess)
         return e;
-    kernel<<<grid, (NE == 16 && !BEST && MODE == 1) ? 32 * (4 + 16) : 32 * (kEpiWarp0 + ((NE == 8 || (NE == 82 && MODE != 0)) ? 8 : 16)),
+    kernel<<<grid, (NE == 16 && !BEST) ? 32 * (4 + 16) : 32 * (kEpiWarp0 + ((NE == 8 || (NE == 82 && MODE != 0)) ? 8 : 16)),
              smemBytes, stream>>>(p);
     return cudaGetLastError();
 }
