@@ -915,6 +915,10 @@ static int scoreAlignGroup(gmm_handle* h, bool accumulate, uint32_t s0, uint32_t
     std::vector<uint32_t> arcMixture;  // label callers: the mixture behind every arc's label
     if (labels) {
         const uint32_t l0 = labels->offsets[s0], nGroupArcs = ao[so[n]];
+        if (nGroupArcs && !arcEmission) {
+            h->setError("gmm_score_align_labels: arcLabel is NULL");
+            return GMM_ERR_ARG;
+        }
         emOff.resize(n + 1);
         for (uint32_t i = 0; i <= n; ++i) {
             if (labels->offsets[s0 + i] < (i ? labels->offsets[s0 + i - 1] : l0)) {
