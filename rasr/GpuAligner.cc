@@ -45,6 +45,7 @@ GpuAligner::~GpuAligner() {}
 void GpuAligner::setModel(Fsa::ConstAutomatonRef model, Core::Ref<const Am::AcousticModel> acousticModel) {
     require(model);
     require(model->initialStateId() != Fsa::InvalidStateId);  // as Aligner.cc:575-576
+    model_         = model;
     acousticModel_ = acousticModel;
     Core::Ref<Fsa::StaticAutomaton> s = Fsa::staticCopy(model);  // what SearchSpace::setModel works on (Aligner.cc:117)
     const u32                       S = s->size();

@@ -1,7 +1,7 @@
 /** RASR-side plugin, second part: the alignment consumer behind the interface of Search::Aligner.
  *
  *  Search::Aligner (src/Search/Aligner.hh:36-176) is what Speech::AlignmentNode drives per segment
- *  (src/Speech/AlignmentNode.cc:279-318): setModel(automaton, acoustic model), feed(scorers of every frame),
+ *  (src/Speech/AlignmentNode.cc:193, 211, 313-322): setModel(automaton, acoustic model), feed(scorers of every frame),
  *  reachedFinalState(), alignmentScore(), getAlignment(Speech::Alignment&).  MmGpu::GpuAligner offers those calls with
  *  the same meaning, for the scorers of a GpuFeatureScorer: the frames the scorers stand for go to the device ONCE,
  *  only the emissions the automaton names are scored (the reference's lazy score(e)), the score block stays in HBM and
@@ -45,6 +45,10 @@ public:
     /** Flattens the automaton: states in id order, arcs in Fsa order (the order the reference expands them in), every
      *  distinct arc label a slot whose mixture is acousticModel->emissionIndex(label) (Aligner.cc:225). */
     void setModel(Fsa::ConstAutomatonRef model, Core::Ref<const Am::AcousticModel>);
+    /** as Search::Aligner::getModel (AlignmentNode.cc:193 reuses the model of the previous segment through it) */
+    Fsa::ConstAutomatonRef getModel() const {
+        return model_;
+    }
     void restart();
 
     /** The scorers must come from a GpuFeatureScorer on the float engine (directly, or through the scaling wrapper
@@ -75,6 +79,7 @@ public:
     }
 
 private:
+    Fsa::ConstAutomatonRef             model_;
     Core::Ref<const Am::AcousticModel> acousticModel_;
     bool                               viterbi_;
     // the flattened automaton (include/gmm_b200.h: one segment)

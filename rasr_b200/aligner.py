@@ -2,7 +2,7 @@
 
 The production host side is the C++ class in rasr/GpuAligner.{hh,cc}; this module states the same interface in Python
 so that the parity tests read like calls into the reference's Search::Aligner
-(/root/reference/src/Search/Aligner.hh:36-176, driven by /root/reference/src/Speech/AlignmentNode.cc:279-318):
+(/root/reference/src/Search/Aligner.hh:36-176, driven by /root/reference/src/Speech/AlignmentNode.cc:211, 313-322):
 
     aligner.setModel(model, acoustic_model)   flatten the automaton; labels -> mixtures (Aligner.cc:225)
     aligner.feed(scorers)                     the context scorers of a segment's frames
