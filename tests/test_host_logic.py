@@ -172,3 +172,42 @@ def test_unknown_scorer_type_and_dimension(stub):
 def test_golden_fixture_loads(name):
     ms, z = load_golden(name)
     assert z["max_score"].shape == (z["x"].shape[0], ms.M)
+
+
+def test_label_slots_keep_tied_labels_apart():
+    """rasr_b200.align.label_slots: per segment the distinct arc labels in order of first use become slots; labels tied
+    to one mixture stay apart (the reference's alignment items name the label, Aligner.cc:185, 205)."""
+    from rasr_b200.align import AlignmentAutomata, label_slots
+    tie = np.array([5, 5, 7, 2, 7, 9], np.uint32)                       # labels 0,1 -> mixture 5; 2,4 -> 7
+    seg_a = ([[(1, 4, 0.0), (1, 2, 0.5), (0, 4, 1.0)], [(1, 1, 0.0)]], 0, {1: 0.0})
+    seg_b = ([[(0, 3, 0.0)], []], 0, {0: 1.0})
+    seg_c = ([[]], 0, {0: 0.0})                                         # no arcs: an empty label list
+    au = AlignmentAutomata.from_arc_lists([seg_a, seg_b, seg_c])
+    slots, lo, ids, mix = label_slots(au, tie)
+    assert lo.tolist() == [0, 3, 4, 4]
+    assert ids.tolist() == [4, 2, 1, 3] and mix.tolist() == [7, 7, 5, 2]
+    assert slots.arc_emission.tolist() == [0, 1, 0, 2, 0]
+    assert np.array_equal(slots.arc_target, au.arc_target) and np.array_equal(slots.arc_weight, au.arc_weight)
+    for i in range(3):                                                  # slot -> label -> the original arc labels
+        a0, a1 = int(au.arc_offsets[au.state_offsets[i]]), int(au.arc_offsets[au.state_offsets[i + 1]])
+        assert np.array_equal(ids[lo[i]:lo[i + 1]][slots.arc_emission[a0:a1]], au.arc_emission[a0:a1])
+
+
+def test_aligner_mirror_configuration_errors():
+    """rasr_b200.aligner.Aligner refuses what the device consumers do not do (as rasr/GpuAligner.cc: criticalError)."""
+    from rasr_b200.aligner import Aligner
+    with pytest.raises(ValueError):
+        Aligner({"min-weight": 0.01})
+    with pytest.raises(ValueError):
+        Aligner({"mode": "forward-backward"})
+    a = Aligner({"mode": "baum-welch"})
+    assert a.getMode() == Aligner.modeBaumWelch and not a.reachedFinalState()
+    a.selectMode(Aligner.modeViterbi)
+    assert a.getMode() == Aligner.modeViterbi
+    from rasr_b200.align import linear_hmm
+    a.setModel(linear_hmm([3, 4]), np.arange(10))
+    a.feed([])                                                          # no frames: the start state is not final
+    assert not a.reachedFinalState() and a.getAlignment() == []
+    a.setModel(([[(0, 1, 0.0)]], 0, {0: 2.5}), np.arange(10))
+    a.feed([])                                                          # no frames, final start state: its weight
+    assert a.reachedFinalState() and a.alignmentScore() == 2.5
