@@ -457,6 +457,54 @@ def test_direct_row_piece_stores_equal_staged_stores(eng, oracle, K, ld, monkeyp
     assert_float_close(direct[:, :ms.M], so)
 
 
+@pytest.mark.parametrize("K,ld", [(16, 308), (64, 304), (32, 304), (8, 320), (16, 301)])
+def test_full_sum_epilogue_variants_agree(eng, oracle, K, ld, monkeypatch):
+    """Full-sum scorer on uniform tiles (sixteen epilogue warps, twenty-warp launch with setmaxnreg): parts without dead
+    columns take an unpredicated pass and leave as row pieces from registers.  GMM_TC_SUM_FULL=0 forces the predicated
+    pass with its skip vote, GMM_TC_STORES=staged the staged stores: the stores change no bit, the passes agree to
+    rounding (different summation paths are NOT taken: same order, same terms -- identical bits expected as well), and
+    all of them meet the oracle; nothing is written beyond column M."""
+    ms = synth.make_model(M=301, K=K, D=45, seed=40 + K)
+    T = 333
+    x = synth.make_features(ms, T)
+    upload_float(eng, tables.float_tables(ms), mode=capi.MODE_SUM, kernel=capi.KERNEL_TENSOR)
+    dx = torch.from_numpy(x).cuda()
+
+    def run():
+        d = torch.full((T, ld), -123.0, dtype=torch.float32, device="cuda")
+        eng.score_device(T, dx, d, None, ld=ld)
+        eng.sync()
+        return d.cpu().numpy()
+
+    full = run()
+    monkeypatch.setenv("GMM_TC_STORES", "staged")
+    staged = run()
+    monkeypatch.setenv("GMM_TC_SUM_FULL", "0")
+    predicated = run()
+    assert np.array_equal(bits(full), bits(staged))
+    assert np.all(full[:, ms.M:] == -123.0) and np.all(predicated[:, ms.M:] == -123.0)
+    so, _ = oracle.score_sum(ms, x)
+    assert_float_close(full[:, :ms.M], so)
+    assert_float_close(predicated[:, :ms.M], so)
+    assert_float_close(full[:, :ms.M], predicated[:, :ms.M], rtol=2e-6)
+
+
+def test_sixteen_warp_maximum_kernel_matches_eight(eng, oracle, monkeypatch):
+    """GMM_TC_EPI_WARPS=16 selects the sixteen-warp epilogue for the maximum approximation too (twenty-warp launch,
+    setmaxnreg): same bits as the default eight-warp kernel."""
+    ms = synth.make_model(M=301, K=16, D=45, seed=61)
+    x = synth.make_features(ms, 333)
+    t = tables.float_tables(ms)
+    upload_float(eng, t, kernel=capi.KERNEL_TENSOR)
+    eight, _ = eng.score_host(x, want_best=False)
+    monkeypatch.setenv("GMM_TC_EPI_WARPS", "16")
+    upload_float(eng, t, kernel=capi.KERNEL_TENSOR)       # the epilogue width is chosen when the model is packed
+    sixteen, _ = eng.score_host(x, want_best=False)
+    assert np.array_equal(bits(eight), bits(sixteen))
+    so, _ = oracle.score_max(ms, x)
+    assert_float_close(sixteen, so)
+
+
 # ---------------------------------------------------------------------------------------------------
 # full-size configurations of BASELINE.json
 # ---------------------------------------------------------------------------------------------------
